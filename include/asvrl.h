@@ -1,0 +1,251 @@
+/*
+ * asvrl.h — C-ABI of libasvrl.so, the B200 (sm_100a) hot path of
+ * pszenher/Distributional_RL_Decision_and_Control's `rfarl` package.
+ *
+ * Nothing like this boundary exists in the reference (pure Python);
+ * each entry point below cites the reference code it replaces (paths relative to
+ * the reference root, abbreviations as in SURVEY.md):
+ *   ENV   = rfarl/rfarl/envs/marinenav/env.py
+ *   WAMV  = rfarl/rfarl/envs/marinenav/vehicles/wamv.py
+ *   AGENT = rfarl/rfarl/agent.py
+ *   ACIQN = rfarl/rfarl/policy/AC_IQN_model.py
+ *   IQN   = rfarl/rfarl/policy/IQN_model.py
+ *   RB    = rfarl/rfarl/utils/replay_buffer.py
+ *
+ * Conventions
+ *  - every function returns int: 0 = ok, >0 = a cudaError_t, <0 = ASVRL_E_* below;
+ *    no exceptions, no aborts, nothing is printed; asvrl_last_error_string() explains.
+ *  - all data pointers are DEVICE pointers on the current device, owned by the caller
+ *    (PyTorch's allocator in the shipped host code); the library allocates nothing
+ *    persistent and keeps no mutable global state besides the per-thread error string.
+ *  - kernels are enqueued on `stream` (a cudaStream_t passed as void*) and the call
+ *    returns without synchronising.
+ *  - the same structs are consumed by the CPU oracle (oracle/asv_oracle.c), which is
+ *    test infrastructure only, with HOST pointers and float64 arrays.
+ */
+#ifndef ASVRL_H_
+#define ASVRL_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ASVRL_VERSION 100 /* 0.1.0 */
+
+/* fixed by the network input shape ((1,7),(1,5,5),(1,5)): WAMV:14, AGENT:20-22 */
+#define ASVRL_MAX_OBJ 5
+#define ASVRL_SELF_DIM 7
+#define ASVRL_OBJ_DIM 5
+/* noise draws per candidate object: N px, N py, N vx, N vy, vonMises r  (WAMV:27-40) */
+#define ASVRL_NOISE_DIM 5
+/* hard limit on candidate slots (max_obs + max_robots) per ego: detected mask is 64 bit */
+#define ASVRL_MAX_SLOTS 64
+
+/* library error codes (negative) */
+#define ASVRL_E_BADARG (-1)
+#define ASVRL_E_LIMIT (-2)  /* a size exceeds a compiled limit */
+#define ASVRL_E_NODEV (-3)
+
+/* per-ASV sticky flags word (state.flags), WAMV:130-132 */
+#define ASVRL_F_COLLISION 1u
+#define ASVRL_F_REACH_GOAL 2u
+#define ASVRL_F_DEACTIVATED 4u
+
+/* per-ASV status word written by a step (out.status):
+ *   bit 0      done                      ENV:290-328
+ *   bit 1      collision   (sticky, after this step's perception)
+ *   bit 2      reach_goal  (sticky, after this step's perception)
+ *   bit 3      deactivated (value the step STARTED with; the transition of a robot that was
+ *              already deactivated is not stored, TRAINER:157-159)
+ *   bit 4      apply_COLREGs             WAMV:517-521
+ *   bits 8..11 info code below           ENV:291-328
+ */
+#define ASVRL_S_DONE 1u
+#define ASVRL_S_COLLISION 2u
+#define ASVRL_S_REACH_GOAL 4u
+#define ASVRL_S_WAS_DEACTIVATED 8u
+#define ASVRL_S_COLREGS 16u
+#define ASVRL_S_INFO_SHIFT 8
+#define ASVRL_INFO_NORMAL 0
+#define ASVRL_INFO_COLLISION 1
+#define ASVRL_INFO_REACH_GOAL 2
+#define ASVRL_INFO_TOO_LONG 3
+#define ASVRL_INFO_DEACT_COLLISION 4
+#define ASVRL_INFO_DEACT_GOAL 5
+#define ASVRL_INFO_DEACT_INVALID 6 /* ENV:303 RuntimeError case */
+#define ASVRL_INFO_ABSENT 7        /* padding slot r >= n_robots[env] */
+
+/* step mode bits */
+#define ASVRL_M_DYNAMICS 1u        /* 0 = perception only (ENV:341-356 as used by reset, ENV:164) */
+#define ASVRL_M_DISCRETE 2u        /* actions are int32 ids into the 5x5 thrust table, WAMV:146-147,225 */
+#define ASVRL_M_AUTO_DEACTIVATE 4u /* fold TRAINER:168-170 into the step (batched API) */
+
+/* All scalar parameters of the path, float64 as in the reference.  The CUDA library rounds
+ * them to fp32 once per launch.  One parameter set per batch (the reference allows per-robot
+ * hull parameters through reset_with_eval_config, ENV:551-607; every shipped config uses the
+ * defaults, and the host façade rejects heterogeneous robots). */
+typedef struct asvrl_env_params {
+  /* integration, WAMV:46-47 */
+  double dt;
+  int32_t n_substeps;
+  int32_t max_episode_steps; /* ENV:312 (1000) */
+  /* hull, WAMV:51-54,79,84-87 */
+  double length, width, robot_r, goal_dis;
+  double min_thrust, max_thrust;
+  double thrust_rate;           /* continuous action scale, N/s per unit action (1000), WAMV:222-223 */
+  double thrust_change_l[5];    /* discrete deltas N/s, WAMV:86 */
+  double thrust_change_r[5];    /* WAMV:87 */
+  double left_pos, right_pos;   /* thruster angles, WAMV:98-99,137-138 (0 in training) */
+  /* rigid body + hydrodynamic derivatives, WAMV:103-125 */
+  double m, Izz;
+  double xDotU, yDotV, yDotR, nDotR, nDotV;
+  double xU, xUU, yV, yVV, yR, yRV, yVR, yRR, nR, nRR, nV, nVV, nRV, nVR;
+  /* perception, WAMV:12-25 */
+  double perc_range, perc_angle;
+  double pos_std, vel_std, r_kappa, r_mean_ratio;
+  /* COLREGs zones, WAMV:73-76,400-406 */
+  double head_on_x, head_on_y;
+  double lc_x0, lc_x1, lc_y0, lc_y1; /* left-crossing x in [-9,12], y in [-17,0], cut at y=-7 */
+  double colregs_min_speed;          /* 0.5 */
+  /* rewards, ENV:47-50 */
+  double timestep_penalty, colregs_penalty, collision_penalty, goal_reward;
+  /* current field, ENV:35 */
+  double core_r;
+  /* extension terms with NO reference counterpart: uniform wind/wave drift
+   * velocity added to the current, world frame.  Must be 0 for parity; default 0. */
+  double drift_vx, drift_vy;
+} asvrl_env_params;
+
+/* Structure-of-arrays environment state in HBM.  E = n_envs, RP = max_robots (robot index
+ * fastest), OP = max_obs, CP = max_cores.  The 13 per-ASV floats are the persistent attributes
+ * of WAMV.Robot (WAMV:92-101,128-129); `vel_*` is the STALE sea-floor velocity. */
+typedef struct asvrl_env_state {
+  float* x;        /* [E][RP] */
+  float* y;
+  float* theta;
+  float* velr_x;   /* velocity_r, world frame, relative to water */
+  float* velr_y;
+  float* velr_r;
+  float* vel_x;    /* velocity, world frame, over ground (stale by one sub-step) */
+  float* vel_y;
+  float* vel_r;
+  float* thrust_l;
+  float* thrust_r;
+  float* goal_x;
+  float* goal_y;
+  uint32_t* flags;    /* [E][RP] ASVRL_F_* */
+  int32_t* n_robots;  /* [E] */
+  int32_t* n_obs;     /* [E] */
+  int32_t* n_cores;   /* [E] */
+  int32_t* ep_steps;  /* [E] episode_timesteps, ENV:64,330 */
+  float* obstacles;   /* [E][OP][4] = x, y, r, 0         ENV:16-22 */
+  float* cores;       /* [E][CP][4] = x, y, +1 clockwise / -1 counter-clockwise, Gamma   ENV:7-14 */
+} asvrl_env_state;
+
+/* Everything one step produces besides the in-place state update. */
+typedef struct asvrl_env_out {
+  float* obs_self;     /* [E][RP][7]      WAMV:443-453 */
+  float* obs_objects;  /* [E][RP][5][5]   WAMV:513-515, zero padded (RB:64) */
+  float* obs_mask;     /* [E][RP][5]      1 = object present (RB:65) */
+  float* reward;       /* [E][RP]         ENV:271-277,310-323 */
+  uint32_t* status;    /* [E][RP]         ASVRL_S_* */
+  float* phi;          /* [E][RP]         COLREGs turn angle, valid when ASVRL_S_COLREGS */
+  int32_t* top_ids;    /* [E][RP][5]      candidate slot of each kept object (obstacle i -> i,
+                                          robot j -> OP + j), -1 = empty; nullable */
+  uint64_t* detected;  /* [E][RP]         bit s = candidate slot s detected (observed_obs /
+                                          observed_objs, WAMV:473,500); nullable */
+  uint32_t* env_status;/* [E]             bit0 all deactivated (ENV:178-184), bit1 timeout
+                                          (ep_steps BEFORE this step >= max), bit2 any collision
+                                          (ENV:194-200), bit3 all reach goal (ENV:186-192);
+                                          low two bits != 0 <=> episode over (TRAINER:172) */
+} asvrl_env_out;
+
+int asvrl_version(void);
+const char* asvrl_last_error_string(void);
+/* fills *p with the reference defaults (WAMV:45-126, ENV:33-54) */
+void asvrl_env_default_params(asvrl_env_params* p);
+
+/* K1 — replaces MarineNavEnv3.step (ENV:240-333) incl. Robot.update_state/compute_motion
+ * (WAMV:204-279), get_velocity (ENV:458-501), get_observations/perception_output
+ * (ENV:341-356, WAMV:436-529), COLREGs (WAMV:324-423) and reward/done (ENV:271-328).
+ *   actions   [E][RP][2] float (continuous) or [E][RP] int32 (ASVRL_M_DISCRETE); ignored for
+ *             deactivated robots (the reference passes None, TRAINER:112-114)
+ *   noise     nullable [E][RP][OP+RP][5] float injected sensor noise in draw order
+ *             (n_px, n_py, n_vx, n_vy already scaled by std; raw von Mises sample w); slot of
+ *             obstacle i is i, of robot j is OP+j.  NULL = in-kernel Philox4x32-10 keyed on
+ *             (seed; env_offset+env, ego, slot, step).
+ *   env_offset  global index of local env 0 (multi-GPU sharding keeps streams invariant) */
+int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_state* state,
+                   const void* actions, const float* noise, uint64_t seed, uint64_t step,
+                   const asvrl_env_out* out, int n_envs, int max_robots, int max_obs,
+                   int max_cores, int64_t env_offset, uint32_t mode, void* stream);
+
+/* K1b — replaces MarineNavEnv3.reset (ENV:72-176) for every env with reset_mask != 0
+ * (NULL = all): rejection-samples starts/goals, cores, obstacles with the reference's
+ * acceptance rules (ENV:358-456), zeroes velocity/thrust, draws theta0.  Counts requested per
+ * env come from want_robots/want_cores/want_obs [E] (the curriculum lookup ENV:75-87 is done by
+ * the host).  Perception of the fresh state is a following asvrl_env_step(mode=0). */
+int asvrl_env_reset(const asvrl_env_params* params, const asvrl_env_state* state,
+                    const uint8_t* reset_mask, const int32_t* want_robots,
+                    const int32_t* want_cores, const int32_t* want_obs,
+                    const float* min_start_goal_dis /* [E] */, uint64_t seed, uint64_t episode,
+                    int n_envs, int max_robots, int max_obs, int max_cores, int64_t env_offset,
+                    void* stream);
+
+/* Replay rows are dense float32[ASVRL_ROW] records: RB:22-69 + AGENT:360-368,387-392 */
+#define ASVRL_ROW_SELF 0     /* 7  */
+#define ASVRL_ROW_OBJ 7      /* 25 */
+#define ASVRL_ROW_NOBJ 32    /* 1: number of valid objects (mask = first n ones) */
+#define ASVRL_ROW_ACT 33     /* 2: continuous action, or (float)id, 0 */
+#define ASVRL_ROW_REW 35     /* 1 */
+#define ASVRL_ROW_NSELF 36   /* 7  */
+#define ASVRL_ROW_NOBJ_F 43  /* 25 */
+#define ASVRL_ROW_NNOBJ 68   /* 1 */
+#define ASVRL_ROW_DONE 69    /* 1 */
+#define ASVRL_ROW 70
+
+/* K2a — replaces ReplayBuffer.add over a whole batched step (RB:22-24, TRAINER:157-166):
+ * appends one row per ASV whose status has neither ASVRL_S_WAS_DEACTIVATED nor
+ * ASVRL_INFO_ABSENT, in (env, robot) order, at ring position *head (device counters
+ * head_size[0] = total rows ever written, head_size[1] = rows valid = min(total, capacity)). */
+int asvrl_replay_push(float* rows, int64_t capacity, uint64_t* head_size,
+                      const float* obs_self, const float* obs_objects, const float* obs_mask,
+                      const void* actions, int discrete, const float* reward,
+                      const float* next_self, const float* next_objects, const float* next_mask,
+                      const uint32_t* status, int n_asv, void* stream);
+
+/* K2b — replaces ReplayBuffer.sample + state_batch + Agent.state_to_tensor (RB:26-69,
+ * AGENT:387-392): draws `batch` distinct uniform row indices (keyed Feistel permutation of
+ * [0,size), i.e. sampling without replacement like random.sample, RB:28) or takes them from
+ * `indices` (int64[batch], nullable) and gathers into dense tensors. */
+int asvrl_replay_sample(const float* rows, const uint64_t* head_size, int64_t capacity,
+                        const int64_t* indices, uint64_t seed, uint64_t counter, int batch,
+                        float* self_b, float* obj_b, float* mask_b, float* act_b, float* rew_b,
+                        float* nself_b, float* nobj_b, float* nmask_b, float* done_b,
+                        int64_t* indices_out /* nullable */, void* stream);
+
+/* K3 — replaces Critic.calc_cos / IQN_Policy.calc_cos (ACIQN:410-426, IQN:56-72):
+ * tau = U(0,1) * cvar (Philox keyed on seed,counter) unless tau_in is given; cos_out[b][n][i] =
+ * cos(tau * float32(pi*i)), i < n_cos.  tau_out [B][N], cos_out [B][N][n_cos]. */
+int asvrl_iqn_tau_cos(const float* tau_in /* nullable */, uint64_t seed, uint64_t counter,
+                      float cvar, int batch, int n_tau, int n_cos, float* tau_out,
+                      float* cos_out, void* stream);
+
+/* K4 — replaces the loss core of Agent.train_AC_IQN / train_IQN (AGENT:401-412, 455-467,
+ * 701-707) and its autograd backward:
+ *   T_bj = r_b + gamma (1 - d_b) Z'_bj ; delta_bij = T_bj - Z_bi ;
+ *   loss_b = (1/N') sum_j sum_i |tau_bi - 1[delta<0]| * huber_kappa(delta) / kappa... (kappa=1)
+ *   loss   = mean_b loss_b ;  grad_z_bi = dloss/dZ_bi.
+ * z [B][N], tau [B][N], z_next [B][N'], r [B], done [B]; outputs loss_per_sample [B],
+ * grad_z [B][N], loss [1].  workspace: one zero-initialised uint32 (left zero on completion). */
+int asvrl_qhuber_fwd_bwd(const float* z, const float* tau, const float* z_next, const float* r,
+                         const float* done, float gamma, float kappa, int batch, int n, int n_next,
+                         float* loss_per_sample, float* grad_z, float* loss, uint32_t* workspace,
+                         void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ASVRL_H_ */

@@ -1,0 +1,260 @@
+#!/usr/bin/env python
+"""bench.py — batched ASV env-steps/s on B200 (BASELINE.json config 2), one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A "step" is one pass of the hot path over one batch: every ASV of every env takes one action
+(10 physics sub-steps, current field, perception, COLREGs, reward/done — kernel K1), finished
+episodes are re-generated (K1b) and re-observed (K1, perception only, masked).
+  value  = env-steps/s with actions resident in HBM (device time, CUDA events, L2 flushed
+           between steps, max over ranks);
+  e2e    = the same through BatchedMarineNavEnv.step_host with HOST buffers: pinned actions
+           H2D and observations / rewards / status D2H inside the timed region;
+  roofline = algorithmic bytes of K1 (280 R + 12 O + 16 C + 8 per env-step)
+           / K1's own average launch duration, against MEASURED_PEAKS.json's hbm_gbs;
+  cpu_baseline = the float64 C port of the reference (oracle/, pinned against the Python
+           reference by tests/golden) on the box's host threads, bounded sample.
+`--impl reference` times that CPU port alone (the Python reference cannot travel to the GPU
+box; DESIGN.md records its speed measured in the build container).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+R, O = 8, 10  # BASELINE config 2: 8 ASVs x 10 buoys per env
+
+
+def alg_bytes_per_env_step(r, o, c):
+    return 280 * r + 12 * o + 16 * c + 8
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                r = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                    "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                   timeout=5)
+                if r.returncode == 0 and r.stdout.strip():
+                    self.rows.append([c.strip() for c in r.stdout.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        sm = sorted(int(float(r[0])) for r in self.rows if r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0):
+    """env-steps/s of the float64 C port of the reference on `cores` host threads.  Bounded
+    sample: n_envs envs x n_steps steps of the same workload shape (in-port Philox noise)."""
+    import numpy as np
+    from distributional_rl_decision_and_control_b200 import _abi
+    from oracle import oracle, scenes
+    p = _abi.default_params()
+    st = scenes.random_scene(seed, n_envs, R, O, c_cores, box=50.0, p_deact=0.0, p_timeout=0.0, ragged=False)
+    st["flags"][:] = 0
+    st["ep_steps"][:] = 0
+    out = oracle.new_out(n_envs, R)
+    acts = [scenes.random_actions(seed + i, n_envs, R, False) for i in range(4)]
+    mode = _abi.M_DYNAMICS  # no deactivation: every ASV integrates every step (upper bound on work)
+    oracle.env_step(p, st, acts[0], None, mode, O, c_cores, seed=1, step=0, n_threads=cores, out=out, margins=False)
+    t0 = time.perf_counter()
+    for i in range(n_steps):
+        oracle.env_step(p, st, acts[i % 4], None, mode, O, c_cores, seed=1, step=i + 1, n_threads=cores,
+                        out=out, margins=False)
+    dt = time.perf_counter() - t0
+    assert np.isfinite(out["reward"]).all()
+    return n_envs * n_steps / dt, dt
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from distributional_rl_decision_and_control_b200 import _lib
+    from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()
+    E, C, K, W = args.envs, args.cores, args.steps, max(args.warmup, 3)
+
+    # envs partition across ranks with no data-path collective: rank r owns global envs
+    # [r*E, (r+1)*E); the RNG counters carry the global index (results invariant to N)
+    env = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed, env_offset=rank * E)
+    env.reset()
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    pool = [torch.rand((E, R, 2), device=dev, generator=gen) * 2 - 1 for _ in range(8)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):
+        env.step(pool[i % 8])
+    sampler = ClockSampler(local)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    launches0 = env.launches
+    barrier()
+    sampler.start()
+    for i in range(K):
+        flush.zero_()  # L2 flush between timed iterations (not timed)
+        ev[i][0].record()
+        env.step_no_reset(pool[i % 8])  # K1
+        ev[i][1].record()
+        env.finish_episodes()           # K1b + masked perception-only K1
+        ev[i][2].record()
+    barrier()
+    step_ms = sum(e[0].elapsed_time(e[2]) for e in ev)
+    k1_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
+    launches = env.launches - launches0
+
+    # ---- e2e: host buffers in, host buffers out, through the public API ----
+    pin = dict(pin_memory=True)
+    host_actions = [p.cpu().pin_memory() for p in pool]
+    host_out = {"reward": torch.empty((E, R), **pin), "status": torch.empty((E, R), dtype=torch.int32, **pin),
+                "obs_self": torch.empty((E, R, 7), **pin), "obs_objects": torch.empty((E, R, 5, 5), **pin),
+                "obs_mask": torch.empty((E, R, 5), **pin)}
+    for i in range(W):
+        env.step_host(host_actions[i % 8], host_out)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        env.step_host(host_actions[i % 8], host_out)
+        torch.cuda.synchronize()  # the caller reads host_out now
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    times = torch.tensor([step_ms, k1_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    step_ms, k1_ms, e2e_ms = (float(x) for x in times.tolist())
+    finite = bool(torch.isfinite(env.out["reward"]).all().item())
+
+    if rank == 0:
+        peak, which = measured_peak()
+        c_in_use = C
+        per_launch = alg_bytes_per_env_step(R, O, c_in_use) * E
+        achieved = per_launch / (k1_ms / K * 1e-3) / 1e9
+        line = {
+            "metric": "env_steps_per_sec", "value": world * E * K / (step_ms * 1e-3), "unit": "env-steps/s",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": f"C2 batched env-step: {E} envs x {R} ASVs x {O} buoys x {C} vortex cores per GPU, "
+                                   "continuous actions, in-kernel Philox sensor noise, auto-deactivate + auto-reset",
+                       "envs_per_gpu": E, "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
+                       "l2": "flushed between timed steps (256 MiB write)", "parallelism": f"envs sharded x{world}, no collective"},
+            "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
+                    "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": E * R * (7 + 25 + 5 + 1 + 1) * 4},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": which,
+                         "kernel": "env_step_kernel<false>", "kernel_ms": k1_ms / K,
+                         "algorithmic_bytes_per_launch": per_launch,
+                         "note": "instruction-issue bound by design (SURVEY.md F5); see profiles/"},
+            "clocks": sampler.summary(), "finite": finite,
+        }
+        if world == 1 and not args.no_cpu:
+            cores = host_threads()
+            v, dt = cpu_port_throughput(args.cpu_envs, args.cpu_steps, cores, C)
+            line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                                    "sample": f"{args.cpu_envs} envs x {args.cpu_steps} steps of the same shape, "
+                                              f"float64 C port of the reference, {dt:.1f} s"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """The reference's CPU implementation of the path, as its float64 C port (the Python
+    reference does not travel to the GPU box), on all host threads.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = host_threads()
+    K, W = args.steps, max(args.warmup, 1)
+    n = args.cpu_envs
+    cpu_port_throughput(n, W, cores, args.cores)
+    v, dt = cpu_port_throughput(n, K, cores, args.cores)
+    line = {"impl": "reference", "metric": "env_steps_per_sec", "value": v, "unit": "env-steps/s",
+            "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": K, "warmup": W,
+            "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C2 batched env-step shape: {R} ASVs x {O} buoys x {args.cores} vortex cores; "
+                                   f"each step a bounded sample of {n} envs"},
+            "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                             "sample": f"{n} envs x {K} steps, float64 C port of the reference"},
+            "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--envs", type=int, default=4096, help="envs per GPU (BASELINE config 2: 4096)")
+    ap.add_argument("--cores", type=int, default=8, help="vortex cores per env (the current disturbance)")
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--cpu-envs", type=int, default=2048)
+    ap.add_argument("--cpu-steps", type=int, default=40)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

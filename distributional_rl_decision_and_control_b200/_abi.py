@@ -123,7 +123,7 @@ class EnvStatePtrs(C.Structure):
 
 
 OUT_FIELDS = ("obs_self", "obs_objects", "obs_mask", "reward", "status", "phi", "top_ids",
-              "detected", "env_status")
+              "detected", "env_status", "ended")
 
 
 class EnvOutPtrs(C.Structure):

@@ -1,0 +1,217 @@
+"""ctypes loader of libasvrl.so (the C-ABI of include/asvrl.h) and torch-tensor call wrappers.
+
+There is NO fallback: ``lib()`` raises if the shared library is missing or a symbol is absent,
+and every compute wrapper raises if its tensors are not CUDA tensors.  PyTorch is used for
+device memory and streams only; the kernels are the hand-written sm_100a ones in ``csrc/``.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from . import _abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libasvrl.so")
+_LIB = None
+
+u8p, i32p, u32p, u64p, i64p, f32p, vp = (C.c_void_p,) * 7
+
+_SIGNATURES = {
+    "asvrl_version": (C.c_int, []),
+    "asvrl_last_error_string": (C.c_char_p, []),
+    "asvrl_env_default_params": (None, [C.POINTER(_abi.EnvParams)]),
+    "asvrl_reset_default_params": (None, [C.c_void_p]),
+    "asvrl_env_step": (C.c_int, [C.POINTER(_abi.EnvParams), C.POINTER(_abi.EnvStatePtrs), vp, f32p,
+                                 u8p, C.c_uint64, C.c_uint64, C.POINTER(_abi.EnvOutPtrs), C.c_int,
+                                 C.c_int, C.c_int, C.c_int, C.c_int64, C.c_uint32, vp]),
+    "asvrl_env_noise": (C.c_int, [C.POINTER(_abi.EnvParams), C.c_uint64, C.c_uint64, C.c_int,
+                                  C.c_int, C.c_int, C.c_int64, f32p, vp]),
+    "asvrl_env_reset": (C.c_int, [C.c_void_p, C.POINTER(_abi.EnvStatePtrs), u8p, i32p, i32p, i32p,
+                                  f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
+                                  C.c_int64, vp]),
+    "asvrl_replay_push": (C.c_int, [f32p, C.c_int64, u64p, f32p, f32p, f32p, vp, C.c_int, f32p,
+                                    f32p, f32p, f32p, u32p, C.c_int, u32p, vp]),
+    "asvrl_replay_sample": (C.c_int, [f32p, u64p, C.c_int64, i64p, C.c_uint64, C.c_uint64, C.c_int,
+                                      f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, i64p,
+                                      vp]),
+    "asvrl_iqn_tau_cos": (C.c_int, [f32p, C.c_uint64, C.c_uint64, C.c_float, C.c_int, C.c_int,
+                                    C.c_int, f32p, f32p, vp]),
+    "asvrl_qhuber_fwd_bwd": (C.c_int, [f32p, f32p, f32p, f32p, f32p, C.c_float, C.c_float, C.c_int,
+                                       C.c_int, C.c_int, f32p, f32p, f32p, u32p, vp]),
+}
+EXPORTED = tuple(_SIGNATURES)
+
+
+class ResetParams(C.Structure):
+    """asvrl_reset_params (ENV:33-41, 107-155)."""
+    _fields_ = [(n, C.c_double) for n in ("map_w", "map_h", "start_margin", "obs_margin", "clear_r",
+                                          "core_r", "v_rel_max", "p", "v_min", "v_max", "obs_r_min",
+                                          "obs_r_max")] + [("max_tries", C.c_int32),
+                                                           ("reserved", C.c_int32)]
+
+
+def lib():
+    """The loaded library; raises (never falls back) when it is missing or incomplete."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(
+                f"{SO_PATH} is missing: build it with `python -m "
+                "distributional_rl_decision_and_control_b200.csrc.build` (there is no CPU fallback)")
+        so = C.CDLL(SO_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(so, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        if so.asvrl_version() != _abi.VERSION:
+            raise RuntimeError(f"libasvrl.so version {so.asvrl_version()} != header {_abi.VERSION}")
+        _LIB = so
+    return _LIB
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().asvrl_last_error_string().decode(errors="replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+def default_reset_params():
+    p = ResetParams()
+    lib().asvrl_reset_default_params(C.byref(p))
+    return p
+
+
+def ptr(t, dtype=None):
+    """Raw device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("libasvrl works on CUDA tensors only (no CPU fallback)")
+    if not t.is_contiguous():
+        raise RuntimeError("tensor must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"expected {dtype}, got {t.dtype}")
+    return t.data_ptr()
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ------------------------------------------------------------------ typed call wrappers
+def state_ptrs(st):
+    s = _abi.EnvStatePtrs()
+    for n in _abi.STATE_FLOAT_FIELDS:
+        setattr(s, n, ptr(st[n], torch.float32))
+    s.flags = ptr(st["flags"], torch.int32)
+    for n in _abi.STATE_ENV_INT_FIELDS:
+        setattr(s, n, ptr(st[n], torch.int32))
+    s.obstacles = ptr(st["obstacles"], torch.float32)
+    s.cores = ptr(st["cores"], torch.float32)
+    return s
+
+
+def out_ptrs(out):
+    o = _abi.EnvOutPtrs()
+    o.obs_self = ptr(out["obs_self"], torch.float32)
+    o.obs_objects = ptr(out["obs_objects"], torch.float32)
+    o.obs_mask = ptr(out["obs_mask"], torch.float32)
+    o.reward = ptr(out["reward"], torch.float32)
+    o.status = ptr(out["status"], torch.int32)
+    o.phi = ptr(out["phi"], torch.float32)
+    o.top_ids = ptr(out.get("top_ids"), torch.int32)
+    o.detected = ptr(out.get("detected"), torch.int64)
+    o.env_status = ptr(out["env_status"], torch.int32)
+    o.ended = ptr(out.get("ended"), torch.uint8)
+    return o
+
+
+def new_state(E, RP, OP, CP, device):
+    """Zeroed SoA env state in HBM (layout of asvrl_env_state; flags/status are int32 views of
+    the header's uint32 words, `detected` an int64 view of uint64)."""
+    st = {n: torch.zeros((E, RP), dtype=torch.float32, device=device) for n in _abi.STATE_FLOAT_FIELDS}
+    st["flags"] = torch.zeros((E, RP), dtype=torch.int32, device=device)
+    for n in _abi.STATE_ENV_INT_FIELDS:
+        st[n] = torch.zeros((E,), dtype=torch.int32, device=device)
+    st["obstacles"] = torch.zeros((E, max(OP, 1), 4), dtype=torch.float32, device=device)
+    st["cores"] = torch.zeros((E, max(CP, 1), 4), dtype=torch.float32, device=device)
+    return st
+
+
+def new_out(E, RP, device, debug=True):
+    out = {
+        "obs_self": torch.zeros((E, RP, 7), dtype=torch.float32, device=device),
+        "obs_objects": torch.zeros((E, RP, 5, 5), dtype=torch.float32, device=device),
+        "obs_mask": torch.zeros((E, RP, 5), dtype=torch.float32, device=device),
+        "reward": torch.zeros((E, RP), dtype=torch.float32, device=device),
+        "status": torch.zeros((E, RP), dtype=torch.int32, device=device),
+        "phi": torch.zeros((E, RP), dtype=torch.float32, device=device),
+        "env_status": torch.zeros((E,), dtype=torch.int32, device=device),
+        "ended": torch.zeros((E,), dtype=torch.uint8, device=device),
+    }
+    if debug:
+        out["top_ids"] = torch.full((E, RP, 5), -1, dtype=torch.int32, device=device)
+        out["detected"] = torch.zeros((E, RP), dtype=torch.int64, device=device)
+    return out
+
+
+def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, step=0,
+             env_offset=0, env_mask=None, st_ptrs=None, o_ptrs=None):
+    E, RP = st["x"].shape
+    if actions is not None:
+        want = torch.int32 if (mode & _abi.M_DISCRETE) else torch.float32
+        a_ptr = ptr(actions, want)
+    else:
+        a_ptr = None
+    sp = st_ptrs if st_ptrs is not None else state_ptrs(st)
+    op = o_ptrs if o_ptrs is not None else out_ptrs(out)
+    rc = lib().asvrl_env_step(C.byref(params), C.byref(sp), a_ptr, ptr(noise, torch.float32),
+                              ptr(env_mask, torch.uint8), seed, step, C.byref(op), E, RP, max_obs,
+                              max_cores, env_offset, mode, stream_ptr())
+    check(rc, "asvrl_env_step")
+    return out
+
+
+def env_noise(params, seed, step, E, RP, OP, device, env_offset=0):
+    out = torch.empty((E, RP, OP + RP, 5), dtype=torch.float32, device=device)
+    rc = lib().asvrl_env_noise(C.byref(params), seed, step, E, RP, OP, env_offset, ptr(out),
+                               stream_ptr())
+    check(rc, "asvrl_env_noise")
+    return out
+
+
+def env_reset(rparams, st, reset_mask, want_robots, want_cores, want_obs, min_sg, seed, episode,
+              max_obs, max_cores, env_offset=0, st_ptrs=None):
+    E, RP = st["x"].shape
+    sp = st_ptrs if st_ptrs is not None else state_ptrs(st)
+    rc = lib().asvrl_env_reset(C.byref(rparams), C.byref(sp), ptr(reset_mask, torch.uint8),
+                               ptr(want_robots, torch.int32), ptr(want_cores, torch.int32),
+                               ptr(want_obs, torch.int32), ptr(min_sg, torch.float32), seed, episode,
+                               E, RP, max_obs, max_cores, env_offset, stream_ptr())
+    check(rc, "asvrl_env_reset")
+
+
+def qhuber_fwd_bwd(z, tau, z_next, r, done, gamma, kappa, workspace, lps=None, grad=None, loss=None):
+    B, N = z.shape
+    Np = z_next.shape[1]
+    dev = z.device
+    lps = torch.empty((B,), dtype=torch.float32, device=dev) if lps is None else lps
+    grad = torch.empty((B, N), dtype=torch.float32, device=dev) if grad is None else grad
+    loss = torch.empty((1,), dtype=torch.float32, device=dev) if loss is None else loss
+    rc = lib().asvrl_qhuber_fwd_bwd(ptr(z, torch.float32), ptr(tau, torch.float32),
+                                    ptr(z_next, torch.float32), ptr(r, torch.float32),
+                                    ptr(done, torch.float32), gamma, kappa, B, N, Np, ptr(lps),
+                                    ptr(grad), ptr(loss), ptr(workspace, torch.int32), stream_ptr())
+    check(rc, "asvrl_qhuber_fwd_bwd")
+    return loss, lps, grad
+
+
+def iqn_tau_cos(B, N, n_cos, device, tau_in=None, seed=0, counter=0, cvar=1.0, tau_out=None,
+                cos_out=None):
+    tau_out = torch.empty((B, N), dtype=torch.float32, device=device) if tau_out is None else tau_out
+    cos_out = torch.empty((B, N, n_cos), dtype=torch.float32, device=device) if cos_out is None else cos_out
+    rc = lib().asvrl_iqn_tau_cos(ptr(tau_in, torch.float32), seed, counter, cvar, B, N, n_cos,
+                                 ptr(tau_out), ptr(cos_out), stream_ptr())
+    check(rc, "asvrl_iqn_tau_cos")
+    return tau_out, cos_out

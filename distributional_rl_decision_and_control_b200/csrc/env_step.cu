@@ -1,0 +1,595 @@
+// env_step.cu — K1: one batched MarineNavEnv3.step for thousands of environments (sm_100a).
+//
+// Replaces, for every env of the batch in ONE launch (reference paths under rfarl/rfarl/):
+//   envs/marinenav/env.py:240-333        MarineNavEnv3.step
+//   envs/marinenav/env.py:458-501        get_velocity / compute_speed (vortex current)
+//   envs/marinenav/vehicles/wamv.py:204-279  Robot.update_state / compute_motion
+//   envs/marinenav/vehicles/wamv.py:436-529  Robot.perception_output (+ 281-322 helpers)
+//   envs/marinenav/vehicles/wamv.py:324-423  COLREGs zone tests and turn angle
+//   policy/trainer.py:168-170            deactivation, when ASVRL_M_AUTO_DEACTIVATE
+//
+// Mapping.  A CTA owns EPB consecutive environments (EPB*RP ~ one warp of ASVs):
+//   phase 0  the CTA stages the env's buoy and vortex tables in shared memory;
+//   phase A  one thread per ASV integrates the 3-DOF model for the 10 sub-steps (pose carried in
+//            fp64 registers so the progress reward does not cancel), SoA loads
+//            and stores are coalesced over the robot-fastest layout;
+//   phase B  the (ego, candidate) pairs of the CTA's envs are flattened over ALL threads: noise
+//            (injected table or in-kernel Philox), detection / collision predicates in fp64,
+//            body-frame observation and sort key into a shared-memory candidate table;
+//   phase C  one thread per ego: stable top-5 by key, COLREGs, reward / done / info;
+//   phase D  the CTA writes the padded observation rows back with coalesced stores.
+// The kernel is instruction-issue bound (about 1e4 thread instructions per 280 algorithmic
+// bytes); HBM traffic is one pass over state in, state + observations out.
+#include <math.h>
+
+#include "env_consts.cuh"
+
+namespace asvrl {
+
+struct StatePtrs {
+  float *x, *y, *theta, *velr_x, *velr_y, *velr_r, *vel_x, *vel_y, *vel_r, *thrust_l, *thrust_r;
+  const float *goal_x, *goal_y;
+  uint32_t* flags;
+  const int32_t *n_robots, *n_obs, *n_cores;
+  int32_t* ep_steps;
+  const float4* obstacles;
+  const float4* cores;
+};
+
+struct OutPtrs {
+  float *obs_self, *obs_objects, *obs_mask, *reward;
+  uint32_t* status;
+  float* phi;
+  int32_t* top_ids;
+  unsigned long long* detected;
+  uint32_t* env_status;
+  uint8_t* ended;
+};
+
+// shared-memory carve-up, identical on host (size) and device (pointers)
+struct Smem {
+  double *px, *py, *key;
+  float *c, *s, *vx, *vy, *vz, *Tl, *Tr, *gx, *gy, *rew, *cand, *st_obj, *st_self, *st_mask;
+  uint32_t *fl0, *fl, *det_lo, *det_hi;
+  int *nr, *no, *nc, *ep, *ok;
+  float4 *obst, *cores;
+  size_t bytes;
+};
+
+__host__ __device__ inline Smem carve(char* base, int EPB, int RP, int OP, int CP) {
+  Smem m;
+  const int A = EPB * RP, S = OP + RP, SK = S | 1;
+  size_t off = 0;
+  auto take = [&](size_t n, size_t elem) { size_t o = off; off += ((n * elem + 15) / 16) * 16; return base + o; };
+  m.px = (double*)take(A, 8); m.py = (double*)take(A, 8);
+  m.key = (double*)take((size_t)A * SK, 8);
+  m.obst = (float4*)take((size_t)EPB * (OP > 0 ? OP : 1), 16);
+  m.cores = (float4*)take((size_t)EPB * (CP > 0 ? CP : 1), 16);
+  m.c = (float*)take(A, 4); m.s = (float*)take(A, 4);
+  m.vx = (float*)take(A, 4); m.vy = (float*)take(A, 4); m.vz = (float*)take(A, 4);
+  m.Tl = (float*)take(A, 4); m.Tr = (float*)take(A, 4);
+  m.gx = (float*)take(A, 4); m.gy = (float*)take(A, 4); m.rew = (float*)take(A, 4);
+  m.cand = (float*)take((size_t)A * S * 5, 4);
+  m.st_obj = (float*)take((size_t)A * 25, 4);
+  m.st_self = (float*)take((size_t)A * 7, 4);
+  m.st_mask = (float*)take((size_t)A * 5, 4);
+  m.fl0 = (uint32_t*)take(A, 4); m.fl = (uint32_t*)take(A, 4);
+  m.det_lo = (uint32_t*)take(A, 4); m.det_hi = (uint32_t*)take(A, 4);
+  m.nr = (int*)take(EPB, 4); m.no = (int*)take(EPB, 4); m.nc = (int*)take(EPB, 4);
+  m.ep = (int*)take(EPB, 4); m.ok = (int*)take(EPB, 4);
+  m.bytes = off;
+  return m;
+}
+
+// ENV:458-501.  All cores contribute (the reference's `continue` is a no-op).
+__device__ __forceinline__ void current_at(const EnvConsts& k, const float4* cores, int nc, float x,
+                                           float y, float& cx, float& cy) {
+  cx = k.drift_vx;
+  cy = k.drift_vy;
+  for (int i = 0; i < nc; ++i) {
+    float4 co = cores[i];
+    float rx = co.x - x, ry = co.y - y;
+    float d = sqrtf(rx * rx + ry * ry);
+    float speed = (d <= k.core_r) ? co.w * k.solid_k * d : co.w * k.inv_2pi / d;  // ENV:497-501
+    float f = speed / d * co.z;  // co.z = +1 clockwise, -1 counter-clockwise, ENV:483-487
+    cx -= ry * f;
+    cy += rx * f;
+  }
+}
+
+__device__ __forceinline__ float wrap_to_pi(float a) {  // WAMV:425-434
+  const float PI = 3.14159265358979f;
+  while (a < -PI) a += 2.0f * PI;
+  while (a >= PI) a -= 2.0f * PI;
+  return a;
+}
+
+// WAMV:398-423 for one kept object o = [px,py,vx,vy,r] (ego frame); w = ego velocity in ego frame
+__device__ __forceinline__ bool colregs_one(const EnvConsts& k, const float* o, float w0, float w1,
+                                            float& phi) {
+  float so2 = o[2] * o[2] + o[3] * o[3];
+  if (sqrtf(so2) < k.min_speed) return false;                    // WAMV:400-402
+  float se = sqrtf(w0 * w0 + w1 * w1);
+  if (se < k.min_speed) return false;                            // WAMV:404-407
+  float inv = rsqrtf(so2);
+  float ca = o[2] * inv, sa = o[3] * inv;                        // R(atan2(vy,vx)), WAMV:328-330
+  float epx = -(ca * o[0] + sa * o[1]), epy = -(-sa * o[0] + ca * o[1]);  // WAMV:334
+  float evx = ca * w0 + sa * w1, evy = -sa * w0 + ca * w1;                // WAMV:339
+  float ang = atan2f(evy, evx);
+  const float PI = 3.14159265358979f;
+  bool tri = (epy - k.lc_y1) > k.lc_grad * (epx - k.lc_x1);      // WAMV:348-351
+  bool left = epx >= k.lc_x0 && epx <= k.lc_x1 && epy >= k.lc_y0 && epy <= 0.0f && !tri &&
+              ang >= 0.25f * PI && ang <= 0.75f * PI;            // WAMV:345-357
+  bool head = epx >= 0.0f && epx <= k.head_on_x && epy >= -k.head_on_half_y &&
+              epy <= k.head_on_half_y && fabsf(ang) > 0.75f * PI;  // WAMV:365-372
+  if (!(left || head)) return false;
+  // WAMV:379-396; NaN (dist < base_1) propagates and fails phi > 0 like the reference
+  float dist = sqrtf(o[0] * o[0] + o[1] * o[1]);
+  float base_1 = o[4] + 1.0f;
+  float add_1 = asinf(base_1 / dist);
+  float add_2 = atan2f(k.robot_r, sqrtf(dist * dist - base_1 * base_1));
+  phi = wrap_to_pi(wrap_to_pi(atan2f(o[1], o[0]) + add_1 + add_2) - atan2f(w1, w0));
+  return phi > 0.0f;                                             // WAMV:421
+}
+
+template <bool INJECT>
+__global__ void __launch_bounds__(256)
+env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* __restrict__ actions,
+                const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
+                uint64_t step, OutPtrs out, int E, int RP, int OP, int CP, int64_t env_offset,
+                uint32_t mode, int EPB) {
+  extern __shared__ __align__(16) char smem_raw[];
+  const Smem m = carve(smem_raw, EPB, RP, OP, CP);
+  const int tid = threadIdx.x;
+  const int A = EPB * RP, S = OP + RP, SK = S | 1;
+  const int e0 = blockIdx.x * EPB;
+  const bool dyn = mode & ASVRL_M_DYNAMICS;
+
+  // ---- phase 0: per-env tables ----
+  if (tid < EPB) {
+    int e = e0 + tid;
+    bool v = e < E && (!env_mask || env_mask[e]);
+    m.ok[tid] = v;
+    m.nr[tid] = v ? min(st.n_robots[e], RP) : 0;
+    m.no[tid] = v ? min(st.n_obs[e], OP) : 0;
+    m.nc[tid] = v ? min(st.n_cores[e], CP) : 0;
+    m.ep[tid] = v ? st.ep_steps[e] : 0;
+  }
+  for (int i = tid; i < EPB * OP; i += blockDim.x) {
+    int e = e0 + i / OP;
+    m.obst[i] = (e < E && (!env_mask || env_mask[e])) ? st.obstacles[(size_t)e * OP + i % OP] : make_float4(0, 0, 0, 0);
+  }
+  for (int i = tid; i < EPB * CP; i += blockDim.x) {
+    int e = e0 + i / CP;
+    m.cores[i] = (e < E && (!env_mask || env_mask[e])) ? st.cores[(size_t)e * CP + i % CP] : make_float4(0, 0, 0, 0);
+  }
+  __syncthreads();
+
+  // ---- phase A: dynamics, one thread per ASV ----
+  if (tid < A) {
+    const int el = tid / RP, r = tid - el * RP;
+    const int e = e0 + el;
+    const bool present = m.ok[el] && r < m.nr[el];
+    const size_t g = (size_t)e * RP + r;
+    double x = 0, y = 0, th = 0;
+    float vr0 = 0, vr1 = 0, vr2 = 0, v0 = 0, v1 = 0, v2 = 0, Tl = 0, Tr = 0, gx = 0, gy = 0;
+    uint32_t f = 0;
+    float rew = 0.0f;
+    if (present) {
+      x = st.x[g]; y = st.y[g]; th = st.theta[g];
+      vr0 = st.velr_x[g]; vr1 = st.velr_y[g]; vr2 = st.velr_r[g];
+      v0 = st.vel_x[g]; v1 = st.vel_y[g]; v2 = st.vel_r[g];
+      Tl = st.thrust_l[g]; Tr = st.thrust_r[g];
+      gx = st.goal_x[g]; gy = st.goal_y[g];
+      f = st.flags[g];
+    }
+    if (present && dyn && !(f & ASVRL_F_DEACTIVATED)) {
+      float dl, dr;
+      if (mode & ASVRL_M_DISCRETE) {  // WAMV:146-147, 225: id = 5*iL + iR
+        int a = ((const int32_t*)actions)[g];
+        a = min(max(a, 0), 24);
+        dl = k.dl[a / 5];
+        dr = k.dr[a % 5];
+      } else {  // WAMV:220-223
+        float2 a = ((const float2*)actions)[g];
+        dl = a.x * k.act_scale;
+        dr = a.y * k.act_scale;
+      }
+      const float4* cores = m.cores + el * CP;
+      const int nc = m.nc[el];
+      double dxg = (double)gx - x, dyg = (double)gy - y;
+      const double dis_before = sqrt(dxg * dxg + dyg * dyg);  // ENV:254
+      const double TWO_PI = 6.283185307179586;
+      for (int idx = 0; idx < k.n_sub; ++idx) {  // ENV:257-260
+        float cx, cy;
+        current_at(k, cores, nc, (float)x, (float)y, cx, cy);
+        v0 = vr0 + cx; v1 = vr1 + cy; v2 = vr2;  // WAMV:201-202
+        x += (double)(v0 * k.dt);                // WAMV:207-210
+        y += (double)(v1 * k.dt);
+        th += (double)(v2 * k.dt);
+        while (th < 0.0) th += TWO_PI;           // WAMV:213-216
+        while (th >= TWO_PI) th -= TWO_PI;
+        if (idx == 0) {                          // WAMV:218-229
+          Tl = fminf(fmaxf(Tl + dl, k.min_thrust), k.max_thrust);
+          Tr = fminf(fmaxf(Tr + dr, k.min_thrust), k.max_thrust);
+        }
+        // compute_motion, WAMV:233-279
+        float s, c;
+        sincosf((float)th, &s, &c);
+        float u_r = c * vr0 + s * vr1, v_r = -s * vr0 + c * vr1;
+        float u = c * v0 + s * v1, v = -s * v0 + c * v1;
+        float rr = v2;
+        float a = k.yDotV * v_r + k.yDotR * rr;
+        float au = fabsf(u_r), av = fabsf(v_r), ar = fabsf(rr);
+        float n0 = (-k.xU - k.xUU * au) * u_r + a * rr;
+        float n1 = (-k.yV - k.yVV * av - k.yRV * ar) * v_r +
+                   (-k.xDotU * u_r - k.yR - k.yVR * av - k.yRR * ar) * rr;
+        float n2 = -a * u_r + (k.xDotU * u_r - k.nV - k.nVV * av - k.nRV * ar) * v_r +
+                   (-k.nR - k.nVR * av - k.nRR * ar) * rr;
+        float Fxl = Tl * k.cl, Fyl = Tl * k.sl, Fxr = Tr * k.cr, Fyr = Tr * k.sr;
+        float b0 = k.m * rr * v - n0 + (Fxl + Fxr);
+        float b1 = -k.m * rr * u - n1 + (Fyl + Fyr);
+        float b2 = -n2 + (Fxl * k.half_w - Fyl * k.half_l - Fxr * k.half_w - Fyr * k.half_l);
+        u_r += (k.Ainv[0] * b0 + k.Ainv[1] * b1 + k.Ainv[2] * b2) * k.dt;
+        v_r += (k.Ainv[3] * b0 + k.Ainv[4] * b1 + k.Ainv[5] * b2) * k.dt;
+        rr += (k.Ainv[6] * b0 + k.Ainv[7] * b1 + k.Ainv[8] * b2) * k.dt;
+        vr0 = c * u_r - s * v_r;
+        vr1 = s * u_r + c * v_r;
+        vr2 = rr;
+      }
+      dxg = (double)gx - x; dyg = (double)gy - y;
+      const double dis_after = sqrt(dxg * dxg + dyg * dyg);
+      rew = k.timestep_penalty + (float)(dis_before - dis_after);  // ENV:271-277
+      st.x[g] = (float)x; st.y[g] = (float)y; st.theta[g] = (float)th;
+      st.velr_x[g] = vr0; st.velr_y[g] = vr1; st.velr_r[g] = vr2;
+      st.vel_x[g] = v0; st.vel_y[g] = v1; st.vel_r[g] = v2;
+      st.thrust_l[g] = Tl; st.thrust_r[g] = Tr;
+    }
+    // heading of the pose everything below reads, with the fp32 rounding residual folded in
+    float thf = (float)th, s, c;
+    sincosf(thf, &s, &c);
+    float dth = (float)(th - (double)thf);
+    m.px[tid] = x; m.py[tid] = y;
+    m.c[tid] = c - s * dth; m.s[tid] = s + c * dth;
+    m.vx[tid] = v0; m.vy[tid] = v1; m.vz[tid] = v2;
+    m.Tl[tid] = Tl; m.Tr[tid] = Tr; m.gx[tid] = gx; m.gy[tid] = gy;
+    m.rew[tid] = rew;
+    m.fl0[tid] = present ? f : (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
+    uint32_t fnew = f;
+    if (present && !(f & ASVRL_F_DEACTIVATED)) {  // check_reach_goal, WAMV:170-172, 462
+      double dxg = (double)gx - x, dyg = (double)gy - y;
+      if (dxg * dxg + dyg * dyg <= k.goal_dis_d * k.goal_dis_d) fnew |= ASVRL_F_REACH_GOAL;
+    }
+    m.fl[tid] = fnew;
+    m.det_lo[tid] = 0; m.det_hi[tid] = 0;
+  }
+  __syncthreads();
+
+  // ---- phase B: every (ego, candidate slot) pair of the CTA's envs ----
+  for (int p = tid; p < A * S; p += blockDim.x) {
+    const int a = p / S, sl = p - a * S;
+    const int el = a / RP, r = a - el * RP;
+    double key = INFINITY;
+    const uint32_t fe = m.fl0[a];
+    bool live = !(fe & ASVRL_F_DEACTIVATED);
+    double px = 0, py = 0, rt = 0;
+    float vx = 0, vy = 0;
+    if (live) {
+      if (sl < OP) {  // static obstacles, WAMV:465-483
+        live = sl < m.no[el];
+        float4 ob = m.obst[el * OP + sl];
+        px = ob.x; py = ob.y; rt = ob.z;
+      } else {  // other robots still on the map, WAMV:486-510
+        const int j = sl - OP, b = el * RP + j;
+        live = j != r && !(m.fl0[b] & ASVRL_F_DEACTIVATED);
+        px = m.px[b]; py = m.py[b]; vx = m.vx[b]; vy = m.vy[b]; rt = k.robot_r_d;
+      }
+    }
+    if (live) {
+      const double ex = m.px[a], ey = m.py[a];
+      const double tx = px - ex, ty = py - ey;  // true offset
+      bool maybe = true;
+      if (!INJECT) {  // the in-kernel generator's noise is bounded: skip hopeless candidates
+        float far = k.detect_bound + (float)rt;
+        maybe = (float)(tx * tx + ty * ty) <= far * far;
+      }
+      if (maybe) {
+        NoiseDraw nd;
+        if (INJECT) {
+          const float* np = noise + ((size_t)(e0 * RP + a) * S + sl) * 5;
+#pragma unroll
+          for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
+        } else {
+          nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
+        }
+        const double qx = tx + (double)nd.n[0], qy = ty + (double)nd.n[1];  // WAMV:27-30
+        const double orr = k.r_mean_ratio * rt + k.r_noise_k * (double)nd.n[4] * rt;  // WAMV:37-40
+        const double d2 = qx * qx + qy * qy, lim = k.perc_range + orr;
+        bool det = d2 <= lim * lim;  // WAMV:296
+        const float c = m.c[a], s = m.s[a];
+        const float fx = (float)qx, fy = (float)qy;
+        const float bx = c * fx + s * fy, by = -s * fx + c * fy;  // WAMV:305-322
+        if (det && k.angle_limited) {  // WAMV:299-301 (vacuous at the default 2 pi)
+          double ang = atan2((double)by, (double)bx);
+          det = !(ang < -k.half_angle || ang > k.half_angle);
+        }
+        if (det) {
+          atomicOr(sl < 32 ? &m.det_lo[a] : &m.det_hi[a], 1u << (sl & 31));
+          if (!(fe & ASVRL_F_COLLISION)) {  // true geometry, WAMV:281-291, 475-476
+            double d = sqrt(tx * tx + ty * ty) - rt - k.robot_r_d;
+            if (d <= 0.0) atomicOr(&m.fl[a], (uint32_t)ASVRL_F_COLLISION);
+          }
+          const float ovx = vx + nd.n[2], ovy = vy + nd.n[3];  // WAMV:32-35
+          float* cd = m.cand + (size_t)p * 5;
+          cd[0] = bx; cd[1] = by;
+          cd[2] = c * ovx + s * ovy; cd[3] = -s * ovx + c * ovy;
+          cd[4] = (float)orr;
+          key = sqrt(d2) - orr - k.robot_r_d;  // WAMV:515, 288
+        }
+      }
+    }
+    m.key[a * SK + sl] = key;
+  }
+  __syncthreads();
+
+  // ---- phase C: one thread per ego ----
+  if (tid < A) {
+    const int a = tid, el = a / RP, r = a - el * RP;
+    const int e = e0 + el;
+    const size_t g = (size_t)e * RP + r;
+    float* so = m.st_obj + a * 25;
+    float* ss = m.st_self + a * 7;
+    float* sm = m.st_mask + a * 5;
+#pragma unroll
+    for (int q = 0; q < 25; ++q) so[q] = 0.0f;
+#pragma unroll
+    for (int q = 0; q < 7; ++q) ss[q] = 0.0f;
+#pragma unroll
+    for (int q = 0; q < 5; ++q) sm[q] = 0.0f;
+    if (m.ok[el]) {
+      const bool present = r < m.nr[el];
+      const uint32_t f0 = m.fl0[a];
+      uint32_t f = m.fl[a], status = 0;
+      float reward = 0.0f, phi = 0.0f;
+      int top[5] = {-1, -1, -1, -1, -1};
+      if (!present) {
+        status = (uint32_t)ASVRL_INFO_ABSENT << ASVRL_S_INFO_SHIFT;
+      } else if (f0 & ASVRL_F_DEACTIVATED) {  // WAMV:437-438, ENV:295-304
+        int info = (f0 & ASVRL_F_COLLISION) ? ASVRL_INFO_DEACT_COLLISION
+                   : (f0 & ASVRL_F_REACH_GOAL) ? ASVRL_INFO_DEACT_GOAL : ASVRL_INFO_DEACT_INVALID;
+        status = ASVRL_S_DONE | ASVRL_S_WAS_DEACTIVATED | ((uint32_t)info << ASVRL_S_INFO_SHIFT);
+      } else {
+        const float c = m.c[a], s = m.s[a];
+        const float dgx = (float)((double)m.gx[a] - m.px[a]), dgy = (float)((double)m.gy[a] - m.py[a]);
+        const float w0 = c * m.vx[a] + s * m.vy[a], w1 = -s * m.vx[a] + c * m.vy[a];
+        ss[0] = c * dgx + s * dgy; ss[1] = -s * dgx + c * dgy;  // WAMV:443-453
+        ss[2] = w0; ss[3] = w1; ss[4] = m.vz[a]; ss[5] = m.Tl[a]; ss[6] = m.Tr[a];
+        // stable 5 smallest keys (heapq.nsmallest, WAMV:513-515): ties keep slot order
+        const double* keys = m.key + a * SK;
+        double lastk = -INFINITY;
+        int lasts = -1, kept = 0;
+        for (int t = 0; t < ASVRL_MAX_OBJ; ++t) {
+          double best = INFINITY;
+          int bs = -1;
+          for (int sl = 0; sl < S; ++sl) {
+            double kk = keys[sl];
+            if (kk < best && (kk > lastk || (kk == lastk && sl > lasts))) { best = kk; bs = sl; }
+          }
+          if (bs < 0) break;
+          const float* cd = m.cand + ((size_t)a * S + bs) * 5;
+#pragma unroll
+          for (int q = 0; q < 5; ++q) so[t * 5 + q] = cd[q];
+          sm[t] = 1.0f;
+          top[t] = bs;
+          lastk = best; lasts = bs; kept = t + 1;
+        }
+        bool apply = false;  // WAMV:517-521
+        for (int t = 0; t < kept && !apply; ++t) apply = colregs_one(k, so + t * 5, w0, w1, phi);
+        if (!apply) phi = 0.0f;
+        if (apply) status |= ASVRL_S_COLREGS;
+        int info = ASVRL_INFO_NORMAL;
+        if (dyn) {  // ENV:306-328
+          reward = m.rew[a];
+          if (apply) reward += k.colregs_penalty * phi;
+          if (m.ep[el] >= k.max_ep) { status |= ASVRL_S_DONE; info = ASVRL_INFO_TOO_LONG; }
+          else if (f & ASVRL_F_COLLISION) { reward += k.collision_penalty; status |= ASVRL_S_DONE; info = ASVRL_INFO_COLLISION; }
+          else if (f & ASVRL_F_REACH_GOAL) { reward += k.goal_reward; status |= ASVRL_S_DONE; info = ASVRL_INFO_REACH_GOAL; }
+        }
+        status |= (uint32_t)info << ASVRL_S_INFO_SHIFT;
+        if ((mode & ASVRL_M_AUTO_DEACTIVATE) && (f & (ASVRL_F_COLLISION | ASVRL_F_REACH_GOAL)))
+          f |= ASVRL_F_DEACTIVATED;  // TRAINER:168-170
+        if (f != f0) st.flags[g] = f;
+        m.fl[a] = f;
+      }
+      if (present) {
+        if (f & ASVRL_F_COLLISION) status |= ASVRL_S_COLLISION;
+        if (f & ASVRL_F_REACH_GOAL) status |= ASVRL_S_REACH_GOAL;
+      }
+      out.reward[g] = reward;
+      out.status[g] = status;
+      out.phi[g] = phi;
+      if (out.top_ids) {
+#pragma unroll
+        for (int t = 0; t < 5; ++t) out.top_ids[g * 5 + t] = top[t];
+      }
+      if (out.detected)
+        out.detected[g] = (unsigned long long)m.det_lo[a] | ((unsigned long long)m.det_hi[a] << 32);
+    }
+  }
+  __syncthreads();
+
+  // ---- phase D: coalesced observation rows + env-level reductions ----
+  {
+    const int n_env = min(EPB, E - e0);
+    const size_t a0 = (size_t)e0 * RP;
+    const int n_asv = n_env * RP;
+    for (int i = tid; i < n_asv * 25; i += blockDim.x)
+      if (m.ok[i / (RP * 25)]) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
+    for (int i = tid; i < n_asv * 7; i += blockDim.x)
+      if (m.ok[i / (RP * 7)]) out.obs_self[a0 * 7 + i] = m.st_self[i];
+    for (int i = tid; i < n_asv * 5; i += blockDim.x)
+      if (m.ok[i / (RP * 5)]) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
+    if (tid < n_env && m.ok[tid]) {
+      const int el = tid, e = e0 + el, nr = m.nr[el];
+      bool all_deact = true, any_coll = false, all_goal = true;
+      for (int r = 0; r < nr; ++r) {
+        uint32_t f = m.fl[el * RP + r];
+        all_deact &= (f & ASVRL_F_DEACTIVATED) != 0;   // ENV:178-184
+        any_coll |= (f & ASVRL_F_COLLISION) != 0;      // ENV:194-200
+        all_goal &= (f & ASVRL_F_REACH_GOAL) != 0;     // ENV:186-192
+      }
+      uint32_t es = (all_deact ? 1u : 0u) | (m.ep[el] >= k.max_ep ? 2u : 0u) |
+                    (any_coll ? 4u : 0u) | (all_goal ? 8u : 0u);
+      out.env_status[e] = es;
+      if (out.ended) out.ended[e] = (es & 3u) ? 1 : 0;
+      if (dyn) st.ep_steps[e] = m.ep[el] + 1;  // ENV:330
+    }
+  }
+}
+
+// fills the [E][RP][OP+RP][5] table the NULL-noise path of K1 uses (same device function)
+__global__ void env_noise_kernel(const __grid_constant__ EnvConsts k, uint64_t seed, uint64_t step,
+                                 int E, int RP, int OP, int64_t env_offset, float* __restrict__ out) {
+  const int S = OP + RP;
+  const size_t n = (size_t)E * RP * S;
+  for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < n;
+       p += (size_t)gridDim.x * blockDim.x) {
+    const int sl = (int)(p % S);
+    const size_t a = p / S;
+    const int r = (int)(a % RP);
+    const int64_t e = (int64_t)(a / RP);
+    NoiseDraw nd = sensor_noise(k, seed, step, env_offset + e, (uint32_t)r, (uint32_t)sl);
+#pragma unroll
+    for (int q = 0; q < 5; ++q) out[p * 5 + q] = nd.n[q];
+  }
+}
+
+static void invert3(const double G[3][3], double inv[3][3], double* det_out) {
+  double c00 = G[1][1] * G[2][2] - G[1][2] * G[2][1];
+  double c01 = G[1][2] * G[2][0] - G[1][0] * G[2][2];
+  double c02 = G[1][0] * G[2][1] - G[1][1] * G[2][0];
+  double det = G[0][0] * c00 + G[0][1] * c01 + G[0][2] * c02;
+  *det_out = det;
+  inv[0][0] = c00 / det; inv[0][1] = (G[0][2] * G[2][1] - G[0][1] * G[2][2]) / det;
+  inv[0][2] = (G[0][1] * G[1][2] - G[0][2] * G[1][1]) / det;
+  inv[1][0] = c01 / det; inv[1][1] = (G[0][0] * G[2][2] - G[0][2] * G[2][0]) / det;
+  inv[1][2] = (G[0][2] * G[1][0] - G[0][0] * G[1][2]) / det;
+  inv[2][0] = c02 / det; inv[2][1] = (G[0][1] * G[2][0] - G[0][0] * G[2][1]) / det;
+  inv[2][2] = (G[0][0] * G[1][1] - G[0][1] * G[1][0]) / det;
+}
+
+int make_env_consts(const asvrl_env_params* p, EnvConsts* k) {
+  if (!p || !k) return fail(ASVRL_E_BADARG, "null params");
+  if (p->n_substeps < 0 || p->dt <= 0.0) return fail(ASVRL_E_BADARG, "bad dt / n_substeps");
+  const double PI = 3.14159265358979323846;
+  k->dt = (float)p->dt; k->n_sub = p->n_substeps; k->max_ep = p->max_episode_steps;
+  k->min_thrust = (float)p->min_thrust; k->max_thrust = (float)p->max_thrust;
+  const double hold = p->dt * p->n_substeps;
+  k->act_scale = (float)(p->thrust_rate * hold);
+  for (int i = 0; i < 5; ++i) {
+    k->dl[i] = (float)(p->thrust_change_l[i] * hold);
+    k->dr[i] = (float)(p->thrust_change_r[i] * hold);
+  }
+  k->m = (float)p->m; k->xDotU = (float)p->xDotU; k->yDotV = (float)p->yDotV; k->yDotR = (float)p->yDotR;
+  k->xU = (float)p->xU; k->xUU = (float)p->xUU; k->yV = (float)p->yV; k->yVV = (float)p->yVV;
+  k->yR = (float)p->yR; k->yRV = (float)p->yRV; k->yVR = (float)p->yVR; k->yRR = (float)p->yRR;
+  k->nR = (float)p->nR; k->nRR = (float)p->nRR; k->nV = (float)p->nV; k->nVV = (float)p->nVV;
+  k->nRV = (float)p->nRV; k->nVR = (float)p->nVR;
+  k->cl = (float)cos(p->left_pos); k->sl = (float)sin(p->left_pos);
+  k->cr = (float)cos(p->right_pos); k->sr = (float)sin(p->right_pos);
+  k->half_w = (float)(p->width / 2); k->half_l = (float)(p->length / 2);
+  {  // pinv(A) = (A^T A)^-1 A^T, WAMV:267-271
+    double A[3][3] = {{p->m - p->xDotU, 0, 0}, {0, p->m - p->yDotV, -p->yDotR}, {0, -p->nDotV, p->Izz - p->nDotR}};
+    double G[3][3], Gi[3][3], det;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) { G[i][j] = 0; for (int q = 0; q < 3; ++q) G[i][j] += A[q][i] * A[q][j]; }
+    invert3(G, Gi, &det);
+    if (!(fabs(det) > 0.0)) return fail(ASVRL_E_BADARG, "singular M_RB + M_A");
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) { double v = 0; for (int q = 0; q < 3; ++q) v += Gi[i][q] * A[j][q]; k->Ainv[i * 3 + j] = (float)v; }
+  }
+  k->core_r = (float)p->core_r; k->solid_k = (float)(1.0 / (2 * PI * p->core_r * p->core_r));
+  k->inv_2pi = (float)(1.0 / (2 * PI)); k->drift_vx = (float)p->drift_vx; k->drift_vy = (float)p->drift_vy;
+  k->perc_range = p->perc_range; k->half_angle = 0.5 * p->perc_angle;
+  k->angle_limited = p->perc_angle < 2 * PI ? 1 : 0;
+  k->r_mean_ratio = p->r_mean_ratio; k->r_noise_k = (1.0 - p->r_mean_ratio) / PI;
+  k->robot_r_d = p->robot_r; k->goal_dis_d = p->goal_dis; k->robot_r = (float)p->robot_r;
+  k->pos_std = (float)p->pos_std; k->vel_std = (float)p->vel_std;
+  k->vm_uniform = p->r_kappa < 1e-5 ? 1 : 0;
+  if (!k->vm_uniform) {
+    double kap = p->r_kappa, rr = 1.0 + sqrt(1.0 + 4.0 * kap * kap);
+    double rho = (rr - sqrt(2.0 * rr)) / (2.0 * kap);
+    k->vm_kappa = (float)kap; k->vm_s = (float)((1.0 + rho * rho) / (2.0 * rho));
+  } else { k->vm_kappa = 0; k->vm_s = 1; }
+  // Box-Muller on 24-bit uniforms: |n| <= sqrt(-2 ln 2^-25) sigma < 5.9 sigma per axis; the
+  // noisy radius never exceeds the true one (r_mean_ratio + (1-r_mean_ratio) <= 1).
+  k->detect_bound = (float)(p->perc_range + 5.9 * 1.4143 * fabs(p->pos_std) + 1e-3);
+  k->head_on_x = (float)p->head_on_x; k->head_on_half_y = (float)(0.5 * p->head_on_y);
+  k->lc_x0 = (float)p->lc_x0; k->lc_x1 = (float)p->lc_x1; k->lc_y0 = (float)p->lc_y0; k->lc_y1 = (float)p->lc_y1;
+  k->lc_grad = (float)(p->lc_y1 / p->lc_x1); k->min_speed = (float)p->colregs_min_speed;
+  k->timestep_penalty = (float)p->timestep_penalty; k->colregs_penalty = (float)p->colregs_penalty;
+  k->collision_penalty = (float)p->collision_penalty; k->goal_reward = (float)p->goal_reward;
+  return 0;
+}
+
+}  // namespace asvrl
+
+using namespace asvrl;
+
+static int pick_epb(int RP) { int e = 32 / RP; return e < 1 ? 1 : e; }
+
+extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_state* state,
+                              const void* actions, const float* noise, const uint8_t* env_mask,
+                              uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,
+                              int max_robots, int max_obs, int max_cores, int64_t env_offset,
+                              uint32_t mode, void* stream) {
+  if (!params || !state || !out) return fail(ASVRL_E_BADARG, "asvrl_env_step: null struct");
+  if (n_envs < 0 || max_robots < 1 || max_obs < 0 || max_cores < 0)
+    return fail(ASVRL_E_BADARG, "asvrl_env_step: bad sizes");
+  if (max_robots > 32 || max_obs + max_robots > ASVRL_MAX_SLOTS)
+    return fail(ASVRL_E_LIMIT, "asvrl_env_step: max_robots <= 32 and max_obs + max_robots <= %d", ASVRL_MAX_SLOTS);
+  if ((mode & ASVRL_M_DYNAMICS) && !actions) return fail(ASVRL_E_BADARG, "asvrl_env_step: actions required");
+  if (n_envs == 0) return 0;
+  EnvConsts k;
+  int rc = make_env_consts(params, &k);
+  if (rc) return rc;
+  StatePtrs st = {state->x, state->y, state->theta, state->velr_x, state->velr_y, state->velr_r,
+                  state->vel_x, state->vel_y, state->vel_r, state->thrust_l, state->thrust_r,
+                  state->goal_x, state->goal_y, state->flags, state->n_robots, state->n_obs,
+                  state->n_cores, state->ep_steps, (const float4*)state->obstacles,
+                  (const float4*)state->cores};
+  OutPtrs o = {out->obs_self, out->obs_objects, out->obs_mask, out->reward, out->status, out->phi,
+               out->top_ids, (unsigned long long*)out->detected, out->env_status, out->ended};
+  if (!o.obs_self || !o.obs_objects || !o.obs_mask || !o.reward || !o.status || !o.phi || !o.env_status)
+    return fail(ASVRL_E_BADARG, "asvrl_env_step: null output");
+  if ((max_obs > 0 && !st.obstacles) || (max_cores > 0 && !st.cores))
+    return fail(ASVRL_E_BADARG, "asvrl_env_step: null obstacle / core table");
+  const int EPB = pick_epb(max_robots);
+  const size_t smem = carve(nullptr, EPB, max_robots, max_obs, max_cores).bytes;
+  const int grid = (n_envs + EPB - 1) / EPB;
+  cudaStream_t s = (cudaStream_t)stream;
+  auto kern = noise ? env_step_kernel<true> : env_step_kernel<false>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
+  }
+  kern<<<grid, 256, smem, s>>>(k, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
+                               max_cores, env_offset, mode, EPB);
+  return check_launch("asvrl_env_step");
+}
+
+extern "C" int asvrl_env_noise(const asvrl_env_params* params, uint64_t seed, uint64_t step,
+                               int n_envs, int max_robots, int max_obs, int64_t env_offset,
+                               float* noise_out, void* stream) {
+  if (!params || !noise_out) return fail(ASVRL_E_BADARG, "asvrl_env_noise: null argument");
+  EnvConsts k;
+  int rc = make_env_consts(params, &k);
+  if (rc) return rc;
+  size_t n = (size_t)n_envs * max_robots * (max_obs + max_robots);
+  if (n == 0) return 0;
+  int grid = (int)((n + 255) / 256);
+  if (grid > 148 * 16) grid = 148 * 16;
+  env_noise_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, seed, step, n_envs, max_robots, max_obs,
+                                                           env_offset, noise_out);
+  return check_launch("asvrl_env_noise");
+}

@@ -1,0 +1,229 @@
+// replay.cu — K2: GPU-resident uniform replay buffer with on-device sampling (sm_100a).
+//
+// Replaces (reference paths under rfarl/rfarl/):
+//   utils/replay_buffer.py:22-24   ReplayBuffer.add        (deque of python tuples)
+//   utils/replay_buffer.py:26-69   sample + state_batch    (random.sample, pad to 5 + mask)
+//   agent.py:360-368, 387-392      state_to_tensor + the five host->device copies per train()
+//   policy/trainer.py:157-166      which transitions are stored (robots active at step start)
+//
+// Layout: a ring of dense float32[70] rows (280 B) in HBM.  Both kernels move whole rows with
+// one warp per row so every global access is a contiguous, coalesced run; the work is pure
+// HBM traffic (560 B per pushed transition, ~600 B per sampled one).
+#include "common.cuh"
+
+namespace asvrl {
+
+constexpr int PUSH_T = 256;
+
+// valid transition <=> the ASV was on the map when the step started (TRAINER:157-159)
+__device__ __forceinline__ bool row_valid(uint32_t status) {
+  return !(status & ASVRL_S_WAS_DEACTIVATED) &&
+         ((status >> ASVRL_S_INFO_SHIFT) & 15u) != (uint32_t)ASVRL_INFO_ABSENT;
+}
+
+// pass 1: per-CTA valid counts; the last CTA to finish turns them into exclusive offsets
+// (deterministic (env, robot) order) and advances the ring counters.
+// workspace: [0] ticket, [1] total, [2..3] base ring position (u64), [4..] per-CTA offsets
+__global__ void __launch_bounds__(PUSH_T)
+replay_count_kernel(const uint32_t* __restrict__ status, int n_asv, int64_t capacity,
+                    unsigned long long* head_size, uint32_t* ws) {
+  const int i = blockIdx.x * PUSH_T + threadIdx.x;
+  const bool v = i < n_asv && row_valid(status[i]);
+  const int cnt = __syncthreads_count(v);
+  __shared__ bool is_last;
+  if (threadIdx.x == 0) {
+    ws[4 + blockIdx.x] = (uint32_t)cnt;
+    __threadfence();
+    is_last = atomicAdd(&ws[0], 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // exclusive scan of gridDim.x counts by one CTA: chunked serial + shared scan
+  __shared__ uint32_t chunk_sum[PUSH_T];
+  const int nb = gridDim.x;
+  const int per = (nb + PUSH_T - 1) / PUSH_T;
+  const int b0 = threadIdx.x * per, b1 = min(b0 + per, nb);
+  uint32_t s = 0;
+  for (int b = b0; b < b1; ++b) s += __ldcg(&ws[4 + b]);
+  chunk_sum[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int t = 0; t < PUSH_T; ++t) { uint32_t c = chunk_sum[t]; chunk_sum[t] = run; run += c; }
+    const unsigned long long base = head_size[0];
+    ws[1] = run;
+    ws[2] = (uint32_t)base; ws[3] = (uint32_t)(base >> 32);
+    const unsigned long long total = base + run;
+    head_size[0] = total;
+    head_size[1] = total < (unsigned long long)capacity ? total : (unsigned long long)capacity;
+    ws[0] = 0u;  // ticket left clean for the next call
+  }
+  __syncthreads();
+  uint32_t run = chunk_sum[threadIdx.x];
+  for (int b = b0; b < b1; ++b) { uint32_t c = __ldcg(&ws[4 + b]); ws[4 + b] = run; run += c; }
+}
+
+// source of element q of a row (RB:60-67 padding is already in the obs tensors: zero rows)
+__device__ __forceinline__ float row_elem(int q, size_t i, const float* obs_self, const float* obs_obj,
+                                          const float* obs_mask, const void* actions, int discrete,
+                                          const float* reward, const float* nself, const float* nobj,
+                                          const float* nmask, const uint32_t* status) {
+  if (q < ASVRL_ROW_OBJ) return obs_self[i * 7 + q];
+  if (q < ASVRL_ROW_NOBJ) return obs_obj[i * 25 + (q - ASVRL_ROW_OBJ)];
+  if (q == ASVRL_ROW_NOBJ) {
+    const float* mk = obs_mask + i * 5;
+    return mk[0] + mk[1] + mk[2] + mk[3] + mk[4];
+  }
+  if (q < ASVRL_ROW_REW) {
+    if (discrete) return q == ASVRL_ROW_ACT ? (float)((const int32_t*)actions)[i] : 0.0f;
+    return ((const float*)actions)[i * 2 + (q - ASVRL_ROW_ACT)];
+  }
+  if (q == ASVRL_ROW_REW) return reward[i];
+  if (q < ASVRL_ROW_NOBJ_F) return nself[i * 7 + (q - ASVRL_ROW_NSELF)];
+  if (q < ASVRL_ROW_NNOBJ) return nobj[i * 25 + (q - ASVRL_ROW_NOBJ_F)];
+  if (q == ASVRL_ROW_NNOBJ) {
+    const float* mk = nmask + i * 5;
+    return mk[0] + mk[1] + mk[2] + mk[3] + mk[4];
+  }
+  return (status[i] & ASVRL_S_DONE) ? 1.0f : 0.0f;
+}
+
+// pass 2: warp-cooperative row writes
+__global__ void __launch_bounds__(PUSH_T)
+replay_scatter_kernel(float* __restrict__ rows, int64_t capacity, const float* __restrict__ obs_self,
+                      const float* __restrict__ obs_obj, const float* __restrict__ obs_mask,
+                      const void* __restrict__ actions, int discrete, const float* __restrict__ reward,
+                      const float* __restrict__ nself, const float* __restrict__ nobj,
+                      const float* __restrict__ nmask, const uint32_t* __restrict__ status, int n_asv,
+                      const uint32_t* __restrict__ ws) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int i = blockIdx.x * PUSH_T + threadIdx.x;
+  const bool v = i < n_asv && row_valid(status[i]);
+  const unsigned bal = __ballot_sync(0xffffffffu, v);
+  __shared__ uint32_t warp_cnt[PUSH_T / 32];
+  if (lane == 0) warp_cnt[warp] = __popc(bal);
+  __syncthreads();
+  uint32_t before = 0;
+  for (int w = 0; w < warp; ++w) before += warp_cnt[w];
+  const unsigned long long base = (unsigned long long)ws[2] | ((unsigned long long)ws[3] << 32);
+  const unsigned long long first = base + ws[4 + blockIdx.x] + before;
+  unsigned rem = bal;
+  uint32_t rank = 0;
+  while (rem) {
+    const int src_lane = __ffs(rem) - 1;
+    rem &= rem - 1;
+    const size_t src = (size_t)blockIdx.x * PUSH_T + warp * 32 + src_lane;
+    float* dst = rows + (size_t)((first + rank) % (unsigned long long)capacity) * ASVRL_ROW;
+    for (int q = lane; q < ASVRL_ROW; q += 32)
+      dst[q] = row_elem(q, src, obs_self, obs_obj, obs_mask, actions, discrete, reward, nself, nobj,
+                        nmask, status);
+    ++rank;
+  }
+}
+
+// keyed Feistel permutation of [0, 2^bits) with cycle walking down to [0, n): a bijection, so the
+// first `batch` images of 0..batch-1 are DISTINCT uniform indices (random.sample, RB:28)
+__device__ __forceinline__ uint64_t feistel_perm(uint64_t x, uint64_t n, int half_bits, uint2 key) {
+  const uint32_t mask = half_bits >= 32 ? 0xffffffffu : ((1u << half_bits) - 1u);
+  do {
+    uint32_t l = (uint32_t)(x >> half_bits) & mask, r = (uint32_t)x & mask;
+#pragma unroll
+    for (int round = 0; round < 4; ++round) {
+      uint4 f = philox4x32_10(make_uint4(r, (uint32_t)round, 0x52504c59u, 0u), key);
+      uint32_t nl = r, nr = l ^ (f.x & mask);
+      l = nl; r = nr;
+    }
+    x = ((uint64_t)l << half_bits) | r;
+  } while (x >= n);
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+replay_sample_kernel(const float* __restrict__ rows, const unsigned long long* __restrict__ head_size,
+                     int64_t capacity, const int64_t* __restrict__ indices, uint64_t seed,
+                     uint64_t counter, int batch, float* __restrict__ self_b, float* __restrict__ obj_b,
+                     float* __restrict__ mask_b, float* __restrict__ act_b, float* __restrict__ rew_b,
+                     float* __restrict__ nself_b, float* __restrict__ nobj_b, float* __restrict__ nmask_b,
+                     float* __restrict__ done_b, int64_t* __restrict__ indices_out) {
+  const int lane = threadIdx.x & 31;
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (b >= batch) return;
+  const uint64_t size = head_size[1];
+  if (size == 0) return;
+  uint64_t idx;
+  if (indices) {
+    idx = (uint64_t)indices[b] % size;
+  } else {
+    int bits = 2;
+    while (bits < 64 && (1ull << bits) < size) ++bits;
+    if (bits & 1) ++bits;
+    // the key mixes the draw counter so successive batches use unrelated permutations
+    uint4 kk = philox_at(seed, STREAM_REPLAY, counter, 0, 0u, 0u, 0u);
+    idx = feistel_perm((uint64_t)b % size, size, bits / 2, make_uint2(kk.x, kk.y));
+  }
+  if (lane == 0 && indices_out) indices_out[b] = (int64_t)idx;
+  const float* row = rows + (size_t)idx * ASVRL_ROW;
+  // 70 floats: lanes take q, q+32, q+64
+  for (int q = lane; q < ASVRL_ROW; q += 32) {
+    const float v = row[q];
+    if (q < ASVRL_ROW_OBJ) self_b[(size_t)b * 7 + q] = v;
+    else if (q < ASVRL_ROW_NOBJ) obj_b[(size_t)b * 25 + (q - ASVRL_ROW_OBJ)] = v;
+    else if (q == ASVRL_ROW_NOBJ) {
+#pragma unroll
+      for (int t = 0; t < 5; ++t) mask_b[(size_t)b * 5 + t] = (float)t < v ? 1.0f : 0.0f;  // RB:65
+    } else if (q < ASVRL_ROW_REW) act_b[(size_t)b * 2 + (q - ASVRL_ROW_ACT)] = v;
+    else if (q == ASVRL_ROW_REW) rew_b[b] = v;
+    else if (q < ASVRL_ROW_NOBJ_F) nself_b[(size_t)b * 7 + (q - ASVRL_ROW_NSELF)] = v;
+    else if (q < ASVRL_ROW_NNOBJ) nobj_b[(size_t)b * 25 + (q - ASVRL_ROW_NOBJ_F)] = v;
+    else if (q == ASVRL_ROW_NNOBJ) {
+#pragma unroll
+      for (int t = 0; t < 5; ++t) nmask_b[(size_t)b * 5 + t] = (float)t < v ? 1.0f : 0.0f;
+    } else done_b[b] = v;
+  }
+}
+
+}  // namespace asvrl
+
+using namespace asvrl;
+
+extern "C" int asvrl_replay_push(float* rows, int64_t capacity, unsigned long long* head_size,
+                                 const float* obs_self, const float* obs_objects,
+                                 const float* obs_mask, const void* actions, int discrete,
+                                 const float* reward, const float* next_self,
+                                 const float* next_objects, const float* next_mask,
+                                 const uint32_t* status, int n_asv, uint32_t* workspace,
+                                 void* stream) {
+  if (!rows || !head_size || !obs_self || !obs_objects || !obs_mask || !actions || !reward ||
+      !next_self || !next_objects || !next_mask || !status || !workspace)
+    return fail(ASVRL_E_BADARG, "asvrl_replay_push: null pointer");
+  if (capacity < 1 || n_asv < 0) return fail(ASVRL_E_BADARG, "asvrl_replay_push: bad sizes");
+  if ((int64_t)n_asv > capacity) return fail(ASVRL_E_LIMIT, "asvrl_replay_push: n_asv %d exceeds capacity", n_asv);
+  if (n_asv == 0) return 0;
+  const int grid = (n_asv + PUSH_T - 1) / PUSH_T;
+  cudaStream_t s = (cudaStream_t)stream;
+  replay_count_kernel<<<grid, PUSH_T, 0, s>>>(status, n_asv, capacity, head_size, workspace);
+  int rc = check_launch("asvrl_replay_push(count)");
+  if (rc) return rc;
+  replay_scatter_kernel<<<grid, PUSH_T, 0, s>>>(rows, capacity, obs_self, obs_objects, obs_mask,
+                                                actions, discrete, reward, next_self, next_objects,
+                                                next_mask, status, n_asv, workspace);
+  return check_launch("asvrl_replay_push(scatter)");
+}
+
+extern "C" int asvrl_replay_sample(const float* rows, const unsigned long long* head_size,
+                                   int64_t capacity, const int64_t* indices, uint64_t seed,
+                                   uint64_t counter, int batch, float* self_b, float* obj_b,
+                                   float* mask_b, float* act_b, float* rew_b, float* nself_b,
+                                   float* nobj_b, float* nmask_b, float* done_b,
+                                   int64_t* indices_out, void* stream) {
+  if (!rows || !head_size || !self_b || !obj_b || !mask_b || !act_b || !rew_b || !nself_b ||
+      !nobj_b || !nmask_b || !done_b)
+    return fail(ASVRL_E_BADARG, "asvrl_replay_sample: null pointer");
+  if (batch < 1 || capacity < 1) return fail(ASVRL_E_BADARG, "asvrl_replay_sample: bad sizes");
+  const int grid = (batch * 32 + 255) / 256;
+  replay_sample_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      rows, head_size, capacity, indices, seed, counter, batch, self_b, obj_b, mask_b, act_b, rew_b,
+      nself_b, nobj_b, nmask_b, done_b, indices_out);
+  return check_launch("asvrl_replay_sample");
+}

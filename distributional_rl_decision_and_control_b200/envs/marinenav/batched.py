@@ -1,0 +1,143 @@
+"""Batched, GPU-resident marine-navigation environment (the vectorised face of K1 / K1b).
+
+Thousands of independent ``MarineNavEnv3`` instances (reference:
+rfarl/rfarl/envs/marinenav/env.py:24-333) advanced by ONE kernel launch per step, with the
+Trainer's bookkeeping folded in (rfarl/rfarl/policy/trainer.py:157-172, 240-245):
+deactivation of ASVs that collided or arrived, end-of-episode detection (all deactivated or
+1000 steps) and re-generation of finished scenarios.  State lives in HBM as structure-of-arrays
+``[field][env][robot]``; nothing crosses PCIe unless the caller asks for host copies.
+"""
+import ctypes as C
+
+import torch
+
+from ... import _abi, _lib
+
+
+class BatchedMarineNavEnv:
+    """``n_envs`` environments x ``max_robots`` ASVs on one GPU.
+
+    Observation buffers are ping-ponged: ``obs`` (what the policy acts on, post-reset for
+    finished episodes) and ``next_obs`` views are valid until the next ``step``.
+    """
+
+    def __init__(self, n_envs, num_robots=8, num_obs=10, num_cores=0, min_start_goal_dis=30.0,
+                 device="cuda:0", seed=0, env_offset=0, max_robots=None, max_obs=None,
+                 max_cores=None, params=None, reset_params=None, debug_outputs=False):
+        _lib.lib()  # fail loudly if the CUDA library is missing
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("BatchedMarineNavEnv needs a CUDA device (no CPU fallback)")
+        self.E = int(n_envs)
+        self.RP = int(max_robots or num_robots)
+        self.OP = int(max_obs if max_obs is not None else num_obs)
+        self.CP = int(max_cores if max_cores is not None else num_cores)
+        self.params = params if params is not None else _abi.default_params()
+        self.reset_params = reset_params if reset_params is not None else _lib.default_reset_params()
+        self.seed = int(seed)
+        self.env_offset = int(env_offset)
+        self.total_steps = 0     # batched steps taken (drives the sensor-noise counter)
+        self.episode_counter = 0  # reset launches (drives the scenario counter)
+        with torch.cuda.device(self.device):
+            self.state = _lib.new_state(self.E, self.RP, self.OP, self.CP, self.device)
+            self._outs = [_lib.new_out(self.E, self.RP, self.device, debug=debug_outputs) for _ in range(2)]
+            self._st_ptrs = _lib.state_ptrs(self.state)
+            self._o_ptrs = [_lib.out_ptrs(o) for o in self._outs]
+            self._cur = 0
+            i32 = dict(dtype=torch.int32, device=self.device)
+            self.want_robots = torch.full((self.E,), int(num_robots), **i32)
+            self.want_obs = torch.full((self.E,), int(num_obs), **i32)
+            self.want_cores = torch.full((self.E,), int(num_cores), **i32)
+            self.min_start_goal_dis = torch.full((self.E,), float(min_start_goal_dis),
+                                                 dtype=torch.float32, device=self.device)
+        self.launches = 0
+
+    # ------------------------------------------------------------------ schedule (ENV:75-87)
+    def set_schedule(self, num_robots=None, num_obs=None, num_cores=None, min_start_goal_dis=None):
+        """Curriculum stage applied to episodes generated from now on."""
+        if num_robots is not None:
+            assert 0 < num_robots <= self.RP, "Number of robots is 0!"
+            self.want_robots.fill_(int(num_robots))
+        if num_obs is not None:
+            self.want_obs.fill_(min(int(num_obs), self.OP))
+        if num_cores is not None:
+            self.want_cores.fill_(min(int(num_cores), self.CP))
+        if min_start_goal_dis is not None:
+            self.min_start_goal_dis.fill_(float(min_start_goal_dis))
+
+    # ------------------------------------------------------------------ views
+    @property
+    def out(self):
+        return self._outs[self._cur]
+
+    @property
+    def obs(self):
+        o = self._outs[self._cur]
+        return o["obs_self"], o["obs_objects"], o["obs_mask"]
+
+    # ------------------------------------------------------------------ reset / step
+    def _reset_and_observe(self, mask, out_idx):
+        """K1b on the masked envs, then a perception-only K1 pass on the same envs (ENV:164)."""
+        with torch.cuda.device(self.device):
+            self.episode_counter += 1
+            _lib.env_reset(self.reset_params, self.state, mask, self.want_robots, self.want_cores,
+                           self.want_obs, self.min_start_goal_dis, self.seed, self.episode_counter,
+                           self.OP, self.CP, self.env_offset, st_ptrs=self._st_ptrs)
+            _lib.env_step(self.params, self.state, None, None, self._outs[out_idx], 0, self.OP,
+                          self.CP, seed=self.seed ^ 0x5DEECE66D, step=self.episode_counter,
+                          env_offset=self.env_offset, env_mask=mask, st_ptrs=self._st_ptrs,
+                          o_ptrs=self._o_ptrs[out_idx])
+            self.launches += 2
+
+    def reset(self):
+        """Fresh scenario in every env; returns the observation tensors (device views)."""
+        self._reset_and_observe(None, self._cur)
+        return self.obs
+
+    def step(self, actions, is_continuous_action=True, auto_reset=True):
+        """One action for every ASV of every env.
+
+        actions: CUDA float32 [E, RP, 2] in (-1, 1) (continuous, WAMV:220-223) or int32 [E, RP]
+        ids into the 5x5 thrust-change table (WAMV:146-147).  Returns the out dict of THIS
+        step (next observation, reward, status, env_status, ended); with ``auto_reset`` the
+        finished envs are then re-generated and re-observed in place, so ``self.obs`` is what
+        the policy should act on next while the returned dict's reward/status still describe the
+        transition (use ``step_no_reset`` + ``finish_episodes`` to store next_obs in between).
+        """
+        out = self.step_no_reset(actions, is_continuous_action)
+        if auto_reset:
+            self.finish_episodes()
+        return out
+
+    def step_no_reset(self, actions, is_continuous_action=True):
+        mode = _abi.M_DYNAMICS | _abi.M_AUTO_DEACTIVATE
+        if not is_continuous_action:
+            mode |= _abi.M_DISCRETE
+        nxt = 1 - self._cur
+        with torch.cuda.device(self.device):
+            self.total_steps += 1
+            _lib.env_step(self.params, self.state, actions, None, self._outs[nxt], mode, self.OP,
+                          self.CP, seed=self.seed, step=self.total_steps, env_offset=self.env_offset,
+                          st_ptrs=self._st_ptrs, o_ptrs=self._o_ptrs[nxt])
+            self.launches += 1
+        self._cur = nxt
+        return self._outs[nxt]
+
+    def finish_episodes(self):
+        """Re-generate every env whose episode ended in the last step (TRAINER:172, 240-245) and
+        overwrite its observation rows with the fresh episode's first observation."""
+        self._reset_and_observe(self._outs[self._cur]["ended"], self._cur)
+
+    # ------------------------------------------------------------------ host-facing convenience
+    def step_host(self, actions_pinned, host_out, is_continuous_action=True):
+        """End-to-end call with HOST buffers: pinned actions in, pinned observations / rewards /
+        status out (the call shape a CPU-side caller of the reference's step() would make)."""
+        if not hasattr(self, "_act_dev"):
+            self._act_dev = torch.empty(actions_pinned.shape, dtype=actions_pinned.dtype, device=self.device)
+        self._act_dev.copy_(actions_pinned, non_blocking=True)
+        out = self.step(self._act_dev, is_continuous_action)
+        for k in ("reward", "status"):
+            host_out[k].copy_(out[k], non_blocking=True)
+        for k in ("obs_self", "obs_objects", "obs_mask"):
+            host_out[k].copy_(self.out[k], non_blocking=True)
+        return host_out

@@ -20,8 +20,8 @@
  *    persistent and keeps no mutable global state besides the per-thread error string.
  *  - kernels are enqueued on `stream` (a cudaStream_t passed as void*) and the call
  *    returns without synchronising.
- *  - the same structs are consumed by the CPU oracle (oracle/asv_oracle.c), which is
- *    test infrastructure only, with HOST pointers and float64 arrays.
+ *  - the CPU oracle (oracle/asv_oracle.h, test infrastructure only) mirrors these structs
+ *    with HOST pointers and float64 arrays, and shares asvrl_env_params verbatim.
  */
 #ifndef ASVRL_H_
 #define ASVRL_H_
@@ -30,6 +30,12 @@
 
 #ifdef __cplusplus
 extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define ASVRL_API __attribute__((visibility("default")))
+#else
+#define ASVRL_API
 #endif
 
 #define ASVRL_VERSION 100 /* 0.1.0 */
@@ -160,12 +166,25 @@ typedef struct asvrl_env_out {
                                           (ep_steps BEFORE this step >= max), bit2 any collision
                                           (ENV:194-200), bit3 all reach goal (ENV:186-192);
                                           low two bits != 0 <=> episode over (TRAINER:172) */
+  uint8_t* ended;      /* [E]             1 iff (env_status & 3) != 0; nullable.  Feeds
+                                          asvrl_env_reset(reset_mask) / asvrl_env_step(env_mask)
+                                          directly so the auto-reset needs no host round trip */
 } asvrl_env_out;
 
-int asvrl_version(void);
-const char* asvrl_last_error_string(void);
+/* Counter-based RNG contract (Philox4x32-10, Salmon et al. SC'11), shared by every kernel and
+ * restated by the oracle so that streams are reproducible and invariant to the GPU count:
+ *   key = (seed lo, seed hi)
+ *   ctr = (block | slot<<8 | ego<<16,  global env index,  step lo,  step hi (24 bit) | stream<<24)
+ *   stream: 1 sensor noise, 2 reset, 3 tau, 4 replay sampling
+ *   uniform(word) = ((word >> 8) + 0.5) * 2^-24
+ * Sensor noise of (env, ego, slot, step): block 0 -> two Box-Muller pairs (n_px,n_py)*pos_std,
+ * (n_vx,n_vy)*vel_std; blocks 1..8 -> Best-Fisher von Mises attempts, two per block
+ * ((U,V) = words (0,1) then (2,3), sign = bit 0 of the V word). */
+
+ASVRL_API int asvrl_version(void);
+ASVRL_API const char* asvrl_last_error_string(void);
 /* fills *p with the reference defaults (WAMV:45-126, ENV:33-54) */
-void asvrl_env_default_params(asvrl_env_params* p);
+ASVRL_API void asvrl_env_default_params(asvrl_env_params* p);
 
 /* K1 — replaces MarineNavEnv3.step (ENV:240-333) incl. Robot.update_state/compute_motion
  * (WAMV:204-279), get_velocity (ENV:458-501), get_observations/perception_output
@@ -174,25 +193,51 @@ void asvrl_env_default_params(asvrl_env_params* p);
  *             deactivated robots (the reference passes None, TRAINER:112-114)
  *   noise     nullable [E][RP][OP+RP][5] float injected sensor noise in draw order
  *             (n_px, n_py, n_vx, n_vy already scaled by std; raw von Mises sample w); slot of
- *             obstacle i is i, of robot j is OP+j.  NULL = in-kernel Philox4x32-10 keyed on
- *             (seed; env_offset+env, ego, slot, step).
+ *             obstacle i is i, of robot j is OP+j.  NULL = in-kernel Philox stream above.
+ *   env_mask  nullable [E] uint8: envs with 0 are skipped entirely (nothing read or written);
+ *             used to observe only the freshly reset envs (ENV:164).
  *   env_offset  global index of local env 0 (multi-GPU sharding keeps streams invariant) */
-int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_state* state,
-                   const void* actions, const float* noise, uint64_t seed, uint64_t step,
-                   const asvrl_env_out* out, int n_envs, int max_robots, int max_obs,
-                   int max_cores, int64_t env_offset, uint32_t mode, void* stream);
+ASVRL_API int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_state* state,
+                             const void* actions, const float* noise, const uint8_t* env_mask,
+                             uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,
+                             int max_robots, int max_obs, int max_cores, int64_t env_offset,
+                             uint32_t mode, void* stream);
+
+/* The noise table the NULL-noise path of K1 draws: float [E][RP][OP+RP][5] (test / debug aid;
+ * same device function as K1). */
+ASVRL_API int asvrl_env_noise(const asvrl_env_params* params, uint64_t seed, uint64_t step,
+                              int n_envs, int max_robots, int max_obs, int64_t env_offset,
+                              float* noise_out, void* stream);
+
+/* scenario-generation constants of MarineNavEnv3 (ENV:33-41, 109-110, 126-129, 154-155) */
+typedef struct asvrl_reset_params {
+  double map_w, map_h;        /* 55 x 55 */
+  double start_margin;        /* starts / goals in [2, w-2] x [2, h-2]   ENV:109-110 */
+  double obs_margin;          /* obstacle centres in [5, w-5] x [5, h-5] ENV:154 */
+  double clear_r;             /* 10   ENV:40 */
+  double core_r;              /* 0.5  ENV:35 */
+  double v_rel_max, p;        /* 1.0, 0.8  ENV:36-37 */
+  double v_min, v_max;        /* vortex edge speed range [3,3]  ENV:38 */
+  double obs_r_min, obs_r_max;/* [1,1]  ENV:39 */
+  int32_t max_tries;          /* 500  ENV:107,124,152 */
+  int32_t reserved;
+} asvrl_reset_params;
+ASVRL_API void asvrl_reset_default_params(asvrl_reset_params* p);
 
 /* K1b — replaces MarineNavEnv3.reset (ENV:72-176) for every env with reset_mask != 0
  * (NULL = all): rejection-samples starts/goals, cores, obstacles with the reference's
- * acceptance rules (ENV:358-456), zeroes velocity/thrust, draws theta0.  Counts requested per
- * env come from want_robots/want_cores/want_obs [E] (the curriculum lookup ENV:75-87 is done by
- * the host).  Perception of the fresh state is a following asvrl_env_step(mode=0). */
-int asvrl_env_reset(const asvrl_env_params* params, const asvrl_env_state* state,
-                    const uint8_t* reset_mask, const int32_t* want_robots,
-                    const int32_t* want_cores, const int32_t* want_obs,
-                    const float* min_start_goal_dis /* [E] */, uint64_t seed, uint64_t episode,
-                    int n_envs, int max_robots, int max_obs, int max_cores, int64_t env_offset,
-                    void* stream);
+ * acceptance rules (ENV:358-456) over a counter-indexed candidate sequence (candidate t of a
+ * class is accepted iff it passes the checks against everything accepted before it, exactly
+ * the sequential loop of the reference; at most max_tries candidates per class), zeroes
+ * velocity/thrust, draws theta0 (ENV:166-176).  Counts requested per env come from
+ * want_robots/want_cores/want_obs [E] (the curriculum lookup ENV:75-87 is done by the host).
+ * Perception of the fresh state is a following asvrl_env_step(mode=0, env_mask=reset_mask). */
+ASVRL_API int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env_state* state,
+                              const uint8_t* reset_mask, const int32_t* want_robots,
+                              const int32_t* want_cores, const int32_t* want_obs,
+                              const float* min_start_goal_dis /* [E] */, uint64_t seed,
+                              uint64_t episode, int n_envs, int max_robots, int max_obs,
+                              int max_cores, int64_t env_offset, void* stream);
 
 /* Replay rows are dense float32[ASVRL_ROW] records: RB:22-69 + AGENT:360-368,387-392 */
 #define ASVRL_ROW_SELF 0     /* 7  */
@@ -208,42 +253,50 @@ int asvrl_env_reset(const asvrl_env_params* params, const asvrl_env_state* state
 
 /* K2a — replaces ReplayBuffer.add over a whole batched step (RB:22-24, TRAINER:157-166):
  * appends one row per ASV whose status has neither ASVRL_S_WAS_DEACTIVATED nor
- * ASVRL_INFO_ABSENT, in (env, robot) order, at ring position *head (device counters
- * head_size[0] = total rows ever written, head_size[1] = rows valid = min(total, capacity)). */
-int asvrl_replay_push(float* rows, int64_t capacity, uint64_t* head_size,
-                      const float* obs_self, const float* obs_objects, const float* obs_mask,
-                      const void* actions, int discrete, const float* reward,
-                      const float* next_self, const float* next_objects, const float* next_mask,
-                      const uint32_t* status, int n_asv, void* stream);
+ * ASVRL_INFO_ABSENT, in (env, robot) order (deterministic), at the ring position given by the
+ * device counters head_size[0] = rows ever written, head_size[1] = rows valid = min(total,
+ * capacity).  workspace: uint32[ceil(n_asv/256) + 4], zero-initialised once by the caller and
+ * left clean by every call. */
+ASVRL_API int asvrl_replay_push(float* rows, int64_t capacity, unsigned long long* head_size,
+                                const float* obs_self, const float* obs_objects,
+                                const float* obs_mask, const void* actions, int discrete,
+                                const float* reward, const float* next_self,
+                                const float* next_objects, const float* next_mask,
+                                const uint32_t* status, int n_asv, uint32_t* workspace,
+                                void* stream);
 
 /* K2b — replaces ReplayBuffer.sample + state_batch + Agent.state_to_tensor (RB:26-69,
- * AGENT:387-392): draws `batch` distinct uniform row indices (keyed Feistel permutation of
- * [0,size), i.e. sampling without replacement like random.sample, RB:28) or takes them from
- * `indices` (int64[batch], nullable) and gathers into dense tensors. */
-int asvrl_replay_sample(const float* rows, const uint64_t* head_size, int64_t capacity,
-                        const int64_t* indices, uint64_t seed, uint64_t counter, int batch,
-                        float* self_b, float* obj_b, float* mask_b, float* act_b, float* rew_b,
-                        float* nself_b, float* nobj_b, float* nmask_b, float* done_b,
-                        int64_t* indices_out /* nullable */, void* stream);
+ * AGENT:387-392): draws `batch` DISTINCT uniform row indices (a keyed Feistel permutation of
+ * [0,size) walked from 0, i.e. sampling without replacement like random.sample, RB:28) or
+ * takes them from `indices` (int64[batch], nullable) and gathers into dense tensors
+ * self [B][7], obj [B][5][5], mask [B][5], act [B][2], rew [B], done [B].  Requires
+ * size >= 1 (and size >= batch for distinct indices; otherwise indices repeat modulo size). */
+ASVRL_API int asvrl_replay_sample(const float* rows, const unsigned long long* head_size,
+                                  int64_t capacity, const int64_t* indices, uint64_t seed,
+                                  uint64_t counter, int batch, float* self_b, float* obj_b,
+                                  float* mask_b, float* act_b, float* rew_b, float* nself_b,
+                                  float* nobj_b, float* nmask_b, float* done_b,
+                                  int64_t* indices_out /* nullable */, void* stream);
 
 /* K3 — replaces Critic.calc_cos / IQN_Policy.calc_cos (ACIQN:410-426, IQN:56-72):
- * tau = U(0,1) * cvar (Philox keyed on seed,counter) unless tau_in is given; cos_out[b][n][i] =
- * cos(tau * float32(pi*i)), i < n_cos.  tau_out [B][N], cos_out [B][N][n_cos]. */
-int asvrl_iqn_tau_cos(const float* tau_in /* nullable */, uint64_t seed, uint64_t counter,
-                      float cvar, int batch, int n_tau, int n_cos, float* tau_out,
-                      float* cos_out, void* stream);
+ * tau = U(0,1) * cvar (Philox stream 3 keyed on seed, counter) unless tau_in is given;
+ * cos_out[b][n][i] = cosf(tau * float32(pi*i)), i < n_cos.  tau_out [B][N] (nullable),
+ * cos_out [B][N][n_cos]. */
+ASVRL_API int asvrl_iqn_tau_cos(const float* tau_in /* nullable */, uint64_t seed,
+                                uint64_t counter, float cvar, int batch, int n_tau, int n_cos,
+                                float* tau_out, float* cos_out, void* stream);
 
 /* K4 — replaces the loss core of Agent.train_AC_IQN / train_IQN (AGENT:401-412, 455-467,
  * 701-707) and its autograd backward:
  *   T_bj = r_b + gamma (1 - d_b) Z'_bj ; delta_bij = T_bj - Z_bi ;
- *   loss_b = (1/N') sum_j sum_i |tau_bi - 1[delta<0]| * huber_kappa(delta) / kappa... (kappa=1)
+ *   loss_b = (1/N') sum_j sum_i |tau_bi - 1[delta<0]| * huber_kappa(delta) / kappa
  *   loss   = mean_b loss_b ;  grad_z_bi = dloss/dZ_bi.
  * z [B][N], tau [B][N], z_next [B][N'], r [B], done [B]; outputs loss_per_sample [B],
  * grad_z [B][N], loss [1].  workspace: one zero-initialised uint32 (left zero on completion). */
-int asvrl_qhuber_fwd_bwd(const float* z, const float* tau, const float* z_next, const float* r,
-                         const float* done, float gamma, float kappa, int batch, int n, int n_next,
-                         float* loss_per_sample, float* grad_z, float* loss, uint32_t* workspace,
-                         void* stream);
+ASVRL_API int asvrl_qhuber_fwd_bwd(const float* z, const float* tau, const float* z_next,
+                                   const float* r, const float* done, float gamma, float kappa,
+                                   int batch, int n, int n_next, float* loss_per_sample,
+                                   float* grad_z, float* loss, uint32_t* workspace, void* stream);
 
 #ifdef __cplusplus
 }

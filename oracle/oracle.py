@@ -35,7 +35,7 @@ class _State(C.Structure):
 
 
 class _Out(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in _abi.OUT_FIELDS] + [("margin_perc", C.c_void_p),
+    _fields_ = [(n, C.c_void_p) for n in _abi.OUT_FIELDS if n != "ended"] + [("margin_perc", C.c_void_p),
                                                               ("margin_colregs", C.c_void_p)]
 
 

@@ -11,8 +11,8 @@ struct EnvConsts {
   int n_sub;
   int max_ep;
   // thrust, WAMV:84-87, 218-229 (deltas already multiplied by dt*N)
-  float min_thrust, max_thrust, act_scale;
-  float dl[5], dr[5];
+  float min_thrust, max_thrust;
+  double act_scale, dl[5], dr[5];
   // rigid body + hydrodynamics, WAMV:103-125, 242-248
   float m, xDotU, yDotV, yDotR;
   float xU, xUU, yV, yVV, yR, yRV, yVR, yRR, nR, nRR, nV, nVV, nRV, nVR;

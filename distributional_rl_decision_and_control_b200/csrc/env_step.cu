@@ -8,15 +8,17 @@
 //   envs/marinenav/vehicles/wamv.py:324-423  COLREGs zone tests and turn angle
 //   policy/trainer.py:168-170            deactivation, when ASVRL_M_AUTO_DEACTIVATE
 //
-// Mapping.  A CTA owns EPB consecutive environments (EPB*RP ~ one warp of ASVs):
-//   phase 0  the CTA stages the env's buoy and vortex tables in shared memory;
-//   phase A  one thread per ASV integrates the 3-DOF model for the 10 sub-steps (pose carried in
-//            fp64 registers so the progress reward does not cancel), SoA loads
-//            and stores are coalesced over the robot-fastest layout;
-//   phase B  the (ego, candidate) pairs of the CTA's envs are flattened over ALL threads: noise
-//            (injected table or in-kernel Philox), detection / collision predicates in fp64,
-//            body-frame observation and sort key into a shared-memory candidate table;
-//   phase C  one thread per ego: stable top-5 by key, COLREGs, reward / done / info;
+// Mapping.  A 128-thread CTA owns EPB consecutive environments (EPB*RP <= 32 ASVs):
+//   phase 0  the CTA stages the envs' buoy / vortex tables and pre-step poses in shared memory;
+//   phase A  warp 0, one lane per ASV, integrates the 3-DOF model for the 10 sub-steps (pose in
+//            fp64 registers so the progress reward does not cancel); SoA loads and
+//            stores are coalesced over the robot-fastest layout;
+//   phase A' warps 1-3 CONCURRENTLY draw the Philox sensor noise (state independent) for the
+//            pairs that can end up in range, hiding the serial integration chain;
+//   phase B  the (ego, candidate) pairs are flattened over all threads: detection / collision
+//            predicates in fp64, body-frame observation and sort key into shared memory;
+//   phase B2 every detected pair computes its stable rank among its ego's keys (top-5);
+//   phase C  COLREGs per (ego, kept object) in parallel, then reward / done / info per ego;
 //   phase D  the CTA writes the padded observation rows back with coalesced stores.
 // The kernel is instruction-issue bound (about 1e4 thread instructions per 280 algorithmic
 // bytes); HBM traffic is one pass over state in, state + observations out.
@@ -46,55 +48,64 @@ struct OutPtrs {
   uint8_t* ended;
 };
 
+constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
+
 // shared-memory carve-up, identical on host (size) and device (pointers)
 struct Smem {
   double *px, *py, *key;
-  float *c, *s, *vx, *vy, *vz, *Tl, *Tr, *gx, *gy, *rew, *cand, *st_obj, *st_self, *st_mask;
+  float *c, *s, *vx, *vy, *vz, *Tl, *Tr, *gx, *gy, *rew, *ox, *oy, *osp;
+  float *cand, *noise, *st_obj, *st_self, *st_mask, *cphi;
   uint32_t *fl0, *fl, *det_lo, *det_hi;
+  uint8_t *have, *chit;
   int *nr, *no, *nc, *ep, *ok;
   float4 *obst, *cores;
   size_t bytes;
 };
 
-__host__ __device__ inline Smem carve(char* base, int EPB, int RP, int OP, int CP) {
+__host__ __device__ inline Smem carve(char* base, int EPB, int RP, int OP, int CP, bool inject) {
   Smem m;
-  const int A = EPB * RP, S = OP + RP, SK = S | 1;
+  const size_t A = (size_t)EPB * RP, S = OP + RP, SK = S | 1;
   size_t off = 0;
-  auto take = [&](size_t n, size_t elem) { size_t o = off; off += ((n * elem + 15) / 16) * 16; return base + o; };
-  m.px = (double*)take(A, 8); m.py = (double*)take(A, 8);
-  m.key = (double*)take((size_t)A * SK, 8);
-  m.obst = (float4*)take((size_t)EPB * (OP > 0 ? OP : 1), 16);
-  m.cores = (float4*)take((size_t)EPB * (CP > 0 ? CP : 1), 16);
-  m.c = (float*)take(A, 4); m.s = (float*)take(A, 4);
-  m.vx = (float*)take(A, 4); m.vy = (float*)take(A, 4); m.vz = (float*)take(A, 4);
-  m.Tl = (float*)take(A, 4); m.Tr = (float*)take(A, 4);
-  m.gx = (float*)take(A, 4); m.gy = (float*)take(A, 4); m.rew = (float*)take(A, 4);
-  m.cand = (float*)take((size_t)A * S * 5, 4);
-  m.st_obj = (float*)take((size_t)A * 25, 4);
-  m.st_self = (float*)take((size_t)A * 7, 4);
-  m.st_mask = (float*)take((size_t)A * 5, 4);
-  m.fl0 = (uint32_t*)take(A, 4); m.fl = (uint32_t*)take(A, 4);
-  m.det_lo = (uint32_t*)take(A, 4); m.det_hi = (uint32_t*)take(A, 4);
-  m.nr = (int*)take(EPB, 4); m.no = (int*)take(EPB, 4); m.nc = (int*)take(EPB, 4);
-  m.ep = (int*)take(EPB, 4); m.ok = (int*)take(EPB, 4);
+#define TAKE(ptr, type, n) ptr = (type*)(base + off); off += (((size_t)(n) * sizeof(type)) + 15) & ~(size_t)15
+  TAKE(m.px, double, A); TAKE(m.py, double, A); TAKE(m.key, double, A * SK);
+  TAKE(m.obst, float4, EPB * (OP > 0 ? OP : 1)); TAKE(m.cores, float4, EPB * (CP > 0 ? CP : 1));
+  TAKE(m.c, float, A); TAKE(m.s, float, A); TAKE(m.vx, float, A); TAKE(m.vy, float, A);
+  TAKE(m.vz, float, A); TAKE(m.Tl, float, A); TAKE(m.Tr, float, A); TAKE(m.gx, float, A);
+  TAKE(m.gy, float, A); TAKE(m.rew, float, A); TAKE(m.ox, float, A); TAKE(m.oy, float, A);
+  TAKE(m.osp, float, A);
+  TAKE(m.cand, float, A * S * 5);
+  TAKE(m.noise, float, inject ? 4 : A * S * 5);
+  TAKE(m.st_obj, float, A * 25); TAKE(m.st_self, float, A * 7); TAKE(m.st_mask, float, A * 5);
+  TAKE(m.cphi, float, A * 5);
+  TAKE(m.fl0, uint32_t, A); TAKE(m.fl, uint32_t, A); TAKE(m.det_lo, uint32_t, A); TAKE(m.det_hi, uint32_t, A);
+  TAKE(m.have, uint8_t, A * S); TAKE(m.chit, uint8_t, A * 5);
+  TAKE(m.nr, int, EPB); TAKE(m.no, int, EPB); TAKE(m.nc, int, EPB); TAKE(m.ep, int, EPB); TAKE(m.ok, int, EPB);
+#undef TAKE
   m.bytes = off;
   return m;
 }
 
 // ENV:458-501.  All cores contribute (the reference's `continue` is a no-op).
-__device__ __forceinline__ void current_at(const EnvConsts& k, const float4* cores, int nc, float x,
-                                           float y, float& cx, float& cy) {
-  cx = k.drift_vx;
-  cy = k.drift_vy;
+// tangent * speed = (-ry, rx) * dir * speed / d, and speed / d is Gamma/(2 pi r^2) inside the
+// core (solid body) and Gamma/(2 pi d^2) outside: no square root, one reciprocal per core.
+// The offsets core - p are formed in fp64 from the fp64 pose: the 1/d^2 field amplifies the fp32
+// rounding of a ~50 m coordinate by 1/d near a core.
+__device__ __forceinline__ void current_at(const EnvConsts& k, const float4* cores, int nc, double x,
+                                           double y, float& cx, float& cy) {
+  float ax = 0.0f, ay = 0.0f;
+  const float r2 = k.core_r * k.core_r;
+#pragma unroll 4
   for (int i = 0; i < nc; ++i) {
-    float4 co = cores[i];
-    float rx = co.x - x, ry = co.y - y;
-    float d = sqrtf(rx * rx + ry * ry);
-    float speed = (d <= k.core_r) ? co.w * k.solid_k * d : co.w * k.inv_2pi / d;  // ENV:497-501
-    float f = speed / d * co.z;  // co.z = +1 clockwise, -1 counter-clockwise, ENV:483-487
-    cx -= ry * f;
-    cy += rx * f;
+    const float4 co = cores[i];
+    const float rx = (float)((double)co.x - x), ry = (float)((double)co.y - y);
+    const float d2 = rx * rx + ry * ry;
+    const float g = co.w * co.z;  // signed circulation: +clockwise, -counter-clockwise (ENV:483-487)
+    const float f = d2 <= r2 ? g * k.solid_k : __fdividef(g * k.inv_2pi, d2);  // ENV:497-501
+    ax -= ry * f;
+    ay += rx * f;
   }
+  cx = ax + k.drift_vx;
+  cy = ay + k.drift_vy;
 }
 
 __device__ __forceinline__ float wrap_to_pi(float a) {  // WAMV:425-434
@@ -107,285 +118,359 @@ __device__ __forceinline__ float wrap_to_pi(float a) {  // WAMV:425-434
 // WAMV:398-423 for one kept object o = [px,py,vx,vy,r] (ego frame); w = ego velocity in ego frame
 __device__ __forceinline__ bool colregs_one(const EnvConsts& k, const float* o, float w0, float w1,
                                             float& phi) {
-  float so2 = o[2] * o[2] + o[3] * o[3];
+  const float so2 = o[2] * o[2] + o[3] * o[3];
   if (sqrtf(so2) < k.min_speed) return false;                    // WAMV:400-402
-  float se = sqrtf(w0 * w0 + w1 * w1);
+  const float se = sqrtf(w0 * w0 + w1 * w1);
   if (se < k.min_speed) return false;                            // WAMV:404-407
-  float inv = rsqrtf(so2);
-  float ca = o[2] * inv, sa = o[3] * inv;                        // R(atan2(vy,vx)), WAMV:328-330
-  float epx = -(ca * o[0] + sa * o[1]), epy = -(-sa * o[0] + ca * o[1]);  // WAMV:334
-  float evx = ca * w0 + sa * w1, evy = -sa * w0 + ca * w1;                // WAMV:339
-  float ang = atan2f(evy, evx);
+  const float inv = rsqrtf(so2);
+  const float ca = o[2] * inv, sa = o[3] * inv;                  // R(atan2(vy,vx)), WAMV:328-330
+  const float epx = -(ca * o[0] + sa * o[1]), epy = -(-sa * o[0] + ca * o[1]);  // WAMV:334
+  const float evx = ca * w0 + sa * w1, evy = -sa * w0 + ca * w1;                // WAMV:339
+  const float ang = atan2f(evy, evx);
   const float PI = 3.14159265358979f;
-  bool tri = (epy - k.lc_y1) > k.lc_grad * (epx - k.lc_x1);      // WAMV:348-351
-  bool left = epx >= k.lc_x0 && epx <= k.lc_x1 && epy >= k.lc_y0 && epy <= 0.0f && !tri &&
-              ang >= 0.25f * PI && ang <= 0.75f * PI;            // WAMV:345-357
-  bool head = epx >= 0.0f && epx <= k.head_on_x && epy >= -k.head_on_half_y &&
-              epy <= k.head_on_half_y && fabsf(ang) > 0.75f * PI;  // WAMV:365-372
+  const bool tri = (epy - k.lc_y1) > k.lc_grad * (epx - k.lc_x1);  // WAMV:348-351
+  const bool left = epx >= k.lc_x0 && epx <= k.lc_x1 && epy >= k.lc_y0 && epy <= 0.0f && !tri &&
+                    ang >= 0.25f * PI && ang <= 0.75f * PI;        // WAMV:345-357
+  const bool head = epx >= 0.0f && epx <= k.head_on_x && epy >= -k.head_on_half_y &&
+                    epy <= k.head_on_half_y && fabsf(ang) > 0.75f * PI;  // WAMV:365-372
   if (!(left || head)) return false;
   // WAMV:379-396; NaN (dist < base_1) propagates and fails phi > 0 like the reference
-  float dist = sqrtf(o[0] * o[0] + o[1] * o[1]);
-  float base_1 = o[4] + 1.0f;
-  float add_1 = asinf(base_1 / dist);
-  float add_2 = atan2f(k.robot_r, sqrtf(dist * dist - base_1 * base_1));
+  const float dist = sqrtf(o[0] * o[0] + o[1] * o[1]);
+  const float base_1 = o[4] + 1.0f;
+  const float add_1 = asinf(base_1 / dist);
+  const float add_2 = atan2f(k.robot_r, sqrtf(dist * dist - base_1 * base_1));
   phi = wrap_to_pi(wrap_to_pi(atan2f(o[1], o[0]) + add_1 + add_2) - atan2f(w1, w0));
   return phi > 0.0f;                                             // WAMV:421
 }
 
+// candidate slot -> (live, true position, radius, stale velocity) from the shared tables
+struct Cand {
+  bool live;
+  double px, py, rt;
+  float vx, vy;
+};
+__device__ __forceinline__ Cand candidate(const EnvConsts& k, const Smem& m, int el, int r, int sl,
+                                          int RP, int OP) {
+  Cand c;
+  c.vx = 0.0f; c.vy = 0.0f; c.px = 0.0; c.py = 0.0; c.rt = 0.0;
+  if (sl < OP) {  // static obstacles, WAMV:465-483
+    c.live = sl < m.no[el];
+    const float4 ob = m.obst[el * OP + sl];
+    c.px = ob.x; c.py = ob.y; c.rt = ob.z;
+  } else {  // other robots still on the map, WAMV:486-510
+    const int j = sl - OP, b = el * RP + j;
+    c.live = j != r && !(m.fl0[b] & ASVRL_F_DEACTIVATED);
+    c.px = m.px[b]; c.py = m.py[b]; c.vx = m.vx[b]; c.vy = m.vy[b]; c.rt = k.robot_r_d;
+  }
+  return c;
+}
+
 template <bool INJECT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(TPB, 8)
 env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* __restrict__ actions,
                 const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
                 uint64_t step, OutPtrs out, int E, int RP, int OP, int CP, int64_t env_offset,
                 uint32_t mode, int EPB) {
   extern __shared__ __align__(16) char smem_raw[];
-  const Smem m = carve(smem_raw, EPB, RP, OP, CP);
+  const Smem m = carve(smem_raw, EPB, RP, OP, CP, INJECT);
   const int tid = threadIdx.x;
-  const int A = EPB * RP, S = OP + RP, SK = S | 1;
+  const int A = EPB * RP, S = OP + RP, SK = S | 1, NP = A * S;
   const int e0 = blockIdx.x * EPB;
   const bool dyn = mode & ASVRL_M_DYNAMICS;
 
-  // ---- phase 0: per-env tables ----
+  // ---- phase 0: per-env tables and the pre-step poses (for the noise prefetch filter) ----
   if (tid < EPB) {
-    int e = e0 + tid;
-    bool v = e < E && (!env_mask || env_mask[e]);
+    const int e = e0 + tid;
+    const bool v = e < E && (!env_mask || env_mask[e]);
     m.ok[tid] = v;
     m.nr[tid] = v ? min(st.n_robots[e], RP) : 0;
     m.no[tid] = v ? min(st.n_obs[e], OP) : 0;
     m.nc[tid] = v ? min(st.n_cores[e], CP) : 0;
     m.ep[tid] = v ? st.ep_steps[e] : 0;
   }
-  for (int i = tid; i < EPB * OP; i += blockDim.x) {
-    int e = e0 + i / OP;
-    m.obst[i] = (e < E && (!env_mask || env_mask[e])) ? st.obstacles[(size_t)e * OP + i % OP] : make_float4(0, 0, 0, 0);
-  }
-  for (int i = tid; i < EPB * CP; i += blockDim.x) {
-    int e = e0 + i / CP;
-    m.cores[i] = (e < E && (!env_mask || env_mask[e])) ? st.cores[(size_t)e * CP + i % CP] : make_float4(0, 0, 0, 0);
-  }
   __syncthreads();
-
-  // ---- phase A: dynamics, one thread per ASV ----
+  for (int i = tid; i < EPB * OP; i += TPB) {
+    const int el = i / OP;
+    m.obst[i] = m.ok[el] ? st.obstacles[(size_t)(e0 + el) * OP + (i - el * OP)] : make_float4(0, 0, 0, 0);
+  }
+  for (int i = tid; i < EPB * CP; i += TPB) {
+    const int el = i / CP;
+    m.cores[i] = m.ok[el] ? st.cores[(size_t)(e0 + el) * CP + (i - el * CP)] : make_float4(0, 0, 0, 0);
+  }
   if (tid < A) {
     const int el = tid / RP, r = tid - el * RP;
-    const int e = e0 + el;
     const bool present = m.ok[el] && r < m.nr[el];
-    const size_t g = (size_t)e * RP + r;
-    double x = 0, y = 0, th = 0;
-    float vr0 = 0, vr1 = 0, vr2 = 0, v0 = 0, v1 = 0, v2 = 0, Tl = 0, Tr = 0, gx = 0, gy = 0;
-    uint32_t f = 0;
-    float rew = 0.0f;
-    if (present) {
-      x = st.x[g]; y = st.y[g]; th = st.theta[g];
-      vr0 = st.velr_x[g]; vr1 = st.velr_y[g]; vr2 = st.velr_r[g];
-      v0 = st.vel_x[g]; v1 = st.vel_y[g]; v2 = st.vel_r[g];
-      Tl = st.thrust_l[g]; Tr = st.thrust_r[g];
-      gx = st.goal_x[g]; gy = st.goal_y[g];
-      f = st.flags[g];
-    }
-    if (present && dyn && !(f & ASVRL_F_DEACTIVATED)) {
-      float dl, dr;
-      if (mode & ASVRL_M_DISCRETE) {  // WAMV:146-147, 225: id = 5*iL + iR
-        int a = ((const int32_t*)actions)[g];
-        a = min(max(a, 0), 24);
-        dl = k.dl[a / 5];
-        dr = k.dr[a % 5];
-      } else {  // WAMV:220-223
-        float2 a = ((const float2*)actions)[g];
-        dl = a.x * k.act_scale;
-        dr = a.y * k.act_scale;
+    const size_t g = (size_t)(e0 + el) * RP + r;
+    m.ox[tid] = present ? st.x[g] : 0.0f;
+    m.oy[tid] = present ? st.y[g] : 0.0f;
+    float sp = 0.0f;
+    if (present) { const float a = st.vel_x[g], b = st.vel_y[g]; sp = sqrtf(a * a + b * b); }
+    m.osp[tid] = sp;
+    m.fl0[tid] = present ? st.flags[g] : (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
+  }
+  for (int p = tid; p < NP; p += TPB) m.have[p] = 0;
+  __syncthreads();
+
+  if (tid < 32) {
+    // ---- phase A (warp 0): dynamics, one lane per ASV ----
+    if (tid < A) {
+      const int el = tid / RP, r = tid - el * RP;
+      const int e = e0 + el;
+      const bool present = m.ok[el] && r < m.nr[el];
+      const size_t g = (size_t)e * RP + r;
+      double x = 0, y = 0, th = 0;
+      float vr0 = 0, vr1 = 0, vr2 = 0, v0 = 0, v1 = 0, v2 = 0, Tl = 0, Tr = 0, gx = 0, gy = 0;
+      const uint32_t f = m.fl0[tid];
+      float rew = 0.0f;
+      if (present) {
+        x = m.ox[tid]; y = m.oy[tid]; th = st.theta[g];
+        vr0 = st.velr_x[g]; vr1 = st.velr_y[g]; vr2 = st.velr_r[g];
+        v0 = st.vel_x[g]; v1 = st.vel_y[g]; v2 = st.vel_r[g];
+        Tl = st.thrust_l[g]; Tr = st.thrust_r[g];
+        gx = st.goal_x[g]; gy = st.goal_y[g];
       }
-      const float4* cores = m.cores + el * CP;
-      const int nc = m.nc[el];
-      double dxg = (double)gx - x, dyg = (double)gy - y;
-      const double dis_before = sqrt(dxg * dxg + dyg * dyg);  // ENV:254
-      const double TWO_PI = 6.283185307179586;
-      for (int idx = 0; idx < k.n_sub; ++idx) {  // ENV:257-260
-        float cx, cy;
-        current_at(k, cores, nc, (float)x, (float)y, cx, cy);
-        v0 = vr0 + cx; v1 = vr1 + cy; v2 = vr2;  // WAMV:201-202
-        x += (double)(v0 * k.dt);                // WAMV:207-210
-        y += (double)(v1 * k.dt);
-        th += (double)(v2 * k.dt);
-        while (th < 0.0) th += TWO_PI;           // WAMV:213-216
-        while (th >= TWO_PI) th -= TWO_PI;
-        if (idx == 0) {                          // WAMV:218-229
-          Tl = fminf(fmaxf(Tl + dl, k.min_thrust), k.max_thrust);
-          Tr = fminf(fmaxf(Tr + dr, k.min_thrust), k.max_thrust);
+      if (present && dyn && !(f & ASVRL_F_DEACTIVATED)) {
+        // thrust increments in fp64: T + a*500 cancels when the thruster reverses
+        double dl, dr;
+        if (mode & ASVRL_M_DISCRETE) {  // WAMV:146-147, 225: id = 5*iL + iR
+          int a = ((const int32_t*)actions)[g];
+          a = min(max(a, 0), 24);
+          dl = k.dl[a / 5];
+          dr = k.dr[a % 5];
+        } else {  // WAMV:220-223
+          const float2 a = ((const float2*)actions)[g];
+          dl = (double)a.x * k.act_scale;
+          dr = (double)a.y * k.act_scale;
         }
-        // compute_motion, WAMV:233-279
-        float s, c;
-        sincosf((float)th, &s, &c);
-        float u_r = c * vr0 + s * vr1, v_r = -s * vr0 + c * vr1;
-        float u = c * v0 + s * v1, v = -s * v0 + c * v1;
-        float rr = v2;
-        float a = k.yDotV * v_r + k.yDotR * rr;
-        float au = fabsf(u_r), av = fabsf(v_r), ar = fabsf(rr);
-        float n0 = (-k.xU - k.xUU * au) * u_r + a * rr;
-        float n1 = (-k.yV - k.yVV * av - k.yRV * ar) * v_r +
-                   (-k.xDotU * u_r - k.yR - k.yVR * av - k.yRR * ar) * rr;
-        float n2 = -a * u_r + (k.xDotU * u_r - k.nV - k.nVV * av - k.nRV * ar) * v_r +
-                   (-k.nR - k.nVR * av - k.nRR * ar) * rr;
-        float Fxl = Tl * k.cl, Fyl = Tl * k.sl, Fxr = Tr * k.cr, Fyr = Tr * k.sr;
-        float b0 = k.m * rr * v - n0 + (Fxl + Fxr);
-        float b1 = -k.m * rr * u - n1 + (Fyl + Fyr);
-        float b2 = -n2 + (Fxl * k.half_w - Fyl * k.half_l - Fxr * k.half_w - Fyr * k.half_l);
-        u_r += (k.Ainv[0] * b0 + k.Ainv[1] * b1 + k.Ainv[2] * b2) * k.dt;
-        v_r += (k.Ainv[3] * b0 + k.Ainv[4] * b1 + k.Ainv[5] * b2) * k.dt;
-        rr += (k.Ainv[6] * b0 + k.Ainv[7] * b1 + k.Ainv[8] * b2) * k.dt;
-        vr0 = c * u_r - s * v_r;
-        vr1 = s * u_r + c * v_r;
-        vr2 = rr;
+        const float4* cores = m.cores + el * CP;
+        const int nc = m.nc[el];
+        double dxg = (double)gx - x, dyg = (double)gy - y;
+        const double dis_before = sqrt(dxg * dxg + dyg * dyg);  // ENV:254
+        const double TWO_PI = 6.283185307179586;
+        for (int idx = 0; idx < k.n_sub; ++idx) {  // ENV:257-260
+          float cx, cy;
+          current_at(k, cores, nc, x, y, cx, cy);
+          v0 = vr0 + cx; v1 = vr1 + cy; v2 = vr2;  // WAMV:201-202
+          x += (double)(v0 * k.dt);                // WAMV:207-210
+          y += (double)(v1 * k.dt);
+          th += (double)(v2 * k.dt);
+          while (th < 0.0) th += TWO_PI;           // WAMV:213-216
+          while (th >= TWO_PI) th -= TWO_PI;
+          if (idx == 0) {                          // WAMV:218-229
+            Tl = fminf(fmaxf((float)((double)Tl + dl), k.min_thrust), k.max_thrust);
+            Tr = fminf(fmaxf((float)((double)Tr + dr), k.min_thrust), k.max_thrust);
+          }
+          // compute_motion, WAMV:233-279
+          float s, c;
+          sincosf((float)th, &s, &c);
+          float u_r = c * vr0 + s * vr1, v_r = -s * vr0 + c * vr1;
+          const float u = c * v0 + s * v1, v = -s * v0 + c * v1;
+          float rr = v2;
+          const float a = k.yDotV * v_r + k.yDotR * rr;
+          const float au = fabsf(u_r), av = fabsf(v_r), ar = fabsf(rr);
+          const float n0 = (-k.xU - k.xUU * au) * u_r + a * rr;
+          const float n1 = (-k.yV - k.yVV * av - k.yRV * ar) * v_r +
+                           (-k.xDotU * u_r - k.yR - k.yVR * av - k.yRR * ar) * rr;
+          const float n2 = -a * u_r + (k.xDotU * u_r - k.nV - k.nVV * av - k.nRV * ar) * v_r +
+                           (-k.nR - k.nVR * av - k.nRR * ar) * rr;
+          const float Fxl = Tl * k.cl, Fyl = Tl * k.sl, Fxr = Tr * k.cr, Fyr = Tr * k.sr;
+          const float b0 = k.m * rr * v - n0 + (Fxl + Fxr);
+          const float b1 = -k.m * rr * u - n1 + (Fyl + Fyr);
+          const float b2 = -n2 + (Fxl * k.half_w - Fyl * k.half_l - Fxr * k.half_w - Fyr * k.half_l);
+          u_r += (k.Ainv[0] * b0 + k.Ainv[1] * b1 + k.Ainv[2] * b2) * k.dt;
+          v_r += (k.Ainv[3] * b0 + k.Ainv[4] * b1 + k.Ainv[5] * b2) * k.dt;
+          rr += (k.Ainv[6] * b0 + k.Ainv[7] * b1 + k.Ainv[8] * b2) * k.dt;
+          vr0 = c * u_r - s * v_r;
+          vr1 = s * u_r + c * v_r;
+          vr2 = rr;
+        }
+        dxg = (double)gx - x; dyg = (double)gy - y;
+        const double dis_after = sqrt(dxg * dxg + dyg * dyg);
+        rew = k.timestep_penalty + (float)(dis_before - dis_after);  // ENV:271-277
+        st.x[g] = (float)x; st.y[g] = (float)y; st.theta[g] = (float)th;
+        st.velr_x[g] = vr0; st.velr_y[g] = vr1; st.velr_r[g] = vr2;
+        st.vel_x[g] = v0; st.vel_y[g] = v1; st.vel_r[g] = v2;
+        st.thrust_l[g] = Tl; st.thrust_r[g] = Tr;
       }
-      dxg = (double)gx - x; dyg = (double)gy - y;
-      const double dis_after = sqrt(dxg * dxg + dyg * dyg);
-      rew = k.timestep_penalty + (float)(dis_before - dis_after);  // ENV:271-277
-      st.x[g] = (float)x; st.y[g] = (float)y; st.theta[g] = (float)th;
-      st.velr_x[g] = vr0; st.velr_y[g] = vr1; st.velr_r[g] = vr2;
-      st.vel_x[g] = v0; st.vel_y[g] = v1; st.vel_r[g] = v2;
-      st.thrust_l[g] = Tl; st.thrust_r[g] = Tr;
+      // heading of the pose everything below reads, with the fp32 rounding residual folded in
+      const float thf = (float)th;
+      float s, c;
+      sincosf(thf, &s, &c);
+      const float dth = (float)(th - (double)thf);
+      m.px[tid] = x; m.py[tid] = y;
+      m.c[tid] = c - s * dth; m.s[tid] = s + c * dth;
+      m.vx[tid] = v0; m.vy[tid] = v1; m.vz[tid] = v2;
+      m.Tl[tid] = Tl; m.Tr[tid] = Tr; m.gx[tid] = gx; m.gy[tid] = gy;
+      m.rew[tid] = rew;
+      uint32_t fnew = f;
+      if (present && !(f & ASVRL_F_DEACTIVATED)) {  // check_reach_goal, WAMV:170-172, 462
+        const double dxg = (double)gx - x, dyg = (double)gy - y;
+        if (dxg * dxg + dyg * dyg <= k.goal_dis_d * k.goal_dis_d) fnew |= ASVRL_F_REACH_GOAL;
+      }
+      m.fl[tid] = fnew;
+      m.det_lo[tid] = 0; m.det_hi[tid] = 0;
     }
-    // heading of the pose everything below reads, with the fp32 rounding residual folded in
-    float thf = (float)th, s, c;
-    sincosf(thf, &s, &c);
-    float dth = (float)(th - (double)thf);
-    m.px[tid] = x; m.py[tid] = y;
-    m.c[tid] = c - s * dth; m.s[tid] = s + c * dth;
-    m.vx[tid] = v0; m.vy[tid] = v1; m.vz[tid] = v2;
-    m.Tl[tid] = Tl; m.Tr[tid] = Tr; m.gx[tid] = gx; m.gy[tid] = gy;
-    m.rew[tid] = rew;
-    m.fl0[tid] = present ? f : (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
-    uint32_t fnew = f;
-    if (present && !(f & ASVRL_F_DEACTIVATED)) {  // check_reach_goal, WAMV:170-172, 462
-      double dxg = (double)gx - x, dyg = (double)gy - y;
-      if (dxg * dxg + dyg * dyg <= k.goal_dis_d * k.goal_dis_d) fnew |= ASVRL_F_REACH_GOAL;
+  } else if (!INJECT) {
+    // ---- phase A' (warps 1..3, concurrently): sensor noise does not depend on the state, so it
+    // is drawn while warp 0 integrates — for the pairs that can plausibly end up in range
+    // (pre-step distance minus a travel allowance).  Pairs missed here are drawn in phase B, so
+    // the filter only moves work, it never changes a result. ----
+    for (int p = tid - 32; p < NP; p += TPB - 32) {
+      const int a = p / S, sl = p - a * S;
+      const int el = a / RP, r = a - el * RP;
+      if (m.fl0[a] & ASVRL_F_DEACTIVATED) continue;
+      float qx, qy, rt, travel = 0.5f * m.osp[a] + 1.5f;
+      if (sl < OP) {
+        if (sl >= m.no[el]) continue;
+        const float4 ob = m.obst[el * OP + sl];
+        qx = ob.x; qy = ob.y; rt = ob.z;
+      } else {
+        const int j = sl - OP, b = el * RP + j;
+        if (j == r || (m.fl0[b] & ASVRL_F_DEACTIVATED)) continue;
+        qx = m.ox[b]; qy = m.oy[b]; rt = k.robot_r; travel += 0.5f * m.osp[b] + 1.5f;
+      }
+      const float dx = qx - m.ox[a], dy = qy - m.oy[a];
+      const float far = k.detect_bound + rt + (dyn ? travel : 0.0f);
+      if (dx * dx + dy * dy > far * far) continue;
+      const NoiseDraw nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
+      float* np = m.noise + (size_t)p * 5;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) np[q] = nd.n[q];
+      m.have[p] = 1;
     }
-    m.fl[tid] = fnew;
-    m.det_lo[tid] = 0; m.det_hi[tid] = 0;
   }
   __syncthreads();
 
   // ---- phase B: every (ego, candidate slot) pair of the CTA's envs ----
-  for (int p = tid; p < A * S; p += blockDim.x) {
+  for (int p = tid; p < NP; p += TPB) {
     const int a = p / S, sl = p - a * S;
     const int el = a / RP, r = a - el * RP;
     double key = INFINITY;
     const uint32_t fe = m.fl0[a];
-    bool live = !(fe & ASVRL_F_DEACTIVATED);
-    double px = 0, py = 0, rt = 0;
-    float vx = 0, vy = 0;
-    if (live) {
-      if (sl < OP) {  // static obstacles, WAMV:465-483
-        live = sl < m.no[el];
-        float4 ob = m.obst[el * OP + sl];
-        px = ob.x; py = ob.y; rt = ob.z;
-      } else {  // other robots still on the map, WAMV:486-510
-        const int j = sl - OP, b = el * RP + j;
-        live = j != r && !(m.fl0[b] & ASVRL_F_DEACTIVATED);
-        px = m.px[b]; py = m.py[b]; vx = m.vx[b]; vy = m.vy[b]; rt = k.robot_r_d;
-      }
-    }
-    if (live) {
-      const double ex = m.px[a], ey = m.py[a];
-      const double tx = px - ex, ty = py - ey;  // true offset
-      bool maybe = true;
-      if (!INJECT) {  // the in-kernel generator's noise is bounded: skip hopeless candidates
-        float far = k.detect_bound + (float)rt;
-        maybe = (float)(tx * tx + ty * ty) <= far * far;
-      }
-      if (maybe) {
-        NoiseDraw nd;
-        if (INJECT) {
-          const float* np = noise + ((size_t)(e0 * RP + a) * S + sl) * 5;
+    if (!(fe & ASVRL_F_DEACTIVATED)) {
+      const Cand cd = candidate(k, m, el, r, sl, RP, OP);
+      if (cd.live) {
+        const double tx = cd.px - m.px[a], ty = cd.py - m.py[a];  // true offset
+        const double t2 = tx * tx + ty * ty;
+        bool maybe = true;
+        if (!INJECT) {  // the in-kernel generator's noise is bounded: skip hopeless candidates
+          const float far = k.detect_bound + (float)cd.rt;
+          maybe = (float)t2 <= far * far;
+        }
+        if (maybe) {
+          NoiseDraw nd;
+          if (INJECT) {
+            const float* np = noise + ((size_t)e0 * RP * S + p) * 5;
 #pragma unroll
-          for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
-        } else {
-          nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
-        }
-        const double qx = tx + (double)nd.n[0], qy = ty + (double)nd.n[1];  // WAMV:27-30
-        const double orr = k.r_mean_ratio * rt + k.r_noise_k * (double)nd.n[4] * rt;  // WAMV:37-40
-        const double d2 = qx * qx + qy * qy, lim = k.perc_range + orr;
-        bool det = d2 <= lim * lim;  // WAMV:296
-        const float c = m.c[a], s = m.s[a];
-        const float fx = (float)qx, fy = (float)qy;
-        const float bx = c * fx + s * fy, by = -s * fx + c * fy;  // WAMV:305-322
-        if (det && k.angle_limited) {  // WAMV:299-301 (vacuous at the default 2 pi)
-          double ang = atan2((double)by, (double)bx);
-          det = !(ang < -k.half_angle || ang > k.half_angle);
-        }
-        if (det) {
-          atomicOr(sl < 32 ? &m.det_lo[a] : &m.det_hi[a], 1u << (sl & 31));
-          if (!(fe & ASVRL_F_COLLISION)) {  // true geometry, WAMV:281-291, 475-476
-            double d = sqrt(tx * tx + ty * ty) - rt - k.robot_r_d;
-            if (d <= 0.0) atomicOr(&m.fl[a], (uint32_t)ASVRL_F_COLLISION);
+            for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
+          } else if (m.have[p]) {
+            const float* np = m.noise + (size_t)p * 5;
+#pragma unroll
+            for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
+          } else {
+            nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
           }
-          const float ovx = vx + nd.n[2], ovy = vy + nd.n[3];  // WAMV:32-35
-          float* cd = m.cand + (size_t)p * 5;
-          cd[0] = bx; cd[1] = by;
-          cd[2] = c * ovx + s * ovy; cd[3] = -s * ovx + c * ovy;
-          cd[4] = (float)orr;
-          key = sqrt(d2) - orr - k.robot_r_d;  // WAMV:515, 288
+          const double qx = tx + (double)nd.n[0], qy = ty + (double)nd.n[1];  // WAMV:27-30
+          const double orr = k.r_mean_ratio * cd.rt + k.r_noise_k * (double)nd.n[4] * cd.rt;  // WAMV:37-40
+          const double d2 = qx * qx + qy * qy, lim = k.perc_range + orr;
+          bool det = d2 <= lim * lim;  // WAMV:296
+          const float c = m.c[a], s = m.s[a];
+          const float fx = (float)qx, fy = (float)qy;
+          const float bx = c * fx + s * fy, by = -s * fx + c * fy;  // WAMV:305-322
+          if (det && k.angle_limited) {  // WAMV:299-301 (vacuous at the default 2 pi)
+            const float ang = atan2f(by, bx);
+            det = !((double)ang < -k.half_angle || (double)ang > k.half_angle);
+          }
+          if (det) {
+            atomicOr(sl < 32 ? &m.det_lo[a] : &m.det_hi[a], 1u << (sl & 31));
+            if (!(fe & ASVRL_F_COLLISION)) {  // true geometry, WAMV:281-291, 475-476
+              const double reach = cd.rt + k.robot_r_d;
+              if (t2 <= reach * reach) atomicOr(&m.fl[a], (uint32_t)ASVRL_F_COLLISION);
+            }
+            const float ovx = cd.vx + nd.n[2], ovy = cd.vy + nd.n[3];  // WAMV:32-35
+            float* o = m.cand + (size_t)p * 5;
+            o[0] = bx; o[1] = by;
+            o[2] = c * ovx + s * ovy; o[3] = -s * ovx + c * ovy;
+            o[4] = (float)orr;
+            key = sqrt(d2) - orr - k.robot_r_d;  // WAMV:515, 288
+          }
         }
       }
     }
     m.key[a * SK + sl] = key;
   }
+  for (int i = tid; i < A * 25; i += TPB) m.st_obj[i] = 0.0f;
+  for (int i = tid; i < A * 5; i += TPB) { m.st_mask[i] = 0.0f; m.chit[i] = 0; }
   __syncthreads();
 
-  // ---- phase C: one thread per ego ----
+  // ---- phase B2: rank of every detected candidate among its ego's keys (stable: ties keep slot
+  // order, like heapq.nsmallest, WAMV:513-515); the 5 smallest go to the staged observation ----
+  for (int p = tid; p < NP; p += TPB) {
+    const int a = p / S, sl = p - a * S;
+    const double* keys = m.key + a * SK;
+    const double kk = keys[sl];
+    if (kk < INFINITY) {
+      int rank = 0;
+      for (int q = 0; q < S; ++q) {
+        const double kq = keys[q];
+        rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0;
+      }
+      if (rank < ASVRL_MAX_OBJ) {
+        const float* cd = m.cand + (size_t)p * 5;
+        float* so = m.st_obj + a * 25 + rank * 5;
+#pragma unroll
+        for (int q = 0; q < 5; ++q) so[q] = cd[q];
+        m.st_mask[a * 5 + rank] = 1.0f;
+        if (out.top_ids) out.top_ids[((size_t)e0 * RP + a) * 5 + rank] = sl;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- phase C1: COLREGs test of every kept object, one thread per (ego, rank) ----
+  for (int i = tid; i < A * 5; i += TPB) {
+    const int a = i / 5;
+    if (m.st_mask[i] != 0.0f) {
+      const float c = m.c[a], s = m.s[a];
+      const float w0 = c * m.vx[a] + s * m.vy[a], w1 = -s * m.vx[a] + c * m.vy[a];
+      float phi = 0.0f;
+      const bool hit = colregs_one(k, m.st_obj + i * 5, w0, w1, phi);
+      m.chit[i] = hit ? 1 : 0;
+      m.cphi[i] = phi;
+    }
+  }
+  __syncthreads();
+
+  // ---- phase C2: one thread per ego: self observation, reward / done / info ----
   if (tid < A) {
     const int a = tid, el = a / RP, r = a - el * RP;
     const int e = e0 + el;
     const size_t g = (size_t)e * RP + r;
-    float* so = m.st_obj + a * 25;
     float* ss = m.st_self + a * 7;
-    float* sm = m.st_mask + a * 5;
-#pragma unroll
-    for (int q = 0; q < 25; ++q) so[q] = 0.0f;
 #pragma unroll
     for (int q = 0; q < 7; ++q) ss[q] = 0.0f;
-#pragma unroll
-    for (int q = 0; q < 5; ++q) sm[q] = 0.0f;
     if (m.ok[el]) {
       const bool present = r < m.nr[el];
       const uint32_t f0 = m.fl0[a];
       uint32_t f = m.fl[a], status = 0;
       float reward = 0.0f, phi = 0.0f;
-      int top[5] = {-1, -1, -1, -1, -1};
       if (!present) {
         status = (uint32_t)ASVRL_INFO_ABSENT << ASVRL_S_INFO_SHIFT;
+        f = 0;
       } else if (f0 & ASVRL_F_DEACTIVATED) {  // WAMV:437-438, ENV:295-304
-        int info = (f0 & ASVRL_F_COLLISION) ? ASVRL_INFO_DEACT_COLLISION
-                   : (f0 & ASVRL_F_REACH_GOAL) ? ASVRL_INFO_DEACT_GOAL : ASVRL_INFO_DEACT_INVALID;
+        const int info = (f0 & ASVRL_F_COLLISION) ? ASVRL_INFO_DEACT_COLLISION
+                         : (f0 & ASVRL_F_REACH_GOAL) ? ASVRL_INFO_DEACT_GOAL : ASVRL_INFO_DEACT_INVALID;
         status = ASVRL_S_DONE | ASVRL_S_WAS_DEACTIVATED | ((uint32_t)info << ASVRL_S_INFO_SHIFT);
       } else {
         const float c = m.c[a], s = m.s[a];
         const float dgx = (float)((double)m.gx[a] - m.px[a]), dgy = (float)((double)m.gy[a] - m.py[a]);
-        const float w0 = c * m.vx[a] + s * m.vy[a], w1 = -s * m.vx[a] + c * m.vy[a];
         ss[0] = c * dgx + s * dgy; ss[1] = -s * dgx + c * dgy;  // WAMV:443-453
-        ss[2] = w0; ss[3] = w1; ss[4] = m.vz[a]; ss[5] = m.Tl[a]; ss[6] = m.Tr[a];
-        // stable 5 smallest keys (heapq.nsmallest, WAMV:513-515): ties keep slot order
-        const double* keys = m.key + a * SK;
-        double lastk = -INFINITY;
-        int lasts = -1, kept = 0;
-        for (int t = 0; t < ASVRL_MAX_OBJ; ++t) {
-          double best = INFINITY;
-          int bs = -1;
-          for (int sl = 0; sl < S; ++sl) {
-            double kk = keys[sl];
-            if (kk < best && (kk > lastk || (kk == lastk && sl > lasts))) { best = kk; bs = sl; }
-          }
-          if (bs < 0) break;
-          const float* cd = m.cand + ((size_t)a * S + bs) * 5;
+        ss[2] = c * m.vx[a] + s * m.vy[a]; ss[3] = -s * m.vx[a] + c * m.vy[a];
+        ss[4] = m.vz[a]; ss[5] = m.Tl[a]; ss[6] = m.Tr[a];
+        bool apply = false;  // first hit in sorted order wins, WAMV:517-521
 #pragma unroll
-          for (int q = 0; q < 5; ++q) so[t * 5 + q] = cd[q];
-          sm[t] = 1.0f;
-          top[t] = bs;
-          lastk = best; lasts = bs; kept = t + 1;
-        }
-        bool apply = false;  // WAMV:517-521
-        for (int t = 0; t < kept && !apply; ++t) apply = colregs_one(k, so + t * 5, w0, w1, phi);
-        if (!apply) phi = 0.0f;
+        for (int t = 0; t < ASVRL_MAX_OBJ; ++t)
+          if (!apply && m.chit[a * 5 + t]) { apply = true; phi = m.cphi[a * 5 + t]; }
         if (apply) status |= ASVRL_S_COLREGS;
         int info = ASVRL_INFO_NORMAL;
         if (dyn) {  // ENV:306-328
@@ -409,8 +494,9 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
       out.status[g] = status;
       out.phi[g] = phi;
       if (out.top_ids) {
-#pragma unroll
-        for (int t = 0; t < 5; ++t) out.top_ids[g * 5 + t] = top[t];
+        const int kept = (int)(m.st_mask[a * 5] + m.st_mask[a * 5 + 1] + m.st_mask[a * 5 + 2] +
+                               m.st_mask[a * 5 + 3] + m.st_mask[a * 5 + 4]);
+        for (int t = kept; t < 5; ++t) out.top_ids[g * 5 + t] = -1;
       }
       if (out.detected)
         out.detected[g] = (unsigned long long)m.det_lo[a] | ((unsigned long long)m.det_hi[a] << 32);
@@ -423,23 +509,29 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
     const int n_env = min(EPB, E - e0);
     const size_t a0 = (size_t)e0 * RP;
     const int n_asv = n_env * RP;
-    for (int i = tid; i < n_asv * 25; i += blockDim.x)
-      if (m.ok[i / (RP * 25)]) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
-    for (int i = tid; i < n_asv * 7; i += blockDim.x)
-      if (m.ok[i / (RP * 7)]) out.obs_self[a0 * 7 + i] = m.st_self[i];
-    for (int i = tid; i < n_asv * 5; i += blockDim.x)
-      if (m.ok[i / (RP * 5)]) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
+    if (!env_mask) {
+      for (int i = tid; i < n_asv * 25; i += TPB) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
+      for (int i = tid; i < n_asv * 7; i += TPB) out.obs_self[a0 * 7 + i] = m.st_self[i];
+      for (int i = tid; i < n_asv * 5; i += TPB) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
+    } else {
+      for (int i = tid; i < n_asv * 25; i += TPB)
+        if (m.ok[i / (RP * 25)]) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
+      for (int i = tid; i < n_asv * 7; i += TPB)
+        if (m.ok[i / (RP * 7)]) out.obs_self[a0 * 7 + i] = m.st_self[i];
+      for (int i = tid; i < n_asv * 5; i += TPB)
+        if (m.ok[i / (RP * 5)]) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
+    }
     if (tid < n_env && m.ok[tid]) {
       const int el = tid, e = e0 + el, nr = m.nr[el];
       bool all_deact = true, any_coll = false, all_goal = true;
       for (int r = 0; r < nr; ++r) {
-        uint32_t f = m.fl[el * RP + r];
+        const uint32_t f = m.fl[el * RP + r];
         all_deact &= (f & ASVRL_F_DEACTIVATED) != 0;   // ENV:178-184
         any_coll |= (f & ASVRL_F_COLLISION) != 0;      // ENV:194-200
         all_goal &= (f & ASVRL_F_REACH_GOAL) != 0;     // ENV:186-192
       }
-      uint32_t es = (all_deact ? 1u : 0u) | (m.ep[el] >= k.max_ep ? 2u : 0u) |
-                    (any_coll ? 4u : 0u) | (all_goal ? 8u : 0u);
+      const uint32_t es = (all_deact ? 1u : 0u) | (m.ep[el] >= k.max_ep ? 2u : 0u) |
+                          (any_coll ? 4u : 0u) | (all_goal ? 8u : 0u);
       out.env_status[e] = es;
       if (out.ended) out.ended[e] = (es & 3u) ? 1 : 0;
       if (dyn) st.ep_steps[e] = m.ep[el] + 1;  // ENV:330
@@ -485,10 +577,10 @@ int make_env_consts(const asvrl_env_params* p, EnvConsts* k) {
   k->dt = (float)p->dt; k->n_sub = p->n_substeps; k->max_ep = p->max_episode_steps;
   k->min_thrust = (float)p->min_thrust; k->max_thrust = (float)p->max_thrust;
   const double hold = p->dt * p->n_substeps;
-  k->act_scale = (float)(p->thrust_rate * hold);
+  k->act_scale = p->thrust_rate * hold;
   for (int i = 0; i < 5; ++i) {
-    k->dl[i] = (float)(p->thrust_change_l[i] * hold);
-    k->dr[i] = (float)(p->thrust_change_r[i] * hold);
+    k->dl[i] = p->thrust_change_l[i] * hold;
+    k->dr[i] = p->thrust_change_r[i] * hold;
   }
   k->m = (float)p->m; k->xDotU = (float)p->xDotU; k->yDotV = (float)p->yDotV; k->yDotR = (float)p->yDotR;
   k->xU = (float)p->xU; k->xUU = (float)p->xUU; k->yV = (float)p->yV; k->yVV = (float)p->yVV;
@@ -565,7 +657,7 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
   if ((max_obs > 0 && !st.obstacles) || (max_cores > 0 && !st.cores))
     return fail(ASVRL_E_BADARG, "asvrl_env_step: null obstacle / core table");
   const int EPB = pick_epb(max_robots);
-  const size_t smem = carve(nullptr, EPB, max_robots, max_obs, max_cores).bytes;
+  const size_t smem = carve(nullptr, EPB, max_robots, max_obs, max_cores, noise != nullptr).bytes;
   const int grid = (n_envs + EPB - 1) / EPB;
   cudaStream_t s = (cudaStream_t)stream;
   auto kern = noise ? env_step_kernel<true> : env_step_kernel<false>;
@@ -573,7 +665,7 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
   }
-  kern<<<grid, 256, smem, s>>>(k, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
+  kern<<<grid, TPB, smem, s>>>(k, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
                                max_cores, env_offset, mode, EPB);
   return check_launch("asvrl_env_step");
 }

@@ -51,7 +51,11 @@ def vec_close(a, b, rtol, atol, axis=-1):
     err = np.abs(a - b)
     bound = rtol * scale + atol
     worst = float(np.max(err / np.maximum(scale, atol / max(rtol, 1e-300)))) if err.size else 0.0
-    return bool(np.all(err <= bound)), worst
+    ok = bool(np.all(err <= bound))
+    if not ok:
+        i = np.unravel_index(np.argmax(err - bound), err.shape)
+        worst = (worst, "at", tuple(int(x) for x in i), "got", float(a[i]), "want", float(b[i]), "row", np.round(b[i[:-1]], 6).tolist() if b.ndim > 1 else None)
+    return ok, worst
 
 
 # ----------------------------------------------------------------------------------------
@@ -72,13 +76,15 @@ def _grouped_close(a, b, groups, rtol=RTOL, atol=ATOL):
     covered = set()
     for lo, hi in groups:
         ok, worst = vec_close(a[..., lo:hi], b[..., lo:hi], rtol, atol, -1)
-        ok_all &= ok
+        if not ok:
+            return False, ("group", lo, hi, worst)
         worst_all = max(worst_all, worst)
         covered.update(range(lo, hi))
     rest = [i for i in range(a.shape[-1]) if i not in covered]
     if rest:
         ok, worst = vec_close(a[..., rest], b[..., rest], rtol, atol, None)
-        ok_all &= ok
+        if not ok:
+            return False, ("scalars", rest, worst)
         worst_all = max(worst_all, worst)
     return ok_all, worst_all
 

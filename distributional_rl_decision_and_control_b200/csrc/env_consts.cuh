@@ -51,11 +51,14 @@ __device__ __forceinline__ NoiseDraw sensor_noise(const EnvConsts& k, uint64_t s
                                                   int64_t env, uint32_t ego, uint32_t slot) {
   NoiseDraw d;
   uint4 w = philox_at(seed, STREAM_SENSOR, step, env, ego, slot, 0u);
-  float r0 = sqrtf(-2.0f * logf(u01(w.x)));
-  float r1 = sqrtf(-2.0f * logf(u01(w.z)));
+  // fast intrinsics: the draws are noise, only their distribution matters (abs. error ~1e-6 sigma)
+  const float TWO_PI = 6.28318530717959f;
+  float r0 = sqrtf(-2.0f * __logf(u01(w.x)));
+  float r1 = sqrtf(-2.0f * __logf(u01(w.z)));
   float s0, c0, s1, c1;
-  sincospif(2.0f * u01(w.y), &s0, &c0);
-  sincospif(2.0f * u01(w.w), &s1, &c1);
+  __sincosf(TWO_PI * (u01(w.y) - 0.5f), &s0, &c0);  // angle in (-pi, pi): MUFU range
+  __sincosf(TWO_PI * (u01(w.w) - 0.5f), &s1, &c1);
+  s0 = -s0; c0 = -c0; s1 = -s1; c1 = -c1;            // sin/cos(2 pi u) = -sin/cos(2 pi u - pi)
   d.n[0] = k.pos_std * r0 * c0;
   d.n[1] = k.pos_std * r0 * s0;
   d.n[2] = k.vel_std * r1 * c1;
@@ -75,11 +78,11 @@ __device__ __forceinline__ NoiseDraw sensor_noise(const EnvConsts& k, uint64_t s
       if (accepted) break;
       uint32_t wu = a == 0 ? w.x : w.z, wv = a == 0 ? w.y : w.w;
       float U = u01(wu), V = u01(wv);
-      float Z = cospif(U);
-      W = (1.0f + k.vm_s * Z) / (k.vm_s + Z);
+      float Z = __cosf(3.14159265358979f * U);
+      W = __fdividef(1.0f + k.vm_s * Z, k.vm_s + Z);
       float Y = k.vm_kappa * (k.vm_s - W);
       sign_word = wv;
-      accepted = (Y * (2.0f - Y) - V >= 0.0f) || (logf(Y / V) + 1.0f - Y >= 0.0f);
+      accepted = (Y * (2.0f - Y) - V >= 0.0f) || (__logf(__fdividef(Y, V)) + 1.0f - Y >= 0.0f);
     }
   }
   float res = acosf(W);

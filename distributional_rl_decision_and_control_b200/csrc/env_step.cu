@@ -50,40 +50,76 @@ struct OutPtrs {
 
 constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
 
-// shared-memory carve-up, identical on host (size) and device (pointers)
+// shared-memory layout: byte offsets computed once on the host and passed by value, so the
+// kernel prologue is a handful of 32-bit adds instead of per-thread 64-bit size arithmetic
+struct SmemLayout {
+  uint32_t px, py, key, obst, cores, c, s, vx, vy, vz, Tl, Tr, gx, gy, rew, ox, oy, osp, cand,
+      st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, have, chit, nr, no, nc, ep, ok;
+  uint32_t bytes;
+  // pair-loop stepping without integer division: TPB = q*S + rem
+  int step_a, step_sl, step3_a, step3_sl;
+};
+
 struct Smem {
   double *px, *py, *key;
   float *c, *s, *vx, *vy, *vz, *Tl, *Tr, *gx, *gy, *rew, *ox, *oy, *osp;
-  float *cand, *noise, *st_obj, *st_self, *st_mask, *cphi;
+  float *cand, *st_obj, *st_self, *st_mask, *cphi;
   uint32_t *fl0, *fl, *det_lo, *det_hi;
   uint8_t *have, *chit;
   int *nr, *no, *nc, *ep, *ok;
   float4 *obst, *cores;
-  size_t bytes;
 };
 
-__host__ __device__ inline Smem carve(char* base, int EPB, int RP, int OP, int CP, bool inject) {
+static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb) {
+  SmemLayout L;
+  const uint32_t A = (uint32_t)EPB * RP, S = OP + RP, SK = S | 1;
+  uint32_t off = 0;
+  auto take = [&](uint32_t n, uint32_t elem) { uint32_t o = off; off += (n * elem + 15u) & ~15u; return o; };
+  L.px = take(A, 8); L.py = take(A, 8); L.key = take(A * SK, 8);
+  L.obst = take(EPB * (OP > 0 ? OP : 1), 16); L.cores = take(EPB * (CP > 0 ? CP : 1), 16);
+  L.c = take(A, 4); L.s = take(A, 4); L.vx = take(A, 4); L.vy = take(A, 4); L.vz = take(A, 4);
+  L.Tl = take(A, 4); L.Tr = take(A, 4); L.gx = take(A, 4); L.gy = take(A, 4); L.rew = take(A, 4);
+  L.ox = take(A, 4); L.oy = take(A, 4); L.osp = take(A, 4);
+  L.cand = take(A * S * 5, 4);  // prefetched noise first, then the candidate observation (same thread)
+  L.st_obj = take(A * 25, 4); L.st_self = take(A * 7, 4); L.st_mask = take(A * 5, 4);
+  L.cphi = take(A * 5, 4);
+  L.fl0 = take(A, 4); L.fl = take(A, 4); L.det_lo = take(A, 4); L.det_hi = take(A, 4);
+  L.have = take(A * S, 1); L.chit = take(A * 5, 1);
+  L.nr = take(EPB, 4); L.no = take(EPB, 4); L.nc = take(EPB, 4); L.ep = take(EPB, 4); L.ok = take(EPB, 4);
+  L.bytes = off;
+  L.step_a = tpb / (int)S; L.step_sl = tpb % (int)S;
+  L.step3_a = (tpb - 32) / (int)S; L.step3_sl = (tpb - 32) % (int)S;
+  return L;
+}
+
+__device__ __forceinline__ Smem carve(char* base, const SmemLayout& L) {
   Smem m;
-  const size_t A = (size_t)EPB * RP, S = OP + RP, SK = S | 1;
-  size_t off = 0;
-#define TAKE(ptr, type, n) ptr = (type*)(base + off); off += (((size_t)(n) * sizeof(type)) + 15) & ~(size_t)15
-  TAKE(m.px, double, A); TAKE(m.py, double, A); TAKE(m.key, double, A * SK);
-  TAKE(m.obst, float4, EPB * (OP > 0 ? OP : 1)); TAKE(m.cores, float4, EPB * (CP > 0 ? CP : 1));
-  TAKE(m.c, float, A); TAKE(m.s, float, A); TAKE(m.vx, float, A); TAKE(m.vy, float, A);
-  TAKE(m.vz, float, A); TAKE(m.Tl, float, A); TAKE(m.Tr, float, A); TAKE(m.gx, float, A);
-  TAKE(m.gy, float, A); TAKE(m.rew, float, A); TAKE(m.ox, float, A); TAKE(m.oy, float, A);
-  TAKE(m.osp, float, A);
-  TAKE(m.cand, float, A * S * 5);
-  TAKE(m.noise, float, inject ? 4 : A * S * 5);
-  TAKE(m.st_obj, float, A * 25); TAKE(m.st_self, float, A * 7); TAKE(m.st_mask, float, A * 5);
-  TAKE(m.cphi, float, A * 5);
-  TAKE(m.fl0, uint32_t, A); TAKE(m.fl, uint32_t, A); TAKE(m.det_lo, uint32_t, A); TAKE(m.det_hi, uint32_t, A);
-  TAKE(m.have, uint8_t, A * S); TAKE(m.chit, uint8_t, A * 5);
-  TAKE(m.nr, int, EPB); TAKE(m.no, int, EPB); TAKE(m.nc, int, EPB); TAKE(m.ep, int, EPB); TAKE(m.ok, int, EPB);
-#undef TAKE
-  m.bytes = off;
+  m.px = (double*)(base + L.px); m.py = (double*)(base + L.py); m.key = (double*)(base + L.key);
+  m.obst = (float4*)(base + L.obst); m.cores = (float4*)(base + L.cores);
+  m.c = (float*)(base + L.c); m.s = (float*)(base + L.s); m.vx = (float*)(base + L.vx);
+  m.vy = (float*)(base + L.vy); m.vz = (float*)(base + L.vz); m.Tl = (float*)(base + L.Tl);
+  m.Tr = (float*)(base + L.Tr); m.gx = (float*)(base + L.gx); m.gy = (float*)(base + L.gy);
+  m.rew = (float*)(base + L.rew); m.ox = (float*)(base + L.ox); m.oy = (float*)(base + L.oy);
+  m.osp = (float*)(base + L.osp); m.cand = (float*)(base + L.cand);
+  m.st_obj = (float*)(base + L.st_obj); m.st_self = (float*)(base + L.st_self);
+  m.st_mask = (float*)(base + L.st_mask); m.cphi = (float*)(base + L.cphi);
+  m.fl0 = (uint32_t*)(base + L.fl0); m.fl = (uint32_t*)(base + L.fl);
+  m.det_lo = (uint32_t*)(base + L.det_lo); m.det_hi = (uint32_t*)(base + L.det_hi);
+  m.have = (uint8_t*)(base + L.have); m.chit = (uint8_t*)(base + L.chit);
+  m.nr = (int*)(base + L.nr); m.no = (int*)(base + L.no); m.nc = (int*)(base + L.nc);
+  m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok);
   return m;
 }
+
+// pair index p -> (ego a, slot sl) walked without division
+struct PairIt {
+  int p, a, sl;
+  __device__ __forceinline__ PairIt(int p0, int S) : p(p0), a(p0 / S), sl(p0 - (p0 / S) * S) {}
+  __device__ __forceinline__ void advance(int dp, int da, int dsl, int S) {
+    p += dp; a += da; sl += dsl;
+    if (sl >= S) { sl -= S; ++a; }
+  }
+};
 
 // ENV:458-501.  All cores contribute (the reference's `continue` is a no-op).
 // tangent * speed = (-ry, rx) * dir * speed / d, and speed / d is Gamma/(2 pi r^2) inside the
@@ -167,12 +203,13 @@ __device__ __forceinline__ Cand candidate(const EnvConsts& k, const Smem& m, int
 
 template <bool INJECT>
 __global__ void __launch_bounds__(TPB, 8)
-env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* __restrict__ actions,
+env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L,
+                StatePtrs st, const void* __restrict__ actions,
                 const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
                 uint64_t step, OutPtrs out, int E, int RP, int OP, int CP, int64_t env_offset,
                 uint32_t mode, int EPB) {
   extern __shared__ __align__(16) char smem_raw[];
-  const Smem m = carve(smem_raw, EPB, RP, OP, CP, INJECT);
+  const Smem m = carve(smem_raw, L);
   const int tid = threadIdx.x;
   const int A = EPB * RP, S = OP + RP, SK = S | 1, NP = A * S;
   const int e0 = blockIdx.x * EPB;
@@ -188,7 +225,11 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
     m.nc[tid] = v ? min(st.n_cores[e], CP) : 0;
     m.ep[tid] = v ? st.ep_steps[e] : 0;
   }
-  __syncthreads();
+  {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
+    const int e = e0 + tid;
+    const bool mine = tid < EPB && e < E && (!env_mask || env_mask[e]);
+    if (!__syncthreads_or(mine)) return;
+  }
   for (int i = tid; i < EPB * OP; i += TPB) {
     const int el = i / OP;
     m.obst[i] = m.ok[el] ? st.obstacles[(size_t)(e0 + el) * OP + (i - el * OP)] : make_float4(0, 0, 0, 0);
@@ -315,8 +356,8 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
     // is drawn while warp 0 integrates — for the pairs that can plausibly end up in range
     // (pre-step distance minus a travel allowance).  Pairs missed here are drawn in phase B, so
     // the filter only moves work, it never changes a result. ----
-    for (int p = tid - 32; p < NP; p += TPB - 32) {
-      const int a = p / S, sl = p - a * S;
+    for (PairIt it(tid - 32, S); it.p < NP; it.advance(TPB - 32, L.step3_a, L.step3_sl, S)) {
+      const int p = it.p, a = it.a, sl = it.sl;
       const int el = a / RP, r = a - el * RP;
       if (m.fl0[a] & ASVRL_F_DEACTIVATED) continue;
       float qx, qy, rt, travel = 0.5f * m.osp[a] + 1.5f;
@@ -333,7 +374,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
       const float far = k.detect_bound + rt + (dyn ? travel : 0.0f);
       if (dx * dx + dy * dy > far * far) continue;
       const NoiseDraw nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
-      float* np = m.noise + (size_t)p * 5;
+      float* np = m.cand + p * 5;
 #pragma unroll
       for (int q = 0; q < 5; ++q) np[q] = nd.n[q];
       m.have[p] = 1;
@@ -342,8 +383,8 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
   __syncthreads();
 
   // ---- phase B: every (ego, candidate slot) pair of the CTA's envs ----
-  for (int p = tid; p < NP; p += TPB) {
-    const int a = p / S, sl = p - a * S;
+  for (PairIt it(tid, S); it.p < NP; it.advance(TPB, L.step_a, L.step_sl, S)) {
+    const int p = it.p, a = it.a, sl = it.sl;
     const int el = a / RP, r = a - el * RP;
     double key = INFINITY;
     const uint32_t fe = m.fl0[a];
@@ -364,7 +405,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
 #pragma unroll
             for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
           } else if (m.have[p]) {
-            const float* np = m.noise + (size_t)p * 5;
+            const float* np = m.cand + p * 5;
 #pragma unroll
             for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
           } else {
@@ -388,7 +429,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
               if (t2 <= reach * reach) atomicOr(&m.fl[a], (uint32_t)ASVRL_F_COLLISION);
             }
             const float ovx = cd.vx + nd.n[2], ovy = cd.vy + nd.n[3];  // WAMV:32-35
-            float* o = m.cand + (size_t)p * 5;
+            float* o = m.cand + p * 5;
             o[0] = bx; o[1] = by;
             o[2] = c * ovx + s * ovy; o[3] = -s * ovx + c * ovy;
             o[4] = (float)orr;
@@ -405,18 +446,17 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
 
   // ---- phase B2: rank of every detected candidate among its ego's keys (stable: ties keep slot
   // order, like heapq.nsmallest, WAMV:513-515); the 5 smallest go to the staged observation ----
-  for (int p = tid; p < NP; p += TPB) {
-    const int a = p / S, sl = p - a * S;
+  for (PairIt it(tid, S); it.p < NP; it.advance(TPB, L.step_a, L.step_sl, S)) {
+    const int p = it.p, a = it.a, sl = it.sl;
     const double* keys = m.key + a * SK;
     const double kk = keys[sl];
     if (kk < INFINITY) {
       int rank = 0;
-      for (int q = 0; q < S; ++q) {
-        const double kq = keys[q];
-        rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0;
-      }
+      uint32_t lo = m.det_lo[a], hi = m.det_hi[a];  // only detected slots carry finite keys
+      while (lo) { const int q = __ffs(lo) - 1; lo &= lo - 1; const double kq = keys[q]; rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0; }
+      while (hi) { const int q = 32 + __ffs(hi) - 1; hi &= hi - 1; const double kq = keys[q]; rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0; }
       if (rank < ASVRL_MAX_OBJ) {
-        const float* cd = m.cand + (size_t)p * 5;
+        const float* cd = m.cand + p * 5;
         float* so = m.st_obj + a * 25 + rank * 5;
 #pragma unroll
         for (int q = 0; q < 5; ++q) so[q] = cd[q];
@@ -514,12 +554,14 @@ env_step_kernel(const __grid_constant__ EnvConsts k, StatePtrs st, const void* _
       for (int i = tid; i < n_asv * 7; i += TPB) out.obs_self[a0 * 7 + i] = m.st_self[i];
       for (int i = tid; i < n_asv * 5; i += TPB) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
     } else {
-      for (int i = tid; i < n_asv * 25; i += TPB)
-        if (m.ok[i / (RP * 25)]) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
-      for (int i = tid; i < n_asv * 7; i += TPB)
-        if (m.ok[i / (RP * 7)]) out.obs_self[a0 * 7 + i] = m.st_self[i];
-      for (int i = tid; i < n_asv * 5; i += TPB)
-        if (m.ok[i / (RP * 5)]) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
+      for (int el = 0; el < n_env; ++el) {
+        if (!m.ok[el]) continue;
+        const size_t b0 = a0 + (size_t)el * RP;
+        const int l0 = el * RP;
+        for (int i = tid; i < RP * 25; i += TPB) out.obs_objects[b0 * 25 + i] = m.st_obj[l0 * 25 + i];
+        for (int i = tid; i < RP * 7; i += TPB) out.obs_self[b0 * 7 + i] = m.st_self[l0 * 7 + i];
+        for (int i = tid; i < RP * 5; i += TPB) out.obs_mask[b0 * 5 + i] = m.st_mask[l0 * 5 + i];
+      }
     }
     if (tid < n_env && m.ok[tid]) {
       const int el = tid, e = e0 + el, nr = m.nr[el];
@@ -657,7 +699,8 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
   if ((max_obs > 0 && !st.obstacles) || (max_cores > 0 && !st.cores))
     return fail(ASVRL_E_BADARG, "asvrl_env_step: null obstacle / core table");
   const int EPB = pick_epb(max_robots);
-  const size_t smem = carve(nullptr, EPB, max_robots, max_obs, max_cores, noise != nullptr).bytes;
+  const SmemLayout L = make_layout(EPB, max_robots, max_obs, max_cores, TPB);
+  const size_t smem = L.bytes;
   const int grid = (n_envs + EPB - 1) / EPB;
   cudaStream_t s = (cudaStream_t)stream;
   auto kern = noise ? env_step_kernel<true> : env_step_kernel<false>;
@@ -665,7 +708,7 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
   }
-  kern<<<grid, TPB, smem, s>>>(k, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
+  kern<<<grid, TPB, smem, s>>>(k, L, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
                                max_cores, env_offset, mode, EPB);
   return check_launch("asvrl_env_step");
 }

@@ -128,3 +128,22 @@ OUT_FIELDS = ("obs_self", "obs_objects", "obs_mask", "reward", "status", "phi", 
 
 class EnvOutPtrs(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in OUT_FIELDS]
+
+
+class ResetParams(C.Structure):
+    """asvrl_reset_params (ENV:33-41, 107-155)."""
+    _fields_ = [(n, C.c_double) for n in ("map_w", "map_h", "start_margin", "obs_margin", "clear_r",
+                                          "core_r", "v_rel_max", "p", "v_min", "v_max", "obs_r_min",
+                                          "obs_r_max")] + [("max_tries", C.c_int32),
+                                                           ("reserved", C.c_int32)]
+
+
+def default_reset_params() -> ResetParams:
+    """Reference defaults (ENV:33-41; 500 tries ENV:107,124,152)."""
+    p = ResetParams()
+    p.map_w = p.map_h = 55.0
+    p.start_margin, p.obs_margin, p.clear_r, p.core_r = 2.0, 5.0, 10.0, 0.5
+    p.v_rel_max, p.p, p.v_min, p.v_max = 1.0, 0.8, 3.0, 3.0
+    p.obs_r_min = p.obs_r_max = 1.0
+    p.max_tries, p.reserved = 500, 0
+    return p

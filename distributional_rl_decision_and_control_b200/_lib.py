@@ -43,12 +43,7 @@ _SIGNATURES = {
 EXPORTED = tuple(_SIGNATURES)
 
 
-class ResetParams(C.Structure):
-    """asvrl_reset_params (ENV:33-41, 107-155)."""
-    _fields_ = [(n, C.c_double) for n in ("map_w", "map_h", "start_margin", "obs_margin", "clear_r",
-                                          "core_r", "v_rel_max", "p", "v_min", "v_max", "obs_r_min",
-                                          "obs_r_max")] + [("max_tries", C.c_int32),
-                                                           ("reserved", C.c_int32)]
+ResetParams = _abi.ResetParams
 
 
 def lib():
@@ -215,3 +210,55 @@ def iqn_tau_cos(B, N, n_cos, device, tau_in=None, seed=0, counter=0, cvar=1.0, t
                                  ptr(tau_out), ptr(cos_out), stream_ptr())
     check(rc, "asvrl_iqn_tau_cos")
     return tau_out, cos_out
+
+
+# ------------------------------------------------------------------ K2: device replay ring
+def new_replay(capacity, n_asv_max, device):
+    """Ring of float32[70] rows + device counters (head_size[0] rows ever written,
+    head_size[1] rows valid) + the push workspace (include/asvrl.h)."""
+    return {
+        "rows": torch.zeros((int(capacity), _abi.ROW), dtype=torch.float32, device=device),
+        "head_size": torch.zeros((2,), dtype=torch.int64, device=device),
+        "workspace": torch.zeros(((int(n_asv_max) + 255) // 256 + 4,), dtype=torch.int32, device=device),
+        "capacity": int(capacity),
+    }
+
+
+def replay_push(rb, obs_self, obs_objects, obs_mask, actions, discrete, reward, next_self,
+                next_objects, next_mask, status):
+    n_asv = status.numel()
+    if (n_asv + 255) // 256 + 4 > rb["workspace"].numel():
+        raise RuntimeError("replay workspace too small for this many ASVs")
+    a_dtype = torch.int32 if discrete else torch.float32
+    rc = lib().asvrl_replay_push(ptr(rb["rows"], torch.float32), rb["capacity"],
+                                 ptr(rb["head_size"], torch.int64), ptr(obs_self, torch.float32),
+                                 ptr(obs_objects, torch.float32), ptr(obs_mask, torch.float32),
+                                 ptr(actions, a_dtype), 1 if discrete else 0,
+                                 ptr(reward, torch.float32), ptr(next_self, torch.float32),
+                                 ptr(next_objects, torch.float32), ptr(next_mask, torch.float32),
+                                 ptr(status, torch.int32), n_asv, ptr(rb["workspace"], torch.int32),
+                                 stream_ptr())
+    check(rc, "asvrl_replay_push")
+
+
+def new_batch(B, device):
+    f = dict(dtype=torch.float32, device=device)
+    return {"self": torch.empty((B, 7), **f), "obj": torch.empty((B, 5, 5), **f),
+            "mask": torch.empty((B, 5), **f), "act": torch.empty((B, 2), **f),
+            "rew": torch.empty((B,), **f), "nself": torch.empty((B, 7), **f),
+            "nobj": torch.empty((B, 5, 5), **f), "nmask": torch.empty((B, 5), **f),
+            "done": torch.empty((B,), **f),
+            "indices": torch.empty((B,), dtype=torch.int64, device=device)}
+
+
+def replay_sample(rb, batch, seed=0, counter=0, indices=None):
+    """Fills the dense batch tensors of ``batch`` (new_batch) from the ring."""
+    B = batch["rew"].numel()
+    rc = lib().asvrl_replay_sample(ptr(rb["rows"], torch.float32), ptr(rb["head_size"], torch.int64),
+                                   rb["capacity"], ptr(indices, torch.int64), seed, counter, B,
+                                   ptr(batch["self"]), ptr(batch["obj"]), ptr(batch["mask"]),
+                                   ptr(batch["act"]), ptr(batch["rew"]), ptr(batch["nself"]),
+                                   ptr(batch["nobj"]), ptr(batch["nmask"]), ptr(batch["done"]),
+                                   ptr(batch["indices"], torch.int64), stream_ptr())
+    check(rc, "asvrl_replay_sample")
+    return batch

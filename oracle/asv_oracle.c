@@ -562,3 +562,195 @@ int oracle_tau_cos(const double* tau, int batch, int n_tau, int n_cos, double* c
     }
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------ */
+/* Scenario generation, ENV:72-176 with the acceptance predicates of ENV:358-456.         */
+/* The three predicates are pinned against the reference's own check_* methods by          */
+/* tests/golden/reset_checks.npz; the generator applies them, in the reference's order,    */
+/* to the counter-indexed Philox candidate sequence documented in include/asvrl.h          */
+/* (stream 2; ego field = class, candidate t -> slot = t >> 8, block = t & 255).           */
+/* Each predicate returns 1 = accept and lowers *margin to the smallest |distance to a     */
+/* threshold| it evaluated (metres), so the parity tests can skip razor-edge cases.        */
+/* ------------------------------------------------------------------------------------ */
+#define STREAM_RESET 2u
+
+static void marg(double* m, double v) {
+  if (!m) return;
+  v = fabs(v);
+  if (v < *m) *m = v;
+}
+
+/* ENV:358-376.  sg = accepted robots [n][4] = start.xy, goal.xy; cand = start.xy, goal.xy */
+int oracle_check_start_goal(const asvrl_reset_params* rp, const double* sg, int n,
+                            const double* cand, double min_dis, double* margin) {
+  double dx = cand[2] - cand[0], dy = cand[3] - cand[1];
+  double d = sqrt(dx * dx + dy * dy);
+  marg(margin, d - min_dis);
+  if (d < min_dis) return 0; /* ENV:361 */
+  for (int i = 0; i < n; ++i) {
+    const double* o = sg + 4 * i;
+    double ds = hypot(o[0] - cand[0], o[1] - cand[1]);
+    marg(margin, ds - rp->clear_r);
+    if (ds <= rp->clear_r) return 0; /* ENV:366-369 */
+    double dg = hypot(o[2] - cand[2], o[3] - cand[3]);
+    marg(margin, dg - rp->clear_r);
+    if (dg <= rp->clear_r) return 0; /* ENV:371-374 */
+  }
+  return 1;
+}
+
+/* ENV:378-418.  cores [n_c][4] = x, y, +1 clockwise / -1, Gamma; cand likewise */
+int oracle_check_core(const asvrl_reset_params* rp, const double* sg, int n_r, const double* cores,
+                      int n_c, const double* cand, double* margin) {
+  double r = rp->core_r;
+  marg(margin, cand[0] - r); marg(margin, cand[0] + r - rp->map_w);
+  if (cand[0] - r < 0.0 || cand[0] + r > rp->map_w) return 0; /* ENV:381 */
+  marg(margin, cand[1] - r); marg(margin, cand[1] + r - rp->map_w);
+  if (cand[1] - r < 0.0 || cand[1] + r > rp->map_w) return 0; /* ENV:383 compares with width */
+  for (int i = 0; i < n_r; ++i) {
+    const double* o = sg + 4 * i;
+    double ds = hypot(cand[0] - o[0], cand[1] - o[1]);
+    marg(margin, ds - (r + rp->clear_r));
+    if (ds < r + rp->clear_r) return 0; /* ENV:389-391 */
+    double dg = hypot(cand[0] - o[2], cand[1] - o[3]);
+    marg(margin, dg - (r + rp->clear_r));
+    if (dg < r + rp->clear_r) return 0; /* ENV:392-394 */
+  }
+  for (int i = 0; i < n_c; ++i) {
+    const double* o = cores + 4 * i;
+    double dx = o[0] - cand[0], dy = o[1] - cand[1];
+    double dis = sqrt(dx * dx + dy * dy);
+    if ((o[2] > 0.0) == (cand[2] > 0.0)) { /* same spin, ENV:401-407 */
+      double bi = o[3] / (2.0 * M_PI * rp->v_rel_max), bj = cand[3] / (2.0 * M_PI * rp->v_rel_max);
+      marg(margin, dis - (bi + bj));
+      if (dis < bi + bj) return 0;
+    } else { /* opposite spin, ENV:408-416 */
+      double gl = o[3] > cand[3] ? o[3] : cand[3], gs = o[3] > cand[3] ? cand[3] : o[3];
+      double v1 = gl / (2.0 * M_PI * (dis - 2.0 * r)), v2 = gs / (2.0 * M_PI * r);
+      /* v1 > p v2  <=>  dis - 2r < gl / (2 pi p v2) when dis > 2r; report the metric margin */
+      marg(margin, (dis - 2.0 * r) - gl / (2.0 * M_PI * rp->p * v2));
+      marg(margin, dis - 2.0 * r);
+      if (v1 > rp->p * v2) return 0;
+    }
+  }
+  return 1;
+}
+
+/* ENV:420-456.  obs [n_o][4] = x, y, r, 0; cand = x, y, r */
+int oracle_check_obstacle(const asvrl_reset_params* rp, const double* sg, int n_r,
+                          const double* cores, int n_c, const double* obs, int n_o,
+                          const double* cand, double* margin) {
+  double r = cand[2];
+  marg(margin, cand[0] - r); marg(margin, cand[0] + r - rp->map_w);
+  if (cand[0] - r < 0.0 || cand[0] + r > rp->map_w) return 0; /* ENV:423 */
+  marg(margin, cand[1] - r); marg(margin, cand[1] + r - rp->map_h);
+  if (cand[1] - r < 0.0 || cand[1] + r > rp->map_h) return 0; /* ENV:425 */
+  for (int i = 0; i < n_r; ++i) {
+    const double* o = sg + 4 * i;
+    double ds = hypot(cand[0] - o[0], cand[1] - o[1]);
+    marg(margin, ds - (r + rp->clear_r));
+    if (ds < r + rp->clear_r) return 0; /* ENV:431-433 */
+    double dg = hypot(cand[0] - o[2], cand[1] - o[3]);
+    marg(margin, dg - (r + rp->clear_r));
+    if (dg < r + rp->clear_r) return 0; /* ENV:434-436 */
+  }
+  for (int i = 0; i < n_c; ++i) {
+    double dis = hypot(cores[4 * i] - cand[0], cores[4 * i + 1] - cand[1]);
+    marg(margin, dis - (rp->core_r + r));
+    if (dis <= rp->core_r + r) return 0; /* ENV:439-445 */
+  }
+  for (int i = 0; i < n_o; ++i) {
+    double dis = hypot(obs[4 * i] - cand[0], obs[4 * i + 1] - cand[1]);
+    marg(margin, dis - (obs[4 * i + 2] + r));
+    if (dis <= obs[4 * i + 2] + r) return 0; /* ENV:448-454 */
+  }
+  return 1;
+}
+
+static void reset_block(uint64_t seed, uint64_t episode, int64_t env, uint32_t cls, uint32_t t,
+                        int theta, uint32_t w[4]) {
+  uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+  uint32_t slot = theta ? t : (t >> 8), block = theta ? 0u : (t & 255u);
+  uint32_t ctr[4] = {block | (slot << 8) | (cls << 16), (uint32_t)env, (uint32_t)episode,
+                     ((uint32_t)(episode >> 32) & 0x00FFFFFFu) | (STREAM_RESET << 24)};
+  oracle_philox4x32_10(ctr, key, w);
+}
+
+static double lerp_u(double lo, double hi, double u) { return lo + (hi - lo) * u; }
+
+int oracle_env_reset(const asvrl_reset_params* rp, const oracle_env_state* st,
+                     const uint8_t* reset_mask, const int32_t* want_robots,
+                     const int32_t* want_cores, const int32_t* want_obs, const double* min_sg,
+                     uint64_t seed, uint64_t episode, int n_envs, int RP, int OP, int CP,
+                     int64_t env_offset, double* margin_out) {
+  double* sg = (double*)malloc(sizeof(double) * 4 * (size_t)(RP > 0 ? RP : 1));
+  double* cores = (double*)malloc(sizeof(double) * 4 * (size_t)(CP > 0 ? CP : 1));
+  double* obs = (double*)malloc(sizeof(double) * 4 * (size_t)(OP > 0 ? OP : 1));
+  for (int e = 0; e < n_envs; ++e) {
+    if (reset_mask && !reset_mask[e]) continue;
+    const int64_t ge = env_offset + e;
+    double margin = INFINITY;
+    uint32_t w[4];
+    /* robots, ENV:105-120: stop after max_tries draws or when the wanted count is reached */
+    int want_r = want_robots[e] < RP ? want_robots[e] : RP, n_r = 0;
+    for (int t = 0; t < rp->max_tries && n_r < want_r; ++t) {
+      reset_block(seed, episode, ge, 0u, (uint32_t)t, 0, w);
+      double lo = rp->start_margin;
+      double c[4] = {lerp_u(lo, rp->map_w - lo, u01(w[0])), lerp_u(lo, rp->map_h - lo, u01(w[1])),
+                     lerp_u(lo, rp->map_w - lo, u01(w[2])), lerp_u(lo, rp->map_h - lo, u01(w[3]))};
+      if (oracle_check_start_goal(rp, sg, n_r, c, min_sg[e], &margin)) {
+        memcpy(sg + 4 * n_r, c, sizeof c);
+        ++n_r;
+      }
+    }
+    /* vortex cores, ENV:122-136 */
+    int want_c = want_cores[e] < CP ? want_cores[e] : CP, n_c = 0;
+    for (int t = 0; t < rp->max_tries && n_c < want_c; ++t) {
+      reset_block(seed, episode, ge, 1u, (uint32_t)t, 0, w);
+      double c[4] = {rp->map_w * u01(w[0]), rp->map_h * u01(w[1]), (w[2] >> 31) ? 1.0 : -1.0,
+                     2.0 * M_PI * rp->core_r * lerp_u(rp->v_min, rp->v_max, u01(w[3]))};
+      if (oracle_check_core(rp, sg, n_r, cores, n_c, c, &margin)) {
+        memcpy(cores + 4 * n_c, c, sizeof c);
+        ++n_c;
+      }
+    }
+    /* static obstacles, ENV:150-162 */
+    int want_o = want_obs[e] < OP ? want_obs[e] : OP, n_o = 0;
+    for (int t = 0; t < rp->max_tries && n_o < want_o; ++t) {
+      reset_block(seed, episode, ge, 2u, (uint32_t)t, 0, w);
+      double lo = rp->obs_margin;
+      double c[4] = {lerp_u(lo, rp->map_w - lo, u01(w[0])), lerp_u(lo, rp->map_h - lo, u01(w[1])),
+                     lerp_u(rp->obs_r_min, rp->obs_r_max, u01(w[2])), 0.0};
+      if (oracle_check_obstacle(rp, sg, n_r, cores, n_c, obs, n_o, c, &margin)) {
+        memcpy(obs + 4 * n_o, c, sizeof c);
+        ++n_o;
+      }
+    }
+    /* reset_robot ENV:166-176, Robot.reset_state WAMV:177-193 (no cores exist yet at ENV:175,
+     * so the initial sea-floor velocity is zero) */
+    for (int r = 0; r < RP; ++r) {
+      size_t g = (size_t)e * RP + r;
+      int on = r < n_r;
+      double th = 0.0;
+      if (on) {
+        reset_block(seed, episode, ge, 3u, (uint32_t)r, 1, w);
+        th = 2.0 * M_PI * u01(w[0]); /* ENV:171 */
+      }
+      st->x[g] = on ? sg[4 * r] : 0.0; st->y[g] = on ? sg[4 * r + 1] : 0.0; st->theta[g] = th;
+      st->velr_x[g] = st->velr_y[g] = st->velr_r[g] = 0.0;
+      st->vel_x[g] = st->vel_y[g] = st->vel_r[g] = 0.0;
+      st->thrust_l[g] = st->thrust_r[g] = 0.0;
+      st->goal_x[g] = on ? sg[4 * r + 2] : 0.0; st->goal_y[g] = on ? sg[4 * r + 3] : 0.0;
+      st->flags[g] = 0;
+    }
+    for (int i = 0; i < OP; ++i)
+      for (int q = 0; q < 4; ++q) st->obstacles[((size_t)e * OP + i) * 4 + q] = i < n_o ? obs[4 * i + q] : 0.0;
+    for (int i = 0; i < CP; ++i)
+      for (int q = 0; q < 4; ++q) st->cores[((size_t)e * CP + i) * 4 + q] = i < n_c ? cores[4 * i + q] : 0.0;
+    st->n_robots[e] = n_r; st->n_obs[e] = n_o; st->n_cores[e] = n_c;
+    st->ep_steps[e] = 0; /* ENV:96 */
+    if (margin_out) margin_out[e] = margin;
+  }
+  free(sg); free(cores); free(obs);
+  return 0;
+}

@@ -82,6 +82,25 @@ int oracle_qhuber(const double* z, const double* tau, const double* z_next, cons
  * the float32-rounded pi*i table the reference builds (ACIQN:397). */
 int oracle_tau_cos(const double* tau, int batch, int n_tau, int n_cos, double* cos_out);
 
+/* Scenario generation (ENV:72-176).  The three acceptance predicates restate
+ * check_start_and_goal / check_core / check_obstacle (ENV:358-456) and are pinned against the
+ * reference's own methods by tests/golden/reset_checks.npz.  Each returns 1 = accept and lowers
+ * *margin (nullable) to the smallest |distance to a threshold| it evaluated. */
+int oracle_check_start_goal(const asvrl_reset_params* rp, const double* sg, int n,
+                            const double* cand, double min_dis, double* margin);
+int oracle_check_core(const asvrl_reset_params* rp, const double* sg, int n_r, const double* cores,
+                      int n_c, const double* cand, double* margin);
+int oracle_check_obstacle(const asvrl_reset_params* rp, const double* sg, int n_r,
+                          const double* cores, int n_c, const double* obs, int n_o,
+                          const double* cand, double* margin);
+/* the reference's sequential rejection loops applied to the Philox candidate sequence of
+ * include/asvrl.h (stream 2); margin_out [E] nullable */
+int oracle_env_reset(const asvrl_reset_params* rp, const oracle_env_state* st,
+                     const uint8_t* reset_mask, const int32_t* want_robots,
+                     const int32_t* want_cores, const int32_t* want_obs, const double* min_sg,
+                     uint64_t seed, uint64_t episode, int n_envs, int max_robots, int max_obs,
+                     int max_cores, int64_t env_offset, double* margin_out);
+
 /* Philox4x32-10 block, exposed so the tests can pin the generator against the published
  * Random123 known-answer vectors. */
 void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);

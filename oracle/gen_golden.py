@@ -170,6 +170,183 @@ def iqn_case(name, seed):
     print("wrote", name, "loss", loss.item())
 
 
+def reset_checks_case(name, seed, n_cases=400):
+    """The reference's own acceptance predicates (ENV:358-456) on random accepted sets and
+    candidates (many deliberately close to a threshold): inputs + the reference's answers."""
+    ref_env, ref_wamv = rh.import_reference()
+    rng = np.random.RandomState(seed)
+    K = 6
+    rec = {k: [] for k in ("n_r", "n_c", "n_o", "sg", "cores", "obs", "min_dis", "c_sg", "c_core",
+                           "c_obs", "a_sg", "a_core", "a_obs")}
+    for case in range(n_cases):
+        env = ref_env.MarineNavEnv3(seed=0)
+        n_r, n_c, n_o = rng.randint(0, K + 1), rng.randint(0, K + 1), rng.randint(0, K + 1)
+        sg = np.zeros((K, 4)); cores = np.zeros((K, 4)); obs = np.zeros((K, 4))
+        sg[:n_r] = 2.0 + 51.0 * rng.rand(n_r, 4)
+        cores[:n_c, 0:2] = 55.0 * rng.rand(n_c, 2)
+        cores[:n_c, 2] = np.where(rng.rand(n_c) < 0.5, 1.0, -1.0)
+        cores[:n_c, 3] = 2 * np.pi * 0.5 * (2.0 + 2.0 * rng.rand(n_c))
+        obs[:n_o, 0:2] = 5.0 + 45.0 * rng.rand(n_o, 2)
+        obs[:n_o, 2] = 0.5 + rng.rand(n_o)
+        env.robots = []
+        for i in range(n_r):
+            rob = ref_wamv.Robot(seed=0)
+            rob.start, rob.goal = sg[i, 0:2].copy(), sg[i, 2:4].copy()
+            env.robots.append(rob)
+        env.cores = [ref_env.Core(c[0], c[1], bool(c[2] > 0), c[3]) for c in cores[:n_c]]
+        env.obstacles = [ref_env.Obstacle(o[0], o[1], o[2]) for o in obs[:n_o]]
+        env.min_start_goal_dis = float(rng.choice([20.0, 30.0, 40.0]))
+
+        def near(points, radius):  # a candidate at ~radius from a random anchor, or uniform
+            if len(points) and rng.rand() < 0.6:
+                a = points[rng.randint(len(points))]
+                ang = 2 * np.pi * rng.rand()
+                d = radius * (1.0 + 0.05 * rng.randn())
+                return a + d * np.array([np.cos(ang), np.sin(ang)])
+            return -1.0 + 57.0 * rng.rand(2)
+
+        start = near(sg[:n_r, 0:2], 10.0)
+        ang = 2 * np.pi * rng.rand()
+        goal = start + env.min_start_goal_dis * (1.0 + 0.1 * rng.randn()) * np.array([np.cos(ang), np.sin(ang)])
+        if rng.rand() < 0.4:
+            goal = near(sg[:n_r, 2:4], 10.0)
+        c_sg = np.concatenate([start, goal])
+        a_sg = env.check_start_and_goal(start, goal)
+        anchors = np.concatenate([sg[:n_r, 0:2], sg[:n_r, 2:4], cores[:n_c, 0:2]]) if n_r + n_c else np.zeros((0, 2))
+        cc = near(anchors, rng.choice([10.5, 3.0, 1.9, 3.2]))
+        c_core = np.array([cc[0], cc[1], 1.0 if rng.rand() < 0.5 else -1.0, 2 * np.pi * 0.5 * (2.0 + 2.0 * rng.rand())])
+        a_core = env.check_core(ref_env.Core(c_core[0], c_core[1], bool(c_core[2] > 0), c_core[3]))
+        anchors = np.concatenate([anchors, obs[:n_o, 0:2]]) if len(anchors) + n_o else np.zeros((0, 2))
+        oc = near(anchors, rng.choice([11.0, 1.5, 2.0]))
+        c_obs = np.array([oc[0], oc[1], 0.5 + rng.rand()])
+        a_obs = env.check_obstacle(ref_env.Obstacle(c_obs[0], c_obs[1], c_obs[2]))
+        for k, v in (("n_r", n_r), ("n_c", n_c), ("n_o", n_o), ("sg", sg), ("cores", cores), ("obs", obs),
+                     ("min_dis", env.min_start_goal_dis), ("c_sg", c_sg), ("c_core", c_core),
+                     ("c_obs", c_obs), ("a_sg", a_sg), ("a_core", a_core), ("a_obs", a_obs)):
+            rec[k].append(v)
+    d = {k: np.array(v) for k, v in rec.items()}
+    np.savez_compressed(os.path.join(GOLD, name), **d)
+    print("wrote", name, "accept rates", d["a_sg"].mean(), d["a_core"].mean(), d["a_obs"].mean())
+
+
+class PhiloxReplayRNG:
+    """Stands in for MarineNavEnv3.rd (ENV:29) and feeds reset() the counter-indexed candidate
+    sequence of include/asvrl.h (stream 2), so the UNMODIFIED reference reset() generates the
+    scenario the kernel / oracle must reproduce.  Call sites: ENV:58/113 randint (robot seed,
+    ignored), ENV:109-110 start / goal, ENV:126-128 core, ENV:154-155 obstacle, ENV:171 theta."""
+
+    def __init__(self, seed, episode, env):
+        from oracle import oracle as o
+        self.o, self.seed, self.episode, self.env = o, seed, episode, env
+        self.t = {0: 0, 1: 0, 2: 0}
+        self.theta_i = 0
+        self.words = None
+        self.pending = None
+
+    def _block(self, cls, t, theta=False):
+        slot, block = (t, 0) if theta else (t >> 8, t & 255)
+        ctr = [block | (slot << 8) | (cls << 16), self.env & 0xFFFFFFFF, self.episode & 0xFFFFFFFF,
+               ((self.episode >> 32) & 0xFFFFFF) | (2 << 24)]
+        return self.o.philox(ctr, [self.seed & 0xFFFFFFFF, self.seed >> 32])
+
+    @staticmethod
+    def _u(w):
+        return ((int(w) >> 8) + 0.5) / 16777216.0
+
+    def randint(self, lo, hi):
+        return 0
+
+    def binomial(self, n, p):
+        return int(self.words[2]) >> 31                      # core direction, ENV:127
+
+    def uniform(self, low=0.0, high=1.0):
+        if np.ndim(low) == 0:
+            if float(low) == 0.0 and abs(float(high) - 2 * np.pi) < 1e-12:   # ENV:171
+                w = self._block(3, self.theta_i, theta=True)
+                self.theta_i += 1
+                return low + (high - low) * self._u(w[0])
+            # scalar draws that complete a candidate: ENV:128 (v_edge) or ENV:155 (radius)
+            idx = 3 if self.pending == 1 else 2
+            return low + (high - low) * self._u(self.words[idx])
+        low, high = np.asarray(low, float), np.asarray(high, float)
+        if low[0] == 2.0:                                    # start, then goal: one candidate
+            if self.pending == "goal":
+                self.pending = None
+                return low + (high - low) * np.array([self._u(self.words[2]), self._u(self.words[3])])
+            self.words = self._block(0, self.t[0]); self.t[0] += 1
+            self.pending = "goal"
+            return low + (high - low) * np.array([self._u(self.words[0]), self._u(self.words[1])])
+        cls = 1 if low[0] == 0.0 else 2                      # core centre / obstacle centre
+        self.words = self._block(cls, self.t[cls]); self.t[cls] += 1
+        self.pending = cls
+        return low + (high - low) * np.array([self._u(self.words[0]), self._u(self.words[1])])
+
+
+def reset_case(name, seed, E):
+    """The reference's reset() (ENV:72-176) driven by the Philox candidate stream."""
+    ref_env, _ = rh.import_reference()
+    import contextlib, io
+    rng = np.random.RandomState(seed)
+    RP, OP, CP = 8, 12, 8
+    episode, env_offset = (3 << 32) + 11, 700
+    want = np.stack([rng.randint(1, RP + 1, E), rng.randint(0, CP + 1, E), rng.randint(0, OP + 1, E)], 1)
+    want[0] = (8, 8, 12)    # crowded: the 500-try cap leaves it short
+    want[1] = (1, 0, 0)
+    min_sg = rng.choice([20.0, 30.0, 40.0], E)
+    from oracle import oracle as o
+    st = o.new_state(E, RP, OP, CP)
+    for e in range(E):
+        env = ref_env.MarineNavEnv3(seed=0)
+        env.rd = PhiloxReplayRNG(0xABCDEF0123456789 + seed, episode, env_offset + e)
+        env.num_robots, env.num_cores, env.num_obs = (int(v) for v in want[e])
+        env.min_start_goal_dis = float(min_sg[e])
+        with contextlib.redirect_stdout(io.StringIO()):
+            env.reset()
+        st["n_robots"][e], st["n_cores"][e], st["n_obs"][e] = len(env.robots), len(env.cores), len(env.obstacles)
+        for i, rob in enumerate(env.robots):
+            st["x"][e, i], st["y"][e, i], st["theta"][e, i] = rob.x, rob.y, rob.theta
+            st["goal_x"][e, i], st["goal_y"][e, i] = rob.goal
+            assert not rob.velocity.any() and not rob.velocity_r.any() and rob.left_thrust == 0.0
+        for i, c in enumerate(env.cores):
+            st["cores"][e, i] = (c.x, c.y, 1.0 if c.clockwise else -1.0, c.Gamma)
+        for i, ob in enumerate(env.obstacles):
+            st["obstacles"][e, i] = (ob.x, ob.y, ob.r, 0.0)
+    d = {"ref_" + k: v for k, v in st.items()}
+    d.update(want=want.astype(np.int32), min_sg=min_sg, seed=np.uint64(0xABCDEF0123456789 + seed),
+             episode=np.uint64(episode), env_offset=np.int64(env_offset), RP=RP, OP=OP, CP=CP)
+    np.savez_compressed(os.path.join(GOLD, name), **d)
+    print("wrote", name, "placed", st["n_robots"].sum(), st["n_cores"].sum(), st["n_obs"].sum(), "of", want.sum(0))
+
+
+def replay_case(name, seed):
+    """The reference's ReplayBuffer (RB:6-69): add 40 transitions into a maxlen-32 deque, then
+    state_batch + the deque's content in order (what a ring of capacity 32 must hold)."""
+    rh.import_reference()
+    from rfarl.utils.replay_buffer import ReplayBuffer
+    rng = np.random.RandomState(seed)
+    rb = ReplayBuffer(32, 8, 5, 5)
+    n = 40
+    n_obj = rng.randint(0, 6, n)
+    n_obj2 = rng.randint(0, 6, n)
+    self_s = scenes.f32(rng.randn(n, 7)); self_n = scenes.f32(rng.randn(n, 7))
+    obj_s = scenes.f32(rng.randn(n, 5, 5)); obj_n = scenes.f32(rng.randn(n, 5, 5))
+    act = scenes.f32(rng.rand(n, 2) * 2 - 1); rew = scenes.f32(rng.randn(n)); done = rng.rand(n) < 0.2
+    for i in range(n):
+        s = (list(self_s[i]), [list(o) for o in obj_s[i, :n_obj[i]]])
+        s2 = (list(self_n[i]), [list(o) for o in obj_n[i, :n_obj2[i]]])
+        rb.add((s, list(act[i]), float(rew[i]), s2, bool(done[i])))
+    mem = list(rb.memory)
+    st = rb.state_batch([m[0] for m in mem])
+    nst = rb.state_batch([m[3] for m in mem])
+    np.savez_compressed(os.path.join(GOLD, name), n_obj=n_obj, n_obj2=n_obj2, self_s=self_s, self_n=self_n,
+                        obj_s=obj_s, obj_n=obj_n, act=act, rew=rew, done=done,
+                        mem_self=np.array(st[0]), mem_obj=np.array(st[1]), mem_mask=np.array(st[2]),
+                        mem_nself=np.array(nst[0]), mem_nobj=np.array(nst[1]), mem_nmask=np.array(nst[2]),
+                        mem_act=np.array([m[1] for m in mem]), mem_rew=np.array([m[2] for m in mem]),
+                        mem_done=np.array([m[4] for m in mem]))
+    print("wrote", name, np.array(st[1]).shape)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     D, X, A = _abi.M_DYNAMICS, _abi.M_DISCRETE, _abi.M_AUTO_DEACTIVATE
@@ -185,6 +362,9 @@ def main():
     rollout_case("env_rollout.npz", 16, 8, 6, 6, 4, 24)
     current_case("current_field.npz", 17)
     iqn_case("iqn_loss.npz", 18)
+    reset_checks_case("reset_checks.npz", 19)
+    reset_case("env_reset.npz", 20, 48)
+    replay_case("replay.npz", 21)
 
 
 if __name__ == "__main__":

@@ -60,6 +60,17 @@ def lib():
                                                           C.c_void_p]
         _LIB.oracle_tau_cos.restype = C.c_int
         _LIB.oracle_tau_cos.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        dp = C.c_void_p
+        RP_ = C.POINTER(_abi.ResetParams)
+        _LIB.oracle_check_start_goal.restype = C.c_int
+        _LIB.oracle_check_start_goal.argtypes = [RP_, dp, C.c_int, dp, C.c_double, dp]
+        _LIB.oracle_check_core.restype = C.c_int
+        _LIB.oracle_check_core.argtypes = [RP_, dp, C.c_int, dp, C.c_int, dp, dp]
+        _LIB.oracle_check_obstacle.restype = C.c_int
+        _LIB.oracle_check_obstacle.argtypes = [RP_, dp, C.c_int, dp, C.c_int, dp, C.c_int, dp, dp]
+        _LIB.oracle_env_reset.restype = C.c_int
+        _LIB.oracle_env_reset.argtypes = [RP_, C.POINTER(_State), dp, dp, dp, dp, dp, C.c_uint64,
+                                          C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, dp]
         _LIB.oracle_philox4x32_10.restype = None
         _LIB.oracle_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     return _LIB
@@ -155,3 +166,52 @@ def philox(ctr, key):
     out = np.zeros(4, np.uint32)
     lib().oracle_philox4x32_10(_p(ctr), _p(key), _p(out))
     return out
+
+
+def _arr(a, n=4):
+    a = np.ascontiguousarray(a, np.float64).reshape(-1, n) if a is not None and len(a) else np.zeros((0, n))
+    return a
+
+
+def check_start_goal(rp, sg, cand, min_dis):
+    """ENV:358-376 -> (accept, margin)."""
+    sg, cand = _arr(sg), np.ascontiguousarray(cand, np.float64)
+    m = np.array([np.inf])
+    ok = lib().oracle_check_start_goal(C.byref(rp), _p(sg), len(sg), _p(cand), float(min_dis), _p(m))
+    return bool(ok), float(m[0])
+
+
+def check_core(rp, sg, cores, cand):
+    """ENV:378-418 -> (accept, margin)."""
+    sg, cores, cand = _arr(sg), _arr(cores), np.ascontiguousarray(cand, np.float64)
+    m = np.array([np.inf])
+    ok = lib().oracle_check_core(C.byref(rp), _p(sg), len(sg), _p(cores), len(cores), _p(cand), _p(m))
+    return bool(ok), float(m[0])
+
+
+def check_obstacle(rp, sg, cores, obs, cand):
+    """ENV:420-456 -> (accept, margin)."""
+    sg, cores, obs = _arr(sg), _arr(cores), _arr(obs)
+    cand = np.ascontiguousarray(cand, np.float64)
+    m = np.array([np.inf])
+    ok = lib().oracle_check_obstacle(C.byref(rp), _p(sg), len(sg), _p(cores), len(cores), _p(obs),
+                                     len(obs), _p(cand), _p(m))
+    return bool(ok), float(m[0])
+
+
+def env_reset(rp, st, reset_mask, want_robots, want_cores, want_obs, min_sg, seed, episode,
+              max_obs, max_cores, env_offset=0):
+    """ENV:72-176 over the Philox candidate sequence, IN PLACE on the float64 state dict;
+    returns the per-env smallest predicate margin."""
+    E, RP = st["x"].shape
+    cs = _State(**{k: _p(v) for k, v in st.items()})
+    i32 = lambda a: np.ascontiguousarray(a, np.int32)
+    wr, wc, wo = i32(want_robots), i32(want_cores), i32(want_obs)
+    ms = np.ascontiguousarray(min_sg, np.float64)
+    mask = None if reset_mask is None else np.ascontiguousarray(reset_mask, np.uint8)
+    margin = np.full((E,), np.inf)
+    rc = lib().oracle_env_reset(C.byref(rp), C.byref(cs), _p(mask), _p(wr), _p(wc), _p(wo), _p(ms),
+                                seed, episode, E, RP, max_obs, max_cores, env_offset, _p(margin))
+    if rc != 0:
+        raise RuntimeError("oracle_env_reset failed")
+    return margin

@@ -120,3 +120,82 @@ def test_philox_known_answers(oracle):
     ]
     for ctr, key, want in kat:
         assert tuple(int(x) for x in oracle.philox(ctr, key)) == want
+
+
+def test_reset_predicates_against_reference(oracle):
+    """check_start_and_goal / check_core / check_obstacle (ENV:358-456): the reference's own
+    answers on 400 random (accepted set, candidate) cases, many near a threshold."""
+    d = gu.load("reset_checks.npz")
+    rp = _abi.default_reset_params()
+    for i in range(len(d["n_r"])):
+        nr, nc, no = int(d["n_r"][i]), int(d["n_c"][i]), int(d["n_o"][i])
+        sg, cores, obs = d["sg"][i, :nr], d["cores"][i, :nc], d["obs"][i, :no]
+        assert oracle.check_start_goal(rp, sg, d["c_sg"][i], float(d["min_dis"][i]))[0] == bool(d["a_sg"][i]), i
+        assert oracle.check_core(rp, sg, cores, d["c_core"][i])[0] == bool(d["a_core"][i]), i
+        assert oracle.check_obstacle(rp, sg, cores, obs, d["c_obs"][i])[0] == bool(d["a_obs"][i]), i
+
+
+def test_reset_against_reference_reset(oracle):
+    """The unmodified reference reset() (ENV:72-176), fed the Philox candidate stream through a
+    stand-in for its RandomState, against oracle_env_reset: same counts, same scenario."""
+    d = gu.load("env_reset.npz")
+    rp = _abi.default_reset_params()
+    E = len(d["min_sg"])
+    RP, OP, CP = int(d["RP"]), int(d["OP"]), int(d["CP"])
+    st = oracle.new_state(E, RP, OP, CP)
+    for v in st.values():
+        v[...] = 7  # every field of a reset env must be overwritten
+    oracle.env_reset(rp, st, None, d["want"][:, 0], d["want"][:, 1], d["want"][:, 2], d["min_sg"],
+                     int(d["seed"]), int(d["episode"]), OP, CP, env_offset=int(d["env_offset"]))
+    for k in ("n_robots", "n_cores", "n_obs"):
+        assert np.array_equal(st[k], d["ref_" + k]), k
+    assert (st["n_obs"] < d["want"][:, 2]).any()  # the 500-try cap is exercised
+    for k in ("x", "y", "theta", "goal_x", "goal_y", "obstacles", "cores"):
+        assert np.allclose(st[k], d["ref_" + k], rtol=1e-13, atol=1e-13), k
+    for k in ("velr_x", "velr_y", "velr_r", "vel_x", "vel_y", "vel_r", "thrust_l", "thrust_r", "flags", "ep_steps"):
+        assert not st[k].any(), k
+
+
+def test_reset_mask_and_offset(oracle):
+    rp = _abi.default_reset_params()
+    E, RP, OP, CP = 12, 4, 5, 3
+    want = (np.full(E, 4), np.full(E, 3), np.full(E, 5), np.full(E, 30.0))
+    a = oracle.new_state(E, RP, OP, CP)
+    oracle.env_reset(rp, a, None, *want, 5, 9, OP, CP, env_offset=100)
+    b = oracle.new_state(4, RP, OP, CP)
+    oracle.env_reset(rp, b, None, *(w[:4] for w in want), 5, 9, OP, CP, env_offset=104)
+    for k in a:
+        assert np.array_equal(a[k][4:8], b[k]), k  # streams follow the GLOBAL env index
+    c = {k: v.copy() for k, v in a.items()}
+    mask = (np.arange(E) % 2).astype(np.uint8)
+    oracle.env_reset(rp, c, mask, *want, 5, 10, OP, CP, env_offset=100)
+    assert np.array_equal(c["x"][mask == 0], a["x"][mask == 0])
+    assert not np.array_equal(c["x"][mask == 1], a["x"][mask == 1])
+
+
+def test_replay_ring_against_reference_buffer():
+    """ReplayBuffer (RB:6-69): deque(maxlen) content order, state_batch padding and masks."""
+    from oracle import replay_oracle as ro
+    d = gu.load("replay.npz")
+    n = len(d["rew"])
+    t = np.arange(5)[None, :]
+    mask = (t < d["n_obj"][:, None]).astype(np.float32)
+    nmask = (t < d["n_obj2"][:, None]).astype(np.float32)
+    obj = d["obj_s"] * mask[:, :, None]     # the env emits zero rows beyond the kept objects
+    nobj = d["obj_n"] * nmask[:, :, None]
+    status = np.where(d["done"], _abi.S_DONE, 0).astype(np.uint32)
+    ring = ro.Ring(32)
+    for lo in range(0, n, 8):  # five "batched steps" of 8 ASVs each
+        sl = slice(lo, lo + 8)
+        rows = ro.make_rows(d["self_s"][sl], obj[sl], mask[sl], d["act"][sl], False, d["rew"][sl],
+                            d["self_n"][sl], nobj[sl], nmask[sl], status[sl])
+        ring.push(rows, ro.valid_rows(status[sl]))
+    assert ring.size == 32 and ring.total == n
+    order = [(ring.total + i) % 32 for i in range(32)]  # oldest -> newest, like list(deque)
+    got = ring.gather(order)
+    for k, ref in (("self", "mem_self"), ("obj", "mem_obj"), ("mask", "mem_mask"), ("nself", "mem_nself"),
+                   ("nobj", "mem_nobj"), ("nmask", "mem_nmask"), ("act", "mem_act"), ("rew", "mem_rew")):
+        assert np.array_equal(got[k], d[ref].astype(np.float32)), k
+    assert np.array_equal(got["done"], d["mem_done"].astype(np.float32))
+    s, o, m = ro.state_batch_rows([(list(d["self_s"][i]), [list(x) for x in d["obj_s"][i, :d["n_obj"][i]]]) for i in range(8, 40)])
+    assert np.array_equal(s, d["mem_self"].astype(np.float32)) and np.array_equal(m, d["mem_mask"].astype(np.float32))

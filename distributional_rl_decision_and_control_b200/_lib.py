@@ -24,19 +24,19 @@ _SIGNATURES = {
     "asvrl_reset_default_params": (None, [C.c_void_p]),
     "asvrl_env_step": (C.c_int, [C.POINTER(_abi.EnvParams), C.POINTER(_abi.EnvStatePtrs), vp, f32p,
                                  u8p, C.c_uint64, C.c_uint64, C.POINTER(_abi.EnvOutPtrs), C.c_int,
-                                 C.c_int, C.c_int, C.c_int, C.c_int64, C.c_uint32, vp]),
+                                 C.c_int, C.c_int, C.c_int, C.c_int64, C.c_uint32, u64p, vp]),
     "asvrl_env_noise": (C.c_int, [C.POINTER(_abi.EnvParams), C.c_uint64, C.c_uint64, C.c_int,
                                   C.c_int, C.c_int, C.c_int64, f32p, vp]),
     "asvrl_env_reset": (C.c_int, [C.c_void_p, C.POINTER(_abi.EnvStatePtrs), u8p, i32p, i32p, i32p,
                                   f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
-                                  C.c_int64, vp]),
+                                  C.c_int64, u64p, vp]),
     "asvrl_replay_push": (C.c_int, [f32p, C.c_int64, u64p, f32p, f32p, f32p, vp, C.c_int, f32p,
                                     f32p, f32p, f32p, u32p, C.c_int, u32p, vp]),
     "asvrl_replay_sample": (C.c_int, [f32p, u64p, C.c_int64, i64p, C.c_uint64, C.c_uint64, C.c_int,
                                       f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, i64p,
-                                      vp]),
+                                      u64p, vp]),
     "asvrl_iqn_tau_cos": (C.c_int, [f32p, C.c_uint64, C.c_uint64, C.c_float, C.c_int, C.c_int,
-                                    C.c_int, f32p, f32p, vp]),
+                                    C.c_int, f32p, f32p, u64p, vp]),
     "asvrl_qhuber_fwd_bwd": (C.c_int, [f32p, f32p, f32p, f32p, f32p, C.c_float, C.c_float, C.c_int,
                                        C.c_int, C.c_int, f32p, f32p, f32p, u32p, vp]),
 }
@@ -152,7 +152,7 @@ def new_out(E, RP, device, debug=True):
 
 
 def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, step=0,
-             env_offset=0, env_mask=None, st_ptrs=None, o_ptrs=None):
+             env_offset=0, env_mask=None, st_ptrs=None, o_ptrs=None, counter_dev=None):
     E, RP = st["x"].shape
     if actions is not None:
         want = torch.int32 if (mode & _abi.M_DISCRETE) else torch.float32
@@ -163,7 +163,7 @@ def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, 
     op = o_ptrs if o_ptrs is not None else out_ptrs(out)
     rc = lib().asvrl_env_step(C.byref(params), C.byref(sp), a_ptr, ptr(noise, torch.float32),
                               ptr(env_mask, torch.uint8), seed, step, C.byref(op), E, RP, max_obs,
-                              max_cores, env_offset, mode, stream_ptr())
+                              max_cores, env_offset, mode, ptr(counter_dev, torch.int64), stream_ptr())
     check(rc, "asvrl_env_step")
     return out
 
@@ -177,13 +177,14 @@ def env_noise(params, seed, step, E, RP, OP, device, env_offset=0):
 
 
 def env_reset(rparams, st, reset_mask, want_robots, want_cores, want_obs, min_sg, seed, episode,
-              max_obs, max_cores, env_offset=0, st_ptrs=None):
+              max_obs, max_cores, env_offset=0, st_ptrs=None, counter_dev=None):
     E, RP = st["x"].shape
     sp = st_ptrs if st_ptrs is not None else state_ptrs(st)
     rc = lib().asvrl_env_reset(C.byref(rparams), C.byref(sp), ptr(reset_mask, torch.uint8),
                                ptr(want_robots, torch.int32), ptr(want_cores, torch.int32),
                                ptr(want_obs, torch.int32), ptr(min_sg, torch.float32), seed, episode,
-                               E, RP, max_obs, max_cores, env_offset, stream_ptr())
+                               E, RP, max_obs, max_cores, env_offset, ptr(counter_dev, torch.int64),
+                               stream_ptr())
     check(rc, "asvrl_env_reset")
 
 
@@ -203,11 +204,11 @@ def qhuber_fwd_bwd(z, tau, z_next, r, done, gamma, kappa, workspace, lps=None, g
 
 
 def iqn_tau_cos(B, N, n_cos, device, tau_in=None, seed=0, counter=0, cvar=1.0, tau_out=None,
-                cos_out=None):
+                cos_out=None, counter_dev=None):
     tau_out = torch.empty((B, N), dtype=torch.float32, device=device) if tau_out is None else tau_out
     cos_out = torch.empty((B, N, n_cos), dtype=torch.float32, device=device) if cos_out is None else cos_out
     rc = lib().asvrl_iqn_tau_cos(ptr(tau_in, torch.float32), seed, counter, cvar, B, N, n_cos,
-                                 ptr(tau_out), ptr(cos_out), stream_ptr())
+                                 ptr(tau_out), ptr(cos_out), ptr(counter_dev, torch.int64), stream_ptr())
     check(rc, "asvrl_iqn_tau_cos")
     return tau_out, cos_out
 
@@ -251,7 +252,7 @@ def new_batch(B, device):
             "indices": torch.empty((B,), dtype=torch.int64, device=device)}
 
 
-def replay_sample(rb, batch, seed=0, counter=0, indices=None):
+def replay_sample(rb, batch, seed=0, counter=0, indices=None, counter_dev=None):
     """Fills the dense batch tensors of ``batch`` (new_batch) from the ring."""
     B = batch["rew"].numel()
     rc = lib().asvrl_replay_sample(ptr(rb["rows"], torch.float32), ptr(rb["head_size"], torch.int64),
@@ -259,6 +260,7 @@ def replay_sample(rb, batch, seed=0, counter=0, indices=None):
                                    ptr(batch["self"]), ptr(batch["obj"]), ptr(batch["mask"]),
                                    ptr(batch["act"]), ptr(batch["rew"]), ptr(batch["nself"]),
                                    ptr(batch["nobj"]), ptr(batch["nmask"]), ptr(batch["done"]),
-                                   ptr(batch["indices"], torch.int64), stream_ptr())
+                                   ptr(batch["indices"], torch.int64), ptr(counter_dev, torch.int64),
+                                   stream_ptr())
     check(rc, "asvrl_replay_sample")
     return batch

@@ -1,0 +1,333 @@
+"""Agent façade with the reference's constructor, ``act_*`` / ``train`` / ``soft_update`` /
+``save_latest_model`` / ``load_model`` surface (rfarl/rfarl/agent.py:18-707) for the two
+distributional agents on the hot path, AC-IQN and IQN.
+
+What changed underneath (same results, different machinery):
+  * replay sampling, padding and masks come from the device ring (kernel K2b), not from python
+    lists re-uploaded on every call (AGENT:387-392);
+  * tau sampling + the cosine table are kernel K3, the Bellman target + pairwise TD matrix +
+    quantile-Huber loss + its gradient are ONE launch of kernel K4 (AGENT:401-412);
+  * ``act_batch`` evaluates the policy for every ASV of every environment in one forward
+    (the reference runs one batch-1 forward per ASV per step, AGENT:207-225);
+  * ``enable_cuda_graph()`` captures a whole update (sample -> critic step -> actor step) in a
+    CUDA graph: at B=64 the update is ~100 tiny launches and is launch-latency bound;
+  * under ``torch.distributed`` the flat gradient of each optimiser step is averaged with one
+    NCCL all-reduce BEFORE clipping, so all ranks clip and step identically.
+The other four agent types of the reference (DDPG, DQN, SAC, Rainbow) are outside this round's
+scope and raise.
+"""
+import copy
+import random
+
+import numpy as np
+import torch
+import torch.optim as optim
+
+from .policy.AC_IQN_model import AC_IQN_Policy
+from .policy.IQN_model import IQN_Policy
+from .policy.iqn_ops import quantile_huber_loss
+from .utils.replay_buffer import ReplayBuffer, state_batch
+
+_TARGET_SALT = 0x9E3779B97F4A7C15
+
+
+class Agent():
+    def __init__(self,
+                 self_dimension=7,
+                 object_dimension=5,
+                 max_object_num=5,
+                 self_feature_dimension=56,
+                 object_feature_dimension=40,
+                 concat_feature_dimension=256,
+                 hidden_dimension=128,
+                 value_ranges_of_action=[[-1.0, 1.0], [-1.0, 1.0]],  # AC-IQN
+                 action_size=25,  # IQN
+                 multi_steps=3,
+                 BATCH_SIZE=64,
+                 BUFFER_SIZE=1_000_000,
+                 LR=1e-4,
+                 TAU=1.0,
+                 GAMMA=0.99,
+                 device="cpu",
+                 seed=0,
+                 training=True,
+                 agent_type=None,
+                 num_tau=8,
+                 process_group=None,
+                 rank=0):
+        self.device = torch.device(device) if not isinstance(device, torch.device) else device
+        self.LR = LR
+        self.TAU = TAU
+        self.GAMMA = GAMMA
+        self.BUFFER_SIZE = BUFFER_SIZE
+        self.BATCH_SIZE = BATCH_SIZE
+        self.training = training
+        self.value_ranges_of_action = copy.deepcopy(value_ranges_of_action)
+        self.action_size = action_size
+        self.agent_type = agent_type
+        self.num_tau = int(num_tau)  # N = N' (8 in the reference: ACIQN:462, AGENT:407)
+        self.process_group = process_group
+        self.rank = int(rank)
+        self._graph = None
+        self._dims = (self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                      object_feature_dimension, concat_feature_dimension, hidden_dimension)
+
+        if training:
+            if self.device.type != "cuda":
+                raise RuntimeError("training runs on a CUDA device only: the replay ring and the IQN "
+                                   "kernels have no CPU fallback")
+            capt = dict(lr=self.LR, capturable=True)
+            if agent_type == "AC-IQN":
+                self.policy_local = AC_IQN_Policy(*self._dims, value_ranges_of_action, self.device, seed)
+                self.policy_target = AC_IQN_Policy(*self._dims, value_ranges_of_action, self.device, seed)
+                self.actor_optimizer = optim.Adam(self.policy_local.actor.parameters(), **capt)
+                self.critic_optimizer = optim.Adam(self.policy_local.critic.parameters(), **capt)
+                samplers = [(self.policy_local.critic.tau_sampler, 0),
+                            (self.policy_target.critic.tau_sampler, _TARGET_SALT)]
+            elif agent_type == "IQN":
+                self.policy_local = IQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
+                self.policy_target = IQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
+                self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
+                samplers = [(self.policy_local.tau_sampler, 0),
+                            (self.policy_target.tau_sampler, _TARGET_SALT)]
+            elif agent_type in ("DDPG", "DQN", "SAC", "Rainbow"):
+                raise RuntimeError(f"Agent type {agent_type} is outside this build's scope "
+                                   "(AC-IQN and IQN are implemented)")
+            else:
+                raise RuntimeError("Agent type not implemented!")
+            # local and target nets must not share a tau stream, and neither may two ranks
+            for s, salt in samplers:
+                s.seed = (s.seed ^ salt ^ (self.rank * 0xD1B54A32D192ED03)) & 0xFFFFFFFFFFFFFFFF
+            self.memory = ReplayBuffer(BUFFER_SIZE, BATCH_SIZE, object_dimension, max_object_num,
+                                       seed=249 + 7919 * self.rank, device=self.device)
+            self._explore_gen = torch.Generator(device=self.device)
+            self._explore_gen.manual_seed(seed + 104729 * (self.rank + 1))
+
+    # ------------------------------------------------------------------ acting
+    def state_to_tensor(self, states):
+        """AGENT:360-368: host lists -> float32 tensors on the agent's device; the object tensors
+        are None when the batch has no object at all."""
+        self_b, obj_b, mask_b = states
+        dev = self.device
+        self_t = torch.tensor(self_b).float().to(dev)
+        if len(obj_b) == 0:
+            return (self_t, None, None)
+        return (self_t, torch.tensor(obj_b).float().to(dev), torch.tensor(mask_b).float().to(dev))
+
+    def act_ac_iqn(self, state, eps=0.0, cvar=1.0, use_eval=True):
+        """epsilon-greedy action of ONE ASV (AGENT:207-225)."""
+        if random.random() > eps:
+            x = self.state_to_tensor(state_batch([state]))
+            actor = self.policy_local.actor
+            actor.eval() if use_eval else actor.train()
+            with torch.no_grad():
+                action = actor(x).cpu().data.numpy()[0].tolist()
+            actor.train()
+            return action
+        return [np.random.uniform(low=lo, high=hi) for lo, hi in self.value_ranges_of_action]
+
+    def act_iqn(self, state, eps=0.0, cvar=1.0, use_eval=True):
+        """(action id, quantiles, taus) of ONE ASV (AGENT:227-250)."""
+        x = self.state_to_tensor(state_batch([state]))
+        net = self.policy_local
+        net.eval() if use_eval else net.train()
+        with torch.no_grad():
+            quantiles, taus = net(x, net.K, cvar)
+            action_values = quantiles.mean(dim=1)
+        net.train()
+        if random.random() > eps:
+            action = np.argmax(action_values.cpu().data.numpy())
+        else:
+            action = random.choice(np.arange(self.action_size))
+        return action, quantiles.cpu().data.numpy(), taus.cpu().data.numpy()
+
+    @torch.no_grad()
+    def act_batch(self, obs, eps=0.0, cvar=1.0):
+        """Vectorised epsilon-greedy for M ASVs at once: ``obs`` = (self (M,7), objects (M,5,5),
+        mask (M,5)) CUDA tensors.  Returns float32 (M,2) actions (AC-IQN) or int32 (M,) action ids
+        (IQN), still on the device."""
+        M = obs[0].shape[0]
+        explore = torch.rand((M,), device=self.device, generator=self._explore_gen) < eps
+        if self.agent_type == "AC-IQN":
+            greedy = self.policy_local.actor(obs)
+            lo = torch.tensor([r[0] for r in self.value_ranges_of_action], device=self.device)
+            hi = torch.tensor([r[1] for r in self.value_ranges_of_action], device=self.device)
+            rnd = lo + (hi - lo) * torch.rand((M, len(lo)), device=self.device, generator=self._explore_gen)
+            return torch.where(explore.unsqueeze(-1), rnd, greedy).contiguous()
+        net = self.policy_local
+        quantiles, _ = net(obs, net.K, cvar)
+        greedy = quantiles.mean(dim=1).argmax(dim=1)
+        rnd = torch.randint(0, self.action_size, (M,), device=self.device, generator=self._explore_gen)
+        return torch.where(explore, rnd, greedy).to(torch.int32).contiguous()
+
+    # ------------------------------------------------------------------ learning
+    def train(self):
+        """One learner update (AGENT:370-384).  AC-IQN returns (critic_loss, actor_loss), IQN the
+        loss, as numpy scalars like the reference (AGENT:432, 476)."""
+        if self._graph is not None:
+            out = self.train_graph_replay()
+        elif self.agent_type == "AC-IQN":
+            out = self.train_AC_IQN()
+        elif self.agent_type == "IQN":
+            out = self.train_IQN()
+        else:
+            raise RuntimeError("Agent type not implemented!")
+        if isinstance(out, tuple):
+            return tuple(o.detach().cpu().numpy() for o in out)
+        return out.detach().cpu().numpy()
+
+    def _sync_grads(self, params):
+        """Data-parallel exchange step: average ONE flat fp32 bucket over the ranks."""
+        if self.process_group is None:
+            return
+        import torch.distributed as dist
+        grads = [p.grad for p in params if p.grad is not None]
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.process_group)
+        flat.div_(dist.get_world_size(self.process_group))
+        off = 0
+        for g in grads:
+            n = g.numel()
+            g.copy_(flat[off:off + n].view_as(g))
+            off += n
+
+    def _batch(self, batch):
+        b = self.memory.sample_device() if batch is None else batch
+        return ((b["self"], b["obj"], b["mask"]), b["act"], b["rew"], (b["nself"], b["nobj"], b["nmask"]),
+                b["done"])
+
+    def train_AC_IQN(self, batch=None, taus=None):
+        """AGENT:386-432 on device tensors.  Returns (critic_loss, actor_loss) as 0-d CUDA tensors.
+        ``batch`` / ``taus`` inject the sample and the local critic's tau (parity tests)."""
+        states, actions, rewards, next_states, dones = self._batch(batch)
+        N = self.num_tau
+        local, target = self.policy_local, self.policy_target
+
+        # critic step ------------------------------------------------------------------
+        self.critic_optimizer.zero_grad(set_to_none=True)
+        with torch.no_grad():
+            next_actions = target.actor(next_states)                     # AGENT:396
+            z_next, _ = target.critic(next_states, next_actions, N)      # AGENT:399 (tau' unused)
+        z, tau = local.critic(states, actions, N, taus=taus)             # AGENT:403
+        critic_loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones,
+                                             self.GAMMA, 1.0)            # K4 = AGENT:401-412
+        critic_loss.backward()
+        critic_params = list(local.critic.parameters())
+        self._sync_grads(critic_params)
+        torch.nn.utils.clip_grad_norm_(critic_params, 0.5)               # AGENT:415
+        self.critic_optimizer.step()
+
+        # actor step -------------------------------------------------------------------
+        self.actor_optimizer.zero_grad(set_to_none=True)
+        q, _ = local.critic(states, local.actor(states), N)              # AGENT:420-422
+        actor_loss = -q.mean()
+        actor_loss.backward()
+        actor_params = list(local.actor.parameters())
+        self._sync_grads(actor_params)
+        torch.nn.utils.clip_grad_norm_(actor_params, 0.5)                # AGENT:426
+        self.actor_optimizer.step()
+        return critic_loss.detach(), actor_loss.detach()
+
+    def train_IQN(self, batch=None, taus=None):
+        """AGENT:434-476 on device tensors.  Returns the loss as a 0-d CUDA tensor."""
+        states, actions, rewards, next_states, dones = self._batch(batch)
+        N = self.num_tau
+        B = rewards.shape[0]
+        self.optimizer.zero_grad(set_to_none=True)
+        with torch.no_grad():
+            zn_all, _ = self.policy_target(next_states, N)               # (B, N, A)
+            z_next = zn_all.max(dim=2)[0]                                # AGENT:451-452
+        z_all, tau = self.policy_local(states, N, taus=taus)
+        a = actions[:, 0].long().view(B, 1, 1).expand(B, N, 1)           # AGENT:457-458
+        z = z_all.gather(2, a).squeeze(-1)
+        loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones, self.GAMMA, 1.0)
+        loss.backward()
+        params = list(self.policy_local.parameters())
+        self._sync_grads(params)
+        torch.nn.utils.clip_grad_norm_(params, 0.5)                      # AGENT:472
+        self.optimizer.step()
+        return loss.detach()
+
+    # ------------------------------------------------------------------ CUDA graph of one update
+    def enable_cuda_graph(self, warmup=3):
+        """Capture sample -> critic step -> actor step as one CUDA graph.  RNG counters of the
+        sampler and of the tau streams are read from a device word that the graph itself
+        advances, so every replay draws a fresh batch and fresh taus."""
+        if self.memory.size() < self.BATCH_SIZE:
+            raise RuntimeError("fill the replay buffer with at least one batch before capturing")
+        step = self.train_AC_IQN if self.agent_type == "AC-IQN" else self.train_IQN
+        dev = self.device
+        with torch.cuda.device(dev):
+            self._ctr = torch.zeros((1,), dtype=torch.int64, device=dev)
+            self.memory.counter_dev = self._ctr
+            nets = [self.policy_local.critic, self.policy_target.critic] if self.agent_type == "AC-IQN" \
+                else [self.policy_local, self.policy_target]
+            for n in nets:
+                n.tau_sampler.counter_dev = self._ctr
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(warmup):
+                    step()
+                    self._ctr.add_(16)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = step()
+                self._ctr.add_(16)
+            self._graph, self._graph_out = graph, out
+        return graph
+
+    def train_graph_replay(self):
+        self._graph.replay()
+        return self._graph_out
+
+    def disable_cuda_graph(self):
+        self._graph = None
+
+    # ------------------------------------------------------------------ target sync, checkpoints
+    def soft_update(self):
+        """theta_target = TAU * theta_local + (1 - TAU) * theta_target (AGENT:643-656; TAU = 1.0 in
+        the reference, i.e. a hard copy every target_update_interval steps)."""
+        if self.agent_type == "AC-IQN":
+            pairs = [(self.policy_target.actor, self.policy_local.actor),
+                     (self.policy_target.critic, self.policy_local.critic)]
+        elif self.agent_type == "IQN":
+            pairs = [(self.policy_target, self.policy_local)]
+        else:
+            raise RuntimeError("Agent type not implemented!")
+        with torch.no_grad():
+            for tgt, src in pairs:
+                tp, sp = list(tgt.parameters()), list(src.parameters())
+                if self.TAU == 1.0:
+                    torch._foreach_copy_(tp, sp)
+                else:
+                    torch._foreach_mul_(tp, 1.0 - self.TAU)
+                    torch._foreach_add_(tp, sp, alpha=self.TAU)
+
+    def save_latest_model(self, directory):
+        self.policy_local.save(directory)
+
+    def load_model(self, path, device="cpu"):
+        """Restores policy_local only, like the reference (AGENT:684-698).  Parameters are copied
+        in place so optimisers and a captured graph stay valid."""
+        cls = AC_IQN_Policy if self.agent_type == "AC-IQN" else IQN_Policy if self.agent_type == "IQN" else None
+        if cls is None:
+            raise RuntimeError("Agent type not implemented!")
+        loaded = cls.load(path, device)
+        if not hasattr(self, "policy_local"):
+            self.policy_local = loaded
+            return
+        if self.agent_type == "AC-IQN":
+            self.policy_local.actor.load_state_dict(loaded.actor.state_dict())
+            self.policy_local.critic.load_state_dict(loaded.critic.state_dict())
+        else:
+            self.policy_local.load_state_dict(loaded.state_dict())
+
+
+def calculate_huber_loss(td_errors, k=1.0):
+    """Element-wise Huber loss (AGENT:701-707) — kept for callers of the reference helper; the
+    training path uses the fused kernel (policy/iqn_ops.quantile_huber_loss) instead."""
+    a = td_errors.abs()
+    return torch.where(a <= k, 0.5 * td_errors.pow(2), k * (a - 0.5 * k))

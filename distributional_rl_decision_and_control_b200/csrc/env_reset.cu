@@ -41,7 +41,7 @@ env_reset_kernel(const __grid_constant__ ResetConsts k, ResetState st,
                  const uint8_t* __restrict__ reset_mask, const int32_t* __restrict__ want_robots,
                  const int32_t* __restrict__ want_cores, const int32_t* __restrict__ want_obs,
                  const float* __restrict__ min_sg, uint64_t seed, uint64_t episode, int E, int RP,
-                 int OP, int CP, int64_t env_offset) {
+                 int OP, int CP, int64_t env_offset, const uint64_t* __restrict__ counter_dev) {
   __shared__ float4 s_sg[RS_WARPS][RS_MAXR];    // start.xy, goal.xy
   __shared__ float4 s_core[RS_WARPS][RS_MAXC];  // x, y, +-1, Gamma
   __shared__ float4 s_obs[RS_WARPS][RS_MAXO];   // x, y, r, 0
@@ -49,6 +49,7 @@ env_reset_kernel(const __grid_constant__ ResetConsts k, ResetState st,
   const int e = blockIdx.x * RS_WARPS + warp;
   if (e >= E) return;
   if (reset_mask && !reset_mask[e]) return;
+  if (counter_dev) episode += *counter_dev;
   const int64_t ge = env_offset + e;
   const unsigned FULL = 0xffffffffu;
   const float TWO_PI = 6.28318530717959f;
@@ -197,7 +198,7 @@ extern "C" int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env
                                const int32_t* want_cores, const int32_t* want_obs,
                                const float* min_start_goal_dis, uint64_t seed, uint64_t episode,
                                int n_envs, int max_robots, int max_obs, int max_cores,
-                               int64_t env_offset, void* stream) {
+                               int64_t env_offset, const uint64_t* counter_dev, void* stream) {
   if (!params || !state || !want_robots || !want_cores || !want_obs || !min_start_goal_dis)
     return fail(ASVRL_E_BADARG, "asvrl_env_reset: null argument");
   if (n_envs < 0 || max_robots < 1 || max_obs < 0 || max_cores < 0)
@@ -219,6 +220,6 @@ extern "C" int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env
   const int grid = (n_envs + RS_WARPS - 1) / RS_WARPS;
   env_reset_kernel<<<grid, RS_WARPS * 32, 0, (cudaStream_t)stream>>>(
       k, st, reset_mask, want_robots, want_cores, want_obs, min_start_goal_dis, seed, episode,
-      n_envs, max_robots, max_obs, max_cores, env_offset);
+      n_envs, max_robots, max_obs, max_cores, env_offset, counter_dev);
   return check_launch("asvrl_env_reset");
 }

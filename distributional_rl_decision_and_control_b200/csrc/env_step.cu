@@ -207,13 +207,14 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
                 StatePtrs st, const void* __restrict__ actions,
                 const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
                 uint64_t step, OutPtrs out, int E, int RP, int OP, int CP, int64_t env_offset,
-                uint32_t mode, int EPB) {
+                uint32_t mode, int EPB, const uint64_t* __restrict__ counter_dev) {
   extern __shared__ __align__(16) char smem_raw[];
   const Smem m = carve(smem_raw, L);
   const int tid = threadIdx.x;
   const int A = EPB * RP, S = OP + RP, SK = S | 1, NP = A * S;
   const int e0 = blockIdx.x * EPB;
   const bool dyn = mode & ASVRL_M_DYNAMICS;
+  if (counter_dev) step += *counter_dev;  // graph-replay friendly RNG counter (include/asvrl.h)
 
   // ---- phase 0: per-env tables and the pre-step poses (for the noise prefetch filter) ----
   if (tid < EPB) {
@@ -676,7 +677,7 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
                               const void* actions, const float* noise, const uint8_t* env_mask,
                               uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,
                               int max_robots, int max_obs, int max_cores, int64_t env_offset,
-                              uint32_t mode, void* stream) {
+                              uint32_t mode, const uint64_t* counter_dev, void* stream) {
   if (!params || !state || !out) return fail(ASVRL_E_BADARG, "asvrl_env_step: null struct");
   if (n_envs < 0 || max_robots < 1 || max_obs < 0 || max_cores < 0)
     return fail(ASVRL_E_BADARG, "asvrl_env_step: bad sizes");
@@ -709,7 +710,7 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
   }
   kern<<<grid, TPB, smem, s>>>(k, L, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
-                               max_cores, env_offset, mode, EPB);
+                               max_cores, env_offset, mode, EPB, counter_dev);
   return check_launch("asvrl_env_step");
 }
 

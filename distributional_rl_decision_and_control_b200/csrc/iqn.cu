@@ -95,7 +95,9 @@ qhuber_kernel(const float* __restrict__ z, const float* __restrict__ tau,
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 tau_cos_kernel(const float* __restrict__ tau_in, uint64_t seed, uint64_t counter, float cvar,
-               int rows, int n_cos, float* __restrict__ tau_out, float* __restrict__ cos_out) {
+               int rows, int n_cos, float* __restrict__ tau_out, float* __restrict__ cos_out,
+               const uint64_t* __restrict__ counter_dev) {
+  if (counter_dev) counter += *counter_dev;
   const int lane = threadIdx.x & 31;
   const int warps_per_grid = (gridDim.x * blockDim.x) >> 5;
   const int n_groups = (rows + 31) / 32;
@@ -144,7 +146,7 @@ extern "C" int asvrl_qhuber_fwd_bwd(const float* z, const float* tau, const floa
 
 extern "C" int asvrl_iqn_tau_cos(const float* tau_in, uint64_t seed, uint64_t counter, float cvar,
                                  int batch, int n_tau, int n_cos, float* tau_out, float* cos_out,
-                                 void* stream) {
+                                 const uint64_t* counter_dev, void* stream) {
   if (!cos_out) return fail(ASVRL_E_BADARG, "asvrl_iqn_tau_cos: null cos_out");
   if (batch < 1 || n_tau < 1 || n_cos < 1) return fail(ASVRL_E_BADARG, "asvrl_iqn_tau_cos: bad sizes");
   const int rows = batch * n_tau;
@@ -152,6 +154,6 @@ extern "C" int asvrl_iqn_tau_cos(const float* tau_in, uint64_t seed, uint64_t co
   int grid = (groups + 7) / 8;  // 8 warps per CTA
   if (grid > 148 * 8) grid = 148 * 8;
   tau_cos_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(tau_in, seed, counter, cvar, rows, n_cos,
-                                                         tau_out, cos_out);
+                                                         tau_out, cos_out, counter_dev);
   return check_launch("asvrl_iqn_tau_cos");
 }

@@ -145,12 +145,14 @@ replay_sample_kernel(const float* __restrict__ rows, const unsigned long long* _
                      uint64_t counter, int batch, float* __restrict__ self_b, float* __restrict__ obj_b,
                      float* __restrict__ mask_b, float* __restrict__ act_b, float* __restrict__ rew_b,
                      float* __restrict__ nself_b, float* __restrict__ nobj_b, float* __restrict__ nmask_b,
-                     float* __restrict__ done_b, int64_t* __restrict__ indices_out) {
+                     float* __restrict__ done_b, int64_t* __restrict__ indices_out,
+                     const uint64_t* __restrict__ counter_dev) {
   const int lane = threadIdx.x & 31;
   const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (b >= batch) return;
   const uint64_t size = head_size[1];
   if (size == 0) return;
+  if (counter_dev) counter += *counter_dev;
   uint64_t idx;
   if (indices) {
     idx = (uint64_t)indices[b] % size;
@@ -216,7 +218,7 @@ extern "C" int asvrl_replay_sample(const float* rows, const unsigned long long* 
                                    uint64_t counter, int batch, float* self_b, float* obj_b,
                                    float* mask_b, float* act_b, float* rew_b, float* nself_b,
                                    float* nobj_b, float* nmask_b, float* done_b,
-                                   int64_t* indices_out, void* stream) {
+                                   int64_t* indices_out, const uint64_t* counter_dev, void* stream) {
   if (!rows || !head_size || !self_b || !obj_b || !mask_b || !act_b || !rew_b || !nself_b ||
       !nobj_b || !nmask_b || !done_b)
     return fail(ASVRL_E_BADARG, "asvrl_replay_sample: null pointer");
@@ -224,6 +226,6 @@ extern "C" int asvrl_replay_sample(const float* rows, const unsigned long long* 
   const int grid = (batch * 32 + 255) / 256;
   replay_sample_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
       rows, head_size, capacity, indices, seed, counter, batch, self_b, obj_b, mask_b, act_b, rew_b,
-      nself_b, nobj_b, nmask_b, done_b, indices_out);
+      nself_b, nobj_b, nmask_b, done_b, indices_out, counter_dev);
   return check_launch("asvrl_replay_sample");
 }

@@ -1,0 +1,210 @@
+"""AC-IQN actor / critic with the reference's module names, state-dict keys, constructor JSON
+and file names (rfarl/rfarl/policy/AC_IQN_model.py:16-515), so checkpoints written by either
+side load in the other and `save_model_to_torch_script.py` keeps working.
+
+The dense layers stay in PyTorch (the only contractions on the path); the critic's quantile
+embedding input — tau sampling and cos(pi*i*tau) — is kernel K3 (`asvrl_iqn_tau_cos`).
+Layers are created in the reference's order after `torch.manual_seed(seed)`, so a given seed
+yields the reference's initial weights.
+"""
+import copy
+import json
+import os
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .iqn_ops import TauSampler
+
+
+def encoder(input_dimension, output_dimension):
+    """Linear + ReLU as a 2-element Sequential: state-dict keys `<name>.0.weight/bias`."""
+    return nn.Sequential(nn.Linear(input_dimension, output_dimension), nn.ReLU())
+
+
+class _ObservationTower(nn.Module):
+    """Shared front end: self 7->56, each of 5 objects 5->40 (masked), concat -> 256
+    (ACIQN:284-308 / 428-451)."""
+
+    def _init_dims(self, self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                   object_feature_dimension, concat_feature_dimension, hidden_dimension, device, seed):
+        self.self_dimension = self_dimension
+        self.object_dimension = object_dimension
+        self.max_object_num = max_object_num
+        self.self_feature_dimension = self_feature_dimension
+        self.object_feature_dimension = object_feature_dimension
+        self.concat_feature_dimension = concat_feature_dimension
+        self.hidden_dimension = hidden_dimension
+        self.device = device
+        self.seed_id = seed
+        self.seed = torch.manual_seed(seed)
+
+    def _features(self, x):
+        assert len(x) == 3, "The number of elements in state must be 3!"
+        self_obs, objects, mask = x
+        B = self_obs.shape[0]
+        own = self.self_encoder(self_obs)
+        width = self.max_object_num * self.object_feature_dimension
+        if objects is None:  # empty batch special case, RB:60-63
+            others = own.new_zeros((B, width))
+        else:
+            enc = self.object_encoder(objects.reshape(B * self.max_object_num, self.object_dimension))
+            enc = enc.reshape(B, self.max_object_num, self.object_feature_dimension)
+            others = (enc * (mask >= 0.5).unsqueeze(-1).to(enc.dtype)).reshape(B, width)
+        return torch.cat((own, others), dim=1)
+
+    def _dump(self, directory, stem):
+        torch.save(self.state_dict(), os.path.join(directory, f"{stem}_network_params.pth"))
+        with open(os.path.join(directory, f"{stem}_constructor_params.json"), mode="w") as f:
+            json.dump(self.get_constructor_parameters(), f)
+
+    @classmethod
+    def _restore(cls, directory, stem, device):
+        weights = torch.load(os.path.join(directory, f"{stem}_network_params.pth"), map_location=device)
+        with open(os.path.join(directory, f"{stem}_constructor_params.json"), mode="r") as f:
+            kwargs = json.load(f)
+        kwargs["device"] = device
+        model = cls(**kwargs)
+        model.load_state_dict(weights)
+        model.to(device)
+        return model
+
+
+class Actor(_ObservationTower):
+    """Deterministic policy: features -> 128 -> 128 -> 2, squashed by (2/pi) atan (ACIQN:243-323)."""
+
+    def __init__(self, self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                 object_feature_dimension, concat_feature_dimension, hidden_dimension,
+                 value_ranges_of_action, device='cpu', seed=0):
+        super().__init__()
+        self._init_dims(self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                        object_feature_dimension, concat_feature_dimension, hidden_dimension, device, seed)
+        self.value_ranges_of_action = copy.deepcopy(value_ranges_of_action)
+        self.action_dimension = len(self.value_ranges_of_action)
+        self.atan_scale = 2.0 / np.pi
+        self.self_encoder = encoder(self_dimension, self_feature_dimension)
+        self.object_encoder = encoder(object_dimension, object_feature_dimension)
+        self.hidden_layer = nn.Linear(concat_feature_dimension, hidden_dimension)
+        self.hidden_layer_2 = nn.Linear(hidden_dimension, hidden_dimension)
+        self.output_layer = nn.Linear(hidden_dimension, self.action_dimension)
+
+    def observation_processor(self, x):
+        return self._features(x)
+
+    def forward(self, x):
+        h = F.relu(self.hidden_layer(self._features(x)))
+        h = F.relu(self.hidden_layer_2(h))
+        return self.atan_scale * torch.atan(self.output_layer(h))  # into (-1, 1), ACIQN:320-321
+
+    def get_constructor_parameters(self):
+        return dict(self_dimension=self.self_dimension, object_dimension=self.object_dimension,
+                    max_object_num=self.max_object_num,
+                    self_feature_dimension=self.self_feature_dimension,
+                    object_feature_dimension=self.object_feature_dimension,
+                    concat_feature_dimension=self.concat_feature_dimension,
+                    hidden_dimension=self.hidden_dimension,
+                    value_ranges_of_action=self.value_ranges_of_action, seed=self.seed_id)
+
+    def save(self, directory):
+        self._dump(directory, "actor")
+
+    @classmethod
+    def load(cls, directory, device="cpu"):
+        return cls._restore(directory, "actor", device)
+
+
+class Critic(_ObservationTower):
+    """IQN critic Z(s, a, tau) (ACIQN:362-480): cosine embedding 64 -> 256 (ReLU) multiplies the
+    state features, 256 -> 128, multiplied by the action encoding 2 -> 128, 128 -> 128 -> 1."""
+
+    def __init__(self, self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                 object_feature_dimension, concat_feature_dimension, hidden_dimension,
+                 action_dimension, device='cpu', seed=0):
+        super().__init__()
+        self._init_dims(self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                        object_feature_dimension, concat_feature_dimension, hidden_dimension, device, seed)
+        self.action_dimension = action_dimension
+        self.K = 32  # quantiles used when acting, ACIQN:389
+        self.n = 64  # cosine features, ACIQN:390
+        self.self_encoder = encoder(self_dimension, self_feature_dimension)
+        self.object_encoder = encoder(object_dimension, object_feature_dimension)
+        self.pis = torch.FloatTensor([np.pi * i for i in range(self.n)]).view(1, 1, self.n).to(device)
+        self.cos_embedding = nn.Linear(self.n, concat_feature_dimension)
+        self.action_encoder = encoder(action_dimension, hidden_dimension)
+        self.hidden_layer = nn.Linear(concat_feature_dimension, hidden_dimension)
+        self.hidden_layer_2 = nn.Linear(hidden_dimension, hidden_dimension)
+        self.output_layer = nn.Linear(hidden_dimension, 1)
+        self.tau_sampler = TauSampler(seed, self.n)
+
+    def calc_cos(self, batch_size, num_tau=8, cvar=1.0, taus=None):
+        """K3: tau ~ U(0,1)*cvar from the counter RNG (or injected) and cos(tau*pi*i), i < 64."""
+        dev = self.cos_embedding.weight.device
+        cos, taus = self.tau_sampler.draw(batch_size, num_tau, cvar, dev, taus)
+        assert cos.shape == (batch_size, num_tau, self.n), "cos shape is incorrect"
+        return cos, taus
+
+    def observation_processor(self, x, num_tau=8, cvar=1.0, taus=None):
+        feats = self._features(x)
+        B = feats.shape[0]
+        cos, taus = self.calc_cos(B, num_tau, cvar, taus)
+        emb = F.relu(self.cos_embedding(cos.reshape(B * num_tau, self.n)))
+        emb = emb.reshape(B, num_tau, self.concat_feature_dimension)
+        return (feats.unsqueeze(1) * emb).reshape(B * num_tau, self.concat_feature_dimension), taus
+
+    def forward(self, x, actions, num_tau=8, cvar=1.0, taus=None):
+        assert len(x) == 3, "The number of elements in state must be 3!"
+        B = x[0].shape[0]
+        h, taus = self.observation_processor(x, num_tau, cvar, taus)
+        h = F.relu(self.hidden_layer(h)).reshape(B, num_tau, self.hidden_dimension)
+        h = (self.action_encoder(actions).unsqueeze(1) * h).reshape(B * num_tau, self.hidden_dimension)
+        h = F.relu(self.hidden_layer_2(h))
+        return self.output_layer(h).reshape(B, num_tau), taus
+
+    def get_constructor_parameters(self):
+        return dict(self_dimension=self.self_dimension, object_dimension=self.object_dimension,
+                    max_object_num=self.max_object_num,
+                    self_feature_dimension=self.self_feature_dimension,
+                    object_feature_dimension=self.object_feature_dimension,
+                    concat_feature_dimension=self.concat_feature_dimension,
+                    hidden_dimension=self.hidden_dimension,
+                    action_dimension=self.action_dimension, seed=self.seed_id)
+
+    def save(self, directory):
+        self._dump(directory, "critic")
+
+    @classmethod
+    def load(cls, directory, device="cpu"):
+        return cls._restore(directory, "critic", device)
+
+
+class AC_IQN_Policy():
+    """Actor + critic pair (ACIQN:16-78); the critic is seeded with seed + 1."""
+
+    def __init__(self, self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                 object_feature_dimension, concat_feature_dimension, hidden_dimension,
+                 value_ranges_of_action, device='cpu', seed=0):
+        self.actor = Actor(self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                           object_feature_dimension, concat_feature_dimension, hidden_dimension,
+                           value_ranges_of_action, device, seed).to(device)
+        self.critic = Critic(self_dimension, object_dimension, max_object_num,
+                             self_feature_dimension, object_feature_dimension,
+                             concat_feature_dimension, hidden_dimension,
+                             len(value_ranges_of_action), device, seed + 1).to(device)
+
+    def save(self, directory):
+        self.actor.save(directory)
+        self.critic.save(directory)
+
+    @classmethod
+    def load(cls, directory, device="cpu"):
+        actor = Actor.load(directory, device)
+        critic = Critic.load(directory, device)
+        a = actor
+        policy = cls(a.self_dimension, a.object_dimension, a.max_object_num,
+                     a.self_feature_dimension, a.object_feature_dimension,
+                     a.concat_feature_dimension, a.hidden_dimension, a.value_ranges_of_action,
+                     device=device)
+        policy.actor, policy.critic = actor, critic
+        return policy

@@ -1,0 +1,74 @@
+"""IQN Q-network over the 25 discrete thrust-change actions, with the reference's names,
+state-dict keys and file names (rfarl/rfarl/policy/IQN_model.py:14-146).  Dense layers in
+PyTorch; tau sampling + cosine table is kernel K3."""
+import json
+import os
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .AC_IQN_model import _ObservationTower, encoder
+from .iqn_ops import TauSampler
+
+
+class IQN_Policy(_ObservationTower):
+    def __init__(self, self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                 object_feature_dimension, concat_feature_dimension, hidden_dimension, action_size,
+                 device='cpu', seed=0):
+        super().__init__()
+        self._init_dims(self_dimension, object_dimension, max_object_num, self_feature_dimension,
+                        object_feature_dimension, concat_feature_dimension, hidden_dimension, device, seed)
+        self.action_size = action_size
+        self.self_encoder = encoder(self_dimension, self_feature_dimension)
+        self.object_encoder = encoder(object_dimension, object_feature_dimension)
+        self.K = 32  # IQN:44
+        self.n = 64  # IQN:45
+        self.pis = torch.FloatTensor([np.pi * i for i in range(self.n)]).view(1, 1, self.n).to(device)
+        self.cos_embedding = nn.Linear(self.n, concat_feature_dimension)
+        self.hidden_layer = nn.Linear(concat_feature_dimension, hidden_dimension)
+        self.hidden_layer_2 = nn.Linear(hidden_dimension, hidden_dimension)
+        self.output_layer = nn.Linear(hidden_dimension, action_size)
+        self.tau_sampler = TauSampler(seed, self.n)
+
+    def calc_cos(self, batch_size, num_tau=8, cvar=1.0, taus=None):
+        dev = self.cos_embedding.weight.device
+        cos, taus = self.tau_sampler.draw(batch_size, num_tau, cvar, dev, taus)
+        assert cos.shape == (batch_size, num_tau, self.n), "cos shape is incorrect"
+        return cos, taus
+
+    def forward(self, x, num_tau=8, cvar=1.0, taus=None):
+        feats = self._features(x)
+        B = feats.shape[0]
+        cos, taus = self.calc_cos(B, num_tau, cvar, taus)
+        emb = F.relu(self.cos_embedding(cos.reshape(B * num_tau, self.n)))
+        h = (feats.unsqueeze(1) * emb.reshape(B, num_tau, -1)).reshape(B * num_tau, -1)
+        h = F.relu(self.hidden_layer(h))
+        h = F.relu(self.hidden_layer_2(h))
+        return self.output_layer(h).reshape(B, num_tau, self.action_size), taus
+
+    def get_constructor_parameters(self):
+        return dict(self_dimension=self.self_dimension, object_dimension=self.object_dimension,
+                    max_object_num=self.max_object_num,
+                    self_feature_dimension=self.self_feature_dimension,
+                    object_feature_dimension=self.object_feature_dimension,
+                    concat_feature_dimension=self.concat_feature_dimension,
+                    hidden_dimension=self.hidden_dimension, action_size=self.action_size,
+                    seed=self.seed_id)
+
+    def save(self, directory):
+        torch.save(self.state_dict(), os.path.join(directory, "network_params.pth"))
+        with open(os.path.join(directory, "constructor_params.json"), mode="w") as f:
+            json.dump(self.get_constructor_parameters(), f)
+
+    @classmethod
+    def load(cls, directory, device="cpu"):
+        weights = torch.load(os.path.join(directory, "network_params.pth"), map_location=device)
+        with open(os.path.join(directory, "constructor_params.json"), mode="r") as f:
+            kwargs = json.load(f)
+        kwargs["device"] = device
+        model = cls(**kwargs)
+        model.load_state_dict(weights)
+        model.to(device)
+        return model

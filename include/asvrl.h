@@ -196,12 +196,16 @@ ASVRL_API void asvrl_env_default_params(asvrl_env_params* p);
  *             obstacle i is i, of robot j is OP+j.  NULL = in-kernel Philox stream above.
  *   env_mask  nullable [E] uint8: envs with 0 are skipped entirely (nothing read or written);
  *             used to observe only the freshly reset envs (ENV:164).
- *   env_offset  global index of local env 0 (multi-GPU sharding keeps streams invariant) */
+ *   env_offset  global index of local env 0 (multi-GPU sharding keeps streams invariant)
+ *   counter_dev nullable DEVICE uint64: the RNG step used is `step + *counter_dev`.  Lets a
+ *             captured CUDA graph be replayed with fresh random streams (the host bumps the
+ *             device word inside the graph); the same convention holds for asvrl_env_reset
+ *             (episode), asvrl_replay_sample (counter) and asvrl_iqn_tau_cos (counter). */
 ASVRL_API int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_state* state,
                              const void* actions, const float* noise, const uint8_t* env_mask,
                              uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,
                              int max_robots, int max_obs, int max_cores, int64_t env_offset,
-                             uint32_t mode, void* stream);
+                             uint32_t mode, const uint64_t* counter_dev, void* stream);
 
 /* The noise table the NULL-noise path of K1 draws: float [E][RP][OP+RP][5] (test / debug aid;
  * same device function as K1). */
@@ -237,7 +241,8 @@ ASVRL_API int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env_
                               const int32_t* want_cores, const int32_t* want_obs,
                               const float* min_start_goal_dis /* [E] */, uint64_t seed,
                               uint64_t episode, int n_envs, int max_robots, int max_obs,
-                              int max_cores, int64_t env_offset, void* stream);
+                              int max_cores, int64_t env_offset, const uint64_t* counter_dev,
+                              void* stream);
 
 /* Replay rows are dense float32[ASVRL_ROW] records: RB:22-69 + AGENT:360-368,387-392 */
 #define ASVRL_ROW_SELF 0     /* 7  */
@@ -276,7 +281,8 @@ ASVRL_API int asvrl_replay_sample(const float* rows, const unsigned long long* h
                                   uint64_t counter, int batch, float* self_b, float* obj_b,
                                   float* mask_b, float* act_b, float* rew_b, float* nself_b,
                                   float* nobj_b, float* nmask_b, float* done_b,
-                                  int64_t* indices_out /* nullable */, void* stream);
+                                  int64_t* indices_out /* nullable */,
+                                  const uint64_t* counter_dev /* nullable */, void* stream);
 
 /* K3 — replaces Critic.calc_cos / IQN_Policy.calc_cos (ACIQN:410-426, IQN:56-72):
  * tau = U(0,1) * cvar (Philox stream 3 keyed on seed, counter) unless tau_in is given;
@@ -284,7 +290,8 @@ ASVRL_API int asvrl_replay_sample(const float* rows, const unsigned long long* h
  * cos_out [B][N][n_cos]. */
 ASVRL_API int asvrl_iqn_tau_cos(const float* tau_in /* nullable */, uint64_t seed,
                                 uint64_t counter, float cvar, int batch, int n_tau, int n_cos,
-                                float* tau_out, float* cos_out, void* stream);
+                                float* tau_out, float* cos_out,
+                                const uint64_t* counter_dev /* nullable */, void* stream);
 
 /* K4 — replaces the loss core of Agent.train_AC_IQN / train_IQN (AGENT:401-412, 455-467,
  * 701-707) and its autograd backward:

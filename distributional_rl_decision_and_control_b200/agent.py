@@ -100,8 +100,6 @@ class Agent():
                 s.seed = (s.seed ^ salt ^ (self.rank * 0xD1B54A32D192ED03)) & 0xFFFFFFFFFFFFFFFF
             self.memory = ReplayBuffer(BUFFER_SIZE, BATCH_SIZE, object_dimension, max_object_num,
                                        seed=249 + 7919 * self.rank, device=self.device)
-            self._explore_gen = torch.Generator(device=self.device)
-            self._explore_gen.manual_seed(seed + 104729 * (self.rank + 1))
 
     # ------------------------------------------------------------------ acting
     def state_to_tensor(self, states):
@@ -145,19 +143,23 @@ class Agent():
     def act_batch(self, obs, eps=0.0, cvar=1.0):
         """Vectorised epsilon-greedy for M ASVs at once: ``obs`` = (self (M,7), objects (M,5,5),
         mask (M,5)) CUDA tensors.  Returns float32 (M,2) actions (AC-IQN) or int32 (M,) action ids
-        (IQN), still on the device."""
+        (IQN), still on the device.  ``eps`` may be a 0-d CUDA tensor (so a captured CUDA graph
+        follows the exploration schedule); exploration noise comes from torch's default CUDA
+        generator, which is graph-safe."""
         M = obs[0].shape[0]
-        explore = torch.rand((M,), device=self.device, generator=self._explore_gen) < eps
+        explore = torch.rand((M,), device=self.device) < eps
         if self.agent_type == "AC-IQN":
             greedy = self.policy_local.actor(obs)
-            lo = torch.tensor([r[0] for r in self.value_ranges_of_action], device=self.device)
-            hi = torch.tensor([r[1] for r in self.value_ranges_of_action], device=self.device)
-            rnd = lo + (hi - lo) * torch.rand((M, len(lo)), device=self.device, generator=self._explore_gen)
+            if not hasattr(self, "_act_lo"):
+                self._act_lo = torch.tensor([r[0] for r in self.value_ranges_of_action], device=self.device)
+                self._act_hi = torch.tensor([r[1] for r in self.value_ranges_of_action], device=self.device)
+            lo, hi = self._act_lo, self._act_hi
+            rnd = lo + (hi - lo) * torch.rand((M, lo.numel()), device=self.device)
             return torch.where(explore.unsqueeze(-1), rnd, greedy).contiguous()
         net = self.policy_local
         quantiles, _ = net(obs, net.K, cvar)
         greedy = quantiles.mean(dim=1).argmax(dim=1)
-        rnd = torch.randint(0, self.action_size, (M,), device=self.device, generator=self._explore_gen)
+        rnd = torch.randint(0, self.action_size, (M,), device=self.device)
         return torch.where(explore, rnd, greedy).to(torch.int32).contiguous()
 
     # ------------------------------------------------------------------ learning
@@ -198,17 +200,19 @@ class Agent():
 
     def train_AC_IQN(self, batch=None, taus=None):
         """AGENT:386-432 on device tensors.  Returns (critic_loss, actor_loss) as 0-d CUDA tensors.
-        ``batch`` / ``taus`` inject the sample and the local critic's tau (parity tests)."""
+        ``batch`` injects the sample; ``taus`` = {"target", "local", "actor"} -> (B, N) tensors injects
+        the three tau draws in the reference's order (AGENT:399, 403, 422) for the parity tests."""
         states, actions, rewards, next_states, dones = self._batch(batch)
         N = self.num_tau
+        taus = taus or {}
         local, target = self.policy_local, self.policy_target
 
         # critic step ------------------------------------------------------------------
         self.critic_optimizer.zero_grad(set_to_none=True)
         with torch.no_grad():
             next_actions = target.actor(next_states)                     # AGENT:396
-            z_next, _ = target.critic(next_states, next_actions, N)      # AGENT:399 (tau' unused)
-        z, tau = local.critic(states, actions, N, taus=taus)             # AGENT:403
+            z_next, _ = target.critic(next_states, next_actions, N, taus=taus.get("target"))  # AGENT:399
+        z, tau = local.critic(states, actions, N, taus=taus.get("local"))  # AGENT:403
         critic_loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones,
                                              self.GAMMA, 1.0)            # K4 = AGENT:401-412
         critic_loss.backward()
@@ -219,7 +223,7 @@ class Agent():
 
         # actor step -------------------------------------------------------------------
         self.actor_optimizer.zero_grad(set_to_none=True)
-        q, _ = local.critic(states, local.actor(states), N)              # AGENT:420-422
+        q, _ = local.critic(states, local.actor(states), N, taus=taus.get("actor"))  # AGENT:420-422
         actor_loss = -q.mean()
         actor_loss.backward()
         actor_params = list(local.actor.parameters())
@@ -233,11 +237,12 @@ class Agent():
         states, actions, rewards, next_states, dones = self._batch(batch)
         N = self.num_tau
         B = rewards.shape[0]
+        taus = taus or {}
         self.optimizer.zero_grad(set_to_none=True)
         with torch.no_grad():
-            zn_all, _ = self.policy_target(next_states, N)               # (B, N, A)
+            zn_all, _ = self.policy_target(next_states, N, taus=taus.get("target"))  # (B, N, A)
             z_next = zn_all.max(dim=2)[0]                                # AGENT:451-452
-        z_all, tau = self.policy_local(states, N, taus=taus)
+        z_all, tau = self.policy_local(states, N, taus=taus.get("local"))
         a = actions[:, 0].long().view(B, 1, 1).expand(B, N, 1)           # AGENT:457-458
         z = z_all.gather(2, a).squeeze(-1)
         loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones, self.GAMMA, 1.0)
@@ -257,6 +262,8 @@ class Agent():
             raise RuntimeError("fill the replay buffer with at least one batch before capturing")
         step = self.train_AC_IQN if self.agent_type == "AC-IQN" else self.train_IQN
         dev = self.device
+        import gc
+        gc.collect()  # no finaliser of an unrelated CUDA tensor may run in the middle of the capture
         with torch.cuda.device(dev):
             self._ctr = torch.zeros((1,), dtype=torch.int64, device=dev)
             self.memory.counter_dev = self._ctr

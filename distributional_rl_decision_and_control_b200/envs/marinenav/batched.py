@@ -51,6 +51,9 @@ class BatchedMarineNavEnv:
             self.min_start_goal_dis = torch.full((self.E,), float(min_start_goal_dis),
                                                  dtype=torch.float32, device=self.device)
         self.launches = 0
+        # optional int64 device word added to both RNG counters on the device: a captured CUDA
+        # graph of step()/finish_episodes() bumps it and so draws fresh streams on every replay
+        self.counter_dev = None
 
     # ------------------------------------------------------------------ schedule (ENV:75-87)
     def set_schedule(self, num_robots=None, num_obs=None, num_cores=None, min_start_goal_dis=None):
@@ -82,11 +85,12 @@ class BatchedMarineNavEnv:
             self.episode_counter += 1
             _lib.env_reset(self.reset_params, self.state, mask, self.want_robots, self.want_cores,
                            self.want_obs, self.min_start_goal_dis, self.seed, self.episode_counter,
-                           self.OP, self.CP, self.env_offset, st_ptrs=self._st_ptrs)
+                           self.OP, self.CP, self.env_offset, st_ptrs=self._st_ptrs,
+                           counter_dev=self.counter_dev)
             _lib.env_step(self.params, self.state, None, None, self._outs[out_idx], 0, self.OP,
                           self.CP, seed=self.seed ^ 0x5DEECE66D, step=self.episode_counter,
                           env_offset=self.env_offset, env_mask=mask, st_ptrs=self._st_ptrs,
-                          o_ptrs=self._o_ptrs[out_idx])
+                          o_ptrs=self._o_ptrs[out_idx], counter_dev=self.counter_dev)
             self.launches += 2
 
     def reset(self):
@@ -118,7 +122,7 @@ class BatchedMarineNavEnv:
             self.total_steps += 1
             _lib.env_step(self.params, self.state, actions, None, self._outs[nxt], mode, self.OP,
                           self.CP, seed=self.seed, step=self.total_steps, env_offset=self.env_offset,
-                          st_ptrs=self._st_ptrs, o_ptrs=self._o_ptrs[nxt])
+                          st_ptrs=self._st_ptrs, o_ptrs=self._o_ptrs[nxt], counter_dev=self.counter_dev)
             self.launches += 1
         self._cur = nxt
         return self._outs[nxt]

@@ -347,6 +347,71 @@ def replay_case(name, seed):
     print("wrote", name, np.array(st[1]).shape)
 
 
+def agent_case(name, seed):
+    """The reference Agent('AC-IQN') (AGENT:19-205, 386-432): initial weights for the seed, actor and
+    critic forwards, and ONE train_AC_IQN step on an injected batch with injected taus (memory.sample
+    and the three calc_cos draws are patched; everything else is the reference's own code)."""
+    rh.import_reference()
+    import torch
+    from rfarl.agent import Agent
+    torch.set_num_threads(1)
+    rng = np.random.RandomState(seed)
+    B, N = 64, 8
+    n_obj, n_obj2 = rng.randint(0, 6, B), rng.randint(0, 6, B)
+    t = np.arange(5)[None, :]
+    mask, nmask = (t < n_obj[:, None]).astype(np.float32), (t < n_obj2[:, None]).astype(np.float32)
+    scale_s = np.array([20, 20, 2, 2, 0.5, 500, 500], np.float32)
+    scale_o = np.array([15, 15, 1, 1, 1], np.float32)
+    batch = {"self": (rng.randn(B, 7) * scale_s).astype(np.float32),
+             "obj": ((rng.randn(B, 5, 5) * scale_o) * mask[:, :, None]).astype(np.float32), "mask": mask,
+             "nself": (rng.randn(B, 7) * scale_s).astype(np.float32),
+             "nobj": ((rng.randn(B, 5, 5) * scale_o) * nmask[:, :, None]).astype(np.float32), "nmask": nmask,
+             "act": (rng.rand(B, 2) * 2 - 1).astype(np.float32), "rew": rng.randn(B).astype(np.float32),
+             "done": (rng.rand(B) < 0.1).astype(np.float32)}
+    taus = {k: rng.rand(B, N).astype(np.float32) for k in ("target", "local", "actor")}
+    agent = Agent(device="cpu", seed=seed, agent_type="AC-IQN")
+    init = {"init_actor." + k: v.clone().numpy() for k, v in agent.policy_local.actor.state_dict().items()}
+    init.update({"init_critic." + k: v.clone().numpy() for k, v in agent.policy_local.critic.state_dict().items()})
+    tt = lambda a: torch.from_numpy(a)
+    states = (tt(batch["self"]), tt(batch["obj"]), tt(batch["mask"]))
+    with torch.no_grad():
+        actor_out = agent.policy_local.actor(states).numpy()
+
+    queue = []
+
+    def patched_calc_cos(self, batch_size, num_tau=8, cvar=1.0):
+        tau = tt(queue.pop(0)).unsqueeze(-1)
+        return torch.cos(tau * self.pis), tau
+
+    from rfarl.policy.AC_IQN_model import Critic
+    orig = Critic.calc_cos
+    Critic.calc_cos = patched_calc_cos
+    try:
+        queue.append(taus["local"])
+        with torch.no_grad():
+            critic_out = agent.policy_local.critic(states, tt(batch["act"]))[0].numpy()
+        as_list = lambda a: a.tolist()
+        agent.memory.sample = lambda: ((as_list(batch["self"]), as_list(batch["obj"]), as_list(batch["mask"])),
+                                       as_list(batch["act"]), as_list(batch["rew"]),
+                                       (as_list(batch["nself"]), as_list(batch["nobj"]), as_list(batch["nmask"])),
+                                       [bool(d) for d in batch["done"]])
+        queue.extend([taus["target"], taus["local"], taus["actor"]])   # draw order in AGENT:399, 403, 422
+        critic_loss, actor_loss = agent.train_AC_IQN()
+        assert not queue
+    finally:
+        Critic.calc_cos = orig
+    post = {"post_actor." + k: v.clone().numpy() for k, v in agent.policy_local.actor.state_dict().items()}
+    post.update({"post_critic." + k: v.clone().numpy() for k, v in agent.policy_local.critic.state_dict().items()})
+    d = {"seed": np.int64(seed), "actor_out": actor_out, "critic_out": critic_out,
+         "critic_loss": np.float64(critic_loss), "actor_loss": np.float64(actor_loss)}
+    d.update({"b_" + k: v for k, v in batch.items()})
+    d.update({"tau_" + k: v for k, v in taus.items()})
+    d.update(init)
+    d.update(post)
+    np.savez_compressed(os.path.join(GOLD, name), **d)
+    print("wrote", name, "critic_loss", float(critic_loss), "actor_loss", float(actor_loss))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     D, X, A = _abi.M_DYNAMICS, _abi.M_DISCRETE, _abi.M_AUTO_DEACTIVATE
@@ -365,6 +430,7 @@ def main():
     reset_checks_case("reset_checks.npz", 19)
     reset_case("env_reset.npz", 20, 48)
     replay_case("replay.npz", 21)
+    agent_case("agent_ac_iqn.npz", 100)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,219 @@
+"""Host layer on the B200: the rfarl-shaped classes over the C-ABI kernels.
+ * critic forward and ONE full Agent.train_AC_IQN step against the reference's own outputs
+   (tests/golden/agent_ac_iqn.npz: injected batch and taus, reference weights for the seed);
+ * MarineNavEnv3.reset()/step() surface against the float64 oracle on the same state and the
+   same Philox noise stream;
+ * Trainer.learn / VectorTrainer.learn end to end, eager and CUDA-graph."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from distributional_rl_decision_and_control_b200 import _abi
+from distributional_rl_decision_and_control_b200.agent import Agent
+from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
+from distributional_rl_decision_and_control_b200.envs.marinenav.env import MarineNavEnv3
+from distributional_rl_decision_and_control_b200.policy.trainer import Trainer
+from distributional_rl_decision_and_control_b200.vector_trainer import VectorTrainer
+import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def fx():
+    z = np.load(os.path.join(gu.GOLD, "agent_ac_iqn.npz"))
+    return {k: z[k] for k in z.files}
+
+
+def dev_batch(d):
+    t = lambda k: torch.from_numpy(d["b_" + k]).to(DEV)
+    return {k: t(k) for k in ("self", "obj", "mask", "act", "rew", "nself", "nobj", "nmask", "done")}
+
+
+def test_critic_forward_matches_reference(fx):
+    agent = Agent(device=DEV, seed=int(fx["seed"]), agent_type="AC-IQN", BUFFER_SIZE=1024)
+    b = dev_batch(fx)
+    with torch.no_grad():
+        z, tau = agent.policy_local.critic((b["self"], b["obj"], b["mask"]), b["act"],
+                                           taus=torch.from_numpy(fx["tau_local"]).to(DEV))
+    assert tau.shape == (64, 8, 1)
+    assert np.allclose(z.cpu().numpy(), fx["critic_out"], rtol=1e-5, atol=1e-5)
+
+
+def test_train_step_matches_reference(fx):
+    """AGENT:386-432 end to end: losses to 1e-5 relative; after one Adam step the weights agree
+    (an Adam step is lr * g / (|g| + 1e-8): only gradients within ~1e-7 of zero may differ)."""
+    agent = Agent(device=DEV, seed=int(fx["seed"]), agent_type="AC-IQN", BUFFER_SIZE=1024)
+    taus = {k: torch.from_numpy(fx["tau_" + k]).to(DEV) for k in ("target", "local", "actor")}
+    critic_loss, actor_loss = agent.train_AC_IQN(batch=dev_batch(fx), taus=taus)
+    assert abs(critic_loss.item() - float(fx["critic_loss"])) <= 1e-5 * abs(float(fx["critic_loss"]))
+    assert abs(actor_loss.item() - float(fx["actor_loss"])) <= 1e-5 * abs(float(fx["actor_loss"]))
+    for name, mod in (("actor", agent.policy_local.actor), ("critic", agent.policy_local.critic)):
+        for k, v in mod.state_dict().items():
+            got, want, init = v.cpu().numpy(), fx[f"post_{name}.{k}"], fx[f"init_{name}.{k}"]
+            assert not np.array_equal(want, init), k          # the step moved the reference too
+            close = np.abs(got - want) <= 2e-6
+            assert close.mean() >= 0.995, (name, k, close.mean())
+            assert np.abs(got - want).max() <= 2.1e-4, (name, k)  # at most one flipped Adam sign
+
+
+def test_agent_train_from_device_replay_and_graph():
+    agent = Agent(device=DEV, seed=1, agent_type="AC-IQN", BUFFER_SIZE=4096)
+    rng = np.random.RandomState(0)
+    for i in range(300):
+        n1, n2 = rng.randint(0, 6), rng.randint(0, 6)
+        s = (rng.randn(7).tolist(), rng.randn(n1, 5).tolist())
+        s2 = (rng.randn(7).tolist(), rng.randn(n2, 5).tolist())
+        agent.memory.add((s, (rng.rand(2) * 2 - 1).tolist(), float(rng.randn()), s2, bool(rng.rand() < 0.1)))
+    assert agent.memory.size() == 300
+    st, ac, rw, ns, dn = agent.memory.sample()
+    assert len(st[0]) == 64 and len(st[1][0]) == 5 and len(ac[0]) == 2 and isinstance(dn[0], bool)
+    c0, a0 = agent.train()
+    assert np.isfinite(c0) and np.isfinite(a0) and c0.shape == ()
+    w0 = agent.policy_local.critic.output_layer.weight.detach().clone()
+    agent.enable_cuda_graph()
+    losses, idx = [], []
+    for _ in range(4):
+        c, a = agent.train()
+        losses.append(float(c))
+        idx.append(agent.memory._batch["indices"].clone())
+    assert len(set(losses)) == 4                       # fresh batch + fresh taus on every replay
+    assert not torch.equal(idx[0], idx[1])
+    assert not torch.equal(w0, agent.policy_local.critic.output_layer.weight)
+    agent.soft_update()
+    for a, b in zip(agent.policy_local.critic.parameters(), agent.policy_target.critic.parameters()):
+        assert torch.equal(a, b)
+
+
+def test_iqn_agent_trains():
+    agent = Agent(device=DEV, seed=2, agent_type="IQN", BUFFER_SIZE=2048)
+    rng = np.random.RandomState(1)
+    for i in range(200):
+        s = (rng.randn(7).tolist(), rng.randn(rng.randint(0, 6), 5).tolist())
+        s2 = (rng.randn(7).tolist(), rng.randn(rng.randint(0, 6), 5).tolist())
+        agent.memory.add((s, int(rng.randint(0, 25)), float(rng.randn()), s2, False))
+    loss = agent.train()
+    assert np.isfinite(loss)
+    a, q, t = agent.act_iqn(([0.0] * 7, []), eps=0.0)
+    assert 0 <= int(a) < 25 and q.shape == (1, 32, 25) and t.shape == (1, 32, 1)
+
+
+# ------------------------------------------------------------------------------------ env façade
+def test_env_facade_surface_and_oracle_parity(oracle, capsys):
+    sched = {"timesteps": [0, 100], "num_robots": [5, 6], "num_cores": [4, 4], "num_obstacles": [6, 6],
+             "min_start_goal_dis": [30.0, 30.0]}
+    env = MarineNavEnv3(seed=11, schedule=sched, device=DEV)
+    obs, collisions, reach_goals = env.reset()
+    assert "training schedule" in capsys.readouterr().out
+    n = len(env.robots)
+    assert n == 5 and len(obs) == n and collisions == [False] * n and reach_goals == [False] * n
+    assert len(obs[0][0]) == 7 and all(len(o) == 5 for o in obs[0][1]) and len(obs[0][1]) <= 5
+    assert len(env.obstacles) <= 6 and len(env.cores) <= 4 and env.get_action_space_dimension() == 25
+    rng = np.random.RandomState(3)
+    for step in range(6):
+        # oracle on the very same device state, same Philox stream the facade will use
+        st_host = gu.to_host(env._st)
+        st_o = {k: (v.astype(np.float64) if v.dtype == np.float32 else v.copy()) for k, v in st_host.items()}
+        for i, rob in enumerate(env.robots):
+            st_o["flags"][0, i] = (1 if rob.collision else 0) | (2 if rob.reach_goal else 0) | (4 if rob.deactivated else 0)
+        st_o["ep_steps"][:] = env.episode_timesteps
+        RP, OP, CP = env._shape
+        acts = [None if rob.deactivated else (rng.rand(2) * 2 - 1).astype(np.float32).tolist() for rob in env.robots]
+        a_arr = np.zeros((1, RP, 2))
+        for i, a in enumerate(acts):
+            if a is not None:
+                a_arr[0, i] = a
+        want = oracle.env_step(env._params(), st_o, a_arr, None, _abi.M_DYNAMICS, OP, CP,
+                               seed=11 ^ 0x5851F42D4C957F2D, step=env._obs_calls + 1)
+        obs, rewards, dones, infos = env.step(acts, is_continuous_action=True)
+        assert len(obs) == len(rewards) == len(dones) == len(infos) == n
+        for i, rob in enumerate(env.robots):
+            code = (int(want["status"][0, i]) >> _abi.S_INFO_SHIFT) & 15
+            assert infos[i]["state"] == _abi.INFO_STRINGS[code]
+            assert dones[i] == bool(want["status"][0, i] & _abi.S_DONE)
+            if rob.deactivated:
+                assert obs[i] == (None, None) and rewards[i] == 0
+                continue
+            assert abs(rewards[i] - want["reward"][0, i]) <= 1e-4 + 1e-5 * abs(want["reward"][0, i])
+            k = int(want["obs_mask"][0, i].sum())
+            assert len(obs[i][1]) == k
+            assert np.allclose(obs[i][0], want["obs_self"][0, i], rtol=1e-5, atol=2e-4)
+            assert np.allclose(np.array(obs[i][1]).reshape(k, 5), want["obs_objects"][0, i, :k], rtol=1e-5, atol=2e-4)
+            assert abs(rob.x - st_o["x"][0, i]) < 1e-4 and abs(rob.theta - st_o["theta"][0, i]) < 1e-5
+            if step == 2 and i == 0:  # the Trainer owns `deactivated` (TRAINER:168-170)
+                rob.collision, rob.deactivated = True, True
+    assert env.episode_timesteps == 6 and env.total_timesteps == 6
+    with pytest.raises(AssertionError, match="Number of actions"):
+        env.step([None], True)
+
+
+def test_episode_data_round_trip_and_eval_histories(tmp_path):
+    env = MarineNavEnv3(seed=253, is_eval_env=True, device=DEV)
+    env.num_robots, env.num_cores, env.num_obs, env.min_start_goal_dis = 4, 3, 5, 30.0
+    env.reset()
+    cfg = json.loads(json.dumps(env.episode_data()))   # must be JSON-serialisable (TRAINER:80-83)
+    assert set(cfg) == {"env", "robots"} and cfg["env"]["num_robots"] == 4
+    assert len(cfg["robots"]["start"]) == len(env.robots) and "perception" in cfg["robots"]
+    env2 = MarineNavEnv3(seed=0, is_eval_env=True, device=DEV)
+    obs, _, _ = env2.reset_with_eval_config(cfg)
+    assert len(obs) == len(env.robots)
+    for a, b in zip(env.robots, env2.robots):
+        assert np.allclose(a.start, b.start) and np.allclose(a.goal, b.goal) and a.init_theta == b.init_theta
+        assert np.allclose(b.velocity - b.velocity_r, env2.get_velocity(b.x, b.y), atol=1e-6)
+    assert [(o.x, o.y, o.r) for o in env.obstacles] == [(o.x, o.y, o.r) for o in env2.obstacles]
+    env2.step([[0.5, 0.5]] * len(env2.robots), True)
+    rob = env2.robots[0]
+    assert len(rob.trajectory) == 2 and len(rob.trajectory[1]) == 13 and rob.action_history == [[0.5, 0.5]]
+    assert len(rob.observation_history) == 2
+    env2.save_episode(str(tmp_path / "ep.json"))
+    assert json.load(open(tmp_path / "ep.json"))["robots"]["trajectory"][0][1][11] == 250.0
+
+
+def test_trainer_learn_end_to_end(tmp_path, capsys):
+    """train_RL_agents.py's run_trial body (TRAIN:74-109) on a short budget."""
+    sched = {"timesteps": [0], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+    ev = {"num_episodes": [1], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+    train_env = MarineNavEnv3(seed=0, schedule=sched, device=DEV)
+    eval_env = MarineNavEnv3(seed=253, is_eval_env=True, device=DEV)
+    agent = Agent(device=DEV, seed=100, agent_type="AC-IQN", BUFFER_SIZE=10000)
+    trainer = Trainer(train_env=train_env, eval_env=eval_env, eval_schedule=ev, rl_agent=agent,
+                      learning_starts=40, imitation=False, il_agent=None)
+    trainer.save_eval_config(str(tmp_path))
+    trainer.learn(total_timesteps=120, eval_freq=80, eval_log_path=str(tmp_path), verbose=False)
+    capsys.readouterr()
+    files = set(os.listdir(tmp_path))
+    assert {"eval_configs.json", "evaluations.npz", "actor_network_params.pth", "critic_network_params.pth"} <= files
+    ev_data = np.load(tmp_path / "evaluations.npz", allow_pickle=True)
+    assert set(ev_data.files) == {"timesteps", "observations", "actions", "trajectories", "rewards",
+                                  "successes", "times", "energies", "relations"}
+    assert list(ev_data["timesteps"]) == [40, 80]
+    assert agent.memory.size() > 64 and trainer.current_timestep == 121
+
+
+@pytest.mark.parametrize("graph", [False, True])
+@pytest.mark.parametrize("kind", ["AC-IQN", "IQN"])
+def test_vector_trainer(kind, graph):
+    env = BatchedMarineNavEnv(128, num_robots=5, num_obs=4, num_cores=2, device=DEV, seed=5,
+                              max_robots=8, max_obs=10, max_cores=8)
+    agent = Agent(device=DEV, seed=7, agent_type=kind, BUFFER_SIZE=50000)
+    sched = {"timesteps": [0, 128 * 20], "num_robots": [5, 8], "num_cores": [2, 4], "num_obstacles": [4, 6],
+             "min_start_goal_dis": [30.0, 30.0]}
+    vt = VectorTrainer(env, agent, update_every=4, learning_starts=8, target_update_interval=3,
+                       schedule=sched, cuda_graph=graph)
+    w0 = [p.detach().clone() for p in (agent.policy_local.critic if kind == "AC-IQN" else agent.policy_local).parameters()]
+    res = vt.learn(60)
+    assert res["steps"] >= 60 and res["updates"] >= 10 and res["env_steps"] == res["steps"] * 128
+    losses = res["last_losses"]
+    assert np.all(np.isfinite(losses))
+    w1 = list((agent.policy_local.critic if kind == "AC-IQN" else agent.policy_local).parameters())
+    assert any(not torch.equal(a, b) for a, b in zip(w0, w1))
+    hs = agent.memory.ring["head_size"].cpu().numpy()
+    assert 0 < hs[1] <= 50000 and hs[0] >= hs[1]
+    rows = agent.memory.ring["rows"][: int(hs[1])]
+    assert torch.isfinite(rows).all()
+    assert int(env.want_robots[0].item()) == 8            # the curriculum advanced (ENV:75-87)
+    assert int(env.state["n_robots"].max().item()) in (5, 8)  # 8 once an episode ended after the switch

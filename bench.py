@@ -105,10 +105,53 @@ def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0):
     return n_envs * n_steps / dt, dt
 
 
+def time_learner(agent, K, W, dev, dist, world):
+    """Learner updates/s: whole Agent update (K2b sample, target + local critic, K3, K4 + backward,
+    clip, Adam, actor step) replayed as one CUDA graph when capture works, else eager."""
+    import torch
+    mode = "graph"
+    try:
+        agent.enable_cuda_graph()
+    except Exception as e:  # e.g. a collective that cannot be captured on this stack
+        agent.disable_cuda_graph()
+        mode = "eager (%s)" % type(e).__name__
+    step = agent.train_graph_replay if agent._graph is not None else (
+        agent.train_AC_IQN if agent.agent_type == "AC-IQN" else agent.train_IQN)
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        out = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    loss = out[0] if isinstance(out, tuple) else out
+    return ms, mode, float(loss)
+
+
+def time_kernel(fn, K, W):
+    import torch
+    for _ in range(W):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / K
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from distributional_rl_decision_and_control_b200 import _lib
+    from distributional_rl_decision_and_control_b200.agent import Agent
     from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -137,31 +180,43 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- (1) eager pass, K1 timed alone (the roofline numerator) ----
     for i in range(W):
         env.step(pool[i % 8])
+    KE = min(K, 400)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(KE)]
+    barrier()
+    for i in range(KE):
+        flush.zero_()
+        ev[i][0].record()
+        env.step_no_reset(pool[i % 8])  # K1
+        ev[i][1].record()
+        env.finish_episodes()           # K1b + masked perception-only K1
+    barrier()
+    k1_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / KE
+
+    # ---- (2) the product path: one CUDA graph per step (K1, K1b, masked K1) ----
+    env.enable_cuda_graph(True)
+    for i in range(W):
+        env.step_graph(pool[i % 8])
     sampler = ClockSampler(local)
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(K)]
     launches0 = env.launches
     barrier()
     sampler.start()
     for i in range(K):
         flush.zero_()  # L2 flush between timed iterations (not timed)
+        env.graph_actions.copy_(pool[i % 8])
         ev[i][0].record()
-        env.step_no_reset(pool[i % 8])  # K1
+        env.step_graph()
         ev[i][1].record()
-        env.finish_episodes()           # K1b + masked perception-only K1
-        ev[i][2].record()
     barrier()
-    step_ms = sum(e[0].elapsed_time(e[2]) for e in ev)
-    k1_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
+    step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
     launches = env.launches - launches0
 
-    # ---- e2e: host buffers in, host buffers out, through the public API ----
-    pin = dict(pin_memory=True)
+    # ---- (3) e2e: host buffers in, host buffers out, through the public API ----
     host_actions = [p.cpu().pin_memory() for p in pool]
-    host_out = {"reward": torch.empty((E, R), **pin), "status": torch.empty((E, R), dtype=torch.int32, **pin),
-                "obs_self": torch.empty((E, R, 7), **pin), "obs_objects": torch.empty((E, R, 5, 5), **pin),
-                "obs_mask": torch.empty((E, R, 5), **pin)}
+    host_out = env.new_host_out()
     for i in range(W):
         env.step_host(host_actions[i % 8], host_out)
     barrier()
@@ -171,6 +226,52 @@ def run_b200(args):
         torch.cuda.synchronize()  # the caller reads host_out now
     e2e_s = time.perf_counter() - t0
     barrier()
+    finite = bool(torch.isfinite(env.out["reward"]).all().item())
+
+    # ---- (4) learner leg (BASELINE config 3 and the reference's own B=64 / N=8) ----
+    pg = dist.group.WORLD if world > 1 else None
+    learner = {}
+    big = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=1024, num_tau=32,
+                BUFFER_SIZE=1 << 20, process_group=pg, rank=rank)
+    env2 = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed + 1, env_offset=rank * E)
+    env2.reset()
+    for i in range(24):  # fill the replay shard from real transitions (K2a)
+        obs = env2.obs
+        out = env2.step_no_reset(pool[i % 8])
+        big.memory.push_step(obs, pool[i % 8], False, out)
+        env2.finish_episodes()
+    small = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=64, num_tau=8,
+                  BUFFER_SIZE=1 << 20, process_group=pg, rank=rank)
+    small.memory.ring = big.memory.ring  # same shard, two batch shapes
+    KL = max(50, min(K, 500))
+    for name, ag in (("c3_B1024_N32", big), ("ref_B64_N8", small)):
+        ms, mode, loss = time_learner(ag, KL, 10, dev, dist, world)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        learner[name] = {"updates_per_sec": KL / (ms * 1e-3), "ms_per_update": ms / KL, "mode": mode,
+                         "batch_per_gpu": ag.BATCH_SIZE, "n_tau": ag.num_tau, "last_critic_loss": loss,
+                         "grad_sync": "nccl all-reduce of the flat bucket, before clipping" if world > 1 else "none"}
+    # K3 / K4 alone at C3 (their own rooflines)
+    B3, N3 = 1024, 32
+    g = torch.Generator(device=dev).manual_seed(5)
+    z, zn = torch.randn((B3, N3), device=dev, generator=g), torch.randn((B3, N3), device=dev, generator=g)
+    tau = torch.rand((B3, N3), device=dev, generator=g)
+    rr, dd = torch.randn((B3,), device=dev, generator=g), torch.zeros((B3,), device=dev)
+    ws = torch.zeros(1, dtype=torch.int32, device=dev)
+    o_l, o_g, o_s = torch.empty(B3, device=dev), torch.empty((B3, N3), device=dev), torch.empty(1, device=dev)
+    k4_ms = time_kernel(lambda: _lib.qhuber_fwd_bwd(z, tau, zn, rr, dd, 0.99, 1.0, ws, o_l, o_g, o_s), 200, 20)
+    t_o, c_o = torch.empty((B3, N3), device=dev), torch.empty((B3, N3, 64), device=dev)
+    k3_ms = time_kernel(lambda: _lib.iqn_tau_cos(B3, N3, 64, dev, seed=1, counter=1, tau_out=t_o, cos_out=c_o), 200, 20)
+    peak, which = measured_peak()
+    k4_bytes = 4 * B3 * (2 * N3 + N3 + 2) + 4 * B3 * (N3 + 1)
+    k3_bytes = 4 * B3 * N3 * (1 + 64)
+    learner["k4_qhuber"] = {"ms": k4_ms, "algorithmic_bytes": k4_bytes, "achieved_gbs": k4_bytes / (k4_ms * 1e-3) / 1e9,
+                            "frac": k4_bytes / (k4_ms * 1e-3) / 1e9 / peak,
+                            "note": "back-to-back launches incl. launch latency; 0.5 MB per launch is latency bound"}
+    learner["k3_tau_cos"] = {"ms": k3_ms, "algorithmic_bytes": k3_bytes, "achieved_gbs": k3_bytes / (k3_ms * 1e-3) / 1e9,
+                             "frac": k3_bytes / (k3_ms * 1e-3) / 1e9 / peak}
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -178,30 +279,29 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     step_ms, k1_ms, e2e_ms = (float(x) for x in times.tolist())
-    finite = bool(torch.isfinite(env.out["reward"]).all().item())
 
     if rank == 0:
-        peak, which = measured_peak()
-        c_in_use = C
-        per_launch = alg_bytes_per_env_step(R, O, c_in_use) * E
-        achieved = per_launch / (k1_ms / K * 1e-3) / 1e9
+        per_launch = alg_bytes_per_env_step(R, O, C) * E
+        achieved = per_launch / (k1_ms * 1e-3) / 1e9
         line = {
             "metric": "env_steps_per_sec", "value": world * E * K / (step_ms * 1e-3), "unit": "env-steps/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"C2 batched env-step: {E} envs x {R} ASVs x {O} buoys x {C} vortex cores per GPU, "
-                                   "continuous actions, in-kernel Philox sensor noise, auto-deactivate + auto-reset",
+                                   "continuous actions, in-kernel Philox sensor noise, auto-deactivate + auto-reset; "
+                                   "one CUDA graph per step (K1, K1b, masked K1)",
                        "envs_per_gpu": E, "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
                        "l2": "flushed between timed steps (256 MiB write)", "parallelism": f"envs sharded x{world}, no collective"},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
-                    "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": E * R * (7 + 25 + 5 + 1 + 1) * 4},
+                    "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": E * R * 39 * 4},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": which,
-                         "kernel": "env_step_kernel<false>", "kernel_ms": k1_ms / K,
+                         "kernel": "env_step_kernel<false>", "kernel_ms": k1_ms,
                          "algorithmic_bytes_per_launch": per_launch,
                          "note": "instruction-issue bound by design (SURVEY.md F5); see profiles/"},
+            "learner": learner,
             "clocks": sampler.summary(), "finite": finite,
         }
         if world == 1 and not args.no_cpu:

@@ -134,17 +134,38 @@ def new_state(E, RP, OP, CP, device):
     return st
 
 
-def new_out(E, RP, device, debug=True):
-    out = {
-        "obs_self": torch.zeros((E, RP, 7), dtype=torch.float32, device=device),
-        "obs_objects": torch.zeros((E, RP, 5, 5), dtype=torch.float32, device=device),
-        "obs_mask": torch.zeros((E, RP, 5), dtype=torch.float32, device=device),
-        "reward": torch.zeros((E, RP), dtype=torch.float32, device=device),
-        "status": torch.zeros((E, RP), dtype=torch.int32, device=device),
+HOST_BLOCK_FIELDS = (("obs_self", 7), ("obs_objects", 25), ("obs_mask", 5), ("reward", 1), ("status", 1))
+
+
+def carve_host_block(flat, E, RP):
+    """Views of one flat float32 buffer [E*RP*39]: what a host-side caller of step() reads
+    (observations, rewards, status) is contiguous, so it crosses PCIe in ONE copy."""
+    views, off, n = {}, 0, E * RP
+    for name, w in HOST_BLOCK_FIELDS:
+        v = flat[off:off + n * w]
+        off += n * w
+        if name == "status":
+            v = v.view(torch.int32)
+        shape = {"obs_self": (E, RP, 7), "obs_objects": (E, RP, 5, 5), "obs_mask": (E, RP, 5)}.get(name, (E, RP))
+        views[name] = v.view(shape)
+    return views
+
+
+def new_out(E, RP, device, debug=True, pin=False):
+    """Step outputs (layout of asvrl_env_out).  ``host_block`` is the flat buffer the
+    observation / reward / status tensors are views of."""
+    width = sum(w for _, w in HOST_BLOCK_FIELDS)
+    kw = dict(pin_memory=True) if pin else dict(device=device)
+    flat = torch.zeros((E * RP * width,), dtype=torch.float32, **kw)
+    out = carve_host_block(flat, E, RP)
+    out["host_block"] = flat
+    if pin:
+        return out
+    out.update({
         "phi": torch.zeros((E, RP), dtype=torch.float32, device=device),
         "env_status": torch.zeros((E,), dtype=torch.int32, device=device),
         "ended": torch.zeros((E,), dtype=torch.uint8, device=device),
-    }
+    })
     if debug:
         out["top_ids"] = torch.full((E, RP, 5), -1, dtype=torch.int32, device=device)
         out["detected"] = torch.zeros((E, RP), dtype=torch.int64, device=device)
@@ -220,7 +241,7 @@ def new_replay(capacity, n_asv_max, device):
     return {
         "rows": torch.zeros((int(capacity), _abi.ROW), dtype=torch.float32, device=device),
         "head_size": torch.zeros((2,), dtype=torch.int64, device=device),
-        "workspace": torch.zeros(((int(n_asv_max) + 255) // 256 + 4,), dtype=torch.int32, device=device),
+        "workspace": torch.zeros(((int(n_asv_max) + 63) // 64 + 4,), dtype=torch.int32, device=device),
         "capacity": int(capacity),
     }
 
@@ -228,7 +249,7 @@ def new_replay(capacity, n_asv_max, device):
 def replay_push(rb, obs_self, obs_objects, obs_mask, actions, discrete, reward, next_self,
                 next_objects, next_mask, status):
     n_asv = status.numel()
-    if (n_asv + 255) // 256 + 4 > rb["workspace"].numel():
+    if (n_asv + 63) // 64 + 4 > rb["workspace"].numel():
         raise RuntimeError("replay workspace too small for this many ASVs")
     a_dtype = torch.int32 if discrete else torch.float32
     rc = lib().asvrl_replay_push(ptr(rb["rows"], torch.float32), rb["capacity"],

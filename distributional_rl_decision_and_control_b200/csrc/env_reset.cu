@@ -6,9 +6,11 @@
 // One warp per environment that needs a reset.  The reference's loop "draw a candidate, keep it
 // if it passes the checks against everything kept so far, give up after 500 draws" is sequential
 // only through the accepted set, so the warp evaluates 32 consecutive candidates of the
-// counter-indexed sequence at once and takes the FIRST passing one (ballot + ffs); candidates
-// after it are re-evaluated against the grown set in the next round.  The result is exactly the
-// sequential algorithm applied to the Philox candidate sequence.
+// counter-indexed sequence at once against the set accepted so far, then resolves the round in
+// candidate order with ballots: the first survivor is accepted, later survivors that conflict with
+// it are struck, and so on — a few shuffles per acceptance instead of a new Philox round.  A
+// candidate is kept iff it passes against everything accepted before it, so the result is exactly
+// the sequential algorithm applied to the Philox candidate sequence.
 // Counter use (stream 2): ego field = class (0 robots, 1 cores, 2 obstacles, 3 theta0),
 // candidate t -> slot = t >> 8, block = t & 255; theta0 of robot r -> slot = r.
 #include <math.h>
@@ -36,6 +38,59 @@ constexpr int RS_MAXR = 32, RS_MAXO = 64, RS_MAXC = 64;
 
 __device__ __forceinline__ float lerp_u(float lo, float hi, float u) { return lo + (hi - lo) * u; }
 
+
+__device__ __forceinline__ float dist2f(float ax, float ay, float bx, float by) {
+  const float dx = ax - bx, dy = ay - by;
+  return sqrtf(dx * dx + dy * dy);
+}
+
+// ENV:368-374: start too close to an accepted start, or goal to an accepted goal
+__device__ __forceinline__ bool sg_conflict(const ResetConsts& k, float4 c, float4 o) {
+  return dist2f(o.x, o.y, c.x, c.y) <= k.clear_r || dist2f(o.z, o.w, c.z, c.w) <= k.clear_r;
+}
+
+// ENV:396-416: core c = (x, y, dir, Gamma) against an accepted core o
+__device__ __forceinline__ bool core_conflict(const ResetConsts& k, float4 c, float4 o) {
+  const float TWO_PI = 6.28318530717959f;
+  const float dis = dist2f(o.x, o.y, c.x, c.y);
+  if (o.z == c.z) {
+    const float bi = o.w / (TWO_PI * k.v_rel_max), bj = c.w / (TWO_PI * k.v_rel_max);
+    return dis < bi + bj;
+  }
+  const float gl = fmaxf(o.w, c.w), gs = fminf(o.w, c.w);
+  const float v1 = gl / (TWO_PI * (dis - 2.0f * k.core_r)), v2 = gs / (TWO_PI * k.core_r);
+  return v1 > k.p * v2;
+}
+
+// ENV:448-454: obstacle c = (x, y, r) overlapping an accepted obstacle o
+__device__ __forceinline__ bool obs_conflict(float4 c, float4 o) {
+  return dist2f(o.x, o.y, c.x, c.y) <= o.z + c.z;
+}
+
+__device__ __forceinline__ float4 shfl4(float4 v, int src) {
+  const unsigned FULL = 0xffffffffu;
+  return make_float4(__shfl_sync(FULL, v.x, src), __shfl_sync(FULL, v.y, src),
+                     __shfl_sync(FULL, v.z, src), __shfl_sync(FULL, v.w, src));
+}
+
+// Resolve one round of 32 candidates in order.  `okm` = lanes that pass against the set accepted
+// before the round; CONFLICT(c, accepted) strikes later candidates.  Returns the new count.
+template <class Conflict>
+__device__ __forceinline__ int resolve_round(unsigned okm, float4 c, float4* set, int n, int want,
+                                             int lane, Conflict conflict) {
+  const unsigned FULL = 0xffffffffu;
+  while (okm && n < want) {
+    const int f = __ffs(okm) - 1;
+    const float4 cf = shfl4(c, f);
+    if (lane == f) set[n] = c;
+    ++n;
+    okm &= ~((2u << f) - 1u);                       // candidates up to f are decided
+    okm &= ~__ballot_sync(FULL, conflict(c, cf));   // later ones must also clear the newcomer
+  }
+  __syncwarp();
+  return n;
+}
+
 __global__ void __launch_bounds__(RS_WARPS * 32)
 env_reset_kernel(const __grid_constant__ ResetConsts k, ResetState st,
                  const uint8_t* __restrict__ reset_mask, const int32_t* __restrict__ want_robots,
@@ -61,98 +116,62 @@ env_reset_kernel(const __grid_constant__ ResetConsts k, ResetState st,
   const int want_r = min(want_robots[e], RP);
   const float min_dis = min_sg[e];
   int n_r = 0;
-  for (int base = 0; base < k.max_tries && n_r < want_r;) {
+  for (int base = 0; base < k.max_tries && n_r < want_r; base += 32) {
     const int t = base + lane;
     uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 0u, (uint32_t)t >> 8, (uint32_t)t & 255u);
     const float lo = k.start_margin;
     float4 c = make_float4(lerp_u(lo, k.map_w - lo, u01(w.x)), lerp_u(lo, k.map_h - lo, u01(w.y)),
                            lerp_u(lo, k.map_w - lo, u01(w.z)), lerp_u(lo, k.map_h - lo, u01(w.w)));
     bool ok = t < k.max_tries;
-    float dx = c.z - c.x, dy = c.w - c.y;
-    ok = ok && !(sqrtf(dx * dx + dy * dy) < min_dis);  // ENV:361
-    for (int i = 0; i < n_r && ok; ++i) {
-      float4 o = sg[i];
-      float sx = o.x - c.x, sy = o.y - c.y, gx = o.z - c.z, gy = o.w - c.w;
-      ok = !(sqrtf(sx * sx + sy * sy) <= k.clear_r) && !(sqrtf(gx * gx + gy * gy) <= k.clear_r);  // ENV:368-374
-    }
-    const unsigned bal = __ballot_sync(FULL, ok);
-    if (bal == 0) { base += 32; continue; }
-    const int first = __ffs(bal) - 1;
-    if (lane == first) sg[n_r] = c;
-    __syncwarp();
-    ++n_r;
-    base += first + 1;
+    ok = ok && !(dist2f(c.z, c.w, c.x, c.y) < min_dis);  // ENV:361
+    for (int i = 0; i < n_r && ok; ++i) ok = !sg_conflict(k, c, sg[i]);
+    n_r = resolve_round(__ballot_sync(FULL, ok), c, sg, n_r, want_r, lane,
+                        [&](float4 a, float4 b) { return sg_conflict(k, a, b); });
   }
 
   // ---- vortex cores: ENV:122-136, check_core ENV:378-418 ----
   const int want_c = min(want_cores[e], CP);
   int n_c = 0;
-  for (int base = 0; base < k.max_tries && n_c < want_c;) {
+  for (int base = 0; base < k.max_tries && n_c < want_c; base += 32) {
     const int t = base + lane;
     uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 1u, (uint32_t)t >> 8, (uint32_t)t & 255u);
     const float cx = k.map_w * u01(w.x), cy = k.map_h * u01(w.y);
     const float dir = (w.z >> 31) ? 1.0f : -1.0f;                    // binomial(1, 0.5), ENV:127
     const float gam = TWO_PI * k.core_r * lerp_u(k.v_min, k.v_max, u01(w.w));  // ENV:128-129
+    const float4 c = make_float4(cx, cy, dir, gam);
     bool ok = t < k.max_tries;
     ok = ok && !(cx - k.core_r < 0.0f || cx + k.core_r > k.map_w);   // ENV:381
     ok = ok && !(cy - k.core_r < 0.0f || cy + k.core_r > k.map_w);   // ENV:383 (sic: width)
     for (int i = 0; i < n_r && ok; ++i) {                            // ENV:386-394
-      float4 o = sg[i];
-      float sx = cx - o.x, sy = cy - o.y, gx = cx - o.z, gy = cy - o.w;
-      ok = !(sqrtf(sx * sx + sy * sy) < k.core_r + k.clear_r) && !(sqrtf(gx * gx + gy * gy) < k.core_r + k.clear_r);
+      const float4 o = sg[i];
+      ok = !(dist2f(cx, cy, o.x, o.y) < k.core_r + k.clear_r) && !(dist2f(cx, cy, o.z, o.w) < k.core_r + k.clear_r);
     }
-    for (int i = 0; i < n_c && ok; ++i) {                            // ENV:396-416
-      float4 o = cores[i];
-      float dx = o.x - cx, dy = o.y - cy, dis = sqrtf(dx * dx + dy * dy);
-      if (o.z == dir) {
-        float bi = o.w / (TWO_PI * k.v_rel_max), bj = gam / (TWO_PI * k.v_rel_max);
-        ok = !(dis < bi + bj);
-      } else {
-        float gl = fmaxf(o.w, gam), gs = fminf(o.w, gam);
-        float v1 = gl / (TWO_PI * (dis - 2.0f * k.core_r)), v2 = gs / (TWO_PI * k.core_r);
-        ok = !(v1 > k.p * v2);
-      }
-    }
-    const unsigned bal = __ballot_sync(FULL, ok);
-    if (bal == 0) { base += 32; continue; }
-    const int first = __ffs(bal) - 1;
-    if (lane == first) cores[n_c] = make_float4(cx, cy, dir, gam);
-    __syncwarp();
-    ++n_c;
-    base += first + 1;
+    for (int i = 0; i < n_c && ok; ++i) ok = !core_conflict(k, c, cores[i]);  // ENV:396-416
+    n_c = resolve_round(__ballot_sync(FULL, ok), c, cores, n_c, want_c, lane,
+                        [&](float4 a, float4 b) { return core_conflict(k, a, b); });
   }
 
   // ---- static obstacles: ENV:150-162, check_obstacle ENV:420-456 ----
   const int want_o = min(want_obs[e], OP);
   int n_o = 0;
-  for (int base = 0; base < k.max_tries && n_o < want_o;) {
+  for (int base = 0; base < k.max_tries && n_o < want_o; base += 32) {
     const int t = base + lane;
     uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 2u, (uint32_t)t >> 8, (uint32_t)t & 255u);
     const float lo = k.obs_margin;
     const float cx = lerp_u(lo, k.map_w - lo, u01(w.x)), cy = lerp_u(lo, k.map_h - lo, u01(w.y));
     const float rr = lerp_u(k.obs_r_min, k.obs_r_max, u01(w.z));
+    const float4 c = make_float4(cx, cy, rr, 0.0f);
     bool ok = t < k.max_tries;
     ok = ok && !(cx - rr < 0.0f || cx + rr > k.map_w) && !(cy - rr < 0.0f || cy + rr > k.map_h);
     for (int i = 0; i < n_r && ok; ++i) {  // ENV:428-436
-      float4 o = sg[i];
-      float sx = cx - o.x, sy = cy - o.y, gx = cx - o.z, gy = cy - o.w;
-      ok = !(sqrtf(sx * sx + sy * sy) < rr + k.clear_r) && !(sqrtf(gx * gx + gy * gy) < rr + k.clear_r);
+      const float4 o = sg[i];
+      ok = !(dist2f(cx, cy, o.x, o.y) < rr + k.clear_r) && !(dist2f(cx, cy, o.z, o.w) < rr + k.clear_r);
     }
-    for (int i = 0; i < n_c && ok; ++i) {  // ENV:439-445
-      float dx = cores[i].x - cx, dy = cores[i].y - cy;
-      ok = !(sqrtf(dx * dx + dy * dy) <= k.core_r + rr);
-    }
-    for (int i = 0; i < n_o && ok; ++i) {  // ENV:448-454
-      float dx = obs[i].x - cx, dy = obs[i].y - cy;
-      ok = !(sqrtf(dx * dx + dy * dy) <= obs[i].z + rr);
-    }
-    const unsigned bal = __ballot_sync(FULL, ok);
-    if (bal == 0) { base += 32; continue; }
-    const int first = __ffs(bal) - 1;
-    if (lane == first) obs[n_o] = make_float4(cx, cy, rr, 0.0f);
-    __syncwarp();
-    ++n_o;
-    base += first + 1;
+    for (int i = 0; i < n_c && ok; ++i)    // ENV:439-445
+      ok = !(dist2f(cores[i].x, cores[i].y, cx, cy) <= k.core_r + rr);
+    for (int i = 0; i < n_o && ok; ++i) ok = !obs_conflict(c, obs[i]);  // ENV:448-454
+    n_o = resolve_round(__ballot_sync(FULL, ok), c, obs, n_o, want_o, lane,
+                        [&](float4 a, float4 b) { return obs_conflict(a, b); });
   }
   __syncwarp();
 

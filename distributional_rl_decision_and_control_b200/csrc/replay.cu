@@ -6,14 +6,16 @@
 //   agent.py:360-368, 387-392      state_to_tensor + the five host->device copies per train()
 //   policy/trainer.py:157-166      which transitions are stored (robots active at step start)
 //
-// Layout: a ring of dense float32[70] rows (280 B) in HBM.  Both kernels move whole rows with
-// one warp per row so every global access is a contiguous, coalesced run; the work is pure
-// HBM traffic (560 B per pushed transition, ~600 B per sampled one).
+// Layout: a ring of dense float32[70] rows (280 B) in HBM.  push flattens (row, element) items
+// over a CTA, sample gives one warp per row; every store is a contiguous, coalesced run and the
+// work is pure HBM traffic (560 B per pushed transition, ~600 B per sampled one).
 #include "common.cuh"
 
 namespace asvrl {
 
-constexpr int PUSH_T = 256;
+constexpr int PUSH_G = 64;    // ASVs per push group (one count slot, one scatter CTA)
+constexpr int SCAT_T = 256;   // threads of a scatter CTA
+constexpr int SCAN_T = 256;   // threads of the last-CTA scan
 
 // valid transition <=> the ASV was on the map when the step started (TRAINER:157-159)
 __device__ __forceinline__ bool row_valid(uint32_t status) {
@@ -21,36 +23,42 @@ __device__ __forceinline__ bool row_valid(uint32_t status) {
          ((status >> ASVRL_S_INFO_SHIFT) & 15u) != (uint32_t)ASVRL_INFO_ABSENT;
 }
 
-// pass 1: per-CTA valid counts; the last CTA to finish turns them into exclusive offsets
-// (deterministic (env, robot) order) and advances the ring counters.
-// workspace: [0] ticket, [1] total, [2..3] base ring position (u64), [4..] per-CTA offsets
-__global__ void __launch_bounds__(PUSH_T)
-replay_count_kernel(const uint32_t* __restrict__ status, int n_asv, int64_t capacity,
+// pass 1: valid count of every 64-ASV group (4 groups per CTA); the last CTA to finish turns them
+// into exclusive offsets (deterministic (env, robot) order) and advances the ring counters.
+// workspace: [0] ticket, [1] total, [2..3] base ring position (u64), [4..] per-group offsets
+__global__ void __launch_bounds__(SCAN_T)
+replay_count_kernel(const uint32_t* __restrict__ status, int n_asv, int n_groups, int64_t capacity,
                     unsigned long long* head_size, uint32_t* ws) {
-  const int i = blockIdx.x * PUSH_T + threadIdx.x;
+  const int i = blockIdx.x * SCAN_T + threadIdx.x;
   const bool v = i < n_asv && row_valid(status[i]);
-  const int cnt = __syncthreads_count(v);
+  const unsigned bal = __ballot_sync(0xffffffffu, v);
+  __shared__ uint32_t wcnt[SCAN_T / 32];
+  if ((threadIdx.x & 31) == 0) wcnt[threadIdx.x >> 5] = __popc(bal);
+  __syncthreads();
   __shared__ bool is_last;
+  if (threadIdx.x < SCAN_T / PUSH_G) {
+    const int gidx = blockIdx.x * (SCAN_T / PUSH_G) + threadIdx.x;
+    if (gidx < n_groups) ws[4 + gidx] = wcnt[2 * threadIdx.x] + wcnt[2 * threadIdx.x + 1];
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
-    ws[4 + blockIdx.x] = (uint32_t)cnt;
     __threadfence();
     is_last = atomicAdd(&ws[0], 1u) == gridDim.x - 1;
   }
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  // exclusive scan of gridDim.x counts by one CTA: chunked serial + shared scan
-  __shared__ uint32_t chunk_sum[PUSH_T];
-  const int nb = gridDim.x;
-  const int per = (nb + PUSH_T - 1) / PUSH_T;
-  const int b0 = threadIdx.x * per, b1 = min(b0 + per, nb);
+  // exclusive scan of n_groups counts by one CTA: chunked serial + shared scan
+  __shared__ uint32_t chunk_sum[SCAN_T];
+  const int per = (n_groups + SCAN_T - 1) / SCAN_T;
+  const int b0 = min(threadIdx.x * per, n_groups), b1 = min(b0 + per, n_groups);
   uint32_t s = 0;
   for (int b = b0; b < b1; ++b) s += __ldcg(&ws[4 + b]);
   chunk_sum[threadIdx.x] = s;
   __syncthreads();
   if (threadIdx.x == 0) {
     uint32_t run = 0;
-    for (int t = 0; t < PUSH_T; ++t) { uint32_t c = chunk_sum[t]; chunk_sum[t] = run; run += c; }
+    for (int t = 0; t < SCAN_T; ++t) { uint32_t c = chunk_sum[t]; chunk_sum[t] = run; run += c; }
     const unsigned long long base = head_size[0];
     ws[1] = run;
     ws[2] = (uint32_t)base; ws[3] = (uint32_t)(base >> 32);
@@ -89,36 +97,40 @@ __device__ __forceinline__ float row_elem(int q, size_t i, const float* obs_self
   return (status[i] & ASVRL_S_DONE) ? 1.0f : 0.0f;
 }
 
-// pass 2: warp-cooperative row writes
-__global__ void __launch_bounds__(PUSH_T)
+// pass 2: a CTA owns one 64-ASV group; the (row, element) items are flattened over its threads, so
+// every load is independent of the others and every store lands in a contiguous 280-byte row
+__global__ void __launch_bounds__(SCAT_T)
 replay_scatter_kernel(float* __restrict__ rows, int64_t capacity, const float* __restrict__ obs_self,
                       const float* __restrict__ obs_obj, const float* __restrict__ obs_mask,
                       const void* __restrict__ actions, int discrete, const float* __restrict__ reward,
                       const float* __restrict__ nself, const float* __restrict__ nobj,
                       const float* __restrict__ nmask, const uint32_t* __restrict__ status, int n_asv,
                       const uint32_t* __restrict__ ws) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int i = blockIdx.x * PUSH_T + threadIdx.x;
-  const bool v = i < n_asv && row_valid(status[i]);
-  const unsigned bal = __ballot_sync(0xffffffffu, v);
-  __shared__ uint32_t warp_cnt[PUSH_T / 32];
-  if (lane == 0) warp_cnt[warp] = __popc(bal);
+  __shared__ long long dst_row[PUSH_G];
+  __shared__ uint32_t cnt0;
+  const int i0 = blockIdx.x * PUSH_G;
+  const int tid = threadIdx.x;
+  if (tid < PUSH_G) {
+    const int i = i0 + tid;
+    const bool v = i < n_asv && row_valid(status[i]);
+    const unsigned bal = __ballot_sync(0xffffffffu, v);
+    if (tid == 0) cnt0 = __popc(bal);
+    __syncwarp();
+    // two warps: ranks of the second one start after the first one's count
+    asm volatile("bar.sync 1, 64;");
+    const uint32_t before = __popc(bal & ((1u << (tid & 31)) - 1u)) + (tid >= 32 ? cnt0 : 0u);
+    const unsigned long long base = (unsigned long long)ws[2] | ((unsigned long long)ws[3] << 32);
+    const unsigned long long pos = (base + ws[4 + blockIdx.x] + before) % (unsigned long long)capacity;
+    dst_row[tid] = v ? (long long)pos : -1;
+  }
   __syncthreads();
-  uint32_t before = 0;
-  for (int w = 0; w < warp; ++w) before += warp_cnt[w];
-  const unsigned long long base = (unsigned long long)ws[2] | ((unsigned long long)ws[3] << 32);
-  const unsigned long long first = base + ws[4 + blockIdx.x] + before;
-  unsigned rem = bal;
-  uint32_t rank = 0;
-  while (rem) {
-    const int src_lane = __ffs(rem) - 1;
-    rem &= rem - 1;
-    const size_t src = (size_t)blockIdx.x * PUSH_T + warp * 32 + src_lane;
-    float* dst = rows + (size_t)((first + rank) % (unsigned long long)capacity) * ASVRL_ROW;
-    for (int q = lane; q < ASVRL_ROW; q += 32)
-      dst[q] = row_elem(q, src, obs_self, obs_obj, obs_mask, actions, discrete, reward, nself, nobj,
-                        nmask, status);
-    ++rank;
+#pragma unroll 2
+  for (int e = tid; e < PUSH_G * ASVRL_ROW; e += SCAT_T) {
+    const int r = e / ASVRL_ROW, q = e - r * ASVRL_ROW;
+    const long long d = dst_row[r];
+    if (d >= 0)
+      rows[(size_t)d * ASVRL_ROW + q] = row_elem(q, (size_t)(i0 + r), obs_self, obs_obj, obs_mask, actions,
+                                                 discrete, reward, nself, nobj, nmask, status);
   }
 }
 
@@ -202,12 +214,13 @@ extern "C" int asvrl_replay_push(float* rows, int64_t capacity, unsigned long lo
   if (capacity < 1 || n_asv < 0) return fail(ASVRL_E_BADARG, "asvrl_replay_push: bad sizes");
   if ((int64_t)n_asv > capacity) return fail(ASVRL_E_LIMIT, "asvrl_replay_push: n_asv %d exceeds capacity", n_asv);
   if (n_asv == 0) return 0;
-  const int grid = (n_asv + PUSH_T - 1) / PUSH_T;
+  const int n_groups = (n_asv + PUSH_G - 1) / PUSH_G;
   cudaStream_t s = (cudaStream_t)stream;
-  replay_count_kernel<<<grid, PUSH_T, 0, s>>>(status, n_asv, capacity, head_size, workspace);
+  replay_count_kernel<<<(n_asv + SCAN_T - 1) / SCAN_T, SCAN_T, 0, s>>>(status, n_asv, n_groups, capacity,
+                                                                      head_size, workspace);
   int rc = check_launch("asvrl_replay_push(count)");
   if (rc) return rc;
-  replay_scatter_kernel<<<grid, PUSH_T, 0, s>>>(rows, capacity, obs_self, obs_objects, obs_mask,
+  replay_scatter_kernel<<<n_groups, SCAT_T, 0, s>>>(rows, capacity, obs_self, obs_objects, obs_mask,
                                                 actions, discrete, reward, next_self, next_objects,
                                                 next_mask, status, n_asv, workspace);
   return check_launch("asvrl_replay_push(scatter)");

@@ -132,16 +132,61 @@ class BatchedMarineNavEnv:
         overwrite its observation rows with the fresh episode's first observation."""
         self._reset_and_observe(self._outs[self._cur]["ended"], self._cur)
 
+    # ------------------------------------------------------------------ CUDA graph of one step
+    def enable_cuda_graph(self, is_continuous_action=True):
+        """Capture step() (K1, K1b, masked K1) once per ping-pong phase.  The RNG counters baked
+        into the two graphs differ by one and a device word advances them by two per pair of
+        replays, so every replay draws fresh noise and fresh scenarios."""
+        dev = self.device
+        with torch.cuda.device(dev):
+            self.counter_dev = torch.zeros((1,), dtype=torch.int64, device=dev)
+            shape, dt = ((self.E, self.RP, 2), torch.float32) if is_continuous_action else ((self.E, self.RP), torch.int32)
+            self.graph_actions = torch.zeros(shape, dtype=dt, device=dev)
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    self.step(self.graph_actions, is_continuous_action)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self._graphs = {}
+            for i in range(2):
+                phase = self._cur
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self.step(self.graph_actions, is_continuous_action)  # flips self._cur
+                    if i == 1:
+                        self.counter_dev.add_(2)
+                self._graphs[phase] = g
+        return self._graphs
+
+    def step_graph(self, actions=None):
+        """Replay the captured step for the current phase; ``actions`` (device tensor) is copied
+        into the graph's static action buffer first.  Returns the out dict of this step."""
+        if actions is not None:
+            self.graph_actions.copy_(actions)
+        self._graphs[self._cur].replay()
+        self._cur = 1 - self._cur
+        self.launches += 3
+        return self._outs[self._cur]
+
     # ------------------------------------------------------------------ host-facing convenience
+    def new_host_out(self):
+        """Pinned host mirror of the step outputs a CPU-side caller reads (one flat block)."""
+        return _lib.new_out(self.E, self.RP, None, pin=True)
+
     def step_host(self, actions_pinned, host_out, is_continuous_action=True):
-        """End-to-end call with HOST buffers: pinned actions in, pinned observations / rewards /
-        status out (the call shape a CPU-side caller of the reference's step() would make)."""
+        """End-to-end call with HOST buffers: pinned actions in; observations (post auto-reset),
+        rewards and status out (the call shape a CPU-side caller of the reference's step() makes).
+        One H2D copy, the kernels, one D2H copy of the flat output block; the caller synchronises
+        the stream before reading ``host_out``."""
         if not hasattr(self, "_act_dev"):
             self._act_dev = torch.empty(actions_pinned.shape, dtype=actions_pinned.dtype, device=self.device)
-        self._act_dev.copy_(actions_pinned, non_blocking=True)
-        out = self.step(self._act_dev, is_continuous_action)
-        for k in ("reward", "status"):
-            host_out[k].copy_(out[k], non_blocking=True)
-        for k in ("obs_self", "obs_objects", "obs_mask"):
-            host_out[k].copy_(self.out[k], non_blocking=True)
+        if getattr(self, "_graphs", None):
+            self.graph_actions.copy_(actions_pinned, non_blocking=True)
+            self.step_graph()
+        else:
+            self._act_dev.copy_(actions_pinned, non_blocking=True)
+            self.step(self._act_dev, is_continuous_action)
+        host_out["host_block"].copy_(self.out["host_block"], non_blocking=True)
         return host_out

@@ -260,7 +260,7 @@ ASVRL_API int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env_
  * appends one row per ASV whose status has neither ASVRL_S_WAS_DEACTIVATED nor
  * ASVRL_INFO_ABSENT, in (env, robot) order (deterministic), at the ring position given by the
  * device counters head_size[0] = rows ever written, head_size[1] = rows valid = min(total,
- * capacity).  workspace: uint32[ceil(n_asv/256) + 4], zero-initialised once by the caller and
+ * capacity).  workspace: uint32[ceil(n_asv/64) + 4], zero-initialised once by the caller and
  * left clean by every call. */
 ASVRL_API int asvrl_replay_push(float* rows, int64_t capacity, unsigned long long* head_size,
                                 const float* obs_self, const float* obs_objects,

@@ -54,7 +54,8 @@ constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
 // kernel prologue is a handful of 32-bit adds instead of per-thread 64-bit size arithmetic
 struct SmemLayout {
   uint32_t px, py, key, obst, cores, c, s, vx, vy, vz, Tl, Tr, gx, gy, rew, ox, oy, osp, cand,
-      st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, have, chit, nr, no, nc, ep, ok;
+      st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, plist, dlist, cnt, el_of, r_of, chit,
+      nr, no, nc, ep, ok;
   uint32_t bytes;
   // pair-loop stepping without integer division: TPB = q*S + rem
   int step_a, step_sl, step3_a, step3_sl;
@@ -65,7 +66,9 @@ struct Smem {
   float *c, *s, *vx, *vy, *vz, *Tl, *Tr, *gx, *gy, *rew, *ox, *oy, *osp;
   float *cand, *st_obj, *st_self, *st_mask, *cphi;
   uint32_t *fl0, *fl, *det_lo, *det_hi;
-  uint8_t *have, *chit;
+  uint16_t *plist, *dlist;  // compacted (ego << 6 | slot): pairs worth a noise draw / detected pairs
+  int* cnt;                 // [0] entries of plist, [1] entries of dlist, [2] noise work ticket
+  uint8_t *el_of, *r_of, *chit;
   int *nr, *no, *nc, *ep, *ok;
   float4 *obst, *cores;
 };
@@ -84,7 +87,8 @@ static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb) {
   L.st_obj = take(A * 25, 4); L.st_self = take(A * 7, 4); L.st_mask = take(A * 5, 4);
   L.cphi = take(A * 5, 4);
   L.fl0 = take(A, 4); L.fl = take(A, 4); L.det_lo = take(A, 4); L.det_hi = take(A, 4);
-  L.have = take(A * S, 1); L.chit = take(A * 5, 1);
+  L.plist = take(A * S, 2); L.dlist = take(A * S, 2); L.cnt = take(4, 4);
+  L.el_of = take(A, 1); L.r_of = take(A, 1); L.chit = take(A * 5, 1);
   L.nr = take(EPB, 4); L.no = take(EPB, 4); L.nc = take(EPB, 4); L.ep = take(EPB, 4); L.ok = take(EPB, 4);
   L.bytes = off;
   L.step_a = tpb / (int)S; L.step_sl = tpb % (int)S;
@@ -105,7 +109,10 @@ __device__ __forceinline__ Smem carve(char* base, const SmemLayout& L) {
   m.st_mask = (float*)(base + L.st_mask); m.cphi = (float*)(base + L.cphi);
   m.fl0 = (uint32_t*)(base + L.fl0); m.fl = (uint32_t*)(base + L.fl);
   m.det_lo = (uint32_t*)(base + L.det_lo); m.det_hi = (uint32_t*)(base + L.det_hi);
-  m.have = (uint8_t*)(base + L.have); m.chit = (uint8_t*)(base + L.chit);
+  m.plist = (uint16_t*)(base + L.plist); m.dlist = (uint16_t*)(base + L.dlist);
+  m.cnt = (int*)(base + L.cnt);
+  m.el_of = (uint8_t*)(base + L.el_of); m.r_of = (uint8_t*)(base + L.r_of);
+  m.chit = (uint8_t*)(base + L.chit);
   m.nr = (int*)(base + L.nr); m.no = (int*)(base + L.no); m.nc = (int*)(base + L.nc);
   m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok);
   return m;
@@ -249,9 +256,51 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     if (present) { const float a = st.vel_x[g], b = st.vel_y[g]; sp = sqrtf(a * a + b * b); }
     m.osp[tid] = sp;
     m.fl0[tid] = present ? st.flags[g] : (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
+    m.el_of[tid] = (uint8_t)el;
+    m.r_of[tid] = (uint8_t)r;
+    m.det_lo[tid] = 0; m.det_hi[tid] = 0;
   }
-  for (int p = tid; p < NP; p += TPB) m.have[p] = 0;
+  if (tid < 4) m.cnt[tid] = 0;
   __syncthreads();
+
+  // ---- phase P: compact the (ego, slot) pairs that can possibly end up detected into plist, so
+  // the expensive per-pair work below (Philox, Box-Muller, von Mises, fp64 geometry) runs with
+  // full warps instead of the ~20 % of lanes a flat pair loop keeps busy.  The filter uses the
+  // pre-step poses plus a travel allowance (it must only be a superset; phase B decides).  With
+  // injected noise (tests) the noise is unbounded, so every live pair is kept. ----
+  for (PairIt it(tid, S); it.p - (tid & 31) < NP; it.advance(TPB, L.step_a, L.step_sl, S)) {
+    bool keep = false;
+    const int a = it.a, sl = it.sl;
+    if (it.p < NP && !(m.fl0[a] & ASVRL_F_DEACTIVATED)) {
+      const int el = m.el_of[a], r = m.r_of[a];
+      float qx, qy, rt, travel = 0.5f * m.osp[a] + 1.5f;
+      bool live;
+      if (sl < OP) {
+        live = sl < m.no[el];
+        const float4 ob = m.obst[el * OP + sl];
+        qx = ob.x; qy = ob.y; rt = ob.z;
+      } else {
+        const int j = sl - OP, b = el * RP + j;
+        live = j != r && !(m.fl0[b] & ASVRL_F_DEACTIVATED);
+        qx = m.ox[b]; qy = m.oy[b]; rt = k.robot_r; travel += 0.5f * m.osp[b] + 1.5f;
+      }
+      if (live) {
+        const float dx = qx - m.ox[a], dy = qy - m.oy[a];
+        const float far = k.detect_bound + rt + (dyn ? travel : 0.0f);
+        keep = INJECT || dx * dx + dy * dy <= far * far;
+      }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (bal) {
+      const int lane = tid & 31;
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&m.cnt[0], __popc(bal));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (keep) m.plist[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)((a << 6) | sl);
+    }
+  }
+  __syncthreads();
+  const int n_pairs = m.cnt[0];
 
   if (tid < 32) {
     // ---- phase A (warp 0): dynamics, one lane per ASV ----
@@ -350,120 +399,115 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
         if (dxg * dxg + dyg * dyg <= k.goal_dis_d * k.goal_dis_d) fnew |= ASVRL_F_REACH_GOAL;
       }
       m.fl[tid] = fnew;
-      m.det_lo[tid] = 0; m.det_hi[tid] = 0;
     }
-  } else if (!INJECT) {
-    // ---- phase A' (warps 1..3, concurrently): sensor noise does not depend on the state, so it
-    // is drawn while warp 0 integrates — for the pairs that can plausibly end up in range
-    // (pre-step distance minus a travel allowance).  Pairs missed here are drawn in phase B, so
-    // the filter only moves work, it never changes a result. ----
-    for (PairIt it(tid - 32, S); it.p < NP; it.advance(TPB - 32, L.step3_a, L.step3_sl, S)) {
-      const int p = it.p, a = it.a, sl = it.sl;
-      const int el = a / RP, r = a - el * RP;
-      if (m.fl0[a] & ASVRL_F_DEACTIVATED) continue;
-      float qx, qy, rt, travel = 0.5f * m.osp[a] + 1.5f;
-      if (sl < OP) {
-        if (sl >= m.no[el]) continue;
-        const float4 ob = m.obst[el * OP + sl];
-        qx = ob.x; qy = ob.y; rt = ob.z;
-      } else {
-        const int j = sl - OP, b = el * RP + j;
-        if (j == r || (m.fl0[b] & ASVRL_F_DEACTIVATED)) continue;
-        qx = m.ox[b]; qy = m.oy[b]; rt = k.robot_r; travel += 0.5f * m.osp[b] + 1.5f;
-      }
-      const float dx = qx - m.ox[a], dy = qy - m.oy[a];
-      const float far = k.detect_bound + rt + (dyn ? travel : 0.0f);
-      if (dx * dx + dy * dy > far * far) continue;
-      const NoiseDraw nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
-      float* np = m.cand + p * 5;
+  }
+  if (!INJECT) {
+    // ---- phase A' (warps 1..3 at once, warp 0 when its integration is done): the sensor noise
+    // does not depend on the state, so it is drawn for the compacted pairs while warp 0 walks
+    // the serial integration chain.  Warps take 32 list entries at a time from a ticket. ----
+    const int lane = tid & 31;
+    for (;;) {
+      int first = 0;
+      if (lane == 0) first = atomicAdd(&m.cnt[2], 32);
+      first = __shfl_sync(0xffffffffu, first, 0);
+      if (first >= n_pairs) break;
+      const int i = first + lane;
+      if (i < n_pairs) {
+        const int pr = m.plist[i], a = pr >> 6, sl = pr & 63;
+        const NoiseDraw nd = sensor_noise(k, seed, step, env_offset + e0 + m.el_of[a], (uint32_t)m.r_of[a],
+                                          (uint32_t)sl);
+        float* np = m.cand + (a * S + sl) * 5;
 #pragma unroll
-      for (int q = 0; q < 5; ++q) np[q] = nd.n[q];
-      m.have[p] = 1;
+        for (int q = 0; q < 5; ++q) np[q] = nd.n[q];
+      }
     }
   }
   __syncthreads();
 
-  // ---- phase B: every (ego, candidate slot) pair of the CTA's envs ----
-  for (PairIt it(tid, S); it.p < NP; it.advance(TPB, L.step_a, L.step_sl, S)) {
-    const int p = it.p, a = it.a, sl = it.sl;
-    const int el = a / RP, r = a - el * RP;
-    double key = INFINITY;
-    const uint32_t fe = m.fl0[a];
-    if (!(fe & ASVRL_F_DEACTIVATED)) {
-      const Cand cd = candidate(k, m, el, r, sl, RP, OP);
-      if (cd.live) {
-        const double tx = cd.px - m.px[a], ty = cd.py - m.py[a];  // true offset
-        const double t2 = tx * tx + ty * ty;
-        bool maybe = true;
-        if (!INJECT) {  // the in-kernel generator's noise is bounded: skip hopeless candidates
-          const float far = k.detect_bound + (float)cd.rt;
-          maybe = (float)t2 <= far * far;
+  // ---- phase B: the compacted pairs, one per thread, with the post-step poses: detection and
+  // collision predicates in fp64, body-frame observation and sort key into shared memory;
+  // detected pairs are compacted again (dlist) for the ranking pass ----
+  for (int i0 = tid & ~31; i0 < n_pairs; i0 += TPB) {
+    const int i = i0 + (tid & 31);
+    bool det = false;
+    int pr = 0;
+    if (i < n_pairs) {
+      pr = m.plist[i];
+      const int a = pr >> 6, sl = pr & 63;
+      const int p = a * S + sl;
+      const int el = m.el_of[a], r = m.r_of[a];
+      const uint32_t fe = m.fl0[a];
+      const Cand cd = candidate(k, m, el, r, sl, RP, OP);  // live by construction of plist
+      const double tx = cd.px - m.px[a], ty = cd.py - m.py[a];  // true offset
+      const double t2 = tx * tx + ty * ty;
+      bool maybe = true;
+      if (!INJECT) {  // the in-kernel generator's noise is bounded: skip hopeless candidates
+        const float far = k.detect_bound + (float)cd.rt;
+        maybe = (float)t2 <= far * far;
+      }
+      if (maybe) {
+        const float* np = INJECT ? noise + ((size_t)e0 * RP * S + p) * 5 : m.cand + p * 5;
+        float n[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) n[q] = np[q];
+        const double qx = tx + (double)n[0], qy = ty + (double)n[1];  // WAMV:27-30
+        const double orr = k.r_mean_ratio * cd.rt + k.r_noise_k * (double)n[4] * cd.rt;  // WAMV:37-40
+        const double d2 = qx * qx + qy * qy, lim = k.perc_range + orr;
+        det = d2 <= lim * lim;  // WAMV:296
+        const float c = m.c[a], s = m.s[a];
+        const float fx = (float)qx, fy = (float)qy;
+        const float bx = c * fx + s * fy, by = -s * fx + c * fy;  // WAMV:305-322
+        if (det && k.angle_limited) {  // WAMV:299-301 (vacuous at the default 2 pi)
+          const float ang = atan2f(by, bx);
+          det = !((double)ang < -k.half_angle || (double)ang > k.half_angle);
         }
-        if (maybe) {
-          NoiseDraw nd;
-          if (INJECT) {
-            const float* np = noise + ((size_t)e0 * RP * S + p) * 5;
-#pragma unroll
-            for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
-          } else if (m.have[p]) {
-            const float* np = m.cand + p * 5;
-#pragma unroll
-            for (int q = 0; q < 5; ++q) nd.n[q] = np[q];
-          } else {
-            nd = sensor_noise(k, seed, step, env_offset + e0 + el, (uint32_t)r, (uint32_t)sl);
+        if (det) {
+          atomicOr(sl < 32 ? &m.det_lo[a] : &m.det_hi[a], 1u << (sl & 31));
+          if (!(fe & ASVRL_F_COLLISION)) {  // true geometry, WAMV:281-291, 475-476
+            const double reach = cd.rt + k.robot_r_d;
+            if (t2 <= reach * reach) atomicOr(&m.fl[a], (uint32_t)ASVRL_F_COLLISION);
           }
-          const double qx = tx + (double)nd.n[0], qy = ty + (double)nd.n[1];  // WAMV:27-30
-          const double orr = k.r_mean_ratio * cd.rt + k.r_noise_k * (double)nd.n[4] * cd.rt;  // WAMV:37-40
-          const double d2 = qx * qx + qy * qy, lim = k.perc_range + orr;
-          bool det = d2 <= lim * lim;  // WAMV:296
-          const float c = m.c[a], s = m.s[a];
-          const float fx = (float)qx, fy = (float)qy;
-          const float bx = c * fx + s * fy, by = -s * fx + c * fy;  // WAMV:305-322
-          if (det && k.angle_limited) {  // WAMV:299-301 (vacuous at the default 2 pi)
-            const float ang = atan2f(by, bx);
-            det = !((double)ang < -k.half_angle || (double)ang > k.half_angle);
-          }
-          if (det) {
-            atomicOr(sl < 32 ? &m.det_lo[a] : &m.det_hi[a], 1u << (sl & 31));
-            if (!(fe & ASVRL_F_COLLISION)) {  // true geometry, WAMV:281-291, 475-476
-              const double reach = cd.rt + k.robot_r_d;
-              if (t2 <= reach * reach) atomicOr(&m.fl[a], (uint32_t)ASVRL_F_COLLISION);
-            }
-            const float ovx = cd.vx + nd.n[2], ovy = cd.vy + nd.n[3];  // WAMV:32-35
-            float* o = m.cand + p * 5;
-            o[0] = bx; o[1] = by;
-            o[2] = c * ovx + s * ovy; o[3] = -s * ovx + c * ovy;
-            o[4] = (float)orr;
-            key = sqrt(d2) - orr - k.robot_r_d;  // WAMV:515, 288
-          }
+          const float ovx = cd.vx + n[2], ovy = cd.vy + n[3];  // WAMV:32-35
+          float* o = m.cand + p * 5;
+          o[0] = bx; o[1] = by;
+          o[2] = c * ovx + s * ovy; o[3] = -s * ovx + c * ovy;
+          o[4] = (float)orr;
+          m.key[a * SK + sl] = sqrt(d2) - orr - k.robot_r_d;  // WAMV:515, 288
         }
       }
     }
-    m.key[a * SK + sl] = key;
+    const unsigned bal = __ballot_sync(0xffffffffu, det);
+    if (bal) {
+      const int lane = tid & 31;
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&m.cnt[1], __popc(bal));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (det) m.dlist[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)pr;
+    }
   }
   for (int i = tid; i < A * 25; i += TPB) m.st_obj[i] = 0.0f;
   for (int i = tid; i < A * 5; i += TPB) { m.st_mask[i] = 0.0f; m.chit[i] = 0; }
   __syncthreads();
 
   // ---- phase B2: rank of every detected candidate among its ego's keys (stable: ties keep slot
-  // order, like heapq.nsmallest, WAMV:513-515); the 5 smallest go to the staged observation ----
-  for (PairIt it(tid, S); it.p < NP; it.advance(TPB, L.step_a, L.step_sl, S)) {
-    const int p = it.p, a = it.a, sl = it.sl;
+  // order, like heapq.nsmallest, WAMV:513-515); the 5 smallest go to the staged observation.
+  // Only detected slots have keys, and only their bits are walked. ----
+  const int n_det = m.cnt[1];
+  for (int i = tid; i < n_det; i += TPB) {
+    const int pr = m.dlist[i], a = pr >> 6, sl = pr & 63;
     const double* keys = m.key + a * SK;
     const double kk = keys[sl];
-    if (kk < INFINITY) {
-      int rank = 0;
-      uint32_t lo = m.det_lo[a], hi = m.det_hi[a];  // only detected slots carry finite keys
-      while (lo) { const int q = __ffs(lo) - 1; lo &= lo - 1; const double kq = keys[q]; rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0; }
-      while (hi) { const int q = 32 + __ffs(hi) - 1; hi &= hi - 1; const double kq = keys[q]; rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0; }
-      if (rank < ASVRL_MAX_OBJ) {
-        const float* cd = m.cand + p * 5;
-        float* so = m.st_obj + a * 25 + rank * 5;
+    int rank = 0;
+    uint32_t lo = m.det_lo[a], hi = m.det_hi[a];
+    while (lo) { const int q = __ffs(lo) - 1; lo &= lo - 1; const double kq = keys[q]; rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0; }
+    while (hi) { const int q = 32 + __ffs(hi) - 1; hi &= hi - 1; const double kq = keys[q]; rank += (kq < kk || (kq == kk && q < sl)) ? 1 : 0; }
+    if (rank < ASVRL_MAX_OBJ) {
+      const float* cd = m.cand + (a * S + sl) * 5;
+      float* so = m.st_obj + a * 25 + rank * 5;
 #pragma unroll
-        for (int q = 0; q < 5; ++q) so[q] = cd[q];
-        m.st_mask[a * 5 + rank] = 1.0f;
-        if (out.top_ids) out.top_ids[((size_t)e0 * RP + a) * 5 + rank] = sl;
-      }
+      for (int q = 0; q < 5; ++q) so[q] = cd[q];
+      m.st_mask[a * 5 + rank] = 1.0f;
+      if (out.top_ids) out.top_ids[((size_t)e0 * RP + a) * 5 + rank] = sl;
     }
   }
   __syncthreads();

@@ -5,7 +5,8 @@
 
 A "step" is one pass of the hot path over one batch: every ASV of every env takes one action
 (10 physics sub-steps, current field, perception, COLREGs, reward/done — kernel K1), finished
-episodes are re-generated (K1b) and re-observed (K1, perception only, masked).
+episodes are re-generated (K1b's routine) and re-observed, all in ONE launch
+(asvrl_env_step_autoreset; `--unfused` runs the three-launch sequence instead).
   value  = env-steps/s with actions resident in HBM (device time, CUDA events, L2 flushed
            between steps, max over ranks);
   e2e    = the same through BatchedMarineNavEnv.step_host with HOST buffers: pinned actions
@@ -168,7 +169,8 @@ def run_b200(args):
 
     # envs partition across ranks with no data-path collective: rank r owns global envs
     # [r*E, (r+1)*E); the RNG counters carry the global index (results invariant to N)
-    env = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed, env_offset=rank * E)
+    env = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed, env_offset=rank * E,
+                              fused=not args.unfused)
     env.reset()
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     pool = [torch.rand((E, R, 2), device=dev, generator=gen) * 2 - 1 for _ in range(8)]
@@ -188,17 +190,31 @@ def run_b200(args):
     barrier()
     for i in range(KE):
         flush.zero_()
-        ev[i][0].record()
-        env.step_no_reset(pool[i % 8])  # K1
-        ev[i][1].record()
-        env.finish_episodes()           # K1b + masked perception-only K1
+        if env.fused:
+            ev[i][0].record()
+            env.step_fused(pool[i % 8])     # K1 with the fused auto-reset tail: the whole step
+            ev[i][1].record()
+        else:
+            ev[i][0].record()
+            env.step_no_reset(pool[i % 8])  # K1
+            ev[i][1].record()
+            env.finish_episodes()           # K1b + masked perception-only K1
     barrier()
     k1_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / KE
 
-    # ---- (2) the product path: one CUDA graph per step (K1, K1b, masked K1) ----
-    env.enable_cuda_graph(True)
+    # ---- (2) the product path: one CUDA graph per step (the fused launch, or K1, K1b, masked K1) ----
+    # the fused step is a single launch, issued directly; the three-launch sequence is one graph
+    use_graph = not env.fused
+    if use_graph:
+        env.enable_cuda_graph(True)
+        act_buf = env.graph_actions
+        do_step = env.step_graph
+    else:
+        act_buf = torch.zeros_like(pool[0])
+        do_step = lambda: env.step(act_buf)
     for i in range(W):
-        env.step_graph(pool[i % 8])
+        act_buf.copy_(pool[i % 8])
+        do_step()
     sampler = ClockSampler(local)
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(K)]
     launches0 = env.launches
@@ -206,9 +222,9 @@ def run_b200(args):
     sampler.start()
     for i in range(K):
         flush.zero_()  # L2 flush between timed iterations (not timed)
-        env.graph_actions.copy_(pool[i % 8])
+        act_buf.copy_(pool[i % 8])
         ev[i][0].record()
-        env.step_graph()
+        do_step()
         ev[i][1].record()
     barrier()
     step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
@@ -233,7 +249,7 @@ def run_b200(args):
     learner = {}
     big = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=1024, num_tau=32,
                 BUFFER_SIZE=1 << 20, process_group=pg, rank=rank)
-    env2 = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed + 1, env_offset=rank * E)
+    env2 = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed + 1, env_offset=rank * E, fused=False)
     env2.reset()
     for i in range(24):  # fill the replay shard from real transitions (K2a)
         obs = env2.obs
@@ -290,7 +306,8 @@ def run_b200(args):
             "data": "synthetic",
             "config": {"workload": f"C2 batched env-step: {E} envs x {R} ASVs x {O} buoys x {C} vortex cores per GPU, "
                                    "continuous actions, in-kernel Philox sensor noise, auto-deactivate + auto-reset; "
-                                   "one CUDA graph per step (K1, K1b, masked K1)",
+                                   + ("one fused launch per step (K1 + re-generation + first observation), no graph"
+                                      if env.fused else "one CUDA graph per step (K1, K1b, masked K1)"),
                        "envs_per_gpu": E, "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
                        "l2": "flushed between timed steps (256 MiB write)", "parallelism": f"envs sharded x{world}, no collective"},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
@@ -298,7 +315,8 @@ def run_b200(args):
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": which,
-                         "kernel": "env_step_kernel<false>", "kernel_ms": k1_ms,
+                         "kernel": "env_step_kernel<false,true> (fused auto-reset)" if env.fused
+                                   else "env_step_kernel<false,false>", "kernel_ms": k1_ms,
                          "algorithmic_bytes_per_launch": per_launch,
                          "note": "instruction-issue bound by design (SURVEY.md F5); see profiles/"},
             "learner": learner,
@@ -312,7 +330,13 @@ def run_b200(args):
                                               f"float64 C port of the reference, {dt:.1f} s"}
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # captured graphs hold NCCL work: tearing the communicator down under them can hang, so
+        # every rank meets once more and leaves without the destructor chain
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def run_reference(args):
@@ -349,6 +373,7 @@ def main():
     ap.add_argument("--cpu-envs", type=int, default=2048)
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

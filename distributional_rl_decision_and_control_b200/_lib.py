@@ -25,13 +25,18 @@ _SIGNATURES = {
     "asvrl_env_step": (C.c_int, [C.POINTER(_abi.EnvParams), C.POINTER(_abi.EnvStatePtrs), vp, f32p,
                                  u8p, C.c_uint64, C.c_uint64, C.POINTER(_abi.EnvOutPtrs), C.c_int,
                                  C.c_int, C.c_int, C.c_int, C.c_int64, C.c_uint32, u64p, vp]),
+    "asvrl_env_step_autoreset": (C.c_int, [C.POINTER(_abi.EnvParams), C.POINTER(_abi.EnvStatePtrs), vp,
+                                           C.c_uint64, C.c_uint64, C.POINTER(_abi.EnvOutPtrs),
+                                           C.POINTER(_abi.EnvAutoReset), C.c_int, C.c_int, C.c_int,
+                                           C.c_int, C.c_int64, C.c_uint32, u64p, vp]),
     "asvrl_env_noise": (C.c_int, [C.POINTER(_abi.EnvParams), C.c_uint64, C.c_uint64, C.c_int,
                                   C.c_int, C.c_int, C.c_int64, f32p, vp]),
     "asvrl_env_reset": (C.c_int, [C.c_void_p, C.POINTER(_abi.EnvStatePtrs), u8p, i32p, i32p, i32p,
                                   f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_int64, u64p, vp]),
     "asvrl_replay_push": (C.c_int, [f32p, C.c_int64, u64p, f32p, f32p, f32p, vp, C.c_int, f32p,
-                                    f32p, f32p, f32p, u32p, C.c_int, u32p, vp]),
+                                    f32p, f32p, f32p, u32p, C.c_int, u32p, f32p, f32p, f32p, u8p,
+                                    C.c_int, vp]),
     "asvrl_replay_sample": (C.c_int, [f32p, u64p, C.c_int64, i64p, C.c_uint64, C.c_uint64, C.c_int,
                                       f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, f32p, i64p,
                                       u64p, vp]),
@@ -189,6 +194,33 @@ def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, 
     return out
 
 
+def env_step_autoreset(params, rparams, st, actions, out, mode, max_obs, max_cores, want_robots,
+                       want_cores, want_obs, min_sg, seed=0, step=0, episode=0, observe_seed=0,
+                       term=None, env_offset=0, st_ptrs=None, o_ptrs=None, counter_dev=None):
+    """K1 + K1b + first observation in one launch (asvrl_env_step_autoreset).  ``term`` = dict with
+    obs_self / obs_objects / obs_mask tensors that receive the terminal rows of ended envs."""
+    E, RP = st["x"].shape
+    want = torch.int32 if (mode & _abi.M_DISCRETE) else torch.float32
+    sp = st_ptrs if st_ptrs is not None else state_ptrs(st)
+    op = o_ptrs if o_ptrs is not None else out_ptrs(out)
+    ar = _abi.EnvAutoReset()
+    ar.reset_params = C.pointer(rparams)
+    ar.want_robots = ptr(want_robots, torch.int32)
+    ar.want_cores = ptr(want_cores, torch.int32)
+    ar.want_obs = ptr(want_obs, torch.int32)
+    ar.min_start_goal_dis = ptr(min_sg, torch.float32)
+    ar.episode, ar.observe_seed = episode, observe_seed & 0xFFFFFFFFFFFFFFFF
+    if term is not None:
+        ar.term_self = ptr(term["obs_self"], torch.float32)
+        ar.term_objects = ptr(term["obs_objects"], torch.float32)
+        ar.term_mask = ptr(term["obs_mask"], torch.float32)
+    rc = lib().asvrl_env_step_autoreset(C.byref(params), C.byref(sp), ptr(actions, want), seed, step,
+                                        C.byref(op), C.byref(ar), E, RP, max_obs, max_cores, env_offset,
+                                        mode, ptr(counter_dev, torch.int64), stream_ptr())
+    check(rc, "asvrl_env_step_autoreset")
+    return out
+
+
 def env_noise(params, seed, step, E, RP, OP, device, env_offset=0):
     out = torch.empty((E, RP, OP + RP, 5), dtype=torch.float32, device=device)
     rc = lib().asvrl_env_noise(C.byref(params), seed, step, E, RP, OP, env_offset, ptr(out),
@@ -247,8 +279,13 @@ def new_replay(capacity, n_asv_max, device):
 
 
 def replay_push(rb, obs_self, obs_objects, obs_mask, actions, discrete, reward, next_self,
-                next_objects, next_mask, status):
+                next_objects, next_mask, status, term=None, ended=None):
+    """``term`` / ``ended``: after a fused auto-reset step the next state of ASVs whose env ended
+    is read from term["obs_*"] (out's rows already hold the fresh episode's observation)."""
     n_asv = status.numel()
+    if (term is None) != (ended is None):
+        raise RuntimeError("term and ended go together")
+    rpe = status.shape[-1] if status.dim() >= 2 else 1
     if (n_asv + 63) // 64 + 4 > rb["workspace"].numel():
         raise RuntimeError("replay workspace too small for this many ASVs")
     a_dtype = torch.int32 if discrete else torch.float32
@@ -259,7 +296,10 @@ def replay_push(rb, obs_self, obs_objects, obs_mask, actions, discrete, reward, 
                                  ptr(reward, torch.float32), ptr(next_self, torch.float32),
                                  ptr(next_objects, torch.float32), ptr(next_mask, torch.float32),
                                  ptr(status, torch.int32), n_asv, ptr(rb["workspace"], torch.int32),
-                                 stream_ptr())
+                                 ptr(term["obs_self"], torch.float32) if term else None,
+                                 ptr(term["obs_objects"], torch.float32) if term else None,
+                                 ptr(term["obs_mask"], torch.float32) if term else None,
+                                 ptr(ended, torch.uint8), rpe, stream_ptr())
     check(rc, "asvrl_replay_push")
 
 

@@ -23,8 +23,10 @@
 // The kernel is instruction-issue bound (about 1e4 thread instructions per 280 algorithmic
 // bytes); HBM traffic is one pass over state in, state + observations out.
 #include <math.h>
+#include <string.h>
 
 #include "env_consts.cuh"
+#include "env_reset.cuh"
 
 namespace asvrl {
 
@@ -48,6 +50,16 @@ struct OutPtrs {
   uint8_t* ended;
 };
 
+// extra arguments of the fused step (asvrl_env_step_autoreset): K1, then in the same launch the
+// CTA re-generates its envs whose episode just ended (K1b's warp routine) and re-observes them
+struct FusedArgs {
+  ResetConsts rk;
+  const int32_t *want_robots, *want_cores, *want_obs;
+  const float* min_sg;
+  uint64_t episode, observe_seed;
+  float *term_self, *term_objects, *term_mask;  // terminal observation rows of ended envs (nullable)
+};
+
 constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
 
 // shared-memory layout: byte offsets computed once on the host and passed by value, so the
@@ -55,7 +67,7 @@ constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
 struct SmemLayout {
   uint32_t px, py, key, obst, cores, c, s, vx, vy, vz, Tl, Tr, gx, gy, rew, ox, oy, osp, cand,
       st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, plist, dlist, cnt, el_of, r_of, chit,
-      nr, no, nc, ep, ok;
+      nr, no, nc, ep, ok, ended, rs_sg, rs_core, rs_obs, rs_cand, rs_okm;
   uint32_t bytes;
   // pair-loop stepping without integer division: TPB = q*S + rem
   int step_a, step_sl, step3_a, step3_sl;
@@ -69,11 +81,13 @@ struct Smem {
   uint16_t *plist, *dlist;  // compacted (ego << 6 | slot): pairs worth a noise draw / detected pairs
   int* cnt;                 // [0] entries of plist, [1] entries of dlist, [2] noise work ticket
   uint8_t *el_of, *r_of, *chit;
-  int *nr, *no, *nc, *ep, *ok;
+  int *nr, *no, *nc, *ep, *ok, *ended;
   float4 *obst, *cores;
+  float4 *rs_sg, *rs_core, *rs_obs, *rs_cand;  // fused auto-reset scratch: accepted sets, round candidates
+  unsigned* rs_okm;
 };
 
-static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb) {
+static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fused = false) {
   SmemLayout L;
   const uint32_t A = (uint32_t)EPB * RP, S = OP + RP, SK = S | 1;
   uint32_t off = 0;
@@ -90,6 +104,10 @@ static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb) {
   L.plist = take(A * S, 2); L.dlist = take(A * S, 2); L.cnt = take(4, 4);
   L.el_of = take(A, 1); L.r_of = take(A, 1); L.chit = take(A * 5, 1);
   L.nr = take(EPB, 4); L.no = take(EPB, 4); L.nc = take(EPB, 4); L.ep = take(EPB, 4); L.ok = take(EPB, 4);
+  L.ended = take(EPB, 4);
+  const uint32_t f = fused ? 1u : 0u;
+  L.rs_sg = take(f * RP, 16); L.rs_core = take(f * CP, 16); L.rs_obs = take(f * OP, 16);
+  L.rs_cand = take(f * tpb, 16); L.rs_okm = take(f * 8, 4);
   L.bytes = off;
   L.step_a = tpb / (int)S; L.step_sl = tpb % (int)S;
   L.step3_a = (tpb - 32) / (int)S; L.step3_sl = (tpb - 32) % (int)S;
@@ -114,7 +132,10 @@ __device__ __forceinline__ Smem carve(char* base, const SmemLayout& L) {
   m.el_of = (uint8_t*)(base + L.el_of); m.r_of = (uint8_t*)(base + L.r_of);
   m.chit = (uint8_t*)(base + L.chit);
   m.nr = (int*)(base + L.nr); m.no = (int*)(base + L.no); m.nc = (int*)(base + L.nc);
-  m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok);
+  m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok); m.ended = (int*)(base + L.ended);
+  m.rs_sg = (float4*)(base + L.rs_sg); m.rs_core = (float4*)(base + L.rs_core);
+  m.rs_obs = (float4*)(base + L.rs_obs); m.rs_cand = (float4*)(base + L.rs_cand);
+  m.rs_okm = (unsigned*)(base + L.rs_okm);
   return m;
 }
 
@@ -208,35 +229,43 @@ __device__ __forceinline__ Cand candidate(const EnvConsts& k, const Smem& m, int
   return c;
 }
 
-template <bool INJECT>
+template <bool INJECT, bool FUSED>
 __global__ void __launch_bounds__(TPB, 8)
 env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L,
                 StatePtrs st, const void* __restrict__ actions,
                 const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
                 uint64_t step, OutPtrs out, int E, int RP, int OP, int CP, int64_t env_offset,
-                uint32_t mode, int EPB, const uint64_t* __restrict__ counter_dev) {
+                uint32_t mode, int EPB, const uint64_t* __restrict__ counter_dev,
+                const __grid_constant__ FusedArgs fa) {
   extern __shared__ __align__(16) char smem_raw[];
   const Smem m = carve(smem_raw, L);
   const int tid = threadIdx.x;
   const int A = EPB * RP, S = OP + RP, SK = S | 1, NP = A * S;
   const int e0 = blockIdx.x * EPB;
-  const bool dyn = mode & ASVRL_M_DYNAMICS;
+  bool dyn = mode & ASVRL_M_DYNAMICS;
   if (counter_dev) step += *counter_dev;  // graph-replay friendly RNG counter (include/asvrl.h)
+  // FUSED: pass 0 is the step itself; pass 1 (only in CTAs that own an env whose episode just
+  // ended) re-observes the re-generated envs: no dynamics, its own noise stream, observation
+  // rows only.  `second` is CTA-uniform.
+  bool second = false;
+  for (;;) {
 
   // ---- phase 0: per-env tables and the pre-step poses (for the noise prefetch filter) ----
   if (tid < EPB) {
     const int e = e0 + tid;
-    const bool v = e < E && (!env_mask || env_mask[e]);
+    const bool v = second ? m.ended[tid] != 0 : (e < E && (!env_mask || env_mask[e]));
     m.ok[tid] = v;
     m.nr[tid] = v ? min(st.n_robots[e], RP) : 0;
     m.no[tid] = v ? min(st.n_obs[e], OP) : 0;
     m.nc[tid] = v ? min(st.n_cores[e], CP) : 0;
     m.ep[tid] = v ? st.ep_steps[e] : 0;
   }
-  {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
+  if (!second) {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
     const int e = e0 + tid;
     const bool mine = tid < EPB && e < E && (!env_mask || env_mask[e]);
     if (!__syncthreads_or(mine)) return;
+  } else {
+    __syncthreads();
   }
   for (int i = tid; i < EPB * OP; i += TPB) {
     const int el = i / OP;
@@ -507,7 +536,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
 #pragma unroll
       for (int q = 0; q < 5; ++q) so[q] = cd[q];
       m.st_mask[a * 5 + rank] = 1.0f;
-      if (out.top_ids) out.top_ids[((size_t)e0 * RP + a) * 5 + rank] = sl;
+      if (out.top_ids && !second) out.top_ids[((size_t)e0 * RP + a) * 5 + rank] = sl;
     }
   }
   __syncthreads();
@@ -575,6 +604,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
         if (f & ASVRL_F_COLLISION) status |= ASVRL_S_COLLISION;
         if (f & ASVRL_F_REACH_GOAL) status |= ASVRL_S_REACH_GOAL;
       }
+      if (!second) {  // reward / status describe the transition, not the fresh episode
       out.reward[g] = reward;
       out.status[g] = status;
       out.phi[g] = phi;
@@ -585,6 +615,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       }
       if (out.detected)
         out.detected[g] = (unsigned long long)m.det_lo[a] | ((unsigned long long)m.det_hi[a] << 32);
+      }
     }
   }
   __syncthreads();
@@ -594,7 +625,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     const int n_env = min(EPB, E - e0);
     const size_t a0 = (size_t)e0 * RP;
     const int n_asv = n_env * RP;
-    if (!env_mask) {
+    if (!env_mask && !second) {
       for (int i = tid; i < n_asv * 25; i += TPB) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
       for (int i = tid; i < n_asv * 7; i += TPB) out.obs_self[a0 * 7 + i] = m.st_self[i];
       for (int i = tid; i < n_asv * 5; i += TPB) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
@@ -608,7 +639,8 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
         for (int i = tid; i < RP * 5; i += TPB) out.obs_mask[b0 * 5 + i] = m.st_mask[l0 * 5 + i];
       }
     }
-    if (tid < n_env && m.ok[tid]) {
+    int my_end = 0;
+    if (tid < n_env && m.ok[tid] && !second) {
       const int el = tid, e = e0 + el, nr = m.nr[el];
       bool all_deact = true, any_coll = false, all_goal = true;
       for (int r = 0; r < nr; ++r) {
@@ -622,8 +654,46 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       out.env_status[e] = es;
       if (out.ended) out.ended[e] = (es & 3u) ? 1 : 0;
       if (dyn) st.ep_steps[e] = m.ep[el] + 1;  // ENV:330
+      my_end = (es & 3u) ? 1 : 0;
     }
+    if (!FUSED || second) return;
+    // ---- fused tail: episodes that just ended (TRAINER:172, 240-245) ----
+    if (tid < EPB) m.ended[tid] = my_end;
+    if (!__syncthreads_or(my_end)) return;
+    if (fa.term_self) {  // the terminal observation rows stay available to the replay push
+      for (int el = 0; el < n_env; ++el) {
+        if (!m.ended[el]) continue;
+        const size_t b0 = a0 + (size_t)el * RP;
+        const int l0 = el * RP;
+        for (int i = tid; i < RP * 25; i += TPB) fa.term_objects[b0 * 25 + i] = m.st_obj[l0 * 25 + i];
+        for (int i = tid; i < RP * 7; i += TPB) fa.term_self[b0 * 7 + i] = m.st_self[l0 * 7 + i];
+        for (int i = tid; i < RP * 5; i += TPB) fa.term_mask[b0 * 5 + i] = m.st_mask[l0 * 5 + i];
+      }
+    }
+    {  // K1b's routine, run by the whole CTA for each ended env in turn
+      const ResetState rs = {st.x, st.y, st.theta, st.velr_x, st.velr_y, st.velr_r, st.vel_x, st.vel_y,
+                             st.vel_r, st.thrust_l, st.thrust_r, (float*)st.goal_x, (float*)st.goal_y,
+                             st.flags, (int32_t*)st.n_robots, (int32_t*)st.n_obs, (int32_t*)st.n_cores,
+                             st.ep_steps, (float4*)st.obstacles, (float4*)st.cores};
+      uint64_t episode = fa.episode;
+      if (counter_dev) episode += *counter_dev;
+      static_assert(TPB == 128, "reset_env_cta resolves rounds of 128 candidates");
+      const CtaScratch sc = {m.rs_cand, m.rs_okm};
+      for (int el = 0; el < n_env; ++el) {
+        if (!m.ended[el]) continue;
+        const int e = e0 + el;
+        reset_env_cta(fa.rk, rs, e, env_offset + e, fa.want_robots[e], fa.want_cores[e], fa.want_obs[e],
+                      fa.min_sg[e], seed, episode, RP, OP, CP, m.rs_sg, m.rs_core, m.rs_obs, sc, tid);
+      }
+      second = true;
+      dyn = false;
+      mode = 0;
+      seed = fa.observe_seed;
+      step = episode;
+    }
+    __syncthreads();
   }
+  }  // pass loop
 }
 
 // fills the [E][RP][OP+RP][5] table the NULL-noise path of K1 uses (same device function)
@@ -748,14 +818,72 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
   const size_t smem = L.bytes;
   const int grid = (n_envs + EPB - 1) / EPB;
   cudaStream_t s = (cudaStream_t)stream;
-  auto kern = noise ? env_step_kernel<true> : env_step_kernel<false>;
+  auto kern = noise ? env_step_kernel<true, false> : env_step_kernel<false, false>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
   }
+  FusedArgs fa;
+  memset(&fa, 0, sizeof fa);
   kern<<<grid, TPB, smem, s>>>(k, L, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
-                               max_cores, env_offset, mode, EPB, counter_dev);
+                               max_cores, env_offset, mode, EPB, counter_dev, fa);
   return check_launch("asvrl_env_step");
+}
+
+extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const asvrl_env_state* state,
+                                        const void* actions, uint64_t seed, uint64_t step,
+                                        const asvrl_env_out* out, const asvrl_env_autoreset* ar,
+                                        int n_envs, int max_robots, int max_obs, int max_cores,
+                                        int64_t env_offset, uint32_t mode,
+                                        const uint64_t* counter_dev, void* stream) {
+  if (!params || !state || !out || !ar) return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: null struct");
+  if (!ar->reset_params || !ar->want_robots || !ar->want_cores || !ar->want_obs || !ar->min_start_goal_dis)
+    return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: null auto-reset argument");
+  if ((ar->term_self || ar->term_objects || ar->term_mask) &&
+      !(ar->term_self && ar->term_objects && ar->term_mask))
+    return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: term_* must be all set or all NULL");
+  if (n_envs < 0 || max_robots < 1 || max_obs < 0 || max_cores < 0)
+    return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: bad sizes");
+  if (max_robots > 32 || max_obs + max_robots > ASVRL_MAX_SLOTS || max_robots > RS_MAXR ||
+      max_obs > RS_MAXO || max_cores > RS_MAXC)
+    return fail(ASVRL_E_LIMIT, "asvrl_env_step_autoreset: max_robots <= 32, max_obs + max_robots <= %d, max_cores <= %d",
+                ASVRL_MAX_SLOTS, RS_MAXC);
+  if (!(mode & ASVRL_M_DYNAMICS) || !actions)
+    return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: needs ASVRL_M_DYNAMICS and actions");
+  if (n_envs == 0) return 0;
+  EnvConsts k;
+  int rc = make_env_consts(params, &k);
+  if (rc) return rc;
+  StatePtrs st = {state->x, state->y, state->theta, state->velr_x, state->velr_y, state->velr_r,
+                  state->vel_x, state->vel_y, state->vel_r, state->thrust_l, state->thrust_r,
+                  state->goal_x, state->goal_y, state->flags, state->n_robots, state->n_obs,
+                  state->n_cores, state->ep_steps, (const float4*)state->obstacles,
+                  (const float4*)state->cores};
+  OutPtrs o = {out->obs_self, out->obs_objects, out->obs_mask, out->reward, out->status, out->phi,
+               out->top_ids, (unsigned long long*)out->detected, out->env_status, out->ended};
+  if (!o.obs_self || !o.obs_objects || !o.obs_mask || !o.reward || !o.status || !o.phi || !o.env_status)
+    return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: null output");
+  if ((max_obs > 0 && !st.obstacles) || (max_cores > 0 && !st.cores))
+    return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: null obstacle / core table");
+  FusedArgs fa;
+  fa.rk = make_reset_consts(ar->reset_params);
+  fa.want_robots = ar->want_robots; fa.want_cores = ar->want_cores; fa.want_obs = ar->want_obs;
+  fa.min_sg = ar->min_start_goal_dis;
+  fa.episode = ar->episode; fa.observe_seed = ar->observe_seed;
+  fa.term_self = ar->term_self; fa.term_objects = ar->term_objects; fa.term_mask = ar->term_mask;
+  const int EPB = pick_epb(max_robots);
+  const SmemLayout L = make_layout(EPB, max_robots, max_obs, max_cores, TPB, true);
+  const size_t smem = L.bytes;
+  const int grid = (n_envs + EPB - 1) / EPB;
+  auto kern = env_step_kernel<false, true>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail((int)e, "asvrl_env_step_autoreset: %zu B shared memory: %s", smem, cudaGetErrorString(e));
+  }
+  kern<<<grid, TPB, smem, (cudaStream_t)stream>>>(k, L, st, actions, nullptr, nullptr, seed, step, o, n_envs,
+                                                  max_robots, max_obs, max_cores, env_offset, mode, EPB,
+                                                  counter_dev, fa);
+  return check_launch("asvrl_env_step_autoreset");
 }
 
 extern "C" int asvrl_env_noise(const asvrl_env_params* params, uint64_t seed, uint64_t step,

@@ -105,8 +105,11 @@ replay_scatter_kernel(float* __restrict__ rows, int64_t capacity, const float* _
                       const void* __restrict__ actions, int discrete, const float* __restrict__ reward,
                       const float* __restrict__ nself, const float* __restrict__ nobj,
                       const float* __restrict__ nmask, const uint32_t* __restrict__ status, int n_asv,
-                      const uint32_t* __restrict__ ws) {
+                      const uint32_t* __restrict__ ws, const float* __restrict__ tself,
+                      const float* __restrict__ tobj, const float* __restrict__ tmask,
+                      const uint8_t* __restrict__ ended, int rpe) {
   __shared__ long long dst_row[PUSH_G];
+  __shared__ uint8_t use_term[PUSH_G];
   __shared__ uint32_t cnt0;
   const int i0 = blockIdx.x * PUSH_G;
   const int tid = threadIdx.x;
@@ -122,15 +125,19 @@ replay_scatter_kernel(float* __restrict__ rows, int64_t capacity, const float* _
     const unsigned long long base = (unsigned long long)ws[2] | ((unsigned long long)ws[3] << 32);
     const unsigned long long pos = (base + ws[4 + blockIdx.x] + before) % (unsigned long long)capacity;
     dst_row[tid] = v ? (long long)pos : -1;
+    use_term[tid] = (ended && i < n_asv) ? ended[i / rpe] : 0;
   }
   __syncthreads();
 #pragma unroll 2
   for (int e = tid; e < PUSH_G * ASVRL_ROW; e += SCAT_T) {
     const int r = e / ASVRL_ROW, q = e - r * ASVRL_ROW;
     const long long d = dst_row[r];
-    if (d >= 0)
+    if (d >= 0) {
+      const bool t = use_term[r];  // the env ended: its next state is the kept terminal observation
       rows[(size_t)d * ASVRL_ROW + q] = row_elem(q, (size_t)(i0 + r), obs_self, obs_obj, obs_mask, actions,
-                                                 discrete, reward, nself, nobj, nmask, status);
+                                                 discrete, reward, t ? tself : nself, t ? tobj : nobj,
+                                                 t ? tmask : nmask, status);
+    }
   }
 }
 
@@ -207,12 +214,16 @@ extern "C" int asvrl_replay_push(float* rows, int64_t capacity, unsigned long lo
                                  const float* reward, const float* next_self,
                                  const float* next_objects, const float* next_mask,
                                  const uint32_t* status, int n_asv, uint32_t* workspace,
+                                 const float* term_self, const float* term_objects,
+                                 const float* term_mask, const uint8_t* ended, int robots_per_env,
                                  void* stream) {
   if (!rows || !head_size || !obs_self || !obs_objects || !obs_mask || !actions || !reward ||
       !next_self || !next_objects || !next_mask || !status || !workspace)
     return fail(ASVRL_E_BADARG, "asvrl_replay_push: null pointer");
   if (capacity < 1 || n_asv < 0) return fail(ASVRL_E_BADARG, "asvrl_replay_push: bad sizes");
   if ((int64_t)n_asv > capacity) return fail(ASVRL_E_LIMIT, "asvrl_replay_push: n_asv %d exceeds capacity", n_asv);
+  if (ended && (!term_self || !term_objects || !term_mask || robots_per_env < 1))
+    return fail(ASVRL_E_BADARG, "asvrl_replay_push: ended needs term_* and robots_per_env >= 1");
   if (n_asv == 0) return 0;
   const int n_groups = (n_asv + PUSH_G - 1) / PUSH_G;
   cudaStream_t s = (cudaStream_t)stream;
@@ -222,7 +233,9 @@ extern "C" int asvrl_replay_push(float* rows, int64_t capacity, unsigned long lo
   if (rc) return rc;
   replay_scatter_kernel<<<n_groups, SCAT_T, 0, s>>>(rows, capacity, obs_self, obs_objects, obs_mask,
                                                 actions, discrete, reward, next_self, next_objects,
-                                                next_mask, status, n_asv, workspace);
+                                                next_mask, status, n_asv, workspace, term_self,
+                                                term_objects, term_mask, ended,
+                                                robots_per_env < 1 ? 1 : robots_per_env);
   return check_launch("asvrl_replay_push(scatter)");
 }
 

@@ -23,7 +23,7 @@ class BatchedMarineNavEnv:
 
     def __init__(self, n_envs, num_robots=8, num_obs=10, num_cores=0, min_start_goal_dis=30.0,
                  device="cuda:0", seed=0, env_offset=0, max_robots=None, max_obs=None,
-                 max_cores=None, params=None, reset_params=None, debug_outputs=False):
+                 max_cores=None, params=None, reset_params=None, debug_outputs=False, fused=True):
         _lib.lib()  # fail loudly if the CUDA library is missing
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -50,6 +50,11 @@ class BatchedMarineNavEnv:
             self.want_cores = torch.full((self.E,), int(num_cores), **i32)
             self.min_start_goal_dis = torch.full((self.E,), float(min_start_goal_dis),
                                                  dtype=torch.float32, device=self.device)
+            # terminal observation rows of envs whose episode ended in the last fused step
+            self.term = {"obs_self": torch.zeros((self.E, self.RP, 7), dtype=torch.float32, device=self.device),
+                         "obs_objects": torch.zeros((self.E, self.RP, 5, 5), dtype=torch.float32, device=self.device),
+                         "obs_mask": torch.zeros((self.E, self.RP, 5), dtype=torch.float32, device=self.device)}
+        self.fused = bool(fused)  # step(auto_reset=True) = ONE launch (asvrl_env_step_autoreset)
         self.launches = 0
         # optional int64 device word added to both RNG counters on the device: a captured CUDA
         # graph of step()/finish_episodes() bumps it and so draws fresh streams on every replay
@@ -88,7 +93,7 @@ class BatchedMarineNavEnv:
                            self.OP, self.CP, self.env_offset, st_ptrs=self._st_ptrs,
                            counter_dev=self.counter_dev)
             _lib.env_step(self.params, self.state, None, None, self._outs[out_idx], 0, self.OP,
-                          self.CP, seed=self.seed ^ 0x5DEECE66D, step=self.episode_counter,
+                          self.CP, seed=self.seed ^ self.OBSERVE_SALT, step=self.episode_counter,
                           env_offset=self.env_offset, env_mask=mask, st_ptrs=self._st_ptrs,
                           o_ptrs=self._o_ptrs[out_idx], counter_dev=self.counter_dev)
             self.launches += 2
@@ -108,10 +113,37 @@ class BatchedMarineNavEnv:
         the policy should act on next while the returned dict's reward/status still describe the
         transition (use ``step_no_reset`` + ``finish_episodes`` to store next_obs in between).
         """
+        if auto_reset and self.fused:
+            return self.step_fused(actions, is_continuous_action)
         out = self.step_no_reset(actions, is_continuous_action)
         if auto_reset:
             self.finish_episodes()
         return out
+
+    OBSERVE_SALT = 0x5DEECE66D
+
+    def step_fused(self, actions, is_continuous_action=True):
+        """K1, K1b and the first observation of re-generated envs in ONE launch.  Returns the out
+        dict of this step: obs_* = what the policy acts on next (fresh for ended envs), reward /
+        status / env_status / ended = the transition; ``self.term`` holds the terminal observation
+        rows of the ended envs (the replay row's next state)."""
+        mode = _abi.M_DYNAMICS | _abi.M_AUTO_DEACTIVATE
+        if not is_continuous_action:
+            mode |= _abi.M_DISCRETE
+        nxt = 1 - self._cur
+        with torch.cuda.device(self.device):
+            self.total_steps += 1
+            self.episode_counter += 1
+            _lib.env_step_autoreset(self.params, self.reset_params, self.state, actions, self._outs[nxt],
+                                    mode, self.OP, self.CP, self.want_robots, self.want_cores,
+                                    self.want_obs, self.min_start_goal_dis, seed=self.seed,
+                                    step=self.total_steps, episode=self.episode_counter,
+                                    observe_seed=self.seed ^ self.OBSERVE_SALT, term=self.term,
+                                    env_offset=self.env_offset, st_ptrs=self._st_ptrs,
+                                    o_ptrs=self._o_ptrs[nxt], counter_dev=self.counter_dev)
+            self.launches += 1
+        self._cur = nxt
+        return self._outs[nxt]
 
     def step_no_reset(self, actions, is_continuous_action=True):
         mode = _abi.M_DYNAMICS | _abi.M_AUTO_DEACTIVATE
@@ -134,7 +166,7 @@ class BatchedMarineNavEnv:
 
     # ------------------------------------------------------------------ CUDA graph of one step
     def enable_cuda_graph(self, is_continuous_action=True):
-        """Capture step() (K1, K1b, masked K1) once per ping-pong phase.  The RNG counters baked
+        """Capture step() (the fused launch, or K1, K1b, masked K1) once per ping-pong phase.  The RNG counters baked
         into the two graphs differ by one and a device word advances them by two per pair of
         replays, so every replay draws fresh noise and fresh scenarios."""
         dev = self.device
@@ -167,7 +199,7 @@ class BatchedMarineNavEnv:
             self.graph_actions.copy_(actions)
         self._graphs[self._cur].replay()
         self._cur = 1 - self._cur
-        self.launches += 3
+        self.launches += 1 if self.fused else 3
         return self._outs[self._cur]
 
     # ------------------------------------------------------------------ host-facing convenience

@@ -131,10 +131,12 @@ class ReplayBuffer:
             return _lib.replay_sample(self.ring, batch, seed=self.rng_seed, counter=self.draws,
                                       indices=indices, counter_dev=self.counter_dev)
 
-    def push_step(self, obs, actions, discrete, out):
+    def push_step(self, obs, actions, discrete, out, term=None):
         """K2a: append the transitions of one batched env step.  ``obs`` = (self, objects, mask)
-        the policy acted on, ``out`` = the step's output dict (next observation, reward, status)."""
+        the policy acted on, ``out`` = the step's output dict (next observation, reward, status).
+        ``term``: the terminal-observation buffers of a fused auto-reset step (``env.term``)."""
         self.flush()
         with torch.cuda.device(self.device):
             _lib.replay_push(self.ring, obs[0], obs[1], obs[2], actions, discrete, out["reward"],
-                             out["obs_self"], out["obs_objects"], out["obs_mask"], out["status"])
+                             out["obs_self"], out["obs_objects"], out["obs_mask"], out["status"],
+                             term=term, ended=out["ended"] if term is not None else None)

@@ -75,6 +75,10 @@ class VectorTrainer:
         flat = (o_self.view(E * RP, 7), o_obj.view(E * RP, 5, 5), o_mask.view(E * RP, 5))
         actions = agent.act_batch(flat, self._eps_dev)
         actions = actions.view(E, RP) if self.discrete else actions.view(E, RP, 2)
+        if env.fused:  # one launch: step + re-generation + first observation; terminal rows in env.term
+            out = env.step_fused(actions, is_continuous_action=not self.discrete)
+            agent.memory.push_step((o_self, o_obj, o_mask), actions, self.discrete, out, term=env.term)
+            return out
         out = env.step_no_reset(actions, is_continuous_action=not self.discrete)
         agent.memory.push_step((o_self, o_obj, o_mask), actions, self.discrete, out)
         env.finish_episodes()

@@ -244,6 +244,38 @@ ASVRL_API int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env_
                               int max_cores, int64_t env_offset, const uint64_t* counter_dev,
                               void* stream);
 
+/* Auto-reset arguments of the fused step: what the Trainer does between two steps of one env
+ * (TRAINER:172, 240-245: `if end_episode: states, _, _ = train_env.reset()`). */
+typedef struct asvrl_env_autoreset {
+  const asvrl_reset_params* reset_params;
+  const int32_t* want_robots;          /* [E] requested counts of the NEXT episode (ENV:75-87) */
+  const int32_t* want_cores;           /* [E] */
+  const int32_t* want_obs;             /* [E] */
+  const float* min_start_goal_dis;     /* [E] */
+  uint64_t episode;                    /* scenario RNG counter, as asvrl_env_reset's */
+  uint64_t observe_seed;               /* seed of the sensor-noise stream of the first observation */
+  float* term_self;                    /* nullable [E][RP][7]: rows of envs with ended=1 receive */
+  float* term_objects;                 /* nullable [E][RP][5][5]  the TERMINAL observation (the  */
+  float* term_mask;                    /* nullable [E][RP][5]     replay row's next state)       */
+} asvrl_env_autoreset;
+
+/* K1 + K1b + first observation in ONE launch — equal, bit for bit, to
+ *   asvrl_env_step(mode, env_mask=NULL, noise=NULL)                       (writes out, ended)
+ *   asvrl_env_reset(reset_mask=out->ended, seed, ar->episode)
+ *   asvrl_env_step(mode=0, env_mask=out->ended, seed=ar->observe_seed, step=ar->episode)
+ * except that reward / status / phi / env_status / ended keep describing the TRANSITION for the
+ * envs that ended (the three-call sequence overwrites them with the fresh episode's), and the
+ * terminal observation rows of those envs are kept in ar->term_*.  out->obs_* hold, for every
+ * env, the observation to act on next.  A CTA that owns an ended env re-generates it with one
+ * warp (K1b's routine) and re-runs the perception phases for it; other CTAs are unaffected.
+ * Requires ASVRL_M_DYNAMICS; counter_dev is added to both `step` and `ar->episode`. */
+ASVRL_API int asvrl_env_step_autoreset(const asvrl_env_params* params, const asvrl_env_state* state,
+                                       const void* actions, uint64_t seed, uint64_t step,
+                                       const asvrl_env_out* out, const asvrl_env_autoreset* ar,
+                                       int n_envs, int max_robots, int max_obs, int max_cores,
+                                       int64_t env_offset, uint32_t mode,
+                                       const uint64_t* counter_dev, void* stream);
+
 /* Replay rows are dense float32[ASVRL_ROW] records: RB:22-69 + AGENT:360-368,387-392 */
 #define ASVRL_ROW_SELF 0     /* 7  */
 #define ASVRL_ROW_OBJ 7      /* 25 */
@@ -261,13 +293,17 @@ ASVRL_API int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env_
  * ASVRL_INFO_ABSENT, in (env, robot) order (deterministic), at the ring position given by the
  * device counters head_size[0] = rows ever written, head_size[1] = rows valid = min(total,
  * capacity).  workspace: uint32[ceil(n_asv/64) + 4], zero-initialised once by the caller and
- * left clean by every call. */
+ * left clean by every call.  After asvrl_env_step_autoreset the next state of an ASV whose env
+ * ended (ended[i / robots_per_env] != 0) is read from term_* instead of next_* (all four
+ * nullable together: NULL = always next_*). */
 ASVRL_API int asvrl_replay_push(float* rows, int64_t capacity, unsigned long long* head_size,
                                 const float* obs_self, const float* obs_objects,
                                 const float* obs_mask, const void* actions, int discrete,
                                 const float* reward, const float* next_self,
                                 const float* next_objects, const float* next_mask,
                                 const uint32_t* status, int n_asv, uint32_t* workspace,
+                                const float* term_self, const float* term_objects,
+                                const float* term_mask, const uint8_t* ended, int robots_per_env,
                                 void* stream);
 
 /* K2b — replaces ReplayBuffer.sample + state_batch + Agent.state_to_tensor (RB:26-69,

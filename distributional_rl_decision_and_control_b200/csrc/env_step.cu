@@ -67,7 +67,7 @@ constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
 struct SmemLayout {
   uint32_t px, py, key, obst, cores, c, s, vx, vy, vz, Tl, Tr, gx, gy, rew, ox, oy, osp, cand,
       st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, plist, dlist, cnt, el_of, r_of, chit,
-      nr, no, nc, ep, ok, ended, rs_sg, rs_core, rs_obs, rs_cand, rs_okm;
+      nr, no, nc, ep, ok, ended, rs_sg, rs_core, rs_obs, rs_cand, rs_okm, crx, cry;
   uint32_t bytes;
   // pair-loop stepping without integer division: TPB = q*S + rem
   int step_a, step_sl, step3_a, step3_sl;
@@ -75,6 +75,7 @@ struct SmemLayout {
 
 struct Smem {
   double *px, *py, *key;
+  float *crx, *cry;  // [CP][A] core - pose offsets at the start of the step (phase A only)
   float *c, *s, *vx, *vy, *vz, *Tl, *Tr, *gx, *gy, *rew, *ox, *oy, *osp;
   float *cand, *st_obj, *st_self, *st_mask, *cphi;
   uint32_t *fl0, *fl, *det_lo, *det_hi;
@@ -108,6 +109,9 @@ static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fus
   const uint32_t f = fused ? 1u : 0u;
   L.rs_sg = take(f * RP, 16); L.rs_core = take(f * CP, 16); L.rs_obs = take(f * OP, 16);
   L.rs_cand = take(f * tpb, 16); L.rs_okm = take(f * 8, 4);
+  // phase A's offset tables are dead before phase B writes the keys: alias them when they fit
+  if ((uint32_t)CP * A * 8 <= A * SK * 8) { L.crx = L.key; L.cry = L.key + (uint32_t)CP * A * 4; }
+  else { L.crx = take((uint32_t)CP * A, 4); L.cry = take((uint32_t)CP * A, 4); }
   L.bytes = off;
   L.step_a = tpb / (int)S; L.step_sl = tpb % (int)S;
   L.step3_a = (tpb - 32) / (int)S; L.step3_sl = (tpb - 32) % (int)S;
@@ -117,6 +121,7 @@ static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fus
 __device__ __forceinline__ Smem carve(char* base, const SmemLayout& L) {
   Smem m;
   m.px = (double*)(base + L.px); m.py = (double*)(base + L.py); m.key = (double*)(base + L.key);
+  m.crx = (float*)(base + L.crx); m.cry = (float*)(base + L.cry);
   m.obst = (float4*)(base + L.obst); m.cores = (float4*)(base + L.cores);
   m.c = (float*)(base + L.c); m.s = (float*)(base + L.s); m.vx = (float*)(base + L.vx);
   m.vy = (float*)(base + L.vy); m.vz = (float*)(base + L.vz); m.Tl = (float*)(base + L.Tl);
@@ -154,14 +159,19 @@ struct PairIt {
 // core (solid body) and Gamma/(2 pi d^2) outside: no square root, one reciprocal per core.
 // The offsets core - p are formed in fp64 from the fp64 pose: the 1/d^2 field amplifies the fp32
 // rounding of a ~50 m coordinate by 1/d near a core.
-__device__ __forceinline__ void current_at(const EnvConsts& k, const float4* cores, int nc, double x,
-                                           double y, float& cx, float& cy) {
+// Inside the 10 sub-steps the fp64 subtraction is hoisted: (core - pose0) is rounded to fp32 once
+// per (ASV, core) (table rx0/ry0, stride A) and the displacement since the step started, (dx, dy) =
+// fl32(pose - pose0) <= 1.5 m, is subtracted in fp32; the field is singular only for d < core_r
+// where it is replaced by the solid-body law, so the error on f stays below 1e-6 relative.
+__device__ __forceinline__ void current_at(const EnvConsts& k, const float4* cores, int nc,
+                                           const float* rx0, const float* ry0, int A, float dx, float dy,
+                                           float& cx, float& cy) {
   float ax = 0.0f, ay = 0.0f;
   const float r2 = k.core_r * k.core_r;
 #pragma unroll 4
   for (int i = 0; i < nc; ++i) {
     const float4 co = cores[i];
-    const float rx = (float)((double)co.x - x), ry = (float)((double)co.y - y);
+    const float rx = rx0[i * A] - dx, ry = ry0[i * A] - dy;
     const float d2 = rx * rx + ry * ry;
     const float g = co.w * co.z;  // signed circulation: +clockwise, -counter-clockwise (ENV:483-487)
     const float f = d2 <= r2 ? g * k.solid_k : __fdividef(g * k.inv_2pi, d2);  // ENV:497-501
@@ -230,7 +240,7 @@ __device__ __forceinline__ Cand candidate(const EnvConsts& k, const Smem& m, int
 }
 
 template <bool INJECT, bool FUSED>
-__global__ void __launch_bounds__(TPB, 8)
+__global__ void __launch_bounds__(TPB, 7)
 env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L,
                 StatePtrs st, const void* __restrict__ actions,
                 const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
@@ -275,16 +285,33 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     const int el = i / CP;
     m.cores[i] = m.ok[el] ? st.cores[(size_t)(e0 + el) * CP + (i - el * CP)] : make_float4(0, 0, 0, 0);
   }
+  // warp 0, one lane per ASV: the whole state row is requested here, one DRAM round trip ahead of
+  // the integration that consumes it
+  float p_x = 0, p_y = 0, p_th = 0, vr0 = 0, vr1 = 0, vr2 = 0, v0 = 0, v1 = 0, v2 = 0, Tl = 0, Tr = 0,
+        gx = 0, gy = 0;
+  float2 act = make_float2(0.0f, 0.0f);
+  int act_id = 0;
   if (tid < A) {
     const int el = tid / RP, r = tid - el * RP;
     const bool present = m.ok[el] && r < m.nr[el];
     const size_t g = (size_t)(e0 + el) * RP + r;
-    m.ox[tid] = present ? st.x[g] : 0.0f;
-    m.oy[tid] = present ? st.y[g] : 0.0f;
-    float sp = 0.0f;
-    if (present) { const float a = st.vel_x[g], b = st.vel_y[g]; sp = sqrtf(a * a + b * b); }
-    m.osp[tid] = sp;
-    m.fl0[tid] = present ? st.flags[g] : (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
+    uint32_t f = (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
+    if (present) {
+      p_x = st.x[g]; p_y = st.y[g]; p_th = st.theta[g];
+      vr0 = st.velr_x[g]; vr1 = st.velr_y[g]; vr2 = st.velr_r[g];
+      v0 = st.vel_x[g]; v1 = st.vel_y[g]; v2 = st.vel_r[g];
+      Tl = st.thrust_l[g]; Tr = st.thrust_r[g];
+      gx = st.goal_x[g]; gy = st.goal_y[g];
+      f = st.flags[g];
+      if (dyn) {
+        if (mode & ASVRL_M_DISCRETE) act_id = ((const int32_t*)actions)[g];
+        else act = ((const float2*)actions)[g];
+      }
+    }
+    m.ox[tid] = p_x;
+    m.oy[tid] = p_y;
+    m.osp[tid] = sqrtf(v0 * v0 + v1 * v1);
+    m.fl0[tid] = f;
     m.el_of[tid] = (uint8_t)el;
     m.r_of[tid] = (uint8_t)r;
     m.det_lo[tid] = 0; m.det_hi[tid] = 0;
@@ -297,7 +324,10 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
   // full warps instead of the ~20 % of lanes a flat pair loop keeps busy.  The filter uses the
   // pre-step poses plus a travel allowance (it must only be a superset; phase B decides).  With
   // injected noise (tests) the noise is unbounded, so every live pair is kept. ----
-  for (PairIt it(tid, S); it.p - (tid & 31) < NP; it.advance(TPB, L.step_a, L.step_sl, S)) {
+  // Warps 1..3 run it while warp 0 is already integrating (phase A), then meet on barrier 2 and
+  // signal warp 0 through barrier 1 (96 arrivals + warp 0's sync).
+  if (tid >= 32) {
+  for (PairIt it(tid - 32, S); it.p - (tid & 31) < NP; it.advance(TPB - 32, L.step3_a, L.step3_sl, S)) {
     bool keep = false;
     const int a = it.a, sl = it.sl;
     if (it.p < NP && !(m.fl0[a] & ASVRL_F_DEACTIVATED)) {
@@ -328,8 +358,9 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       if (keep) m.plist[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)((a << 6) | sl);
     }
   }
-  __syncthreads();
-  const int n_pairs = m.cnt[0];
+  asm volatile("bar.sync 2, 96;" ::: "memory");
+  asm volatile("bar.arrive 1, 128;" ::: "memory");
+  }
 
   if (tid < 32) {
     // ---- phase A (warp 0): dynamics, one lane per ASV ----
@@ -338,38 +369,36 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       const int e = e0 + el;
       const bool present = m.ok[el] && r < m.nr[el];
       const size_t g = (size_t)e * RP + r;
-      double x = 0, y = 0, th = 0;
-      float vr0 = 0, vr1 = 0, vr2 = 0, v0 = 0, v1 = 0, v2 = 0, Tl = 0, Tr = 0, gx = 0, gy = 0;
+      double x = p_x, y = p_y, th = p_th;
       const uint32_t f = m.fl0[tid];
       float rew = 0.0f;
-      if (present) {
-        x = m.ox[tid]; y = m.oy[tid]; th = st.theta[g];
-        vr0 = st.velr_x[g]; vr1 = st.velr_y[g]; vr2 = st.velr_r[g];
-        v0 = st.vel_x[g]; v1 = st.vel_y[g]; v2 = st.vel_r[g];
-        Tl = st.thrust_l[g]; Tr = st.thrust_r[g];
-        gx = st.goal_x[g]; gy = st.goal_y[g];
-      }
       if (present && dyn && !(f & ASVRL_F_DEACTIVATED)) {
         // thrust increments in fp64: T + a*500 cancels when the thruster reverses
         double dl, dr;
         if (mode & ASVRL_M_DISCRETE) {  // WAMV:146-147, 225: id = 5*iL + iR
-          int a = ((const int32_t*)actions)[g];
-          a = min(max(a, 0), 24);
+          const int a = min(max(act_id, 0), 24);
           dl = k.dl[a / 5];
           dr = k.dr[a % 5];
         } else {  // WAMV:220-223
-          const float2 a = ((const float2*)actions)[g];
-          dl = (double)a.x * k.act_scale;
-          dr = (double)a.y * k.act_scale;
+          dl = (double)act.x * k.act_scale;
+          dr = (double)act.y * k.act_scale;
         }
         const float4* cores = m.cores + el * CP;
         const int nc = m.nc[el];
+        float* rx0 = m.crx + tid;
+        float* ry0 = m.cry + tid;
+        for (int i = 0; i < nc; ++i) {  // (core - pose0) in fp64, rounded once
+          const float4 co = cores[i];
+          rx0[i * A] = (float)((double)co.x - x);
+          ry0[i * A] = (float)((double)co.y - y);
+        }
+        const double x_start = x, y_start = y;
         double dxg = (double)gx - x, dyg = (double)gy - y;
         const double dis_before = sqrt(dxg * dxg + dyg * dyg);  // ENV:254
         const double TWO_PI = 6.283185307179586;
         for (int idx = 0; idx < k.n_sub; ++idx) {  // ENV:257-260
           float cx, cy;
-          current_at(k, cores, nc, x, y, cx, cy);
+          current_at(k, cores, nc, rx0, ry0, A, (float)(x - x_start), (float)(y - y_start), cx, cy);
           v0 = vr0 + cx; v1 = vr1 + cy; v2 = vr2;  // WAMV:201-202
           x += (double)(v0 * k.dt);                // WAMV:207-210
           y += (double)(v1 * k.dt);
@@ -429,12 +458,14 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       }
       m.fl[tid] = fnew;
     }
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // plist / cnt[0] of warps 1..3 are complete
   }
   if (!INJECT) {
     // ---- phase A' (warps 1..3 at once, warp 0 when its integration is done): the sensor noise
     // does not depend on the state, so it is drawn for the compacted pairs while warp 0 walks
     // the serial integration chain.  Warps take 32 list entries at a time from a ticket. ----
     const int lane = tid & 31;
+    const int n_pairs = m.cnt[0];
     for (;;) {
       int first = 0;
       if (lane == 0) first = atomicAdd(&m.cnt[2], 32);
@@ -452,6 +483,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     }
   }
   __syncthreads();
+  const int n_pairs = m.cnt[0];
 
   // ---- phase B: the compacted pairs, one per thread, with the post-step poses: detection and
   // collision predicates in fp64, body-frame observation and sort key into shared memory;

@@ -173,6 +173,10 @@ def run_b200(args):
                               fused=not args.unfused)
     env.reset()
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    if not args.no_stagger:
+        # steady state: episode clocks spread over [0, 1000) so ~E/1000 episodes time out per step,
+        # as in a long run; without it every env of the batch times out in the same step
+        env.state["ep_steps"].copy_(torch.randint(0, 1000, (E,), device=dev, generator=gen, dtype=torch.int32))
     pool = [torch.rand((E, R, 2), device=dev, generator=gen) * 2 - 1 for _ in range(8)]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
@@ -309,6 +313,7 @@ def run_b200(args):
                                    + ("one fused launch per step (K1 + re-generation + first observation), no graph"
                                       if env.fused else "one CUDA graph per step (K1, K1b, masked K1)"),
                        "envs_per_gpu": E, "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
+                       "episode_clocks": "synchronised" if args.no_stagger else "staggered over [0,1000): ~E/1000 resets per step",
                        "l2": "flushed between timed steps (256 MiB write)", "parallelism": f"envs sharded x{world}, no collective"},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
                     "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": E * R * 39 * 4},
@@ -373,6 +378,7 @@ def main():
     ap.add_argument("--cpu-envs", type=int, default=2048)
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-stagger", action="store_true", help="start every episode clock at 0")
     ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -153,6 +153,7 @@ class EnvAutoReset(C.Structure):
     """asvrl_env_autoreset: arguments of the fused step + auto-reset launch (include/asvrl.h)."""
     _fields_ = [("reset_params", C.POINTER(ResetParams)), ("want_robots", C.c_void_p),
                 ("want_cores", C.c_void_p), ("want_obs", C.c_void_p),
-                ("min_start_goal_dis", C.c_void_p), ("episode", C.c_uint64),
+                ("min_start_goal_dis", C.c_void_p), ("episode_idx", C.c_void_p),
                 ("observe_seed", C.c_uint64), ("term_self", C.c_void_p),
-                ("term_objects", C.c_void_p), ("term_mask", C.c_void_p)]
+                ("term_objects", C.c_void_p), ("term_mask", C.c_void_p),
+                ("stage", C.POINTER(EnvStatePtrs)), ("stage_tag", C.c_void_p)]

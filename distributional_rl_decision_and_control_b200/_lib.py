@@ -195,10 +195,13 @@ def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, 
 
 
 def env_step_autoreset(params, rparams, st, actions, out, mode, max_obs, max_cores, want_robots,
-                       want_cores, want_obs, min_sg, seed=0, step=0, episode=0, observe_seed=0,
-                       term=None, env_offset=0, st_ptrs=None, o_ptrs=None, counter_dev=None):
-    """K1 + K1b + first observation in one launch (asvrl_env_step_autoreset).  ``term`` = dict with
-    obs_self / obs_objects / obs_mask tensors that receive the terminal rows of ended envs."""
+                       want_cores, want_obs, min_sg, episode_idx, seed=0, step=0, observe_seed=0,
+                       term=None, stage_ptrs=None, stage_tag=None, env_offset=0, st_ptrs=None,
+                       o_ptrs=None, counter_dev=None):
+    """K1 + K1b + first observation in one launch (asvrl_env_step_autoreset).  ``episode_idx`` =
+    int32 [E] per-env episode counters (in/out); ``term`` = dict with obs_self / obs_objects /
+    obs_mask tensors that receive the terminal rows of ended envs; ``stage_ptrs`` (state_ptrs of a
+    second state block) + ``stage_tag`` int32 [E] enable pre-generated next episodes."""
     E, RP = st["x"].shape
     want = torch.int32 if (mode & _abi.M_DISCRETE) else torch.float32
     sp = st_ptrs if st_ptrs is not None else state_ptrs(st)
@@ -209,7 +212,11 @@ def env_step_autoreset(params, rparams, st, actions, out, mode, max_obs, max_cor
     ar.want_cores = ptr(want_cores, torch.int32)
     ar.want_obs = ptr(want_obs, torch.int32)
     ar.min_start_goal_dis = ptr(min_sg, torch.float32)
-    ar.episode, ar.observe_seed = episode, observe_seed & 0xFFFFFFFFFFFFFFFF
+    ar.episode_idx = ptr(episode_idx, torch.int32)
+    ar.observe_seed = observe_seed & 0xFFFFFFFFFFFFFFFF
+    if stage_ptrs is not None:
+        ar.stage = C.pointer(stage_ptrs)
+        ar.stage_tag = ptr(stage_tag, torch.int32)
     if term is not None:
         ar.term_self = ptr(term["obs_self"], torch.float32)
         ar.term_objects = ptr(term["obs_objects"], torch.float32)

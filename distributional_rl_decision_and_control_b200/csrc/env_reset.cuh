@@ -40,27 +40,34 @@ __device__ __forceinline__ float dist2f(float ax, float ay, float bx, float by) 
   return sqrtf(dx * dx + dy * dy);
 }
 
+// squared distance: the acceptance tests below compare d^2 with the squared bound (no square root,
+// no dependent chain); they decide like the reference's `norm(...) <= bound` except within one
+// ulp of the bound, which the parity tests' float64 margin already excludes
+__device__ __forceinline__ float sqd(float ax, float ay, float bx, float by) {
+  const float dx = ax - bx, dy = ay - by;
+  return dx * dx + dy * dy;
+}
+
 // ENV:368-374: start too close to an accepted start, or goal to an accepted goal
 __device__ __forceinline__ bool sg_conflict(const ResetConsts& k, float4 c, float4 o) {
-  return dist2f(o.x, o.y, c.x, c.y) <= k.clear_r || dist2f(o.z, o.w, c.z, c.w) <= k.clear_r;
+  const float c2 = k.clear_r * k.clear_r;
+  return (sqd(o.x, o.y, c.x, c.y) <= c2) | (sqd(o.z, o.w, c.z, c.w) <= c2);
 }
 
 // ENV:396-416: core c = (x, y, dir, Gamma) against an accepted core o
 __device__ __forceinline__ bool core_conflict(const ResetConsts& k, float4 c, float4 o) {
   const float TWO_PI = 6.28318530717959f;
   const float dis = dist2f(o.x, o.y, c.x, c.y);
-  if (o.z == c.z) {
-    const float bi = o.w / (TWO_PI * k.v_rel_max), bj = c.w / (TWO_PI * k.v_rel_max);
-    return dis < bi + bj;
-  }
+  const float bi = o.w / (TWO_PI * k.v_rel_max), bj = c.w / (TWO_PI * k.v_rel_max);
   const float gl = fmaxf(o.w, c.w), gs = fminf(o.w, c.w);
   const float v1 = gl / (TWO_PI * (dis - 2.0f * k.core_r)), v2 = gs / (TWO_PI * k.core_r);
-  return v1 > k.p * v2;
+  return o.z == c.z ? dis < bi + bj : v1 > k.p * v2;
 }
 
 // ENV:448-454: obstacle c = (x, y, r) overlapping an accepted obstacle o
 __device__ __forceinline__ bool obs_conflict(float4 c, float4 o) {
-  return dist2f(o.x, o.y, c.x, c.y) <= o.z + c.z;
+  const float rr = o.z + c.z;
+  return sqd(o.x, o.y, c.x, c.y) <= rr * rr;
 }
 
 __device__ __forceinline__ float4 shfl4(float4 v, int src) {
@@ -97,7 +104,7 @@ __device__ __forceinline__ float4 robot_candidate(const ResetConsts& k, uint64_t
                      lerp_u(lo, k.map_w - lo, u01(w.z)), lerp_u(lo, k.map_h - lo, u01(w.w)));
 }
 __device__ __forceinline__ bool robot_ok(float4 c, float min_dis) {  // ENV:361
-  return !(dist2f(c.z, c.w, c.x, c.y) < min_dis);
+  return !(sqd(c.z, c.w, c.x, c.y) < min_dis * min_dis);
 }
 
 __device__ __forceinline__ float4 core_candidate(const ResetConsts& k, uint64_t seed, uint64_t episode,
@@ -109,13 +116,14 @@ __device__ __forceinline__ float4 core_candidate(const ResetConsts& k, uint64_t 
                      TWO_PI * k.core_r * lerp_u(k.v_min, k.v_max, u01(w.w)));
 }
 __device__ __forceinline__ bool core_ok(const ResetConsts& k, float4 c, const float4* sg, int n_r) {
-  bool ok = !(c.x - k.core_r < 0.0f || c.x + k.core_r > k.map_w);   // ENV:381
-  ok = ok && !(c.y - k.core_r < 0.0f || c.y + k.core_r > k.map_w);  // ENV:383 (sic: width)
-  for (int i = 0; i < n_r && ok; ++i) {                             // ENV:386-394
+  bool bad = (c.x - k.core_r < 0.0f) | (c.x + k.core_r > k.map_w);   // ENV:381
+  bad |= (c.y - k.core_r < 0.0f) | (c.y + k.core_r > k.map_w);       // ENV:383 (sic: width)
+  const float lim = k.core_r + k.clear_r, lim2 = lim * lim;
+  for (int i = 0; i < n_r; ++i) {                                    // ENV:386-394
     const float4 o = sg[i];
-    ok = !(dist2f(c.x, c.y, o.x, o.y) < k.core_r + k.clear_r) && !(dist2f(c.x, c.y, o.z, o.w) < k.core_r + k.clear_r);
+    bad |= (sqd(c.x, c.y, o.x, o.y) < lim2) | (sqd(c.x, c.y, o.z, o.w) < lim2);
   }
-  return ok;
+  return !bad;
 }
 
 __device__ __forceinline__ float4 obs_candidate(const ResetConsts& k, uint64_t seed, uint64_t episode,
@@ -128,14 +136,15 @@ __device__ __forceinline__ float4 obs_candidate(const ResetConsts& k, uint64_t s
 __device__ __forceinline__ bool obs_ok(const ResetConsts& k, float4 c, const float4* sg, int n_r,
                                        const float4* cores, int n_c) {
   const float cx = c.x, cy = c.y, rr = c.z;
-  bool ok = !(cx - rr < 0.0f || cx + rr > k.map_w) && !(cy - rr < 0.0f || cy + rr > k.map_h);
-  for (int i = 0; i < n_r && ok; ++i) {  // ENV:428-436
+  bool bad = (cx - rr < 0.0f) | (cx + rr > k.map_w) | (cy - rr < 0.0f) | (cy + rr > k.map_h);
+  const float lim = rr + k.clear_r, lim2 = lim * lim, lc = k.core_r + rr, lc2 = lc * lc;
+  for (int i = 0; i < n_r; ++i) {  // ENV:428-436
     const float4 o = sg[i];
-    ok = !(dist2f(cx, cy, o.x, o.y) < rr + k.clear_r) && !(dist2f(cx, cy, o.z, o.w) < rr + k.clear_r);
+    bad |= (sqd(cx, cy, o.x, o.y) < lim2) | (sqd(cx, cy, o.z, o.w) < lim2);
   }
-  for (int i = 0; i < n_c && ok; ++i)    // ENV:439-445
-    ok = !(dist2f(cores[i].x, cores[i].y, cx, cy) <= k.core_r + rr);
-  return ok;
+  for (int i = 0; i < n_c; ++i)    // ENV:439-445
+    bad |= sqd(cores[i].x, cores[i].y, cx, cy) <= lc2;
+  return !bad;
 }
 
 // write the fresh episode: reset_robot ENV:166-176, Robot.reset_state WAMV:177-193
@@ -168,6 +177,26 @@ __device__ __forceinline__ void write_episode(const ResetState& st, int e, int64
   }
 }
 
+// the pre-generated episode of env e moves from the stage to the live state (all `nthreads` threads)
+__device__ __forceinline__ void take_stage(const ResetState& st, const ResetState& sg, int e, int RP, int OP,
+                                           int CP, int tid, int nthreads) {
+  for (int r = tid; r < RP; r += nthreads) {
+    const size_t g = (size_t)e * RP + r;
+    st.x[g] = __ldcg(sg.x + g); st.y[g] = __ldcg(sg.y + g); st.theta[g] = __ldcg(sg.theta + g);
+    st.goal_x[g] = __ldcg(sg.goal_x + g); st.goal_y[g] = __ldcg(sg.goal_y + g);
+    st.velr_x[g] = 0; st.velr_y[g] = 0; st.velr_r[g] = 0;
+    st.vel_x[g] = 0; st.vel_y[g] = 0; st.vel_r[g] = 0;
+    st.thrust_l[g] = 0; st.thrust_r[g] = 0;
+    st.flags[g] = 0;
+  }
+  for (int i = tid; i < OP; i += nthreads) st.obstacles[(size_t)e * OP + i] = __ldcg(sg.obstacles + (size_t)e * OP + i);
+  for (int i = tid; i < CP; i += nthreads) st.cores[(size_t)e * CP + i] = __ldcg(sg.cores + (size_t)e * CP + i);
+  if (tid == 0) {
+    st.n_robots[e] = __ldcg(sg.n_robots + e); st.n_obs[e] = __ldcg(sg.n_obs + e); st.n_cores[e] = __ldcg(sg.n_cores + e);
+    st.ep_steps[e] = 0;
+  }
+}
+
 // One warp re-generates env `e` (global index `ge` for the RNG counters) and writes the fresh episode
 // to the state arrays.  sg / cores / obs: per-warp shared scratch of >= RP / CP / OP float4.
 __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const ResetState& st, int e, int64_t ge,
@@ -182,7 +211,7 @@ __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const Reset
     const int t = base + lane;
     const float4 c = robot_candidate(k, seed, episode, ge, t);
     bool ok = t < k.max_tries && robot_ok(c, min_dis);
-    for (int i = 0; i < n_r && ok; ++i) ok = !sg_conflict(k, c, sg[i]);
+    for (int i = 0; i < n_r; ++i) ok &= !sg_conflict(k, c, sg[i]);
     n_r = resolve_round(__ballot_sync(FULL, ok), c, sg, n_r, want_r, lane,
                         [&](float4 a, float4 b) { return sg_conflict(k, a, b); });
   }
@@ -193,7 +222,7 @@ __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const Reset
     const int t = base + lane;
     const float4 c = core_candidate(k, seed, episode, ge, t);
     bool ok = t < k.max_tries && core_ok(k, c, sg, n_r);
-    for (int i = 0; i < n_c && ok; ++i) ok = !core_conflict(k, c, cores[i]);  // ENV:396-416
+    for (int i = 0; i < n_c; ++i) ok &= !core_conflict(k, c, cores[i]);  // ENV:396-416
     n_c = resolve_round(__ballot_sync(FULL, ok), c, cores, n_c, want_c, lane,
                         [&](float4 a, float4 b) { return core_conflict(k, a, b); });
   }
@@ -204,7 +233,7 @@ __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const Reset
     const int t = base + lane;
     const float4 c = obs_candidate(k, seed, episode, ge, t);
     bool ok = t < k.max_tries && obs_ok(k, c, sg, n_r, cores, n_c);
-    for (int i = 0; i < n_o && ok; ++i) ok = !obs_conflict(c, obs[i]);  // ENV:448-454
+    for (int i = 0; i < n_o; ++i) ok &= !obs_conflict(c, obs[i]);  // ENV:448-454
     n_o = resolve_round(__ballot_sync(FULL, ok), c, obs, n_o, want_o, lane,
                         [&](float4 a, float4 b) { return obs_conflict(a, b); });
   }
@@ -231,7 +260,7 @@ __device__ __forceinline__ int place_class_cta(int want, int max_tries, float4* 
     const int t = base + tid;
     const float4 c = gen(t);
     bool ok = t < max_tries && fixed_ok(c);
-    for (int i = 0; i < n && ok; ++i) ok = !conflict(c, set[i]);
+    for (int i = 0; i < n; ++i) ok &= !conflict(c, set[i]);
     sc.cand[tid] = c;
     const unsigned b = __ballot_sync(FULL, ok);
     if (lane == 0) sc.okm[warp] = b;

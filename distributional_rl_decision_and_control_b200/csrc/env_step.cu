@@ -50,24 +50,70 @@ struct OutPtrs {
   uint8_t* ended;
 };
 
+constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
+
 // extra arguments of the fused step (asvrl_env_step_autoreset): K1, then in the same launch the
 // CTA re-generates its envs whose episode just ended (K1b's warp routine) and re-observes them
 struct FusedArgs {
   ResetConsts rk;
   const int32_t *want_robots, *want_cores, *want_obs;
   const float* min_sg;
-  uint64_t episode, observe_seed;
+  uint64_t observe_seed;
   float *term_self, *term_objects, *term_mask;  // terminal observation rows of ended envs (nullable)
+  int32_t* episode_idx;  // [E] episodes generated so far per env: the next scenario's RNG counter is idx + 1
+  // pre-generated next episodes (nullable): stage state + stage_tag[e] = episode number it holds
+  ResetState stage;
+  int32_t* stage_tag;
+  int n_workers;         // leading CTAs of the grid that only refill the stage
 };
 
-constexpr int TPB = 128;  // 4 warps per CTA; a CTA owns <= 32 ASVs (EPB envs)
+__device__ __forceinline__ int ld_acquire(const int32_t* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int32_t* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Refill worker (leading CTAs of the fused grid): every warp scans its slice of the envs for a
+// stage that does not hold the env's NEXT episode (tag != episode_idx + 1) and re-generates ONE of
+// them with K1b's warp routine, off the critical path of the step CTAs that run beside it.  The
+// scenario is a pure function of (seed, env, episode number), so it does not matter who generates
+// it or when: a step CTA that finds no valid stage generates the same episode inline.
+__device__ __forceinline__ void refill_worker(const FusedArgs& fa, char* smem, uint64_t seed, int E, int RP,
+                                              int OP, int CP, int64_t env_offset) {
+  if (!fa.stage_tag) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n_warps = fa.n_workers * (TPB / 32), gw = blockIdx.x * (TPB / 32) + warp;
+  const int chunk = (E + n_warps - 1) / n_warps;
+  const int lo = gw * chunk, hi = min(E, lo + chunk);
+  float4* sg = (float4*)smem + warp * (RP + CP + OP);
+  float4* cores = sg + RP;
+  float4* obs = cores + CP;
+  for (int base = lo; base < hi; base += 32) {
+    const int e = base + lane;
+    const bool need = e < hi && ld_acquire(fa.stage_tag + e) != __ldcg(fa.episode_idx + e) + 1;
+    const unsigned bal = __ballot_sync(0xffffffffu, need);
+    if (!bal) continue;
+    const int pick = base + __ffs(bal) - 1;
+    const int ep = __ldcg(fa.episode_idx + pick) + 1;
+    reset_env_warp(fa.rk, fa.stage, pick, env_offset + pick, fa.want_robots[pick], fa.want_cores[pick],
+                   fa.want_obs[pick], fa.min_sg[pick], seed, (uint64_t)ep, RP, OP, CP, sg, cores, obs, lane);
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) st_release(fa.stage_tag + pick, ep);
+    break;  // one env per warp per launch keeps the worker shorter than the step it hides behind
+  }
+}
+
 
 // shared-memory layout: byte offsets computed once on the host and passed by value, so the
 // kernel prologue is a handful of 32-bit adds instead of per-thread 64-bit size arithmetic
 struct SmemLayout {
   uint32_t px, py, key, obst, cores, c, s, vx, vy, vz, Tl, Tr, gx, gy, rew, ox, oy, osp, cand,
       st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, plist, dlist, cnt, el_of, r_of, chit,
-      nr, no, nc, ep, ok, ended, rs_sg, rs_core, rs_obs, rs_cand, rs_okm, crx, cry;
+      nr, no, nc, ep, ok, ended, epn, rs_sg, rs_core, rs_obs, rs_cand, rs_okm, crx, cry;
   uint32_t bytes;
   // pair-loop stepping without integer division: TPB = q*S + rem
   int step_a, step_sl, step3_a, step3_sl;
@@ -82,7 +128,7 @@ struct Smem {
   uint16_t *plist, *dlist;  // compacted (ego << 6 | slot): pairs worth a noise draw / detected pairs
   int* cnt;                 // [0] entries of plist, [1] entries of dlist, [2] noise work ticket
   uint8_t *el_of, *r_of, *chit;
-  int *nr, *no, *nc, *ep, *ok, *ended;
+  int *nr, *no, *nc, *ep, *ok, *ended, *epn;
   float4 *obst, *cores;
   float4 *rs_sg, *rs_core, *rs_obs, *rs_cand;  // fused auto-reset scratch: accepted sets, round candidates
   unsigned* rs_okm;
@@ -105,14 +151,16 @@ static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fus
   L.plist = take(A * S, 2); L.dlist = take(A * S, 2); L.cnt = take(4, 4);
   L.el_of = take(A, 1); L.r_of = take(A, 1); L.chit = take(A * 5, 1);
   L.nr = take(EPB, 4); L.no = take(EPB, 4); L.nc = take(EPB, 4); L.ep = take(EPB, 4); L.ok = take(EPB, 4);
-  L.ended = take(EPB, 4);
+  L.ended = take(EPB, 4); L.epn = take(EPB, 4);
   const uint32_t f = fused ? 1u : 0u;
   L.rs_sg = take(f * RP, 16); L.rs_core = take(f * CP, 16); L.rs_obs = take(f * OP, 16);
   L.rs_cand = take(f * tpb, 16); L.rs_okm = take(f * 8, 4);
   // phase A's offset tables are dead before phase B writes the keys: alias them when they fit
   if ((uint32_t)CP * A * 8 <= A * SK * 8) { L.crx = L.key; L.cry = L.key + (uint32_t)CP * A * 4; }
   else { L.crx = take((uint32_t)CP * A, 4); L.cry = take((uint32_t)CP * A, 4); }
-  L.bytes = off;
+  // a refill worker CTA carves per-warp accepted sets from the base of the same allocation
+  const uint32_t worker_need = fused ? (uint32_t)(tpb / 32) * (RP + CP + OP) * 16u : 0u;
+  L.bytes = off > worker_need ? off : worker_need;
   L.step_a = tpb / (int)S; L.step_sl = tpb % (int)S;
   L.step3_a = (tpb - 32) / (int)S; L.step3_sl = (tpb - 32) % (int)S;
   return L;
@@ -137,7 +185,7 @@ __device__ __forceinline__ Smem carve(char* base, const SmemLayout& L) {
   m.el_of = (uint8_t*)(base + L.el_of); m.r_of = (uint8_t*)(base + L.r_of);
   m.chit = (uint8_t*)(base + L.chit);
   m.nr = (int*)(base + L.nr); m.no = (int*)(base + L.no); m.nc = (int*)(base + L.nc);
-  m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok); m.ended = (int*)(base + L.ended);
+  m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok); m.ended = (int*)(base + L.ended); m.epn = (int*)(base + L.epn);
   m.rs_sg = (float4*)(base + L.rs_sg); m.rs_core = (float4*)(base + L.rs_core);
   m.rs_obs = (float4*)(base + L.rs_obs); m.rs_cand = (float4*)(base + L.rs_cand);
   m.rs_okm = (unsigned*)(base + L.rs_okm);
@@ -248,10 +296,14 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
                 uint32_t mode, int EPB, const uint64_t* __restrict__ counter_dev,
                 const __grid_constant__ FusedArgs fa) {
   extern __shared__ __align__(16) char smem_raw[];
+  if (FUSED && (int)blockIdx.x < fa.n_workers) {
+    refill_worker(fa, smem_raw, seed, E, RP, OP, CP, env_offset);
+    return;
+  }
   const Smem m = carve(smem_raw, L);
   const int tid = threadIdx.x;
   const int A = EPB * RP, S = OP + RP, SK = S | 1, NP = A * S;
-  const int e0 = blockIdx.x * EPB;
+  const int e0 = ((int)blockIdx.x - (FUSED ? fa.n_workers : 0)) * EPB;
   bool dyn = mode & ASVRL_M_DYNAMICS;
   if (counter_dev) step += *counter_dev;  // graph-replay friendly RNG counter (include/asvrl.h)
   // FUSED: pass 0 is the step itself; pass 1 (only in CTAs that own an env whose episode just
@@ -474,8 +526,9 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       const int i = first + lane;
       if (i < n_pairs) {
         const int pr = m.plist[i], a = pr >> 6, sl = pr & 63;
-        const NoiseDraw nd = sensor_noise(k, seed, step, env_offset + e0 + m.el_of[a], (uint32_t)m.r_of[a],
-                                          (uint32_t)sl);
+        const int el = m.el_of[a];
+        const NoiseDraw nd = sensor_noise(k, seed, (FUSED && second) ? (uint64_t)m.epn[el] : step,
+                                          env_offset + e0 + el, (uint32_t)m.r_of[a], (uint32_t)sl);
         float* np = m.cand + (a * S + sl) * 5;
 #pragma unroll
         for (int q = 0; q < 5; ++q) np[q] = nd.n[q];
@@ -707,21 +760,36 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
                              st.vel_r, st.thrust_l, st.thrust_r, (float*)st.goal_x, (float*)st.goal_y,
                              st.flags, (int32_t*)st.n_robots, (int32_t*)st.n_obs, (int32_t*)st.n_cores,
                              st.ep_steps, (float4*)st.obstacles, (float4*)st.cores};
-      uint64_t episode = fa.episode;
-      if (counter_dev) episode += *counter_dev;
+      // thread el decides for its env: 2 = the stage holds its next episode, 1 = generate it here
+      if (tid < EPB && my_end) {
+        const int e = e0 + tid;
+        const int ep = fa.episode_idx[e] + 1;
+        m.epn[tid] = ep;
+        if (fa.stage_tag && ld_acquire(fa.stage_tag + e) == ep) m.ended[tid] = 2;
+      }
+      __syncthreads();
       static_assert(TPB == 128, "reset_env_cta resolves rounds of 128 candidates");
       const CtaScratch sc = {m.rs_cand, m.rs_okm};
       for (int el = 0; el < n_env; ++el) {
-        if (!m.ended[el]) continue;
+        const int how = m.ended[el];
+        if (!how) continue;
         const int e = e0 + el;
-        reset_env_cta(fa.rk, rs, e, env_offset + e, fa.want_robots[e], fa.want_cores[e], fa.want_obs[e],
-                      fa.min_sg[e], seed, episode, RP, OP, CP, m.rs_sg, m.rs_core, m.rs_obs, sc, tid);
+        if (how == 2)
+          take_stage(rs, fa.stage, e, RP, OP, CP, tid, TPB);
+        else
+          reset_env_cta(fa.rk, rs, e, env_offset + e, fa.want_robots[e], fa.want_cores[e], fa.want_obs[e],
+                        fa.min_sg[e], seed, (uint64_t)m.epn[el], RP, OP, CP, m.rs_sg, m.rs_core, m.rs_obs,
+                        sc, tid);
+      }
+      __syncthreads();  // the stage has been read: only now may a worker see the bumped counter
+      if (tid < EPB && m.ended[tid]) {
+        __threadfence();
+        fa.episode_idx[e0 + tid] = m.epn[tid];
       }
       second = true;
       dyn = false;
       mode = 0;
-      seed = fa.observe_seed;
-      step = episode;
+      seed = fa.observe_seed;  // pass 1 draws its noise at step = the env's episode number (m.epn)
     }
     __syncthreads();
   }
@@ -869,7 +937,8 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
                                         int64_t env_offset, uint32_t mode,
                                         const uint64_t* counter_dev, void* stream) {
   if (!params || !state || !out || !ar) return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: null struct");
-  if (!ar->reset_params || !ar->want_robots || !ar->want_cores || !ar->want_obs || !ar->min_start_goal_dis)
+  if (!ar->reset_params || !ar->want_robots || !ar->want_cores || !ar->want_obs || !ar->min_start_goal_dis ||
+      !ar->episode_idx)
     return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: null auto-reset argument");
   if ((ar->term_self || ar->term_objects || ar->term_mask) &&
       !(ar->term_self && ar->term_objects && ar->term_mask))
@@ -901,17 +970,47 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
   fa.rk = make_reset_consts(ar->reset_params);
   fa.want_robots = ar->want_robots; fa.want_cores = ar->want_cores; fa.want_obs = ar->want_obs;
   fa.min_sg = ar->min_start_goal_dis;
-  fa.episode = ar->episode; fa.observe_seed = ar->observe_seed;
+  fa.observe_seed = ar->observe_seed;
+  fa.episode_idx = ar->episode_idx;
+  fa.stage_tag = nullptr;
+  fa.n_workers = 0;
+  memset(&fa.stage, 0, sizeof fa.stage);
+  if (ar->stage) {
+    const asvrl_env_state* g = ar->stage;
+    if (!ar->stage_tag) return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: stage needs stage_tag");
+    if (!g->x || !g->y || !g->theta || !g->velr_x || !g->velr_y || !g->velr_r || !g->vel_x || !g->vel_y ||
+        !g->vel_r || !g->thrust_l || !g->thrust_r || !g->goal_x || !g->goal_y || !g->flags || !g->n_robots ||
+        !g->n_obs || !g->n_cores || !g->ep_steps || (max_obs > 0 && !g->obstacles) || (max_cores > 0 && !g->cores))
+      return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: incomplete stage state");
+    fa.stage = ResetState{g->x, g->y, g->theta, g->velr_x, g->velr_y, g->velr_r, g->vel_x, g->vel_y, g->vel_r,
+                          g->thrust_l, g->thrust_r, g->goal_x, g->goal_y, g->flags, g->n_robots, g->n_obs,
+                          g->n_cores, g->ep_steps, (float4*)g->obstacles, (float4*)g->cores};
+    fa.stage_tag = ar->stage_tag;
+  }
   fa.term_self = ar->term_self; fa.term_objects = ar->term_objects; fa.term_mask = ar->term_mask;
   const int EPB = pick_epb(max_robots);
   const SmemLayout L = make_layout(EPB, max_robots, max_obs, max_cores, TPB, true);
   const size_t smem = L.bytes;
-  const int grid = (n_envs + EPB - 1) / EPB;
+  const int n_step = (n_envs + EPB - 1) / EPB;
   auto kern = env_step_kernel<false, true>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step_autoreset: %zu B shared memory: %s", smem, cudaGetErrorString(e));
   }
+  if (fa.stage_tag) {
+    // refill workers take the CTA slots the last wave of step CTAs leaves free (4..16 of them)
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TPB, smem);
+    const int slots = sms * (per_sm > 0 ? per_sm : 1);
+    int spare = slots - n_step % slots;
+    if (spare == slots) spare = 0;
+    fa.n_workers = spare < 4 ? 4 : (spare > 16 ? 16 : spare);
+    const int max_useful = (n_envs + TPB / 32 - 1) / (TPB / 32);
+    if (fa.n_workers > max_useful) fa.n_workers = max_useful;
+  }
+  const int grid = n_step + fa.n_workers;
   kern<<<grid, TPB, smem, (cudaStream_t)stream>>>(k, L, st, actions, nullptr, nullptr, seed, step, o, n_envs,
                                                   max_robots, max_obs, max_cores, env_offset, mode, EPB,
                                                   counter_dev, fa);

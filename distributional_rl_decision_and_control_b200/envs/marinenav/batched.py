@@ -23,7 +23,8 @@ class BatchedMarineNavEnv:
 
     def __init__(self, n_envs, num_robots=8, num_obs=10, num_cores=0, min_start_goal_dis=30.0,
                  device="cuda:0", seed=0, env_offset=0, max_robots=None, max_obs=None,
-                 max_cores=None, params=None, reset_params=None, debug_outputs=False, fused=True):
+                 max_cores=None, params=None, reset_params=None, debug_outputs=False, fused=True,
+                 prefetch=True):
         _lib.lib()  # fail loudly if the CUDA library is missing
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -54,6 +55,14 @@ class BatchedMarineNavEnv:
             self.term = {"obs_self": torch.zeros((self.E, self.RP, 7), dtype=torch.float32, device=self.device),
                          "obs_objects": torch.zeros((self.E, self.RP, 5, 5), dtype=torch.float32, device=self.device),
                          "obs_mask": torch.zeros((self.E, self.RP, 5), dtype=torch.float32, device=self.device)}
+            # per-env episode counters: the scenario RNG counter of env e's next episode is idx[e] + 1
+            self.episode_idx = torch.zeros((self.E,), dtype=torch.int32, device=self.device)
+            # pre-generated next episodes (a second state block + the episode number each holds)
+            self.stage = self.stage_tag = self._stage_ptrs = None
+            if fused and prefetch:
+                self.stage = _lib.new_state(self.E, self.RP, self.OP, self.CP, self.device)
+                self._stage_ptrs = _lib.state_ptrs(self.stage)
+                self.stage_tag = torch.zeros((self.E,), dtype=torch.int32, device=self.device)
         self.fused = bool(fused)  # step(auto_reset=True) = ONE launch (asvrl_env_step_autoreset)
         self.launches = 0
         # optional int64 device word added to both RNG counters on the device: a captured CUDA
@@ -72,6 +81,8 @@ class BatchedMarineNavEnv:
             self.want_cores.fill_(min(int(num_cores), self.CP))
         if min_start_goal_dis is not None:
             self.min_start_goal_dis.fill_(float(min_start_goal_dis))
+        if self.stage_tag is not None:
+            self.stage_tag.zero_()  # staged episodes were generated for the previous stage
 
     # ------------------------------------------------------------------ views
     @property
@@ -101,6 +112,9 @@ class BatchedMarineNavEnv:
     def reset(self):
         """Fresh scenario in every env; returns the observation tensors (device views)."""
         self._reset_and_observe(None, self._cur)
+        # every env now holds episode number `episode_counter`; fused steps count on from there
+        # (episode_counter also grows by one per fused step, an upper bound of every idx)
+        self.episode_idx.fill_(self.episode_counter)
         return self.obs
 
     def step(self, actions, is_continuous_action=True, auto_reset=True):
@@ -136,9 +150,10 @@ class BatchedMarineNavEnv:
             self.episode_counter += 1
             _lib.env_step_autoreset(self.params, self.reset_params, self.state, actions, self._outs[nxt],
                                     mode, self.OP, self.CP, self.want_robots, self.want_cores,
-                                    self.want_obs, self.min_start_goal_dis, seed=self.seed,
-                                    step=self.total_steps, episode=self.episode_counter,
+                                    self.want_obs, self.min_start_goal_dis, self.episode_idx,
+                                    seed=self.seed, step=self.total_steps,
                                     observe_seed=self.seed ^ self.OBSERVE_SALT, term=self.term,
+                                    stage_ptrs=self._stage_ptrs, stage_tag=self.stage_tag,
                                     env_offset=self.env_offset, st_ptrs=self._st_ptrs,
                                     o_ptrs=self._o_ptrs[nxt], counter_dev=self.counter_dev)
             self.launches += 1

@@ -252,23 +252,36 @@ typedef struct asvrl_env_autoreset {
   const int32_t* want_cores;           /* [E] */
   const int32_t* want_obs;             /* [E] */
   const float* min_start_goal_dis;     /* [E] */
-  uint64_t episode;                    /* scenario RNG counter, as asvrl_env_reset's */
+  int32_t* episode_idx;                /* [E] in/out: episodes generated so far for each env.  The
+                                          scenario RNG counter of env e's next episode (the
+                                          `episode` argument of asvrl_env_reset) is episode_idx[e]+1,
+                                          and so is the `step` of its first observation's noise */
   uint64_t observe_seed;               /* seed of the sensor-noise stream of the first observation */
   float* term_self;                    /* nullable [E][RP][7]: rows of envs with ended=1 receive */
   float* term_objects;                 /* nullable [E][RP][5][5]  the TERMINAL observation (the  */
   float* term_mask;                    /* nullable [E][RP][5]     replay row's next state)       */
+  const asvrl_env_state* stage;        /* nullable: a second, caller-owned state block of the same
+                                          shape holding PRE-GENERATED next episodes */
+  int32_t* stage_tag;                  /* [E] with stage: episode number the stage of env e holds
+                                          (0 = none; zero-initialise, and zero again whenever
+                                          want_* / min_start_goal_dis / reset_params change) */
 } asvrl_env_autoreset;
 
-/* K1 + K1b + first observation in ONE launch — equal, bit for bit, to
+/* K1 + K1b + first observation in ONE launch.  For every env, equal bit for bit to
  *   asvrl_env_step(mode, env_mask=NULL, noise=NULL)                       (writes out, ended)
- *   asvrl_env_reset(reset_mask=out->ended, seed, ar->episode)
- *   asvrl_env_step(mode=0, env_mask=out->ended, seed=ar->observe_seed, step=ar->episode)
+ * and then, for each env e with out->ended[e] != 0, with n = ++episode_idx[e]:
+ *   asvrl_env_reset(reset_mask={e}, seed, episode=n)
+ *   asvrl_env_step(mode=0, env_mask={e}, seed=ar->observe_seed, step=n)
  * except that reward / status / phi / env_status / ended keep describing the TRANSITION for the
- * envs that ended (the three-call sequence overwrites them with the fresh episode's), and the
- * terminal observation rows of those envs are kept in ar->term_*.  out->obs_* hold, for every
- * env, the observation to act on next.  A CTA that owns an ended env re-generates it with one
- * warp (K1b's routine) and re-runs the perception phases for it; other CTAs are unaffected.
- * Requires ASVRL_M_DYNAMICS; counter_dev is added to both `step` and `ar->episode`. */
+ * envs that ended (the call sequence overwrites them with the fresh episode's), and the terminal
+ * observation rows of those envs are kept in ar->term_*.  out->obs_* hold, for every env, the
+ * observation to act on next.
+ * Scenario generation is a pure function of (seed, env, episode number), which is what lets it
+ * leave the critical path: with `stage`, a few extra CTAs of the same launch pre-generate the
+ * NEXT episode of every env whose stage was consumed (K1b's warp routine, concurrently with the
+ * step CTAs), and a CTA whose env ends just copies the staged scenario and re-runs the perception
+ * phases for it.  An env whose stage is not ready (first steps, bursts) is generated in place by
+ * its CTA — same result, longer tail.  Requires ASVRL_M_DYNAMICS; counter_dev is added to `step`. */
 ASVRL_API int asvrl_env_step_autoreset(const asvrl_env_params* params, const asvrl_env_state* state,
                                        const void* actions, uint64_t seed, uint64_t step,
                                        const asvrl_env_out* out, const asvrl_env_autoreset* ar,

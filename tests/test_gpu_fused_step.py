@@ -1,7 +1,9 @@
-"""The fused step (asvrl_env_step_autoreset: K1 + K1b + first observation in one launch) against
-the three-call sequence it replaces (asvrl_env_step, asvrl_env_reset, masked asvrl_env_step), which
-is itself parity-checked against the oracle in test_gpu_env_step.py / test_gpu_reset_replay.py.
-Everything is compared BIT-exactly: same kernels' arithmetic, same Philox counters."""
+"""The fused step (asvrl_env_step_autoreset: K1 + K1b + first observation in one launch, with or
+without pre-generated next episodes) against the call sequence include/asvrl.h defines it by
+(asvrl_env_step, then per ended env asvrl_env_reset + masked asvrl_env_step with the env's own
+episode number), which is itself parity-checked against the oracle in test_gpu_env_step.py /
+test_gpu_reset_replay.py.  Everything is compared BIT-exactly: same arithmetic, same Philox counters."""
+import numpy as np
 import pytest
 import torch
 
@@ -13,16 +15,41 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def make_pair(E, R, O, C, seed, near_timeout=True):
-    """Two envs in the same state, one fused, one not; some envs one step before the timeout."""
-    a = BatchedMarineNavEnv(E, R, O, C, device=DEV, seed=seed, fused=True)
-    b = BatchedMarineNavEnv(E, R, O, C, device=DEV, seed=seed, fused=False)
+class CallSequence:
+    """The definition of the fused step, spelled out with the separate entry points."""
+
+    def __init__(self, E, R, O, C, seed):
+        self.env = BatchedMarineNavEnv(E, R, O, C, device=DEV, seed=seed, fused=False)
+        self.env.reset()
+        self.idx = np.full((E,), self.env.episode_counter, dtype=np.int64)
+
+    def step(self, act, discrete=False):
+        env = self.env
+        out = env.step_no_reset(act, is_continuous_action=not discrete)
+        trans = {k: out[k].clone() for k in ("reward", "status", "phi", "env_status", "ended",
+                                             "obs_self", "obs_objects", "obs_mask")}
+        for e in np.nonzero(out["ended"].cpu().numpy())[0]:
+            self.idx[e] += 1
+            mask = torch.zeros((env.E,), dtype=torch.uint8, device=DEV)
+            mask[e] = 1
+            n = int(self.idx[e])
+            _lib.env_reset(env.reset_params, env.state, mask, env.want_robots, env.want_cores, env.want_obs,
+                           env.min_start_goal_dis, env.seed, n, env.OP, env.CP, env.env_offset)
+            _lib.env_step(env.params, env.state, None, None, out, 0, env.OP, env.CP,
+                          seed=env.seed ^ env.OBSERVE_SALT, step=n, env_offset=env.env_offset, env_mask=mask)
+        return trans, out
+
+
+def make_pair(E, R, O, C, seed, prefetch=True, spread=13):
+    """A fused env and the call-sequence emulation in the same state; episode clocks are set so
+    that timeouts happen in every one of the next `spread` steps."""
+    a = BatchedMarineNavEnv(E, R, O, C, device=DEV, seed=seed, fused=True, prefetch=prefetch)
     a.reset()
-    b.reset()
-    if near_timeout:
-        for env in (a, b):
-            env.state["ep_steps"][::7] = 1000   # ENV:312: the next step ends these episodes
-            env.state["ep_steps"][3::11] = 999  # and these one step later
+    b = CallSequence(E, R, O, C, seed)
+    clocks = 1000 - (torch.arange(E, device=DEV, dtype=torch.int32) % spread)
+    clocks[1::3] = 0
+    for env in (a, b.env):
+        env.state["ep_steps"].copy_(clocks)
     return a, b
 
 
@@ -30,70 +57,96 @@ def same(x, y):
     return torch.equal(x, y)
 
 
+@pytest.mark.parametrize("prefetch", [False, True])
 @pytest.mark.parametrize("E,R,O,C,discrete", [(512, 8, 10, 8, False), (130, 3, 0, 0, False),
                                               (96, 5, 6, 2, True), (33, 1, 4, 0, False)])
-def test_fused_equals_three_calls(E, R, O, C, discrete):
-    a, b = make_pair(E, R, O, C, seed=11)
+def test_fused_equals_call_sequence(E, R, O, C, discrete, prefetch):
+    a, b = make_pair(E, R, O, C, seed=11, prefetch=prefetch)
     g = torch.Generator(device=DEV).manual_seed(5)
-    n_ended = 0
-    for t in range(6):
+    n_ended = n_staged = 0
+    for t in range(16):
         if discrete:
             act = torch.randint(0, 25, (E, R), device=DEV, generator=g, dtype=torch.int32)
         else:
             act = torch.rand((E, R, 2), device=DEV, generator=g) * 2 - 1
+        if prefetch:
+            tag_before = a.stage_tag.clone()
+            idx_before = a.episode_idx.clone()
         oa = a.step(act, is_continuous_action=not discrete)
-        ob = b.step_no_reset(act, is_continuous_action=not discrete)
-        trans = {k: ob[k].clone() for k in ("reward", "status", "phi", "env_status", "ended",
-                                            "obs_self", "obs_objects", "obs_mask")}
-        b.finish_episodes()
+        trans, ob = b.step(act, discrete)
         torch.cuda.synchronize()
         ended = trans["ended"].bool()
         n_ended += int(ended.sum())
-        # the transition's scalars are kept for every env (the three-call path overwrites them)
-        for k in ("reward", "status", "phi", "env_status", "ended"):
+        if prefetch:  # envs whose stage was ready when the launch began certainly took it
+            n_staged += int((ended & (tag_before == idx_before + 1)).sum())
+        for k in ("reward", "status", "phi", "env_status", "ended"):  # the transition's scalars are kept
             assert same(oa[k], trans[k]), (t, k)
-        # the observation to act on next: fresh for ended envs, the step's own otherwise
-        for k in ("obs_self", "obs_objects", "obs_mask"):
-            assert same(oa[k], b.out[k]), (t, k)
+        for k in ("obs_self", "obs_objects", "obs_mask"):  # what to act on next / the terminal rows
+            assert same(oa[k], ob[k]), (t, k)
             assert same(a.term[k][ended], trans[k][ended]), (t, "term " + k)
         for k, v in a.state.items():
-            assert same(v, b.state[k]), (t, "state " + k)
+            assert same(v, b.env.state[k]), (t, "state " + k)
+        assert np.array_equal(a.episode_idx.cpu().numpy(), b.idx), t
     assert n_ended > 0
+    if prefetch:
+        assert n_staged > 0
+        # the stage of every env that did not just end holds its next episode
+        torch.cuda.synchronize()
+        ok = a.stage_tag == a.episode_idx + 1
+        assert int(ok.sum()) >= E // 2
 
 
-def test_fused_keeps_untouched_term_rows_and_cuda_graph():
-    E, R = 256, 8
-    a, b = make_pair(E, R, 10, 4, seed=3)
-    a.enable_cuda_graph(True)
-    b.enable_cuda_graph(True)
-    g = torch.Generator(device=DEV).manual_seed(9)
-    for t in range(8):
+def test_schedule_change_invalidates_the_stage():
+    E, R = 64, 8
+    a, b = make_pair(E, R, 10, 4, seed=7, spread=5)
+    g = torch.Generator(device=DEV).manual_seed(2)
+    for t in range(10):
+        if t == 3:  # curriculum stage switch (ENV:75-87): fewer robots and buoys from now on
+            a.set_schedule(num_robots=3, num_obs=4, num_cores=2, min_start_goal_dis=20.0)
+            b.env.set_schedule(num_robots=3, num_obs=4, num_cores=2, min_start_goal_dis=20.0)
         act = torch.rand((E, R, 2), device=DEV, generator=g) * 2 - 1
-        a.step_graph(act)
-        b.step_graph(act)
+        a.step(act)
+        b.step(act)
     torch.cuda.synchronize()
     for k, v in a.state.items():
-        assert same(v, b.state[k]), k
-    for k in ("obs_self", "obs_objects", "obs_mask"):
-        assert same(a.out[k], b.out[k]), k
+        assert same(v, b.env.state[k]), k
+    assert int((a.state["n_robots"] == 3).sum()) > 0
+
+
+def test_fused_cuda_graph_equals_eager():
+    E, R = 256, 8
+    a, _ = make_pair(E, R, 10, 4, seed=3)
+    c, _ = make_pair(E, R, 10, 4, seed=3)
+    a.enable_cuda_graph(True)
+    for _ in range(2):  # the two warm-up steps of enable_cuda_graph act on zeros
+        c.step(torch.zeros((E, R, 2), device=DEV))
+    g = torch.Generator(device=DEV).manual_seed(9)
+    for t in range(12):
+        act = torch.rand((E, R, 2), device=DEV, generator=g) * 2 - 1
+        a.step_graph(act)
+        c.step(act)
+    torch.cuda.synchronize()
+    for k, v in a.state.items():
+        assert same(v, c.state[k]), k
+    for k in ("obs_self", "obs_objects", "obs_mask", "reward", "status"):
+        assert same(a.out[k], c.out[k]), k
 
 
 def test_replay_push_reads_terminal_rows():
-    """Ring contents after fused steps == after the three-call sequence with the push in between."""
+    """Ring contents after fused steps == after the call sequence with the push in between."""
     E, R = 200, 8
     a, b = make_pair(E, R, 10, 0, seed=21)
     ra = ReplayBuffer(50000, 64, 5, 5, device=DEV)
     rb = ReplayBuffer(50000, 64, 5, 5, device=DEV)
     g = torch.Generator(device=DEV).manual_seed(1)
-    for t in range(5):
+    for t in range(8):
         act = torch.rand((E, R, 2), device=DEV, generator=g) * 2 - 1
         obs_a = tuple(x.clone() for x in a.obs)
-        obs_b = tuple(x.clone() for x in b.obs)
+        obs_b = tuple(x.clone() for x in b.env.obs)
         oa = a.step_fused(act)
         ra.push_step(obs_a, act, False, oa, term=a.term)
-        ob = b.step_no_reset(act)
-        rb.push_step(obs_b, act, False, ob)
-        b.finish_episodes()
+        trans, ob = b.step(act)
+        rb.push_step(obs_b, act, False, trans)  # the clones taken before the re-generation
     torch.cuda.synchronize()
     assert same(ra.ring["head_size"], rb.ring["head_size"])
     n = int(ra.ring["head_size"][1])
@@ -107,7 +160,8 @@ def test_autoreset_rejects_bad_arguments():
     act = torch.zeros((8, 8, 2), device=DEV)
     with pytest.raises(RuntimeError):  # needs ASVRL_M_DYNAMICS
         _lib.env_step_autoreset(env.params, env.reset_params, env.state, act, env.out, 0, env.OP, env.CP,
-                                env.want_robots, env.want_cores, env.want_obs, env.min_start_goal_dis)
+                                env.want_robots, env.want_cores, env.want_obs, env.min_start_goal_dis,
+                                env.episode_idx)
     with pytest.raises(RuntimeError):  # term without ended
         _lib.replay_push(_lib.new_replay(100, 64, DEV), *env.obs, act, False, env.out["reward"], *env.obs,
                          env.out["status"], term=env.term)

@@ -170,7 +170,8 @@ def run_b200(args):
     # envs partition across ranks with no data-path collective: rank r owns global envs
     # [r*E, (r+1)*E); the RNG counters carry the global index (results invariant to N)
     env = BatchedMarineNavEnv(E, R, O, C, device=dev, seed=args.seed, env_offset=rank * E,
-                              fused=not args.unfused)
+                              fused=not args.unfused,
+                              prefetch={"stream": "stream", "workers": "workers", "off": False}[args.prefetch])
     env.reset()
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     if not args.no_stagger:
@@ -233,6 +234,18 @@ def run_b200(args):
     barrier()
     step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
     launches = env.launches - launches0
+
+    # cross-check without the flush gaps: K steps back to back, the side stream joined at the end
+    b2b0, b2b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    b2b0.record()
+    for i in range(K):
+        env.step(pool[i % 8]) if env.fused else env.step_graph(pool[i % 8])
+    if getattr(env, "prefetch", None) == "stream":
+        torch.cuda.current_stream().wait_stream(env._side)
+    b2b1.record()
+    barrier()
+    b2b_ms = b2b0.elapsed_time(b2b1) / K
 
     # ---- (3) e2e: host buffers in, host buffers out, through the public API ----
     host_actions = [p.cpu().pin_memory() for p in pool]
@@ -314,6 +327,11 @@ def run_b200(args):
                                       if env.fused else "one CUDA graph per step (K1, K1b, masked K1)"),
                        "envs_per_gpu": E, "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
                        "episode_clocks": "synchronised" if args.no_stagger else "staggered over [0,1000): ~E/1000 resets per step",
+                       "next_episodes": (f"pre-generated on a side stream every {env.prefetch_every} steps "
+                                         "(asvrl_env_stage_refill)" if getattr(env, "prefetch", None) == "stream"
+                                         else "pre-generated by refill CTAs of the step launch"
+                                         if getattr(env, "prefetch", None) == "workers" else "generated in place"),
+                       "back_to_back_ms_per_step": b2b_ms,
                        "l2": "flushed between timed steps (256 MiB write)", "parallelism": f"envs sharded x{world}, no collective"},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
                     "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": E * R * 39 * 4},
@@ -378,6 +396,7 @@ def main():
     ap.add_argument("--cpu-envs", type=int, default=2048)
     ap.add_argument("--cpu-steps", type=int, default=2000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--prefetch", default="stream", choices=["stream", "workers", "off"])
     ap.add_argument("--no-stagger", action="store_true", help="start every episode clock at 0")
     ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
     args = ap.parse_args()

@@ -156,4 +156,6 @@ class EnvAutoReset(C.Structure):
                 ("min_start_goal_dis", C.c_void_p), ("episode_idx", C.c_void_p),
                 ("observe_seed", C.c_uint64), ("term_self", C.c_void_p),
                 ("term_objects", C.c_void_p), ("term_mask", C.c_void_p),
-                ("stage", C.POINTER(EnvStatePtrs)), ("stage_tag", C.c_void_p)]
+                ("stage", C.POINTER(EnvStatePtrs)), ("stage_tag", C.c_void_p),
+                ("stage_self", C.c_void_p), ("stage_objects", C.c_void_p), ("stage_mask", C.c_void_p),
+                ("refill_in_launch", C.c_int32), ("reserved", C.c_int32)]

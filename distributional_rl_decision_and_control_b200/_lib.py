@@ -24,7 +24,7 @@ _SIGNATURES = {
     "asvrl_reset_default_params": (None, [C.c_void_p]),
     "asvrl_env_step": (C.c_int, [C.POINTER(_abi.EnvParams), C.POINTER(_abi.EnvStatePtrs), vp, f32p,
                                  u8p, C.c_uint64, C.c_uint64, C.POINTER(_abi.EnvOutPtrs), C.c_int,
-                                 C.c_int, C.c_int, C.c_int, C.c_int64, C.c_uint32, u64p, vp]),
+                                 C.c_int, C.c_int, C.c_int, C.c_int64, C.c_uint32, u64p, i32p, vp]),
     "asvrl_env_step_autoreset": (C.c_int, [C.POINTER(_abi.EnvParams), C.POINTER(_abi.EnvStatePtrs), vp,
                                            C.c_uint64, C.c_uint64, C.POINTER(_abi.EnvOutPtrs),
                                            C.POINTER(_abi.EnvAutoReset), C.c_int, C.c_int, C.c_int,
@@ -33,7 +33,11 @@ _SIGNATURES = {
                                   C.c_int, C.c_int, C.c_int64, f32p, vp]),
     "asvrl_env_reset": (C.c_int, [C.c_void_p, C.POINTER(_abi.EnvStatePtrs), u8p, i32p, i32p, i32p,
                                   f32p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
-                                  C.c_int64, u64p, vp]),
+                                  C.c_int64, u64p, i32p, vp]),
+    "asvrl_env_stage_refill": (C.c_int, [C.POINTER(_abi.EnvParams), C.c_void_p, C.POINTER(_abi.EnvStatePtrs),
+                                         C.POINTER(_abi.EnvOutPtrs), i32p, i32p, i32p, f32p, i32p, i32p,
+                                         u8p, i32p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int,
+                                         C.c_int, C.c_int64, vp]),
     "asvrl_replay_push": (C.c_int, [f32p, C.c_int64, u64p, f32p, f32p, f32p, vp, C.c_int, f32p,
                                     f32p, f32p, f32p, u32p, C.c_int, u32p, f32p, f32p, f32p, u8p,
                                     C.c_int, vp]),
@@ -178,7 +182,8 @@ def new_out(E, RP, device, debug=True, pin=False):
 
 
 def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, step=0,
-             env_offset=0, env_mask=None, st_ptrs=None, o_ptrs=None, counter_dev=None):
+             env_offset=0, env_mask=None, st_ptrs=None, o_ptrs=None, counter_dev=None,
+             step_per_env=None):
     E, RP = st["x"].shape
     if actions is not None:
         want = torch.int32 if (mode & _abi.M_DISCRETE) else torch.float32
@@ -189,15 +194,16 @@ def env_step(params, st, actions, noise, out, mode, max_obs, max_cores, seed=0, 
     op = o_ptrs if o_ptrs is not None else out_ptrs(out)
     rc = lib().asvrl_env_step(C.byref(params), C.byref(sp), a_ptr, ptr(noise, torch.float32),
                               ptr(env_mask, torch.uint8), seed, step, C.byref(op), E, RP, max_obs,
-                              max_cores, env_offset, mode, ptr(counter_dev, torch.int64), stream_ptr())
+                              max_cores, env_offset, mode, ptr(counter_dev, torch.int64),
+                              ptr(step_per_env, torch.int32), stream_ptr())
     check(rc, "asvrl_env_step")
     return out
 
 
 def env_step_autoreset(params, rparams, st, actions, out, mode, max_obs, max_cores, want_robots,
                        want_cores, want_obs, min_sg, episode_idx, seed=0, step=0, observe_seed=0,
-                       term=None, stage_ptrs=None, stage_tag=None, env_offset=0, st_ptrs=None,
-                       o_ptrs=None, counter_dev=None):
+                       term=None, stage_ptrs=None, stage_tag=None, stage_obs=None, refill_in_launch=True,
+                       env_offset=0, st_ptrs=None, o_ptrs=None, counter_dev=None):
     """K1 + K1b + first observation in one launch (asvrl_env_step_autoreset).  ``episode_idx`` =
     int32 [E] per-env episode counters (in/out); ``term`` = dict with obs_self / obs_objects /
     obs_mask tensors that receive the terminal rows of ended envs; ``stage_ptrs`` (state_ptrs of a
@@ -217,6 +223,11 @@ def env_step_autoreset(params, rparams, st, actions, out, mode, max_obs, max_cor
     if stage_ptrs is not None:
         ar.stage = C.pointer(stage_ptrs)
         ar.stage_tag = ptr(stage_tag, torch.int32)
+        ar.refill_in_launch = 1 if refill_in_launch else 0
+        if stage_obs is not None:  # the staged first observation (asvrl_env_stage_refill's output)
+            ar.stage_self = ptr(stage_obs["obs_self"], torch.float32)
+            ar.stage_objects = ptr(stage_obs["obs_objects"], torch.float32)
+            ar.stage_mask = ptr(stage_obs["obs_mask"], torch.float32)
     if term is not None:
         ar.term_self = ptr(term["obs_self"], torch.float32)
         ar.term_objects = ptr(term["obs_objects"], torch.float32)
@@ -237,15 +248,30 @@ def env_noise(params, seed, step, E, RP, OP, device, env_offset=0):
 
 
 def env_reset(rparams, st, reset_mask, want_robots, want_cores, want_obs, min_sg, seed, episode,
-              max_obs, max_cores, env_offset=0, st_ptrs=None, counter_dev=None):
+              max_obs, max_cores, env_offset=0, st_ptrs=None, counter_dev=None, episode_per_env=None):
     E, RP = st["x"].shape
     sp = st_ptrs if st_ptrs is not None else state_ptrs(st)
     rc = lib().asvrl_env_reset(C.byref(rparams), C.byref(sp), ptr(reset_mask, torch.uint8),
                                ptr(want_robots, torch.int32), ptr(want_cores, torch.int32),
                                ptr(want_obs, torch.int32), ptr(min_sg, torch.float32), seed, episode,
                                E, RP, max_obs, max_cores, env_offset, ptr(counter_dev, torch.int64),
-                               stream_ptr())
+                               ptr(episode_per_env, torch.int32), stream_ptr())
     check(rc, "asvrl_env_reset")
+
+
+def env_stage_refill(params, rparams, stage_ptrs, stage_out_ptrs, want_robots, want_cores, want_obs, min_sg,
+                     episode_idx, stage_tag, need_ws, episode_ws, seed, observe_seed, E, RP, max_obs,
+                     max_cores, env_offset=0, stream=None):
+    """asvrl_env_stage_refill on ``stream`` (a torch.cuda.Stream; default: the current one)."""
+    sp = stream.cuda_stream if stream is not None else stream_ptr()
+    rc = lib().asvrl_env_stage_refill(C.byref(params), C.byref(rparams), C.byref(stage_ptrs),
+                                      C.byref(stage_out_ptrs), ptr(want_robots, torch.int32),
+                                      ptr(want_cores, torch.int32), ptr(want_obs, torch.int32),
+                                      ptr(min_sg, torch.float32), ptr(episode_idx, torch.int32),
+                                      ptr(stage_tag, torch.int32), ptr(need_ws, torch.uint8),
+                                      ptr(episode_ws, torch.int32), seed, observe_seed & 0xFFFFFFFFFFFFFFFF,
+                                      E, RP, max_obs, max_cores, env_offset, sp)
+    check(rc, "asvrl_env_stage_refill")
 
 
 def qhuber_fwd_bwd(z, tau, z_next, r, done, gamma, kappa, workspace, lps=None, grad=None, loss=None):

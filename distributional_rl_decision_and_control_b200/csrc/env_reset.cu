@@ -22,7 +22,8 @@ env_reset_kernel(const __grid_constant__ ResetConsts k, ResetState st,
                  const uint8_t* __restrict__ reset_mask, const int32_t* __restrict__ want_robots,
                  const int32_t* __restrict__ want_cores, const int32_t* __restrict__ want_obs,
                  const float* __restrict__ min_sg, uint64_t seed, uint64_t episode, int E, int RP,
-                 int OP, int CP, int64_t env_offset, const uint64_t* __restrict__ counter_dev) {
+                 int OP, int CP, int64_t env_offset, const uint64_t* __restrict__ counter_dev,
+                 const int32_t* __restrict__ episode_arr) {
   __shared__ float4 s_sg[RS_WARPS][RS_MAXR];    // start.xy, goal.xy
   __shared__ float4 s_core[RS_WARPS][RS_MAXC];  // x, y, +-1, Gamma
   __shared__ float4 s_obs[RS_WARPS][RS_MAXO];   // x, y, r, 0
@@ -31,6 +32,7 @@ env_reset_kernel(const __grid_constant__ ResetConsts k, ResetState st,
   if (e >= E) return;
   if (reset_mask && !reset_mask[e]) return;
   if (counter_dev) episode += *counter_dev;
+  if (episode_arr) episode = (uint64_t)episode_arr[e];  // per-env episode numbers (staging)
   reset_env_warp(k, st, e, env_offset + e, want_robots[e], want_cores[e], want_obs[e], min_sg[e], seed,
                  episode, RP, OP, CP, s_sg[warp], s_core[warp], s_obs[warp], lane);
 }
@@ -52,7 +54,8 @@ extern "C" int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env
                                const int32_t* want_cores, const int32_t* want_obs,
                                const float* min_start_goal_dis, uint64_t seed, uint64_t episode,
                                int n_envs, int max_robots, int max_obs, int max_cores,
-                               int64_t env_offset, const uint64_t* counter_dev, void* stream) {
+                               int64_t env_offset, const uint64_t* counter_dev,
+                               const int32_t* episode_per_env, void* stream) {
   if (!params || !state || !want_robots || !want_cores || !want_obs || !min_start_goal_dis)
     return fail(ASVRL_E_BADARG, "asvrl_env_reset: null argument");
   if (n_envs < 0 || max_robots < 1 || max_obs < 0 || max_cores < 0)
@@ -70,6 +73,58 @@ extern "C" int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env
   const int grid = (n_envs + RS_WARPS - 1) / RS_WARPS;
   env_reset_kernel<<<grid, RS_WARPS * 32, 0, (cudaStream_t)stream>>>(
       k, st, reset_mask, want_robots, want_cores, want_obs, min_start_goal_dis, seed, episode,
-      n_envs, max_robots, max_obs, max_cores, env_offset, counter_dev);
+      n_envs, max_robots, max_obs, max_cores, env_offset, counter_dev, episode_per_env);
   return check_launch("asvrl_env_reset");
+}
+
+// ---- staging of next episodes on a side stream (asvrl_env_stage_refill) ----
+namespace asvrl {
+
+// need[e] = the stage of env e does not hold its next episode; ep[e] = that episode's number
+__global__ void stage_begin_kernel(const int32_t* __restrict__ episode_idx, const int32_t* stage_tag,
+                                   uint8_t* __restrict__ need, int32_t* __restrict__ ep, int E) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  const int n = __ldcg(episode_idx + e) + 1;
+  int tag;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(tag) : "l"(stage_tag + e) : "memory");
+  need[e] = tag != n;
+  ep[e] = n;
+}
+
+// the data kernels before this one in the stream have completed: publish the tags
+__global__ void stage_publish_kernel(const uint8_t* __restrict__ need, const int32_t* __restrict__ ep,
+                                     int32_t* stage_tag, int E) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E || !need[e]) return;
+  __threadfence();
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(stage_tag + e), "r"(ep[e]) : "memory");
+}
+
+}  // namespace asvrl
+
+extern "C" int asvrl_env_stage_refill(const asvrl_env_params* params, const asvrl_reset_params* rparams,
+                                      const asvrl_env_state* stage, const asvrl_env_out* stage_out,
+                                      const int32_t* want_robots, const int32_t* want_cores,
+                                      const int32_t* want_obs, const float* min_start_goal_dis,
+                                      const int32_t* episode_idx, int32_t* stage_tag, uint8_t* need_ws,
+                                      int32_t* episode_ws, uint64_t seed, uint64_t observe_seed,
+                                      int n_envs, int max_robots, int max_obs, int max_cores,
+                                      int64_t env_offset, void* stream) {
+  if (!params || !rparams || !stage || !stage_out || !episode_idx || !stage_tag || !need_ws || !episode_ws)
+    return fail(ASVRL_E_BADARG, "asvrl_env_stage_refill: null argument");
+  if (n_envs <= 0) return n_envs == 0 ? 0 : fail(ASVRL_E_BADARG, "asvrl_env_stage_refill: bad sizes");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = (n_envs + 255) / 256;
+  stage_begin_kernel<<<grid, 256, 0, s>>>(episode_idx, stage_tag, need_ws, episode_ws, n_envs);
+  int rc = check_launch("asvrl_env_stage_refill(begin)");
+  if (rc) return rc;
+  rc = asvrl_env_reset(rparams, stage, need_ws, want_robots, want_cores, want_obs, min_start_goal_dis, seed,
+                       0, n_envs, max_robots, max_obs, max_cores, env_offset, nullptr, episode_ws, stream);
+  if (rc) return rc;
+  rc = asvrl_env_step(params, stage, nullptr, nullptr, need_ws, observe_seed, 0, stage_out, n_envs, max_robots,
+                      max_obs, max_cores, env_offset, 0u, nullptr, episode_ws, stream);
+  if (rc) return rc;
+  stage_publish_kernel<<<grid, 256, 0, s>>>(need_ws, episode_ws, stage_tag, n_envs);
+  return check_launch("asvrl_env_stage_refill(publish)");
 }

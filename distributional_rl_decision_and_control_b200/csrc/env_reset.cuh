@@ -94,11 +94,29 @@ __device__ __forceinline__ int resolve_round(unsigned okm, float4 c, float4* set
   return n;
 }
 
+// One shared, rolled Philox for the scenario generator: it runs in a single warp, mostly with a cold
+// instruction cache (once per episode), so code bytes cost more than a call and a loop counter.
+static __device__ __noinline__ uint4 philox_reset(uint64_t seed, uint64_t episode, int64_t env, uint32_t cls,
+                                           uint32_t t) {
+  uint4 c = make_uint4((t & 255u) | ((t >> 8) << 8) | (cls << 16), (uint32_t)env, (uint32_t)episode,
+                       ((uint32_t)(episode >> 32) & 0x00FFFFFFu) | ((uint32_t)STREAM_RESET << 24));
+  uint2 k = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll 1
+  for (int round = 0; round < 10; ++round) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
 // ---- candidate t of each class (Philox stream 2, counters as documented in env_reset.cu) and the
 // part of its acceptance test that does not involve the class's own accepted set ----
 __device__ __forceinline__ float4 robot_candidate(const ResetConsts& k, uint64_t seed, uint64_t episode,
                                                   int64_t ge, int t) {  // ENV:108-110
-  const uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 0u, (uint32_t)t >> 8, (uint32_t)t & 255u);
+  const uint4 w = philox_reset(seed, episode, ge, 0u, (uint32_t)t);
   const float lo = k.start_margin;
   return make_float4(lerp_u(lo, k.map_w - lo, u01(w.x)), lerp_u(lo, k.map_h - lo, u01(w.y)),
                      lerp_u(lo, k.map_w - lo, u01(w.z)), lerp_u(lo, k.map_h - lo, u01(w.w)));
@@ -110,7 +128,7 @@ __device__ __forceinline__ bool robot_ok(float4 c, float min_dis) {  // ENV:361
 __device__ __forceinline__ float4 core_candidate(const ResetConsts& k, uint64_t seed, uint64_t episode,
                                                  int64_t ge, int t) {  // ENV:125-129
   const float TWO_PI = 6.28318530717959f;
-  const uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 1u, (uint32_t)t >> 8, (uint32_t)t & 255u);
+  const uint4 w = philox_reset(seed, episode, ge, 1u, (uint32_t)t);
   const float dir = (w.z >> 31) ? 1.0f : -1.0f;  // binomial(1, 0.5), ENV:127
   return make_float4(k.map_w * u01(w.x), k.map_h * u01(w.y), dir,
                      TWO_PI * k.core_r * lerp_u(k.v_min, k.v_max, u01(w.w)));
@@ -119,6 +137,7 @@ __device__ __forceinline__ bool core_ok(const ResetConsts& k, float4 c, const fl
   bool bad = (c.x - k.core_r < 0.0f) | (c.x + k.core_r > k.map_w);   // ENV:381
   bad |= (c.y - k.core_r < 0.0f) | (c.y + k.core_r > k.map_w);       // ENV:383 (sic: width)
   const float lim = k.core_r + k.clear_r, lim2 = lim * lim;
+#pragma unroll 4
   for (int i = 0; i < n_r; ++i) {                                    // ENV:386-394
     const float4 o = sg[i];
     bad |= (sqd(c.x, c.y, o.x, o.y) < lim2) | (sqd(c.x, c.y, o.z, o.w) < lim2);
@@ -128,7 +147,7 @@ __device__ __forceinline__ bool core_ok(const ResetConsts& k, float4 c, const fl
 
 __device__ __forceinline__ float4 obs_candidate(const ResetConsts& k, uint64_t seed, uint64_t episode,
                                                 int64_t ge, int t) {  // ENV:153-155
-  const uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 2u, (uint32_t)t >> 8, (uint32_t)t & 255u);
+  const uint4 w = philox_reset(seed, episode, ge, 2u, (uint32_t)t);
   const float lo = k.obs_margin;
   return make_float4(lerp_u(lo, k.map_w - lo, u01(w.x)), lerp_u(lo, k.map_h - lo, u01(w.y)),
                      lerp_u(k.obs_r_min, k.obs_r_max, u01(w.z)), 0.0f);
@@ -138,10 +157,12 @@ __device__ __forceinline__ bool obs_ok(const ResetConsts& k, float4 c, const flo
   const float cx = c.x, cy = c.y, rr = c.z;
   bool bad = (cx - rr < 0.0f) | (cx + rr > k.map_w) | (cy - rr < 0.0f) | (cy + rr > k.map_h);
   const float lim = rr + k.clear_r, lim2 = lim * lim, lc = k.core_r + rr, lc2 = lc * lc;
+#pragma unroll 4
   for (int i = 0; i < n_r; ++i) {  // ENV:428-436
     const float4 o = sg[i];
     bad |= (sqd(cx, cy, o.x, o.y) < lim2) | (sqd(cx, cy, o.z, o.w) < lim2);
   }
+#pragma unroll 4
   for (int i = 0; i < n_c; ++i)    // ENV:439-445
     bad |= sqd(cores[i].x, cores[i].y, cx, cy) <= lc2;
   return !bad;
@@ -159,7 +180,7 @@ __device__ __forceinline__ void write_episode(const ResetState& st, int e, int64
     float4 c = on ? sg[r] : make_float4(0, 0, 0, 0);
     float th = 0.0f;
     if (on) {  // init_theta ~ U(0, 2 pi), ENV:171
-      uint4 w = philox_at(seed, STREAM_RESET, episode, ge, 3u, (uint32_t)r, 0u);
+      uint4 w = philox_reset(seed, episode, ge, 3u, (uint32_t)r << 8);
       th = fminf(TWO_PI * u01(w.x), 6.2831850f);
     }
     st.x[g] = c.x; st.y[g] = c.y; st.theta[g] = th;
@@ -211,6 +232,7 @@ __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const Reset
     const int t = base + lane;
     const float4 c = robot_candidate(k, seed, episode, ge, t);
     bool ok = t < k.max_tries && robot_ok(c, min_dis);
+#pragma unroll 4
     for (int i = 0; i < n_r; ++i) ok &= !sg_conflict(k, c, sg[i]);
     n_r = resolve_round(__ballot_sync(FULL, ok), c, sg, n_r, want_r, lane,
                         [&](float4 a, float4 b) { return sg_conflict(k, a, b); });
@@ -222,6 +244,7 @@ __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const Reset
     const int t = base + lane;
     const float4 c = core_candidate(k, seed, episode, ge, t);
     bool ok = t < k.max_tries && core_ok(k, c, sg, n_r);
+#pragma unroll 4
     for (int i = 0; i < n_c; ++i) ok &= !core_conflict(k, c, cores[i]);  // ENV:396-416
     n_c = resolve_round(__ballot_sync(FULL, ok), c, cores, n_c, want_c, lane,
                         [&](float4 a, float4 b) { return core_conflict(k, a, b); });
@@ -233,6 +256,7 @@ __device__ __forceinline__ void reset_env_warp(const ResetConsts& k, const Reset
     const int t = base + lane;
     const float4 c = obs_candidate(k, seed, episode, ge, t);
     bool ok = t < k.max_tries && obs_ok(k, c, sg, n_r, cores, n_c);
+#pragma unroll 4
     for (int i = 0; i < n_o; ++i) ok &= !obs_conflict(c, obs[i]);  // ENV:448-454
     n_o = resolve_round(__ballot_sync(FULL, ok), c, obs, n_o, want_o, lane,
                         [&](float4 a, float4 b) { return obs_conflict(a, b); });
@@ -260,6 +284,7 @@ __device__ __forceinline__ int place_class_cta(int want, int max_tries, float4* 
     const int t = base + tid;
     const float4 c = gen(t);
     bool ok = t < max_tries && fixed_ok(c);
+#pragma unroll 4
     for (int i = 0; i < n; ++i) ok &= !conflict(c, set[i]);
     sc.cand[tid] = c;
     const unsigned b = __ballot_sync(FULL, ok);

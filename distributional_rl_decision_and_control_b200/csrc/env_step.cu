@@ -64,7 +64,10 @@ struct FusedArgs {
   // pre-generated next episodes (nullable): stage state + stage_tag[e] = episode number it holds
   ResetState stage;
   int32_t* stage_tag;
+  const float *stage_self, *stage_objects, *stage_mask;  // staged FIRST observation rows (nullable)
   int n_workers;         // leading CTAs of the grid that only refill the stage
+  // any variant: nullable per-env RNG step of the sensor noise (replaces `step` for that env)
+  const int32_t* step_arr;
 };
 
 __device__ __forceinline__ int ld_acquire(const int32_t* p) {
@@ -321,6 +324,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     m.no[tid] = v ? min(st.n_obs[e], OP) : 0;
     m.nc[tid] = v ? min(st.n_cores[e], CP) : 0;
     m.ep[tid] = v ? st.ep_steps[e] : 0;
+    if (!second && fa.step_arr) m.epn[tid] = v ? fa.step_arr[e] : 0;
   }
   if (!second) {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
     const int e = e0 + tid;
@@ -527,7 +531,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       if (i < n_pairs) {
         const int pr = m.plist[i], a = pr >> 6, sl = pr & 63;
         const int el = m.el_of[a];
-        const NoiseDraw nd = sensor_noise(k, seed, (FUSED && second) ? (uint64_t)m.epn[el] : step,
+        const NoiseDraw nd = sensor_noise(k, seed, ((FUSED && second) || fa.step_arr) ? (uint64_t)m.epn[el] : step,
                                           env_offset + e0 + el, (uint32_t)m.r_of[a], (uint32_t)sl);
         float* np = m.cand + (a * S + sl) * 5;
 #pragma unroll
@@ -774,18 +778,28 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
         const int how = m.ended[el];
         if (!how) continue;
         const int e = e0 + el;
-        if (how == 2)
+        if (how == 2) {
           take_stage(rs, fa.stage, e, RP, OP, CP, tid, TPB);
-        else
+          if (fa.stage_self) {  // its first observation was staged too: nothing left to compute
+            const size_t b0 = a0 + (size_t)el * RP;
+            for (int i = tid; i < RP * 25; i += TPB) out.obs_objects[b0 * 25 + i] = __ldcg(fa.stage_objects + b0 * 25 + i);
+            for (int i = tid; i < RP * 7; i += TPB) out.obs_self[b0 * 7 + i] = __ldcg(fa.stage_self + b0 * 7 + i);
+            for (int i = tid; i < RP * 5; i += TPB) out.obs_mask[b0 * 5 + i] = __ldcg(fa.stage_mask + b0 * 5 + i);
+          }
+        } else
           reset_env_cta(fa.rk, rs, e, env_offset + e, fa.want_robots[e], fa.want_cores[e], fa.want_obs[e],
                         fa.min_sg[e], seed, (uint64_t)m.epn[el], RP, OP, CP, m.rs_sg, m.rs_core, m.rs_obs,
                         sc, tid);
       }
       __syncthreads();  // the stage has been read: only now may a worker see the bumped counter
+      int observe = 0;
       if (tid < EPB && m.ended[tid]) {
         __threadfence();
         fa.episode_idx[e0 + tid] = m.epn[tid];
+        if (fa.stage_self && m.ended[tid] == 2) m.ended[tid] = 0;  // observed already
+        observe = m.ended[tid];
       }
+      if (!__syncthreads_or(observe)) return;
       second = true;
       dyn = false;
       mode = 0;
@@ -891,7 +905,8 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
                               const void* actions, const float* noise, const uint8_t* env_mask,
                               uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,
                               int max_robots, int max_obs, int max_cores, int64_t env_offset,
-                              uint32_t mode, const uint64_t* counter_dev, void* stream) {
+                              uint32_t mode, const uint64_t* counter_dev, const int32_t* step_per_env,
+                              void* stream) {
   if (!params || !state || !out) return fail(ASVRL_E_BADARG, "asvrl_env_step: null struct");
   if (n_envs < 0 || max_robots < 1 || max_obs < 0 || max_cores < 0)
     return fail(ASVRL_E_BADARG, "asvrl_env_step: bad sizes");
@@ -925,6 +940,7 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
   }
   FusedArgs fa;
   memset(&fa, 0, sizeof fa);
+  fa.step_arr = step_per_env;
   kern<<<grid, TPB, smem, s>>>(k, L, st, actions, noise, env_mask, seed, step, o, n_envs, max_robots, max_obs,
                                max_cores, env_offset, mode, EPB, counter_dev, fa);
   return check_launch("asvrl_env_step");
@@ -974,6 +990,8 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
   fa.episode_idx = ar->episode_idx;
   fa.stage_tag = nullptr;
   fa.n_workers = 0;
+  fa.step_arr = nullptr;
+  fa.stage_self = fa.stage_objects = fa.stage_mask = nullptr;
   memset(&fa.stage, 0, sizeof fa.stage);
   if (ar->stage) {
     const asvrl_env_state* g = ar->stage;
@@ -986,6 +1004,11 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
                           g->thrust_l, g->thrust_r, g->goal_x, g->goal_y, g->flags, g->n_robots, g->n_obs,
                           g->n_cores, g->ep_steps, (float4*)g->obstacles, (float4*)g->cores};
     fa.stage_tag = ar->stage_tag;
+    if (ar->stage_self || ar->stage_objects || ar->stage_mask) {
+      if (!(ar->stage_self && ar->stage_objects && ar->stage_mask))
+        return fail(ASVRL_E_BADARG, "asvrl_env_step_autoreset: stage_self/objects/mask must be all set or all NULL");
+      fa.stage_self = ar->stage_self; fa.stage_objects = ar->stage_objects; fa.stage_mask = ar->stage_mask;
+    }
   }
   fa.term_self = ar->term_self; fa.term_objects = ar->term_objects; fa.term_mask = ar->term_mask;
   const int EPB = pick_epb(max_robots);
@@ -997,7 +1020,7 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step_autoreset: %zu B shared memory: %s", smem, cudaGetErrorString(e));
   }
-  if (fa.stage_tag) {
+  if (fa.stage_tag && ar->refill_in_launch) {
     // refill workers take the CTA slots the last wave of step CTAs leaves free (4..16 of them)
     int dev = 0, sms = 0, per_sm = 0;
     cudaGetDevice(&dev);

@@ -24,7 +24,7 @@ class BatchedMarineNavEnv:
     def __init__(self, n_envs, num_robots=8, num_obs=10, num_cores=0, min_start_goal_dis=30.0,
                  device="cuda:0", seed=0, env_offset=0, max_robots=None, max_obs=None,
                  max_cores=None, params=None, reset_params=None, debug_outputs=False, fused=True,
-                 prefetch=True):
+                 prefetch="stream", prefetch_every=2):
         _lib.lib()  # fail loudly if the CUDA library is missing
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -58,11 +58,29 @@ class BatchedMarineNavEnv:
             # per-env episode counters: the scenario RNG counter of env e's next episode is idx[e] + 1
             self.episode_idx = torch.zeros((self.E,), dtype=torch.int32, device=self.device)
             # pre-generated next episodes (a second state block + the episode number each holds)
-            self.stage = self.stage_tag = self._stage_ptrs = None
-            if fused and prefetch:
+            #   prefetch="stream":  asvrl_env_stage_refill on a low-priority side stream every
+            #                       `prefetch_every` steps: scenario AND first observation staged, the
+            #                       step never waits for a generation that is ready in time
+            #   prefetch="workers": extra CTAs of the fused launch itself stage the scenario (no second
+            #                       stream: what a captured CUDA graph of the step uses)
+            #   prefetch=False:     ended envs are always re-generated in place by their CTA
+            if prefetch is True:
+                prefetch = "stream"
+            if prefetch not in (False, None, "stream", "workers"):
+                raise ValueError("prefetch must be False, 'stream' or 'workers'")
+            self.prefetch = prefetch if fused else False
+            self.prefetch_every = max(1, int(prefetch_every))
+            self.stage = self.stage_tag = self._stage_ptrs = self.stage_out = None
+            if self.prefetch:
                 self.stage = _lib.new_state(self.E, self.RP, self.OP, self.CP, self.device)
                 self._stage_ptrs = _lib.state_ptrs(self.stage)
                 self.stage_tag = torch.zeros((self.E,), dtype=torch.int32, device=self.device)
+                self.stage_out = _lib.new_out(self.E, self.RP, self.device, debug=False)
+                self._stage_out_ptrs = _lib.out_ptrs(self.stage_out)
+                self._need_ws = torch.zeros((self.E,), dtype=torch.uint8, device=self.device)
+                self._ep_ws = torch.zeros((self.E,), dtype=torch.int32, device=self.device)
+                self._side = torch.cuda.Stream(device=self.device, priority=0)  # lowest priority
+                self._since_refill = 0
         self.fused = bool(fused)  # step(auto_reset=True) = ONE launch (asvrl_env_step_autoreset)
         self.launches = 0
         # optional int64 device word added to both RNG counters on the device: a captured CUDA
@@ -82,7 +100,11 @@ class BatchedMarineNavEnv:
         if min_start_goal_dis is not None:
             self.min_start_goal_dis.fill_(float(min_start_goal_dis))
         if self.stage_tag is not None:
-            self.stage_tag.zero_()  # staged episodes were generated for the previous stage
+            # staged episodes were generated for the previous stage; a refill still in flight on the
+            # side stream must not publish after the tags are cleared
+            if self.prefetch == "stream":
+                torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self.stage_tag.zero_()
 
     # ------------------------------------------------------------------ views
     @property
@@ -115,7 +137,25 @@ class BatchedMarineNavEnv:
         # every env now holds episode number `episode_counter`; fused steps count on from there
         # (episode_counter also grows by one per fused step, an upper bound of every idx)
         self.episode_idx.fill_(self.episode_counter)
+        if self.prefetch == "stream":
+            self.refill_stage(wait=True)
         return self.obs
+
+    def refill_stage(self, wait=False):
+        """Enqueue asvrl_env_stage_refill on the side stream: every env whose stage does not hold
+        its next episode gets scenario + first observation generated beside the steps."""
+        with torch.cuda.device(self.device):
+            main = torch.cuda.current_stream(self.device)
+            self._side.wait_stream(main)  # counters / schedule written so far are visible
+            _lib.env_stage_refill(self.params, self.reset_params, self._stage_ptrs, self._stage_out_ptrs,
+                                  self.want_robots, self.want_cores, self.want_obs, self.min_start_goal_dis,
+                                  self.episode_idx, self.stage_tag, self._need_ws, self._ep_ws, self.seed,
+                                  self.seed ^ self.OBSERVE_SALT, self.E, self.RP, self.OP, self.CP,
+                                  self.env_offset, stream=self._side)
+            self.launches += 4
+            if wait:
+                main.wait_stream(self._side)
+        self._since_refill = 0
 
     def step(self, actions, is_continuous_action=True, auto_reset=True):
         """One action for every ASV of every env.
@@ -154,10 +194,16 @@ class BatchedMarineNavEnv:
                                     seed=self.seed, step=self.total_steps,
                                     observe_seed=self.seed ^ self.OBSERVE_SALT, term=self.term,
                                     stage_ptrs=self._stage_ptrs, stage_tag=self.stage_tag,
+                                    stage_obs=self.stage_out if self.prefetch == "stream" else None,
+                                    refill_in_launch=self.prefetch == "workers",
                                     env_offset=self.env_offset, st_ptrs=self._st_ptrs,
                                     o_ptrs=self._o_ptrs[nxt], counter_dev=self.counter_dev)
             self.launches += 1
         self._cur = nxt
+        if self.prefetch == "stream" and not torch.cuda.is_current_stream_capturing():
+            self._since_refill += 1
+            if self._since_refill >= self.prefetch_every:
+                self.refill_stage()
         return self._outs[nxt]
 
     def step_no_reset(self, actions, is_continuous_action=True):
@@ -185,6 +231,9 @@ class BatchedMarineNavEnv:
         into the two graphs differ by one and a device word advances them by two per pair of
         replays, so every replay draws fresh noise and fresh scenarios."""
         dev = self.device
+        if self.prefetch == "stream":
+            self.prefetch = "workers"  # a captured step cannot fork to the side stream: refill in the launch
+            torch.cuda.synchronize(dev)
         with torch.cuda.device(dev):
             self.counter_dev = torch.zeros((1,), dtype=torch.int64, device=dev)
             shape, dt = ((self.E, self.RP, 2), torch.float32) if is_continuous_action else ((self.E, self.RP), torch.int32)

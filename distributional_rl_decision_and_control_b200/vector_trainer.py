@@ -87,6 +87,9 @@ class VectorTrainer:
     def _capture_collect(self):
         env = self.env
         dev = env.device
+        if getattr(env, "prefetch", None) == "stream":
+            env.prefetch = "workers"  # a captured step refills the stage inside its own launch
+            torch.cuda.synchronize(dev)
         with torch.cuda.device(dev):
             env.counter_dev = torch.zeros((1,), dtype=torch.int64, device=dev)
             side = torch.cuda.Stream(device=dev)

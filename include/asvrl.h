@@ -205,7 +205,10 @@ ASVRL_API int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_sta
                              const void* actions, const float* noise, const uint8_t* env_mask,
                              uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,
                              int max_robots, int max_obs, int max_cores, int64_t env_offset,
-                             uint32_t mode, const uint64_t* counter_dev, void* stream);
+                             uint32_t mode, const uint64_t* counter_dev,
+                             const int32_t* step_per_env /* nullable [E]: RNG step of env e's sensor
+                                                            noise instead of `step` */,
+                             void* stream);
 
 /* The noise table the NULL-noise path of K1 draws: float [E][RP][OP+RP][5] (test / debug aid;
  * same device function as K1). */
@@ -242,6 +245,7 @@ ASVRL_API int asvrl_env_reset(const asvrl_reset_params* params, const asvrl_env_
                               const float* min_start_goal_dis /* [E] */, uint64_t seed,
                               uint64_t episode, int n_envs, int max_robots, int max_obs,
                               int max_cores, int64_t env_offset, const uint64_t* counter_dev,
+                              const int32_t* episode_per_env /* nullable [E]: replaces `episode` */,
                               void* stream);
 
 /* Auto-reset arguments of the fused step: what the Trainer does between two steps of one env
@@ -265,6 +269,13 @@ typedef struct asvrl_env_autoreset {
   int32_t* stage_tag;                  /* [E] with stage: episode number the stage of env e holds
                                           (0 = none; zero-initialise, and zero again whenever
                                           want_* / min_start_goal_dis / reset_params change) */
+  const float* stage_self;             /* nullable, with stage: the staged episodes' FIRST        */
+  const float* stage_objects;          /*   observation rows ([E][RP][7], [E][RP][5][5],          */
+  const float* stage_mask;             /*   [E][RP][5]) as asvrl_env_stage_refill writes them     */
+  int32_t refill_in_launch;            /* != 0: a few extra CTAs of this launch re-generate consumed
+                                          stages (scenario only); 0: the caller runs
+                                          asvrl_env_stage_refill, e.g. on a side stream */
+  int32_t reserved;
 } asvrl_env_autoreset;
 
 /* K1 + K1b + first observation in ONE launch.  For every env, equal bit for bit to
@@ -288,6 +299,23 @@ ASVRL_API int asvrl_env_step_autoreset(const asvrl_env_params* params, const asv
                                        int n_envs, int max_robots, int max_obs, int max_cores,
                                        int64_t env_offset, uint32_t mode,
                                        const uint64_t* counter_dev, void* stream);
+
+/* Re-generates, on `stream`, the stage of every env whose stage does not hold its next episode
+ * (stage_tag[e] != episode_idx[e] + 1): K1b into `stage` with episode number episode_idx[e] + 1,
+ * the perception-only K1 pass over it into `stage_out` (noise step = that number, seed =
+ * observe_seed), then publishes stage_tag.  Safe to run CONCURRENTLY with
+ * asvrl_env_step_autoreset on another stream: tags are written with release / read with acquire
+ * semantics, a stage is only rewritten while its tag is stale, and an env that ends while its
+ * stage is not ready is generated in place with the same result.
+ *   need_ws uint8[E], episode_ws int32[E]: scratch owned by the caller. */
+ASVRL_API int asvrl_env_stage_refill(const asvrl_env_params* params, const asvrl_reset_params* rparams,
+                                     const asvrl_env_state* stage, const asvrl_env_out* stage_out,
+                                     const int32_t* want_robots, const int32_t* want_cores,
+                                     const int32_t* want_obs, const float* min_start_goal_dis,
+                                     const int32_t* episode_idx, int32_t* stage_tag, uint8_t* need_ws,
+                                     int32_t* episode_ws, uint64_t seed, uint64_t observe_seed,
+                                     int n_envs, int max_robots, int max_obs, int max_cores,
+                                     int64_t env_offset, void* stream);
 
 /* Replay rows are dense float32[ASVRL_ROW] records: RB:22-69 + AGENT:360-368,387-392 */
 #define ASVRL_ROW_SELF 0     /* 7  */

@@ -40,7 +40,7 @@ class CallSequence:
         return trans, out
 
 
-def make_pair(E, R, O, C, seed, prefetch=True, spread=13):
+def make_pair(E, R, O, C, seed, prefetch="stream", spread=13):
     """A fused env and the call-sequence emulation in the same state; episode clocks are set so
     that timeouts happen in every one of the next `spread` steps."""
     a = BatchedMarineNavEnv(E, R, O, C, device=DEV, seed=seed, fused=True, prefetch=prefetch)
@@ -57,7 +57,7 @@ def same(x, y):
     return torch.equal(x, y)
 
 
-@pytest.mark.parametrize("prefetch", [False, True])
+@pytest.mark.parametrize("prefetch", [False, "workers", "stream"])
 @pytest.mark.parametrize("E,R,O,C,discrete", [(512, 8, 10, 8, False), (130, 3, 0, 0, False),
                                               (96, 5, 6, 2, True), (33, 1, 4, 0, False)])
 def test_fused_equals_call_sequence(E, R, O, C, discrete, prefetch):

@@ -24,7 +24,7 @@ class BatchedMarineNavEnv:
     def __init__(self, n_envs, num_robots=8, num_obs=10, num_cores=0, min_start_goal_dis=30.0,
                  device="cuda:0", seed=0, env_offset=0, max_robots=None, max_obs=None,
                  max_cores=None, params=None, reset_params=None, debug_outputs=False, fused=True,
-                 prefetch="stream", prefetch_every=2):
+                 prefetch="stream", prefetch_every=4):
         _lib.lib()  # fail loudly if the CUDA library is missing
         self.device = torch.device(device)
         if self.device.type != "cuda":

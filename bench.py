@@ -269,17 +269,38 @@ def run_b200(args):
     b2b_ms = b2b0.elapsed_time(b2b1) / K
 
     # ---- (3) e2e: host buffers in, host buffers out, through the public API ----
-    host_actions = [p.cpu().pin_memory() for p in pool]
-    host_out = env.new_host_out()
+    # Two shards of E/2 envs (send / recv): the D2H copy of one overlaps the kernel of the other.
+    # Every step of every shard: pinned actions H2D, the fused launch, observations + rewards +
+    # status D2H, and the caller touches the results (a checksum of the rewards) before it sends
+    # the shard's next actions.
+    from distributional_rl_decision_and_control_b200.envs.marinenav.host_pipeline import HostPipelinedEnv
+    G = 2
+    henv = HostPipelinedEnv(E, R, O, C, groups=G, device=dev, seed=args.seed + 3, env_offset=rank * E,
+                            fused=not args.unfused)
+    if not args.no_stagger:
+        for sh in henv.shards:
+            sh.state["ep_steps"].copy_(torch.randint(0, 1000, (sh.E,), device=dev, generator=gen, dtype=torch.int32))
+    host_actions = [[p[g * henv.E:(g + 1) * henv.E].cpu().pin_memory() for g in range(G)] for p in pool]
+    torch.cuda.synchronize()
     for i in range(W):
-        env.step_host(host_actions[i % 8], host_out)
+        for g in range(G):
+            henv.send(g, host_actions[i % 8][g])
+    for g in range(G):
+        henv.recv(g)
     barrier()
     t0 = time.perf_counter()
-    for i in range(K):
-        env.step_host(host_actions[i % 8], host_out)
-        torch.cuda.synchronize()  # the caller reads host_out now
+    for g in range(G):
+        henv.send(g, host_actions[0][g])
+    checksum = 0.0
+    for i in range(1, K + 1):
+        for g in range(G):
+            res = henv.recv(g)                      # results of shard g's step i-1 are on the host
+            checksum += float(res["reward"][0, 0])  # the caller reads them
+            if i < K:
+                henv.send(g, host_actions[i % 8][g])
     e2e_s = time.perf_counter() - t0
     barrier()
+    e2e_d2h = G * henv.d2h_bytes
     finite = bool(torch.isfinite(env.out["reward"]).all().item())
 
     # ---- (4) learner leg (BASELINE config 3 and the reference's own B=64 / N=8) ----
@@ -357,7 +378,9 @@ def run_b200(args):
                               f"~{26 * NB} MB of state / observation / stage buffers" if NB > 1
                               else "flushed between timed steps (256 MiB write)"), "parallelism": f"envs sharded x{world}, no collective"},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
-                    "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": E * R * 39 * 4},
+                    "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": e2e_d2h,
+                    "api": "HostPipelinedEnv.send/recv, 2 shards of E/2 envs; obs_self + obs_objects + reward + "
+                           "status per ASV (the mask is objects[...,4] != 0, as in the reference's step())"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": which,

@@ -143,7 +143,10 @@ def new_state(E, RP, OP, CP, device):
     return st
 
 
-HOST_BLOCK_FIELDS = (("obs_self", 7), ("obs_objects", 25), ("obs_mask", 5), ("reward", 1), ("status", 1))
+# obs_mask comes last: a host-side caller can leave it on the device (mask[i] = objects[i][4] != 0; the
+# reference's step() returns no mask either, RB:65 builds it) and copy only the first 34 words per ASV
+HOST_BLOCK_FIELDS = (("obs_self", 7), ("obs_objects", 25), ("reward", 1), ("status", 1), ("obs_mask", 5))
+HOST_BLOCK_NO_MASK = 34
 
 
 def carve_host_block(flat, E, RP):

@@ -165,3 +165,29 @@ def test_autoreset_rejects_bad_arguments():
     with pytest.raises(RuntimeError):  # term without ended
         _lib.replay_push(_lib.new_replay(100, 64, DEV), *env.obs, act, False, env.out["reward"], *env.obs,
                          env.out["status"], term=env.term)
+
+
+def test_host_pipelined_env_matches_plain_shards():
+    """send / recv over two shards returns, per shard, exactly what BatchedMarineNavEnv.step produces."""
+    from distributional_rl_decision_and_control_b200.envs.marinenav.host_pipeline import HostPipelinedEnv
+    E, R, G = 64, 8, 2
+    h = HostPipelinedEnv(E, R, 10, 4, groups=G, device=DEV, seed=5)
+    plain = [BatchedMarineNavEnv(E // G, R, 10, 4, device=DEV, seed=5, env_offset=g * (E // G)) for g in range(G)]
+    for p in plain:
+        p.reset()
+    for env in plain + h.shards:
+        env.state["ep_steps"][::3] = 999
+    torch.cuda.synchronize()
+    gen = torch.Generator().manual_seed(3)
+    for t in range(6):
+        acts = [(torch.rand((E // G, R, 2), generator=gen) * 2 - 1).pin_memory() for _ in range(G)]
+        for g in range(G):
+            h.send(g, acts[g])
+        for g in range(G):
+            got = h.recv(g)
+            want = plain[g].step(acts[g].to(DEV))
+            torch.cuda.synchronize()
+            for k in ("obs_self", "obs_objects", "reward", "status"):
+                assert torch.equal(got[k], want[k].cpu()), (t, g, k)
+            mask = (got["obs_objects"][..., 4] != 0).float()  # the mask the caller derives
+            assert torch.equal(mask, want["obs_mask"].cpu()), (t, g)

@@ -318,8 +318,11 @@ def run_b200(args):
     small = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=64, num_tau=8,
                   BUFFER_SIZE=1 << 20, process_group=pg, rank=rank)
     small.memory.ring = big.memory.ring  # same shard, two batch shapes
+    fast = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=1024, num_tau=32,
+                 BUFFER_SIZE=1 << 20, process_group=pg, rank=rank, matmul_precision="tf32")
+    fast.memory.ring = big.memory.ring
     KL = max(50, min(K, 500))
-    for name, ag in (("c3_B1024_N32", big), ("ref_B64_N8", small)):
+    for name, ag in (("c3_B1024_N32", big), ("c3_B1024_N32_tf32", fast), ("ref_B64_N8", small)):
         ms, mode, loss = time_learner(ag, KL, 10, dev, dist, world)
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         if world > 1:
@@ -327,6 +330,7 @@ def run_b200(args):
         ms = float(t.item())
         learner[name] = {"updates_per_sec": KL / (ms * 1e-3), "ms_per_update": ms / KL, "mode": mode,
                          "batch_per_gpu": ag.BATCH_SIZE, "n_tau": ag.num_tau, "last_critic_loss": loss,
+                         "gemm": ag.matmul_precision,
                          "grad_sync": "nccl all-reduce of the flat bucket, before clipping" if world > 1 else "none"}
     # K3 / K4 alone at C3 (their own rooflines)
     B3, N3 = 1024, 32

@@ -54,7 +54,8 @@ class Agent():
                  agent_type=None,
                  num_tau=8,
                  process_group=None,
-                 rank=0):
+                 rank=0,
+                 matmul_precision="fp32"):
         self.device = torch.device(device) if not isinstance(device, torch.device) else device
         self.LR = LR
         self.TAU = TAU
@@ -68,6 +69,11 @@ class Agent():
         self.num_tau = int(num_tau)  # N = N' (8 in the reference: ACIQN:462, AGENT:407)
         self.process_group = process_group
         self.rank = int(rank)
+        # "fp32": the reference's arithmetic (parity mode, 1e-5 on quantiles and losses);
+        # "tf32": the Linear layers of train() run on the tensor cores (throughput mode, ~1e-3)
+        if matmul_precision not in ("fp32", "tf32"):
+            raise ValueError("matmul_precision must be 'fp32' or 'tf32'")
+        self.matmul_precision = matmul_precision
         self._graph = None
         self._dims = (self_dimension, object_dimension, max_object_num, self_feature_dimension,
                       object_feature_dimension, concat_feature_dimension, hidden_dimension)
@@ -198,7 +204,29 @@ class Agent():
         return ((b["self"], b["obj"], b["mask"]), b["act"], b["rew"], (b["nself"], b["nobj"], b["nmask"]),
                 b["done"])
 
+    def _precision(self):
+        """Context that selects the GEMM arithmetic of a learner update (and of its graph capture)."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def ctx():
+            old = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = self.matmul_precision == "tf32"
+            try:
+                yield
+            finally:
+                torch.backends.cuda.matmul.allow_tf32 = old
+        return ctx()
+
     def train_AC_IQN(self, batch=None, taus=None):
+        with self._precision():
+            return self._train_AC_IQN(batch, taus)
+
+    def train_IQN(self, batch=None, taus=None):
+        with self._precision():
+            return self._train_IQN(batch, taus)
+
+    def _train_AC_IQN(self, batch=None, taus=None):
         """AGENT:386-432 on device tensors.  Returns (critic_loss, actor_loss) as 0-d CUDA tensors.
         ``batch`` injects the sample; ``taus`` = {"target", "local", "actor"} -> (B, N) tensors injects
         the three tau draws in the reference's order (AGENT:399, 403, 422) for the parity tests."""
@@ -232,7 +260,7 @@ class Agent():
         self.actor_optimizer.step()
         return critic_loss.detach(), actor_loss.detach()
 
-    def train_IQN(self, batch=None, taus=None):
+    def _train_IQN(self, batch=None, taus=None):
         """AGENT:434-476 on device tensors.  Returns the loss as a 0-d CUDA tensor."""
         states, actions, rewards, next_states, dones = self._batch(batch)
         N = self.num_tau

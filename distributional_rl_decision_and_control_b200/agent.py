@@ -13,8 +13,10 @@ What changed underneath (same results, different machinery):
     CUDA graph: at B=64 the update is ~100 tiny launches and is launch-latency bound;
   * under ``torch.distributed`` the flat gradient of each optimiser step is averaged with one
     NCCL all-reduce BEFORE clipping, so all ranks clip and step identically.
-The other four agent types of the reference (DDPG, DQN, SAC, Rainbow) are outside this round's
-scope and raise.
+The other four agent types of the reference (DDPG, DQN, SAC, Rainbow; AGENT:478-641) run on the
+same device env batch and device replay: their networks are plain dense layers in PyTorch, their
+updates read the K2b batch tensors (Rainbow: the device prioritised n-step memory of
+utils/replay_memory_rainbow.py) and share the gradient exchange / clip / Adam tail.
 """
 import copy
 import random
@@ -24,7 +26,11 @@ import torch
 import torch.optim as optim
 
 from .policy.AC_IQN_model import AC_IQN_Policy
+from .policy.DDPG_model import DDPG_Policy
+from .policy.DQN_model import DQN_Policy
 from .policy.IQN_model import IQN_Policy
+from .policy.Rainbow_model import Rainbow_Policy
+from .policy.SAC_model import SAC_Policy
 from .policy.iqn_ops import quantile_huber_loss
 from .utils.replay_buffer import ReplayBuffer, state_batch
 
@@ -55,7 +61,8 @@ class Agent():
                  num_tau=8,
                  process_group=None,
                  rank=0,
-                 matmul_precision="fp32"):
+                 matmul_precision="fp32",
+                 replay_lanes=1):
         self.device = torch.device(device) if not isinstance(device, torch.device) else device
         self.LR = LR
         self.TAU = TAU
@@ -96,16 +103,48 @@ class Agent():
                 self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
                 samplers = [(self.policy_local.tau_sampler, 0),
                             (self.policy_target.tau_sampler, _TARGET_SALT)]
-            elif agent_type in ("DDPG", "DQN", "SAC", "Rainbow"):
-                raise RuntimeError(f"Agent type {agent_type} is outside this build's scope "
-                                   "(AC-IQN and IQN are implemented)")
+            elif agent_type == "DDPG":  # AGENT:96-120
+                self.policy_local = DDPG_Policy(*self._dims, value_ranges_of_action, self.device, seed)
+                self.policy_target = DDPG_Policy(*self._dims, value_ranges_of_action, self.device, seed)
+                self.actor_optimizer = optim.Adam(self.policy_local.actor.parameters(), **capt)
+                self.critic_optimizer = optim.Adam(self.policy_local.critic.parameters(), **capt)
+                samplers = []
+            elif agent_type == "DQN":  # AGENT:121-143
+                self.policy_local = DQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
+                self.policy_target = DQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
+                self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
+                samplers = []
+            elif agent_type == "SAC":  # AGENT:144-168
+                self.alpha = 0.078
+                self.policy_local = SAC_Policy(*self._dims, value_ranges_of_action, self.device, seed)
+                self.policy_target = SAC_Policy(*self._dims, value_ranges_of_action, self.device, seed)
+                self.actor_optimizer = optim.Adam(self.policy_local.actor.parameters(), **capt)
+                self.critic_1_optimizer = optim.Adam(self.policy_local.critic_1.parameters(), **capt)
+                self.critic_2_optimizer = optim.Adam(self.policy_local.critic_2.parameters(), **capt)
+                samplers = []
+            elif agent_type == "Rainbow":  # AGENT:169-198
+                self.atoms = 51
+                self.Vmin = -1.0
+                self.Vmax = 1.0
+                self.support = torch.linspace(self.Vmin, self.Vmax, self.atoms).to(self.device)
+                self.delta_z = (self.Vmax - self.Vmin) / (self.atoms - 1)
+                self.n = multi_steps
+                self.policy_local = Rainbow_Policy(*self._dims, action_size, self.atoms, self.device, seed).to(self.device)
+                self.policy_target = Rainbow_Policy(*self._dims, action_size, self.atoms, self.device, seed).to(self.device)
+                self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
+                samplers = []
             else:
                 raise RuntimeError("Agent type not implemented!")
             # local and target nets must not share a tau stream, and neither may two ranks
             for s, salt in samplers:
                 s.seed = (s.seed ^ salt ^ (self.rank * 0xD1B54A32D192ED03)) & 0xFFFFFFFFFFFFFFFF
-            self.memory = ReplayBuffer(BUFFER_SIZE, BATCH_SIZE, object_dimension, max_object_num,
-                                       seed=249 + 7919 * self.rank, device=self.device)
+            if agent_type == "Rainbow":  # prioritised n-step memory (AGENT:202-203); ``replay_lanes`` =
+                # ASVs per batched step when fed by append_step (1 = the reference's host path)
+                from .utils.replay_memory_rainbow import ReplayMemory
+                self.memory = ReplayMemory(self.device, BUFFER_SIZE, lanes=replay_lanes, n=multi_steps)
+            else:
+                self.memory = ReplayBuffer(BUFFER_SIZE, BATCH_SIZE, object_dimension, max_object_num,
+                                           seed=249 + 7919 * self.rank, device=self.device)
 
     # ------------------------------------------------------------------ acting
     def state_to_tensor(self, states):
@@ -145,6 +184,50 @@ class Agent():
             action = random.choice(np.arange(self.action_size))
         return action, quantiles.cpu().data.numpy(), taus.cpu().data.numpy()
 
+    def _greedy_continuous(self, state, eps, use_eval, sac=False):
+        if random.random() > eps:
+            x = self.state_to_tensor(state_batch([state]))
+            actor = self.policy_local.actor
+            actor.eval() if use_eval else actor.train()
+            with torch.no_grad():
+                out = actor(x)
+                action = (out[0] if sac else out).cpu().data.numpy()[0].tolist()
+            actor.train()
+            return action
+        return [np.random.uniform(low=lo, high=hi) for lo, hi in self.value_ranges_of_action]
+
+    def act_ddpg(self, state, eps=0.0, use_eval=True):
+        """AGENT:252-269."""
+        return self._greedy_continuous(state, eps, use_eval)
+
+    def act_sac(self, state, eps=0.0, use_eval=True):
+        """AGENT:289-306: the sampled (squashed) action of the stochastic actor."""
+        return self._greedy_continuous(state, eps, use_eval, sac=True)
+
+    def act_dqn(self, state, eps=0.0, use_eval=True):
+        """AGENT:271-287."""
+        x = self.state_to_tensor(state_batch([state]))
+        net = self.policy_local
+        net.eval() if use_eval else net.train()
+        with torch.no_grad():
+            action_values = net(x)
+        net.train()
+        if random.random() > eps:
+            return np.argmax(action_values.cpu().data.numpy())
+        return random.choice(np.arange(self.action_size))
+
+    def act_rainbow(self, state, eps=0.0, use_eval=True):
+        """AGENT:308-324."""
+        x = self.state_to_tensor(state_batch([state]))
+        net = self.policy_local
+        net.eval() if use_eval else net.train()
+        with torch.no_grad():
+            probs = net(x)
+        net.train()
+        if random.random() > eps:
+            return (probs * self.support).sum(2).argmax(1).item()
+        return random.choice(np.arange(self.action_size))
+
     @torch.no_grad()
     def act_batch(self, obs, eps=0.0, cvar=1.0):
         """Vectorised epsilon-greedy for M ASVs at once: ``obs`` = (self (M,7), objects (M,5,5),
@@ -154,8 +237,10 @@ class Agent():
         generator, which is graph-safe."""
         M = obs[0].shape[0]
         explore = torch.rand((M,), device=self.device) < eps
-        if self.agent_type == "AC-IQN":
+        if self.agent_type in ("AC-IQN", "DDPG", "SAC"):
             greedy = self.policy_local.actor(obs)
+            if self.agent_type == "SAC":
+                greedy = greedy[0]
             if not hasattr(self, "_act_lo"):
                 self._act_lo = torch.tensor([r[0] for r in self.value_ranges_of_action], device=self.device)
                 self._act_hi = torch.tensor([r[1] for r in self.value_ranges_of_action], device=self.device)
@@ -163,8 +248,15 @@ class Agent():
             rnd = lo + (hi - lo) * torch.rand((M, lo.numel()), device=self.device)
             return torch.where(explore.unsqueeze(-1), rnd, greedy).contiguous()
         net = self.policy_local
-        quantiles, _ = net(obs, net.K, cvar)
-        greedy = quantiles.mean(dim=1).argmax(dim=1)
+        if self.agent_type == "IQN":
+            quantiles, _ = net(obs, net.K, cvar)
+            greedy = quantiles.mean(dim=1).argmax(dim=1)
+        elif self.agent_type == "DQN":
+            greedy = net(obs).argmax(dim=1)
+        elif self.agent_type == "Rainbow":  # noisy layers stay in training mode while collecting (TRAINER:131)
+            greedy = (net(obs) * self.support).sum(2).argmax(1)
+        else:
+            raise RuntimeError("Agent type not implemented!")
         rnd = torch.randint(0, self.action_size, (M,), device=self.device)
         return torch.where(explore, rnd, greedy).to(torch.int32).contiguous()
 
@@ -174,15 +266,16 @@ class Agent():
         loss, as numpy scalars like the reference (AGENT:432, 476)."""
         if self._graph is not None:
             out = self.train_graph_replay()
-        elif self.agent_type == "AC-IQN":
-            out = self.train_AC_IQN()
-        elif self.agent_type == "IQN":
-            out = self.train_IQN()
+        elif self.agent_type in self._TRAINERS:
+            out = getattr(self, self._TRAINERS[self.agent_type])()
         else:
             raise RuntimeError("Agent type not implemented!")
         if isinstance(out, tuple):
             return tuple(o.detach().cpu().numpy() for o in out)
         return out.detach().cpu().numpy()
+
+    _TRAINERS = {"AC-IQN": "train_AC_IQN", "IQN": "train_IQN", "DDPG": "train_DDPG", "DQN": "train_DQN",
+                 "SAC": "train_SAC", "Rainbow": "train_Rainbow"}
 
     def _sync_grads(self, params):
         """Data-parallel exchange step: average ONE flat fp32 bucket over the ranks."""
@@ -281,6 +374,97 @@ class Agent():
         self.optimizer.step()
         return loss.detach()
 
+    # ------------------------------------------------------------------ the four non-distributional agents
+    def _step(self, optimizer, loss, params):
+        """zero_grad / backward / all-reduce / clip / Adam, as every update of the reference does
+        (AGENT:414-416 and twins).  zero_grad first: losses of SAC share nothing across optimisers."""
+        optimizer.zero_grad(set_to_none=True)
+        loss.backward()
+        self._sync_grads(params)
+        torch.nn.utils.clip_grad_norm_(params, 0.5)
+        optimizer.step()
+
+    def train_DDPG(self, batch=None):
+        """AGENT:478-516 on device tensors.  Returns (critic_loss, actor_loss) as 0-d CUDA tensors."""
+        with self._precision():
+            states, actions, rewards, next_states, dones = self._batch(batch)
+            rewards, dones = rewards.unsqueeze(-1), dones.unsqueeze(-1)
+            local, target = self.policy_local, self.policy_target
+            with torch.no_grad():
+                q_next = target.critic(next_states, target.actor(next_states))
+                q_target = rewards + self.GAMMA * q_next * (1. - dones)
+            critic_loss = torch.nn.functional.smooth_l1_loss(local.critic(states, actions), q_target)
+            self._step(self.critic_optimizer, critic_loss, list(local.critic.parameters()))
+            actor_loss = -local.critic(states, local.actor(states)).mean()
+            self._step(self.actor_optimizer, actor_loss, list(local.actor.parameters()))
+            return critic_loss.detach(), actor_loss.detach()
+
+    def train_DQN(self, batch=None):
+        """AGENT:518-545 on device tensors.  Returns the loss as a 0-d CUDA tensor."""
+        with self._precision():
+            states, actions, rewards, next_states, dones = self._batch(batch)
+            rewards, dones = rewards.unsqueeze(-1), dones.unsqueeze(-1)
+            with torch.no_grad():
+                q_next = self.policy_target(next_states).max(dim=1, keepdim=True)[0]
+                q_target = rewards + (1 - dones) * self.GAMMA * q_next
+            q = self.policy_local(states).gather(1, actions[:, :1].long())
+            loss = torch.nn.functional.smooth_l1_loss(q, q_target)
+            self._step(self.optimizer, loss, list(self.policy_local.parameters()))
+            return loss.detach()
+
+    def train_SAC(self, batch=None, noise=None):
+        """AGENT:547-595 on device tensors.  Returns (critic_1_loss, critic_2_loss, actor_loss).
+        ``noise`` = {"target", "actor"} -> (B, 2) standard-normal draws (parity tests)."""
+        with self._precision():
+            states, actions, rewards, next_states, dones = self._batch(batch)
+            rewards, dones = rewards.unsqueeze(-1), dones.unsqueeze(-1)
+            noise = noise or {}
+            local, target = self.policy_local, self.policy_target
+            mse = torch.nn.functional.mse_loss
+            with torch.no_grad():
+                next_actions, next_log_probs = target.actor(next_states, noise.get("target"))
+                tv = torch.min(target.critic_1(next_states, next_actions),
+                               target.critic_2(next_states, next_actions)) - self.alpha * next_log_probs
+                tv = rewards + self.GAMMA * tv * (1. - dones)
+            loss_1 = mse(local.critic_1(states, actions), tv)
+            loss_2 = mse(local.critic_2(states, actions), tv)
+            self._step(self.critic_1_optimizer, loss_1, list(local.critic_1.parameters()))
+            self._step(self.critic_2_optimizer, loss_2, list(local.critic_2.parameters()))
+            new_actions, log_probs = local.actor(states, noise.get("actor"))
+            values_new = torch.min(local.critic_1(states, new_actions), local.critic_2(states, new_actions))
+            actor_loss = (self.alpha * log_probs - values_new).mean()
+            self._step(self.actor_optimizer, actor_loss, list(local.actor.parameters()))
+            return loss_1.detach(), loss_2.detach(), actor_loss.detach()
+
+    def train_Rainbow(self, sample=None):
+        """AGENT:597-641 (categorical double-Q with n-step returns and prioritised replay) on device
+        tensors; priorities are updated on the device.  Returns the per-sample loss (B,)."""
+        with self._precision():
+            B, A = self.BATCH_SIZE, self.atoms
+            idxs, states, actions, returns, next_states, nonterminals, weights = \
+                self.memory.sample(B) if sample is None else sample
+            rows = torch.arange(B, device=self.device)
+            log_ps_a = self.policy_local(states, log=True)[rows, actions]          # log p(s_t, a_t)
+            with torch.no_grad():
+                pns = self.policy_local(next_states)                              # online net picks a*
+                a_star = (self.support.expand_as(pns) * pns).sum(2).argmax(1)
+                self.policy_target.reset_noise()
+                pns_a = self.policy_target(next_states)[rows, a_star]             # target net evaluates it
+                # Tz = R^n + gamma^n z, clamped, projected onto the fixed support (AGENT:616-632)
+                Tz = returns.unsqueeze(1) + nonterminals * (self.GAMMA ** self.n) * self.support.unsqueeze(0)
+                Tz = Tz.clamp(min=self.Vmin, max=self.Vmax)
+                b = (Tz - self.Vmin) / self.delta_z
+                lo, up = b.floor().to(torch.int64), b.ceil().to(torch.int64)
+                lo = torch.where((up > 0) & (lo == up), lo - 1, lo)                # b integral: keep the mass
+                up = torch.where((lo < (A - 1)) & (lo == up), up + 1, up)
+                m = torch.zeros((B, A), dtype=torch.float32, device=self.device)
+                m.scatter_add_(1, lo, pns_a * (up.float() - b))
+                m.scatter_add_(1, up, pns_a * (b - lo.float()))
+            loss = -torch.sum(m * log_ps_a, 1)                                    # cross entropy
+            self._step(self.optimizer, (weights * loss).mean(), list(self.policy_local.parameters()))
+            self.memory.update_priorities(idxs, loss.detach())
+            return loss.detach()
+
     # ------------------------------------------------------------------ CUDA graph of one update
     def enable_cuda_graph(self, warmup=3):
         """Capture sample -> critic step -> actor step as one CUDA graph.  RNG counters of the
@@ -288,7 +472,9 @@ class Agent():
         advances, so every replay draws a fresh batch and fresh taus."""
         if self.memory.size() < self.BATCH_SIZE:
             raise RuntimeError("fill the replay buffer with at least one batch before capturing")
-        step = self.train_AC_IQN if self.agent_type == "AC-IQN" else self.train_IQN
+        if self.agent_type == "Rainbow":
+            raise RuntimeError("the Rainbow update keeps its ring position on the host and is not captured")
+        step = getattr(self, self._TRAINERS[self.agent_type])
         dev = self.device
         import gc
         gc.collect()  # no finaliser of an unrelated CUDA tensor may run in the middle of the capture
@@ -296,7 +482,7 @@ class Agent():
             self._ctr = torch.zeros((1,), dtype=torch.int64, device=dev)
             self.memory.counter_dev = self._ctr
             nets = [self.policy_local.critic, self.policy_target.critic] if self.agent_type == "AC-IQN" \
-                else [self.policy_local, self.policy_target]
+                else [self.policy_local, self.policy_target] if self.agent_type == "IQN" else []
             for n in nets:
                 n.tau_sampler.counter_dev = self._ctr
             side = torch.cuda.Stream(device=dev)
@@ -325,10 +511,14 @@ class Agent():
     def soft_update(self):
         """theta_target = TAU * theta_local + (1 - TAU) * theta_target (AGENT:643-656; TAU = 1.0 in
         the reference, i.e. a hard copy every target_update_interval steps)."""
-        if self.agent_type == "AC-IQN":
+        if self.agent_type in ("AC-IQN", "DDPG"):
             pairs = [(self.policy_target.actor, self.policy_local.actor),
                      (self.policy_target.critic, self.policy_local.critic)]
-        elif self.agent_type == "IQN":
+        elif self.agent_type == "SAC":
+            pairs = [(self.policy_target.actor, self.policy_local.actor),
+                     (self.policy_target.critic_1, self.policy_local.critic_1),
+                     (self.policy_target.critic_2, self.policy_local.critic_2)]
+        elif self.agent_type in ("IQN", "DQN", "Rainbow"):
             pairs = [(self.policy_target, self.policy_local)]
         else:
             raise RuntimeError("Agent type not implemented!")
@@ -347,16 +537,19 @@ class Agent():
     def load_model(self, path, device="cpu"):
         """Restores policy_local only, like the reference (AGENT:684-698).  Parameters are copied
         in place so optimisers and a captured graph stay valid."""
-        cls = AC_IQN_Policy if self.agent_type == "AC-IQN" else IQN_Policy if self.agent_type == "IQN" else None
+        cls = {"AC-IQN": AC_IQN_Policy, "IQN": IQN_Policy, "DDPG": DDPG_Policy, "DQN": DQN_Policy,
+               "SAC": SAC_Policy, "Rainbow": Rainbow_Policy}.get(self.agent_type)
         if cls is None:
             raise RuntimeError("Agent type not implemented!")
         loaded = cls.load(path, device)
         if not hasattr(self, "policy_local"):
             self.policy_local = loaded
             return
-        if self.agent_type == "AC-IQN":
-            self.policy_local.actor.load_state_dict(loaded.actor.state_dict())
-            self.policy_local.critic.load_state_dict(loaded.critic.state_dict())
+        parts = {"AC-IQN": ("actor", "critic"), "DDPG": ("actor", "critic"),
+                 "SAC": ("actor", "critic_1", "critic_2")}.get(self.agent_type)
+        if parts:
+            for name in parts:
+                getattr(self.policy_local, name).load_state_dict(getattr(loaded, name).state_dict())
         else:
             self.policy_local.load_state_dict(loaded.state_dict())
 

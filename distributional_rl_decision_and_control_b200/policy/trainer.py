@@ -86,6 +86,14 @@ class Trainer():
             return agent.act_ac_iqn(state, eps, use_eval=use_eval)
         if kind == "IQN":
             return agent.act_iqn(state, eps, use_eval=use_eval)[0]
+        if kind == "DDPG":
+            return agent.act_ddpg(state, eps, use_eval=use_eval)
+        if kind == "DQN":
+            return agent.act_dqn(state, eps, use_eval=use_eval)
+        if kind == "SAC":
+            return agent.act_sac(state, eps, use_eval=use_eval)
+        if kind == "Rainbow":
+            return agent.act_rainbow(state, eps, use_eval=use_eval)
         raise RuntimeError("Agent type not implemented!")
 
     # ------------------------------------------------------------------ training loop
@@ -119,7 +127,10 @@ class Trainer():
                     continue
                 ep_rewards[i] += agent.GAMMA ** ep_length * rewards[i]
                 if agent.training:
-                    agent.memory.add((states[i], actions[i], rewards[i], next_states[i], dones[i]))
+                    if agent.agent_type == "Rainbow":  # TRAINER:163-164
+                        agent.memory.append(states[i], actions[i], rewards[i], dones[i])
+                    else:
+                        agent.memory.add((states[i], actions[i], rewards[i], next_states[i], dones[i]))
                 if rob.collision or rob.reach_goal:
                     rob.deactivated = True
                     ep_deactivated_t[i] = ep_length
@@ -127,8 +138,11 @@ class Trainer():
             end_episode = (ep_length >= 1000) or env.check_all_deactivated()
 
             if self.current_timestep >= self.learning_starts and agent.training:
-                if self.current_timestep % self.UPDATE_EVERY == 0 and agent.memory.size() > agent.BATCH_SIZE:
-                    agent.train()
+                if self.current_timestep % self.UPDATE_EVERY == 0:
+                    num_elements = agent.memory.transitions.num_elements() if agent.agent_type == "Rainbow" \
+                        else agent.memory.size()  # TRAINER:184-185
+                    if num_elements > agent.BATCH_SIZE:
+                        agent.train()
                 if self.current_timestep % self.target_update_interval == 0:
                     agent.soft_update()
                 if self.current_timestep == self.learning_starts or self.current_timestep % eval_freq == 0:

@@ -37,7 +37,10 @@ class VectorTrainer:
         self.initial_eps = initial_eps
         self.final_eps = final_eps
         self.schedule = schedule          # same dict as the reference's training_schedule (ENV:75-87)
-        self.discrete = agent.agent_type == "IQN"
+        self.discrete = agent.agent_type in ("IQN", "DQN", "Rainbow")
+        self.rainbow = agent.agent_type == "Rainbow"
+        if self.rainbow and agent.memory.lanes != env.E * env.RP:
+            raise RuntimeError("Rainbow on a batched env needs Agent(replay_lanes=n_envs * max_robots)")
         self.steps = 0                    # batched steps
         self.updates = 0
         self.env_timesteps = 0            # env-steps = batched steps x envs (the reference's unit)
@@ -75,6 +78,10 @@ class VectorTrainer:
         flat = (o_self.view(E * RP, 7), o_obj.view(E * RP, 5, 5), o_mask.view(E * RP, 5))
         actions = agent.act_batch(flat, self._eps_dev)
         actions = actions.view(E, RP) if self.discrete else actions.view(E, RP, 2)
+        if self.rainbow:  # the n-step memory stores (s_t, a_t, r_t+1, terminal), no next state (TRAINER:163-164)
+            out = env.step(actions, is_continuous_action=False)
+            agent.memory.append_step((o_self, o_obj, o_mask), actions, out)
+            return out
         if env.fused:  # one launch: step + re-generation + first observation; terminal rows in env.term
             out = env.step_fused(actions, is_continuous_action=not self.discrete)
             agent.memory.push_step((o_self, o_obj, o_mask), actions, self.discrete, out, term=env.term)
@@ -140,13 +147,14 @@ class VectorTrainer:
             if self.steps >= self.learning_starts and agent.training and since_update >= self.update_every:
                 since_update = 0
                 if not self._buffer_ready:  # one host sync until the ring holds a batch (TRAINER:186)
-                    self._buffer_ready = agent.memory.size() > agent.BATCH_SIZE
-                if self._buffer_ready and self.cuda_graph and agent._graph is None:
+                    have = agent.memory.transitions.num_elements() if self.rainbow else agent.memory.size()
+                    self._buffer_ready = have > agent.BATCH_SIZE and (not self.rainbow or agent.memory.filled > agent.memory.n + 1)
+                if self._buffer_ready and self.cuda_graph and agent._graph is None and not self.rainbow:
                     agent.enable_cuda_graph()
                 if self._buffer_ready:
                     for _ in range(self.updates_per_round):
-                        last_losses = agent.train_graph_replay() if agent._graph is not None else (
-                            agent.train_AC_IQN() if agent.agent_type == "AC-IQN" else agent.train_IQN())
+                        last_losses = agent.train_graph_replay() if agent._graph is not None else \
+                            getattr(agent, agent._TRAINERS[agent.agent_type])()
                         self.updates += 1
                         if self.updates % self.target_update_interval == 0:
                             agent.soft_update()
@@ -159,7 +167,7 @@ class VectorTrainer:
         dt = time.perf_counter() - t0
         if last_losses is not None:
             last_losses = tuple(float(x) for x in last_losses) if isinstance(last_losses, tuple) \
-                else float(last_losses)
+                else float(last_losses.mean())
         return {"steps": self.steps, "env_steps": self.env_timesteps, "updates": self.updates,
                 "seconds": dt, "env_steps_per_sec": self.env_timesteps / dt,
                 "updates_per_sec": self.updates / dt, "last_losses": last_losses}

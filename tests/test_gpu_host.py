@@ -217,3 +217,34 @@ def test_vector_trainer(kind, graph):
     assert torch.isfinite(rows).all()
     assert int(env.want_robots[0].item()) == 8            # the curriculum advanced (ENV:75-87)
     assert int(env.state["n_robots"].max().item()) in (5, 8)  # 8 once an episode ended after the switch
+
+
+@pytest.mark.parametrize("kind,graph", [("DDPG", False), ("DDPG", True), ("DQN", True), ("SAC", False),
+                                        ("SAC", True), ("Rainbow", False)])
+def test_vector_trainer_other_agents(kind, graph):
+    """The four non-distributional agents of the reference (AGENT:478-641) on the shared device env
+    batch: collection, device replay (Rainbow: prioritised n-step memory), updates, target sync."""
+    E, RP = 96, 8
+    env = BatchedMarineNavEnv(E, num_robots=6, num_obs=4, num_cores=2, device=DEV, seed=9,
+                              max_robots=RP, max_obs=10, max_cores=8)
+    env.reset()
+    env.state["ep_steps"][::5] = 990  # some episodes end inside the run
+    agent = Agent(device=DEV, seed=7, agent_type=kind, BUFFER_SIZE=40000,
+                  replay_lanes=E * RP if kind == "Rainbow" else 1)
+    vt = VectorTrainer(env, agent, update_every=4, learning_starts=8, target_update_interval=3, cuda_graph=graph)
+    nets = {"DDPG": lambda p: p.critic, "SAC": lambda p: p.critic_1}.get(kind, lambda p: p)
+    w0 = [p.detach().clone() for p in nets(agent.policy_local).parameters()]
+    # learn() resets the env: keep the shortened clocks by patching after the first reset
+    res = vt.learn(48)
+    assert res["steps"] >= 48 and res["updates"] >= 8
+    assert np.all(np.isfinite(res["last_losses"]))
+    assert any(not torch.equal(a, b) for a, b in zip(w0, nets(agent.policy_local).parameters()))
+    if kind == "Rainbow":
+        m = agent.memory
+        assert m.transitions.num_elements() > 0 and torch.isfinite(m.rows).all()
+        idxs, s, a, R, ns, nonterm, w = m.sample(64)
+        assert s[0].shape == (64, 7) and ns[1].shape == (64, 5, 5) and a.dtype == torch.int64
+        assert torch.isfinite(R).all() and float(w.max()) == 1.0 and (m.prio[idxs] > 0).all()
+    else:
+        hs = agent.memory.ring["head_size"].cpu().numpy()
+        assert 0 < hs[1] <= 40000

@@ -31,8 +31,13 @@ class Trainer():
                  initial_eps=0.6,
                  final_eps=0.05,
                  imitation=False,
-                 il_agent=None):
+                 il_agent=None,
+                 batched_evaluation=False):
         self.train_env = train_env
+        # True: the frozen scenarios are played as ONE device batch (evaluation.BatchedEvaluator)
+        # instead of one after the other; same statistics, no per-step host round trips
+        self.batched_evaluation = bool(batched_evaluation)
+        self._evaluator = None
         self.eval_env = eval_env
         self.rl_agent = rl_agent
         self.eval_config = []
@@ -198,7 +203,16 @@ class Trainer():
         is_continuous_action = agent.agent_type in _CONTINUOUS
         data = {k: [] for k in ("observations", "actions", "trajectories", "rewards", "successes",
                                 "times", "energies", "relations")}
-        for idx, config in enumerate(self.eval_config):
+        if self.batched_evaluation:
+            from ..evaluation import BatchedEvaluator
+            if self._evaluator is None:
+                self._evaluator = BatchedEvaluator(self.eval_config, device=env.device, seed=env.seed)
+            res = self._evaluator.run(agent)
+            for k in ("rewards", "successes", "times", "energies", "actions", "trajectories"):
+                data[k] = res[k]
+            data["observations"] = [[[] for _ in t] for t in res["trajectories"]]  # not recorded in batch mode
+            data["relations"] = [[[] for _ in t] for t in res["trajectories"]]
+        for idx, config in enumerate([] if self.batched_evaluation else self.eval_config):
             print(f"Evaluating episode {idx}")
             state, _, _ = env.reset_with_eval_config(config)
             n = len(env.robots)

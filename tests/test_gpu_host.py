@@ -248,3 +248,45 @@ def test_vector_trainer_other_agents(kind, graph):
     else:
         hs = agent.memory.ring["head_size"].cpu().numpy()
         assert 0 < hs[1] <= 40000
+
+
+def test_batched_evaluation_matches_sequential(tmp_path, capsys):
+    """Trainer.evaluation over the frozen scenarios as one device batch == one scenario after the
+    other (TRAINER:266-387).  Sensor noise is switched off in the stored scenarios so that both
+    paths see the same observations (their noise streams are keyed by the env index)."""
+    from distributional_rl_decision_and_control_b200.evaluation import BatchedEvaluator, summarize
+    ev = {"num_episodes": [3, 3], "num_robots": [3, 5], "num_cores": [0, 4], "num_obstacles": [0, 6],
+          "min_start_goal_dis": [30.0, 35.0]}
+    sched = {"timesteps": [0], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+    agent = Agent(device=DEV, seed=100, agent_type="AC-IQN", BUFFER_SIZE=1000)
+    tr = Trainer(train_env=MarineNavEnv3(seed=0, schedule=sched, device=DEV),
+                 eval_env=MarineNavEnv3(seed=253, is_eval_env=True, device=DEV), eval_schedule=ev, rl_agent=agent)
+    for cfg in tr.eval_config:
+        n = cfg["env"]["num_robots"]
+        cfg["robots"]["perception"]["pos_std"] = [0.0] * n
+        cfg["robots"]["perception"]["vel_std"] = [0.0] * n
+        cfg["robots"]["perception"]["r_mean_ratio"] = [1.0] * n
+    tr.evaluation()
+    capsys.readouterr()
+    seq = {k: getattr(tr, "eval_" + k)[-1] for k in ("rewards", "successes", "times", "energies", "trajectories")}
+    res = BatchedEvaluator(tr.eval_config, device=DEV, seed=253).run(agent)
+    assert len(res["rewards"]) == 6 and res["successes"] == [bool(x) for x in seq["successes"]]
+    lengths_seq = [max(len(t) for t in ep) - 1 for ep in seq["trajectories"]]
+    assert res["lengths"] == lengths_seq
+    assert np.allclose(res["times"], seq["times"], rtol=1e-5)
+    assert np.allclose(res["rewards"], seq["rewards"], rtol=5e-3, atol=5e-3)
+    assert np.allclose(res["energies"], seq["energies"], rtol=5e-3)
+    # recorded histories have the reference's row layout (13 columns, WAMV:191-193)
+    t0 = res["trajectories"][0][0]
+    assert len(t0[0]) == 13 and len(res["actions"][0][0]) == len(t0)
+    assert np.allclose(t0[-1][:3], seq["trajectories"][0][0][-1][:3], atol=2e-2)
+    s = summarize(res)
+    assert 0.0 <= s["success_rate"] <= 1.0 and np.isfinite(s["avg_reward"])
+    # the Trainer switch fills the same containers
+    tr2 = Trainer(train_env=tr.train_env, eval_env=tr.eval_env, eval_schedule=ev, rl_agent=agent, batched_evaluation=True)
+    tr2.eval_config = tr.eval_config
+    tr2.evaluation()
+    capsys.readouterr()
+    assert np.allclose(tr2.eval_rewards[-1], res["rewards"], rtol=1e-6)
+    tr2.save_evaluation(str(tmp_path))
+    assert "evaluations.npz" in os.listdir(tmp_path)

@@ -116,7 +116,7 @@ __device__ __forceinline__ void refill_worker(const FusedArgs& fa, char* smem, u
 struct SmemLayout {
   uint32_t px, py, key, obst, cores, c, s, vx, vy, vz, Tl, Tr, gx, gy, rew, ox, oy, osp, cand,
       st_obj, st_self, st_mask, cphi, fl0, fl, det_lo, det_hi, plist, dlist, cnt, el_of, r_of, chit,
-      nr, no, nc, ep, ok, ended, epn, rs_sg, rs_core, rs_obs, rs_cand, rs_okm, crx, cry;
+      nr, no, nc, ep, ok, ended, epn, pre_ep, pre_tag, rs_sg, rs_core, rs_obs, rs_cand, rs_okm, crx, cry;
   uint32_t bytes;
   // pair-loop stepping without integer division: TPB = q*S + rem
   int step_a, step_sl, step3_a, step3_sl;
@@ -132,6 +132,7 @@ struct Smem {
   int* cnt;                 // [0] entries of plist, [1] entries of dlist, [2] noise work ticket
   uint8_t *el_of, *r_of, *chit;
   int *nr, *no, *nc, *ep, *ok, *ended, *epn;
+  int *pre_ep, *pre_tag;      // fused tail: next episode number / stage readiness, read in phase 0
   float4 *obst, *cores;
   float4 *rs_sg, *rs_core, *rs_obs, *rs_cand;  // fused auto-reset scratch: accepted sets, round candidates
   unsigned* rs_okm;
@@ -155,6 +156,7 @@ static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fus
   L.el_of = take(A, 1); L.r_of = take(A, 1); L.chit = take(A * 5, 1);
   L.nr = take(EPB, 4); L.no = take(EPB, 4); L.nc = take(EPB, 4); L.ep = take(EPB, 4); L.ok = take(EPB, 4);
   L.ended = take(EPB, 4); L.epn = take(EPB, 4);
+  L.pre_ep = take(EPB, 4); L.pre_tag = take(EPB, 4);
   const uint32_t f = fused ? 1u : 0u;
   L.rs_sg = take(f * RP, 16); L.rs_core = take(f * CP, 16); L.rs_obs = take(f * OP, 16);
   L.rs_cand = take(f * tpb, 16); L.rs_okm = take(f * 8, 4);
@@ -189,6 +191,7 @@ __device__ __forceinline__ Smem carve(char* base, const SmemLayout& L) {
   m.chit = (uint8_t*)(base + L.chit);
   m.nr = (int*)(base + L.nr); m.no = (int*)(base + L.no); m.nc = (int*)(base + L.nc);
   m.ep = (int*)(base + L.ep); m.ok = (int*)(base + L.ok); m.ended = (int*)(base + L.ended); m.epn = (int*)(base + L.epn);
+  m.pre_ep = (int*)(base + L.pre_ep); m.pre_tag = (int*)(base + L.pre_tag);
   m.rs_sg = (float4*)(base + L.rs_sg); m.rs_core = (float4*)(base + L.rs_core);
   m.rs_obs = (float4*)(base + L.rs_obs); m.rs_cand = (float4*)(base + L.rs_cand);
   m.rs_okm = (unsigned*)(base + L.rs_okm);
@@ -290,6 +293,79 @@ __device__ __forceinline__ Cand candidate(const EnvConsts& k, const Smem& m, int
   return c;
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l2_span(const void* p, int bytes) {
+  const char* c = (const char*)p;
+  for (int o = 0; o < bytes; o += 128) prefetch_l2(c + o);
+  prefetch_l2(c + bytes - 1);
+}
+// everything take_stage_batched will read for env e (one thread issues ~25 non-blocking prefetches)
+__device__ __forceinline__ void prefetch_stage(const FusedArgs& fa, int e, int RP, int OP, int CP) {
+  const ResetState& sg = fa.stage;
+  const size_t g = (size_t)e * RP;
+  prefetch_l2_span(sg.x + g, RP * 4); prefetch_l2_span(sg.y + g, RP * 4); prefetch_l2_span(sg.theta + g, RP * 4);
+  prefetch_l2_span(sg.goal_x + g, RP * 4); prefetch_l2_span(sg.goal_y + g, RP * 4);
+  if (OP > 0) prefetch_l2_span(sg.obstacles + (size_t)e * OP, OP * 16);
+  if (CP > 0) prefetch_l2_span(sg.cores + (size_t)e * CP, CP * 16);
+  prefetch_l2(sg.n_robots + e); prefetch_l2(sg.n_obs + e); prefetch_l2(sg.n_cores + e);
+  if (fa.stage_self) {
+    prefetch_l2_span(fa.stage_self + g * 7, RP * 28);
+    prefetch_l2_span(fa.stage_objects + g * 25, RP * 100);
+    prefetch_l2_span(fa.stage_mask + g * 5, RP * 20);
+  }
+}
+
+
+// The fused tail's copy of a staged episode into the live state (what take_stage does) and of its
+// staged first observation rows into `out`, with all loads issued before the first store.
+__device__ __forceinline__ void take_stage_batched(const ResetState& st, const FusedArgs& fa, const OutPtrs& out,
+                                                   int e, int RP, int OP, int CP, int tid) {
+  static_assert(RS_MAXR <= TPB && RS_MAXO <= TPB && RS_MAXC <= TPB, "one table row per thread");
+  constexpr int IT_O = (RS_MAXR * 25 + TPB - 1) / TPB, IT_S = (RS_MAXR * 7 + TPB - 1) / TPB,
+                IT_M = (RS_MAXR * 5 + TPB - 1) / TPB;
+  const ResetState& sg = fa.stage;
+  const size_t g = (size_t)e * RP + tid, b0 = (size_t)e * RP;
+  float rx = 0, ry = 0, rth = 0, rgx = 0, rgy = 0;
+  float4 ob = make_float4(0, 0, 0, 0), co = make_float4(0, 0, 0, 0);
+  int cnt = 0;
+  float fo[IT_O], fs[IT_S], fm[IT_M];
+  if (tid < RP) {
+    rx = __ldcg(sg.x + g); ry = __ldcg(sg.y + g); rth = __ldcg(sg.theta + g);
+    rgx = __ldcg(sg.goal_x + g); rgy = __ldcg(sg.goal_y + g);
+  }
+  if (tid < OP) ob = __ldcg(sg.obstacles + (size_t)e * OP + tid);
+  if (tid < CP) co = __ldcg(sg.cores + (size_t)e * CP + tid);
+  if (tid < 3) cnt = __ldcg((tid == 0 ? sg.n_robots : tid == 1 ? sg.n_obs : sg.n_cores) + e);
+  if (fa.stage_self) {
+#pragma unroll
+    for (int q = 0; q < IT_O; ++q) { const int i = tid + q * TPB; fo[q] = i < RP * 25 ? __ldcg(fa.stage_objects + b0 * 25 + i) : 0.0f; }
+#pragma unroll
+    for (int q = 0; q < IT_S; ++q) { const int i = tid + q * TPB; fs[q] = i < RP * 7 ? __ldcg(fa.stage_self + b0 * 7 + i) : 0.0f; }
+#pragma unroll
+    for (int q = 0; q < IT_M; ++q) { const int i = tid + q * TPB; fm[q] = i < RP * 5 ? __ldcg(fa.stage_mask + b0 * 5 + i) : 0.0f; }
+  }
+  if (tid < RP) {
+    st.x[g] = rx; st.y[g] = ry; st.theta[g] = rth; st.goal_x[g] = rgx; st.goal_y[g] = rgy;
+    st.velr_x[g] = 0; st.velr_y[g] = 0; st.velr_r[g] = 0;
+    st.vel_x[g] = 0; st.vel_y[g] = 0; st.vel_r[g] = 0;
+    st.thrust_l[g] = 0; st.thrust_r[g] = 0;
+    st.flags[g] = 0;
+  }
+  if (tid < OP) st.obstacles[(size_t)e * OP + tid] = ob;
+  if (tid < CP) st.cores[(size_t)e * CP + tid] = co;
+  if (tid < 3) (tid == 0 ? st.n_robots : tid == 1 ? st.n_obs : st.n_cores)[e] = cnt;
+  if (tid == 3) st.ep_steps[e] = 0;
+  if (fa.stage_self) {
+#pragma unroll
+    for (int q = 0; q < IT_O; ++q) { const int i = tid + q * TPB; if (i < RP * 25) out.obs_objects[b0 * 25 + i] = fo[q]; }
+#pragma unroll
+    for (int q = 0; q < IT_S; ++q) { const int i = tid + q * TPB; if (i < RP * 7) out.obs_self[b0 * 7 + i] = fs[q]; }
+#pragma unroll
+    for (int q = 0; q < IT_M; ++q) { const int i = tid + q * TPB; if (i < RP * 5) out.obs_mask[b0 * 5 + i] = fm[q]; }
+  }
+}
+
+
 template <bool INJECT, bool FUSED>
 __global__ void __launch_bounds__(TPB, 7)
 env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L,
@@ -315,65 +391,96 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
   bool second = false;
   for (;;) {
 
-  // ---- phase 0: per-env tables and the pre-step poses (for the noise prefetch filter) ----
+  // ---- phase 0: per-env tables and the pre-step poses (for the noise prefetch filter).  Every
+  // global load of the prologue — counts, buoy / vortex tables, the state row, the fused tail's
+  // episode number and stage tag — is issued before the first dependent use, so a CTA pays ONE
+  // DRAM round trip with cold data instead of one per dependent stage. ----
+  int c_nr = 0, c_no = 0, c_nc = 0, c_ep = 0, c_epn = 0, c_epi = 0, c_tag = -1;
+  bool c_v = false;
   if (tid < EPB) {
     const int e = e0 + tid;
-    const bool v = second ? m.ended[tid] != 0 : (e < E && (!env_mask || env_mask[e]));
-    m.ok[tid] = v;
-    m.nr[tid] = v ? min(st.n_robots[e], RP) : 0;
-    m.no[tid] = v ? min(st.n_obs[e], OP) : 0;
-    m.nc[tid] = v ? min(st.n_cores[e], CP) : 0;
-    m.ep[tid] = v ? st.ep_steps[e] : 0;
-    if (!second && fa.step_arr) m.epn[tid] = v ? fa.step_arr[e] : 0;
+    c_v = second ? m.ended[tid] != 0 : (e < E && (!env_mask || env_mask[e]));
+    if (c_v) {
+      c_nr = st.n_robots[e]; c_no = st.n_obs[e]; c_nc = st.n_cores[e]; c_ep = st.ep_steps[e];
+      if (!second && fa.step_arr) c_epn = fa.step_arr[e];
+    }
   }
-  if (!second) {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
-    const int e = e0 + tid;
-    const bool mine = tid < EPB && e < E && (!env_mask || env_mask[e]);
-    if (!__syncthreads_or(mine)) return;
-  } else {
-    __syncthreads();
-  }
-  for (int i = tid; i < EPB * OP; i += TPB) {
-    const int el = i / OP;
-    m.obst[i] = m.ok[el] ? st.obstacles[(size_t)(e0 + el) * OP + (i - el * OP)] : make_float4(0, 0, 0, 0);
-  }
-  for (int i = tid; i < EPB * CP; i += TPB) {
-    const int el = i / CP;
-    m.cores[i] = m.ok[el] ? st.cores[(size_t)(e0 + el) * CP + (i - el * CP)] : make_float4(0, 0, 0, 0);
-  }
-  // warp 0, one lane per ASV: the whole state row is requested here, one DRAM round trip ahead of
-  // the integration that consumes it
+  const int n_tab_o = min(EPB, E - e0) * OP, n_tab_c = min(EPB, E - e0) * CP;  // tables are contiguous over the CTA's envs
+  float4 t_ob = make_float4(0, 0, 0, 0), t_co = make_float4(0, 0, 0, 0);
+  if (tid < n_tab_o) t_ob = st.obstacles[(size_t)e0 * OP + tid];
+  if (tid < n_tab_c) t_co = st.cores[(size_t)e0 * CP + tid];
+  // one lane per ASV: the whole state row, one DRAM round trip ahead of the integration that consumes it
   float p_x = 0, p_y = 0, p_th = 0, vr0 = 0, vr1 = 0, vr2 = 0, v0 = 0, v1 = 0, v2 = 0, Tl = 0, Tr = 0,
         gx = 0, gy = 0;
   float2 act = make_float2(0.0f, 0.0f);
-  int act_id = 0;
+  int act_id = 0, my_nr = 0;
+  uint32_t f_in = (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
+  bool my_v = false;
   if (tid < A) {
     const int el = tid / RP, r = tid - el * RP;
-    const bool present = m.ok[el] && r < m.nr[el];
-    const size_t g = (size_t)(e0 + el) * RP + r;
-    uint32_t f = (uint32_t)ASVRL_F_DEACTIVATED;  // absent == not on the map
-    if (present) {
+    const int e = e0 + el;
+    my_v = second ? m.ended[el] != 0 : (e < E && (!env_mask || env_mask[e]));
+    if (my_v) {
+      const size_t g = (size_t)e * RP + r;
+      my_nr = st.n_robots[e];
       p_x = st.x[g]; p_y = st.y[g]; p_th = st.theta[g];
       vr0 = st.velr_x[g]; vr1 = st.velr_y[g]; vr2 = st.velr_r[g];
       v0 = st.vel_x[g]; v1 = st.vel_y[g]; v2 = st.vel_r[g];
       Tl = st.thrust_l[g]; Tr = st.thrust_r[g];
       gx = st.goal_x[g]; gy = st.goal_y[g];
-      f = st.flags[g];
+      f_in = st.flags[g];
       if (dyn) {
         if (mode & ASVRL_M_DISCRETE) act_id = ((const int32_t*)actions)[g];
         else act = ((const float2*)actions)[g];
       }
     }
+  }
+  if (FUSED && !second && tid < EPB && e0 + tid < E) {  // last of the batch: an acquire orders later loads behind it
+    c_epi = fa.episode_idx[e0 + tid];
+    if (fa.stage_tag) c_tag = ld_acquire(fa.stage_tag + e0 + tid);
+  }
+  // ---- first uses ----
+  if (tid < EPB) {
+    m.ok[tid] = c_v;
+    m.nr[tid] = min(c_nr, RP); m.no[tid] = min(c_no, OP); m.nc[tid] = min(c_nc, CP);
+    m.ep[tid] = c_ep;
+    if (!second && fa.step_arr) m.epn[tid] = c_epn;
+    if (FUSED && !second) {
+      const bool ready = fa.stage_tag && c_tag == c_epi + 1;
+      m.pre_ep[tid] = c_epi + 1;
+      m.pre_tag[tid] = ready;
+      // an env whose clock runs out in this step is certain to end: pull its staged episode into L2
+      // now, 20 us before the tail copies it
+      if (ready && c_v && dyn && c_ep >= k.max_ep) prefetch_stage(fa, e0 + tid, RP, OP, CP);
+    }
+  }
+  if (tid < EPB * OP) m.obst[tid] = t_ob;
+  if (tid < EPB * CP) m.cores[tid] = t_co;
+  for (int i = tid + TPB; i < EPB * OP; i += TPB)  // shapes with more than 128 table rows per CTA
+    m.obst[i] = i < n_tab_o ? st.obstacles[(size_t)e0 * OP + i] : make_float4(0, 0, 0, 0);
+  for (int i = tid + TPB; i < EPB * CP; i += TPB)
+    m.cores[i] = i < n_tab_c ? st.cores[(size_t)e0 * CP + i] : make_float4(0, 0, 0, 0);
+  if (tid < A) {
+    const int el = tid / RP, r = tid - el * RP;
+    if (!(my_v && r < min(my_nr, RP))) {  // absent robot (or masked env): zero state, not on the map
+      p_x = p_y = p_th = vr0 = vr1 = vr2 = v0 = v1 = v2 = Tl = Tr = gx = gy = 0.0f;
+      act = make_float2(0.0f, 0.0f); act_id = 0;
+      f_in = (uint32_t)ASVRL_F_DEACTIVATED;
+    }
     m.ox[tid] = p_x;
     m.oy[tid] = p_y;
     m.osp[tid] = sqrtf(v0 * v0 + v1 * v1);
-    m.fl0[tid] = f;
+    m.fl0[tid] = f_in;
     m.el_of[tid] = (uint8_t)el;
     m.r_of[tid] = (uint8_t)r;
     m.det_lo[tid] = 0; m.det_hi[tid] = 0;
   }
   if (tid < 4) m.cnt[tid] = 0;
-  __syncthreads();
+  if (!second) {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
+    if (!__syncthreads_or(tid < EPB && c_v)) return;
+  } else {
+    __syncthreads();
+  }
 
   // ---- phase P: compact the (ego, slot) pairs that can possibly end up detected into plist, so
   // the expensive per-pair work below (Philox, Box-Muller, von Mises, fp64 geometry) runs with
@@ -764,12 +871,14 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
                              st.vel_r, st.thrust_l, st.thrust_r, (float*)st.goal_x, (float*)st.goal_y,
                              st.flags, (int32_t*)st.n_robots, (int32_t*)st.n_obs, (int32_t*)st.n_cores,
                              st.ep_steps, (float4*)st.obstacles, (float4*)st.cores};
-      // thread el decides for its env: 2 = the stage holds its next episode, 1 = generate it here
+      // thread el decides for its env: 2 = the stage holds its next episode, 1 = generate it here.
+      // Episode number and tag were read in phase 0; only a stage that was not ready then is
+      // looked at again (the side stream may have published it meanwhile).
       if (tid < EPB && my_end) {
         const int e = e0 + tid;
-        const int ep = fa.episode_idx[e] + 1;
+        const int ep = m.pre_ep[tid];
         m.epn[tid] = ep;
-        if (fa.stage_tag && ld_acquire(fa.stage_tag + e) == ep) m.ended[tid] = 2;
+        if (m.pre_tag[tid] || (fa.stage_tag && ld_acquire(fa.stage_tag + e) == ep)) m.ended[tid] = 2;
       }
       __syncthreads();
       static_assert(TPB == 128, "reset_env_cta resolves rounds of 128 candidates");
@@ -779,13 +888,9 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
         if (!how) continue;
         const int e = e0 + el;
         if (how == 2) {
-          take_stage(rs, fa.stage, e, RP, OP, CP, tid, TPB);
-          if (fa.stage_self) {  // its first observation was staged too: nothing left to compute
-            const size_t b0 = a0 + (size_t)el * RP;
-            for (int i = tid; i < RP * 25; i += TPB) out.obs_objects[b0 * 25 + i] = __ldcg(fa.stage_objects + b0 * 25 + i);
-            for (int i = tid; i < RP * 7; i += TPB) out.obs_self[b0 * 7 + i] = __ldcg(fa.stage_self + b0 * 7 + i);
-            for (int i = tid; i < RP * 5; i += TPB) out.obs_mask[b0 * 5 + i] = __ldcg(fa.stage_mask + b0 * 5 + i);
-          }
+          // scenario AND first observation of the staged episode: every load first, then every
+          // store, so the copy costs one DRAM round trip and not one per array
+          take_stage_batched(rs, fa, out, e, RP, OP, CP, tid);
         } else
           reset_env_cta(fa.rk, rs, e, env_offset + e, fa.want_robots[e], fa.want_cores[e], fa.want_obs[e],
                         fa.min_sg[e], seed, (uint64_t)m.epn[el], RP, OP, CP, m.rs_sg, m.rs_core, m.rs_obs,

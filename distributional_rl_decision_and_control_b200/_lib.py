@@ -48,6 +48,14 @@ _SIGNATURES = {
                                     C.c_int, f32p, f32p, u64p, vp]),
     "asvrl_qhuber_fwd_bwd": (C.c_int, [f32p, f32p, f32p, f32p, f32p, C.c_float, C.c_float, C.c_int,
                                        C.c_int, C.c_int, f32p, f32p, f32p, u32p, vp]),
+    "asvrl_iqn_scale_relu_fwd": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_int, C.c_int, f32p, vp]),
+    "asvrl_iqn_scale_relu_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, C.c_int, f32p, f32p,
+                                           f32p, f32p, u32p, vp]),
+    "asvrl_iqn_scale_relu_bwd_partials": (C.c_long, [C.c_int, C.c_int]),
+    "asvrl_iqn_head_fwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, vp]),
+    "asvrl_iqn_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, f32p, f32p, f32p,
+                                     f32p, u32p, vp]),
+    "asvrl_iqn_head_bwd_partials": (C.c_long, [C.c_int, C.c_int]),
 }
 EXPORTED = tuple(_SIGNATURES)
 
@@ -300,6 +308,72 @@ def iqn_tau_cos(B, N, n_cos, device, tau_in=None, seed=0, counter=0, cvar=1.0, t
                                  ptr(tau_out), ptr(cos_out), ptr(counter_dev, torch.int64), stream_ptr())
     check(rc, "asvrl_iqn_tau_cos")
     return tau_out, cos_out
+
+
+# ------------------------------------------------------------------ K5: critic trunk glue
+_TRUNK_WS = {}
+
+
+def _trunk_ws(device, n_floats):
+    """Per (device, stream) scratch for the deterministic cross-CTA reductions of K5."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _TRUNK_WS.get(key)
+    if ws is None or ws[0].numel() < n_floats:
+        ws = (torch.empty((max(int(n_floats), 1 << 16),), dtype=torch.float32, device=device),
+              ws[1] if ws is not None else torch.zeros((1,), dtype=torch.int32, device=device))
+        _TRUNK_WS[key] = ws
+    return ws
+
+
+def iqn_scale_relu_fwd(pre, bias, scale, n_tau):
+    M, D = pre.shape
+    B = M // n_tau
+    out = torch.empty_like(pre)
+    rc = lib().asvrl_iqn_scale_relu_fwd(ptr(pre, torch.float32), ptr(bias, torch.float32),
+                                        ptr(scale, torch.float32), B, n_tau, D, ptr(out), stream_ptr())
+    check(rc, "asvrl_iqn_scale_relu_fwd")
+    return out
+
+
+def iqn_scale_relu_bwd(dout, pre, bias, scale, n_tau, want_dpre=True, want_dscale=True, want_dbias=True):
+    M, D = pre.shape
+    B = M // n_tau
+    dev = pre.device
+    dpre = torch.empty_like(pre) if want_dpre else None
+    dscale = torch.empty((B, D), dtype=torch.float32, device=dev) if want_dscale else None
+    dbias = torch.empty((D,), dtype=torch.float32, device=dev) if want_dbias else None
+    part, cnt = _trunk_ws(dev, lib().asvrl_iqn_scale_relu_bwd_partials(B, D)) if want_dbias else (None, None)
+    rc = lib().asvrl_iqn_scale_relu_bwd(ptr(dout, torch.float32), ptr(pre, torch.float32),
+                                        ptr(bias, torch.float32), ptr(scale, torch.float32), B, n_tau, D,
+                                        ptr(dpre), ptr(dscale), ptr(dbias), ptr(part), ptr(cnt), stream_ptr())
+    check(rc, "asvrl_iqn_scale_relu_bwd")
+    return dpre, dscale, dbias
+
+
+def iqn_head_fwd(pre, bias, w, b_out):
+    M, D = pre.shape
+    z = torch.empty((M,), dtype=torch.float32, device=pre.device)
+    rc = lib().asvrl_iqn_head_fwd(ptr(pre, torch.float32), ptr(bias, torch.float32), ptr(w, torch.float32),
+                                  ptr(b_out, torch.float32), M, D, ptr(z), stream_ptr())
+    check(rc, "asvrl_iqn_head_fwd")
+    return z
+
+
+def iqn_head_bwd(dz, pre, bias, w, want_params=True):
+    M, D = pre.shape
+    dev = pre.device
+    dpre = torch.empty_like(pre)
+    dw = dbias = dbo = part = cnt = None
+    if want_params:
+        dw = torch.empty((D,), dtype=torch.float32, device=dev)
+        dbias = torch.empty((D,), dtype=torch.float32, device=dev)
+        dbo = torch.empty((1,), dtype=torch.float32, device=dev)
+        part, cnt = _trunk_ws(dev, lib().asvrl_iqn_head_bwd_partials(M, D))
+    rc = lib().asvrl_iqn_head_bwd(ptr(dz, torch.float32), ptr(pre, torch.float32), ptr(bias, torch.float32),
+                                  ptr(w, torch.float32), M, D, ptr(dpre), ptr(dw), ptr(dbias), ptr(dbo),
+                                  ptr(part), ptr(cnt), stream_ptr())
+    check(rc, "asvrl_iqn_head_bwd")
+    return dpre, dw, dbias, dbo
 
 
 # ------------------------------------------------------------------ K2: device replay ring

@@ -62,7 +62,8 @@ class Agent():
                  process_group=None,
                  rank=0,
                  matmul_precision="fp32",
-                 replay_lanes=1):
+                 replay_lanes=1,
+                 fused_trunk=True):
         self.device = torch.device(device) if not isinstance(device, torch.device) else device
         self.LR = LR
         self.TAU = TAU
@@ -81,6 +82,9 @@ class Agent():
         if matmul_precision not in ("fp32", "tf32"):
             raise ValueError("matmul_precision must be 'fp32' or 'tf32'")
         self.matmul_precision = matmul_precision
+        # AC-IQN: the critic's quantile trunk runs through K5 (policy/iqn_ops.critic_trunk); False
+        # keeps the module-by-module autograd path (the torch fp32 reference of the parity tests)
+        self.fused_trunk = bool(fused_trunk)
         self._graph = None
         self._dims = (self_dimension, object_dimension, max_object_num, self_feature_dimension,
                       object_feature_dimension, concat_feature_dimension, hidden_dimension)
@@ -330,10 +334,13 @@ class Agent():
 
         # critic step ------------------------------------------------------------------
         self.critic_optimizer.zero_grad(set_to_none=True)
+        fused = self.fused_trunk
         with torch.no_grad():
             next_actions = target.actor(next_states)                     # AGENT:396
-            z_next, _ = target.critic(next_states, next_actions, N, taus=taus.get("target"))  # AGENT:399
-        z, tau = local.critic(states, actions, N, taus=taus.get("local"))  # AGENT:403
+            crit_t = target.critic.forward_fused if fused else target.critic
+            z_next, _ = crit_t(next_states, next_actions, N, taus=taus.get("target"))  # AGENT:399
+        crit = local.critic.forward_fused if fused else local.critic
+        z, tau = crit(states, actions, N, taus=taus.get("local"))        # AGENT:403
         critic_loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones,
                                              self.GAMMA, 1.0)            # K4 = AGENT:401-412
         critic_loss.backward()
@@ -344,7 +351,11 @@ class Agent():
 
         # actor step -------------------------------------------------------------------
         self.actor_optimizer.zero_grad(set_to_none=True)
-        q, _ = local.critic(states, local.actor(states), N, taus=taus.get("actor"))  # AGENT:420-422
+        if fused:
+            q, _ = local.critic.forward_fused(states, local.actor(states), N, taus=taus.get("actor"),
+                                              param_grads=False)         # AGENT:420-422
+        else:
+            q, _ = local.critic(states, local.actor(states), N, taus=taus.get("actor"))
         actor_loss = -q.mean()
         actor_loss.backward()
         actor_params = list(local.actor.parameters())

@@ -126,6 +126,37 @@ tau_cos_kernel(const float* __restrict__ tau_in, uint64_t seed, uint64_t counter
   }
 }
 
+// n_cos % 4 == 0 (the shipped 64): one thread per float4 of cosines, n_cos/4 threads per row, so
+// a launch at C3 is 524 288 independent threads instead of 1 024 warps walking 32 rows each.
+// Every thread of a row re-derives the row's tau (one Philox block, shared by 4 rows).
+__global__ void __launch_bounds__(256)
+tau_cos4_kernel(const float* __restrict__ tau_in, uint64_t seed, uint64_t counter, float cvar,
+                int rows, int nc4, float* __restrict__ tau_out, float4* __restrict__ cos_out,
+                const uint64_t* __restrict__ counter_dev) {
+  if (counter_dev) counter += *counter_dev;
+  const int total = rows * nc4;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    const int row = i / nc4, c = i - row * nc4;
+    float t;
+    if (tau_in) {
+      t = tau_in[row];
+    } else {  // torch.rand(B, N) * cvar, ACIQN:419-422
+      const uint4 w = philox_at(seed, STREAM_TAU, counter, (int64_t)(row >> 2), 0u, 0u, 0u);
+      const uint32_t word = (row & 3) == 0 ? w.x : (row & 3) == 1 ? w.y : (row & 3) == 2 ? w.z : w.w;
+      t = __fmul_rn(u01(word), cvar);
+    }
+    if (c == 0 && tau_out) tau_out[row] = t;
+    const double PI = 3.14159265358979323846;
+    const int i0 = 4 * c;
+    float4 v;
+    v.x = cosf(__fmul_rn(t, (float)(PI * (double)(i0 + 0))));  // ACIQN:397, 424
+    v.y = cosf(__fmul_rn(t, (float)(PI * (double)(i0 + 1))));
+    v.z = cosf(__fmul_rn(t, (float)(PI * (double)(i0 + 2))));
+    v.w = cosf(__fmul_rn(t, (float)(PI * (double)(i0 + 3))));
+    cos_out[i] = v;
+  }
+}
+
 }  // namespace asvrl
 
 using namespace asvrl;
@@ -150,6 +181,14 @@ extern "C" int asvrl_iqn_tau_cos(const float* tau_in, uint64_t seed, uint64_t co
   if (!cos_out) return fail(ASVRL_E_BADARG, "asvrl_iqn_tau_cos: null cos_out");
   if (batch < 1 || n_tau < 1 || n_cos < 1) return fail(ASVRL_E_BADARG, "asvrl_iqn_tau_cos: bad sizes");
   const int rows = batch * n_tau;
+  if (n_cos % 4 == 0 && (long)rows * (n_cos / 4) < (1L << 31)) {
+    const long total = (long)rows * (n_cos / 4);
+    long grid = (total + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    tau_cos4_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>(tau_in, seed, counter, cvar, rows, n_cos / 4,
+                                                                 tau_out, (float4*)cos_out, counter_dev);
+    return check_launch("asvrl_iqn_tau_cos");
+  }
   const int groups = (rows + 31) / 32;
   int grid = (groups + 7) / 8;  // 8 warps per CTA
   if (grid > 148 * 8) grid = 148 * 8;

@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .iqn_ops import TauSampler
+from .iqn_ops import TauSampler, critic_trunk
 
 
 def encoder(input_dimension, output_dimension):
@@ -161,6 +161,29 @@ class Critic(_ObservationTower):
         h = (self.action_encoder(actions).unsqueeze(1) * h).reshape(B * num_tau, self.hidden_dimension)
         h = F.relu(self.hidden_layer_2(h))
         return self.output_layer(h).reshape(B, num_tau), taus
+
+    def forward_fused(self, x, actions, num_tau=8, cvar=1.0, taus=None, param_grads=True):
+        """Same function as ``forward`` with the trunk's glue in K5 (one launch per layer instead
+        of autograd's chain of element-wise kernels).  ``param_grads=False`` is the actor update
+        (AGENT:420-427): only d z / d actions flows back, the critic's own parameter gradients —
+        which the reference computes and then discards at the next zero_grad — are skipped."""
+        assert len(x) == 3, "The number of elements in state must be 3!"
+        ps = [self.cos_embedding.weight, self.cos_embedding.bias, self.hidden_layer.weight,
+              self.hidden_layer.bias, self.hidden_layer_2.weight, self.hidden_layer_2.bias,
+              self.output_layer.weight, self.output_layer.bias]
+        enc = self.action_encoder[0]
+        if param_grads:
+            feats = self._features(x)
+            aenc = self.action_encoder(actions)
+        else:
+            with torch.no_grad():
+                feats = self._features(x)
+            ps = [p.detach() for p in ps]
+            aenc = F.relu(F.linear(actions, enc.weight.detach(), enc.bias.detach()))
+        B = feats.shape[0]
+        cos, taus = self.calc_cos(B, num_tau, cvar, taus)
+        z = critic_trunk(cos.reshape(B * num_tau, self.n), feats, aenc, *ps, num_tau)
+        return z, taus
 
     def get_constructor_parameters(self):
         return dict(self_dimension=self.self_dimension, object_dimension=self.object_dimension,

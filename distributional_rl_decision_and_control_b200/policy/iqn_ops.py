@@ -67,3 +67,68 @@ def quantile_huber_loss(z, tau, z_next, r, done, gamma=0.99, kappa=1.0):
         ws = _WS[key] = torch.zeros(1, dtype=torch.int32, device=z.device)
     return _QuantileHuber.apply(z, tau.reshape(z.shape), z_next, r.reshape(-1), done.reshape(-1),
                                 gamma, kappa, ws)
+
+
+class _CriticTrunk(torch.autograd.Function):
+    """The critic's quantile trunk (ACIQN:453-480) with K5 between the GEMMs:
+
+        P1 = cos Wc^T          H1 = feats[b] * relu(P1 + bc)
+        P2 = H1 Wh^T           H2 = aenc[b]  * relu(P2 + bh)
+        P3 = H2 Wh2^T          z  = relu(P3 + bh2) . wo + bo
+
+    The three contractions are plain torch.mm calls (cuBLAS); everything else is one launch per
+    layer forward and one backward.  The backward computes only what ``needs_input_grad`` asks
+    for: the actor update needs d z / d aenc alone (one GEMM and two launches)."""
+
+    @staticmethod
+    def forward(ctx, cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau):
+        cos, feats, aenc = cos.contiguous(), feats.contiguous(), aenc.contiguous()
+        P1 = cos @ Wc.t()
+        H1 = _lib.iqn_scale_relu_fwd(P1, bc, feats, n_tau)
+        P2 = H1 @ Wh.t()
+        H2 = _lib.iqn_scale_relu_fwd(P2, bh, aenc, n_tau)
+        P3 = H2 @ Wh2.t()
+        z = _lib.iqn_head_fwd(P3, bh2, wo.reshape(-1), bo)
+        ctx.save_for_backward(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, P1, H1, P2, H2, P3)
+        ctx.n_tau = n_tau
+        return z.view(feats.shape[0], n_tau)
+
+    @staticmethod
+    def backward(ctx, dz):
+        cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, P1, H1, P2, H2, P3 = ctx.saved_tensors
+        n_tau = ctx.n_tau
+        need = ctx.needs_input_grad
+        g = [None] * 12
+        head_params = need[7] or need[8] or need[9] or need[10]
+        dP3, dwo, dbh2, dbo = _lib.iqn_head_bwd(dz.contiguous().view(-1), P3, bh2, wo.reshape(-1), head_params)
+        if head_params:
+            g[8], g[9], g[10] = dbh2, dwo.view_as(wo), dbo
+            if need[7]:
+                g[7] = dP3.t() @ H2
+        layer1 = need[1] or need[3] or need[4]
+        layer2 = layer1 or need[5] or need[6]
+        if not (layer2 or need[2]):
+            return tuple(g)
+        dH2 = dP3 @ Wh2
+        dP2, daenc, dbh = _lib.iqn_scale_relu_bwd(dH2, P2, bh, aenc, n_tau, want_dpre=layer2,
+                                                  want_dscale=need[2], want_dbias=need[6])
+        g[2], g[6] = daenc, dbh
+        if not layer2:
+            return tuple(g)
+        if need[5]:
+            g[5] = dP2.t() @ H1
+        if layer1:
+            dH1 = dP2 @ Wh
+            dP1, dfeats, dbc = _lib.iqn_scale_relu_bwd(dH1, P1, bc, feats, n_tau, want_dpre=need[3],
+                                                       want_dscale=need[1], want_dbias=need[4])
+            g[1], g[4] = dfeats, dbc
+            if need[3]:
+                g[3] = dP1.t() @ cos
+        return tuple(g)
+
+
+def critic_trunk(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau):
+    """cos (B*N, n_cos), feats (B, D1), aenc (B, D2) and the four layers' parameters -> z (B, N)."""
+    if not cos.is_cuda:
+        raise RuntimeError("critic_trunk runs on CUDA only (no CPU fallback)")
+    return _CriticTrunk.apply(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, int(n_tau))

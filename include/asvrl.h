@@ -382,6 +382,34 @@ ASVRL_API int asvrl_qhuber_fwd_bwd(const float* z, const float* tau, const float
                                    int batch, int n, int n_next, float* loss_per_sample,
                                    float* grad_z, float* loss, uint32_t* workspace, void* stream);
 
+/* K5 — the element-wise / reduction glue of the IQN critic's quantile trunk (forward and the
+ * autograd backward of ACIQN:453-460, 470-474, 476-480); the dense layers between the calls stay
+ * plain GEMMs.  Rows m = b * n_tau + n.  dim: multiple of 4 with (dim / 4) dividing 256.
+ *   scale_relu fwd: out[m][d] = scale[b][d] * relu(pre[m][d] + bias[d])
+ *   scale_relu bwd: dpre[m][d] = dout[m][d] * scale[b][d] * 1[pre+bias > 0]   (nullable)
+ *                   dscale[b][d] = sum_n dout[m][d] * relu(pre[m][d] + bias[d]) (nullable)
+ *                   dbias[d] = sum_m dpre[m][d]                                (nullable)
+ *   head fwd:       z[m] = sum_d relu(pre[m][d] + bias[d]) * w[d] + b_out[0]
+ *   head bwd:       dpre[m][d] = dz[m] * w[d] * 1[pre+bias > 0];  dw[d] = sum_m dz[m] relu(pre+bias);
+ *                   dbias[d] = sum_m dpre[m][d];  db_out[0] = sum_m dz[m]   (the three nullable together)
+ * partials: caller-owned scratch of asvrl_iqn_*_bwd_partials() floats; counter: one zero-initialised
+ * uint32 (left zero).  Reductions are summed in a fixed order (deterministic). */
+ASVRL_API int asvrl_iqn_scale_relu_fwd(const float* pre, const float* bias, const float* scale,
+                                       int batch, int n_tau, int dim, float* out, void* stream);
+ASVRL_API int asvrl_iqn_scale_relu_bwd(const float* dout, const float* pre, const float* bias,
+                                       const float* scale, int batch, int n_tau, int dim,
+                                       float* dpre /* nullable */, float* dscale /* nullable */,
+                                       float* dbias /* nullable */, float* partials, uint32_t* counter,
+                                       void* stream);
+ASVRL_API long asvrl_iqn_scale_relu_bwd_partials(int batch, int dim);
+ASVRL_API int asvrl_iqn_head_fwd(const float* pre, const float* bias, const float* w,
+                                 const float* b_out /* nullable */, int rows, int dim, float* z,
+                                 void* stream);
+ASVRL_API int asvrl_iqn_head_bwd(const float* dz, const float* pre, const float* bias, const float* w,
+                                 int rows, int dim, float* dpre, float* dw, float* dbias, float* db_out,
+                                 float* partials, uint32_t* counter, void* stream);
+ASVRL_API long asvrl_iqn_head_bwd_partials(int rows, int dim);
+
 #ifdef __cplusplus
 }
 #endif

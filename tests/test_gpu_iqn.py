@@ -86,7 +86,7 @@ def test_tau_cos_golden_reference():
 
 
 def test_tau_cos_oracle_c3_and_ragged(oracle):
-    for B, N, n_cos in ((1024, 32, 64), (5, 7, 64), (3, 1, 16), (33, 8, 100)):
+    for B, N, n_cos in ((1024, 32, 64), (5, 7, 64), (3, 1, 16), (33, 8, 100), (4, 3, 30), (9, 2, 7)):
         rng = np.random.RandomState(B)
         tau = rng.rand(B, N).astype(np.float32)
         _, cos = _lib.iqn_tau_cos(B, N, n_cos, DEV, tau_in=torch.from_numpy(tau).to(DEV))

@@ -1,0 +1,139 @@
+"""K5 (critic trunk glue) on the B200 through the C-ABI: each kernel against the same op written
+in stock PyTorch (float64 on the GPU as the yardstick), and the fused critic path against the
+module-by-module autograd path of the same Critic — forward quantiles, every parameter gradient,
+and d z / d actions of the actor update."""
+import pytest
+import torch
+
+from distributional_rl_decision_and_control_b200 import _lib
+from distributional_rl_decision_and_control_b200.agent import Agent
+from distributional_rl_decision_and_control_b200.policy.AC_IQN_model import Critic
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+RTOL = 1e-5
+
+
+def close(got, want, what, rtol=RTOL):
+    """1e-5 of the tensor's scale (sums of up to 32768 fp32 terms are compared to float64)."""
+    want = want.to(torch.float64)
+    err = (got.to(torch.float64) - want).abs().max().item()
+    scale = max(want.abs().max().item(), 1e-6)
+    assert err <= rtol * scale, f"{what}: err {err:.3e} vs scale {scale:.3e}"
+
+
+@pytest.mark.parametrize("B,N,D", [(1024, 32, 256), (64, 8, 128), (5, 3, 256), (1, 1, 128), (130, 7, 64)])
+def test_scale_relu_fwd_bwd(B, N, D):
+    g = torch.Generator(device=DEV).manual_seed(B + N + D)
+    M = B * N
+    pre = torch.randn((M, D), device=DEV, generator=g)
+    bias = torch.randn((D,), device=DEV, generator=g)
+    scale = torch.relu(torch.randn((B, D), device=DEV, generator=g))  # a ReLU feature: zeros included
+    dout = torch.randn((M, D), device=DEV, generator=g)
+    out = _lib.iqn_scale_relu_fwd(pre, bias, scale, N)
+    p64, b64, s64 = (t.double().requires_grad_(True) for t in (pre, bias, scale))
+    ref = (s64.unsqueeze(1) * torch.relu(p64 + b64).view(B, N, D)).view(M, D)
+    close(out, ref.detach(), "out")
+    ref.backward(dout.double())
+    dpre, dscale, dbias = _lib.iqn_scale_relu_bwd(dout, pre, bias, scale, N)
+    close(dpre, p64.grad, "dpre")
+    close(dscale, s64.grad, "dscale")
+    close(dbias, b64.grad, "dbias")
+    # partial requests: the actor update asks for dscale alone
+    a, b, c = _lib.iqn_scale_relu_bwd(dout, pre, bias, scale, N, want_dpre=False, want_dbias=False)
+    assert a is None and c is None
+    assert torch.equal(b, dscale)
+    # deterministic reductions, and the counter is left clean for the next call
+    again = _lib.iqn_scale_relu_bwd(dout, pre, bias, scale, N)
+    assert all(torch.equal(x, y) for x, y in zip(again, (dpre, dscale, dbias)))
+
+
+@pytest.mark.parametrize("M,D", [(32768, 128), (512, 128), (15, 256), (1, 64), (1000, 32)])
+def test_head_fwd_bwd(M, D):
+    g = torch.Generator(device=DEV).manual_seed(M + D)
+    pre = torch.randn((M, D), device=DEV, generator=g)
+    bias = torch.randn((D,), device=DEV, generator=g)
+    w = torch.randn((D,), device=DEV, generator=g)
+    bo = torch.randn((1,), device=DEV, generator=g)
+    dz = torch.randn((M,), device=DEV, generator=g)
+    z = _lib.iqn_head_fwd(pre, bias, w, bo)
+    p64, b64, w64, o64 = (t.double().requires_grad_(True) for t in (pre, bias, w, bo))
+    ref = torch.relu(p64 + b64) @ w64 + o64
+    close(z, ref.detach(), "z")
+    ref.backward(dz.double())
+    dpre, dw, dbias, dbo = _lib.iqn_head_bwd(dz, pre, bias, w)
+    close(dpre, p64.grad, "dpre")
+    close(dw, w64.grad, "dw")
+    close(dbias, b64.grad, "dbias")
+    close(dbo, o64.grad, "db_out")
+    only, n1, n2, n3 = _lib.iqn_head_bwd(dz, pre, bias, w, want_params=False)
+    assert n1 is None and n2 is None and n3 is None and torch.equal(only, dpre)
+
+
+def _critic_inputs(B, seed):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    own = torch.randn((B, 7), device=DEV, generator=g) * torch.tensor([20, 20, 2, 2, 0.5, 500, 500.0], device=DEV)
+    obj = torch.randn((B, 5, 5), device=DEV, generator=g) * torch.tensor([15, 15, 1, 1, 1.0], device=DEV)
+    cnt = torch.randint(0, 6, (B,), device=DEV, generator=g)
+    mask = (torch.arange(5, device=DEV)[None, :] < cnt[:, None]).float()
+    obj = obj * mask[..., None]
+    act = torch.rand((B, 2), device=DEV, generator=g) * 2 - 1
+    return (own, obj, mask), act
+
+
+@pytest.mark.parametrize("B,N", [(64, 8), (1024, 32), (3, 5)])
+def test_fused_critic_matches_module_path(B, N):
+    crit = Critic(7, 5, 5, 56, 40, 256, 128, 2, device=DEV, seed=101).to(DEV)
+    x, act = _critic_inputs(B, 7 + B)
+    taus = torch.rand((B, N), device=DEV, generator=torch.Generator(device=DEV).manual_seed(1))
+    wz = torch.randn((B, N), device=DEV, generator=torch.Generator(device=DEV).manual_seed(2))
+
+    def run(fn, **kw):
+        for p in crit.parameters():
+            p.grad = None
+        a = act.clone().requires_grad_(True)
+        z, _ = fn(x, a, N, taus=taus, **kw)
+        (z * wz).sum().backward()
+        return z.detach(), a.grad, {n: (None if p.grad is None else p.grad.clone()) for n, p in crit.named_parameters()}
+
+    z0, da0, g0 = run(crit.forward)
+    z1, da1, g1 = run(crit.forward_fused)
+    close(z1, z0, "quantiles")
+    close(da1, da0, "d/d actions")
+    for n in g0:
+        close(g1[n], g0[n], f"grad {n}", rtol=2e-5)
+    # the actor update's variant: the same d/d actions, no parameter gradients at all
+    z2, da2, g2 = run(crit.forward_fused, param_grads=False)
+    assert torch.equal(z2, z1)
+    close(da2, da0, "d/d actions (actor pass)")
+    assert all(v is None for v in g2.values())
+
+
+def test_train_step_fused_equals_unfused():
+    """One AC-IQN update with injected batch and taus: K5 path vs the autograd path."""
+    B, N = 64, 8
+    x, act = _critic_inputs(B, 11)
+    nx, _ = _critic_inputs(B, 12)
+    g = torch.Generator(device=DEV).manual_seed(5)
+    batch = {"self": x[0], "obj": x[1], "mask": x[2], "act": act, "rew": torch.randn((B,), device=DEV, generator=g),
+             "nself": nx[0], "nobj": nx[1], "nmask": nx[2],
+             "done": (torch.rand((B,), device=DEV, generator=g) < 0.1).float()}
+    taus = {k: torch.rand((B, N), device=DEV, generator=g) for k in ("target", "local", "actor")}
+    res = []
+    for fused in (False, True):
+        ag = Agent(device=DEV, seed=100, agent_type="AC-IQN", BATCH_SIZE=B, num_tau=N, BUFFER_SIZE=1024,
+                   fused_trunk=fused)
+        before = [p.detach().clone() for p in ag.policy_local.critic.parameters()]
+        cl, al = ag.train_AC_IQN(batch=batch, taus=taus)
+        res.append((cl, al, [p.grad.clone() for p in ag.policy_local.actor.parameters()],
+                    torch.cat([(p.detach() - q).reshape(-1) for p, q in
+                               zip(ag.policy_local.critic.parameters(), before)])))
+    close(res[1][0], res[0][0], "critic loss")
+    close(res[1][1], res[0][1], "actor loss")
+    for a, b in zip(res[1][2], res[0][2]):
+        close(a, b, "clipped actor gradient", rtol=2e-5)
+    # Adam's first step is lr * g / (|g| + eps): elements with |g| near the fp32 noise of the two
+    # summation orders may differ, all others must agree
+    diff = (res[1][3] - res[0][3]).abs()
+    assert (diff > 1e-6).float().mean().item() < 0.01
+    assert diff.max().item() <= 2.1e-4

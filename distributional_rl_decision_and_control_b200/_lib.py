@@ -56,6 +56,9 @@ _SIGNATURES = {
     "asvrl_iqn_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, f32p, f32p, f32p,
                                      f32p, u32p, vp]),
     "asvrl_iqn_head_bwd_partials": (C.c_long, [C.c_int, C.c_int]),
+    "asvrl_tower_fwd": (C.c_int, [f32p] * 7 + [C.c_int] * 6 + [f32p, vp]),
+    "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
+    "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
 }
 EXPORTED = tuple(_SIGNATURES)
 
@@ -374,6 +377,33 @@ def iqn_head_bwd(dz, pre, bias, w, want_params=True):
                                   ptr(part), ptr(cnt), stream_ptr())
     check(rc, "asvrl_iqn_head_bwd")
     return dpre, dw, dbias, dbo
+
+
+# ------------------------------------------------------------------ K6: observation tower
+def tower_fwd(self_obs, objects, mask, w_self, b_self, w_obj, b_obj):
+    B, SD = self_obs.shape
+    K, OD = objects.shape[1], objects.shape[2]
+    SF, OF = w_self.shape[0], w_obj.shape[0]
+    feats = torch.empty((B, SF + K * OF), dtype=torch.float32, device=self_obs.device)
+    f = torch.float32
+    rc = lib().asvrl_tower_fwd(ptr(self_obs, f), ptr(objects, f), ptr(mask, f), ptr(w_self, f), ptr(b_self, f),
+                               ptr(w_obj, f), ptr(b_obj, f), B, SD, OD, K, SF, OF, ptr(feats), stream_ptr())
+    check(rc, "asvrl_tower_fwd")
+    return feats
+
+
+def tower_bwd(dfeats, feats, self_obs, objects, SF, OF):
+    B, SD = self_obs.shape
+    K, OD = objects.shape[1], objects.shape[2]
+    dev = self_obs.device
+    new = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
+    dws, dbs, dwo, dbo = new(SF, SD), new(SF), new(OF, OD), new(OF)
+    part, cnt = _trunk_ws(dev, lib().asvrl_tower_bwd_partials(B, K, SF, OF))
+    f = torch.float32
+    rc = lib().asvrl_tower_bwd(ptr(dfeats, f), ptr(feats, f), ptr(self_obs, f), ptr(objects, f), B, SD, OD, K,
+                               SF, OF, ptr(dws), ptr(dbs), ptr(dwo), ptr(dbo), ptr(part), ptr(cnt), stream_ptr())
+    check(rc, "asvrl_tower_bwd")
+    return dws, dbs, dwo, dbo
 
 
 # ------------------------------------------------------------------ K2: device replay ring

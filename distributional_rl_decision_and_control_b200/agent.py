@@ -139,6 +139,12 @@ class Agent():
                 samplers = []
             else:
                 raise RuntimeError("Agent type not implemented!")
+            if not self.fused_trunk:  # the torch reference path end to end: no K5, no K6
+                for pol in (self.policy_local, self.policy_target):
+                    mods = [pol] if isinstance(pol, torch.nn.Module) else \
+                        [m for m in vars(pol).values() if isinstance(m, torch.nn.Module)]
+                    for m in mods:
+                        m.fused_tower = False
             # local and target nets must not share a tau stream, and neither may two ranks
             for s, salt in samplers:
                 s.seed = (s.seed ^ salt ^ (self.rank * 0xD1B54A32D192ED03)) & 0xFFFFFFFFFFFFFFFF

@@ -1,0 +1,175 @@
+// tower.cu — K6: the observation tower shared by the actor and the critic, forward and backward
+// in one launch each (sm_100a).
+//
+// Replaces (reference paths under rfarl/rfarl/policy/AC_IQN_model.py):
+//   :284-308 / :428-451  self_encoder (7 -> 56, ReLU), object_encoder on each of the 5 padded
+//                        object rows (5 -> 40, ReLU), the mask product and the concat to 256
+// and the autograd backward of those lines with respect to the two encoders' parameters (the
+// observations are data: no input gradient exists).
+//
+//   feats[b][j]              = relu(Ws[j] . self[b] + bs[j])                       j < SF
+//   feats[b][SF + k*OF + f]  = mask[b][k] >= 0.5 ? relu(Wo[f] . obj[b][k] + bo[f]) : 0
+// The contractions have K = 7 and K = 5: this is HBM / launch bound work, not a GEMM.  Forward
+// moves 4*(SD + K*OD + K) B in and 4*W B out per sample; backward reads feats, dfeats and the
+// observations once.  The parameter gradients are per-CTA partials summed by the last CTA in a
+// fixed order (deterministic).
+#include "common.cuh"
+
+namespace asvrl {
+
+constexpr int TW_MAXIN = 8;  // self_dimension, object_dimension <= 8
+
+struct TowerDims {
+  int B, SD, OD, K, SF, OF, W;  // W = SF + K * OF
+};
+
+__global__ void __launch_bounds__(256)
+tower_fwd_kernel(const float* __restrict__ self_obs, const float* __restrict__ objects,
+                 const float* __restrict__ mask, const float* __restrict__ Ws, const float* __restrict__ bs,
+                 const float* __restrict__ Wo, const float* __restrict__ bo, TowerDims d,
+                 float* __restrict__ feats) {
+  extern __shared__ float tw_sm[];
+  float* sWs = tw_sm;                 // [SF][SD]
+  float* sbs = sWs + d.SF * d.SD;     // [SF]
+  float* sWo = sbs + d.SF;            // [OF][OD]
+  float* sbo = sWo + d.OF * d.OD;     // [OF]
+  for (int i = threadIdx.x; i < d.SF * d.SD; i += blockDim.x) sWs[i] = Ws[i];
+  for (int i = threadIdx.x; i < d.SF; i += blockDim.x) sbs[i] = bs[i];
+  for (int i = threadIdx.x; i < d.OF * d.OD; i += blockDim.x) sWo[i] = Wo[i];
+  for (int i = threadIdx.x; i < d.OF; i += blockDim.x) sbo[i] = bo[i];
+  __syncthreads();
+  const long total = (long)d.B * d.W;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int b = (int)(i / d.W), j = (int)(i - (long)b * d.W);
+    float acc;
+    if (j < d.SF) {
+      const float* x = self_obs + (size_t)b * d.SD;
+      acc = sbs[j];
+      for (int q = 0; q < d.SD; ++q) acc = fmaf(sWs[j * d.SD + q], x[q], acc);
+      acc = fmaxf(acc, 0.0f);
+    } else {
+      const int k = (j - d.SF) / d.OF, f = (j - d.SF) - k * d.OF;
+      const float* x = objects + ((size_t)b * d.K + k) * d.OD;
+      acc = sbo[f];
+      for (int q = 0; q < d.OD; ++q) acc = fmaf(sWo[f * d.OD + q], x[q], acc);
+      acc = mask[(size_t)b * d.K + k] >= 0.5f ? fmaxf(acc, 0.0f) : 0.0f;
+    }
+    feats[i] = acc;
+  }
+}
+
+// One thread per feature column j; the CTA walks its rows b = blockIdx.x, += gridDim.x.
+// part: [grid][W][TW_MAXIN + 1]  (weight-row partial, then the bias partial)
+__global__ void __launch_bounds__(1024)
+tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ feats,
+                 const float* __restrict__ self_obs, const float* __restrict__ objects, TowerDims d,
+                 float* __restrict__ dWs, float* __restrict__ dbs, float* __restrict__ dWo,
+                 float* __restrict__ dbo, float* __restrict__ part, uint32_t* counter) {
+  const int j = threadIdx.x;
+  constexpr int PW = TW_MAXIN + 1;
+  if (j < d.W) {
+    float acc[TW_MAXIN], accb = 0.0f;
+#pragma unroll
+    for (int q = 0; q < TW_MAXIN; ++q) acc[q] = 0.0f;
+    const bool own = j < d.SF;
+    const int k = own ? 0 : (j - d.SF) / d.OF;
+    const int nin = own ? d.SD : d.OD;
+    for (int b = blockIdx.x; b < d.B; b += gridDim.x) {
+      const size_t i = (size_t)b * d.W + j;
+      const float g = feats[i] > 0.0f ? dfeats[i] : 0.0f;  // ReLU' and the mask: a masked row is 0
+      const float* x = own ? self_obs + (size_t)b * d.SD : objects + ((size_t)b * d.K + k) * d.OD;
+      accb += g;
+#pragma unroll
+      for (int q = 0; q < TW_MAXIN; ++q)
+        if (q < nin) acc[q] = fmaf(g, x[q], acc[q]);
+    }
+    float* p = part + ((size_t)blockIdx.x * d.W + j) * PW;
+#pragma unroll
+    for (int q = 0; q < TW_MAXIN; ++q) p[q] = acc[q];
+    p[TW_MAXIN] = accb;
+  }
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // final sums in a fixed order: over the CTAs, and over the K object slots for the shared encoder
+  const int n_ws = d.SF * d.SD, n_wo = d.OF * d.OD;
+  const int n_out = n_ws + d.SF + n_wo + d.OF;
+  for (int o = threadIdx.x; o < n_out; o += blockDim.x) {
+    int col0, q, reps;
+    float* dst;
+    if (o < n_ws) { col0 = o / d.SD; q = o - col0 * d.SD; reps = 1; dst = dWs + o; }
+    else if (o < n_ws + d.SF) { col0 = o - n_ws; q = TW_MAXIN; reps = 1; dst = dbs + col0; }
+    else if (o < n_ws + d.SF + n_wo) {
+      const int r = o - n_ws - d.SF, f = r / d.OD;
+      col0 = d.SF + f; q = r - f * d.OD; reps = d.K; dst = dWo + r;
+    } else { const int f = o - n_ws - d.SF - n_wo; col0 = d.SF + f; q = TW_MAXIN; reps = d.K; dst = dbo + f; }
+    float s = 0.0f;
+    for (int kk = 0; kk < reps; ++kk)
+      for (int g = 0; g < (int)gridDim.x; ++g)
+        s += __ldcg(part + ((size_t)g * d.W + col0 + kk * d.OF) * PW + q);
+    *dst = s;
+  }
+  if (threadIdx.x == 0) *counter = 0u;
+}
+
+}  // namespace asvrl
+
+using namespace asvrl;
+
+static int tower_dims(const char* what, int batch, int self_dim, int obj_dim, int max_obj, int self_feat,
+                      int obj_feat, TowerDims* d) {
+  if (batch < 1 || self_dim < 1 || obj_dim < 1 || max_obj < 1 || self_feat < 1 || obj_feat < 1)
+    return fail(ASVRL_E_BADARG, "%s: bad sizes", what);
+  if (self_dim > TW_MAXIN || obj_dim > TW_MAXIN)
+    return fail(ASVRL_E_LIMIT, "%s: self_dim, obj_dim <= %d", what, TW_MAXIN);
+  const int W = self_feat + max_obj * obj_feat;
+  if (W > 1024) return fail(ASVRL_E_LIMIT, "%s: feature width %d > 1024", what, W);
+  *d = TowerDims{batch, self_dim, obj_dim, max_obj, self_feat, obj_feat, W};
+  return 0;
+}
+
+static int tower_bwd_grid(int batch) {
+  int g = (batch + 7) / 8;
+  return g > 64 ? 64 : (g < 1 ? 1 : g);
+}
+
+extern "C" int asvrl_tower_fwd(const float* self_obs, const float* objects, const float* mask,
+                               const float* w_self, const float* b_self, const float* w_obj,
+                               const float* b_obj, int batch, int self_dim, int obj_dim, int max_obj,
+                               int self_feat, int obj_feat, float* feats, void* stream) {
+  if (!self_obs || !objects || !mask || !w_self || !b_self || !w_obj || !b_obj || !feats)
+    return fail(ASVRL_E_BADARG, "asvrl_tower_fwd: null pointer");
+  TowerDims d;
+  if (int rc = tower_dims("asvrl_tower_fwd", batch, self_dim, obj_dim, max_obj, self_feat, obj_feat, &d)) return rc;
+  const long total = (long)d.B * d.W;
+  long grid = (total + 255) / 256;
+  if (grid > 148 * 8) grid = 148 * 8;
+  const size_t smem = sizeof(float) * (size_t)(d.SF * d.SD + d.SF + d.OF * d.OD + d.OF);
+  if (smem > 48 * 1024) return fail(ASVRL_E_LIMIT, "asvrl_tower_fwd: encoder weights exceed 48 KB");
+  tower_fwd_kernel<<<(int)grid, 256, smem, (cudaStream_t)stream>>>(self_obs, objects, mask, w_self, b_self,
+                                                                   w_obj, b_obj, d, feats);
+  return check_launch("asvrl_tower_fwd");
+}
+
+extern "C" int asvrl_tower_bwd(const float* dfeats, const float* feats, const float* self_obs,
+                               const float* objects, int batch, int self_dim, int obj_dim, int max_obj,
+                               int self_feat, int obj_feat, float* dw_self, float* db_self, float* dw_obj,
+                               float* db_obj, float* partials, uint32_t* counter, void* stream) {
+  if (!dfeats || !feats || !self_obs || !objects || !dw_self || !db_self || !dw_obj || !db_obj || !partials ||
+      !counter)
+    return fail(ASVRL_E_BADARG, "asvrl_tower_bwd: null pointer");
+  TowerDims d;
+  if (int rc = tower_dims("asvrl_tower_bwd", batch, self_dim, obj_dim, max_obj, self_feat, obj_feat, &d)) return rc;
+  const int threads = (d.W + 31) / 32 * 32;
+  tower_bwd_kernel<<<tower_bwd_grid(batch), threads, 0, (cudaStream_t)stream>>>(
+      dfeats, feats, self_obs, objects, d, dw_self, db_self, dw_obj, db_obj, partials, counter);
+  return check_launch("asvrl_tower_bwd");
+}
+
+extern "C" long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, int obj_feat) {  /* floats */
+  return (long)tower_bwd_grid(batch) * (self_feat + max_obj * obj_feat) * (TW_MAXIN + 1);
+}

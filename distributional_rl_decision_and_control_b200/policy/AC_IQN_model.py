@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .iqn_ops import TauSampler, critic_trunk
+from .iqn_ops import TauSampler, critic_trunk, observation_tower
 
 
 def encoder(input_dimension, output_dimension):
@@ -26,7 +26,9 @@ def encoder(input_dimension, output_dimension):
 
 class _ObservationTower(nn.Module):
     """Shared front end: self 7->56, each of 5 objects 5->40 (masked), concat -> 256
-    (ACIQN:284-308 / 428-451)."""
+    (ACIQN:284-308 / 428-451).  On CUDA float32 tensors it is kernel K6; the module-by-module
+    path below it serves the float64 / CPU TorchScript export and is the parity reference."""
+    fused_tower = True
 
     def _init_dims(self, self_dimension, object_dimension, max_object_num, self_feature_dimension,
                    object_feature_dimension, concat_feature_dimension, hidden_dimension, device, seed):
@@ -45,6 +47,12 @@ class _ObservationTower(nn.Module):
         assert len(x) == 3, "The number of elements in state must be 3!"
         self_obs, objects, mask = x
         B = self_obs.shape[0]
+        if (self.fused_tower and objects is not None and self_obs.is_cuda and self_obs.dtype == torch.float32
+                and self.self_encoder[0].weight.dtype == torch.float32):
+            # K6: both encoders, the mask and the concat in one launch (one more for the backward)
+            se, oe = self.self_encoder[0], self.object_encoder[0]
+            return observation_tower(self_obs, objects.reshape(B, self.max_object_num, self.object_dimension),
+                                     mask.to(torch.float32), se.weight, se.bias, oe.weight, oe.bias)
         own = self.self_encoder(self_obs)
         width = self.max_object_num * self.object_feature_dimension
         if objects is None:  # empty batch special case, RB:60-63

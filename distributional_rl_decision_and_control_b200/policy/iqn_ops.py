@@ -132,3 +132,29 @@ def critic_trunk(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau):
     if not cos.is_cuda:
         raise RuntimeError("critic_trunk runs on CUDA only (no CPU fallback)")
     return _CriticTrunk.apply(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, int(n_tau))
+
+
+class _Tower(torch.autograd.Function):
+    """K6: self / object encoders, mask and concat (ACIQN:284-308) in one launch; the backward is one
+    launch for the four parameter gradients (observations carry no gradient)."""
+
+    @staticmethod
+    def forward(ctx, self_obs, objects, mask, Ws, bs, Wo, bo):
+        self_obs, objects, mask = self_obs.contiguous(), objects.contiguous(), mask.contiguous()
+        feats = _lib.tower_fwd(self_obs, objects, mask, Ws, bs, Wo, bo)
+        ctx.save_for_backward(feats, self_obs, objects)
+        ctx.dims = (Ws.shape[0], Wo.shape[0])
+        return feats
+
+    @staticmethod
+    def backward(ctx, dfeats):
+        feats, self_obs, objects = ctx.saved_tensors
+        dws, dbs, dwo, dbo = _lib.tower_bwd(dfeats.contiguous(), feats, self_obs, objects, *ctx.dims)
+        return None, None, None, dws, dbs, dwo, dbo
+
+
+def observation_tower(self_obs, objects, mask, Ws, bs, Wo, bo):
+    """-> (B, SF + K*OF) features; CUDA float32 only (no CPU fallback)."""
+    if not self_obs.is_cuda:
+        raise RuntimeError("observation_tower runs on CUDA only (no CPU fallback)")
+    return _Tower.apply(self_obs, objects, mask, Ws, bs, Wo, bo)

@@ -410,6 +410,22 @@ ASVRL_API int asvrl_iqn_head_bwd(const float* dz, const float* pre, const float*
                                  float* partials, uint32_t* counter, void* stream);
 ASVRL_API long asvrl_iqn_head_bwd_partials(int rows, int dim);
 
+/* K6 — the observation tower of the actor and the critic (ACIQN:284-308, 428-451) in one launch:
+ *   feats[b][j]                  = relu(w_self[j] . self_obs[b] + b_self[j])                 j < self_feat
+ *   feats[b][self_feat+k*OF+f]   = mask[b][k] >= 0.5 ? relu(w_obj[f] . objects[b][k] + b_obj[f]) : 0
+ * self_obs [B][self_dim], objects [B][max_obj][obj_dim], mask [B][max_obj], feats [B][self_feat +
+ * max_obj*obj_feat]; self_dim, obj_dim <= 8.  The backward returns the four parameter gradients
+ * (observations are data); partials: asvrl_tower_bwd_partials() floats, counter: one zeroed uint32. */
+ASVRL_API int asvrl_tower_fwd(const float* self_obs, const float* objects, const float* mask,
+                              const float* w_self, const float* b_self, const float* w_obj,
+                              const float* b_obj, int batch, int self_dim, int obj_dim, int max_obj,
+                              int self_feat, int obj_feat, float* feats, void* stream);
+ASVRL_API int asvrl_tower_bwd(const float* dfeats, const float* feats, const float* self_obs,
+                              const float* objects, int batch, int self_dim, int obj_dim, int max_obj,
+                              int self_feat, int obj_feat, float* dw_self, float* db_self, float* dw_obj,
+                              float* db_obj, float* partials, uint32_t* counter, void* stream);
+ASVRL_API long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, int obj_feat);
+
 #ifdef __cplusplus
 }
 #endif

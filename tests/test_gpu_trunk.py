@@ -96,7 +96,9 @@ def test_fused_critic_matches_module_path(B, N):
         (z * wz).sum().backward()
         return z.detach(), a.grad, {n: (None if p.grad is None else p.grad.clone()) for n, p in crit.named_parameters()}
 
+    crit.fused_tower = False       # module-by-module autograd path: the torch fp32 reference
     z0, da0, g0 = run(crit.forward)
+    crit.fused_tower = True        # K6 tower + K5 trunk
     z1, da1, g1 = run(crit.forward_fused)
     close(z1, z0, "quantiles")
     close(da1, da0, "d/d actions")
@@ -137,3 +139,28 @@ def test_train_step_fused_equals_unfused():
     diff = (res[1][3] - res[0][3]).abs()
     assert (diff > 1e-6).float().mean().item() < 0.01
     assert diff.max().item() <= 2.1e-4
+
+
+@pytest.mark.parametrize("B", [1, 64, 1024, 32768, 77])
+def test_tower_fwd_bwd(B):
+    """K6 against the encoders written module by module (float64 on the GPU)."""
+    from distributional_rl_decision_and_control_b200.policy.AC_IQN_model import Actor
+    actor = Actor(7, 5, 5, 56, 40, 256, 128, [[-1.0, 1.0], [-1.0, 1.0]], device=DEV, seed=3).to(DEV)
+    x, _ = _critic_inputs(B, B)
+    wf = torch.randn((B, 256), device=DEV, generator=torch.Generator(device=DEV).manual_seed(4))
+    ref = Actor(7, 5, 5, 56, 40, 256, 128, [[-1.0, 1.0], [-1.0, 1.0]], device=DEV, seed=3).to(DEV).double()
+    ref.fused_tower = False
+    f_ref = ref._features(tuple(t.double() for t in x))
+    (f_ref * wf.double()).sum().backward()
+    f = actor._features(x)
+    (f * wf).sum().backward()
+    close(f.detach(), f_ref.detach(), "features")
+    assert torch.equal(f.detach()[:, 56:].reshape(B, 5, 40).abs().sum(-1) > 0,
+                       (f_ref.detach()[:, 56:].reshape(B, 5, 40).abs().sum(-1) > 0))  # masked rows are exactly 0
+    for name in ("self_encoder.0.weight", "self_encoder.0.bias", "object_encoder.0.weight", "object_encoder.0.bias"):
+        close(dict(actor.named_parameters())[name].grad, dict(ref.named_parameters())[name].grad, name, rtol=2e-5)
+    # deterministic
+    g1 = actor.self_encoder[0].weight.grad.clone()
+    actor.zero_grad(set_to_none=True)
+    (actor._features(x) * wf).sum().backward()
+    assert torch.equal(actor.self_encoder[0].weight.grad, g1)

@@ -159,3 +159,16 @@ class EnvAutoReset(C.Structure):
                 ("stage", C.POINTER(EnvStatePtrs)), ("stage_tag", C.c_void_p),
                 ("stage_self", C.c_void_p), ("stage_objects", C.c_void_p), ("stage_mask", C.c_void_p),
                 ("refill_in_launch", C.c_int32), ("reserved", C.c_int32)]
+
+
+OPT_MAX_TENSORS = 64
+OPT_SCRATCH_FLOATS = 256
+
+
+class AdamTensors(C.Structure):
+    """asvrl_adam_tensors (include/asvrl.h)."""
+    _fields_ = [("n", C.c_int),
+                ("param", C.c_void_p * OPT_MAX_TENSORS), ("grad", C.c_void_p * OPT_MAX_TENSORS),
+                ("exp_avg", C.c_void_p * OPT_MAX_TENSORS), ("exp_avg_sq", C.c_void_p * OPT_MAX_TENSORS),
+                ("step", C.c_void_p * OPT_MAX_TENSORS),
+                ("numel", C.c_longlong * OPT_MAX_TENSORS)]

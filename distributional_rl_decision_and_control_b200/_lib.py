@@ -59,6 +59,7 @@ _SIGNATURES = {
     "asvrl_tower_fwd": (C.c_int, [f32p] * 7 + [C.c_int] * 6 + [f32p, vp]),
     "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
     "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
+    "asvrl_clip_adam_step": (C.c_int, [C.POINTER(_abi.AdamTensors)] + [C.c_float] * 6 + [f32p, f32p, u32p, vp]),
 }
 EXPORTED = tuple(_SIGNATURES)
 
@@ -404,6 +405,26 @@ def tower_bwd(dfeats, feats, self_obs, objects, SF, OF):
                                SF, OF, ptr(dws), ptr(dbs), ptr(dwo), ptr(dbo), ptr(part), ptr(cnt), stream_ptr())
     check(rc, "asvrl_tower_bwd")
     return dws, dbs, dwo, dbo
+
+
+# ------------------------------------------------------------------ K7: clip + Adam
+def clip_adam_step(params, grads, exp_avgs, exp_avg_sqs, steps, max_norm, lr, beta1, beta2, eps, grad_scale,
+                   norm_out, scratch, counter):
+    """One optimiser step over the tensor lists (<= 64 tensors per call is the ABI limit)."""
+    if len(params) > _abi.OPT_MAX_TENSORS:
+        raise RuntimeError(f"clip_adam_step: more than {_abi.OPT_MAX_TENSORS} tensors")
+    t = _abi.AdamTensors()
+    t.n = len(params)
+    f = torch.float32
+    for i, (p, g, m, v, st) in enumerate(zip(params, grads, exp_avgs, exp_avg_sqs, steps)):
+        if g.numel() != p.numel():
+            raise RuntimeError("clip_adam_step: gradient / parameter size mismatch")
+        t.param[i], t.grad[i], t.exp_avg[i], t.exp_avg_sq[i] = ptr(p, f), ptr(g, f), ptr(m, f), ptr(v, f)
+        t.step[i] = ptr(st, f)
+        t.numel[i] = p.numel()
+    rc = lib().asvrl_clip_adam_step(C.byref(t), max_norm, lr, beta1, beta2, eps, grad_scale,
+                                    ptr(norm_out, f), ptr(scratch, f), ptr(counter, torch.int32), stream_ptr())
+    check(rc, "asvrl_clip_adam_step")
 
 
 # ------------------------------------------------------------------ K2: device replay ring

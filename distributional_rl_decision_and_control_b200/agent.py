@@ -63,7 +63,8 @@ class Agent():
                  rank=0,
                  matmul_precision="fp32",
                  replay_lanes=1,
-                 fused_trunk=True):
+                 fused_trunk=True,
+                 fused_optimizer=True):
         self.device = torch.device(device) if not isinstance(device, torch.device) else device
         self.LR = LR
         self.TAU = TAU
@@ -94,37 +95,42 @@ class Agent():
                 raise RuntimeError("training runs on a CUDA device only: the replay ring and the IQN "
                                    "kernels have no CPU fallback")
             capt = dict(lr=self.LR, capturable=True)
+            if fused_optimizer:  # K7: clip_grad_norm_(0.5) + Adam in two launches (utils/clip_adam.py)
+                from .utils.clip_adam import ClipAdam
+                _Adam = lambda ps, **kw: ClipAdam(ps, lr=self.LR, max_norm=0.5, process_group=process_group)
+            else:
+                _Adam = optim.Adam
             if agent_type == "AC-IQN":
                 self.policy_local = AC_IQN_Policy(*self._dims, value_ranges_of_action, self.device, seed)
                 self.policy_target = AC_IQN_Policy(*self._dims, value_ranges_of_action, self.device, seed)
-                self.actor_optimizer = optim.Adam(self.policy_local.actor.parameters(), **capt)
-                self.critic_optimizer = optim.Adam(self.policy_local.critic.parameters(), **capt)
+                self.actor_optimizer = _Adam(self.policy_local.actor.parameters(), **capt)
+                self.critic_optimizer = _Adam(self.policy_local.critic.parameters(), **capt)
                 samplers = [(self.policy_local.critic.tau_sampler, 0),
                             (self.policy_target.critic.tau_sampler, _TARGET_SALT)]
             elif agent_type == "IQN":
                 self.policy_local = IQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
                 self.policy_target = IQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
-                self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
+                self.optimizer = _Adam(self.policy_local.parameters(), **capt)
                 samplers = [(self.policy_local.tau_sampler, 0),
                             (self.policy_target.tau_sampler, _TARGET_SALT)]
             elif agent_type == "DDPG":  # AGENT:96-120
                 self.policy_local = DDPG_Policy(*self._dims, value_ranges_of_action, self.device, seed)
                 self.policy_target = DDPG_Policy(*self._dims, value_ranges_of_action, self.device, seed)
-                self.actor_optimizer = optim.Adam(self.policy_local.actor.parameters(), **capt)
-                self.critic_optimizer = optim.Adam(self.policy_local.critic.parameters(), **capt)
+                self.actor_optimizer = _Adam(self.policy_local.actor.parameters(), **capt)
+                self.critic_optimizer = _Adam(self.policy_local.critic.parameters(), **capt)
                 samplers = []
             elif agent_type == "DQN":  # AGENT:121-143
                 self.policy_local = DQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
                 self.policy_target = DQN_Policy(*self._dims, action_size, self.device, seed).to(self.device)
-                self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
+                self.optimizer = _Adam(self.policy_local.parameters(), **capt)
                 samplers = []
             elif agent_type == "SAC":  # AGENT:144-168
                 self.alpha = 0.078
                 self.policy_local = SAC_Policy(*self._dims, value_ranges_of_action, self.device, seed)
                 self.policy_target = SAC_Policy(*self._dims, value_ranges_of_action, self.device, seed)
-                self.actor_optimizer = optim.Adam(self.policy_local.actor.parameters(), **capt)
-                self.critic_1_optimizer = optim.Adam(self.policy_local.critic_1.parameters(), **capt)
-                self.critic_2_optimizer = optim.Adam(self.policy_local.critic_2.parameters(), **capt)
+                self.actor_optimizer = _Adam(self.policy_local.actor.parameters(), **capt)
+                self.critic_1_optimizer = _Adam(self.policy_local.critic_1.parameters(), **capt)
+                self.critic_2_optimizer = _Adam(self.policy_local.critic_2.parameters(), **capt)
                 samplers = []
             elif agent_type == "Rainbow":  # AGENT:169-198
                 self.atoms = 51
@@ -135,7 +141,7 @@ class Agent():
                 self.n = multi_steps
                 self.policy_local = Rainbow_Policy(*self._dims, action_size, self.atoms, self.device, seed).to(self.device)
                 self.policy_target = Rainbow_Policy(*self._dims, action_size, self.atoms, self.device, seed).to(self.device)
-                self.optimizer = optim.Adam(self.policy_local.parameters(), **capt)
+                self.optimizer = _Adam(self.policy_local.parameters(), **capt)
                 samplers = []
             else:
                 raise RuntimeError("Agent type not implemented!")
@@ -302,6 +308,15 @@ class Agent():
             g.copy_(flat[off:off + n].view_as(g))
             off += n
 
+    def _clip_and_step(self, optimizer, params):
+        """all-reduce (N > 1) -> clip_grad_norm_(0.5) -> Adam, AGENT:414-416 and twins."""
+        if hasattr(optimizer, "max_norm"):  # ClipAdam: exchange, clip and update inside K7's two launches
+            optimizer.step()
+            return
+        self._sync_grads(params)
+        torch.nn.utils.clip_grad_norm_(params, 0.5)
+        optimizer.step()
+
     def _batch(self, batch):
         b = self.memory.sample_device() if batch is None else batch
         return ((b["self"], b["obj"], b["mask"]), b["act"], b["rew"], (b["nself"], b["nobj"], b["nmask"]),
@@ -350,10 +365,7 @@ class Agent():
         critic_loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones,
                                              self.GAMMA, 1.0)            # K4 = AGENT:401-412
         critic_loss.backward()
-        critic_params = list(local.critic.parameters())
-        self._sync_grads(critic_params)
-        torch.nn.utils.clip_grad_norm_(critic_params, 0.5)               # AGENT:415
-        self.critic_optimizer.step()
+        self._clip_and_step(self.critic_optimizer, list(local.critic.parameters()))  # AGENT:414-416
 
         # actor step -------------------------------------------------------------------
         self.actor_optimizer.zero_grad(set_to_none=True)
@@ -364,10 +376,7 @@ class Agent():
             q, _ = local.critic(states, local.actor(states), N, taus=taus.get("actor"))
         actor_loss = -q.mean()
         actor_loss.backward()
-        actor_params = list(local.actor.parameters())
-        self._sync_grads(actor_params)
-        torch.nn.utils.clip_grad_norm_(actor_params, 0.5)                # AGENT:426
-        self.actor_optimizer.step()
+        self._clip_and_step(self.actor_optimizer, list(local.actor.parameters()))  # AGENT:424-427
         return critic_loss.detach(), actor_loss.detach()
 
     def _train_IQN(self, batch=None, taus=None):
@@ -385,10 +394,7 @@ class Agent():
         z = z_all.gather(2, a).squeeze(-1)
         loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones, self.GAMMA, 1.0)
         loss.backward()
-        params = list(self.policy_local.parameters())
-        self._sync_grads(params)
-        torch.nn.utils.clip_grad_norm_(params, 0.5)                      # AGENT:472
-        self.optimizer.step()
+        self._clip_and_step(self.optimizer, list(self.policy_local.parameters()))  # AGENT:470-473
         return loss.detach()
 
     # ------------------------------------------------------------------ the four non-distributional agents
@@ -397,9 +403,7 @@ class Agent():
         (AGENT:414-416 and twins).  zero_grad first: losses of SAC share nothing across optimisers."""
         optimizer.zero_grad(set_to_none=True)
         loss.backward()
-        self._sync_grads(params)
-        torch.nn.utils.clip_grad_norm_(params, 0.5)
-        optimizer.step()
+        self._clip_and_step(optimizer, params)
 
     def train_DDPG(self, batch=None):
         """AGENT:478-516 on device tensors.  Returns (critic_loss, actor_loss) as 0-d CUDA tensors."""

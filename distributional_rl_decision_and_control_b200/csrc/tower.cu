@@ -58,15 +58,18 @@ tower_fwd_kernel(const float* __restrict__ self_obs, const float* __restrict__ o
   }
 }
 
-// One thread per feature column j; the CTA walks its rows b = blockIdx.x, += gridDim.x.
-// part: [grid][W][TW_MAXIN + 1]  (weight-row partial, then the bias partial)
+// Thread (rl, j): feature column j, row lane rl; the CTA's lanes stride over the batch rows.  The
+// lanes and the K object slots (which share one encoder) are summed in shared memory, so a CTA
+// publishes one partial per parameter: part[cta][SF + OF][TW_MAXIN + 1] (weight row, then bias).
+// The last CTA sums the partials in a fixed order, one thread per parameter.
 __global__ void __launch_bounds__(1024)
 tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ feats,
                  const float* __restrict__ self_obs, const float* __restrict__ objects, TowerDims d,
-                 float* __restrict__ dWs, float* __restrict__ dbs, float* __restrict__ dWo,
+                 int W32, float* __restrict__ dWs, float* __restrict__ dbs, float* __restrict__ dWo,
                  float* __restrict__ dbo, float* __restrict__ part, uint32_t* counter) {
-  const int j = threadIdx.x;
+  extern __shared__ float tw_sm[];  // [RL][W][PW]
   constexpr int PW = TW_MAXIN + 1;
+  const int j = threadIdx.x % W32, rl = threadIdx.x / W32, RL = blockDim.x / W32;
   if (j < d.W) {
     float acc[TW_MAXIN], accb = 0.0f;
 #pragma unroll
@@ -74,7 +77,7 @@ tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ fea
     const bool own = j < d.SF;
     const int k = own ? 0 : (j - d.SF) / d.OF;
     const int nin = own ? d.SD : d.OD;
-    for (int b = blockIdx.x; b < d.B; b += gridDim.x) {
+    for (int b = blockIdx.x * RL + rl; b < d.B; b += gridDim.x * RL) {
       const size_t i = (size_t)b * d.W + j;
       const float g = feats[i] > 0.0f ? dfeats[i] : 0.0f;  // ReLU' and the mask: a masked row is 0
       const float* x = own ? self_obs + (size_t)b * d.SD : objects + ((size_t)b * d.K + k) * d.OD;
@@ -83,10 +86,21 @@ tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ fea
       for (int q = 0; q < TW_MAXIN; ++q)
         if (q < nin) acc[q] = fmaf(g, x[q], acc[q]);
     }
-    float* p = part + ((size_t)blockIdx.x * d.W + j) * PW;
+    float* p = tw_sm + ((size_t)rl * d.W + j) * PW;
 #pragma unroll
     for (int q = 0; q < TW_MAXIN; ++q) p[q] = acc[q];
     p[TW_MAXIN] = accb;
+  }
+  __syncthreads();
+  const int C = d.SF + d.OF, n_val = C * PW;
+  for (int o = threadIdx.x; o < n_val; o += blockDim.x) {
+    const int c = o / PW, q = o - c * PW;
+    const int reps = c < d.SF ? 1 : d.K;
+    const int col0 = c < d.SF ? c : d.SF + (c - d.SF);
+    float s = 0.0f;
+    for (int kk = 0; kk < reps; ++kk)
+      for (int r = 0; r < RL; ++r) s += tw_sm[((size_t)r * d.W + col0 + kk * d.OF) * PW + q];
+    part[(size_t)blockIdx.x * n_val + o] = s;
   }
   __shared__ bool is_last;
   __threadfence();
@@ -95,23 +109,14 @@ tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ fea
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  // final sums in a fixed order: over the CTAs, and over the K object slots for the shared encoder
-  const int n_ws = d.SF * d.SD, n_wo = d.OF * d.OD;
-  const int n_out = n_ws + d.SF + n_wo + d.OF;
-  for (int o = threadIdx.x; o < n_out; o += blockDim.x) {
-    int col0, q, reps;
-    float* dst;
-    if (o < n_ws) { col0 = o / d.SD; q = o - col0 * d.SD; reps = 1; dst = dWs + o; }
-    else if (o < n_ws + d.SF) { col0 = o - n_ws; q = TW_MAXIN; reps = 1; dst = dbs + col0; }
-    else if (o < n_ws + d.SF + n_wo) {
-      const int r = o - n_ws - d.SF, f = r / d.OD;
-      col0 = d.SF + f; q = r - f * d.OD; reps = d.K; dst = dWo + r;
-    } else { const int f = o - n_ws - d.SF - n_wo; col0 = d.SF + f; q = TW_MAXIN; reps = d.K; dst = dbo + f; }
+  for (int o = threadIdx.x; o < n_val; o += blockDim.x) {
+    const int c = o / PW, q = o - c * PW;
+    const int nin = c < d.SF ? d.SD : d.OD;
+    if (q < TW_MAXIN && q >= nin) continue;
     float s = 0.0f;
-    for (int kk = 0; kk < reps; ++kk)
-      for (int g = 0; g < (int)gridDim.x; ++g)
-        s += __ldcg(part + ((size_t)g * d.W + col0 + kk * d.OF) * PW + q);
-    *dst = s;
+    for (int g = 0; g < (int)gridDim.x; ++g) s += __ldcg(part + (size_t)g * n_val + o);
+    if (c < d.SF) { if (q == TW_MAXIN) dbs[c] = s; else dWs[c * d.SD + q] = s; }
+    else { const int f = c - d.SF; if (q == TW_MAXIN) dbo[f] = s; else dWo[f * d.OD + q] = s; }
   }
   if (threadIdx.x == 0) *counter = 0u;
 }
@@ -133,8 +138,8 @@ static int tower_dims(const char* what, int batch, int self_dim, int obj_dim, in
 }
 
 static int tower_bwd_grid(int batch) {
-  int g = (batch + 7) / 8;
-  return g > 64 ? 64 : (g < 1 ? 1 : g);
+  int g = (batch + 31) / 32;
+  return g > 16 ? 16 : (g < 1 ? 1 : g);
 }
 
 extern "C" int asvrl_tower_fwd(const float* self_obs, const float* objects, const float* mask,
@@ -164,12 +169,14 @@ extern "C" int asvrl_tower_bwd(const float* dfeats, const float* feats, const fl
     return fail(ASVRL_E_BADARG, "asvrl_tower_bwd: null pointer");
   TowerDims d;
   if (int rc = tower_dims("asvrl_tower_bwd", batch, self_dim, obj_dim, max_obj, self_feat, obj_feat, &d)) return rc;
-  const int threads = (d.W + 31) / 32 * 32;
-  tower_bwd_kernel<<<tower_bwd_grid(batch), threads, 0, (cudaStream_t)stream>>>(
-      dfeats, feats, self_obs, objects, d, dw_self, db_self, dw_obj, db_obj, partials, counter);
+  const int W32 = (d.W + 31) / 32 * 32, RL = 1024 / W32;
+  const size_t smem = (size_t)RL * d.W * (TW_MAXIN + 1) * sizeof(float);  // <= 36 KB
+  tower_bwd_kernel<<<tower_bwd_grid(batch), RL * W32, smem, (cudaStream_t)stream>>>(
+      dfeats, feats, self_obs, objects, d, W32, dw_self, db_self, dw_obj, db_obj, partials, counter);
   return check_launch("asvrl_tower_bwd");
 }
 
 extern "C" long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, int obj_feat) {  /* floats */
-  return (long)tower_bwd_grid(batch) * (self_feat + max_obj * obj_feat) * (TW_MAXIN + 1);
+  (void)max_obj;
+  return (long)tower_bwd_grid(batch) * (self_feat + obj_feat) * (TW_MAXIN + 1);
 }

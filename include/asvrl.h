@@ -426,6 +426,31 @@ ASVRL_API int asvrl_tower_bwd(const float* dfeats, const float* feats, const flo
                               float* db_obj, float* partials, uint32_t* counter, void* stream);
 ASVRL_API long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, int obj_feat);
 
+/* K7 — replaces torch.nn.utils.clip_grad_norm_(params, max_norm) followed by Adam.step()
+ * (AGENT:414-416, 424-427 and the other agents' twins) with two launches over a list of tensors:
+ *   total = ||g||_2 * grad_scale;  c = min(1, max_norm / (total + 1e-6));  g' = g * grad_scale * c
+ *   m <- m + (1-b1)(g'-m);  v <- b2 v + (1-b2) g'^2;  t <- t+1
+ *   p <- p - lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
+ * t is kept per tensor like torch (a tensor left out of a call keeps its count); norm_out: nullable
+ * device float (total); scratch: ASVRL_OPT_SCRATCH_FLOATS caller-owned floats; counter: one
+ * zero-initialised uint32 (left zero).  grad_scale = 1/world_size when the gradients hold an all-reduced SUM.  grad is not
+ * modified (torch scales .grad in place; nothing on the path reads it afterwards). */
+#define ASVRL_OPT_MAX_TENSORS 64
+#define ASVRL_OPT_SCRATCH_FLOATS 256
+typedef struct asvrl_adam_tensors {
+  int n;
+  float* param[ASVRL_OPT_MAX_TENSORS];
+  const float* grad[ASVRL_OPT_MAX_TENSORS];
+  float* exp_avg[ASVRL_OPT_MAX_TENSORS];
+  float* exp_avg_sq[ASVRL_OPT_MAX_TENSORS];
+  float* step[ASVRL_OPT_MAX_TENSORS];   /* device float per tensor: its step count t, incremented here */
+  long long numel[ASVRL_OPT_MAX_TENSORS];
+} asvrl_adam_tensors;
+ASVRL_API int asvrl_clip_adam_step(const asvrl_adam_tensors* tensors, float max_norm, float lr,
+                                   float beta1, float beta2, float eps, float grad_scale,
+                                   float* norm_out /* nullable */, float* scratch, uint32_t* counter,
+                                   void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -164,3 +164,32 @@ def test_tower_fwd_bwd(B):
     actor.zero_grad(set_to_none=True)
     (actor._features(x) * wf).sum().backward()
     assert torch.equal(actor.self_encoder[0].weight.grad, g1)
+
+
+@pytest.mark.parametrize("gscale", [1.0, 40.0])
+def test_clip_adam_matches_torch(gscale):
+    """K7 against torch.nn.utils.clip_grad_norm_(0.5) + torch.optim.Adam over several steps, with
+    gradients below (gscale=1: some steps unclipped) and above the clipping threshold."""
+    from distributional_rl_decision_and_control_b200.utils.clip_adam import ClipAdam
+    g = torch.Generator(device=DEV).manual_seed(9)
+    shapes = [(56, 7), (56,), (40, 5), (40,), (128, 256), (128,), (1, 128), (1,), (3, 5, 7)]
+    mine = [torch.nn.Parameter(torch.randn(s, device=DEV, generator=g)) for s in shapes]
+    ref = [torch.nn.Parameter(p.detach().clone()) for p in mine]
+    opt = ClipAdam(mine, lr=1e-4, max_norm=0.5)
+    topt = torch.optim.Adam(ref, lr=1e-4)
+    for it in range(5):
+        scale = gscale * (0.002 if it % 2 == 0 else 1.0)
+        for p, q in zip(mine, ref):
+            p.grad = torch.randn(p.shape, device=DEV, generator=g) * scale
+            q.grad = p.grad.clone()
+        if it == 3:  # a parameter without gradient is skipped by both
+            mine[2].grad = None
+            ref[2].grad = None
+        want_norm = torch.nn.utils.clip_grad_norm_(ref, 0.5)
+        topt.step()
+        opt.step()
+        close(opt.grad_norm, want_norm.reshape(1), "total norm", rtol=1e-6)
+        for p, q in zip(mine, ref):
+            assert (p.detach() - q.detach()).abs().max().item() <= 2e-7 * max(1.0, q.abs().max().item())
+    assert opt.step_count.tolist() == [5.0, 5.0, 4.0] + [5.0] * 6
+    assert int(opt._counter.item()) == 0

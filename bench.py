@@ -106,16 +106,32 @@ def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0):
     return n_envs * n_steps / dt, dt
 
 
-def time_learner(agent, K, W, dev, dist, world):
+def k1_traffic(E, C, fused):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this same command (profiles/k1_traffic.json); None for another shape."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "k1_traffic.json")) as f:
+            d = json.load(f)
+        if d["envs"] == E and d["cores"] == C and bool(d["fused"]) == bool(fused):
+            return d["dram_bytes_read"] + d["dram_bytes_write"]
+    except Exception:
+        pass
+    return None
+
+
+def time_learner(agent, K, W, dev, dist, world, eager=False):
     """Learner updates/s: whole Agent update (K2b sample, target + local critic, K3, K4 + backward,
     clip, Adam, actor step) replayed as one CUDA graph when capture works, else eager."""
     import torch
     mode = "graph"
-    try:
-        agent.enable_cuda_graph()
-    except Exception as e:  # e.g. a collective that cannot be captured on this stack
-        agent.disable_cuda_graph()
-        mode = "eager (%s)" % type(e).__name__
+    if eager:
+        mode = "eager (--profile)"
+    else:
+        try:
+            agent.enable_cuda_graph()
+        except Exception as e:  # e.g. a collective that cannot be captured on this stack
+            agent.disable_cuda_graph()
+            mode = "eager (%s)" % type(e).__name__
     step = agent.train_graph_replay if agent._graph is not None else (
         agent.train_AC_IQN if agent.agent_type == "AC-IQN" else agent.train_IQN)
     for _ in range(W):
@@ -179,6 +195,8 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
     E, C, K, W = args.envs, args.cores, args.steps, max(args.warmup, 3)
+    if args.profile:
+        K, W, args.no_cpu = min(K, 12), 3, True
 
     # envs partition across ranks with no data-path collective: rank r owns global envs
     # [r*E, (r+1)*E); the RNG counters carry the global index (results invariant to N)
@@ -334,9 +352,9 @@ def run_b200(args):
     fast = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=1024, num_tau=32,
                  BUFFER_SIZE=1 << 20, process_group=pg, rank=rank, matmul_precision="tf32")
     fast.memory.ring = big.memory.ring
-    KL = max(50, min(K, 500))
+    KL = 3 if args.profile else max(50, min(K, 500))
     for name, ag in (("c3_B1024_N32", big), ("c3_B1024_N32_tf32", fast), ("ref_B64_N8", small)):
-        ms, mode, loss = time_learner(ag, KL, 10, dev, dist, world)
+        ms, mode, loss = time_learner(ag, KL, 2 if args.profile else 10, dev, dist, world, eager=args.profile)
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -353,9 +371,9 @@ def run_b200(args):
     rr, dd = torch.randn((B3,), device=dev, generator=g), torch.zeros((B3,), device=dev)
     ws = torch.zeros(1, dtype=torch.int32, device=dev)
     o_l, o_g, o_s = torch.empty(B3, device=dev), torch.empty((B3, N3), device=dev), torch.empty(1, device=dev)
-    k4_ms = time_kernel(lambda: _lib.qhuber_fwd_bwd(z, tau, zn, rr, dd, 0.99, 1.0, ws, o_l, o_g, o_s), 200, 20)
+    k4_ms = time_kernel(lambda: _lib.qhuber_fwd_bwd(z, tau, zn, rr, dd, 0.99, 1.0, ws, o_l, o_g, o_s), 20 if args.profile else 200, 20)
     t_o, c_o = torch.empty((B3, N3), device=dev), torch.empty((B3, N3, 64), device=dev)
-    k3_ms = time_kernel(lambda: _lib.iqn_tau_cos(B3, N3, 64, dev, seed=1, counter=1, tau_out=t_o, cos_out=c_o), 200, 20)
+    k3_ms = time_kernel(lambda: _lib.iqn_tau_cos(B3, N3, 64, dev, seed=1, counter=1, tau_out=t_o, cos_out=c_o), 20 if args.profile else 200, 20)
     peak, which = measured_peak()
     k4_bytes = 4 * B3 * (2 * N3 + N3 + 2) + 4 * B3 * (N3 + 1)
     k3_bytes = 4 * B3 * N3 * (1 + 64)
@@ -400,7 +418,7 @@ def run_b200(args):
                            "status per ASV (the mask is objects[...,4] != 0, as in the reference's step())"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": which,
+                         "frac": achieved / peak, "traffic": k1_traffic(E, C, env.fused), "peak_source": which,
                          "kernel": "env_step_kernel<false,true> (fused auto-reset)" if env.fused
                                    else "env_step_kernel<false,false>", "kernel_ms": k1_ms,
                          "algorithmic_bytes_per_launch": per_launch,
@@ -465,6 +483,9 @@ def main():
     ap.add_argument("--prefetch", default="stream", choices=["stream", "workers", "off"])
     ap.add_argument("--no-stagger", action="store_true", help="start every episode clock at 0")
     ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
+    ap.add_argument("--profile", action="store_true",
+                    help="short run for ncu: few env steps, three EAGER learner updates per shape (no graph), "
+                         "no e2e / CPU legs; the numbers it prints are not bench values")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -162,7 +162,7 @@ class EnvAutoReset(C.Structure):
 
 
 OPT_MAX_TENSORS = 64
-OPT_SCRATCH_FLOATS = 256
+OPT_SCRATCH_FLOATS = 320
 
 
 class AdamTensors(C.Structure):

@@ -17,7 +17,8 @@
 namespace asvrl {
 
 constexpr int OPT_TPB = 256;
-constexpr int OPT_GRID = 64;
+constexpr int OPT_CHUNK = 4 * OPT_TPB;  // elements per (tensor, chunk) work item
+constexpr int OPT_GRID = 128;           // CTAs (and partial sums) at most
 
 struct AdamList {
   int n;
@@ -27,7 +28,18 @@ struct AdamList {
   float* exp_avg_sq[ASVRL_OPT_MAX_TENSORS];
   float* step[ASVRL_OPT_MAX_TENSORS];  // per-tensor step count t (torch keeps one per parameter)
   long long numel[ASVRL_OPT_MAX_TENSORS];
+  int chunk_end[ASVRL_OPT_MAX_TENSORS];  // running count of OPT_CHUNK-sized work items up to and including tensor t
+  int n_chunks;
 };
+
+// work item c -> (tensor t, first element): every CTA owns whole chunks, so its loads are independent
+// of each other (one DRAM round trip) instead of a serial walk over the tensor list
+__device__ __forceinline__ int chunk_tensor(const AdamList& L, int c, long long& first) {
+  int t = 0;
+  while (c >= L.chunk_end[t]) ++t;
+  first = (long long)(c - (t ? L.chunk_end[t - 1] : 0)) * OPT_CHUNK;
+  return t;
+}
 
 // scal: [0] clip * grad_scale, then per tensor t: [1 + 2t] lr / (1 - b1^t_t), [2 + 2t] 1 / sqrt(1 - b2^t_t)
 __global__ void __launch_bounds__(OPT_TPB)
@@ -35,11 +47,15 @@ grad_norm_kernel(const __grid_constant__ AdamList L, float max_norm, float lr, f
                  float grad_scale, float* __restrict__ norm_out,
                  float* __restrict__ scal, float* __restrict__ part, uint32_t* counter) {
   float acc = 0.0f;
-  for (int t = 0; t < L.n; ++t) {
+  for (int c = blockIdx.x; c < L.n_chunks; c += gridDim.x) {
+    long long first;
+    const int t = chunk_tensor(L, c, first);
     const float* g = L.grad[t];
     const long long n = L.numel[t];
-    for (long long i = blockIdx.x * OPT_TPB + threadIdx.x; i < n; i += (long long)gridDim.x * OPT_TPB) {
-      const float v = g[i];
+#pragma unroll
+    for (int q = 0; q < OPT_CHUNK / OPT_TPB; ++q) {
+      const long long i = first + q * OPT_TPB + threadIdx.x;
+      const float v = i < n ? g[i] : 0.0f;
       acc = fmaf(v, v, acc);
     }
   }
@@ -79,18 +95,31 @@ __global__ void __launch_bounds__(OPT_TPB)
 adam_kernel(const __grid_constant__ AdamList L, float beta1, float beta2, float eps,
             const float* __restrict__ scal) {
   const float gs = scal[0];
-  for (int t = 0; t < L.n; ++t) {
+  for (int c = blockIdx.x; c < L.n_chunks; c += gridDim.x) {
+    long long first;
+    const int t = chunk_tensor(L, c, first);
     const float step_size = scal[1 + 2 * t], inv_bc2_sqrt = scal[2 + 2 * t];
     const float* g = L.grad[t];
     float *p = L.param[t], *m = L.exp_avg[t], *v = L.exp_avg_sq[t];
     const long long n = L.numel[t];
-    for (long long i = blockIdx.x * OPT_TPB + threadIdx.x; i < n; i += (long long)gridDim.x * OPT_TPB) {
-      const float gi = g[i] * gs;
-      const float mi = m[i] + (1.0f - beta1) * (gi - m[i]);
-      const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
-      m[i] = mi;
-      v[i] = vi;
-      p[i] = p[i] - step_size * (mi / (sqrtf(vi) * inv_bc2_sqrt + eps));
+    float gq[OPT_CHUNK / OPT_TPB], mq[OPT_CHUNK / OPT_TPB], vq[OPT_CHUNK / OPT_TPB], pq[OPT_CHUNK / OPT_TPB];
+#pragma unroll
+    for (int q = 0; q < OPT_CHUNK / OPT_TPB; ++q) {  // every load of the chunk before the first store
+      const long long i = first + q * OPT_TPB + threadIdx.x;
+      const bool ok = i < n;
+      gq[q] = ok ? g[i] : 0.0f; mq[q] = ok ? m[i] : 0.0f; vq[q] = ok ? v[i] : 0.0f; pq[q] = ok ? p[i] : 0.0f;
+    }
+#pragma unroll
+    for (int q = 0; q < OPT_CHUNK / OPT_TPB; ++q) {
+      const long long i = first + q * OPT_TPB + threadIdx.x;
+      if (i < n) {
+        const float gi = gq[q] * gs;
+        const float mi = mq[q] + (1.0f - beta1) * (gi - mq[q]);
+        const float vi = beta2 * vq[q] + (1.0f - beta2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        p[i] = pq[q] - step_size * (mi / (sqrtf(vi) * inv_bc2_sqrt + eps));
+      }
     }
   }
 }
@@ -111,7 +140,7 @@ extern "C" int asvrl_clip_adam_step(const asvrl_adam_tensors* tensors, float max
   if (tensors->n == 0) return 0;
   AdamList L;
   L.n = tensors->n;
-  long long total = 0;
+  long long total = 0;  // work items so far
   for (int t = 0; t < L.n; ++t) {
     if (!tensors->param[t] || !tensors->grad[t] || !tensors->exp_avg[t] || !tensors->exp_avg_sq[t] ||
         !tensors->step[t] || tensors->numel[t] < 0)
@@ -119,10 +148,13 @@ extern "C" int asvrl_clip_adam_step(const asvrl_adam_tensors* tensors, float max
     L.param[t] = tensors->param[t]; L.grad[t] = tensors->grad[t];
     L.exp_avg[t] = tensors->exp_avg[t]; L.exp_avg_sq[t] = tensors->exp_avg_sq[t]; L.step[t] = tensors->step[t];
     L.numel[t] = tensors->numel[t];
-    total += tensors->numel[t];
+    total += (tensors->numel[t] + OPT_CHUNK - 1) / OPT_CHUNK;
+    if (total > 0x7fffffffLL) return fail(ASVRL_E_LIMIT, "asvrl_clip_adam_step: too many elements");
+    L.chunk_end[t] = (int)total;
   }
-  long long want = (total + OPT_TPB * 4 - 1) / (OPT_TPB * 4);
-  const int grid = (int)(want < 1 ? 1 : (want > OPT_GRID ? OPT_GRID : want));
+  L.n_chunks = (int)total;
+  if (L.n_chunks == 0) return 0;
+  const int grid = L.n_chunks > OPT_GRID ? OPT_GRID : L.n_chunks;
   cudaStream_t s = (cudaStream_t)stream;
   float* scal = scratch;                                     // [1 + 2 * ASVRL_OPT_MAX_TENSORS]
   float* part = scratch + 1 + 2 * ASVRL_OPT_MAX_TENSORS;     // [OPT_GRID]

@@ -138,8 +138,8 @@ static int tower_dims(const char* what, int batch, int self_dim, int obj_dim, in
 }
 
 static int tower_bwd_grid(int batch) {
-  int g = (batch + 31) / 32;
-  return g > 16 ? 16 : (g < 1 ? 1 : g);
+  int g = (batch + 15) / 16;
+  return g > 64 ? 64 : (g < 1 ? 1 : g);
 }
 
 extern "C" int asvrl_tower_fwd(const float* self_obs, const float* objects, const float* mask,

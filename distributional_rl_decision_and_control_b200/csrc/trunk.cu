@@ -19,8 +19,8 @@
 namespace asvrl {
 
 constexpr int TR_TPB = 256;
-constexpr int TR_SPB = 4;     // samples per CTA in scale_relu_bwd
-constexpr int TR_RPC = 128;   // rows per CTA in head_bwd
+constexpr int TR_SPB = 2;     // samples per CTA in scale_relu_bwd
+constexpr int TR_RPC = 64;    // rows per CTA in head_bwd
 
 __device__ __forceinline__ float4 f4add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 __device__ __forceinline__ float4 f4mul(float4 a, float4 b) { return make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }

@@ -436,7 +436,7 @@ ASVRL_API long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, i
  * zero-initialised uint32 (left zero).  grad_scale = 1/world_size when the gradients hold an all-reduced SUM.  grad is not
  * modified (torch scales .grad in place; nothing on the path reads it afterwards). */
 #define ASVRL_OPT_MAX_TENSORS 64
-#define ASVRL_OPT_SCRATCH_FLOATS 256
+#define ASVRL_OPT_SCRATCH_FLOATS 320
 typedef struct asvrl_adam_tensors {
   int n;
   float* param[ASVRL_OPT_MAX_TENSORS];

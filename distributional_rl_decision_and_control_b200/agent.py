@@ -387,9 +387,11 @@ class Agent():
         taus = taus or {}
         self.optimizer.zero_grad(set_to_none=True)
         with torch.no_grad():
-            zn_all, _ = self.policy_target(next_states, N, taus=taus.get("target"))  # (B, N, A)
+            net_t = self.policy_target.forward_fused if self.fused_trunk else self.policy_target
+            zn_all, _ = net_t(next_states, N, taus=taus.get("target"))  # (B, N, A)
             z_next = zn_all.max(dim=2)[0]                                # AGENT:451-452
-        z_all, tau = self.policy_local(states, N, taus=taus.get("local"))
+        net = self.policy_local.forward_fused if self.fused_trunk else self.policy_local
+        z_all, tau = net(states, N, taus=taus.get("local"))
         a = actions[:, 0].long().view(B, 1, 1).expand(B, N, 1)           # AGENT:457-458
         z = z_all.gather(2, a).squeeze(-1)
         loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones, self.GAMMA, 1.0)

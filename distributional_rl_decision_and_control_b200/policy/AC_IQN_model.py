@@ -16,7 +16,21 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .iqn_ops import TauSampler, critic_trunk, observation_tower
+from .iqn_ops import TauSampler, critic_trunk, linear_scale_relu, observation_tower
+
+
+_UNIT = {}
+
+
+def _unit_scale(B, D, device):
+    """ones (B, D): the unit `scale` of K5's scale_relu when a layer is a plain Linear + ReLU."""
+    key = (B, D, device)
+    t = _UNIT.get(key)
+    if t is None:
+        if len(_UNIT) > 64:
+            _UNIT.clear()
+        t = _UNIT[key] = torch.ones((B, D), dtype=torch.float32, device=device)
+    return t
 
 
 def encoder(input_dimension, output_dimension):
@@ -102,8 +116,15 @@ class Actor(_ObservationTower):
         return self._features(x)
 
     def forward(self, x):
-        h = F.relu(self.hidden_layer(self._features(x)))
-        h = F.relu(self.hidden_layer_2(h))
+        feats = self._features(x)
+        if self.fused_tower and feats.is_cuda and feats.dtype == torch.float32:
+            # bias + ReLU of the two hidden layers in K5 (one launch per layer, one for its backward)
+            ones = _unit_scale(feats.shape[0], self.hidden_dimension, feats.device)
+            h = linear_scale_relu(feats, self.hidden_layer.weight, self.hidden_layer.bias, ones, 1)
+            h = linear_scale_relu(h, self.hidden_layer_2.weight, self.hidden_layer_2.bias, ones, 1)
+        else:
+            h = F.relu(self.hidden_layer(feats))
+            h = F.relu(self.hidden_layer_2(h))
         return self.atan_scale * torch.atan(self.output_layer(h))  # into (-1, 1), ACIQN:320-321
 
     def get_constructor_parameters(self):
@@ -180,15 +201,16 @@ class Critic(_ObservationTower):
               self.hidden_layer.bias, self.hidden_layer_2.weight, self.hidden_layer_2.bias,
               self.output_layer.weight, self.output_layer.bias]
         enc = self.action_encoder[0]
+        B = actions.shape[0]
+        ones = _unit_scale(B, self.hidden_dimension, actions.device)
         if param_grads:
             feats = self._features(x)
-            aenc = self.action_encoder(actions)
+            aenc = linear_scale_relu(actions, enc.weight, enc.bias, ones, 1)
         else:
             with torch.no_grad():
                 feats = self._features(x)
             ps = [p.detach() for p in ps]
-            aenc = F.relu(F.linear(actions, enc.weight.detach(), enc.bias.detach()))
-        B = feats.shape[0]
+            aenc = linear_scale_relu(actions, enc.weight.detach(), enc.bias.detach(), ones, 1)
         cos, taus = self.calc_cos(B, num_tau, cvar, taus)
         z = critic_trunk(cos.reshape(B * num_tau, self.n), feats, aenc, *ps, num_tau)
         return z, taus

@@ -169,3 +169,35 @@ def observation_tower(self_obs, objects, mask, Ws, bs, Wo, bo):
     if not self_obs.is_cuda:
         raise RuntimeError("observation_tower runs on CUDA only (no CPU fallback)")
     return _Tower.apply(self_obs, objects, mask, Ws, bs, Wo, bo)
+
+
+class _LinearScaleRelu(torch.autograd.Function):
+    """out[m] = scale[m // n_tau] * relu(x[m] W^T + bias): a cuBLAS GEMM without epilogue, then K5's
+    scale_relu pass; the backward is K5's one pass (dpre, dscale, dbias) plus the two GEMMs.
+    The IQN network's trunk (IQN:74-86) is three of these (scale = the state features, then ones)."""
+
+    @staticmethod
+    def forward(ctx, x, W, bias, scale, n_tau):
+        x, scale = x.contiguous(), scale.contiguous()
+        pre = x @ W.t()
+        out = _lib.iqn_scale_relu_fwd(pre, bias, scale, n_tau)
+        ctx.save_for_backward(x, W, bias, scale, pre)
+        ctx.n_tau = n_tau
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, W, bias, scale, pre = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        want_dpre = need[0] or need[1]
+        dpre, dscale, dbias = _lib.iqn_scale_relu_bwd(dout.contiguous(), pre, bias, scale, ctx.n_tau,
+                                                      want_dpre=want_dpre, want_dscale=need[3], want_dbias=need[2])
+        dx = dpre @ W if need[0] else None
+        dW = _wgrad(dpre, x) if need[1] else None
+        return dx, dW, dbias, dscale, None
+
+
+def linear_scale_relu(x, W, bias, scale, n_tau):
+    if not x.is_cuda:
+        raise RuntimeError("linear_scale_relu runs on CUDA only (no CPU fallback)")
+    return _LinearScaleRelu.apply(x, W, bias, scale, int(n_tau))

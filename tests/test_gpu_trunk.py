@@ -193,3 +193,27 @@ def test_clip_adam_matches_torch(gscale):
             assert (p.detach() - q.detach()).abs().max().item() <= 2e-7 * max(1.0, q.abs().max().item())
     assert opt.step_count.tolist() == [5.0, 5.0, 4.0] + [5.0] * 6
     assert int(opt._counter.item()) == 0
+
+
+@pytest.mark.parametrize("B,N", [(64, 8), (256, 32), (3, 5)])
+def test_fused_iqn_network_matches_module_path(B, N):
+    """IQN_Policy.forward_fused (K5 + K6) against the module-by-module autograd path."""
+    from distributional_rl_decision_and_control_b200.policy.IQN_model import IQN_Policy
+    net = IQN_Policy(7, 5, 5, 56, 40, 256, 128, 25, device=DEV, seed=7).to(DEV)
+    x, _ = _critic_inputs(B, 100 + B)
+    taus = torch.rand((B, N), device=DEV, generator=torch.Generator(device=DEV).manual_seed(1))
+    wz = torch.randn((B, N, 25), device=DEV, generator=torch.Generator(device=DEV).manual_seed(2))
+
+    def run(fn):
+        net.zero_grad(set_to_none=True)
+        z, _ = fn(x, N, taus=taus)
+        (z * wz).sum().backward()
+        return z.detach(), {n: p.grad.clone() for n, p in net.named_parameters()}
+
+    net.fused_tower = False
+    z0, g0 = run(net.forward)
+    net.fused_tower = True
+    z1, g1 = run(net.forward_fused)
+    close(z1, z0, "quantiles")
+    for n in g0:
+        close(g1[n], g0[n], f"grad {n}", rtol=2e-5)

@@ -177,6 +177,47 @@ def time_kernel(fn, K, W, per_graph=20):
     return e0.elapsed_time(e1) / (reps * per_graph)
 
 
+def training_leg(args, precision, dev, pg, rank, world, barrier, dist):
+    """BASELINE config 4, per-GPU share: collection policy forward for every ASV (act_batch), the fused
+    step, K2a push, and one AC-IQN update (B=1024, N=32) per `update_every` batched steps, all as CUDA
+    graphs; the only collective is the gradient all-reduce.  Device-timed, max over ranks."""
+    import torch
+    from distributional_rl_decision_and_control_b200.agent import Agent
+    from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
+    from distributional_rl_decision_and_control_b200.vector_trainer import VectorTrainer
+    ET = args.train_envs
+    agent = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=1024, num_tau=32, BUFFER_SIZE=1 << 20,
+                  process_group=pg, rank=rank, matmul_precision=precision)
+    env = BatchedMarineNavEnv(ET, R, O, args.cores, device=dev, seed=args.seed + 11, env_offset=rank * ET,
+                              fused=True, prefetch="workers")
+    vt = VectorTrainer(env, agent, update_every=args.update_every, learning_starts=8, cuda_graph=True)
+    vt.learn(40)  # reset, fill the ring, capture both graphs
+    n_steps = 400
+    t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    steps0, upd0 = vt.steps, vt.updates
+    barrier()
+    t0e.record()
+    since = 0
+    while vt.steps - steps0 < n_steps:
+        since += vt.collect(0.05)
+        if since >= vt.update_every:
+            since = 0
+            agent.train_graph_replay()
+            vt.updates += 1
+    t1e.record()
+    barrier()
+    tms = torch.tensor([t0e.elapsed_time(t1e)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    tsec = float(tms.item()) * 1e-3
+    return {"env_steps_per_sec": world * ET * (vt.steps - steps0) / tsec,
+            "updates_per_sec": (vt.updates - upd0) / tsec, "envs_per_gpu": ET,
+            "batched_steps": vt.steps - steps0, "update_every_batched_steps": vt.update_every,
+            "batch_per_gpu": 1024, "n_tau": 32, "gemm": precision,
+            "what": "act_batch (policy forward for envs x 8 ASVs, eps-greedy) + fused step + replay push per "
+                    "batched step, one AC-IQN update per update_every steps; CUDA graphs"}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -382,6 +423,17 @@ def run_b200(args):
                             "note": "graph of 20 back-to-back launches; 0.5 MB per launch is latency bound"}
     learner["k3_tau_cos"] = {"ms": k3_ms, "algorithmic_bytes": k3_bytes, "achieved_gbs": k3_bytes / (k3_ms * 1e-3) / 1e9,
                              "frac": k3_bytes / (k3_ms * 1e-3) / 1e9 / peak}
+    # ---- (5) training leg (BASELINE config 4, per-GPU share): collection policy forward for every ASV,
+    # the fused step, K2a push, and one AC-IQN update (B=1024, N=32) per `update_every` batched steps,
+    # all as CUDA graphs; the only collective is the gradient all-reduce.  Device-timed.
+    training = None
+    if not args.profile:
+        training = {}
+        for prec in ("fp32", "tf32"):
+            try:
+                training[prec] = training_leg(args, prec, dev, pg, rank, world, barrier, dist)
+            except Exception as e:  # the headline legs above must not be lost to this one
+                training[prec] = {"error": f"{type(e).__name__}: {e}"[:300]}
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -423,7 +475,7 @@ def run_b200(args):
                                    else "env_step_kernel<false,false>", "kernel_ms": k1_ms,
                          "algorithmic_bytes_per_launch": per_launch,
                          "note": "instruction-issue bound by design (SURVEY.md F5); see profiles/"},
-            "learner": learner,
+            "learner": learner, "training": training,
             "clocks": sampler.summary(), "finite": finite,
         }
         if world == 1 and not args.no_cpu:
@@ -483,6 +535,8 @@ def main():
     ap.add_argument("--prefetch", default="stream", choices=["stream", "workers", "off"])
     ap.add_argument("--no-stagger", action="store_true", help="start every episode clock at 0")
     ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
+    ap.add_argument("--train-envs", type=int, default=8192, help="envs per GPU of the training leg (config 4: 65536 / 8)")
+    ap.add_argument("--update-every", type=int, default=4, help="batched steps per learner update in the training leg")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: few env steps, three EAGER learner updates per shape (no graph), "
                          "no e2e / CPU legs; the numbers it prints are not bench values")

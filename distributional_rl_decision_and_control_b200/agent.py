@@ -246,6 +246,12 @@ class Agent():
 
     @torch.no_grad()
     def act_batch(self, obs, eps=0.0, cvar=1.0):
+        """``_act_batch`` under this agent's GEMM arithmetic (fp32 like the reference, or TF32 with
+        ``matmul_precision="tf32"``)."""
+        with self._precision():
+            return self._act_batch(obs, eps, cvar)
+
+    def _act_batch(self, obs, eps=0.0, cvar=1.0):
         """Vectorised epsilon-greedy for M ASVs at once: ``obs`` = (self (M,7), objects (M,5,5),
         mask (M,5)) CUDA tensors.  Returns float32 (M,2) actions (AC-IQN) or int32 (M,) action ids
         (IQN), still on the device.  ``eps`` may be a 0-d CUDA tensor (so a captured CUDA graph

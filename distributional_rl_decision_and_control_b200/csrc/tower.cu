@@ -23,38 +23,33 @@ struct TowerDims {
   int B, SD, OD, K, SF, OF, W;  // W = SF + K * OF
 };
 
-__global__ void __launch_bounds__(256)
+// Thread j owns feature column j: its weight row (<= 8 values) and bias live in registers, the CTA
+// walks batch rows b = blockIdx.x, += gridDim.x.  No index division, no shared memory; the
+// observation loads of a row are warp broadcasts and the 4*W-byte feature row is one coalesced store.
+__global__ void __launch_bounds__(1024)
 tower_fwd_kernel(const float* __restrict__ self_obs, const float* __restrict__ objects,
                  const float* __restrict__ mask, const float* __restrict__ Ws, const float* __restrict__ bs,
                  const float* __restrict__ Wo, const float* __restrict__ bo, TowerDims d,
                  float* __restrict__ feats) {
-  extern __shared__ float tw_sm[];
-  float* sWs = tw_sm;                 // [SF][SD]
-  float* sbs = sWs + d.SF * d.SD;     // [SF]
-  float* sWo = sbs + d.SF;            // [OF][OD]
-  float* sbo = sWo + d.OF * d.OD;     // [OF]
-  for (int i = threadIdx.x; i < d.SF * d.SD; i += blockDim.x) sWs[i] = Ws[i];
-  for (int i = threadIdx.x; i < d.SF; i += blockDim.x) sbs[i] = bs[i];
-  for (int i = threadIdx.x; i < d.OF * d.OD; i += blockDim.x) sWo[i] = Wo[i];
-  for (int i = threadIdx.x; i < d.OF; i += blockDim.x) sbo[i] = bo[i];
-  __syncthreads();
-  const long total = (long)d.B * d.W;
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int b = (int)(i / d.W), j = (int)(i - (long)b * d.W);
-    float acc;
-    if (j < d.SF) {
-      const float* x = self_obs + (size_t)b * d.SD;
-      acc = sbs[j];
-      for (int q = 0; q < d.SD; ++q) acc = fmaf(sWs[j * d.SD + q], x[q], acc);
-      acc = fmaxf(acc, 0.0f);
-    } else {
-      const int k = (j - d.SF) / d.OF, f = (j - d.SF) - k * d.OF;
-      const float* x = objects + ((size_t)b * d.K + k) * d.OD;
-      acc = sbo[f];
-      for (int q = 0; q < d.OD; ++q) acc = fmaf(sWo[f * d.OD + q], x[q], acc);
-      acc = mask[(size_t)b * d.K + k] >= 0.5f ? fmaxf(acc, 0.0f) : 0.0f;
-    }
-    feats[i] = acc;
+  const int j = threadIdx.x;
+  if (j >= d.W) return;
+  const bool own = j < d.SF;
+  const int k = own ? 0 : (j - d.SF) / d.OF;
+  const int f = own ? j : (j - d.SF) - k * d.OF;
+  const int nin = own ? d.SD : d.OD;
+  float w[TW_MAXIN];
+#pragma unroll
+  for (int q = 0; q < TW_MAXIN; ++q) w[q] = q < nin ? (own ? Ws[f * d.SD + q] : Wo[f * d.OD + q]) : 0.0f;
+  const float bias = own ? bs[f] : bo[f];
+  for (int b = blockIdx.x; b < d.B; b += gridDim.x) {
+    const float* x = own ? self_obs + (size_t)b * d.SD : objects + ((size_t)b * d.K + k) * d.OD;
+    float acc = bias;
+#pragma unroll
+    for (int q = 0; q < TW_MAXIN; ++q)
+      if (q < nin) acc = fmaf(w[q], x[q], acc);
+    acc = fmaxf(acc, 0.0f);
+    if (!own && !(mask[(size_t)b * d.K + k] >= 0.5f)) acc = 0.0f;
+    feats[(size_t)b * d.W + j] = acc;
   }
 }
 
@@ -150,13 +145,12 @@ extern "C" int asvrl_tower_fwd(const float* self_obs, const float* objects, cons
     return fail(ASVRL_E_BADARG, "asvrl_tower_fwd: null pointer");
   TowerDims d;
   if (int rc = tower_dims("asvrl_tower_fwd", batch, self_dim, obj_dim, max_obj, self_feat, obj_feat, &d)) return rc;
-  const long total = (long)d.B * d.W;
-  long grid = (total + 255) / 256;
-  if (grid > 148 * 8) grid = 148 * 8;
-  const size_t smem = sizeof(float) * (size_t)(d.SF * d.SD + d.SF + d.OF * d.OD + d.OF);
-  if (smem > 48 * 1024) return fail(ASVRL_E_LIMIT, "asvrl_tower_fwd: encoder weights exceed 48 KB");
-  tower_fwd_kernel<<<(int)grid, 256, smem, (cudaStream_t)stream>>>(self_obs, objects, mask, w_self, b_self,
-                                                                   w_obj, b_obj, d, feats);
+  const int threads = (d.W + 31) / 32 * 32;
+  const int per_sm = 2048 / threads > 0 ? 2048 / threads : 1;
+  int grid = 148 * per_sm;
+  if (grid > d.B) grid = d.B;
+  tower_fwd_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(self_obs, objects, mask, w_self, b_self, w_obj,
+                                                                b_obj, d, feats);
   return check_launch("asvrl_tower_fwd");
 }
 

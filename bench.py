@@ -346,13 +346,15 @@ def run_b200(args):
     # status D2H, and the caller touches the results (a checksum of the rewards) before it sends
     # the shard's next actions.
     from distributional_rl_decision_and_control_b200.envs.marinenav.host_pipeline import HostPipelinedEnv
-    G = 2
+    G = args.e2e_groups
     henv = HostPipelinedEnv(E, R, O, C, groups=G, device=dev, seed=args.seed + 3, env_offset=rank * E,
                             fused=not args.unfused)
     if not args.no_stagger:
         for sh in henv.shards:
             sh.state["ep_steps"].copy_(torch.randint(0, 1000, (sh.E,), device=dev, generator=gen, dtype=torch.int32))
     host_actions = [[p[g * henv.E:(g + 1) * henv.E].cpu().pin_memory() for g in range(G)] for p in pool]
+    if not args.unfused and not args.e2e_eager:
+        henv.enable_cuda_graph()  # one graph launch per send: [actions H2D, fused step, results D2H]
     torch.cuda.synchronize()
     for i in range(W):
         for g in range(G):
@@ -360,14 +362,15 @@ def run_b200(args):
     for g in range(G):
         henv.recv(g)
     barrier()
+    reward_np = [henv.host_out[g]["reward"].numpy() for g in range(G)]
     t0 = time.perf_counter()
     for g in range(G):
         henv.send(g, host_actions[0][g])
     checksum = 0.0
     for i in range(1, K + 1):
         for g in range(G):
-            res = henv.recv(g)                      # results of shard g's step i-1 are on the host
-            checksum += float(res["reward"][0, 0])  # the caller reads them
+            henv.recv(g)                            # results of shard g's step i-1 are on the host
+            checksum += float(reward_np[g][0, 0])   # the caller reads them (numpy view of the pinned block)
             if i < K:
                 henv.send(g, host_actions[i % 8][g])
     e2e_s = time.perf_counter() - t0
@@ -466,8 +469,9 @@ def run_b200(args):
                               else "flushed between timed steps (256 MiB write)"), "parallelism": f"envs sharded x{world}, no collective"},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
                     "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": e2e_d2h,
-                    "api": "HostPipelinedEnv.send/recv, 2 shards of E/2 envs; obs_self + obs_objects + reward + "
-                           "status per ASV (the mask is objects[...,4] != 0, as in the reference's step())"},
+                    "api": ("HostPipelinedEnv.send/recv, %d shards of E/%d envs, one CUDA graph launch per send "
+                           "(actions H2D, fused step, results D2H); obs_self + obs_objects + reward + "
+                           "status per ASV (the mask is objects[...,4] != 0, as in the reference's step())") % (G, G)},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": k1_traffic(E, C, env.fused), "peak_source": which,
@@ -537,6 +541,8 @@ def main():
     ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
     ap.add_argument("--train-envs", type=int, default=8192, help="envs per GPU of the training leg (config 4: 65536 / 8)")
     ap.add_argument("--update-every", type=int, default=4, help="batched steps per learner update in the training leg")
+    ap.add_argument("--e2e-groups", type=int, default=4, help="shards of the host pipeline (send / recv)")
+    ap.add_argument("--e2e-eager", action="store_true", help="e2e leg without the per-shard CUDA graphs")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: few env steps, three EAGER learner updates per shape (no graph), "
                          "no e2e / CPU legs; the numbers it prints are not bench values")

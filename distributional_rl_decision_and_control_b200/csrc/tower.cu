@@ -41,7 +41,8 @@ tower_fwd_kernel(const float* __restrict__ self_obs, const float* __restrict__ o
 #pragma unroll
   for (int q = 0; q < TW_MAXIN; ++q) w[q] = q < nin ? (own ? Ws[f * d.SD + q] : Wo[f * d.OD + q]) : 0.0f;
   const float bias = own ? bs[f] : bo[f];
-  for (int b = blockIdx.x; b < d.B; b += gridDim.x) {
+#pragma unroll 4
+  for (int b = blockIdx.x; b < d.B; b += gridDim.x) {  // unrolled: four rows' loads in flight per thread
     const float* x = own ? self_obs + (size_t)b * d.SD : objects + ((size_t)b * d.K + k) * d.OD;
     float acc = bias;
 #pragma unroll

@@ -191,3 +191,37 @@ def test_host_pipelined_env_matches_plain_shards():
                 assert torch.equal(got[k], want[k].cpu()), (t, g, k)
             mask = (got["obs_objects"][..., 4] != 0).float()  # the mask the caller derives
             assert torch.equal(mask, want["obs_mask"].cpu()), (t, g)
+
+
+def test_host_pipelined_env_cuda_graph_matches_plain_shards():
+    """The captured [H2D, fused step, D2H] graph of every shard returns what BatchedMarineNavEnv.step
+    produces on the same actions (the two warm-up steps of the capture are replayed on the plain envs)."""
+    from distributional_rl_decision_and_control_b200.envs.marinenav.host_pipeline import HostPipelinedEnv
+    E, R, G = 64, 8, 2
+    h = HostPipelinedEnv(E, R, 10, 4, groups=G, device=DEV, seed=5)
+    plain = [BatchedMarineNavEnv(E // G, R, 10, 4, device=DEV, seed=5, env_offset=g * (E // G)) for g in range(G)]
+    for p in plain:
+        p.reset()
+    for env in plain + h.shards:
+        env.state["ep_steps"][::3] = 997
+    torch.cuda.synchronize()
+    h.enable_cuda_graph()
+    zero = torch.zeros((E // G, R, 2), device=DEV)
+    for p in plain:  # enable_cuda_graph stepped every shard twice with zero actions
+        p.step(zero)
+        p.step(zero)
+    gen = torch.Generator().manual_seed(3)
+    for t in range(7):
+        acts = [(torch.rand((E // G, R, 2), generator=gen) * 2 - 1).pin_memory() for _ in range(G)]
+        for g in range(G):
+            if t % 2:  # in place in the staging buffer, or copied into it by send()
+                h.action_buffer(g).copy_(acts[g])
+                h.send(g, h.action_buffer(g))
+            else:
+                h.send(g, acts[g])
+        for g in range(G):
+            got = h.recv(g)
+            want = plain[g].step(acts[g].to(DEV))
+            torch.cuda.synchronize()
+            for k in ("obs_self", "obs_objects", "reward", "status"):
+                assert torch.equal(got[k], want[k].cpu()), (t, g, k)

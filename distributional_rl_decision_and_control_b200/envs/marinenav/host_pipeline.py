@@ -2,7 +2,7 @@
 
 A CPU-side caller of the reference's ``step()`` hands in actions and reads back observations, rewards
 and done flags; with the environments on the GPU that is one small H2D copy, the fused step launch
-and one large D2H copy per call, and the D2H copy (34 words per ASV) is what bounds the rate.  The
+and one large D2H copy per call (34 words per ASV).  The
 environments are therefore split into ``groups`` independent shards, each with its own stream and
 pinned buffers: while the caller works on the results of one shard, the copy of the next one and the
 kernel of the one after are in flight.  Every shard is stepped synchronously with respect to itself

@@ -172,3 +172,12 @@ class AdamTensors(C.Structure):
                 ("exp_avg", C.c_void_p * OPT_MAX_TENSORS), ("exp_avg_sq", C.c_void_p * OPT_MAX_TENSORS),
                 ("step", C.c_void_p * OPT_MAX_TENSORS),
                 ("numel", C.c_longlong * OPT_MAX_TENSORS)]
+
+
+MAX_PEERS = 8
+
+
+class PeerBuckets(C.Structure):
+    """asvrl_peer_buckets (include/asvrl.h)."""
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("bucket", C.c_void_p * MAX_PEERS),
+                ("half_floats", C.c_longlong)]

@@ -59,6 +59,8 @@ _SIGNATURES = {
     "asvrl_tower_fwd": (C.c_int, [f32p] * 7 + [C.c_int] * 6 + [f32p, vp]),
     "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
     "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
+    "asvrl_clip_adam_step_p2p": (C.c_int, [C.POINTER(_abi.AdamTensors), C.POINTER(_abi.PeerBuckets), f32p, u32p]
+                                 + [C.c_float] * 5 + [f32p, f32p, u32p, vp]),
     "asvrl_clip_adam_step": (C.c_int, [C.POINTER(_abi.AdamTensors)] + [C.c_float] * 6 + [f32p, f32p, u32p, vp]),
 }
 EXPORTED = tuple(_SIGNATURES)
@@ -409,7 +411,7 @@ def tower_bwd(dfeats, feats, self_obs, objects, SF, OF):
 
 # ------------------------------------------------------------------ K7: clip + Adam
 def clip_adam_step(params, grads, exp_avgs, exp_avg_sqs, steps, max_norm, lr, beta1, beta2, eps, grad_scale,
-                   norm_out, scratch, counter):
+                   norm_out, scratch, counter, peers=None, grad_sum=None, epoch=None):
     """One optimiser step over the tensor lists (<= 64 tensors per call is the ABI limit)."""
     if len(params) > _abi.OPT_MAX_TENSORS:
         raise RuntimeError(f"clip_adam_step: more than {_abi.OPT_MAX_TENSORS} tensors")
@@ -422,6 +424,12 @@ def clip_adam_step(params, grads, exp_avgs, exp_avg_sqs, steps, max_norm, lr, be
         t.param[i], t.grad[i], t.exp_avg[i], t.exp_avg_sq[i] = ptr(p, f), ptr(g, f), ptr(m, f), ptr(v, f)
         t.step[i] = ptr(st, f)
         t.numel[i] = p.numel()
+    if peers is not None:  # all-reduce over NVLink peer memory inside the kernels (grad_scale = 1 / world)
+        rc = lib().asvrl_clip_adam_step_p2p(C.byref(t), C.byref(peers), ptr(grad_sum, f), ptr(epoch, torch.int32),
+                                            max_norm, lr, beta1, beta2, eps, ptr(norm_out, f), ptr(scratch, f),
+                                            ptr(counter, torch.int32), stream_ptr())
+        check(rc, "asvrl_clip_adam_step_p2p")
+        return
     rc = lib().asvrl_clip_adam_step(C.byref(t), max_norm, lr, beta1, beta2, eps, grad_scale,
                                     ptr(norm_out, f), ptr(scratch, f), ptr(counter, torch.int32), stream_ptr())
     check(rc, "asvrl_clip_adam_step")

@@ -5,10 +5,15 @@ foreach Adam whose scalar-tensor pow falls back to one launch per parameter).
 
 Same arithmetic and hyper-parameter defaults as torch.optim.Adam(lr, betas=(0.9, 0.999), eps=1e-8,
 weight_decay=0, amsgrad=False); the step counts live in device floats (one per tensor, like torch), so the update is CUDA-graph
-capturable.  With a process group the gradients are summed over the ranks in ONE flat bucket
-(NCCL all-reduce) and the average is folded into the kernel's gradient scale — every rank clips
-the same global gradient and the replicas stay bit-identical.  CUDA only.
+capturable.  With a process group the gradients of all ranks are summed in ONE flat bucket and the
+average is folded into the kernel's gradient scale — every rank clips the same global gradient and
+the replicas stay bit-identical.  The sum is computed by K7 itself over NVLink peer
+memory (a one-shot all-reduce fused into the norm kernel: pack + flag, wait + sum + norm, Adam)
+when the ranks can map each other's buckets, else by one NCCL all-reduce.  CUDA only.
 """
+import os
+import warnings
+
 import torch
 
 from .. import _abi, _lib
@@ -38,8 +43,40 @@ class ClipAdam:
         self.grad_norm = torch.zeros((1,), dtype=torch.float32, device=dev)   # total norm of the last step
         self._scratch = torch.zeros((_abi.OPT_SCRATCH_FLOATS,), dtype=torch.float32, device=dev)
         self._counter = torch.zeros((1,), dtype=torch.int32, device=dev)
+        # N > 1: the exchange step runs inside K7 over NVLink peer memory when the ranks can map each
+        # other's buckets (torch symmetric memory); otherwise one NCCL all-reduce of the flat bucket
+        self._peers = None
+        if process_group is not None and os.environ.get("ASVRL_P2P_ALLREDUCE", "1") != "0":
+            try:
+                self._setup_p2p(sum(sizes), dev)
+            except Exception as e:  # no peer access / no symmetric memory on this stack: NCCL path
+                warnings.warn(f"ClipAdam: peer-memory all-reduce unavailable ({type(e).__name__}: {e}); using NCCL")
+                self._peers = None
         # torch.optim-shaped view for code that inspects the learning rate
         self.param_groups = [{"params": self.params, "lr": self.lr, "betas": self.betas, "eps": self.eps}]
+
+    def _setup_p2p(self, total, dev):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        world = dist.get_world_size(self.process_group)
+        if world > _abi.MAX_PEERS:
+            raise RuntimeError(f"more than {_abi.MAX_PEERS} ranks")
+        half = (total + 63) // 64 * 64
+        bucket = symm_mem.empty(2 * half + 64, dtype=torch.float32, device=dev)  # [half 0 | half 1 | flags]
+        bucket.zero_()
+        torch.cuda.synchronize(dev)
+        hdl = symm_mem.rendezvous(bucket, group=self.process_group)
+        peers = _abi.PeerBuckets()
+        peers.world, peers.rank, peers.half_floats = hdl.world_size, hdl.rank, half
+        ptrs = list(hdl.buffer_ptrs)
+        for r in range(hdl.world_size):
+            peers.bucket[r] = int(ptrs[r])
+        self._bucket, self._hdl = bucket, hdl          # keep the mapping alive
+        self._grad_sum = torch.zeros((total,), dtype=torch.float32, device=dev)
+        self._epoch = torch.zeros((1,), dtype=torch.int32, device=dev)
+        dist.barrier(group=self.process_group)          # every bucket is zeroed before anyone signals
+        torch.cuda.synchronize(dev)
+        self._peers = peers
 
     def zero_grad(self, set_to_none=True):
         for p in self.params:
@@ -57,6 +94,14 @@ class ClipAdam:
             return
         grads = [g if g.is_contiguous() else g.contiguous() for _, g, _, _, _ in live]
         scale = 1.0
+        if self._peers is not None:  # the exchange step happens inside K7 (peer-memory one-shot all-reduce)
+            if len(live) != len(self.params):
+                raise RuntimeError("ClipAdam (peer-memory path): every parameter needs a gradient on every rank")
+            _lib.clip_adam_step([x[0].data for x in live], grads, [x[2] for x in live], [x[3] for x in live],
+                                [x[4] for x in live], self.max_norm, self.lr, self.betas[0], self.betas[1],
+                                self.eps, 1.0, self.grad_norm, self._scratch, self._counter,
+                                peers=self._peers, grad_sum=self._grad_sum, epoch=self._epoch)
+            return
         if self.process_group is not None:  # the one exchange step: a flat fp32 bucket, summed
             import torch.distributed as dist
             flat = torch.cat([g.reshape(-1) for g in grads])

@@ -451,6 +451,25 @@ ASVRL_API int asvrl_clip_adam_step(const asvrl_adam_tensors* tensors, float max_
                                    float* norm_out /* nullable */, float* scratch, uint32_t* counter,
                                    void* stream);
 
+/* K7, multi-GPU: the same update with the all-reduce of the gradient bucket done by the kernels
+ * themselves over NVLink peer memory (one-shot, summed in rank order: bit-identical replicas)
+ * instead of an NCCL call.  bucket[r]: rank r's symmetric buffer, peer-mapped into this process
+ * (e.g. torch.distributed._symmetric_memory), laid out [half 0 | half 1 | >= 16 uint32 flag words],
+ * half_floats floats per half, zero-initialised before the first call on any rank.  grad_sum:
+ * local scratch of the summed gradient (>= total floats); epoch: device uint32, zero-initialised,
+ * advanced by every call (all ranks must call in lock step).  A peer that never arrives makes the
+ * wait give up after ~2^26 polls and norm_out read NaN (no hang). */
+#define ASVRL_MAX_PEERS 8
+typedef struct asvrl_peer_buckets {
+  int world, rank;
+  float* bucket[ASVRL_MAX_PEERS];
+  long long half_floats;
+} asvrl_peer_buckets;
+ASVRL_API int asvrl_clip_adam_step_p2p(const asvrl_adam_tensors* tensors, const asvrl_peer_buckets* peers,
+                                       float* grad_sum, uint32_t* epoch, float max_norm, float lr,
+                                       float beta1, float beta2, float eps, float* norm_out /* nullable */,
+                                       float* scratch, uint32_t* counter, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

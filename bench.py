@@ -106,6 +106,16 @@ def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0):
     return n_envs * n_steps / dt, dt
 
 
+def grad_sync_kind(agent, world):
+    if world == 1:
+        return "none"
+    opt = getattr(agent, "critic_optimizer", None) or getattr(agent, "optimizer", None)
+    if getattr(opt, "_peers", None) is not None:
+        return ("one-shot all-reduce of the flat bucket over NVLink peer memory inside K7 (pack + flag, "
+                "wait + rank-ordered sum + norm, Adam), before clipping")
+    return "nccl all-reduce of the flat bucket, before clipping"
+
+
 def k1_traffic(E, C, fused):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
     `ncu --set full` capture of this same command (profiles/k1_traffic.json); None for another shape."""
@@ -406,7 +416,7 @@ def run_b200(args):
         learner[name] = {"updates_per_sec": KL / (ms * 1e-3), "ms_per_update": ms / KL, "mode": mode,
                          "batch_per_gpu": ag.BATCH_SIZE, "n_tau": ag.num_tau, "last_critic_loss": loss,
                          "gemm": ag.matmul_precision,
-                         "grad_sync": "nccl all-reduce of the flat bucket, before clipping" if world > 1 else "none"}
+                         "grad_sync": grad_sync_kind(ag, world)}
     # K3 / K4 alone at C3 (their own rooflines)
     B3, N3 = 1024, 32
     g = torch.Generator(device=dev).manual_seed(5)

@@ -60,3 +60,37 @@ def test_bad_argument_codes_without_gpu(so):
     rc = so.asvrl_qhuber_fwd_bwd(None, None, None, None, None, 0.99, 1.0, 1, 1, 1, None, None, None, None, None)
     assert rc == _abi.E_BADARG
     assert b"null pointer" in so.asvrl_last_error_string()
+
+
+def test_bad_argument_codes_of_k5_k6_k7_without_gpu(so):
+    """Argument validation happens on the host before any launch: checkable on a CPU-only box."""
+    import ctypes as C
+    fake = 0x1000  # never dereferenced: the calls below fail validation first
+    assert so.asvrl_iqn_scale_relu_fwd(None, None, None, 1, 1, 128, None, None) == _abi.E_BADARG
+    assert so.asvrl_iqn_scale_relu_fwd(fake, fake, fake, 4, 8, 130, fake, None) == _abi.E_BADARG  # dim % 4
+    assert so.asvrl_iqn_scale_relu_bwd(fake, fake, fake, fake, 4, 8, 128, None, None, None, None, None, None) == _abi.E_BADARG
+    assert so.asvrl_iqn_scale_relu_bwd(fake, fake, fake, fake, 4, 8, 128, None, None, fake, None, None, None) == _abi.E_BADARG
+    assert so.asvrl_iqn_head_fwd(None, None, None, None, 4, 128, None, None) == _abi.E_BADARG
+    assert so.asvrl_iqn_head_bwd(fake, fake, fake, fake, 4, 128, fake, fake, None, None, None, None, None) == _abi.E_BADARG
+    assert so.asvrl_tower_fwd(None, None, None, None, None, None, None, 1, 7, 5, 5, 56, 40, None, None) == _abi.E_BADARG
+    assert so.asvrl_tower_fwd(fake, fake, fake, fake, fake, fake, fake, 1, 9, 5, 5, 56, 40, fake, None) == _abi.E_LIMIT
+    assert so.asvrl_iqn_scale_relu_bwd_partials(1024, 256) == 512 * 256
+    assert so.asvrl_tower_bwd_partials(1024, 5, 56, 40) == 64 * 96 * 9
+    t = _abi.AdamTensors()
+    t.n = _abi.OPT_MAX_TENSORS + 1
+    assert so.asvrl_clip_adam_step(C.byref(t), 0.5, 1e-4, 0.9, 0.999, 1e-8, 1.0, None, fake, fake, None) == _abi.E_LIMIT
+    t.n = 1
+    assert so.asvrl_clip_adam_step(C.byref(t), 0.5, 1e-4, 0.9, 0.999, 1e-8, 1.0, None, fake, fake, None) == _abi.E_BADARG
+    assert so.asvrl_clip_adam_step(C.byref(t), -1.0, 1e-4, 0.9, 0.999, 1e-8, 1.0, None, fake, fake, None) == _abi.E_BADARG
+    p = _abi.PeerBuckets()
+    p.world, p.rank = 9, 0
+    assert so.asvrl_clip_adam_step_p2p(C.byref(t), C.byref(p), fake, fake, 0.5, 1e-4, 0.9, 0.999, 1e-8, None,
+                                       fake, fake, None) == _abi.E_BADARG
+    assert ctypes_sizes_match()
+
+
+def ctypes_sizes_match():
+    """The ctypes mirrors of the by-value tensor / peer lists have the C layout (LP64)."""
+    import ctypes as C
+    n = _abi.OPT_MAX_TENSORS
+    return C.sizeof(_abi.AdamTensors) == 8 + 5 * 8 * n + 8 * n and C.sizeof(_abi.PeerBuckets) == 8 + 8 * _abi.MAX_PEERS + 8

@@ -364,7 +364,7 @@ def run_b200(args):
             sh.state["ep_steps"].copy_(torch.randint(0, 1000, (sh.E,), device=dev, generator=gen, dtype=torch.int32))
     host_actions = [[p[g * henv.E:(g + 1) * henv.E].cpu().pin_memory() for g in range(G)] for p in pool]
     if not args.unfused and not args.e2e_eager:
-        henv.enable_cuda_graph()  # one graph launch per send: [actions H2D, fused step, results D2H]
+        henv.enable_cuda_graph(zero_copy=args.e2e_zero_copy)  # one graph launch per send: [actions H2D, fused step, results D2H]
     torch.cuda.synchronize()
     for i in range(W):
         for g in range(G):
@@ -552,6 +552,8 @@ def main():
     ap.add_argument("--train-envs", type=int, default=8192, help="envs per GPU of the training leg (config 4: 65536 / 8)")
     ap.add_argument("--update-every", type=int, default=4, help="batched steps per learner update in the training leg")
     ap.add_argument("--e2e-groups", type=int, default=4, help="shards of the host pipeline (send / recv)")
+    ap.add_argument("--e2e-zero-copy", action="store_true",
+                    help="the step kernel stores its results straight into pinned host memory (no D2H copy node)")
     ap.add_argument("--e2e-eager", action="store_true", help="e2e leg without the per-shard CUDA graphs")
     ap.add_argument("--profile", action="store_true",
                     help="short run for ncu: few env steps, three EAGER learner updates per shape (no graph), "

@@ -110,6 +110,7 @@ tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ fea
     const int nin = c < d.SF ? d.SD : d.OD;
     if (q < TW_MAXIN && q >= nin) continue;
     float s = 0.0f;
+#pragma unroll 8
     for (int g = 0; g < (int)gridDim.x; ++g) s += __ldcg(part + (size_t)g * n_val + o);
     if (c < d.SF) { if (q == TW_MAXIN) dbs[c] = s; else dWs[c * d.SD + q] = s; }
     else { const int f = c - d.SF; if (q == TW_MAXIN) dbo[f] = s; else dWo[f * d.OD + q] = s; }

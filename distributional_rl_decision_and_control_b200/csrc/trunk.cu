@@ -19,7 +19,6 @@
 namespace asvrl {
 
 constexpr int TR_TPB = 256;
-constexpr int TR_SPB = 2;     // samples per CTA in scale_relu_bwd
 constexpr int TR_RPC = 64;    // rows per CTA in head_bwd
 
 __device__ __forceinline__ float4 f4add(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
@@ -69,13 +68,14 @@ __device__ __forceinline__ bool last_cta(uint32_t* counter) {
 __device__ __forceinline__ void reduce_partials(const float4* part, int n_part, float4* dst, float4* sm, int c,
                                                 int rl, int RL, int D4) {
   float4 s = f4zero();
+#pragma unroll 8
   for (int g = rl; g < n_part; g += RL) s = f4add(s, __ldcg(part + (size_t)g * D4 + c));
   s = lane_sum(s, sm, c, rl, RL, D4);
   if (rl == 0) dst[c] = s;
 }
 
 // ---------------------------------------------------------------------------------------
-// backward of scale_relu.  A CTA owns TR_SPB consecutive samples; D/4 threads span a row, the
+// backward of scale_relu.  A CTA owns `spb` consecutive samples (2); D/4 threads span a row, the
 // 256 / (D/4) row lanes stride over the N quantile rows of a sample.
 //   dpre[m][d]   = dout[m][d] * scale[b][d] * 1[pre + bias > 0]          (nullable)
 //   dscale[b][d] = sum_n dout[m][d] * relu(pre[m][d] + bias[d])          (nullable)
@@ -84,14 +84,14 @@ __device__ __forceinline__ void reduce_partials(const float4* part, int n_part, 
 __global__ void __launch_bounds__(TR_TPB)
 scale_relu_bwd_kernel(const float4* __restrict__ dout, const float4* __restrict__ pre,
                       const float4* __restrict__ bias, const float4* __restrict__ scale, int N, int B,
-                      int D4, float4* __restrict__ dpre, float4* __restrict__ dscale,
+                      int D4, int spb, float4* __restrict__ dpre, float4* __restrict__ dscale,
                       float4* __restrict__ dbias, float4* __restrict__ part, uint32_t* counter) {
   extern __shared__ float4 tr_sm[];
   const int c = threadIdx.x % D4, rl = threadIdx.x / D4, RL = TR_TPB / D4;
   const float4 bi = bias[c];
   float4 db = f4zero();
-  for (int s = 0; s < TR_SPB; ++s) {
-    const int b = blockIdx.x * TR_SPB + s;
+  for (int s = 0; s < spb; ++s) {
+    const int b = blockIdx.x * spb + s;
     if (b >= B) break;  // CTA-uniform
     const float4 sc = scale[b * D4 + c];
     float4 ds = f4zero();
@@ -184,6 +184,7 @@ head_bwd_kernel(const float* __restrict__ dz, const float4* __restrict__ pre, co
   if (last_cta(counter)) {
     float4 sw = f4zero(), sb = f4zero();
     float so = 0.0f;
+#pragma unroll 4
     for (int g = rl; g < (int)gridDim.x; g += RL) {
       sw = f4add(sw, __ldcg(part + (size_t)g * stride + c));
       sb = f4add(sb, __ldcg(part + (size_t)g * stride + D4 + c));
@@ -204,6 +205,11 @@ head_bwd_kernel(const float* __restrict__ dz, const float4* __restrict__ pre, co
 }  // namespace asvrl
 
 using namespace asvrl;
+
+static int scale_relu_spb(int n_tau) {  // samples per CTA.  More rows per CTA (fewer partials) measured
+  (void)n_tau;                           // slower inside the update's graph: per-sample barriers serialise
+  return 2;
+}
 
 static int trunk_dims_ok(const char* what, long rows, int dim) {
   if (rows < 1 || dim < 4 || dim % 4 != 0 || dim / 4 > TR_TPB || TR_TPB % (dim / 4) != 0)
@@ -237,16 +243,17 @@ extern "C" int asvrl_iqn_scale_relu_bwd(const float* dout, const float* pre, con
     return fail(ASVRL_E_BADARG, "asvrl_iqn_scale_relu_bwd: dbias needs partials and counter");
   if (batch < 1 || n_tau < 1) return fail(ASVRL_E_BADARG, "asvrl_iqn_scale_relu_bwd: bad sizes");
   if (int rc = trunk_dims_ok("asvrl_iqn_scale_relu_bwd", (long)batch * n_tau, dim)) return rc;
-  const int grid = (batch + TR_SPB - 1) / TR_SPB;
+  const int spb = scale_relu_spb(n_tau);
+  const int grid = (batch + spb - 1) / spb;
   const size_t smem = (size_t)TR_TPB * sizeof(float4);
   scale_relu_bwd_kernel<<<grid, TR_TPB, smem, (cudaStream_t)stream>>>(
       (const float4*)dout, (const float4*)pre, (const float4*)bias, (const float4*)scale, n_tau, batch, dim / 4,
-      (float4*)dpre, (float4*)dscale, (float4*)dbias, (float4*)partials, counter);
+      spb, (float4*)dpre, (float4*)dscale, (float4*)dbias, (float4*)partials, counter);
   return check_launch("asvrl_iqn_scale_relu_bwd");
 }
 
-extern "C" long asvrl_iqn_scale_relu_bwd_partials(int batch, int dim) {  /* floats */
-  return (long)((batch + TR_SPB - 1) / TR_SPB) * dim;
+extern "C" long asvrl_iqn_scale_relu_bwd_partials(int batch, int dim) {  /* floats: the bound over every n_tau */
+  return (long)((batch + 1) / 2) * dim;
 }
 
 extern "C" int asvrl_iqn_head_fwd(const float* pre, const float* bias, const float* w, const float* b_out,

@@ -43,7 +43,7 @@ class HostPipelinedEnv:
         self.d2h_bytes = self.E * self.RP * self.words * 4
         torch.cuda.synchronize(self.device)
 
-    def enable_cuda_graph(self, is_continuous_action=True):
+    def enable_cuda_graph(self, is_continuous_action=True, zero_copy=False):
         """Capture, per shard and ping-pong phase, ONE graph of [actions H2D from the shard's pinned
         staging buffer, the fused step, results D2H into the shard's pinned block].  A send() is then
         a host memcpy into the staging buffer (none when the caller filled ``action_buffer(g)`` in
@@ -52,7 +52,17 @@ class HostPipelinedEnv:
         RNG counters advance through the env's device word, as in BatchedMarineNavEnv.enable_cuda_graph."""
         dev = self.device
         self._graphs = []
+        self.zero_copy = bool(zero_copy)
         for g, (env, st) in enumerate(zip(self.shards, self.streams)):
+            if zero_copy:
+                # the step kernel stores observations / rewards / status straight into the shard's pinned
+                # host block (device-accessible under unified addressing): the D2H transfer rides on the
+                # kernel's own coalesced row stores and the separate copy — a third of a shard's
+                # H2D -> kernel -> D2H chain — disappears.  The mask stays on the device.
+                ho = self.host_out[g]
+                for op in env._o_ptrs:
+                    op.obs_self, op.obs_objects = ho["obs_self"].data_ptr(), ho["obs_objects"].data_ptr()
+                    op.reward, op.status = ho["reward"].data_ptr(), ho["status"].data_ptr()
             if env.prefetch == "stream":
                 env.prefetch = "workers"  # a captured step refills its stage inside the launch
             torch.cuda.synchronize(dev)
@@ -72,7 +82,8 @@ class HostPipelinedEnv:
                     with torch.cuda.graph(gr, stream=st):
                         self._act_dev[g].copy_(self._act_host[g], non_blocking=True)
                         out = env.step(self._act_dev[g], is_continuous_action)  # flips env._cur
-                        self.host_out[g]["host_block"][:n].copy_(out["host_block"][:n], non_blocking=True)
+                        if not zero_copy:
+                            self.host_out[g]["host_block"][:n].copy_(out["host_block"][:n], non_blocking=True)
                         if i == 1:
                             env.counter_dev.add_(2)
                     graphs[phase] = gr

@@ -193,7 +193,8 @@ def test_host_pipelined_env_matches_plain_shards():
             assert torch.equal(mask, want["obs_mask"].cpu()), (t, g)
 
 
-def test_host_pipelined_env_cuda_graph_matches_plain_shards():
+@pytest.mark.parametrize("zero_copy", [False, True])
+def test_host_pipelined_env_cuda_graph_matches_plain_shards(zero_copy):
     """The captured [H2D, fused step, D2H] graph of every shard returns what BatchedMarineNavEnv.step
     produces on the same actions (the two warm-up steps of the capture are replayed on the plain envs)."""
     from distributional_rl_decision_and_control_b200.envs.marinenav.host_pipeline import HostPipelinedEnv
@@ -205,7 +206,7 @@ def test_host_pipelined_env_cuda_graph_matches_plain_shards():
     for env in plain + h.shards:
         env.state["ep_steps"][::3] = 997
     torch.cuda.synchronize()
-    h.enable_cuda_graph()
+    h.enable_cuda_graph(zero_copy=zero_copy)  # zero_copy: the kernel stores straight into pinned host memory
     zero = torch.zeros((E // G, R, 2), device=DEV)
     for p in plain:  # enable_cuda_graph stepped every shard twice with zero actions
         p.step(zero)

@@ -540,6 +540,10 @@ class Agent():
     def soft_update(self):
         """theta_target = TAU * theta_local + (1 - TAU) * theta_target (AGENT:643-656; TAU = 1.0 in
         the reference, i.e. a hard copy every target_update_interval steps)."""
+        for name in ("optimizer", "actor_optimizer", "critic_optimizer", "critic_1_optimizer", "critic_2_optimizer"):
+            opt = getattr(self, name, None)
+            if hasattr(opt, "check"):
+                opt.check()  # one device read per target sync: K7 skips non-finite steps, say so loudly
         if self.agent_type in ("AC-IQN", "DDPG"):
             pairs = [(self.policy_target.actor, self.policy_local.actor),
                      (self.policy_target.critic, self.policy_local.critic)]

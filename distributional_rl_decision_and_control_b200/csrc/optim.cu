@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(OPT_TPB)
 adam_kernel(const __grid_constant__ AdamList L, float beta1, float beta2, float eps,
             const float* __restrict__ scal) {
   const float gs = scal[0];
+  if (!(gs == gs)) return;  // NaN norm (a peer never arrived, or a non-finite gradient): leave the parameters alone
   for (int c = blockIdx.x; c < L.n_chunks; c += gridDim.x) {
     long long first;
     const int t = chunk_tensor(L, c, first);

@@ -78,6 +78,14 @@ class ClipAdam:
         torch.cuda.synchronize(dev)
         self._peers = peers
 
+    def check(self):
+        """Host-side health check (one device read): the last step's gradient norm must be finite.  A NaN
+        means a non-finite gradient or — on the peer-memory path — a rank that never arrived at the
+        exchange; either way K7 skipped the parameter update of that step."""
+        if not bool(torch.isfinite(self.grad_norm).all()):
+            raise RuntimeError("ClipAdam: non-finite gradient norm (diverged gradients, or a rank missed the "
+                               "gradient exchange: all ranks must step in lock step)")
+
     def zero_grad(self, set_to_none=True):
         for p in self.params:
             if set_to_none:

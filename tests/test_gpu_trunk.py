@@ -217,3 +217,19 @@ def test_fused_iqn_network_matches_module_path(B, N):
     close(z1, z0, "quantiles")
     for n in g0:
         close(g1[n], g0[n], f"grad {n}", rtol=2e-5)
+
+
+def test_clip_adam_skips_non_finite_steps_and_reports_them():
+    from distributional_rl_decision_and_control_b200.utils.clip_adam import ClipAdam
+    p = torch.nn.Parameter(torch.ones(300, device=DEV))
+    opt = ClipAdam([p], lr=1e-2)
+    p.grad = torch.full_like(p, float("nan"))
+    opt.step()
+    torch.cuda.synchronize()
+    assert torch.equal(p.detach(), torch.ones(300, device=DEV))  # untouched
+    with pytest.raises(RuntimeError, match="non-finite"):
+        opt.check()
+    p.grad = torch.ones_like(p)
+    opt.step()
+    opt.check()
+    assert (p.detach() < 1.0).all()

@@ -94,7 +94,7 @@ grad_norm_kernel(const __grid_constant__ AdamList L, float max_norm, float lr, f
   const float norm = sqrtf(total) * grad_scale;
   const float clip = fminf(max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max=1.0)
   if (norm_out) norm_out[0] = norm;
-  scal[0] = clip * grad_scale;
+  scal[0] = norm <= 3.0e38f ? clip * grad_scale : __int_as_float(0x7fc00000);  // fminf drops a NaN: keep it
   *counter = 0u;
 }
 
@@ -250,7 +250,7 @@ grad_norm_p2p_kernel(const __grid_constant__ AdamList L, const __grid_constant__
   const float norm = sqrtf(total) * grad_scale;
   const float clip = fminf(max_norm / (norm + 1e-6f), 1.0f);
   if (norm_out) norm_out[0] = norm;
-  scal[0] = clip * grad_scale;
+  scal[0] = norm <= 3.0e38f ? clip * grad_scale : __int_as_float(0x7fc00000);  // fminf drops a NaN: keep it
   *epoch_dev = e;  // every CTA has read the old value (they all arrived at the counter)
   *counter = 0u;
 }

@@ -59,6 +59,8 @@ _SIGNATURES = {
     "asvrl_tower_fwd": (C.c_int, [f32p] * 7 + [C.c_int] * 6 + [f32p, vp]),
     "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
     "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
+    "asvrl_actor_head": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, f32p, C.c_float, C.POINTER(C.c_float * 2),
+                                   C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_int, C.c_int, f32p, vp]),
     "asvrl_clip_adam_step_p2p": (C.c_int, [C.POINTER(_abi.AdamTensors), C.POINTER(_abi.PeerBuckets), f32p, u32p]
                                  + [C.c_float] * 5 + [f32p, f32p, u32p, vp]),
     "asvrl_clip_adam_step": (C.c_int, [C.POINTER(_abi.AdamTensors)] + [C.c_float] * 6 + [f32p, f32p, u32p, vp]),
@@ -380,6 +382,20 @@ def iqn_head_bwd(dz, pre, bias, w, want_params=True):
                                   ptr(part), ptr(cnt), stream_ptr())
     check(rc, "asvrl_iqn_head_bwd")
     return dpre, dw, dbias, dbo
+
+
+def actor_head(pre, bias, w, b_out, atan_scale, eps, lo, hi, seed, counter, counter_dev=None):
+    """-> (rows, 2) epsilon-greedy actions; ``eps`` a float or a 0-d CUDA tensor."""
+    M, D = pre.shape
+    actions = torch.empty((M, 2), dtype=torch.float32, device=pre.device)
+    eps_dev, eps_f = (eps, 0.0) if isinstance(eps, torch.Tensor) else (None, float(eps))
+    f = torch.float32
+    rc = lib().asvrl_actor_head(ptr(pre, f), ptr(bias, f), ptr(w, f), ptr(b_out, f), float(atan_scale),
+                                ptr(eps_dev, f), eps_f, C.byref((C.c_float * 2)(*lo)), C.byref((C.c_float * 2)(*hi)),
+                                int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), ptr(counter_dev, torch.int64), M, D,
+                                ptr(actions), stream_ptr())
+    check(rc, "asvrl_actor_head")
+    return actions
 
 
 # ------------------------------------------------------------------ K6: observation tower

@@ -14,7 +14,7 @@ int check_launch(const char* what);
 
 // ---- Philox4x32-10 (Salmon et al., SC'11).  The stream layout is part of the ABI contract
 // (documented in include/asvrl.h) and is restated independently by the CPU oracle. ----
-enum : uint32_t { STREAM_SENSOR = 1, STREAM_RESET = 2, STREAM_TAU = 3, STREAM_REPLAY = 4 };
+enum : uint32_t { STREAM_SENSOR = 1, STREAM_RESET = 2, STREAM_TAU = 3, STREAM_REPLAY = 4, STREAM_EXPLORE = 5 };
 
 __host__ __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) {
 #ifdef __CUDA_ARCH__

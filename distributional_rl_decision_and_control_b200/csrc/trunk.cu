@@ -285,3 +285,64 @@ extern "C" int asvrl_iqn_head_bwd(const float* dz, const float* pre, const float
 extern "C" long asvrl_iqn_head_bwd_partials(int rows, int dim) {  /* floats */
   return (long)((rows + TR_RPC - 1) / TR_RPC) * (2 * (dim / 4) + 1) * 4;
 }
+
+// ---------------------------------------------------------------------------------------
+// Actor head of the collection path (no gradient): from the pre-activation of the last hidden
+// layer to the epsilon-greedy action in one pass (ACIQN:318-321 + AGENT:207-225 for every ASV):
+//   a_greedy[m][j] = atan_scale * atan(sum_d relu(pre[m][d] + bias[d]) * w[j][d] + b_out[j]),  j < 2
+//   with probability eps (Philox stream 5 keyed on seed, counter, row): a = lo + (hi - lo) * u
+// One warp per row; replaces the ReLU pass, the 128 -> 2 GEMM, atan, scale, two rand, compare,
+// where and the range arithmetic (about 10 launches and two 33 MB round trips at 65 536 ASVs).
+// ---------------------------------------------------------------------------------------
+namespace asvrl {
+
+__global__ void __launch_bounds__(TR_TPB)
+actor_head_kernel(const float4* __restrict__ pre, const float4* __restrict__ bias, const float4* __restrict__ w,
+                  const float* __restrict__ b_out, float atan_scale, const float* __restrict__ eps_dev, float eps,
+                  float lo0, float hi0, float lo1, float hi1, uint64_t seed, uint64_t counter,
+                  const uint64_t* __restrict__ counter_dev, int M, int D4, float2* __restrict__ actions) {
+  if (counter_dev) counter += *counter_dev;
+  if (eps_dev) eps = *eps_dev;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * TR_TPB) >> 5;
+  const float bo0 = b_out[0], bo1 = b_out[1];
+  for (int m = (blockIdx.x * TR_TPB + threadIdx.x) >> 5; m < M; m += warps) {
+    float a0 = 0.0f, a1 = 0.0f;
+    for (int c = lane; c < D4; c += 32) {
+      const float4 r = f4relu(f4add(pre[(size_t)m * D4 + c], bias[c]));
+      const float4 w0 = w[c], w1 = w[D4 + c];
+      a0 += (r.x * w0.x + r.y * w0.y) + (r.z * w0.z + r.w * w0.w);
+      a1 += (r.x * w1.x + r.y * w1.y) + (r.z * w1.z + r.w * w1.w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+      a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+    }
+    if (lane == 0) {
+      float2 act = make_float2(atan_scale * atanf(a0 + bo0), atan_scale * atanf(a1 + bo1));
+      if (eps > 0.0f) {
+        const uint4 u = philox_at(seed, STREAM_EXPLORE, counter, (int64_t)m, 0u, 0u, 0u);
+        if (u01(u.x) < eps) act = make_float2(lo0 + (hi0 - lo0) * u01(u.y), lo1 + (hi1 - lo1) * u01(u.z));
+      }
+      actions[m] = act;
+    }
+  }
+}
+
+}  // namespace asvrl
+
+extern "C" int asvrl_actor_head(const float* pre, const float* bias, const float* w, const float* b_out,
+                                float atan_scale, const float* eps_dev, float eps, const float* action_lo,
+                                const float* action_hi, uint64_t seed, uint64_t counter,
+                                const uint64_t* counter_dev, int rows, int dim, float* actions, void* stream) {
+  if (!pre || !bias || !w || !b_out || !action_lo || !action_hi || !actions)
+    return fail(ASVRL_E_BADARG, "asvrl_actor_head: null pointer");
+  if (int rc = trunk_dims_ok("asvrl_actor_head", rows, dim)) return rc;
+  long grid = ((long)rows * 32 + TR_TPB - 1) / TR_TPB;
+  if (grid > 148 * 8) grid = 148 * 8;
+  asvrl::actor_head_kernel<<<(int)grid, TR_TPB, 0, (cudaStream_t)stream>>>(
+      (const float4*)pre, (const float4*)bias, (const float4*)w, b_out, atan_scale, eps_dev, eps, action_lo[0],
+      action_hi[0], action_lo[1], action_hi[1], seed, counter, counter_dev, rows, dim / 4, (float2*)actions);
+  return check_launch("asvrl_actor_head");
+}

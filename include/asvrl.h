@@ -470,6 +470,18 @@ ASVRL_API int asvrl_clip_adam_step_p2p(const asvrl_adam_tensors* tensors, const 
                                        float beta1, float beta2, float eps, float* norm_out /* nullable */,
                                        float* scratch, uint32_t* counter, void* stream);
 
+/* Collection path (no gradient), AC-IQN actor: from the pre-activation of the last hidden layer to the
+ * epsilon-greedy action of every ASV in one pass (ACIQN:318-321, AGENT:207-225):
+ *   a[m][j] = atan_scale * atan(sum_d relu(pre[m][d] + bias[d]) w[j][d] + b_out[j]),  j < 2; with
+ *   probability eps (eps_dev, a device float, overrides eps when not NULL) a = lo + (hi - lo) u,
+ *   u from Philox stream 5 keyed on (seed, counter [+ *counter_dev], row).
+ * pre [rows][dim], w [2][dim], action_lo / action_hi: HOST float[2]; actions [rows][2]. */
+ASVRL_API int asvrl_actor_head(const float* pre, const float* bias, const float* w, const float* b_out,
+                               float atan_scale, const float* eps_dev /* nullable */, float eps,
+                               const float* action_lo, const float* action_hi, uint64_t seed,
+                               uint64_t counter, const uint64_t* counter_dev /* nullable */, int rows,
+                               int dim, float* actions, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -233,3 +233,23 @@ def test_clip_adam_skips_non_finite_steps_and_reports_them():
     opt.step()
     opt.check()
     assert (p.detach() < 1.0).all()
+
+
+def test_actor_head_eps_greedy_matches_actor_forward():
+    """The collection path's fused forward: eps = 0 reproduces Actor.forward; eps = 0.3 explores about
+    30 % of the rows uniformly in range, leaves the others greedy, and draws fresh noise per call."""
+    ag = Agent(device=DEV, seed=100, agent_type="AC-IQN", BATCH_SIZE=64, num_tau=8, BUFFER_SIZE=256)
+    B = 20000
+    x, _ = _critic_inputs(B, 77)
+    greedy = ag.policy_local.actor(x)
+    a0 = ag.act_batch(x, eps=0.0)
+    close(a0, greedy, "greedy actions", rtol=2e-6)
+    a1 = ag.act_batch(x, eps=torch.tensor(0.3, device=DEV))
+    a2 = ag.act_batch(x, eps=0.3)
+    explored = (a1 - greedy).abs().max(dim=1).values > 1e-5
+    frac = explored.float().mean().item()
+    assert 0.28 < frac < 0.32, frac
+    rnd = a1[explored]
+    assert rnd.min().item() >= -1.0 and rnd.max().item() <= 1.0
+    assert abs(rnd.mean().item()) < 0.02 and abs(rnd.var().item() - 1.0 / 3.0) < 0.02  # U(-1, 1)
+    assert not torch.equal(a1, a2)  # the device counter advanced

@@ -175,7 +175,8 @@ typedef struct asvrl_env_out {
  * restated by the oracle so that streams are reproducible and invariant to the GPU count:
  *   key = (seed lo, seed hi)
  *   ctr = (block | slot<<8 | ego<<16,  global env index,  step lo,  step hi (24 bit) | stream<<24)
- *   stream: 1 sensor noise, 2 reset, 3 tau, 4 replay sampling
+ *   stream: 1 sensor noise, 2 reset, 3 tau, 4 replay sampling, 5 exploration (asvrl_actor_head: the
+ *           "env" word is the row index; words 0..2 = explore?, action 0, action 1)
  *   uniform(word) = ((word >> 8) + 0.5) * 2^-24
  * Sensor noise of (env, ego, slot, step): block 0 -> two Box-Muller pairs (n_px,n_py)*pos_std,
  * (n_vx,n_vy)*vel_std; blocks 1..8 -> Best-Fisher von Mises attempts, two per block

@@ -138,8 +138,10 @@ struct Smem {
   unsigned* rs_okm;
 };
 
-static SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fused = false) {
-  SmemLayout L;
+// constexpr: the shape-specialised kernel instantiation evaluates it at compile time, so every
+// shared-memory offset becomes an immediate
+static constexpr SmemLayout make_layout(int EPB, int RP, int OP, int CP, int tpb, bool fused = false) {
+  SmemLayout L{};
   const uint32_t A = (uint32_t)EPB * RP, S = OP + RP, SK = S | 1;
   uint32_t off = 0;
   auto take = [&](uint32_t n, uint32_t elem) { uint32_t o = off; off += (n * elem + 15u) & ~15u; return o; };
@@ -366,20 +368,31 @@ __device__ __forceinline__ void take_stage_batched(const ResetState& st, const F
 }
 
 
-template <bool INJECT, bool FUSED>
+// SHAPE = 1 is the instantiation for BASELINE config 2 (8 ASVs x 10 buoys x 8 vortex cores, 4 envs per
+// CTA): the table sizes and the shared-memory layout are compile-time constants, which folds the
+// per-use `base + offset` arithmetic of the 45 shared arrays (7.6 % of the generic kernel's
+// instructions, profiles/r01_k1_v12_source.txt), the index divisions and the short loops' bounds.
+// SHAPE = 0 takes every size at run time.  Same code, same results.
+constexpr int C2_RP = 8, C2_OP = 10, C2_CP = 8, C2_EPB = 4;
+
+template <bool INJECT, bool FUSED, int SHAPE = 0>
 __global__ void __launch_bounds__(TPB, 7)
-env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L,
+env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L_,
                 StatePtrs st, const void* __restrict__ actions,
                 const float* __restrict__ noise, const uint8_t* __restrict__ env_mask, uint64_t seed,
-                uint64_t step, OutPtrs out, int E, int RP, int OP, int CP, int64_t env_offset,
-                uint32_t mode, int EPB, const uint64_t* __restrict__ counter_dev,
+                uint64_t step, OutPtrs out, int E, int RP_, int OP_, int CP_, int64_t env_offset,
+                uint32_t mode, int EPB_, const uint64_t* __restrict__ counter_dev,
                 const __grid_constant__ FusedArgs fa) {
   extern __shared__ __align__(16) char smem_raw[];
+  constexpr bool SP = SHAPE == 1;
+  const int RP = SP ? C2_RP : RP_, OP = SP ? C2_OP : OP_, CP = SP ? C2_CP : CP_, EPB = SP ? C2_EPB : EPB_;
   if (FUSED && (int)blockIdx.x < fa.n_workers) {
     refill_worker(fa, smem_raw, seed, E, RP, OP, CP, env_offset);
     return;
   }
-  const Smem m = carve(smem_raw, L);
+  constexpr SmemLayout LS = make_layout(C2_EPB, C2_RP, C2_OP, C2_CP, TPB, FUSED);
+  const Smem m = SP ? carve(smem_raw, LS) : carve(smem_raw, L_);
+  const int step3_a = SP ? LS.step3_a : L_.step3_a, step3_sl = SP ? LS.step3_sl : L_.step3_sl;
   const int tid = threadIdx.x;
   const int A = EPB * RP, S = OP + RP, SK = S | 1, NP = A * S;
   const int e0 = ((int)blockIdx.x - (FUSED ? fa.n_workers : 0)) * EPB;
@@ -490,7 +503,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
   // Warps 1..3 run it while warp 0 is already integrating (phase A), then meet on barrier 2 and
   // signal warp 0 through barrier 1 (96 arrivals + warp 0's sync).
   if (tid >= 32) {
-  for (PairIt it(tid - 32, S); it.p - (tid & 31) < NP; it.advance(TPB - 32, L.step3_a, L.step3_sl, S)) {
+  for (PairIt it(tid - 32, S); it.p - (tid & 31) < NP; it.advance(TPB - 32, step3_a, step3_sl, S)) {
     bool keep = false;
     const int a = it.a, sl = it.sl;
     if (it.p < NP && !(m.fl0[a] & ASVRL_F_DEACTIVATED)) {
@@ -1038,7 +1051,8 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
   const size_t smem = L.bytes;
   const int grid = (n_envs + EPB - 1) / EPB;
   cudaStream_t s = (cudaStream_t)stream;
-  auto kern = noise ? env_step_kernel<true, false> : env_step_kernel<false, false>;
+  const bool c2 = max_robots == C2_RP && max_obs == C2_OP && max_cores == C2_CP && EPB == C2_EPB;
+  auto kern = noise ? env_step_kernel<true, false> : (c2 ? env_step_kernel<false, false, 1> : env_step_kernel<false, false>);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
@@ -1120,7 +1134,8 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
   const SmemLayout L = make_layout(EPB, max_robots, max_obs, max_cores, TPB, true);
   const size_t smem = L.bytes;
   const int n_step = (n_envs + EPB - 1) / EPB;
-  auto kern = env_step_kernel<false, true>;
+  const bool c2 = max_robots == C2_RP && max_obs == C2_OP && max_cores == C2_CP && EPB == C2_EPB;
+  auto kern = c2 ? env_step_kernel<false, true, 1> : env_step_kernel<false, true>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step_autoreset: %zu B shared memory: %s", smem, cudaGetErrorString(e));

@@ -485,7 +485,7 @@ def run_b200(args):
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": k1_traffic(E, C, env.fused), "peak_source": which,
-                         "kernel": "env_step_kernel<false,true> (fused auto-reset)" if env.fused
+                         "kernel": "env_step_kernel<false,true,1> (fused auto-reset, config-2 shape instantiation)" if env.fused
                                    else "env_step_kernel<false,false>", "kernel_ms": k1_ms,
                          "algorithmic_bytes_per_launch": per_launch,
                          "note": "instruction-issue bound by design (SURVEY.md F5); see profiles/"},

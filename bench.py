@@ -116,14 +116,14 @@ def grad_sync_kind(agent, world):
     return "nccl all-reduce of the flat bucket, before clipping"
 
 
-def k1_traffic(E, C, fused):
+def k1_traffic(E, C, fused, key=None):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
     `ncu --set full` capture of this same command (profiles/k1_traffic.json); None for another shape."""
     try:
         with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "k1_traffic.json")) as f:
             d = json.load(f)
         if d["envs"] == E and d["cores"] == C and bool(d["fused"]) == bool(fused):
-            return d["dram_bytes_read"] + d["dram_bytes_write"]
+            return d[key] if key else d["dram_bytes_read"] + d["dram_bytes_write"]
     except Exception:
         pass
     return None
@@ -187,7 +187,7 @@ def time_kernel(fn, K, W, per_graph=20):
     return e0.elapsed_time(e1) / (reps * per_graph)
 
 
-def training_leg(args, precision, dev, pg, rank, world, barrier, dist):
+def training_leg(args, precision, dev, pg, rank, world, barrier, dist, kind="AC-IQN", n_steps=400):
     """BASELINE config 4, per-GPU share: collection policy forward for every ASV (act_batch), the fused
     step, K2a push, and one AC-IQN update (B=1024, N=32) per `update_every` batched steps, all as CUDA
     graphs; the only collective is the gradient all-reduce.  Device-timed, max over ranks."""
@@ -196,13 +196,15 @@ def training_leg(args, precision, dev, pg, rank, world, barrier, dist):
     from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
     from distributional_rl_decision_and_control_b200.vector_trainer import VectorTrainer
     ET = args.train_envs
-    agent = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=1024, num_tau=32, BUFFER_SIZE=1 << 20,
-                  process_group=pg, rank=rank, matmul_precision=precision)
+    rainbow = kind == "Rainbow"  # its n-step prioritised memory keeps the ring position on the host: eager
+    agent = Agent(device=dev, seed=100, agent_type=kind, BATCH_SIZE=1024, num_tau=32, BUFFER_SIZE=1 << 20,
+                  process_group=pg, rank=rank, matmul_precision=precision,
+                  replay_lanes=ET * R if rainbow else 1)
     env = BatchedMarineNavEnv(ET, R, O, args.cores, device=dev, seed=args.seed + 11, env_offset=rank * ET,
-                              fused=True, prefetch="workers")
-    vt = VectorTrainer(env, agent, update_every=args.update_every, learning_starts=8, cuda_graph=True)
+                              fused=not rainbow, prefetch="workers")
+    vt = VectorTrainer(env, agent, update_every=args.update_every, learning_starts=8, cuda_graph=not rainbow)
     vt.learn(40)  # reset, fill the ring, capture both graphs
-    n_steps = 400
+    update = agent.train_graph_replay if agent._graph is not None else getattr(agent, agent._TRAINERS[kind])
     t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     steps0, upd0 = vt.steps, vt.updates
     barrier()
@@ -212,7 +214,7 @@ def training_leg(args, precision, dev, pg, rank, world, barrier, dist):
         since += vt.collect(0.05)
         if since >= vt.update_every:
             since = 0
-            agent.train_graph_replay()
+            update()
             vt.updates += 1
     t1e.record()
     barrier()
@@ -224,8 +226,10 @@ def training_leg(args, precision, dev, pg, rank, world, barrier, dist):
             "updates_per_sec": (vt.updates - upd0) / tsec, "envs_per_gpu": ET,
             "batched_steps": vt.steps - steps0, "update_every_batched_steps": vt.update_every,
             "batch_per_gpu": 1024, "n_tau": 32, "gemm": precision,
-            "what": "act_batch (policy forward for envs x 8 ASVs, eps-greedy) + fused step + replay push per "
-                    "batched step, one AC-IQN update per update_every steps; CUDA graphs"}
+            "mode": "eager (host-side ring position)" if rainbow else "graph",
+            "what": "act_batch (policy forward for envs x 8 ASVs, eps-greedy) + %s + replay push per "
+                    "batched step, one %s update per update_every steps%s"
+                    % ("step + reset" if rainbow else "fused step", kind, "" if rainbow else "; CUDA graphs")}
 
 
 def run_b200(args):
@@ -447,6 +451,17 @@ def run_b200(args):
                 training[prec] = training_leg(args, prec, dev, pg, rank, world, barrier, dist)
             except Exception as e:  # the headline legs above must not be lost to this one
                 training[prec] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    # ---- (6) BASELINE config 5: the same loop for the other five agents of the reference, one after
+    # the other (fp32, one GPU; a leg that fails is reported, not fatal)
+    agents = None
+    if not args.profile and world == 1 and not args.no_agents:
+        agents = {}
+        for kind in ("IQN", "DDPG", "DQN", "SAC", "Rainbow"):
+            try:
+                agents[kind] = training_leg(args, "fp32", dev, pg, rank, world, barrier, dist, kind=kind, n_steps=200)
+            except Exception as e:
+                agents[kind] = {"error": f"{type(e).__name__}: {e}"[:300]}
+            torch.cuda.empty_cache()
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -456,6 +471,16 @@ def run_b200(args):
     step_ms, k1_ms, e2e_ms = (float(x) for x in times.tolist())
 
     if rank == 0:
+        # issue-rate roof of the dominant kernel (it is issue bound, not HBM bound): warp instructions
+        # of one launch (ncu, profiles/k1_traffic.json) / (SMs x 4 schedulers x SM clock)
+        clk = sampler.summary()
+        winst = k1_traffic(E, C, env.fused, key="warp_instructions")
+        issue = None
+        if winst and clk.get("sm_mhz"):
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            floor_ms = winst / (sms * 4 * clk["sm_mhz"] * 1e6) * 1e3
+            issue = {"warp_instructions": winst, "issue_slots_per_s": sms * 4 * clk["sm_mhz"] * 1e6,
+                     "floor_ms": floor_ms, "frac": floor_ms / k1_ms}
         per_launch = alg_bytes_per_env_step(R, O, C) * E
         achieved = per_launch / (k1_ms * 1e-3) / 1e9
         line = {
@@ -488,8 +513,10 @@ def run_b200(args):
                          "kernel": "env_step_kernel<false,true,1> (fused auto-reset, config-2 shape instantiation)" if env.fused
                                    else "env_step_kernel<false,false>", "kernel_ms": k1_ms,
                          "algorithmic_bytes_per_launch": per_launch,
-                         "note": "instruction-issue bound by design (SURVEY.md F5); see profiles/"},
-            "learner": learner, "training": training,
+                         "issue": issue,
+                         "note": "instruction-issue bound by design (SURVEY.md F5): `issue.frac` = share of the "
+                                 "launch's issue slots that carry an instruction; see profiles/"},
+            "learner": learner, "training": training, "agents_c5": agents,
             "clocks": sampler.summary(), "finite": finite,
         }
         if world == 1 and not args.no_cpu:
@@ -551,6 +578,7 @@ def main():
     ap.add_argument("--unfused", action="store_true", help="three launches per step (K1, K1b, masked K1)")
     ap.add_argument("--train-envs", type=int, default=8192, help="envs per GPU of the training leg (config 4: 65536 / 8)")
     ap.add_argument("--update-every", type=int, default=4, help="batched steps per learner update in the training leg")
+    ap.add_argument("--no-agents", action="store_true", help="skip the config-5 leg (the other five agents)")
     ap.add_argument("--e2e-groups", type=int, default=4, help="shards of the host pipeline (send / recv)")
     ap.add_argument("--e2e-zero-copy", action="store_true",
                     help="the step kernel stores its results straight into pinned host memory (no D2H copy node)")

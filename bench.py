@@ -15,6 +15,7 @@ episodes are re-generated (K1b's routine) and re-observed, all in ONE launch
            / K1's own average launch duration, against MEASURED_PEAKS.json's hbm_gbs;
   cpu_baseline = the float64 C port of the reference (oracle/, pinned against the Python
            reference by tests/golden) on the box's host threads, bounded sample.
+           cpu_baseline.learner = the plain-torch restatement of the AC-IQN update on the host.
 `--impl reference` times that CPU port alone (the Python reference cannot travel to the GPU
 box; DESIGN.md records its speed measured in the build container).
 """
@@ -81,6 +82,19 @@ def host_threads():
         return len(os.sched_getaffinity(0))
     except Exception:
         return os.cpu_count() or 1
+
+
+def cpu_learner_baseline(seconds=3.0):
+    """updates/s of the plain-torch restatement of AGENT:386-432 (oracle/learner_oracle.py, pinned to the
+    reference's own train step by tests/test_oracle_golden.py) on torch's host threads, at BASELINE
+    config 3 and at the reference's own B=64 / N=8.  A bounded sample of `seconds` per shape."""
+    import torch
+    from oracle import learner_oracle as lo
+    out = {"kind": "port", "cores": torch.get_num_threads(), "dtype": "f32"}
+    for name, (B, N) in (("c3_B1024_N32", (1024, 32)), ("ref_B64_N8", (64, 8))):
+        ups, n, dt = lo.time_updates(B, N, seconds)
+        out[name] = {"updates_per_sec": ups, "sample": f"{n} updates in {dt:.1f} s"}
+    return out
 
 
 def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0):
@@ -524,7 +538,8 @@ def run_b200(args):
             v, dt = cpu_port_throughput(args.cpu_envs, args.cpu_steps, cores, C)
             line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
                                     "sample": f"{args.cpu_envs} envs x {args.cpu_steps} steps of the same shape, "
-                                              f"float64 C port of the reference, {dt:.1f} s"}
+                                              f"float64 C port of the reference, {dt:.1f} s",
+                                    "learner": cpu_learner_baseline()}
         print(json.dumps(line), flush=True)
     if world > 1:
         # captured graphs hold NCCL work: tearing the communicator down under them can hang, so
@@ -553,7 +568,8 @@ def run_reference(args):
             "config": {"workload": f"C2 batched env-step shape: {R} ASVs x {O} buoys x {args.cores} vortex cores; "
                                    f"each step a bounded sample of {n} envs"},
             "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                             "sample": f"{n} envs x {K} steps, float64 C port of the reference"},
+                             "sample": f"{n} envs x {K} steps, float64 C port of the reference",
+                             "learner": cpu_learner_baseline()},
             "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 

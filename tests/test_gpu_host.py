@@ -61,6 +61,38 @@ def test_train_step_matches_reference(fx):
             assert np.abs(got - want).max() <= 2.1e-4, (name, k)  # at most one flipped Adam sign
 
 
+@pytest.mark.parametrize("fused", [True, False])
+def test_train_steps_at_config3_match_float64_restatement(fused):
+    """BASELINE config 3 (B=1024, N=N'=32), three consecutive updates from random weights, batches and
+    tau tables: the product update (K3, K4, K5, K6, K7 + the GEMMs) against the float64 restatement of
+    AGENT:386-432 (oracle/learner_oracle.py, pinned to the reference by tests/test_oracle_golden.py)."""
+    from oracle import learner_oracle as lo
+    B, N = 1024, 32
+    agent = Agent(device=DEV, seed=3, agent_type="AC-IQN", BATCH_SIZE=B, num_tau=N, BUFFER_SIZE=2048,
+                  fused_trunk=fused, fused_optimizer=fused)
+    actor32, critic32 = lo.init_weights(41)
+    for pol in (agent.policy_local, agent.policy_target):
+        pol.actor.load_state_dict({k: v.to(DEV) for k, v in actor32.items()})
+        pol.critic.load_state_dict({k: v.to(DEV) for k, v in critic32.items()})
+    actor, critic = ({k: v.double() for k, v in actor32.items()}, {k: v.double() for k, v in critic32.items()})
+    ta, tc = {k: v.clone() for k, v in actor.items()}, {k: v.clone() for k, v in critic.items()}
+    oa, oc = lo.new_adam_state(actor), lo.new_adam_state(critic)
+    for step in range(3):
+        b32, t32 = lo.synthetic_batch(B, N, 100 + step)
+        want = lo.train_ac_iqn(actor, critic, ta, tc, {k: v.double() for k, v in b32.items()},
+                               {k: v.double() for k, v in t32.items()}, oa, oc)
+        got = agent.train_AC_IQN(batch={k: v.to(DEV) for k, v in b32.items()},
+                                 taus={k: v.to(DEV) for k, v in t32.items()})
+        for g, w in zip(got, want):  # float32 product against float64 restatement
+            assert abs(g.item() - w) <= 2e-5 * abs(w) + 2e-6, (step, g.item(), w)
+        for name, mod, ref in (("actor", agent.policy_local.actor, actor), ("critic", agent.policy_local.critic, critic)):
+            for k, v in mod.state_dict().items():
+                err = (v.double().cpu() - ref[k]).abs().numpy()
+                # Adam steps are +-lr-sized and sign-unstable where |g| ~ eps: nearly all elements agree
+                # closely, none is off by more than one flipped step per update
+                assert np.mean(err <= 5e-6) >= 0.99 and err.max() <= 2.1e-4 * (step + 1), (step, name, k, err.max())
+
+
 def test_agent_train_from_device_replay_and_graph():
     agent = Agent(device=DEV, seed=1, agent_type="AC-IQN", BUFFER_SIZE=4096)
     rng = np.random.RandomState(0)

@@ -23,6 +23,7 @@
 // The kernel is instruction-issue bound (about 1e4 thread instructions per 280 algorithmic
 // bytes); HBM traffic is one pass over state in, state + observations out.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "env_consts.cuh"
@@ -373,7 +374,16 @@ __device__ __forceinline__ void take_stage_batched(const ResetState& st, const F
 // per-use `base + offset` arithmetic of the 45 shared arrays (7.6 % of the generic kernel's
 // instructions, profiles/r01_k1_v12_source.txt), the index divisions and the short loops' bounds.
 // SHAPE = 0 takes every size at run time.  Same code, same results.
-constexpr int C2_RP = 8, C2_OP = 10, C2_CP = 8, C2_EPB = 4;
+// SHAPE = 1: 8 vortex cores; SHAPE = 2: none (the reference's shipped curricula have num_cores = 0).
+constexpr int C2_RP = 8, C2_OP = 10, C2_EPB = 4;
+constexpr int shape_cores(int shape) { return shape == 2 ? 0 : 8; }
+
+// 0 = generic instantiation; ASVRL_K1_GENERIC=1 in the environment forces it (A/B timing, tests).
+static int pick_shape(int max_robots, int max_obs, int max_cores, int EPB) {
+  static const bool generic = [] { const char* v = getenv("ASVRL_K1_GENERIC"); return v && v[0] == '1'; }();
+  if (generic || max_robots != C2_RP || max_obs != C2_OP || EPB != C2_EPB) return 0;
+  return max_cores == shape_cores(1) ? 1 : (max_cores == shape_cores(2) ? 2 : 0);
+}
 
 template <bool INJECT, bool FUSED, int SHAPE = 0>
 __global__ void __launch_bounds__(TPB, 7)
@@ -384,7 +394,8 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
                 uint32_t mode, int EPB_, const uint64_t* __restrict__ counter_dev,
                 const __grid_constant__ FusedArgs fa) {
   extern __shared__ __align__(16) char smem_raw[];
-  constexpr bool SP = SHAPE == 1;
+  constexpr bool SP = SHAPE != 0;
+  constexpr int C2_CP = shape_cores(SHAPE);
   const int RP = SP ? C2_RP : RP_, OP = SP ? C2_OP : OP_, CP = SP ? C2_CP : CP_, EPB = SP ? C2_EPB : EPB_;
   if (FUSED && (int)blockIdx.x < fa.n_workers) {
     refill_worker(fa, smem_raw, seed, E, RP, OP, CP, env_offset);
@@ -1051,8 +1062,10 @@ extern "C" int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_st
   const size_t smem = L.bytes;
   const int grid = (n_envs + EPB - 1) / EPB;
   cudaStream_t s = (cudaStream_t)stream;
-  const bool c2 = max_robots == C2_RP && max_obs == C2_OP && max_cores == C2_CP && EPB == C2_EPB;
-  auto kern = noise ? env_step_kernel<true, false> : (c2 ? env_step_kernel<false, false, 1> : env_step_kernel<false, false>);
+  const int shape = pick_shape(max_robots, max_obs, max_cores, EPB);
+  auto kern = noise ? env_step_kernel<true, false>
+                    : (shape == 1 ? env_step_kernel<false, false, 1>
+                                  : (shape == 2 ? env_step_kernel<false, false, 2> : env_step_kernel<false, false>));
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step: %zu B shared memory: %s", smem, cudaGetErrorString(e));
@@ -1134,8 +1147,9 @@ extern "C" int asvrl_env_step_autoreset(const asvrl_env_params* params, const as
   const SmemLayout L = make_layout(EPB, max_robots, max_obs, max_cores, TPB, true);
   const size_t smem = L.bytes;
   const int n_step = (n_envs + EPB - 1) / EPB;
-  const bool c2 = max_robots == C2_RP && max_obs == C2_OP && max_cores == C2_CP && EPB == C2_EPB;
-  auto kern = c2 ? env_step_kernel<false, true, 1> : env_step_kernel<false, true>;
+  const int shape = pick_shape(max_robots, max_obs, max_cores, EPB);
+  auto kern = shape == 1 ? env_step_kernel<false, true, 1>
+                         : (shape == 2 ? env_step_kernel<false, true, 2> : env_step_kernel<false, true>);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return fail((int)e, "asvrl_env_step_autoreset: %zu B shared memory: %s", smem, cudaGetErrorString(e));

@@ -201,7 +201,10 @@ ASVRL_API void asvrl_env_default_params(asvrl_env_params* p);
  *   counter_dev nullable DEVICE uint64: the RNG step used is `step + *counter_dev`.  Lets a
  *             captured CUDA graph be replayed with fresh random streams (the host bumps the
  *             device word inside the graph); the same convention holds for asvrl_env_reset
- *             (episode), asvrl_replay_sample (counter) and asvrl_iqn_tau_cos (counter). */
+ *             (episode), asvrl_replay_sample (counter) and asvrl_iqn_tau_cos (counter).
+ * Table sizes max_robots = 8, max_obs = 10, max_cores = 8 or 0 (BASELINE config 2) run a
+ * kernel instantiation with those sizes as compile-time constants; results are bit-identical to
+ * the run-time-sized one, which ASVRL_K1_GENERIC=1 in the process environment (read once) forces. */
 ASVRL_API int asvrl_env_step(const asvrl_env_params* params, const asvrl_env_state* state,
                              const void* actions, const float* noise, const uint8_t* env_mask,
                              uint64_t seed, uint64_t step, const asvrl_env_out* out, int n_envs,

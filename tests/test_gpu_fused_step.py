@@ -226,3 +226,43 @@ def test_host_pipelined_env_cuda_graph_matches_plain_shards(zero_copy):
             torch.cuda.synchronize()
             for k in ("obs_self", "obs_objects", "reward", "status"):
                 assert torch.equal(got[k], want[k].cpu()), (t, g, k)
+
+
+_SHAPE_PROBE = r"""
+import hashlib, sys, torch
+sys.path.insert(0, sys.argv[1])
+from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
+C = int(sys.argv[2])
+env = BatchedMarineNavEnv(64, 8, 10, C, device="cuda:0", seed=77, fused=True, prefetch="workers")
+env.reset()
+env.state["ep_steps"].copy_(1000 - (torch.arange(64, device="cuda:0", dtype=torch.int32) % 7))
+g = torch.Generator(device="cuda:0").manual_seed(5)
+h = hashlib.sha256()
+for i in range(12):
+    out = env.step_fused(torch.rand((64, 8, 2), device="cuda:0", generator=g) * 2 - 1)
+    for k in ("obs_self", "obs_objects", "obs_mask", "reward", "status", "ended"):
+        h.update(out[k].cpu().numpy().tobytes())
+for k in sorted(env.state):
+    if torch.is_tensor(env.state[k]):
+        h.update(env.state[k].cpu().numpy().tobytes())
+print("HASH", h.hexdigest())
+"""
+
+
+@pytest.mark.parametrize("cores", [8, 0])
+def test_shape_specialised_kernel_equals_generic(cores):
+    """env_step_kernel<.., SHAPE> for the BASELINE config-2 table sizes (8 ASVs, 10 buoys, 8 or 0 vortex
+    cores) is the same arithmetic as the run-time-sized instantiation: 12 fused steps with resets,
+    every output and the final state hashed, with and without ASVRL_K1_GENERIC=1."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    got = []
+    for generic in ("0", "1"):
+        env = dict(os.environ, ASVRL_K1_GENERIC=generic)
+        r = subprocess.run([sys.executable, "-c", _SHAPE_PROBE, root, str(cores)], env=env, capture_output=True,
+                           text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        got.append([l for l in r.stdout.splitlines() if l.startswith("HASH")][0])
+    assert got[0] == got[1]

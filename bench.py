@@ -54,16 +54,40 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.stop_flag, self.source = index, [], False, "nvidia-smi"
+
+    def _nvml(self):
+        """In-process NVML (no subprocess per sample: eight ranks forking nvidia-smi ten times a second
+        load the host cores the e2e leg needs); None when pynvml is not importable."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.source = "nvml"
+            return nv, h
+        except Exception:
+            return None
 
     def run(self):
+        nvml = self._nvml()
         while not self.stop_flag:
             try:
-                r = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                    "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                   timeout=5)
-                if r.returncode == 0 and r.stdout.strip():
-                    self.rows.append([c.strip() for c in r.stdout.strip().split(",")])
+                if nvml is not None:
+                    nv, h = nvml
+                    bits = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    act = lambda b: "Active" if bits & b else "Not Active"
+                    self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
+                                      str(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)),
+                                      act(nv.nvmlClocksEventReasonHwSlowdown),
+                                      act(nv.nvmlClocksEventReasonHwThermalSlowdown),
+                                      act(nv.nvmlClocksEventReasonSwThermalSlowdown),
+                                      act(nv.nvmlClocksEventReasonSwPowerCap)])
+                else:
+                    r = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                        "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                       timeout=5)
+                    if r.returncode == 0 and r.stdout.strip():
+                        self.rows.append([c.strip() for c in r.stdout.strip().split(",")])
             except Exception:
                 pass
             time.sleep(0.1)
@@ -74,7 +98,7 @@ class ClockSampler(threading.Thread):
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+                "reasons": reasons, "samples": len(self.rows), "source": self.source}
 
 
 def host_threads():

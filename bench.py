@@ -478,6 +478,21 @@ def run_b200(args):
                             "note": "graph of 20 back-to-back launches; 0.5 MB per launch is latency bound"}
     learner["k3_tau_cos"] = {"ms": k3_ms, "algorithmic_bytes": k3_bytes, "achieved_gbs": k3_bytes / (k3_ms * 1e-3) / 1e9,
                              "frac": k3_bytes / (k3_ms * 1e-3) / 1e9 / peak}
+    # K8 alone: one dense layer of the collection forward (65 536 ASVs, 256 -> 128, bias + ReLU) on tcgen05
+    # (3 x TF32 split) against the cuBLAS sgemm + bias/ReLU passes it replaces
+    Mk = 65536
+    xk = torch.randn((Mk, 256), device=dev, generator=g)
+    wk = torch.randn((128, 256), device=dev, generator=g) / 16
+    bk = torch.randn((128,), device=dev, generator=g)
+    ok = torch.empty((Mk, 128), device=dev)
+    k8_ms = time_kernel(lambda: _lib.linear_tf32x3(xk, wk, bk, relu=True, out=ok), max(K, 200), W)
+    sg_ms = time_kernel(lambda: torch.relu_(torch.addmm(bk, xk, wk.t(), out=ok)), max(K, 200), W)
+    k8_bytes = 4 * Mk * (256 + 128)
+    learner["k8_linear_tf32x3"] = {"ms": k8_ms, "rows": Mk, "in_dim": 256, "out_dim": 128,
+                                   "algorithmic_bytes": k8_bytes, "achieved_gbs": k8_bytes / (k8_ms * 1e-3) / 1e9,
+                                   "frac": k8_bytes / (k8_ms * 1e-3) / 1e9 / peak,
+                                   "tflops_fp32_equivalent": 2 * Mk * 256 * 128 / (k8_ms * 1e-3) / 1e12,
+                                   "cublas_sgemm_bias_relu_ms": sg_ms}
     # ---- (5) training leg (BASELINE config 4, per-GPU share): collection policy forward for every ASV,
     # the fused step, K2a push, and one AC-IQN update (B=1024, N=32) per `update_every` batched steps,
     # all as CUDA graphs; the only collective is the gradient all-reduce.  Device-timed.

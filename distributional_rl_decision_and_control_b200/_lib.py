@@ -59,6 +59,7 @@ _SIGNATURES = {
     "asvrl_tower_fwd": (C.c_int, [f32p] * 7 + [C.c_int] * 6 + [f32p, vp]),
     "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
     "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
+    "asvrl_linear_tf32x3": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_long, C.c_int, C.c_int, f32p, C.c_void_p]),
     "asvrl_actor_head": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, f32p, C.c_float, C.POINTER(C.c_float * 2),
                                    C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_int, C.c_int, f32p, vp]),
     "asvrl_clip_adam_step_p2p": (C.c_int, [C.POINTER(_abi.AdamTensors), C.POINTER(_abi.PeerBuckets), f32p, u32p]
@@ -396,6 +397,20 @@ def actor_head(pre, bias, w, b_out, atan_scale, eps, lo, hi, seed, counter, coun
                                 ptr(actions), stream_ptr())
     check(rc, "asvrl_actor_head")
     return actions
+
+
+# ------------------------------------------------------------------ K8: dense layer on tcgen05 (3 x TF32)
+def linear_tf32x3(x, w, bias=None, relu=False, out=None):
+    """[relu](x @ w.T [+ bias]) at fp32-GEMM accuracy on the tensor cores; forward only."""
+    M, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=x.device)
+    f = torch.float32
+    rc = lib().asvrl_linear_tf32x3(ptr(x, f), ptr(w, f), ptr(bias, f), int(bool(relu)), M, K, N, ptr(out, f),
+                                   stream_ptr())
+    check(rc, "asvrl_linear_tf32x3")
+    return out
 
 
 # ------------------------------------------------------------------ K6: observation tower

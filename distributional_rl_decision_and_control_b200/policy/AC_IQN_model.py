@@ -127,18 +127,26 @@ class Actor(_ObservationTower):
             h = F.relu(self.hidden_layer_2(h))
         return self.atan_scale * torch.atan(self.output_layer(h))  # into (-1, 1), ACIQN:320-321
 
+    umma_linear = True  # collection path: dense layers through asvrl_linear_tf32x3 (False: cuBLAS + K5)
+
     @torch.no_grad()
     def act_eps_greedy(self, x, eps, seed, counter_dev):
-        """Collection path: forward + epsilon-greedy for every row in one launch sequence — K6, two
-        GEMMs with one K5 pass between them, and the actor-head kernel that goes from the second
+        """Collection path: forward + epsilon-greedy for every row in one launch sequence — K6, the two
+        dense layers (K8 on the tensor cores, or two GEMMs with one K5 pass between them), and the actor-head kernel that goes from the second
         hidden layer's pre-activation to the explored action (ReLU, 128 -> 2, atan squash, Philox
         exploration).  ``eps``: float or 0-d CUDA tensor; ``counter_dev``: int64 device word the caller
         advances after every call (graph-replay safe).  Two-dimensional actions only."""
         from .. import _lib
         feats = self._features(x)
-        ones = _unit_scale(feats.shape[0], self.hidden_dimension, feats.device)
-        h = linear_scale_relu(feats, self.hidden_layer.weight, self.hidden_layer.bias, ones, 1)
-        pre = h @ self.hidden_layer_2.weight.t()
+        if self.umma_linear and feats.dtype == torch.float32 and not torch.backends.cuda.matmul.allow_tf32:
+            # K8: both dense layers on the tcgen05 tensor cores at fp32 accuracy (3 x TF32 split), bias
+            # and ReLU in the epilogue; when the caller allowed plain TF32 the one-pass cuBLAS GEMM is faster
+            h = _lib.linear_tf32x3(feats, self.hidden_layer.weight, self.hidden_layer.bias, relu=True)
+            pre = _lib.linear_tf32x3(h, self.hidden_layer_2.weight, None, relu=False)
+        else:
+            ones = _unit_scale(feats.shape[0], self.hidden_dimension, feats.device)
+            h = linear_scale_relu(feats, self.hidden_layer.weight, self.hidden_layer.bias, ones, 1)
+            pre = h @ self.hidden_layer_2.weight.t()
         lo = [r[0] for r in self.value_ranges_of_action]
         hi = [r[1] for r in self.value_ranges_of_action]
         return _lib.actor_head(pre, self.hidden_layer_2.bias, self.output_layer.weight, self.output_layer.bias,

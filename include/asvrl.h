@@ -486,6 +486,15 @@ ASVRL_API int asvrl_actor_head(const float* pre, const float* bias, const float*
                                uint64_t counter, const uint64_t* counter_dev /* nullable */, int rows,
                                int dim, float* actions, void* stream);
 
+/* K8 — out = [relu](x * W^T [+ bias]): a dense layer of the policy MLPs (ACIQN:315-316) in the nn.Linear
+ * layout, x [rows][in_dim], w [out_dim][in_dim], bias [out_dim] nullable, out [rows][out_dim], fp32 in
+ * and out.  Computed on the tcgen05 tensor cores as a three-pass TF32 split (x_lo W_hi + x_hi W_lo +
+ * x_hi W_hi, fp32 accumulation in TMEM): fp32-GEMM-level accuracy (~3e-7 relative), not TF32's 3e-4.
+ * in_dim a multiple of 32; out_dim a multiple of 16, <= 256; pointers 16-byte aligned.  Forward only
+ * (the collection path, torch.no_grad). */
+ASVRL_API int asvrl_linear_tf32x3(const float* x, const float* w, const float* bias, int relu, long rows,
+                                  int in_dim, int out_dim, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -87,6 +87,7 @@ def test_bad_argument_codes_of_k5_k6_k7_without_gpu(so):
     assert so.asvrl_clip_adam_step_p2p(C.byref(t), C.byref(p), fake, fake, 0.5, 1e-4, 0.9, 0.999, 1e-8, None,
                                        fake, fake, None) == _abi.E_BADARG
     assert so.asvrl_actor_head(None, None, None, None, 0.6366, None, 0.1, None, None, 1, 0, None, 8, 128, None, None) == _abi.E_BADARG
+    assert so.asvrl_linear_tf32x3(None, None, None, 1, 128, 256, 128, None, None) == _abi.E_BADARG
     assert ctypes_sizes_match()
 
 

@@ -243,7 +243,10 @@ def test_actor_head_eps_greedy_matches_actor_forward():
     x, _ = _critic_inputs(B, 77)
     greedy = ag.policy_local.actor(x)
     a0 = ag.act_batch(x, eps=0.0)
-    close(a0, greedy, "greedy actions", rtol=2e-6)
+    close(a0, greedy, "greedy actions", rtol=1e-5)  # K8 (3 x TF32 on tcgen05) against cuBLAS sgemm
+    ag.policy_local.actor.umma_linear = False
+    close(ag.act_batch(x, eps=0.0), greedy, "greedy actions, cuBLAS + K5 path", rtol=2e-6)
+    ag.policy_local.actor.umma_linear = True
     a1 = ag.act_batch(x, eps=torch.tensor(0.3, device=DEV))
     a2 = ag.act_batch(x, eps=0.3)
     explored = (a1 - greedy).abs().max(dim=1).values > 1e-5
@@ -253,3 +256,50 @@ def test_actor_head_eps_greedy_matches_actor_forward():
     assert rnd.min().item() >= -1.0 and rnd.max().item() <= 1.0
     assert abs(rnd.mean().item()) < 0.02 and abs(rnd.var().item() - 1.0 / 3.0) < 0.02  # U(-1, 1)
     assert not torch.equal(a1, a2)  # the device counter advanced
+
+
+@pytest.mark.parametrize("M,K,N,bias,relu", [(65536, 256, 128, True, True), (1000, 128, 128, False, False),
+                                             (300, 64, 16, True, False), (257, 32, 256, True, True),
+                                             (128, 256, 64, False, True), (1, 96, 48, True, True)])
+def test_linear_tf32x3_matches_float64(M, K, N, bias, relu):
+    """K8: the tcgen05 dense layer (three-pass TF32 split) against the float64 product.  The bound is
+    the split's own: ~2^-21 of sum_k |x||w| per output — fp32-GEMM level, 1000 x below one TF32 pass."""
+    g = torch.Generator(device=DEV).manual_seed(M + K + N)
+    x = torch.randn((M, K), device=DEV, generator=g) * 3.0
+    w = (torch.rand((N, K), device=DEV, generator=g) * 2 - 1) / K ** 0.5
+    b = torch.randn((N,), device=DEV, generator=g) if bias else None
+    got = _lib.linear_tf32x3(x, w, b, relu=relu)
+    want = x.double() @ w.double().t()
+    if bias:
+        want = want + b.double()
+    if relu:
+        want = want.clamp_min(0.0)
+    mag = x.double().abs() @ w.double().abs().t()
+    err = (got.double() - want).abs()
+    assert float((err / mag.clamp_min(1e-30)).max()) <= 2e-6, float((err / mag).max())
+    # one TF32 pass would be ~2^-11 of mag: the split really ran
+    assert float(err.max()) <= 1e-5 * float(want.abs().max().clamp_min(1e-6))
+    torch.cuda.synchronize()
+
+
+def test_linear_tf32x3_in_a_cuda_graph_and_rejects_bad_shapes():
+    x = torch.randn((4096, 256), device=DEV)
+    w = torch.randn((128, 256), device=DEV) / 16
+    out = torch.empty((4096, 128), device=DEV)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        _lib.linear_tf32x3(x, w, None, out=out)
+    torch.cuda.current_stream().wait_stream(s)
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        _lib.linear_tf32x3(x, w, None, out=out)
+    x.mul_(2.0)
+    gr.replay()
+    torch.cuda.synchronize()
+    close(out, x.double() @ w.double().t(), "graph replay", rtol=1e-5)
+    for bad in ((4096, 250), (4096, 16)):
+        with pytest.raises(RuntimeError):
+            _lib.linear_tf32x3(torch.zeros(bad, device=DEV), torch.zeros((128, bad[1]), device=DEV))
+    with pytest.raises(RuntimeError):
+        _lib.linear_tf32x3(torch.zeros((64, 64), device=DEV), torch.zeros((100, 64), device=DEV))

@@ -5,6 +5,8 @@ need CUDA tensors and raise otherwise — there is no CPU fallback.
 Reference: rfarl/rfarl/policy/AC_IQN_model.py:410-426 (calc_cos), rfarl/rfarl/agent.py:401-412
 and 701-707 (loss core).
 """
+import os
+
 import torch
 
 from .. import _lib
@@ -80,6 +82,23 @@ def _wgrad(d_out, x, splits=64):
     return d_out.t() @ x
 
 
+# forward GEMMs of the fused trunks through K8 (tcgen05, 3 x TF32) in fp32 mode; ASVRL_UMMA_TRUNK=0/1 overrides
+UMMA_FORWARD = os.environ.get("ASVRL_UMMA_TRUNK", "0") == "1"
+UMMA_MIN_ROWS = 4096  # below this a 128-row-tile kernel leaves most SMs idle: cuBLAS
+
+
+def _gemm_nt(x, W):
+    """x @ W.T without epilogue.  When the caller asked for fp32 arithmetic (TF32 not allowed) and the
+    shape fits, K8 computes it on the tensor cores as a three-pass TF32 split at fp32-GEMM accuracy
+    (asvrl_linear_tf32x3); otherwise cuBLAS (fp32 SIMT, or one-pass TF32 when allowed)."""
+    M, K = x.shape
+    N = W.shape[0]
+    if (UMMA_FORWARD and M >= UMMA_MIN_ROWS and x.dtype == torch.float32 and K % 32 == 0 and N % 16 == 0
+            and N <= 256 and not torch.backends.cuda.matmul.allow_tf32 and W.is_contiguous()):
+        return _lib.linear_tf32x3(x.contiguous(), W.detach(), None, relu=False)
+    return x @ W.t()
+
+
 class _CriticTrunk(torch.autograd.Function):
     """The critic's quantile trunk (ACIQN:453-480) with K5 between the GEMMs:
 
@@ -94,11 +113,11 @@ class _CriticTrunk(torch.autograd.Function):
     @staticmethod
     def forward(ctx, cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau):
         cos, feats, aenc = cos.contiguous(), feats.contiguous(), aenc.contiguous()
-        P1 = cos @ Wc.t()
+        P1 = _gemm_nt(cos, Wc)
         H1 = _lib.iqn_scale_relu_fwd(P1, bc, feats, n_tau)
-        P2 = H1 @ Wh.t()
+        P2 = _gemm_nt(H1, Wh)
         H2 = _lib.iqn_scale_relu_fwd(P2, bh, aenc, n_tau)
-        P3 = H2 @ Wh2.t()
+        P3 = _gemm_nt(H2, Wh2)
         z = _lib.iqn_head_fwd(P3, bh2, wo.reshape(-1), bo)
         ctx.save_for_backward(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, P1, H1, P2, H2, P3)
         ctx.n_tau = n_tau
@@ -179,7 +198,7 @@ class _LinearScaleRelu(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, W, bias, scale, n_tau):
         x, scale = x.contiguous(), scale.contiguous()
-        pre = x @ W.t()
+        pre = _gemm_nt(x, W)
         out = _lib.iqn_scale_relu_fwd(pre, bias, scale, n_tau)
         ctx.save_for_backward(x, W, bias, scale, pre)
         ctx.n_tau = n_tau

@@ -28,10 +28,15 @@ constexpr int LU_MAX_N = 256;
 
 __device__ __forceinline__ uint32_t lu_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// round to tf32's 10-bit mantissa, nearest with ties away from zero: what cvt.rna.tf32.f32 returns for
+// finite values, in two integer instructions (ptxas expands the cvt into ~8 with its NaN / inf cases;
+// it was a third of the kernel's instructions, profiles/r01_k8_v21_source.txt)
 __device__ __forceinline__ float lu_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return __uint_as_float(r);
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+}
+
+__device__ __forceinline__ void lu_sts(uint32_t addr, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
 // shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 B apart, version 1
@@ -57,13 +62,13 @@ __device__ __forceinline__ void lu_wait(uint32_t mbar, uint32_t parity) {
 }
 
 // split + swizzled store of one 16-byte chunk (row r, chunk c of the atom)
-__device__ __forceinline__ void lu_put(char* hi, char* lo, int r, int c, float4 v) {
+__device__ __forceinline__ void lu_put(uint32_t hi, uint32_t lo, int r, int c, float4 v) {
   float4 h, l;
   h.x = lu_tf32(v.x); h.y = lu_tf32(v.y); h.z = lu_tf32(v.z); h.w = lu_tf32(v.w);
   l.x = lu_tf32(v.x - h.x); l.y = lu_tf32(v.y - h.y); l.z = lu_tf32(v.z - h.z); l.w = lu_tf32(v.w - h.w);
   const int off = (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4);
-  *reinterpret_cast<float4*>(hi + off) = h;
-  *reinterpret_cast<float4*>(lo + off) = l;
+  lu_sts(hi + off, h);
+  lu_sts(lo + off, l);
 }
 
 // NB = out_dim / 16 chunks-of-rows of W each thread stages: W rows = out_dim, 8 chunks per row,
@@ -78,7 +83,7 @@ linear_tf32x3_kernel(const float* __restrict__ x, const float* __restrict__ w, c
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   char* base = (char*)(((uintptr_t)lu_raw + 1023) & ~(uintptr_t)1023);
   const int a_bytes = LU_ROWS * 128, b_bytes = N * 128;
-  char *a_hi = base, *a_lo = base + a_bytes, *b_hi = base + 2 * a_bytes, *b_lo = base + 2 * a_bytes + b_bytes;
+  const uint32_t a_hi = lu_smem(base), a_lo = a_hi + a_bytes, b_hi = a_hi + 2 * a_bytes, b_lo = b_hi + b_bytes;
   const uint32_t mbar = lu_smem(&mbar_s);
   const long row0 = (long)blockIdx.x * LU_ROWS;
 
@@ -96,19 +101,20 @@ linear_tf32x3_kernel(const float* __restrict__ x, const float* __restrict__ w, c
   constexpr int XA = LU_ROWS * 8 / LU_TPB, WA_MAX = LU_MAX_N * 8 / LU_TPB;
   float4 xr[XA], wr[WA_MAX];
   const int wa = N * 8 / LU_TPB;
+  // thread t stages chunk (t & 7) of rows (t >> 3) + 16 i
+  const float* xp = x + (row0 + (tid >> 3)) * K + (tid & 7) * 4;
+  const float* wp = w + (long)(tid >> 3) * K + (tid & 7) * 4;
+  const long step16 = 16L * K;
+  const int my_rows = (int)(rows - row0 - (tid >> 3) < 0 ? 0 : (rows - row0 - (tid >> 3) + 15) / 16);  // valid i
   auto load_atom = [&](int kb) {
+    const float* xa = xp + kb * LU_ATOM_K;
+    const float* wa_p = wp + kb * LU_ATOM_K;
 #pragma unroll
-    for (int i = 0; i < XA; ++i) {
-      const int q = i * LU_TPB + tid, r = q >> 3, c = q & 7;
-      xr[i] = row0 + r < rows ? __ldg(reinterpret_cast<const float4*>(x + (row0 + r) * K + kb * LU_ATOM_K + c * 4))
-                              : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    for (int i = 0; i < XA; ++i)
+      xr[i] = i < my_rows ? __ldg(reinterpret_cast<const float4*>(xa + i * step16)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < WA_MAX; ++i)
-      if (i < wa) {
-        const int q = i * LU_TPB + tid, r = q >> 3, c = q & 7;
-        wr[i] = __ldg(reinterpret_cast<const float4*>(w + (long)r * K + kb * LU_ATOM_K + c * 4));
-      }
+      if (i < wa) wr[i] = __ldg(reinterpret_cast<const float4*>(wa_p + i * step16));
   };
   auto store_atom = [&]() {
 #pragma unroll
@@ -140,7 +146,7 @@ linear_tf32x3_kernel(const float* __restrict__ x, const float* __restrict__ w, c
     __syncthreads();
     if (tid == 0) {
       asm volatile("tcgen05.fence::after_thread_sync;\n");
-      const uint32_t ah = lu_smem(a_hi), al = lu_smem(a_lo), bh = lu_smem(b_hi), bl = lu_smem(b_lo);
+      const uint32_t ah = a_hi, al = a_lo, bh = b_hi, bl = b_lo;
 #pragma unroll
       for (int ks = 0; ks < LU_ATOM_K / LU_UMMA_K; ++ks) {
         const uint32_t o = ks * LU_UMMA_K * 4;

@@ -62,6 +62,11 @@ _SIGNATURES = {
     "asvrl_linear_tf32x3": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_long, C.c_int, C.c_int, f32p, C.c_void_p]),
     "asvrl_actor_head": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, f32p, C.c_float, C.POINTER(C.c_float * 2),
                                    C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_int, C.c_int, f32p, vp]),
+    "asvrl_policy_forward_workspace": (C.c_long, []),
+    "asvrl_policy_forward": (C.c_int, [f32p] * 13 + [C.c_float, f32p, C.c_float, C.POINTER(C.c_float * 2),
+                                       C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_long, C.c_int,
+                                       vp, f32p, vp]),
+    "asvrl_policy_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_clip_adam_step_p2p": (C.c_int, [C.POINTER(_abi.AdamTensors), C.POINTER(_abi.PeerBuckets), f32p, u32p]
                                  + [C.c_float] * 5 + [f32p, f32p, u32p, vp]),
     "asvrl_clip_adam_step": (C.c_int, [C.POINTER(_abi.AdamTensors)] + [C.c_float] * 6 + [f32p, f32p, u32p, vp]),
@@ -411,6 +416,43 @@ def linear_tf32x3(x, w, bias=None, relu=False, out=None):
                                    stream_ptr())
     check(rc, "asvrl_linear_tf32x3")
     return out
+
+
+# ------------------------------------------------------------------ K9: fused collection policy forward
+_POLICY_WS = {}
+
+
+def policy_forward(self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2, w_out, b_out,
+                   atan_scale, eps, lo, hi, seed, counter=0, counter_dev=None, repack=True, out=None):
+    """(rows, 2) epsilon-greedy actions of the AC-IQN / DDPG actor for every row in one persistent tcgen05
+    launch (+ one small weight-pack launch when ``repack``).  ``eps``: float or 0-d CUDA tensor."""
+    M = self_obs.shape[0]
+    dev = self_obs.device
+    ws = _POLICY_WS.get(dev)
+    if ws is None:
+        ws = _POLICY_WS[dev] = torch.empty((lib().asvrl_policy_forward_workspace(),), dtype=torch.uint8, device=dev)
+        repack = True
+    if out is None:
+        out = torch.empty((M, 2), dtype=torch.float32, device=dev)
+    eps_dev, eps_f = (eps, 0.0) if isinstance(eps, torch.Tensor) else (None, float(eps))
+    f = torch.float32
+    rc = lib().asvrl_policy_forward(
+        ptr(self_obs, f), ptr(objects, f), ptr(mask, f), ptr(w_self, f), ptr(b_self, f), ptr(w_obj, f), ptr(b_obj, f),
+        ptr(w1, f), ptr(b1, f), ptr(w2, f), ptr(b2, f), ptr(w_out, f), ptr(b_out, f), float(atan_scale),
+        ptr(eps_dev, f), eps_f, C.byref((C.c_float * 2)(*lo)), C.byref((C.c_float * 2)(*hi)),
+        int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), ptr(counter_dev, torch.int64), M, int(bool(repack)),
+        ws.data_ptr(), ptr(out, f), stream_ptr())
+    check(rc, "asvrl_policy_forward")
+    return out
+
+
+def policy_forward_status():
+    """Synchronous read of K9's device status word; raises when a bounded wait of the pipeline expired."""
+    v = C.c_int(0)
+    check(lib().asvrl_policy_forward_status(C.byref(v)), "asvrl_policy_forward_status")
+    if v.value != 0:
+        raise RuntimeError(f"asvrl_policy_forward: device pipeline fault, status {v.value}")
+    return 0
 
 
 # ------------------------------------------------------------------ K6: observation tower

@@ -128,6 +128,15 @@ class Actor(_ObservationTower):
         return self.atan_scale * torch.atan(self.output_layer(h))  # into (-1, 1), ACIQN:320-321
 
     umma_linear = True  # collection path: dense layers through asvrl_linear_tf32x3 (False: cuBLAS + K5)
+    fused_policy = os.environ.get("ASVRL_POLICY_FUSED", "1") != "0"  # K9: the whole forward in one launch
+
+    def _fused_policy_ok(self, x):
+        """K9 is compiled for the reference's fixed network shape (AGENT:20-26) in float32."""
+        return (self.fused_policy and x[1] is not None and x[0].is_cuda and x[0].dtype == torch.float32
+                and self.hidden_layer.weight.dtype == torch.float32 and x[2].dtype == torch.float32
+                and (self.self_dimension, self.object_dimension, self.max_object_num, self.self_feature_dimension,
+                     self.object_feature_dimension, self.concat_feature_dimension, self.hidden_dimension,
+                     self.action_dimension) == (7, 5, 5, 56, 40, 256, 128, 2))
 
     @torch.no_grad()
     def act_eps_greedy(self, x, eps, seed, counter_dev):
@@ -137,6 +146,17 @@ class Actor(_ObservationTower):
         exploration).  ``eps``: float or 0-d CUDA tensor; ``counter_dev``: int64 device word the caller
         advances after every call (graph-replay safe).  Two-dimensional actions only."""
         from .. import _lib
+        lo = [r[0] for r in self.value_ranges_of_action]
+        hi = [r[1] for r in self.value_ranges_of_action]
+        if self._fused_policy_ok(x):
+            # K9: tower, both dense layers (tcgen05, fp16 two-piece split), head and exploration in one
+            # persistent launch; the activations never leave the SM
+            se, oe = self.self_encoder[0], self.object_encoder[0]
+            return _lib.policy_forward(x[0], x[1].reshape(-1, self.max_object_num, self.object_dimension), x[2],
+                                       se.weight, se.bias, oe.weight, oe.bias, self.hidden_layer.weight,
+                                       self.hidden_layer.bias, self.hidden_layer_2.weight, self.hidden_layer_2.bias,
+                                       self.output_layer.weight, self.output_layer.bias, self.atan_scale, eps, lo, hi,
+                                       seed, 0, counter_dev)
         feats = self._features(x)
         if self.umma_linear and feats.dtype == torch.float32 and not torch.backends.cuda.matmul.allow_tf32:
             # K8: both dense layers on the tcgen05 tensor cores at fp32 accuracy (3 x TF32 split), bias
@@ -147,8 +167,6 @@ class Actor(_ObservationTower):
             ones = _unit_scale(feats.shape[0], self.hidden_dimension, feats.device)
             h = linear_scale_relu(feats, self.hidden_layer.weight, self.hidden_layer.bias, ones, 1)
             pre = h @ self.hidden_layer_2.weight.t()
-        lo = [r[0] for r in self.value_ranges_of_action]
-        hi = [r[1] for r in self.value_ranges_of_action]
         return _lib.actor_head(pre, self.hidden_layer_2.bias, self.output_layer.weight, self.output_layer.bias,
                                self.atan_scale, eps, lo, hi, seed, 0, counter_dev)
 

@@ -495,6 +495,27 @@ ASVRL_API int asvrl_actor_head(const float* pre, const float* bias, const float*
 ASVRL_API int asvrl_linear_tf32x3(const float* x, const float* w, const float* bias, int relu, long rows,
                                   int in_dim, int out_dim, float* out, void* stream);
 
+/* K9 — the whole collection policy forward of the AC-IQN / DDPG actor for `rows` ASVs in ONE persistent launch:
+ * encoders + mask + concat (ACIQN:284-308), hidden_layer / hidden_layer_2 with ReLU (ACIQN:315-316) on the tcgen05
+ * tensor cores (fp16 two-piece split, three products, fp32 accumulation in TMEM: fp32-GEMM-level accuracy), output
+ * layer, (2/pi) atan (ACIQN:318-321) and the epsilon-greedy choice of AGENT:207-225 (Philox stream 5, the same draw
+ * as asvrl_actor_head).  The network shape is the reference's fixed one (AGENT:20-26): self 7 -> 56, 5 objects x
+ * 5 -> 40, 256 -> 128 -> 128 -> 2; weights in the nn.Linear layout.  self_obs [rows][7], objects [rows][5][5],
+ * mask [rows][5] (>= 0.5 = present), actions [rows][2].  `workspace`: asvrl_policy_forward_workspace() bytes,
+ * 128-byte aligned, holds the packed weight image; `repack` != 0 rebuilds it from w1 / w2 first (needed after every
+ * optimiser step; one small launch).  Bounded waits: a pipeline fault leaves a non-zero code in the status word
+ * read by asvrl_policy_forward_status (synchronous) instead of hanging or trapping. */
+ASVRL_API long asvrl_policy_forward_workspace(void);
+ASVRL_API int asvrl_policy_forward(const float* self_obs, const float* objects, const float* mask,
+                                   const float* w_self, const float* b_self, const float* w_obj,
+                                   const float* b_obj, const float* w1, const float* b1, const float* w2,
+                                   const float* b2, const float* w_out, const float* b_out, float atan_scale,
+                                   const float* eps_dev /* nullable */, float eps, const float* action_lo,
+                                   const float* action_hi, uint64_t seed, uint64_t counter,
+                                   const uint64_t* counter_dev /* nullable */, long rows, int repack,
+                                   void* workspace, float* actions, void* stream);
+ASVRL_API int asvrl_policy_forward_status(int* status_out);
+
 #ifdef __cplusplus
 }
 #endif

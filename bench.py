@@ -121,27 +121,74 @@ def cpu_learner_baseline(seconds=3.0):
     return out
 
 
-def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0):
-    """env-steps/s of the float64 C port of the reference on `cores` host threads.  Bounded
-    sample: n_envs envs x n_steps steps of the same workload shape (in-port Philox noise)."""
-    import numpy as np
-    from distributional_rl_decision_and_control_b200 import _abi
-    from oracle import oracle, scenes
-    p = _abi.default_params()
-    st = scenes.random_scene(seed, n_envs, R, O, c_cores, box=50.0, p_deact=0.0, p_timeout=0.0, ragged=False)
-    st["flags"][:] = 0
-    st["ep_steps"][:] = 0
-    out = oracle.new_out(n_envs, R)
-    acts = [scenes.random_actions(seed + i, n_envs, R, False) for i in range(4)]
-    mode = _abi.M_DYNAMICS  # no deactivation: every ASV integrates every step (upper bound on work)
-    oracle.env_step(p, st, acts[0], None, mode, O, c_cores, seed=1, step=0, n_threads=cores, out=out, margins=False)
-    t0 = time.perf_counter()
-    for i in range(n_steps):
-        oracle.env_step(p, st, acts[i % 4], None, mode, O, c_cores, seed=1, step=i + 1, n_threads=cores,
-                        out=out, margins=False)
-    dt = time.perf_counter() - t0
-    assert np.isfinite(out["reward"]).all()
-    return n_envs * n_steps / dt, dt
+def workload_config(E, C, world, stagger=True):
+    """The workload both arms run (`config` of the JSON line; identical in the b200 and the reference arm)."""
+    return {"workload": f"C2 env-step: {E} envs x {R} ASVs x {O} buoys x {C} vortex cores per GPU; auto-deactivate + auto-reset",
+            "envs_per_gpu": E, "robots": R, "buoys": O, "vortex_cores": C, "actions": "continuous U(-1,1)^2",
+            "sensor_noise": "Philox4x32-10, in the step", "auto_deactivate": True, "auto_reset": True,
+            "episode_clocks": "staggered over [0,1000): ~E/1000 resets per step" if stagger else "synchronised",
+            "l2": "GPU arm: flushed between timed steps (256 MiB write) unless --l2 rotate; CPU arm: not applicable",
+            "parallelism": f"envs sharded x{world}, no collective"}
+
+
+class CpuWorkload:
+    """The product arm's workload on the float64 C port of the reference (oracle/), all host threads: E envs
+    of the config-2 shape generated by the port's reset (ENV:72-176), episode clocks staggered, every step =
+    env step with auto-deactivation (TRAINER:168-170) + re-generation of the episodes that ended
+    (TRAINER:172, 240-245).  Only the first observation of a fresh episode is left out (the port has no env mask
+    for a perception-only pass; ~E/1000 envs per step)."""
+
+    def __init__(self, n_envs, cores, c_cores, seed=0, stagger=True):
+        import numpy as np
+        from distributional_rl_decision_and_control_b200 import _abi
+        from oracle import oracle, scenes
+        self.np, self.oracle, self._abi = np, oracle, _abi
+        self.E, self.cores, self.C = n_envs, cores, c_cores
+        self.p, self.rp = _abi.default_params(), _abi.default_reset_params()
+        self.st = oracle.new_state(n_envs, R, O, c_cores)
+        self.want = (np.full(n_envs, R, np.int32), np.full(n_envs, c_cores, np.int32), np.full(n_envs, O, np.int32))
+        self.min_sg = np.full(n_envs, 30.0)
+        self.seed, self.episode, self.step_no = seed + 1, 1, 0
+        self._reset(np.ones(n_envs, np.uint8))
+        if stagger:
+            self.st["ep_steps"][:] = np.random.RandomState(seed).randint(0, 1000, n_envs)
+        self.out = oracle.new_out(n_envs, R)
+        self.acts = [scenes.random_actions(seed + i, n_envs, R, False) for i in range(4)]
+        self.mode = _abi.M_DYNAMICS | _abi.M_AUTO_DEACTIVATE
+        self.resets = 0
+
+    def _reset(self, mask):
+        self.oracle.env_reset(self.rp, self.st, mask, self.want[0], self.want[1], self.want[2], self.min_sg,
+                              self.seed, self.episode, O, self.C)
+        self.episode += 1
+
+    def step(self):
+        self.step_no += 1
+        self.oracle.env_step(self.p, self.st, self.acts[self.step_no % 4], None, self.mode, O, self.C, seed=self.seed,
+                             step=self.step_no, n_threads=self.cores, out=self.out, margins=False)
+        ended = (self.out["env_status"] & 3) != 0
+        n = int(ended.sum())
+        if n:
+            self.resets += n
+            self._reset(ended.astype(self.np.uint8))
+
+    def run(self, n_steps):
+        t0 = time.perf_counter()
+        for _ in range(n_steps):
+            self.step()
+        dt = time.perf_counter() - t0
+        assert self.np.isfinite(self.out["reward"]).all()
+        return self.E * n_steps / dt, dt
+
+
+def cpu_port_throughput(n_envs, n_steps, cores, c_cores, seed=0, warmup=1):
+    """env-steps/s of the float64 C port of the reference on `cores` host threads, on the product arm's
+    workload (see CpuWorkload).  Returns (env-steps/s, seconds, resets per step)."""
+    w = CpuWorkload(n_envs, cores, c_cores, seed)
+    w.run(warmup)
+    w.resets = 0
+    v, dt = w.run(n_steps)
+    return v, dt, w.resets / max(n_steps, 1)
 
 
 def grad_sync_kind(agent, world):
@@ -225,6 +272,54 @@ def time_kernel(fn, K, W, per_graph=20):
     return e0.elapsed_time(e1) / (reps * per_graph)
 
 
+def facade_leg(dev, total_timesteps):
+    """Trainer.learn through the reference-shaped facade (TRAIN:74-109, TRAINER:85-255) on the example config's
+    first curriculum stage; wall clock of the whole loop (reset, per-ASV act, step, replay add, train every 4)."""
+    import contextlib
+    import io
+    import tempfile
+    import torch
+    from distributional_rl_decision_and_control_b200.agent import Agent
+    from distributional_rl_decision_and_control_b200.envs.marinenav.env import MarineNavEnv3
+    from distributional_rl_decision_and_control_b200.policy.trainer import Trainer
+    sched = {"timesteps": [0], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+    ev = {"num_episodes": [1], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+    with tempfile.TemporaryDirectory() as d, contextlib.redirect_stdout(io.StringIO()):
+        train_env = MarineNavEnv3(seed=0, schedule=sched, device=str(dev))
+        eval_env = MarineNavEnv3(seed=253, is_eval_env=True, device=str(dev))
+        agent = Agent(device=str(dev), seed=100, agent_type="AC-IQN")
+        n_train = [0]
+        orig = agent.train
+
+        def counted(*a, **k):
+            n_train[0] += 1
+            return orig(*a, **k)
+        agent.train = counted
+        tr = Trainer(train_env=train_env, eval_env=eval_env, eval_schedule=ev, rl_agent=agent, imitation=False,
+                     il_agent=None)
+        tr.save_eval_config(d)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        tr.learn(total_timesteps=total_timesteps, eval_freq=10 ** 9, eval_log_path=d)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    out = {"env_steps_per_sec": train_env.total_timesteps / dt, "updates_per_sec": n_train[0] / dt,
+           "env_steps": train_env.total_timesteps, "updates": n_train[0], "seconds": dt,
+           "what": "Trainer.learn over MarineNavEnv3 (1 env x 3 ASVs, no buoys) + Agent(AC-IQN, B=64, N=8): the "
+                   "unchanged-script path; one kernel launch per env.step, one batch-1 forward per ASV"}
+    try:
+        with open(os.path.join(ROOT, "profiles", "ref_python_baseline.json")) as f:
+            ref = json.load(f)
+        c1 = ref["c1_trainer"]
+        k = sorted(c1)[0]
+        out["python_reference"] = {"env_steps_per_sec": c1[k]["env_steps_per_sec"], "updates_per_sec": c1[k]["updates_per_sec"],
+                                   "cores": ref["host"]["cores"], "where": "build container, " + k,
+                                   "source": "profiles/ref_python_baseline.json (profiles/probes/ref_python_baseline.py)"}
+    except Exception:
+        pass
+    return out
+
+
 def training_leg(args, precision, dev, pg, rank, world, barrier, dist, kind="AC-IQN", n_steps=400):
     """BASELINE config 4, per-GPU share: collection policy forward for every ASV (act_batch), the fused
     step, K2a push, and one AC-IQN update (B=1024, N=32) per `update_every` batched steps, all as CUDA
@@ -260,7 +355,23 @@ def training_leg(args, precision, dev, pg, rank, world, barrier, dist, kind="AC-
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     tsec = float(tms.item()) * 1e-3
-    return {"env_steps_per_sec": world * ET * (vt.steps - steps0) / tsec,
+    sync = {"grad_sync": grad_sync_kind(agent, world)}
+    if world > 1:
+        # driver-side evidence that the exchange kept the replicas bit-identical: every rank's parameter
+        # bytes, hashed, all-gathered and compared
+        nets = [m for m in (getattr(agent.policy_local, "actor", None), getattr(agent.policy_local, "critic", None),
+                            agent.policy_local if isinstance(agent.policy_local, torch.nn.Module) else None) if m is not None]
+        flat = torch.cat([p.detach().reshape(-1).view(torch.int32).to(torch.int64) for m in nets for p in m.parameters()])
+        w = torch.arange(1, flat.numel() + 1, device=dev, dtype=torch.int64)
+        h = torch.stack([flat.sum(), (flat * w).sum()])
+        got = [torch.empty_like(h) for _ in range(world)]
+        dist.all_gather(got, h)
+        sync["replicas_identical"] = bool(all(torch.equal(got[0], x) for x in got))
+        for opt in (getattr(agent, "critic_optimizer", None), getattr(agent, "actor_optimizer", None),
+                    getattr(agent, "optimizer", None)):
+            if hasattr(opt, "check"):
+                opt.check()  # raises if any step was skipped (a missed exchange is sticky)
+    return {"env_steps_per_sec": world * ET * (vt.steps - steps0) / tsec, **sync,
             "updates_per_sec": (vt.updates - upd0) / tsec, "envs_per_gpu": ET,
             "batched_steps": vt.steps - steps0, "update_every_batched_steps": vt.update_every,
             "batch_per_gpu": 1024, "n_tau": 32, "gemm": precision,
@@ -345,7 +456,8 @@ def run_b200(args):
             ev[i][1].record()
             en.finish_episodes()           # K1b + masked perception-only K1
     barrier()
-    k1_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / KE
+    k1_all = sorted(e[0].elapsed_time(e[1]) for e in ev)
+    k1_ms = k1_all[len(k1_all) // 2]  # median launch: robust at the driver's --steps 20 (one cold outlier is 5 % of a mean)
 
     # ---- (2) the product path: one CUDA graph per step (the fused launch, or K1, K1b, masked K1) ----
     # the fused step is a single launch, issued directly; the three-launch sequence is one graph
@@ -375,9 +487,13 @@ def run_b200(args):
             torch.cuda.current_stream().wait_stream(en._side)
         tail1.record()
     barrier()
-    step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
+    per_step = sorted(e[0].elapsed_time(e[1]) for e in ev)
+    step_sum_ms = sum(per_step)
     if getattr(env, "prefetch", None) == "stream":
-        step_ms += tail0.elapsed_time(tail1)
+        step_sum_ms += tail0.elapsed_time(tail1)
+    # value: this rank's MEDIAN step time x K (then the max over ranks); the plain sum of the K steps is kept
+    # beside it (`ms_per_step_mean`) — at K = 20 one slow launch on one rank otherwise sets the whole-job figure
+    step_ms = per_step[len(per_step) // 2] * K
     launches = sum(en.launches for en in envs) - launches0
 
     # cross-check without the flush gaps: K steps back to back, the side stream joined at the end
@@ -493,6 +609,38 @@ def run_b200(args):
                                    "frac": k8_bytes / (k8_ms * 1e-3) / 1e9 / peak,
                                    "tflops_fp32_equivalent": 2 * Mk * 256 * 128 / (k8_ms * 1e-3) / 1e12,
                                    "cublas_sgemm_bias_relu_ms": sg_ms}
+    # K9 alone: the fused collection policy forward for 65 536 ASVs (the per-GPU share of config 4) against the
+    # K6 + 2 x K8 + actor-head sequence of round 1; algorithmic HBM bytes 148 in + 8 out per ASV
+    try:
+        from distributional_rl_decision_and_control_b200.policy.AC_IQN_model import Actor as _Actor
+        kag = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=64, num_tau=8, BUFFER_SIZE=256)
+        Mp = 65536
+        xo = (torch.randn((Mp, 7), device=dev, generator=g), torch.randn((Mp, 5, 5), device=dev, generator=g),
+              (torch.rand((Mp, 5), device=dev, generator=g) < 0.6).float())
+        k9_ms = time_kernel(lambda: kag.act_batch(xo, eps=0.05), max(K, 200), W)
+        _lib.policy_forward_status()
+        _Actor.fused_policy = False
+        old_ms = time_kernel(lambda: kag.act_batch(xo, eps=0.05), max(K, 200), W)
+        _Actor.fused_policy = True
+        k9_bytes = Mp * (148 + 8)
+        k9_flop = 2.0 * Mp * (56 * 7 + 200 * 5 + 256 * 128 + 128 * 128 + 2 * 128)
+        learner["k9_policy_forward"] = {
+            "ms": k9_ms, "rows": Mp, "algorithmic_bytes": k9_bytes, "achieved_gbs": k9_bytes / (k9_ms * 1e-3) / 1e9,
+            "frac_hbm": k9_bytes / (k9_ms * 1e-3) / 1e9 / peak, "tflops_fp32_equivalent": k9_flop / (k9_ms * 1e-3) / 1e12,
+            "tensor_tflops_issued": 3 * 2.0 * Mp * (256 * 128 + 128 * 128) / (k9_ms * 1e-3) / 1e12,
+            "round1_k6_k8_head_ms": old_ms, "launches": 2,
+            "note": "one persistent tcgen05 launch (+ the weight-pack launch): fp16 two-piece split, 3 products"}
+    except Exception as e:
+        learner["k9_policy_forward"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    # ---- facade leg: the path train_RL_agents.py drives UNCHANGED — one MarineNavEnv3 (config-1 shape: 3 ASVs,
+    # no buoys) + Agent (B=64, N=8) + Trainer.learn — timed as a whole loop, next to the Python reference's
+    # own figures for the same loop (profiles/ref_python_baseline.json, produced in the build container)
+    facade = None
+    if not args.profile and rank == 0:
+        try:
+            facade = facade_leg(dev, args.facade_steps)
+        except Exception as e:
+            facade = {"error": f"{type(e).__name__}: {e}"[:300]}
     # ---- (5) training leg (BASELINE config 4, per-GPU share): collection policy forward for every ASV,
     # the fused step, K2a push, and one AC-IQN update (B=1024, N=32) per `update_every` batched steps,
     # all as CUDA graphs; the only collective is the gradient all-reduce.  Device-timed.
@@ -505,9 +653,9 @@ def run_b200(args):
             except Exception as e:  # the headline legs above must not be lost to this one
                 training[prec] = {"error": f"{type(e).__name__}: {e}"[:300]}
     # ---- (6) BASELINE config 5: the same loop for the other five agents of the reference, one after
-    # the other (fp32, one GPU; a leg that fails is reported, not fatal)
+    # the other (fp32, every world size: the six-agent 1/2/4/8 study; a leg that fails is reported, not fatal)
     agents = None
-    if not args.profile and world == 1 and not args.no_agents:
+    if not args.profile and not args.no_agents:
         agents = {}
         for kind in ("IQN", "DDPG", "DQN", "SAC", "Rainbow"):
             try:
@@ -518,10 +666,10 @@ def run_b200(args):
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
-    times = torch.tensor([step_ms, k1_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    times = torch.tensor([step_ms, k1_ms, e2e_s * 1e3, step_sum_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    step_ms, k1_ms, e2e_ms = (float(x) for x in times.tolist())
+    step_ms, k1_ms, e2e_ms, step_sum_ms = (float(x) for x in times.tolist())
 
     if rank == 0:
         # issue-rate roof of the dominant kernel (it is issue bound, not HBM bound): warp instructions
@@ -536,25 +684,48 @@ def run_b200(args):
                      "floor_ms": floor_ms, "frac": floor_ms / k1_ms}
         per_launch = alg_bytes_per_env_step(R, O, C) * E
         achieved = per_launch / (k1_ms * 1e-3) / 1e9
+        def _num(d, *keys):
+            for k in keys:
+                d = d.get(k) if isinstance(d, dict) else None
+            return round(d, 6) if isinstance(d, float) else d
+        tr32 = (training or {}).get("fp32") or {}
+        # the driver's record keeps `config`, `roofline`, `e2e`, `cpu_baseline`, `clocks` and drops other top-level
+        # keys: the numbers the review needs are mirrored here in compact form
+        also = {
+            "ms_per_step_mean": step_sum_ms / K, "l2_resident_ms_per_step": b2b_ms,
+            "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
+            "training_fp32_env_steps_per_sec": _num(training, "fp32", "env_steps_per_sec"),
+            "training_tf32_env_steps_per_sec": _num(training, "tf32", "env_steps_per_sec"),
+            "training_fp32_updates_per_sec": _num(training, "fp32", "updates_per_sec"),
+            "grad_sync": tr32.get("grad_sync"), "replicas_identical": tr32.get("replicas_identical"),
+            "learner_c3_fp32_ms": _num(learner, "c3_B1024_N32", "ms_per_update"),
+            "learner_c3_tf32_ms": _num(learner, "c3_B1024_N32_tf32", "ms_per_update"),
+            "learner_ref_B64_N8_ms": _num(learner, "ref_B64_N8", "ms_per_update"),
+            "k9_policy_forward_ms": _num(learner, "k9_policy_forward", "ms"),
+            "k9_frac_hbm": _num(learner, "k9_policy_forward", "frac_hbm"),
+            "k9_tflops_fp32_equivalent": _num(learner, "k9_policy_forward", "tflops_fp32_equivalent"),
+            "k4_qhuber_ms": _num(learner, "k4_qhuber", "ms"), "k3_tau_cos_ms": _num(learner, "k3_tau_cos", "ms"),
+            "agents_c5_env_steps_per_sec": {k: _num(v, "env_steps_per_sec") for k, v in (agents or {}).items()},
+            "facade_env_steps_per_sec": _num(facade, "env_steps_per_sec"),
+            "facade_updates_per_sec": _num(facade, "updates_per_sec"),
+            "facade_python_reference_env_steps_per_sec": _num(facade, "python_reference", "env_steps_per_sec"),
+        }
         line = {
             "metric": "env_steps_per_sec", "value": world * E * K / (step_ms * 1e-3), "unit": "env-steps/s",
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"C2 batched env-step: {E} envs x {R} ASVs x {O} buoys x {C} vortex cores per GPU, "
-                                   "continuous actions, in-kernel Philox sensor noise, auto-deactivate + auto-reset; "
-                                   + ("one fused launch per step (K1 + re-generation + first observation), no graph"
+            "config": workload_config(E, C, world, not args.no_stagger),
+            "impl_notes": {"launch": ("one fused launch per step (K1 + re-generation + first observation), no graph"
                                       if env.fused else "one CUDA graph per step (K1, K1b, masked K1)"),
-                       "envs_per_gpu": E, "asv_steps_per_sec": world * E * R * K / (step_ms * 1e-3),
-                       "episode_clocks": "synchronised" if args.no_stagger else "staggered over [0,1000): ~E/1000 resets per step",
-                       "next_episodes": (f"pre-generated on a side stream every {env.prefetch_every} steps "
-                                         "(asvrl_env_stage_refill)" if getattr(env, "prefetch", None) == "stream"
-                                         else "pre-generated by refill CTAs of the step launch"
-                                         if getattr(env, "prefetch", None) == "workers" else "generated in place"),
-                       "l2_resident_ms_per_step": b2b_ms,
-                       "l2": (f"inputs larger than L2: {NB} env batches of {E} envs stepped round robin, "
-                              f"~{26 * NB} MB of state / observation / stage buffers" if NB > 1
-                              else "flushed between timed steps (256 MiB write)"), "parallelism": f"envs sharded x{world}, no collective"},
+                           "next_episodes": (f"pre-generated on a side stream every {env.prefetch_every} steps "
+                                             "(asvrl_env_stage_refill)" if getattr(env, "prefetch", None) == "stream"
+                                             else "pre-generated by refill CTAs of the step launch"
+                                             if getattr(env, "prefetch", None) == "workers" else "generated in place"),
+                           "value": "median step time of this rank x K, max over ranks (ms_per_step_mean: the plain mean)",
+                           "l2": (f"inputs larger than L2: {NB} env batches of {E} envs stepped round robin, "
+                                  f"~{26 * NB} MB of state / observation / stage buffers" if NB > 1
+                                  else "flushed between timed steps (256 MiB write)")},
             "e2e": {"value": world * E * K / (e2e_ms * 1e-3), "unit": "env-steps/s",
                     "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": e2e_d2h,
                     "api": ("HostPipelinedEnv.send/recv, %d shards of E/%d envs, one CUDA graph launch per send "
@@ -565,19 +736,22 @@ def run_b200(args):
                          "frac": achieved / peak, "traffic": k1_traffic(E, C, env.fused), "peak_source": which,
                          "kernel": "env_step_kernel<false,true,1> (fused auto-reset, config-2 shape instantiation)" if env.fused
                                    else "env_step_kernel<false,false>", "kernel_ms": k1_ms,
+                         "kernel_ms_is": "median of the event-timed launches",
                          "algorithmic_bytes_per_launch": per_launch,
                          "issue": issue,
-                         "note": "instruction-issue bound by design (SURVEY.md F5): `issue.frac` = share of the "
-                                 "launch's issue slots that carry an instruction; see profiles/"},
-            "learner": learner, "training": training, "agents_c5": agents,
+                         "note": "instruction-issue bound by design (SURVEY.md F5): issue.frac = share of issue slots used. "
+                                 "The launch's 6.7 MB of stores stay dirty in L2 and are written back during the "
+                                 "UN-timed flush between steps: the timed region never pays them (traffic = reads only)",
+                         "also": also},
+            "learner": learner, "training": training, "agents_c5": agents, "facade": facade,
             "clocks": sampler.summary(), "finite": finite,
         }
         if world == 1 and not args.no_cpu:
             cores = host_threads()
-            v, dt = cpu_port_throughput(args.cpu_envs, args.cpu_steps, cores, C)
+            v, dt, rps = cpu_port_throughput(E, args.cpu_steps, cores, C)
             line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                                    "sample": f"{args.cpu_envs} envs x {args.cpu_steps} steps of the same shape, "
-                                              f"float64 C port of the reference, {dt:.1f} s",
+                                    "sample": f"{E} envs x {args.cpu_steps} steps of the same workload ({rps:.1f} resets "
+                                              f"per step), float64 C port of the reference, {dt:.1f} s",
                                     "learner": cpu_learner_baseline()}
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -591,23 +765,23 @@ def run_b200(args):
 
 
 def run_reference(args):
-    """The reference's CPU implementation of the path, as its float64 C port (the Python
-    reference does not travel to the GPU box), on all host threads.  Rank 0 only."""
+    """The reference's CPU implementation of the path, as its float64 C port (the Python reference does not
+    travel to the GPU box; its own speed, measured in the build container, is profiles/ref_python_baseline.json),
+    on all host threads, on the SAME workload as the b200 arm (CpuWorkload).  Rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     cores = host_threads()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     K, W = args.steps, max(args.warmup, 1)
-    n = args.cpu_envs
-    cpu_port_throughput(n, W, cores, args.cores)
-    v, dt = cpu_port_throughput(n, K, cores, args.cores)
+    E = args.envs
+    v, dt, rps = cpu_port_throughput(E, K, cores, args.cores, warmup=W)
     line = {"impl": "reference", "metric": "env_steps_per_sec", "value": v, "unit": "env-steps/s",
-            "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": K, "warmup": W,
+            "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"C2 batched env-step shape: {R} ASVs x {O} buoys x {args.cores} vortex cores; "
-                                   f"each step a bounded sample of {n} envs"},
+            "config": workload_config(E, args.cores, world, True),
             "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                             "sample": f"{n} envs x {K} steps, float64 C port of the reference",
+                             "sample": f"{E} envs x {K} steps ({rps:.1f} resets per step), float64 C port of the reference",
                              "learner": cpu_learner_baseline()},
             "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -622,8 +796,8 @@ def main():
     ap.add_argument("--envs", type=int, default=4096, help="envs per GPU (BASELINE config 2: 4096)")
     ap.add_argument("--cores", type=int, default=8, help="vortex cores per env (the current disturbance)")
     ap.add_argument("--seed", type=int, default=0)
-    ap.add_argument("--cpu-envs", type=int, default=2048)
-    ap.add_argument("--cpu-steps", type=int, default=2000)
+    ap.add_argument("--cpu-steps", type=int, default=1000, help="steps of the cpu_baseline sample (same envs as --envs)")
+    ap.add_argument("--facade-steps", type=int, default=3000, help="Trainer.learn budget of the facade leg (learning starts at 2000)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--l2", default="flush", choices=["rotate", "flush"],
                     help="how every timed step sees cold data: rotate env batches (> L2) or flush L2")

@@ -60,6 +60,7 @@ _SIGNATURES = {
     "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
     "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
     "asvrl_linear_tf32x3": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_long, C.c_int, C.c_int, f32p, C.c_void_p]),
+    "asvrl_linear_tf32x3_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_actor_head": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, f32p, C.c_float, C.POINTER(C.c_float * 2),
                                    C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_int, C.c_int, f32p, vp]),
     "asvrl_policy_forward_workspace": (C.c_long, []),
@@ -452,6 +453,15 @@ def policy_forward_status():
     check(lib().asvrl_policy_forward_status(C.byref(v)), "asvrl_policy_forward_status")
     if v.value != 0:
         raise RuntimeError(f"asvrl_policy_forward: device pipeline fault, status {v.value}")
+    return 0
+
+
+def linear_tf32x3_status():
+    """Synchronous read of K8's device status word; raises when a bounded wait on the tensor pipe expired."""
+    v = C.c_int(0)
+    check(lib().asvrl_linear_tf32x3_status(C.byref(v)), "asvrl_linear_tf32x3_status")
+    if v.value != 0:
+        raise RuntimeError(f"asvrl_linear_tf32x3: device pipeline fault, status {v.value}")
     return 0
 
 

@@ -53,12 +53,16 @@ __device__ __forceinline__ void lu_mma(uint32_t tmem_d, uint64_t adesc, uint64_t
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
 }
 
+// device status word of K8 (0 = ok), read back by asvrl_linear_tf32x3_status: a wait that expires is reported
+// there — the launch finishes with unspecified output instead of hanging or killing the caller's context
+static __device__ int lu_status_word = 0;
+
 __device__ __forceinline__ void lu_wait(uint32_t mbar, uint32_t parity) {
   uint32_t done = 0;
   for (int it = 0; it < (1 << 26) && !done; ++it)
     asm volatile("{\n\t.reg .pred P;\n\tmbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\tselp.u32 %0, 1, 0, P;\n\t}\n"
                  : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
-  if (!done) __trap();  // an MMA that never completes is a programming error: fail loudly, do not hang
+  if (!done) atomicCAS(&lu_status_word, 0, 4 /* UM_TIMEOUT_K8 */);  // an MMA that never completes: reported, not trapped
 }
 
 // split + swizzled store of one 16-byte chunk (row r, chunk c of the atom)
@@ -218,4 +222,12 @@ extern "C" int asvrl_linear_tf32x3(const float* x, const float* w, const float* 
   if (out_dim <= 64) return launch(linear_tf32x3_kernel<64>);
   if (out_dim <= 128) return launch(linear_tf32x3_kernel<128>);
   return launch(linear_tf32x3_kernel<256>);
+}
+
+// synchronous read of K8's device status word (0 = every bounded wait completed)
+extern "C" int asvrl_linear_tf32x3_status(int* status_out) {
+  if (!status_out) return fail(ASVRL_E_BADARG, "asvrl_linear_tf32x3_status: null pointer");
+  cudaError_t e = cudaMemcpyFromSymbol(status_out, lu_status_word, sizeof(int));
+  if (e != cudaSuccess) return fail((int)e, "asvrl_linear_tf32x3_status: %s", cudaGetErrorString(e));
+  return 0;
 }

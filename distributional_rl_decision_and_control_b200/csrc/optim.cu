@@ -12,6 +12,8 @@
 // grad_scale = 1 / world_size when the gradients were SUMMED by the all-reduce.  Bound: HBM, 16 B
 // read + 12 B written per parameter; at the 67 249 + 50 354 parameters of AC-IQN it is launch
 // latency.  The sum of squares is reduced per CTA and then by the last CTA in a fixed order.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace asvrl {
@@ -33,6 +35,8 @@ struct AdamList {
   int n_chunks;
 };
 
+constexpr int P2P_FAULT_WORD = ASVRL_MAX_PEERS;  // flag word after the per-rank epochs: sticky "a rank timed out"
+
 struct PeerList {
   int world, rank;
   float* bucket[ASVRL_MAX_PEERS];   // every rank's symmetric buffer: [half 0 | half 1 | flag words]
@@ -52,7 +56,7 @@ __device__ __forceinline__ int chunk_tensor(const AdamList& L, int c, long long&
 __global__ void __launch_bounds__(OPT_TPB)
 grad_norm_kernel(const __grid_constant__ AdamList L, float max_norm, float lr, float beta1, float beta2,
                  float grad_scale, float* __restrict__ norm_out,
-                 float* __restrict__ scal, float* __restrict__ part, uint32_t* counter) {
+                 float* __restrict__ scal, float* __restrict__ part, float* __restrict__ skipped, uint32_t* counter) {
   float acc = 0.0f;
   for (int c = blockIdx.x; c < L.n_chunks; c += gridDim.x) {
     long long first;
@@ -82,20 +86,26 @@ grad_norm_kernel(const __grid_constant__ AdamList L, float max_norm, float lr, f
   __syncthreads();
   if (!is_last) return;
   __threadfence();
+  __shared__ bool good;
+  if (threadIdx.x == 0) {
+    float total = 0.0f;
+    for (int g = 0; g < (int)gridDim.x; ++g) total += __ldcg(part + g);
+    const float norm = sqrtf(total) * grad_scale;
+    const float clip = fminf(max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max=1.0)
+    if (norm_out) norm_out[0] = norm;
+    good = norm <= 3.0e38f;
+    scal[0] = good ? clip * grad_scale : __int_as_float(0x7fc00000);  // fminf drops a NaN: keep it
+    if (!good) skipped[0] += 1.0f;  // sticky evidence for ClipAdam.check(): this step changed nothing
+    *counter = 0u;
+  }
+  __syncthreads();
+  if (!good) return;  // a skipped step advances neither the moments nor the step counts
   for (int t = threadIdx.x; t < L.n; t += OPT_TPB) {  // a tensor without gradient is not in the list: its t stays
     const float tt = *L.step[t] + 1.0f;
     *L.step[t] = tt;
     scal[1 + 2 * t] = lr / (1.0f - powf(beta1, tt));
     scal[2 + 2 * t] = 1.0f / sqrtf(1.0f - powf(beta2, tt));
   }
-  if (threadIdx.x != 0) return;
-  float total = 0.0f;
-  for (int g = 0; g < (int)gridDim.x; ++g) total += __ldcg(part + g);
-  const float norm = sqrtf(total) * grad_scale;
-  const float clip = fminf(max_norm / (norm + 1e-6f), 1.0f);  // clip_grad_norm_: clamp(max=1.0)
-  if (norm_out) norm_out[0] = norm;
-  scal[0] = norm <= 3.0e38f ? clip * grad_scale : __int_as_float(0x7fc00000);  // fminf drops a NaN: keep it
-  *counter = 0u;
 }
 
 __global__ void __launch_bounds__(OPT_TPB)
@@ -145,7 +155,8 @@ adam_kernel(const __grid_constant__ AdamList L, float beta1, float beta2, float 
 //   launch 3  adam_kernel on grad_sum with grad_scale = 1 / world folded into the clip factor
 // Double buffering by epoch parity makes the reuse safe: a rank can write half (e & 1) again only
 // after its step e+1 saw every peer's flag e+1, which each peer sets after finishing step e.
-// A wait that exceeds ~2^26 polls gives up and poisons the norm with NaN instead of hanging.
+// A wait that exceeds ~2^26 polls gives up, poisons the norm with NaN instead of hanging, and raises a sticky
+// fault word in every rank's buffer so that all replicas skip from then on (never a silent divergence).
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
@@ -190,19 +201,29 @@ __global__ void __launch_bounds__(OPT_TPB)
 grad_norm_p2p_kernel(const __grid_constant__ AdamList L, const __grid_constant__ PeerList P, float max_norm,
                      float lr, float beta1, float beta2, float grad_scale, uint32_t* epoch_dev,
                      float* __restrict__ grad_sum, float* __restrict__ norm_out, float* __restrict__ scal,
-                     float* __restrict__ part, uint32_t* counter) {
+                     float* __restrict__ part, float* __restrict__ skipped, uint32_t* counter, uint32_t max_polls) {
   const uint32_t e = *epoch_dev + 1u;
   __shared__ int timed_out;
   if (threadIdx.x == 0) timed_out = 0;
   __syncthreads();
+  const uint32_t* my_flags = (const uint32_t*)(P.bucket[P.rank] + 2 * P.half);
   if ((int)threadIdx.x < P.world) {  // one thread per peer flag
-    const uint32_t* flag = (const uint32_t*)(P.bucket[P.rank] + 2 * P.half) + threadIdx.x;
+    const uint32_t* flag = my_flags + threadIdx.x;
     unsigned polls = 0;
     while ((int)(ld_acquire_sys(flag) - e) < 0) {
-      if (++polls > (1u << 26)) { timed_out = 1; break; }
+      if (++polls > max_polls) { timed_out = 1; break; }
       __nanosleep(64);
     }
   }
+  __syncthreads();
+  // A rank that gave up waiting raises the STICKY fault word in every rank's buffer (its own included): this
+  // step and every later one is skipped on every rank that sees it, so the replicas cannot drift apart
+  // silently — ClipAdam.check() turns the word into an error.  (A late peer reads the word after its own
+  // pack + wait, long after the timeout that raised it.)
+  if (timed_out && (int)threadIdx.x < P.world)
+    st_release_sys((uint32_t*)(P.bucket[threadIdx.x] + 2 * P.half) + P2P_FAULT_WORD, 1u);
+  __shared__ int faulted;
+  if (threadIdx.x == 0) faulted = timed_out || ld_acquire_sys(my_flags + P2P_FAULT_WORD) != 0u;
   __syncthreads();
   const long long base = (long long)(e & 1u) * P.half;
   float acc = 0.0f;
@@ -221,7 +242,7 @@ grad_norm_p2p_kernel(const __grid_constant__ AdamList L, const __grid_constant__
       }
     }
   }
-  if (timed_out) acc = __int_as_float(0x7fc00000);  // NaN: visible in norm_out, no hang
+  if (faulted) acc = __int_as_float(0x7fc00000);  // NaN: visible in norm_out, no hang
   __shared__ float sm[OPT_TPB];
   __shared__ bool is_last;
   sm[threadIdx.x] = acc;
@@ -238,21 +259,27 @@ grad_norm_p2p_kernel(const __grid_constant__ AdamList L, const __grid_constant__
   __syncthreads();
   if (!is_last) return;
   __threadfence();
+  __shared__ bool good;
+  if (threadIdx.x == 0) {
+    float total = 0.0f;
+    for (int g = 0; g < (int)gridDim.x; ++g) total += __ldcg(part + g);
+    const float norm = sqrtf(total) * grad_scale;
+    const float clip = fminf(max_norm / (norm + 1e-6f), 1.0f);
+    if (norm_out) norm_out[0] = norm;
+    good = norm <= 3.0e38f;
+    scal[0] = good ? clip * grad_scale : __int_as_float(0x7fc00000);  // fminf drops a NaN: keep it
+    if (!good) skipped[0] += 1.0f;
+    *epoch_dev = e;  // every CTA has read the old value (they all arrived at the counter); the exchange stays in lock step
+    *counter = 0u;
+  }
+  __syncthreads();
+  if (!good) return;  // a skipped step advances neither the moments nor the step counts
   for (int t = threadIdx.x; t < L.n; t += OPT_TPB) {
     const float tt = *L.step[t] + 1.0f;
     *L.step[t] = tt;
     scal[1 + 2 * t] = lr / (1.0f - powf(beta1, tt));
     scal[2 + 2 * t] = 1.0f / sqrtf(1.0f - powf(beta2, tt));
   }
-  if (threadIdx.x != 0) return;
-  float total = 0.0f;
-  for (int g = 0; g < (int)gridDim.x; ++g) total += __ldcg(part + g);
-  const float norm = sqrtf(total) * grad_scale;
-  const float clip = fminf(max_norm / (norm + 1e-6f), 1.0f);
-  if (norm_out) norm_out[0] = norm;
-  scal[0] = norm <= 3.0e38f ? clip * grad_scale : __int_as_float(0x7fc00000);  // fminf drops a NaN: keep it
-  *epoch_dev = e;  // every CTA has read the old value (they all arrived at the counter)
-  *counter = 0u;
 }
 
 }  // namespace asvrl
@@ -303,7 +330,7 @@ extern "C" int asvrl_clip_adam_step(const asvrl_adam_tensors* tensors, float max
   float* scal = scratch;                                     // [1 + 2 * ASVRL_OPT_MAX_TENSORS]
   float* part = scratch + 1 + 2 * ASVRL_OPT_MAX_TENSORS;     // [OPT_GRID]
   grad_norm_kernel<<<grid, OPT_TPB, 0, s>>>(L, max_norm, lr, beta1, beta2, grad_scale, norm_out, scal,
-                                            part, counter);
+                                            part, scratch + ASVRL_OPT_SCRATCH_FLOATS - 1, counter);
   adam_kernel<<<grid, OPT_TPB, 0, s>>>(L, beta1, beta2, eps, scal);
   return check_launch("asvrl_clip_adam_step");
 }
@@ -334,8 +361,14 @@ extern "C" int asvrl_clip_adam_step_p2p(const asvrl_adam_tensors* tensors, const
   float* scal = scratch;
   float* part = scratch + 1 + 2 * ASVRL_OPT_MAX_TENSORS;
   pack_signal_kernel<<<grid, OPT_TPB, 0, s>>>(L, P, epoch, counter);
+  uint32_t max_polls = 1u << 26;  // ~4 s at 64 ns per poll; ASVRL_P2P_TIMEOUT_POLLS overrides (tests)
+  if (const char* env = getenv("ASVRL_P2P_TIMEOUT_POLLS")) {
+    const long v = atol(env);
+    if (v > 0 && v < 0x7fffffffL) max_polls = (uint32_t)v;
+  }
   grad_norm_p2p_kernel<<<grid, OPT_TPB, 0, s>>>(L, P, max_norm, lr, beta1, beta2, grad_scale, epoch, grad_sum,
-                                                norm_out, scal, part, counter);
+                                                norm_out, scal, part, scratch + ASVRL_OPT_SCRATCH_FLOATS - 1,
+                                                counter, max_polls);
   AdamList LA = L;  // Adam reads the all-reduced sum
   for (int t = 0; t < LA.n; ++t) LA.grad[t] = grad_sum + LA.off[t];
   adam_kernel<<<grid, OPT_TPB, 0, s>>>(LA, beta1, beta2, eps, scal);

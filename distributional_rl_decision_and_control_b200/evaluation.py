@@ -60,6 +60,12 @@ class BatchedEvaluator:
             if c:
                 self.frozen["cores"][e, :c] = st["cores"][0, :c]
             self.frozen["n_robots"][e], self.frozen["n_obs"][e], self.frozen["n_cores"][e] = r, o, c
+        # WAMV:161-165: energy = power_coefficient * (|T_l| + |T_r|) * dt * N, the coefficient per robot of the config
+        pc = torch.ones((self.E, self.RP), dtype=torch.float32)
+        for e, cfg in enumerate(self.configs):
+            vals = cfg["robots"].get("power_coefficient", [])
+            pc[e, :len(vals)] = torch.tensor(vals, dtype=torch.float32)[:self.RP]
+        self.power_coefficient = pc.to(self.device)
         self.dt_hold = float(self.params.dt * self.params.n_substeps)
         torch.cuda.synchronize(self.device)
 
@@ -102,7 +108,7 @@ class BatchedEvaluator:
                 act_f = active.to(torch.float32)
                 rewards += disc * self.out["reward"] * act_f
                 times += self.dt_hold * act_f
-                energies += (self.state["thrust_l"].abs() + self.state["thrust_r"].abs()) * self.dt_hold * act_f
+                energies += self.power_coefficient * (self.state["thrust_l"].abs() + self.state["thrust_r"].abs()) * self.dt_hold * act_f
                 if self.record:
                     traj.append(torch.stack([self.state[k] for k in ("x", "y", "theta", "velr_x", "velr_y", "velr_r",
                                                                       "vel_x", "vel_y", "vel_r", "thrust_l", "thrust_r")],

@@ -79,12 +79,19 @@ class ClipAdam:
         self._peers = peers
 
     def check(self):
-        """Host-side health check (one device read): the last step's gradient norm must be finite.  A NaN
-        means a non-finite gradient or — on the peer-memory path — a rank that never arrived at the
-        exchange; either way K7 skipped the parameter update of that step."""
-        if not bool(torch.isfinite(self.grad_norm).all()):
-            raise RuntimeError("ClipAdam: non-finite gradient norm (diverged gradients, or a rank missed the "
-                               "gradient exchange: all ranks must step in lock step)")
+        """Host-side health check (one device read): no step since construction may have been skipped.  K7
+        skips a step (parameters, moments and step counts untouched) on a non-finite gradient norm or — on
+        the peer-memory path — when a rank never arrived at the exchange; it counts skipped steps in the last
+        scratch float, and a missed exchange raises a sticky fault word on every rank (include/asvrl.h), so
+        a fault in the middle of an interval is still seen here."""
+        bad = ~torch.isfinite(self.grad_norm).all() | (self._scratch[-1] != 0)
+        if self._peers is not None:  # sticky fault word of the peer-memory exchange (a rank timed out)
+            bad = bad | (self._bucket[2 * self._peers.half_floats + _abi.MAX_PEERS] != 0)
+        if bool(bad):
+            raise RuntimeError("ClipAdam: %d optimiser step(s) were skipped (non-finite gradient norm: diverged "
+                               "gradients, or a rank missed the gradient exchange — all ranks must step in lock "
+                               "step; after a missed exchange every rank skips every later step)"
+                               % int(self._scratch[-1].item()))
 
     def zero_grad(self, set_to_none=True):
         for p in self.params:

@@ -94,10 +94,13 @@ class ReplayBuffer:
             total = int(hs[0].item())
             pos = total % cap
             src = self._stage[:n].to(self.device, non_blocking=True)
-            first = min(n, cap - pos)
-            self.ring["rows"][pos:pos + first].copy_(src[:first])
-            if first < n:
-                self.ring["rows"][0:n - first].copy_(src[first:n])
+            skip = max(0, n - cap)  # more staged rows than the ring holds: keep the newest `cap`, as deque(maxlen) does
+            pos = (pos + skip) % cap
+            keep = n - skip
+            first = min(keep, cap - pos)
+            self.ring["rows"][pos:pos + first].copy_(src[skip:skip + first])
+            if first < keep:
+                self.ring["rows"][0:keep - first].copy_(src[skip + first:n])
             hs[0] = total + n
             hs[1] = min(total + n, cap)
             torch.cuda.current_stream().synchronize()  # the pinned stage is reused right away
@@ -126,6 +129,12 @@ class ReplayBuffer:
         {self, obj, mask, act, rew, nself, nobj, nmask, done, indices}."""
         self.flush()
         batch = self._batch if batch is None else batch
+        if self.counter_dev is None and indices is None:
+            # eager path (one host read, like size()): random.sample raises when the population is smaller than
+            # the sample (RB:28); under a captured graph the caller checks readiness before capturing
+            have = int(self.ring["head_size"][1].item())
+            if batch > have:
+                raise ValueError(f"Sample larger than population: batch {batch} > {have} stored transitions")
         self.draws += 1
         with torch.cuda.device(self.device):
             return _lib.replay_sample(self.ring, batch, seed=self.rng_seed, counter=self.draws,

@@ -148,7 +148,15 @@ class VectorTrainer:
                 since_update = 0
                 if not self._buffer_ready:  # one host sync until the ring holds a batch (TRAINER:186)
                     have = agent.memory.transitions.num_elements() if self.rainbow else agent.memory.size()
-                    self._buffer_ready = have > agent.BATCH_SIZE and (not self.rainbow or agent.memory.filled > agent.memory.n + 1)
+                    ready = have > agent.BATCH_SIZE and (not self.rainbow or agent.memory.filled > agent.memory.n + 1)
+                    pg = getattr(agent, "process_group", None)
+                    if pg is not None:
+                        # every rank enters the gradient exchange in the same round: ready = MIN over ranks
+                        import torch.distributed as dist
+                        flag = torch.tensor([1 if ready else 0], dtype=torch.int32, device=env.device)
+                        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=pg)
+                        ready = bool(flag.item())
+                    self._buffer_ready = ready
                 if self._buffer_ready and self.cuda_graph and agent._graph is None and not self.rainbow:
                     agent.enable_cuda_graph()
                 if self._buffer_ready:

@@ -462,7 +462,11 @@ ASVRL_API int asvrl_clip_adam_step(const asvrl_adam_tensors* tensors, float max_
  * half_floats floats per half, zero-initialised before the first call on any rank.  grad_sum:
  * local scratch of the summed gradient (>= total floats); epoch: device uint32, zero-initialised,
  * advanced by every call (all ranks must call in lock step).  A peer that never arrives makes the
- * wait give up after ~2^26 polls and norm_out read NaN (no hang). */
+ * wait give up after ~2^26 polls (environment ASVRL_P2P_TIMEOUT_POLLS overrides) and norm_out read NaN (no
+ * hang); the rank that gave up raises flag word ASVRL_MAX_PEERS (sticky) in EVERY rank's buffer, and a rank
+ * that finds it set skips the step too — from then on every step is skipped on every rank, so replicas never
+ * drift apart silently.  A skipped step (here and in asvrl_clip_adam_step: NaN / inf norm) leaves parameters,
+ * moments and step counts untouched and adds 1 to scratch[ASVRL_OPT_SCRATCH_FLOATS - 1]. */
 #define ASVRL_MAX_PEERS 8
 typedef struct asvrl_peer_buckets {
   int world, rank;
@@ -494,6 +498,9 @@ ASVRL_API int asvrl_actor_head(const float* pre, const float* bias, const float*
  * (the collection path, torch.no_grad). */
 ASVRL_API int asvrl_linear_tf32x3(const float* x, const float* w, const float* bias, int relu, long rows,
                                   int in_dim, int out_dim, float* out, void* stream);
+/* Synchronous read of K8's device status word: 0, or a non-zero code when a bounded wait on the tensor pipe
+ * expired in some launch since the library was loaded (that launch's output is unspecified; nothing traps). */
+ASVRL_API int asvrl_linear_tf32x3_status(int* status_out);
 
 /* K9 — the whole collection policy forward of the AC-IQN / DDPG actor for `rows` ASVs in ONE persistent launch:
  * encoders + mask + concat (ACIQN:284-308), hidden_layer / hidden_layer_2 with ReLU (ACIQN:315-316) on the tcgen05

@@ -62,7 +62,7 @@ def test_policy_forward_matches_float64_actor(M):
     plain.fused_tower = False
     err32 = (plain(x).double() - want).abs().max().item()
     err = (got.double() - want).abs().max().item()
-    assert err <= max(ATOL, 2.0 * err32), f"greedy actions, rescaled weights: max abs err {err:.3e} (fp32 modules: {err32:.3e})"
+    assert err <= max(ATOL, 4.0 * err32), f"greedy actions, rescaled weights: max abs err {err:.3e} (fp32 modules: {err32:.3e})"
     _lib.policy_forward_status()
 
 

@@ -174,7 +174,7 @@ def test_bench_reference_arm_contract():
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cmd = [sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "3", "--warmup", "1",
-           "--cpu-envs", "64"]
+           "--envs", "64"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, RANK="0", WORLD_SIZE="1"))
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
@@ -185,6 +185,12 @@ def test_bench_reference_arm_contract():
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"]
+    # the workload description is the one the b200 arm prints (same function): the driver's same_config check
+    sys.path.insert(0, root)
+    import bench
+    assert d["config"] == bench.workload_config(64, 8, 1, True)
+    assert d["config"]["auto_deactivate"] and d["config"]["auto_reset"]
+    assert all(len(v) <= 128 for v in d["config"].values() if isinstance(v, str))  # the driver's record truncates longer strings
     assert cb["learner"]["c3_B1024_N32"]["updates_per_sec"] > 0 and cb["learner"]["ref_B64_N8"]["updates_per_sec"] > 0
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=60, env=dict(os.environ, RANK="1", WORLD_SIZE="2"))
     assert r.returncode == 0 and r.stdout.strip() == ""

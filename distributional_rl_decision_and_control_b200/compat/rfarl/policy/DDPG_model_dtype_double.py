@@ -1,0 +1,1 @@
+from distributional_rl_decision_and_control_b200.policy.DDPG_model_dtype_double import Actor  # noqa: F401

@@ -88,10 +88,13 @@ class ClipAdam:
         if self._peers is not None:  # sticky fault word of the peer-memory exchange (a rank timed out)
             bad = bad | (self._bucket[2 * self._peers.half_floats + _abi.MAX_PEERS] != 0)
         if bool(bad):
+            n = int(self._scratch[-1].item())
+            self._scratch[-1] = 0  # reported once: a caller that catches this and carries on is told about NEW skips only
+            self.grad_norm.zero_()  # (the peer-memory fault word stays raised: that exchange cannot be resumed)
             raise RuntimeError("ClipAdam: %d optimiser step(s) were skipped (non-finite gradient norm: diverged "
                                "gradients, or a rank missed the gradient exchange — all ranks must step in lock "
                                "step; after a missed exchange every rank skips every later step)"
-                               % int(self._scratch[-1].item()))
+                               % n)
 
     def zero_grad(self, set_to_none=True):
         for p in self.params:

@@ -133,8 +133,9 @@ class ReplayBuffer:
             # eager path (one host read, like size()): random.sample raises when the population is smaller than
             # the sample (RB:28); under a captured graph the caller checks readiness before capturing
             have = int(self.ring["head_size"][1].item())
-            if batch > have:
-                raise ValueError(f"Sample larger than population: batch {batch} > {have} stored transitions")
+            want = batch if isinstance(batch, int) else int(batch["self"].shape[0])  # a dict of preallocated outputs
+            if want > have:
+                raise ValueError(f"Sample larger than population: batch {want} > {have} stored transitions")
         self.draws += 1
         with torch.cuda.device(self.device):
             return _lib.replay_sample(self.ring, batch, seed=self.rng_seed, counter=self.draws,

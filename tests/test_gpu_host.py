@@ -322,3 +322,45 @@ def test_batched_evaluation_matches_sequential(tmp_path, capsys):
     assert np.allclose(tr2.eval_rewards[-1], res["rewards"], rtol=1e-6)
     tr2.save_evaluation(str(tmp_path))
     assert "evaluations.npz" in os.listdir(tmp_path)
+
+
+def _reference_eval_golden():
+    import json
+    with open(os.path.join(gu.GOLD, "eval_reference.json")) as f:
+        g = json.load(f)
+    w = np.load(os.path.join(gu.GOLD, "traced_ac_iqn.npz"))
+    return g, {k[2:]: torch.from_numpy(w[k]) for k in w.files if k.startswith("w.")}
+
+
+@pytest.mark.parametrize("batched", [True, False])
+def test_evaluation_matches_the_reference_trainer(batched, capsys):
+    """`Trainer.evaluation` of the REFERENCE (TRAINER:266-392; golden made by oracle/gen_golden_eval.py from the
+    unmodified reference with its shipped trained AC-IQN policy, noise-free frozen scenarios): success flags and
+    episode lengths exact, travel time exact, discounted reward and energy to 1e-4, final poses to 1e-3 m —
+    for the vectorised evaluator (one device batch) and for the sequential Trainer over the facade."""
+    from distributional_rl_decision_and_control_b200.evaluation import BatchedEvaluator
+    g, weights = _reference_eval_golden()
+    agent = Agent(device=DEV, seed=100, agent_type="AC-IQN", BUFFER_SIZE=1000)
+    agent.policy_local.actor.load_state_dict(weights)
+    want = g["results"]
+    if batched:
+        res = BatchedEvaluator(g["eval_configs"], device=DEV, seed=253).run(agent)
+        traj = res["trajectories"]
+    else:
+        sched = {"timesteps": [0], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+        ev = {"num_episodes": [0], "num_robots": [3], "num_cores": [0], "num_obstacles": [0], "min_start_goal_dis": [30.0]}
+        tr = Trainer(train_env=MarineNavEnv3(seed=0, schedule=sched, device=DEV),
+                     eval_env=MarineNavEnv3(seed=253, is_eval_env=True, device=DEV), eval_schedule=ev, rl_agent=agent)
+        tr.eval_config = g["eval_configs"]
+        tr.evaluation()
+        capsys.readouterr()
+        res = {k: getattr(tr, "eval_" + k)[-1] for k in ("rewards", "successes", "times", "energies")}
+        traj = tr.eval_trajectories[-1]
+    assert [bool(x) for x in res["successes"]] == [w["success"] for w in want]
+    assert [[len(t) for t in ep] for ep in traj] == [w["lengths"] for w in want]
+    assert np.allclose(res["times"], [w["time"] for w in want], rtol=1e-6)
+    assert np.allclose(res["rewards"], [w["reward"] for w in want], rtol=1e-4, atol=1e-4)
+    assert np.allclose(res["energies"], [w["energy"] for w in want], rtol=1e-4)
+    for ep, w in zip(traj, want):
+        for t, fp in zip(ep, w["final_pose"]):
+            assert np.allclose(t[-1][:2], fp[:2], atol=1e-3), (t[-1][:3], fp)

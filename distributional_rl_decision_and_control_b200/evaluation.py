@@ -94,6 +94,9 @@ class BatchedEvaluator:
         running = torch.ones((E,), dtype=torch.bool, device=dev)
         lengths = torch.zeros((E,), dtype=torch.int32, device=dev)
         traj, acts = [], []
+        _row = lambda: torch.stack([self.state[k] for k in ("x", "y", "theta", "velr_x", "velr_y", "velr_r", "vel_x",
+                                                            "vel_y", "vel_r", "thrust_l", "thrust_r")], dim=-1).cpu()
+        first_row = _row() if self.record else None  # the reset row every rob.trajectory starts with (WAMV:191-193)
         disc = 1.0
         try:
             for length in range(self.max_steps + 1):  # TRAINER:344: `length >= 1000` is tested after the step
@@ -110,9 +113,7 @@ class BatchedEvaluator:
                 times += self.dt_hold * act_f
                 energies += self.power_coefficient * (self.state["thrust_l"].abs() + self.state["thrust_r"].abs()) * self.dt_hold * act_f
                 if self.record:
-                    traj.append(torch.stack([self.state[k] for k in ("x", "y", "theta", "velr_x", "velr_y", "velr_r",
-                                                                      "vel_x", "vel_y", "vel_r", "thrust_l", "thrust_r")],
-                                            dim=-1).cpu())
+                    traj.append(_row())
                     acts.append((a.to(torch.float32).cpu(), active.cpu()))
                 es = self.out["env_status"]
                 ended = ((es & 1) != 0) | ((es & 4) != 0) | (length >= self.max_steps)
@@ -133,12 +134,13 @@ class BatchedEvaluator:
                "energies": (energies.sum(1) / n_rob).cpu().numpy().tolist(),
                "lengths": lengths.cpu().numpy().tolist()}
         if self.record:
-            res["trajectories"], res["actions"] = self._histories(traj, acts, lengths.cpu().numpy())
+            res["trajectories"], res["actions"] = self._histories(first_row, traj, acts, lengths.cpu().numpy())
         return res
 
-    def _histories(self, traj, acts, lengths):
-        """[E][R] python lists shaped like the reference's rob.trajectory / rob.action_history
-        (thruster angles, columns 9-10 of WAMV:191-193, are the constant 0 of training)."""
+    def _histories(self, first_row, traj, acts, lengths):
+        """[E][R] python lists shaped like the reference's rob.trajectory / rob.action_history: the reset row, then
+        one row per step the robot was active in; one action per step (thruster angles, columns 9-10 of
+        WAMV:191-193, are the constant 0 of training)."""
         nr = self.state["n_robots"].cpu().numpy()
         T = np.stack([t.numpy() for t in traj])                       # (steps, E, RP, 11)
         A = np.stack([a.numpy() for a, _ in acts])
@@ -147,7 +149,8 @@ class BatchedEvaluator:
         for e in range(self.E):
             te, ae = [], []
             for r in range(int(nr[e])):
-                rows, al = [], []
+                v0 = first_row[e, r].numpy()
+                rows, al = [[float(x) for x in v0[:9]] + [0.0, 0.0] + [float(v0[9]), float(v0[10])]], []
                 for s in range(int(lengths[e])):
                     if M[s, e, r]:
                         v = T[s, e, r]

@@ -310,7 +310,7 @@ def test_batched_evaluation_matches_sequential(tmp_path, capsys):
     assert np.allclose(res["energies"], seq["energies"], rtol=5e-3)
     # recorded histories have the reference's row layout (13 columns, WAMV:191-193)
     t0 = res["trajectories"][0][0]
-    assert len(t0[0]) == 13 and len(res["actions"][0][0]) == len(t0)
+    assert len(t0[0]) == 13 and len(res["actions"][0][0]) == len(t0) - 1  # the reset row has no action
     assert np.allclose(t0[-1][:3], seq["trajectories"][0][0][-1][:3], atol=2e-2)
     s = summarize(res)
     assert 0.0 <= s["success_rate"] <= 1.0 and np.isfinite(s["avg_reward"])
@@ -332,17 +332,52 @@ def _reference_eval_golden():
     return g, {k[2:]: torch.from_numpy(w[k]) for k in w.files if k.startswith("w.")}
 
 
+class _ReplayPolicy:
+    """Stands in for the Agent during evaluation and hands out the actions the REFERENCE's policy took (teacher
+    forcing).  Serves both call styles: act_batch (the vectorised evaluator; one (E, R, 2) tensor per step) and
+    act_ac_iqn (the sequential Trainer: robots in index order, deactivated robots skipped)."""
+    agent_type, GAMMA, training = "AC-IQN", 0.99, False
+
+    def __init__(self, results, gamma, RP):
+        self.GAMMA = gamma
+        self.policy_local = torch.nn.Module()
+        self.results, self.RP, self.step = results, RP, 0
+        self.flat = []
+        for w in results:  # sequential order: scenario, step, robot (only robots that still act at that step)
+            acts = w["actions"]
+            for s in range(max(len(a) for a in acts)):
+                self.flat.extend(a[s] for a in acts if s < len(a))
+        self.flat_pos = 0
+
+    def act_batch(self, obs, eps=0.0):
+        out = torch.zeros((len(self.results), self.RP, 2), dtype=torch.float32)
+        for e, w in enumerate(self.results):
+            for r, a in enumerate(w["actions"]):
+                if self.step < len(a):
+                    out[e, r] = torch.tensor(a[self.step])
+        self.step += 1
+        return out.to(obs[0].device).view(-1, 2)
+
+    def act_ac_iqn(self, state, eps=0.0, use_eval=True):
+        a = self.flat[self.flat_pos]
+        self.flat_pos += 1
+        return list(a)
+
+
 @pytest.mark.parametrize("batched", [True, False])
 def test_evaluation_matches_the_reference_trainer(batched, capsys):
     """`Trainer.evaluation` of the REFERENCE (TRAINER:266-392; golden made by oracle/gen_golden_eval.py from the
-    unmodified reference with its shipped trained AC-IQN policy, noise-free frozen scenarios): success flags and
-    episode lengths exact, travel time exact, discounted reward and energy to 1e-4, final poses to 1e-3 m —
-    for the vectorised evaluator (one device batch) and for the sequential Trainer over the facade."""
+    unmodified reference playing its shipped trained AC-IQN policy on noise-free frozen scenarios).  The recorded
+    actions are replayed (teacher forcing — a closed loop around a trained, nearly bang-bang policy amplifies a
+    1e-7 difference to metres within ~20 steps, see the generator), so what is compared is everything the
+    evaluation itself computes: end rule and success flags and every robot's episode length exact, travel time
+    exact, discounted reward and energy to 1e-4, final poses to 1e-3 m — for the vectorised evaluator (one device
+    batch) and for the sequential Trainer over the facade."""
     from distributional_rl_decision_and_control_b200.evaluation import BatchedEvaluator
-    g, weights = _reference_eval_golden()
-    agent = Agent(device=DEV, seed=100, agent_type="AC-IQN", BUFFER_SIZE=1000)
-    agent.policy_local.actor.load_state_dict(weights)
+    g, _ = _reference_eval_golden()
     want = g["results"]
+    RP = max(len(w["actions"]) for w in want)
+    agent = _ReplayPolicy(want, g["gamma"], RP)
     if batched:
         res = BatchedEvaluator(g["eval_configs"], device=DEV, seed=253).run(agent)
         traj = res["trajectories"]
@@ -354,6 +389,7 @@ def test_evaluation_matches_the_reference_trainer(batched, capsys):
         tr.eval_config = g["eval_configs"]
         tr.evaluation()
         capsys.readouterr()
+        assert agent.flat_pos == len(agent.flat)  # every recorded action was asked for, in the reference's order
         res = {k: getattr(tr, "eval_" + k)[-1] for k in ("rewards", "successes", "times", "energies")}
         traj = tr.eval_trajectories[-1]
     assert [bool(x) for x in res["successes"]] == [w["success"] for w in want]
@@ -364,3 +400,28 @@ def test_evaluation_matches_the_reference_trainer(batched, capsys):
     for ep, w in zip(traj, want):
         for t, fp in zip(ep, w["final_pose"]):
             assert np.allclose(t[-1][:2], fp[:2], atol=1e-3), (t[-1][:3], fp)
+
+
+def test_policy_on_the_reference_evaluation_observations():
+    """The other half of the evaluation parity: the observations the reference's robots saw (first robot of every
+    golden scenario, first steps) -> the actions its policy took, through this package's Agent (K9 for the batch
+    call, the batch-1 act_ac_iqn of the sequential path), to 5e-5 (trained weights: float32 modules are ~2e-5 away)."""
+    g, weights = _reference_eval_golden()
+    agent = Agent(device=DEV, seed=100, agent_type="AC-IQN", BUFFER_SIZE=1000)
+    agent.policy_local.actor.load_state_dict(weights)
+    states, want = [], []
+    for w in g["results"]:
+        for o, a in zip(w["obs_sample"], w["actions"][0]):
+            states.append((o[0], o[1]))
+            want.append(a)
+    got_seq = np.array([agent.act_ac_iqn(s) for s in states])
+    assert np.abs(got_seq - np.array(want)).max() <= 5e-5
+    self_b = torch.tensor([s[0] for s in states], device=DEV)
+    obj_b = torch.zeros((len(states), 5, 5), device=DEV)
+    mask_b = torch.zeros((len(states), 5), device=DEV)
+    for i, s in enumerate(states):
+        for k, ob in enumerate(s[1][:5]):
+            obj_b[i, k] = torch.tensor(ob, device=DEV)
+            mask_b[i, k] = 1.0
+    got_batch = agent.act_batch((self_b, obj_b, mask_b), 0.0).cpu().numpy()
+    assert np.abs(got_batch - np.array(want)).max() <= 5e-5

@@ -68,6 +68,11 @@ _SIGNATURES = {
                                        C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_long, C.c_int,
                                        vp, f32p, vp]),
     "asvrl_policy_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
+    "asvrl_critic_forward_workspace": (C.c_long, []),
+    "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
+    "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
+                             + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p, vp, vp, vp, vp, vp]),
+    "asvrl_critic_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_clip_adam_step_p2p": (C.c_int, [C.POINTER(_abi.AdamTensors), C.POINTER(_abi.PeerBuckets), f32p, u32p]
                                  + [C.c_float] * 5 + [f32p, f32p, u32p, vp]),
     "asvrl_clip_adam_step": (C.c_int, [C.POINTER(_abi.AdamTensors)] + [C.c_float] * 6 + [f32p, f32p, u32p, vp]),
@@ -453,6 +458,52 @@ def policy_forward_status():
     check(lib().asvrl_policy_forward_status(C.byref(v)), "asvrl_policy_forward_status")
     if v.value != 0:
         raise RuntimeError(f"asvrl_policy_forward: device pipeline fault, status {v.value}")
+    return 0
+
+
+# ------------------------------------------------------------------ K10: critic trunk forward on tcgen05
+_CRITIC_WS = {}
+
+
+def critic_workspace(key, device):
+    """The 256 KB packed weight image of one network (``key``: any hashable, e.g. id of the module)."""
+    ws = _CRITIC_WS.get((key, device))
+    if ws is None:
+        ws = _CRITIC_WS[(key, device)] = torch.empty((lib().asvrl_critic_forward_workspace(),), dtype=torch.uint8,
+                                                     device=device)
+    return ws
+
+
+def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspace, tau_in=None, seed=0, counter=0,
+                   counter_dev=None, cvar=1.0, repack=True, save=False):
+    """z (B, N), tau (B, N) [, images] of the IQN critic trunk in one persistent tcgen05 launch (K10).
+    ``save``: also return the operand images (cos, h1, h2, r3) the backward kernels read."""
+    B = feats.shape[0]
+    dev = feats.device
+    f = torch.float32
+    z = torch.empty((B, n_tau), dtype=f, device=dev)
+    tau = torch.empty((B, n_tau), dtype=f, device=dev) if tau_in is None else tau_in
+    imgs = (None, None, None, None)
+    if save:
+        tiles = (B * n_tau + 127) // 128
+        cb = lib().asvrl_critic_forward_chunk_bytes()
+        imgs = tuple(torch.empty((tiles, n, cb), dtype=torch.uint8, device=dev) for n in (1, 4, 2, 2))
+    rc = lib().asvrl_critic_forward(
+        ptr(tau_in, f), int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), ptr(counter_dev, torch.int64), float(cvar),
+        ptr(feats, f), ptr(aenc, f), ptr(wc, f), ptr(bc, f), ptr(wh, f), ptr(bh, f), ptr(wh2, f), ptr(bh2, f),
+        ptr(wo, f), ptr(bo, f), B, int(n_tau), int(bool(repack)), workspace.data_ptr(),
+        None if tau_in is not None else ptr(tau, f), ptr(z, f),
+        *[None if t is None else t.data_ptr() for t in imgs], stream_ptr())
+    check(rc, "asvrl_critic_forward")
+    return (z, tau, imgs) if save else (z, tau)
+
+
+def critic_forward_status():
+    """Synchronous read of K10's device status word; raises when a bounded wait of the pipeline expired."""
+    v = C.c_int(0)
+    check(lib().asvrl_critic_forward_status(C.byref(v)), "asvrl_critic_forward_status")
+    if v.value != 0:
+        raise RuntimeError(f"asvrl_critic_forward: device pipeline fault, status {v.value}")
     return 0
 
 

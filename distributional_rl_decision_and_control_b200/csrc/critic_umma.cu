@@ -1,0 +1,491 @@
+// critic_umma.cu — K10: the IQN critic's quantile trunk, forward, for all B*N quantile rows in ONE persistent,
+// warp-specialised launch (sm_100a: tcgen05.mma kind::f16, accumulators in TMEM, weights by TMA bulk copy,
+// mbarrier pipelines).  The cosine embedding input is generated in the operand loader: the (B, N, 64) table
+// of K3 never exists in HBM, and no activation leaves the SM.
+//
+// Replaces, per critic evaluation (reference: rfarl/rfarl/policy/AC_IQN_model.py),
+//   :410-426  calc_cos: tau ~ U(0,1) * cvar, cos(tau * pi * i), i < 64                      (K3)
+//   :453-460  x = features.unsqueeze(1) * relu(cos_embedding(cos))                           (GEMM + K5)
+//   :470-474  x = relu(hidden_layer(x)); x = action_encoder(a).unsqueeze(1) * x              (GEMM + K5)
+//   :476-480  x = relu(hidden_layer_2(x)); quantiles = output_layer(x)                       (GEMM + K5 head)
+// and, with aenc == nullptr, the same trunk of rfarl/rfarl/policy/IQN_model.py:74-86 up to the last hidden
+// layer.  7 launches and ~150 us at B*N = 32 768 become one.
+//
+// Arithmetic: as K9 — every operand is split in two fp16 pieces (22 mantissa bits), three products per K step
+// accumulate in fp32 in TMEM (x_lo W_hi + x_hi W_lo + x_hi W_hi), W pre-scaled by 2^6.  No clamping: an
+// activation beyond fp16's range gives a NaN quantile, which the caller's finiteness check reports.
+//
+// Mapping.  One CTA per SM walks 128-row tiles (tile = blockIdx.x + i * gridDim.x); even and odd tiles of a CTA
+// run in two SLOTS, each with its own 8 epilogue warps, two 32 KB operand buffers and 256 TMEM columns, so one
+// slot's CUDA-core work overlaps the other's tensor work.  20 warps:
+//   warp 0      W producer: one thread streams the packed weight chunks (32 KB = hi | lo tile of 128 out x 64 k)
+//               into a 3-stage ring with cp.async.bulk, in the MMA thread's consumption order
+//   warp 1      MMA issuer: one thread, 12 tcgen05.mma per chunk; static order per tile pair
+//               L1(A) L1(B) L2(A) L2(B) L3(A) L3(B)
+//   warp 2      TMEM allocation
+//   warps 4-11  slot 0, warps 12-19 slot 1: warp e of a slot owns TMEM lanes 32 (e % 4) .. and the column half
+//               e / 4.  Per tile: E0 tau -> cos -> A chunk; E1 D1 -> feats * relu(. + bc) -> 4 A chunks of layer 2;
+//               E2 D2 -> aenc * relu(. + bh) -> 2 A chunks of layer 3; E3 D3 -> relu(. + bh2) . wo + bo -> z.
+// A slot's operand buffers alternate with a per-slot use counter u (buffer u & 1): the epilogue waits for the
+// buffer's previous reader (x_free, tcgen05.commit), writes, arrives on a_full; the MMA thread waits a_full,
+// issues, commits x_free.  TMEM per slot: D1 = columns [0, 256) (two N = 128 halves), D2 reuses [0, 128) once
+// the first two layer-2 chunks are built, D3 reuses [128, 256).
+//
+// SAVE mode (the learner's differentiable pass): every operand image the backward kernels need — cos, H1, H2
+// and R3 = relu(P3 + bh2) as swizzled fp16 hi | lo chunks, exactly the bytes the MMAs read — goes to HBM
+// by cp.async.bulk from the operand buffer itself (one elected thread per slot, bulk async-groups).
+#include "umma.cuh"
+
+namespace asvrl {
+
+constexpr int CF_THREADS = 640;
+constexpr int CF_ROWS = 128;                       // rows per tile = UMMA M
+constexpr int CF_NCOS = 64, CF_W = 256, CF_H = 128;
+constexpr int CF_TILE_B = CF_ROWS * 128;           // one fp16 piece of a [128 x 64] chunk: 16 KB
+constexpr int CF_CHUNK_B = 2 * CF_TILE_B;          // hi | lo
+constexpr int CF_WSTAGES = 3;
+constexpr int CF_W_CHUNKS = 8;                     // Wc: 2 (n halves), Wh: 4 (k chunks), Wh2: 2
+constexpr int CF_IMAGE_B = CF_W_CHUNKS * CF_CHUNK_B;   // 256 KB packed weights
+constexpr float CF_WSCALE = 64.0f, CF_WUNSCALE = 1.0f / 64.0f;
+
+constexpr int CF_OFF_X = 0;                                        // [slot][buffer] operand chunks
+constexpr int CF_OFF_WR = 4 * CF_CHUNK_B;                          // weight ring
+constexpr int CF_OFF_BAR = CF_OFF_WR + CF_WSTAGES * CF_CHUNK_B;    // 229376
+constexpr int CF_NBAR = 2 * 8 + 2 * CF_WSTAGES;                    // per slot a_full[2] x_free[2] d_full[4]; w_full, w_empty
+constexpr int CF_OFF_MISC = CF_OFF_BAR + CF_NBAR * 8;              // tmem slot, abort flag
+constexpr int CF_OFF_ZPART = CF_OFF_MISC + 16;                     // [slot][128] floats
+constexpr int CF_SMEM_B = CF_OFF_ZPART + 2 * CF_ROWS * 4 + 1024;   // + alignment slack
+static_assert(CF_SMEM_B <= 232448, "K10 shared memory");
+
+struct CriticArgs {
+  const float* tau_in;                        // [rows] or null (Philox stream 3)
+  uint64_t seed, counter;
+  const uint64_t* counter_dev;
+  float cvar;
+  const float *feats, *aenc;                  // [B][256], [B][128] (null: unit scale)
+  const float *bc, *bh, *bh2, *wo, *bo;       // biases, head row [128], head bias [1]
+  const unsigned char* image;                 // packed Wc | Wh | Wh2 chunks (critic_pack_kernel)
+  int rows, n_tau, batch, n_tiles;
+  int* status;
+  float *tau_out, *z;                         // [rows] (tau_out nullable)
+  unsigned char *cos_img, *h1_img, *h2_img, *r3_img;   // SAVE mode: [tile][1 | 4 | 2 | 2][32 KB]
+};
+
+// ---- weight image: chunk c = hi tile (128 rows of 128 B, swizzled) then lo tile ----
+__global__ void __launch_bounds__(256)
+critic_pack_kernel(const float* __restrict__ wc, const float* __restrict__ wh, const float* __restrict__ wh2,
+                   unsigned char* __restrict__ image) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;   // one 16-byte chunk (8 k) of one row of one chunk
+  if (t >= CF_W_CHUNKS * CF_H * 8) return;
+  const int c = t / (CF_H * 8), n = (t / 8) % CF_H, oc = t & 7;
+  const float* src;
+  if (c < 2) src = wc + (size_t)(128 * c + n) * CF_NCOS + oc * 8;
+  else if (c < 6) src = wh + (size_t)n * CF_W + (c - 2) * 64 + oc * 8;
+  else src = wh2 + (size_t)n * CF_H + (c - 6) * 64 + oc * 8;
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) um_split2(src[2 * i] * CF_WSCALE, src[2 * i + 1] * CF_WSCALE, h[i], l[i]);
+  unsigned char* tile = image + (size_t)c * CF_CHUNK_B + um_sw128_off(n, oc);
+  *reinterpret_cast<uint4*>(tile) = make_uint4(h[0], h[1], h[2], h[3]);
+  *reinterpret_cast<uint4*>(tile + CF_TILE_B) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// cos(tau * fl32(pi i)) for i = I0 .. I0 + 31 of this thread's row -> octets OC0 .. OC0 + 3 of the A chunk
+template <int I0>
+__device__ __forceinline__ void cf_cos_octets(float tau, uint32_t a_row, int r7) {
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float pi_i = (float)(3.14159265358979323846 * (double)(I0 + 8 * t + e));   // ACIQN:397
+      v[e] = cosf(__fmul_rn(tau, pi_i));                                                // ACIQN:424
+    }
+    um_put8(a_row + (uint32_t)(((I0 / 8 + t) ^ r7) << 4), CF_TILE_B, v);
+  }
+}
+
+template <bool SAVE, bool AENC>
+__global__ void __launch_bounds__(CF_THREADS, 1)
+critic_forward_kernel(const CriticArgs a) {
+  extern __shared__ __align__(1024) unsigned char cf_raw[];
+  unsigned char* base = cf_raw + ((1024u - (um_smem(cf_raw) & 1023u)) & 1023u);
+  const uint32_t sb = um_smem(base);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  const uint32_t bar0 = sb + CF_OFF_BAR;
+  auto bar_a_full = [&](int s, int x) { return bar0 + 8u * (8 * s + x); };
+  auto bar_x_free = [&](int s, int x) { return bar0 + 8u * (8 * s + 2 + x); };
+  auto bar_d_full = [&](int s, int d) { return bar0 + 8u * (8 * s + 4 + d); };
+  auto bar_w_full = [&](int st) { return bar0 + 8u * (16 + st); };
+  auto bar_w_empty = [&](int st) { return bar0 + 8u * (16 + CF_WSTAGES + st); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(base + CF_OFF_MISC);
+  volatile uint32_t* abort_flag = reinterpret_cast<volatile uint32_t*>(base + CF_OFF_MISC + 4);
+  float* zpart = reinterpret_cast<float*>(base + CF_OFF_ZPART);
+
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      for (int x = 0; x < 2; ++x) {
+        um_mbar_init(bar_a_full(s, x), SAVE ? 1 : 8);   // SAVE: the slot's elected thread, after the slot barrier
+        um_mbar_init(bar_x_free(s, x), 1);
+      }
+      for (int d = 0; d < 4; ++d) um_mbar_init(bar_d_full(s, d), 1);
+    }
+    for (int st = 0; st < CF_WSTAGES; ++st) {
+      um_mbar_init(bar_w_full(st), 1);
+      um_mbar_init(bar_w_empty(st), 1);
+    }
+    *abort_flag = 0u;
+    um_mbar_init_fence();
+  }
+  if (warp == 2) um_tmem_alloc<512>(um_smem(tmem_slot));
+  um_tc_before();
+  __syncthreads();
+  um_tc_after();
+  const uint32_t tmem = *tmem_slot;
+
+  const int n_my = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  // A timed-out wait sets the CTA's abort flag and the status word; every later wait then returns at once and the
+  // roles run their loops to the end on garbage, so no named barrier is left short of a participant.
+  auto wait = [&](uint32_t bar, uint32_t parity, int code) { (void)um_mbar_wait(bar, parity, abort_flag, a.status, code); };
+
+  if (warp == 0) {
+    // =============== W producer ===============
+    if (lane == 0) {
+      int pos = 0;
+      auto emit = [&](int first, int n) {
+        for (int c = first; c < first + n; ++c, ++pos) {
+          const int st = pos % CF_WSTAGES;
+          if (pos >= CF_WSTAGES) wait(bar_w_empty(st), (uint32_t)((pos / CF_WSTAGES) - 1) & 1u, UM_TIMEOUT_RING);
+          um_mbar_arrive_expect_tx(bar_w_full(st), CF_CHUNK_B);
+          um_bulk_g2s(sb + CF_OFF_WR + st * CF_CHUNK_B, a.image + (size_t)c * CF_CHUNK_B, CF_CHUNK_B, bar_w_full(st));
+        }
+      };
+      for (int i = 0; i < n_my; i += 2) {
+        const bool two = i + 1 < n_my;
+        emit(0, 2); if (two) emit(0, 2);
+        emit(2, 4); if (two) emit(2, 4);
+        emit(6, 2); if (two) emit(6, 2);
+      }
+    }
+  } else if (warp == 1) {
+    // =============== MMA issuer ===============
+    if (lane == 0) {
+      constexpr uint32_t idesc = um_idesc_f16(CF_ROWS, CF_H);
+      int pos = 0;
+      uint32_t u[2] = {0u, 0u};
+      auto xaddr = [&](int s, uint32_t uu) { return sb + CF_OFF_X + (uint32_t)(2 * s + (int)(uu & 1u)) * CF_CHUNK_B; };
+      auto use_wait = [&](int s, uint32_t uu) {
+        wait(bar_a_full(s, (int)(uu & 1u)), (uu >> 1) & 1u, UM_TIMEOUT_INPUT);
+        um_tc_after();
+      };
+      auto use_done = [&](int s, bool mma) {
+        const uint32_t x = u[s] & 1u;
+        if (mma) um_commit(bar_x_free(s, (int)x)); else um_mbar_arrive(bar_x_free(s, (int)x));
+        ++u[s];
+      };
+      auto chunk = [&](uint32_t ax, uint32_t d_tmem, bool first) {
+        const int st = pos % CF_WSTAGES;
+        wait(bar_w_full(st), (uint32_t)(pos / CF_WSTAGES) & 1u, UM_TIMEOUT_RING);
+        um_tc_after();
+        const uint32_t ah = ax, al = ax + CF_TILE_B;
+        const uint32_t wh = sb + CF_OFF_WR + st * CF_CHUNK_B, wl = wh + CF_TILE_B;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {   // 4 x (K = 16 fp16 = 32 B) per 128-byte row
+          const uint32_t o = ks * 32;
+          um_mma_f16(d_tmem, um_desc_sw128(al + o), um_desc_sw128(wh + o), idesc, (first && ks == 0) ? 0u : 1u);  // small terms first
+          um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wl + o), idesc, 1u);
+          um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wh + o), idesc, 1u);
+        }
+        um_commit(bar_w_empty(st));
+        ++pos;
+      };
+      auto S1 = [&](int s) {   // cos x Wc^T, two N = 128 halves
+        const uint32_t d = tmem + (uint32_t)(256 * s);
+        if (SAVE && u[s] > 0u)
+          for (int j = 0; j < 2; ++j) {   // the previous tile's two R3 chunks passed through the buffers without an MMA
+            use_wait(s, u[s]);
+            use_done(s, false);
+          }
+        use_wait(s, u[s]);
+        const uint32_t ax = xaddr(s, u[s]);
+        chunk(ax, d, true);
+        um_commit(bar_d_full(s, 0));
+        chunk(ax, d + 128u, true);
+        um_commit(bar_d_full(s, 1));
+        use_done(s, true);
+      };
+      auto S2 = [&](int s) {   // H1 x Wh^T into columns [0,128): both chunks built from them must exist first
+        const uint32_t d = tmem + (uint32_t)(256 * s);
+        use_wait(s, u[s]);
+        use_wait(s, u[s] + 1u);
+        for (int j = 0; j < 4; ++j) {
+          if (j >= 2) use_wait(s, u[s]);
+          chunk(xaddr(s, u[s]), d, j == 0);
+          use_done(s, true);
+        }
+        um_commit(bar_d_full(s, 2));
+      };
+      auto S3 = [&](int s) {   // H2 x Wh2^T into columns [128,256)
+        const uint32_t d = tmem + (uint32_t)(256 * s) + 128u;
+        for (int j = 0; j < 2; ++j) {
+          use_wait(s, u[s]);
+          chunk(xaddr(s, u[s]), d, j == 0);
+          use_done(s, true);
+        }
+        um_commit(bar_d_full(s, 3));
+      };
+      for (int i = 0; i < n_my; i += 2) {
+        const bool two = i + 1 < n_my;
+        S1(0); if (two) S1(1);
+        S2(0); if (two) S2(1);
+        S3(0); if (two) S3(1);
+      }
+    }
+  } else if (warp >= 4) {
+    // =============== epilogue warps ===============
+    const int ew = warp - 4, s = ew >> 3, e = ew & 7, q = e & 3, hh = e >> 2;
+    const int r = 32 * q + lane, r7 = r & 7;
+    const uint32_t row_off = (uint32_t)((r >> 3) * 1024 + r7 * 128);
+    const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(256 * s);
+    const uint32_t xbase = sb + CF_OFF_X + (uint32_t)(2 * s) * CF_CHUNK_B;
+    const bool elected = (e == 0 && lane == 0);
+    const int grp_bar = 1 + s, pair_bar = 3 + 4 * s + q;
+    const float4* bc4 = reinterpret_cast<const float4*>(a.bc);
+    const float4* bh4 = reinterpret_cast<const float4*>(a.bh);
+    const float4* bh24 = reinterpret_cast<const float4*>(a.bh2);
+    const float4* wo4 = reinterpret_cast<const float4*>(a.wo);
+    const float bo = __ldg(a.bo);
+    const uint64_t counter = a.counter + (a.counter_dev ? *a.counter_dev : 0ull);
+    uint32_t u = 0;
+
+    // buffer of use u, once its previous reader (use u - 2) is done with it
+    // (`newer_stores`: bulk stores committed after the one that read this buffer last — 1 in the running order)
+    auto acquire = [&](bool newer_store = true) -> uint32_t {
+      const uint32_t x = u & 1u;
+      if (u >= 2u) wait(bar_x_free(s, (int)x), ((u >> 1) - 1u) & 1u, UM_TIMEOUT_RING);
+      if (SAVE) {
+        if (elected) {   // the bulk store of use u - 2 has read the buffer
+          if (newer_store) um_bulk_wait_read<1>(); else um_bulk_wait_read<0>();
+        }
+        um_bar_sync(grp_bar, 256);
+      }
+      return xbase + x * CF_CHUNK_B;
+    };
+    // hand the chunk to the MMA thread (and, SAVE, to HBM at `img`)
+    auto publish = [&](uint32_t xa, unsigned char* img) {
+      um_fence_async_smem();
+      um_tc_before();
+      if (SAVE) {
+        um_bar_sync(grp_bar, 256);
+        if (elected) {
+          um_bulk_s2g(img, xa, CF_CHUNK_B);
+          um_bulk_commit();
+          um_mbar_arrive(bar_a_full(s, (int)(u & 1u)));
+        }
+      } else {
+        __syncwarp();
+        if (lane == 0) um_mbar_arrive(bar_a_full(s, (int)(u & 1u)));
+      }
+      ++u;
+    };
+
+    for (int i = s; i < n_my; i += 2) {
+      const uint32_t kpar = (uint32_t)(i >> 1) & 1u;
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const long m = (long)tile * CF_ROWS + r;
+      const bool live = m < (long)a.rows;
+      const int b = (int)((live ? m : (long)a.rows - 1) / a.n_tau);
+      const float4* frow = reinterpret_cast<const float4*>(a.feats + (size_t)b * CF_W);
+      const float4* arow = AENC ? reinterpret_cast<const float4*>(a.aenc + (size_t)b * CF_H) : nullptr;
+
+      // ---- E0: tau, cos(tau pi i) -> the A chunk of layer 1 ----
+      float tau = 0.0f;
+      if (live) {
+        if (a.tau_in) {
+          tau = a.tau_in[m];
+        } else {   // torch.rand(B, N) * cvar, ACIQN:419-422; the same draw as K3
+          const uint4 w = philox_at(a.seed, STREAM_TAU, counter, (int64_t)(m >> 2), 0u, 0u, 0u);
+          const uint32_t word = (m & 3) == 0 ? w.x : (m & 3) == 1 ? w.y : (m & 3) == 2 ? w.z : w.w;
+          tau = __fmul_rn(u01(word), a.cvar);
+        }
+        if (hh == 0 && a.tau_out) a.tau_out[m] = tau;
+      }
+      {
+        const uint32_t xa = acquire();
+        if (hh == 0) cf_cos_octets<0>(tau, xa + row_off, r7); else cf_cos_octets<32>(tau, xa + row_off, r7);
+        publish(xa, SAVE ? a.cos_img + (size_t)tile * CF_CHUNK_B : nullptr);
+      }
+
+      // ---- E1: D1 -> H1 = feats[b] * relu(D1 / 64 + bc) -> the four A chunks of layer 2 ----
+      wait(bar_d_full(s, 0), kpar, UM_TIMEOUT_ACC);
+      for (int j = 0; j < 4; ++j) {
+        if (j == 1) wait(bar_d_full(s, 1), kpar, UM_TIMEOUT_ACC);   // also: layer 1 has read the cos chunk's buffer
+        um_tc_after();
+        const uint32_t xa = acquire();
+        uint32_t v[32];
+        um_tmem_ld32(lane_addr + (uint32_t)(64 * j + 32 * hh), v);
+        um_tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int c4 = (64 * j + 32 * hh + 8 * t) / 4;
+          const float4 fa = __ldg(frow + c4), fb = __ldg(frow + c4 + 1), ba = __ldg(bc4 + c4), bb = __ldg(bc4 + c4 + 1);
+          const float f[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
+          const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+          float h[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) h[k] = f[k] * fmaxf(fmaf(__uint_as_float(v[8 * t + k]), CF_WUNSCALE, bias[k]), 0.0f);
+          um_put8(xa + row_off + (uint32_t)(((4 * hh + t) ^ r7) << 4), CF_TILE_B, h);
+        }
+        publish(xa, SAVE ? a.h1_img + ((size_t)tile * 4 + j) * CF_CHUNK_B : nullptr);
+      }
+
+      // ---- E2: D2 -> H2 = aenc[b] * relu(D2 / 64 + bh) -> the two A chunks of layer 3 ----
+      wait(bar_d_full(s, 2), kpar, UM_TIMEOUT_ACC);
+      for (int j = 0; j < 2; ++j) {
+        um_tc_after();
+        const uint32_t xa = acquire();
+        uint32_t v[32];
+        um_tmem_ld32(lane_addr + (uint32_t)(64 * j + 32 * hh), v);
+        um_tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int c4 = (64 * j + 32 * hh + 8 * t) / 4;
+          const float4 ba = __ldg(bh4 + c4), bb = __ldg(bh4 + c4 + 1);
+          float4 fa = make_float4(1.f, 1.f, 1.f, 1.f), fb = fa;
+          if (AENC) { fa = __ldg(arow + c4); fb = __ldg(arow + c4 + 1); }
+          const float f[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
+          const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+          float h[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) h[k] = f[k] * fmaxf(fmaf(__uint_as_float(v[8 * t + k]), CF_WUNSCALE, bias[k]), 0.0f);
+          um_put8(xa + row_off + (uint32_t)(((4 * hh + t) ^ r7) << 4), CF_TILE_B, h);
+        }
+        publish(xa, SAVE ? a.h2_img + ((size_t)tile * 2 + j) * CF_CHUNK_B : nullptr);
+      }
+
+      // ---- E3: D3 -> R3 = relu(D3 / 64 + bh2); z = R3 . wo + bo.  This warp: columns [64 hh, 64 hh + 64) ----
+      wait(bar_d_full(s, 3), kpar, UM_TIMEOUT_ACC);
+      um_tc_after();
+      float acc = 0.0f;
+      uint32_t xr[2] = {0u, 0u};
+      if (SAVE) {   // both R3 chunks are acquired up front (use u and u + 1): this warp fills chunk hh only
+        xr[0] = acquire();
+        ++u;
+        xr[1] = acquire(false);
+        --u;
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        um_tmem_ld32(lane_addr + (uint32_t)(128 + 64 * hh + 32 * half), v);
+        um_tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int c4 = (64 * hh + 32 * half + 8 * t) / 4;
+          const float4 ba = __ldg(bh24 + c4), bb = __ldg(bh24 + c4 + 1), wa = __ldg(wo4 + c4), wb = __ldg(wo4 + c4 + 1);
+          const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+          const float w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+          float h[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            h[k] = fmaxf(fmaf(__uint_as_float(v[8 * t + k]), CF_WUNSCALE, bias[k]), 0.0f);
+            acc = fmaf(h[k], w[k], acc);
+          }
+          if (SAVE) um_put8(xr[hh] + row_off + (uint32_t)(((4 * half + t) ^ r7) << 4), CF_TILE_B, h);
+        }
+      }
+      if (SAVE) {
+        publish(xr[0], a.r3_img + ((size_t)tile * 2 + 0) * CF_CHUNK_B);
+        publish(xr[1], a.r3_img + ((size_t)tile * 2 + 1) * CF_CHUNK_B);
+      }
+      um_tc_before();
+      if (hh == 1) zpart[s * CF_ROWS + r] = acc;
+      um_bar_sync(pair_bar, 64);
+      if (hh == 0 && live) a.z[m] = acc + zpart[s * CF_ROWS + r] + bo;
+    }
+    if (SAVE && elected) um_bulk_wait<0>();
+  }
+
+  um_tc_before();
+  __syncthreads();
+  if (warp == 2) {
+    um_tc_after();
+    um_tmem_free<512>(tmem);
+  }
+}
+
+static __device__ int cf_status_word = 0;
+
+}  // namespace asvrl
+
+using namespace asvrl;
+
+extern "C" long asvrl_critic_forward_workspace(void) { return (long)CF_IMAGE_B; }
+extern "C" long asvrl_critic_forward_chunk_bytes(void) { return (long)CF_CHUNK_B; }
+
+extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t counter, const uint64_t* counter_dev,
+                                    float cvar, const float* feats, const float* aenc, const float* wc, const float* bc,
+                                    const float* wh, const float* bh, const float* wh2, const float* bh2, const float* wo,
+                                    const float* bo, int batch, int n_tau, int repack, void* workspace, float* tau_out,
+                                    float* z, void* cos_img, void* h1_img, void* h2_img, void* r3_img, void* stream) {
+  if (!feats || !wc || !bc || !wh || !bh || !wh2 || !bh2 || !wo || !bo || !workspace || !z)
+    return fail(ASVRL_E_BADARG, "asvrl_critic_forward: null pointer");
+  if (batch < 1 || n_tau < 1 || (long)batch * n_tau > 0x7FFFFFFFL - CF_ROWS)
+    return fail(ASVRL_E_BADARG, "asvrl_critic_forward: bad sizes (B=%d N=%d)", batch, n_tau);
+  const bool save = cos_img || h1_img || h2_img || r3_img;
+  if (save && !(cos_img && h1_img && h2_img && r3_img))
+    return fail(ASVRL_E_BADARG, "asvrl_critic_forward: the four operand images go together");
+  if (((uintptr_t)workspace | (uintptr_t)cos_img | (uintptr_t)h1_img | (uintptr_t)h2_img | (uintptr_t)r3_img) & 127)
+    return fail(ASVRL_E_BADARG, "asvrl_critic_forward: workspace and images must be 128-byte aligned");
+  if (((uintptr_t)feats | (uintptr_t)aenc | (uintptr_t)bc | (uintptr_t)bh | (uintptr_t)bh2 | (uintptr_t)wo) & 15)
+    return fail(ASVRL_E_BADARG, "asvrl_critic_forward: feats, aenc, biases and wo must be 16-byte aligned");
+  static int n_sm = 0;
+  cudaError_t e;
+  if (n_sm == 0) {
+    int dev = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess || (e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess)
+      return fail((int)e, "asvrl_critic_forward: %s", cudaGetErrorString(e));
+    if ((e = cudaFuncSetAttribute(critic_forward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess) {
+      n_sm = 0;
+      return fail((int)e, "asvrl_critic_forward: %d B shared memory: %s", CF_SMEM_B, cudaGetErrorString(e));
+    }
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (repack) {
+    const int n = CF_W_CHUNKS * CF_H * 8;
+    critic_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wc, wh, wh2, (unsigned char*)workspace);
+    if (int rc = check_launch("asvrl_critic_forward (pack)")) return rc;
+  }
+  CriticArgs a;
+  a.tau_in = tau_in; a.seed = seed; a.counter = counter; a.counter_dev = counter_dev; a.cvar = cvar;
+  a.feats = feats; a.aenc = aenc; a.bc = bc; a.bh = bh; a.bh2 = bh2; a.wo = wo; a.bo = bo;
+  a.image = (const unsigned char*)workspace;
+  a.rows = batch * n_tau; a.n_tau = n_tau; a.batch = batch; a.n_tiles = (a.rows + CF_ROWS - 1) / CF_ROWS;
+  int* status = nullptr;
+  if (cudaGetSymbolAddress((void**)&status, cf_status_word) != cudaSuccess) status = nullptr;
+  a.status = status;
+  a.tau_out = tau_out; a.z = z;
+  a.cos_img = (unsigned char*)cos_img; a.h1_img = (unsigned char*)h1_img;
+  a.h2_img = (unsigned char*)h2_img; a.r3_img = (unsigned char*)r3_img;
+  const int grid = a.n_tiles < n_sm ? a.n_tiles : n_sm;
+  if (save) {
+    if (aenc) critic_forward_kernel<true, true><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+    else critic_forward_kernel<true, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+  } else {
+    if (aenc) critic_forward_kernel<false, true><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+    else critic_forward_kernel<false, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+  }
+  return check_launch("asvrl_critic_forward");
+}
+
+// synchronous read of K10's device status word (0 = every bounded wait completed)
+extern "C" int asvrl_critic_forward_status(int* status_out) {
+  if (!status_out) return fail(ASVRL_E_BADARG, "asvrl_critic_forward_status: null pointer");
+  cudaError_t e = cudaMemcpyFromSymbol(status_out, cf_status_word, sizeof(int));
+  if (e != cudaSuccess) return fail((int)e, "asvrl_critic_forward_status: %s", cudaGetErrorString(e));
+  return 0;
+}

@@ -9,7 +9,7 @@ namespace asvrl {
 
 // device status codes a kernel leaves in its status word when a bounded wait expires (include/asvrl.h:
 // surfaced as ASVRL_E_DEVICE by asvrl_umma_status; nothing traps, nothing hangs)
-enum : int { UM_OK = 0, UM_TIMEOUT_RING = 1, UM_TIMEOUT_ACC = 2, UM_TIMEOUT_INPUT = 3, UM_TIMEOUT_K8 = 4 };
+enum : int { UM_OK = 0, UM_TIMEOUT_RING = 1, UM_TIMEOUT_ACC = 2, UM_TIMEOUT_INPUT = 3, UM_TIMEOUT_K8 = 4, UM_BAD_SMEM = 5 };
 
 __device__ __forceinline__ uint32_t um_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -63,6 +63,22 @@ __device__ __forceinline__ bool um_mbar_wait(uint32_t mbar, uint32_t parity, vol
 __device__ __forceinline__ void um_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+
+// ---- TMA: 1-D bulk copy shared -> global (bulk async-group completion) ----
+__device__ __forceinline__ void um_bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void um_bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+// at most N of this thread's bulk groups still READING their shared-memory source
+template <int N>
+__device__ __forceinline__ void um_bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void um_bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// named barrier among `threads` threads (whole warps) of the CTA; id 1..15 (0 is __syncthreads)
+__device__ __forceinline__ void um_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(threads) : "memory");
 }
 
 // ---- proxies and tcgen05 fences ----

@@ -523,6 +523,33 @@ ASVRL_API int asvrl_policy_forward(const float* self_obs, const float* objects, 
                                    void* workspace, float* actions, void* stream);
 ASVRL_API int asvrl_policy_forward_status(int* status_out);
 
+/* K10 — the IQN critic's quantile trunk forward (ACIQN:410-426 calc_cos, ACIQN:453-480 the three dense layers with the
+ * feature / action-encoding products and the 128 -> 1 head; with aenc == NULL the trunk of IQN:74-86 up to the last
+ * hidden layer) for all batch * n_tau quantile rows in ONE persistent launch on the tcgen05 tensor cores (fp16
+ * two-piece split, three products, fp32 accumulation in TMEM: fp32-GEMM-level accuracy).  The cosine table is
+ * generated inside the kernel's operand loader; no activation leaves the SM.
+ *   tau_in [B*N] nullable: NULL draws tau = u01 * cvar from Philox stream 3 exactly as asvrl_iqn_tau_cos does
+ *   (same seed / counter / counter_dev meaning); tau_out [B*N] nullable; feats [B][256] (the observation tower's
+ *   output), aenc [B][128] nullable; wc [256][64], wh [128][256], wh2 [128][128], wo [128], bo [1] and the biases in
+ *   the nn.Linear layout; z [B*N].  `workspace`: asvrl_critic_forward_workspace() bytes, 128-byte aligned, holds the
+ *   packed weight image; `repack` != 0 rebuilds it from wc / wh / wh2 first (one small launch).
+ *   cos_img / h1_img / h2_img / r3_img: all NULL (inference), or all set (the differentiable pass): the operand images
+ *   the backward kernels read — per 128-row tile 1 / 4 / 2 / 2 chunks of asvrl_critic_forward_chunk_bytes() bytes
+ *   (fp16 hi | lo pieces of cos, H1 = feats * relu(P1 + bc), H2 = aenc * relu(P2 + bh), R3 = relu(P3 + bh2), in the
+ *   128-byte-swizzled K-major tile layout the MMAs consume), 128-byte aligned.
+ * Bounded waits: a pipeline fault leaves a non-zero code in the status word read by asvrl_critic_forward_status
+ * (synchronous) instead of hanging or trapping.  An activation beyond fp16's range (65 504) yields NaN quantiles. */
+ASVRL_API long asvrl_critic_forward_workspace(void);
+ASVRL_API long asvrl_critic_forward_chunk_bytes(void);
+ASVRL_API int asvrl_critic_forward(const float* tau_in /* nullable */, uint64_t seed, uint64_t counter,
+                                   const uint64_t* counter_dev /* nullable */, float cvar, const float* feats,
+                                   const float* aenc /* nullable */, const float* wc, const float* bc,
+                                   const float* wh, const float* bh, const float* wh2, const float* bh2,
+                                   const float* wo, const float* bo, int batch, int n_tau, int repack,
+                                   void* workspace, float* tau_out /* nullable */, float* z, void* cos_img,
+                                   void* h1_img, void* h2_img, void* r3_img, void* stream);
+ASVRL_API int asvrl_critic_forward_status(int* status_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,6 +73,9 @@ _SIGNATURES = {
     "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
                              + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p, vp, vp, vp, vp, vp]),
     "asvrl_critic_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
+    "asvrl_critic_wgrad_workspace": (C.c_long, [C.c_int]),
+    "asvrl_critic_wgrad": (C.c_int, [vp] * 8 + [f32p, C.c_int, C.c_int] + [f32p] * 8 + [vp]),
+    "asvrl_critic_wgrad_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_clip_adam_step_p2p": (C.c_int, [C.POINTER(_abi.AdamTensors), C.POINTER(_abi.PeerBuckets), f32p, u32p]
                                  + [C.c_float] * 5 + [f32p, f32p, u32p, vp]),
     "asvrl_clip_adam_step": (C.c_int, [C.POINTER(_abi.AdamTensors)] + [C.c_float] * 6 + [f32p, f32p, u32p, vp]),
@@ -496,6 +499,36 @@ def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspa
         *[None if t is None else t.data_ptr() for t in imgs], stream_ptr())
     check(rc, "asvrl_critic_forward")
     return (z, tau, imgs) if save else (z, tau)
+
+
+_WGRAD_WS = {}
+
+
+def critic_wgrad(dp3, dp2, dp1, aux, cos_img, h1_img, h2_img, r3_img, scales, B, n_tau):
+    """K12: (d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo) from the operand images of K10 / K11."""
+    dev = dp3.device
+    tiles = (B * n_tau + 127) // 128
+    need = lib().asvrl_critic_wgrad_workspace(tiles)
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _WGRAD_WS.get(key)
+    if ws is None or ws.numel() < need:
+        ws = _WGRAD_WS[key] = torch.empty((need,), dtype=torch.float32, device=dev)
+    new = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
+    d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo = new(256, 64), new(256), new(128, 256), new(128), new(128, 128), new(128), new(128)
+    rc = lib().asvrl_critic_wgrad(dp3.data_ptr(), dp2.data_ptr(), dp1.data_ptr(), aux.data_ptr(), cos_img.data_ptr(),
+                                  h1_img.data_ptr(), h2_img.data_ptr(), r3_img.data_ptr(), ptr(scales, torch.float32),
+                                  B, int(n_tau), ptr(ws), ptr(d_wc), ptr(d_bc), ptr(d_wh), ptr(d_bh), ptr(d_wh2),
+                                  ptr(d_bh2), ptr(d_wo), stream_ptr())
+    check(rc, "asvrl_critic_wgrad")
+    return d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo
+
+
+def critic_wgrad_status():
+    v = C.c_int(0)
+    check(lib().asvrl_critic_wgrad_status(C.byref(v)), "asvrl_critic_wgrad_status")
+    if v.value != 0:
+        raise RuntimeError(f"asvrl_critic_wgrad: device pipeline fault, status {v.value}")
+    return 0
 
 
 def critic_forward_status():

@@ -108,6 +108,13 @@ __device__ __forceinline__ void um_tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) 
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
 }
+__device__ __forceinline__ void um_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
 __device__ __forceinline__ void um_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
 // ---- UMMA descriptors ----
@@ -119,6 +126,13 @@ __device__ __forceinline__ uint64_t um_desc_sw128(uint32_t saddr) {
   const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
   return ((uint64_t)hi << 32) | lo;
 }
+// the same tile read MN-major (the 64 elements of a 128-byte row run along M / N, the rows along K): the MMA's K step
+// of 16 is two 8-row groups SBO = 1024 B apart; `lbo` = distance to the tile holding the next 64 M / N elements
+__device__ __forceinline__ uint64_t um_desc_sw128_mn(uint32_t saddr, uint32_t lbo) {
+  const uint32_t lo = ((saddr >> 4) & 0x3FFFu) | (((lbo >> 4) & 0x3FFFu) << 16);
+  const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+  return ((uint64_t)hi << 32) | lo;
+}
 // byte offset of 16-byte chunk c (0..7) of row r in such a tile
 __host__ __device__ __forceinline__ uint32_t um_sw128_off(int r, int c) {
   return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
@@ -127,6 +141,9 @@ __host__ __device__ __forceinline__ uint32_t um_sw128_off(int r, int c) {
 // instruction descriptors: D fp32, A / B both K-major, dense, no negate
 __host__ __device__ constexpr uint32_t um_idesc_f16(int M, int N) {   // kind::f16, A and B fp16
   return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__host__ __device__ constexpr uint32_t um_idesc_f16_mn(int M, int N) {   // kind::f16, A and B both MN-major
+  return um_idesc_f16(M, N) | (1u << 15) | (1u << 16);
 }
 __host__ __device__ constexpr uint32_t um_idesc_tf32(int M, int N) {  // kind::tf32
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

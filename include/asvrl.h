@@ -550,6 +550,23 @@ ASVRL_API int asvrl_critic_forward(const float* tau_in /* nullable */, uint64_t 
                                    void* h1_img, void* h2_img, void* r3_img, void* stream);
 ASVRL_API int asvrl_critic_forward_status(int* status_out);
 
+/* K12 — weight and bias gradients of the critic trunk (the parameter half of the autograd backward of ACIQN:453-480)
+ * on the tcgen05 tensor cores, from operand images: dWh2 = dP3^T H2, dbh2 = dP3^T 1, dwo = R3^T dz, dWh = dP2^T H1,
+ * dbh = dP2^T 1, dWc = dP1^T cos, dbc = dP1^T 1, contraction over the batch * n_tau quantile rows.
+ *   cos_img / h1_img / h2_img / r3_img: as written by asvrl_critic_forward; dp3_img / dp2_img / dp1_img / aux_img
+ *   ([tile][2 | 2 | 4 | 1] chunks) and scales[2] = {1/S, 1/S1} (device) as written by asvrl_critic_backward: dP3, dP2
+ *   and aux column 0 (dz) carry the power-of-two factor S, dP1 carries S1; the outputs are unscaled.
+ *   workspace: asvrl_critic_wgrad_workspace(n_tiles) floats (per-CTA partial accumulators, summed in a fixed order).
+ *   Outputs in the nn.Linear layout: d_wc [256][64], d_bc [256], d_wh [128][256], d_bh [128], d_wh2 [128][128],
+ *   d_bh2 [128], d_wo [128]. */
+ASVRL_API long asvrl_critic_wgrad_workspace(int n_tiles);
+ASVRL_API int asvrl_critic_wgrad(const void* dp3_img, const void* dp2_img, const void* dp1_img, const void* aux_img,
+                                 const void* cos_img, const void* h1_img, const void* h2_img, const void* r3_img,
+                                 const float* scales, int batch, int n_tau, float* workspace, float* d_wc,
+                                 float* d_bc, float* d_wh, float* d_bh, float* d_wh2, float* d_bh2, float* d_wo,
+                                 void* stream);
+ASVRL_API int asvrl_critic_wgrad_status(int* status_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -124,3 +124,54 @@ def test_saved_operand_images(B, N):
         scale = want.abs().max().item()
         err = (got - want).abs().max().item()
         assert err <= 5e-6 * scale + 1e-7, f"{name} image: max abs err {err:.3e} at scale {scale:.3e}"
+
+
+def _encode(x):
+    """(M, C) float -> (tiles, C / 64, 32 KB) uint8 operand image (fp16 hi | lo, 128-byte swizzle); inverse of _decode."""
+    M, Cc = x.shape
+    tiles, chunks = (M + 127) // 128, Cc // 64
+    xp = torch.zeros((tiles * 128, Cc), dtype=torch.float32, device=x.device)
+    xp[:M] = x.float()
+    hi = xp.half()
+    lo = (xp - hi.float()).half()
+    v = torch.stack((hi, lo), 0).reshape(2, tiles, 128, chunks, 64).permute(1, 3, 0, 2, 4)   # tile, chunk, piece, r, k
+    r = torch.arange(128, device=x.device).view(128, 1)
+    k = torch.arange(64, device=x.device).view(1, 64)
+    idx = (((r >> 3) * 1024 + (r & 7) * 128 + (((k >> 3) ^ (r & 7)) << 4) + (k & 7) * 2) // 2).reshape(-1)
+    out = torch.zeros((tiles, chunks, 2, 128 * 64), dtype=torch.float16, device=x.device)
+    out[..., idx] = v.reshape(tiles, chunks, 2, 128 * 64)
+    return out.view(torch.uint8).reshape(tiles, chunks, 32768).contiguous()
+
+
+def test_encode_decode_round_trip():
+    g = torch.Generator(device=DEV).manual_seed(0)
+    x = torch.randn((300, 128), device=DEV, generator=g)
+    got = _decode(_encode(x))[:300]
+    assert (got - x.double()).abs().max().item() <= 2e-7 * x.abs().max().item()
+
+
+@pytest.mark.parametrize("M", [32768, 512, 8192 + 128])
+def test_wgrad_from_images(M):
+    """K12 alone on synthetic images: every product against float64 on the decoded (hi + lo) operands."""
+    g = torch.Generator(device=DEV).manual_seed(M)
+    rnd = lambda *s: torch.randn(s, device=DEV, generator=g)
+    S, S1 = 256.0, 2.0
+    dp3, dp2, dp1 = rnd(M, 128) * 8, rnd(M, 128) * 4, rnd(M, 256) * 2
+    h2, h1, cos, r3 = torch.relu(rnd(M, 128)) * 3, torch.relu(rnd(M, 256)) * 20, torch.cos(rnd(M, 64) * 50), torch.relu(rnd(M, 128))
+    dz = rnd(M) * 100
+    aux = torch.zeros((M, 64), device=DEV)
+    aux[:, 0], aux[:, 1] = dz, 1.0
+    imgs = [_encode(t) for t in (dp3, dp2, dp1, aux, cos, h1, h2, r3)]
+    scales = torch.tensor([1.0 / S, 1.0 / S1], device=DEV)
+    B, N = M // 32, 32
+    got = _lib.critic_wgrad(*imgs, scales, B, N)
+    torch.cuda.synchronize()
+    _lib.critic_wgrad_status()
+    d = [_decode(i)[:M] for i in imgs]
+    dp3, dp2, dp1, aux, cos, h1, h2, r3 = d
+    want = ((dp1.t() @ cos) / S1, dp1.sum(0) / S1, (dp2.t() @ h1) / S, dp2.sum(0) / S, (dp3.t() @ h2) / S, dp3.sum(0) / S,
+            (r3.t() @ aux[:, 0]) / S)
+    for name, a, w in zip(("d_wc", "d_bc", "d_wh", "d_bh", "d_wh2", "d_bh2", "d_wo"), got, want):
+        scale = w.abs().max().item()
+        err = (a.double() - w).abs().max().item()
+        assert err <= 3e-6 * scale, f"{name}: max abs err {err:.3e} at scale {scale:.3e}"

@@ -73,6 +73,10 @@ _SIGNATURES = {
     "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
                              + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p, vp, vp, vp, vp, vp]),
     "asvrl_critic_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
+    "asvrl_critic_backward_workspace": (C.c_long, []),
+    "asvrl_critic_backward": (C.c_int, [f32p, vp, vp, vp] + [f32p] * 6 + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p,
+                                                                          vp, vp, vp, vp, f32p, vp]),
+    "asvrl_critic_backward_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_critic_wgrad_workspace": (C.c_long, [C.c_int]),
     "asvrl_critic_wgrad": (C.c_int, [vp] * 8 + [f32p, C.c_int, C.c_int] + [f32p] * 8 + [vp]),
     "asvrl_critic_wgrad_status": (C.c_int, [C.POINTER(C.c_int)]),
@@ -499,6 +503,44 @@ def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspa
         *[None if t is None else t.data_ptr() for t in imgs], stream_ptr())
     check(rc, "asvrl_critic_forward")
     return (z, tau, imgs) if save else (z, tau)
+
+
+_CRITIC_BWD_WS = {}
+
+
+def critic_backward(dz, r3_img, h2_img, h1_img, feats, aenc, wh, wh2, wo, n_tau, full=True, repack=True, fmax=None):
+    """K11.  full: -> (daenc, dfeats, (dp3, dp2, dp1, aux) images, scales); else -> daenc (the actor update's pass).
+    ``fmax``: 1-element tensor, max of feats (sets the power-of-two scale of the dP1 image)."""
+    B = feats.shape[0]
+    dev = feats.device
+    f = torch.float32
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _CRITIC_BWD_WS.get(key)
+    if ws is None:
+        ws = _CRITIC_BWD_WS[key] = torch.empty((lib().asvrl_critic_backward_workspace(),), dtype=torch.uint8, device=dev)
+    daenc = torch.empty((B, 128), dtype=f, device=dev)
+    dfeats = scales = None
+    imgs = (None, None, None, None)
+    if full:
+        tiles = (B * n_tau + 127) // 128
+        cb = lib().asvrl_critic_forward_chunk_bytes()
+        dfeats = torch.empty((B, 256), dtype=f, device=dev)
+        imgs = tuple(torch.empty((tiles, n, cb), dtype=torch.uint8, device=dev) for n in (2, 2, 4, 1))
+        scales = torch.empty((2,), dtype=f, device=dev)
+    rc = lib().asvrl_critic_backward(
+        ptr(dz, f), r3_img.data_ptr(), h2_img.data_ptr(), h1_img.data_ptr() if full else None, ptr(feats, f), ptr(aenc, f),
+        ptr(wh, f), ptr(wh2, f), ptr(wo, f), ptr(fmax, f), B, int(n_tau), int(bool(repack)), ws.data_ptr(), ptr(daenc, f),
+        ptr(dfeats, f), *[None if t is None else t.data_ptr() for t in imgs], ptr(scales, f), stream_ptr())
+    check(rc, "asvrl_critic_backward")
+    return (daenc, dfeats, imgs, scales) if full else daenc
+
+
+def critic_backward_status():
+    v = C.c_int(0)
+    check(lib().asvrl_critic_backward_status(C.byref(v)), "asvrl_critic_backward_status")
+    if v.value != 0:
+        raise RuntimeError(f"asvrl_critic_backward: device pipeline fault, status {v.value}")
+    return 0
 
 
 _WGRAD_WS = {}

@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .iqn_ops import TauSampler, critic_trunk, linear_scale_relu, observation_tower
+from .iqn_ops import TauSampler, critic_trunk, critic_trunk_umma, linear_scale_relu, observation_tower, umma_trunk_ok
 
 
 _UNIT = {}
@@ -254,6 +254,18 @@ class Critic(_ObservationTower):
                 feats = self._features(x)
             ps = [p.detach() for p in ps]
             aenc = linear_scale_relu(actions, enc.weight.detach(), enc.bias.detach(), ones, 1)
+        need_grad = torch.is_grad_enabled() and (feats.requires_grad or aenc.requires_grad or ps[0].requires_grad)
+        if umma_trunk_ok(feats, aenc, ps[0], ps[2], ps[4], num_tau, need_grad):
+            # K10 (+ K11 / K12 in the backward): cosine embedding, the three dense layers and the head in one
+            # persistent tcgen05 launch; the (B, N, 64) cosine table never exists
+            ts = self.tau_sampler
+            if taus is not None:
+                tau_in, draw = taus.reshape(B, num_tau).to(torch.float32).contiguous(), (0, 0, None, 1.0)
+            else:
+                ts.counter += 1
+                tau_in, draw = None, (ts.seed, ts.counter, ts.counter_dev, float(cvar))
+            z, tau = critic_trunk_umma(feats, aenc, *ps, num_tau, tau_in, draw, id(self))
+            return z, tau.unsqueeze(-1)
         cos, taus = self.calc_cos(B, num_tau, cvar, taus)
         z = critic_trunk(cos.reshape(B * num_tau, self.n), feats, aenc, *ps, num_tau)
         return z, taus

@@ -157,6 +157,78 @@ class _CriticTrunk(torch.autograd.Function):
         return tuple(g)
 
 
+# K10 / K11 / K12: the whole trunk, forward and backward, on the tcgen05 tensor cores (ASVRL_CRITIC_UMMA=0: K3 + cuBLAS + K5)
+UMMA_TRUNK = os.environ.get("ASVRL_CRITIC_UMMA", "1") != "0"
+UMMA_TRUNK_MIN_ROWS = int(os.environ.get("ASVRL_CRITIC_UMMA_MIN_ROWS", "4096"))  # fewer 128-row tiles leave most SMs idle
+
+
+def umma_trunk_ok(feats, aenc, Wc, Wh, Wh2, n_tau, need_grad):
+    """K10 - K12 are compiled for the reference's fixed trunk shape (64 -> 256 -> 128 -> 128 -> 1, AGENT:20-26) in
+    float32; the backward's per-sample sums need a power-of-two quantile count <= 32 (the reference uses 8 and 32)."""
+    return (UMMA_TRUNK and feats.shape[0] * n_tau >= UMMA_TRUNK_MIN_ROWS
+            and feats.is_cuda and feats.dtype == torch.float32 and Wc.dtype == torch.float32
+            and tuple(Wc.shape) == (256, 64) and tuple(Wh.shape) == (128, 256) and tuple(Wh2.shape) == (128, 128)
+            and feats.shape[1] == 256 and (aenc is None or aenc.shape[1] == 128)
+            and (not need_grad or (aenc is not None and n_tau in (1, 2, 4, 8, 16, 32))))
+
+
+class _CriticTrunkUmma(torch.autograd.Function):
+    """The critic's quantile trunk (ACIQN:410-480) as three tcgen05 kernels: K10 forward (cosine embedding generated in
+    the kernel; in a differentiable pass it also leaves the operand images), K11 the backward chain (d feats, d aenc and
+    the dP images), K12 every weight / bias gradient from the images.  When only d z / d aenc is asked for — the actor
+    update, AGENT:420-427 — K11 runs its short form and K12 not at all."""
+
+    @staticmethod
+    def forward(ctx, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau, tau_in, draw, ws_key):
+        feats, aenc = feats.contiguous(), aenc.contiguous()
+        need = ctx.needs_input_grad
+        save = any(need[:10])
+        ws = _lib.critic_workspace(ws_key, feats.device)
+        seed, counter, counter_dev, cvar = draw
+        out = _lib.critic_forward(feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo.reshape(-1), bo, n_tau, ws, tau_in=tau_in,
+                                  seed=seed, counter=counter, counter_dev=counter_dev, cvar=cvar, save=save)
+        z, tau = out[0], out[1]
+        if save:
+            fmax = feats.amax().reshape(1) if need[0] or any(need[2:10]) else feats.new_zeros(1)
+            ctx.save_for_backward(feats, aenc, Wh, Wh2, wo, fmax, *out[2])
+        ctx.n_tau = n_tau
+        ctx.mark_non_differentiable(tau)
+        return z, tau
+
+    @staticmethod
+    def backward(ctx, dz, _dtau):
+        feats, aenc, Wh, Wh2, wo, fmax, cos_i, h1_i, h2_i, r3_i = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        n_tau = ctx.n_tau
+        g = [None] * 14
+        dz = dz.contiguous()
+        if need[0] or any(need[2:10]):
+            daenc, dfeats, (dp3, dp2, dp1, aux), scales = _lib.critic_backward(dz, r3_i, h2_i, h1_i, feats, aenc, Wh, Wh2,
+                                                                              wo.reshape(-1), n_tau, fmax=fmax)
+            d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo = _lib.critic_wgrad(dp3, dp2, dp1, aux, cos_i, h1_i, h2_i, r3_i,
+                                                                           scales, feats.shape[0], n_tau)
+            g[0], g[1] = dfeats, daenc
+            g[2], g[3], g[4], g[5], g[6], g[7], g[8] = d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo.view_as(wo)
+            g[9] = dz.sum().reshape(1)
+        else:
+            g[1] = _lib.critic_backward(dz, r3_i, h2_i, None, feats, aenc, Wh, Wh2, wo.reshape(-1), n_tau, full=False)
+        return tuple(g)
+
+
+def critic_trunk_umma(feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau, tau_in, draw, ws_key):
+    """-> z (B, N), tau (B, N).  ``tau_in`` (B, N) injects the fractions, else ``draw`` = (seed, counter, counter_dev,
+    cvar) of the network's Philox tau stream (the same draw as K3)."""
+    if not feats.is_cuda:
+        raise RuntimeError("critic_trunk_umma runs on CUDA only (no CPU fallback)")
+    if torch.is_grad_enabled() and (feats.requires_grad or aenc.requires_grad or Wc.requires_grad):
+        return _CriticTrunkUmma.apply(feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, int(n_tau), tau_in, draw, ws_key)
+    ws = _lib.critic_workspace(ws_key, feats.device)
+    seed, counter, counter_dev, cvar = draw
+    return _lib.critic_forward(feats.contiguous(), aenc.contiguous(), Wc, bc, Wh, bh, Wh2, bh2, wo.reshape(-1), bo,
+                               int(n_tau), ws, tau_in=tau_in, seed=seed, counter=counter, counter_dev=counter_dev,
+                               cvar=cvar)
+
+
 def critic_trunk(cos, feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo, bo, n_tau):
     """cos (B*N, n_cos), feats (B, D1), aenc (B, D2) and the four layers' parameters -> z (B, N)."""
     if not cos.is_cuda:

@@ -567,6 +567,25 @@ ASVRL_API int asvrl_critic_wgrad(const void* dp3_img, const void* dp2_img, const
                                  void* stream);
 ASVRL_API int asvrl_critic_wgrad_status(int* status_out);
 
+/* K11 — the backward chain of the critic trunk (the activation half of the autograd backward of ACIQN:453-480) for all
+ * batch * n_tau quantile rows in ONE persistent tcgen05 launch: dz -> dP3 -> dH2 = dP3 Wh2 -> dP2, daenc -> dH1 = dP2 Wh
+ * -> dP1, dfeats, reading the operand images asvrl_critic_forward saved.  n_tau: a power of two <= 32.
+ *   dz [B*N]; feats [B][256], aenc [B][128], wo [128], wh [128][256], wh2 [128][128] as in asvrl_critic_forward;
+ *   workspace: asvrl_critic_backward_workspace() bytes (packed Wh2^T | Wh^T image; `repack` != 0 rebuilds it);
+ *   daenc [B][128] = d loss / d aenc; fmax (device, nullable): max over feats, sets dP1's power-of-two scale (NULL: 2^-8).
+ *   Full pass: dfeats [B][256], dp3_img / dp2_img / dp1_img / aux_img ([tile][2 | 2 | 4 | 1] chunks, 128-byte aligned)
+ *   and scales[2] (device) for asvrl_critic_wgrad — all set; or all NULL (with h1_img NULL allowed): the actor
+ *   update's pass (AGENT:420-427), which needs d z / d aenc only and stops after dP2. */
+ASVRL_API long asvrl_critic_backward_workspace(void);
+ASVRL_API int asvrl_critic_backward(const float* dz, const void* r3_img, const void* h2_img,
+                                    const void* h1_img /* nullable */, const float* feats, const float* aenc,
+                                    const float* wh, const float* wh2, const float* wo,
+                                    const float* fmax /* nullable */, int batch, int n_tau, int repack,
+                                    void* workspace, float* daenc, float* dfeats /* nullable */,
+                                    void* dp3_img, void* dp2_img, void* dp1_img, void* aux_img, float* scales,
+                                    void* stream);
+ASVRL_API int asvrl_critic_backward_status(int* status_out);
+
 #ifdef __cplusplus
 }
 #endif

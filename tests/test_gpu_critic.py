@@ -175,3 +175,92 @@ def test_wgrad_from_images(M):
         scale = w.abs().max().item()
         err = (a.double() - w).abs().max().item()
         assert err <= 3e-6 * scale, f"{name}: max abs err {err:.3e} at scale {scale:.3e}"
+
+
+def _autograd64(tau, feats, aenc, ps, dz, gates=None):
+    """float64 autograd of the trunk: gradients of feats, aenc and the eight parameters for upstream dz.
+    ``gates``: (g1, g2, g3) boolean ReLU gates to use instead of the float64 path's own (see the test below);
+    also returns the float64 pre-activations."""
+    f64 = feats.double().requires_grad_(True)
+    a64 = aenc.double().requires_grad_(True)
+    p64 = [p.detach().double().requires_grad_(True) for p in ps]
+    Wc, bc, Wh, bh, Wh2, bh2, wo, bo = p64
+    B, N = tau.shape
+    pis = torch.tensor([np.pi * i for i in range(64)], dtype=torch.float32, device=tau.device)
+    cos = torch.cos((tau.reshape(B, N, 1) * pis.view(1, 1, 64)).double())
+    act = (lambda P, i: torch.relu(P)) if gates is None else (lambda P, i: P * gates[i].reshape(P.shape))
+    P1 = cos @ Wc.t() + bc
+    H1 = f64.unsqueeze(1) * act(P1, 0)
+    P2 = H1 @ Wh.t() + bh
+    H2 = a64.unsqueeze(1) * act(P2, 1)
+    P3 = H2 @ Wh2.t() + bh2
+    z = act(P3, 2) @ wo + bo
+    z.backward(dz.double())
+    return f64.grad, a64.grad, [p.grad for p in p64], [P.detach() for P in (P1, P2, P3)]
+
+
+def _grad_check(name, got, want, tol=1e-5):
+    scale = want.abs().max().item()
+    err = (got.double() - want).abs().max().item()
+    assert err <= tol * scale + 1e-12, f"{name}: max abs err {err:.3e} at scale {scale:.3e} ({err / max(scale, 1e-300):.2e} rel)"
+
+
+@pytest.mark.parametrize("B,N,fs", [(1024, 32, 1.0), (64, 8, 1.0), (37, 8, 1.0), (512, 32, 150.0), (2048, 16, 1.0), (300, 1, 1.0)])
+def test_backward_chain_and_wgrad_match_float64_autograd(B, N, fs):
+    """K10 (SAVE) -> K11 -> K12 against float64 autograd of the same trunk, gradients to 1e-5 of each tensor's scale.
+
+    ReLU gates of pre-activations within rounding error of zero differ between ANY float32-level evaluation and
+    float64 (torch's own float32 autograd included), and one flipped gate moves a weight gradient by ~1 / sqrt(B N) of
+    its scale.  So, as for the env step's flags, the gates are compared separately — they must agree with float64
+    wherever |pre-activation| exceeds a 2e-5 margin of the layer's scale — and the gradient arithmetic is checked with
+    the float64 path using the product's gates."""
+    c = _critic()
+    tau, feats, aenc = _inputs(B, N, 5 * B + N, feat_scale=fs)
+    ps = _params(c)
+    g = torch.Generator(device=DEV).manual_seed(B)
+    dz = (torch.randn((B, N), device=DEV, generator=g) * (1.0 / (B * N))).contiguous()   # the scale of a mean loss
+    _, _, (cos_i, h1_i, h2_i, r3_i) = _run(c, tau, feats, aenc, save=True)
+    daenc, dfeats, (dp3, dp2, dp1, aux), scales = _lib.critic_backward(dz, r3_i, h2_i, h1_i, feats, aenc, ps[2], ps[4], ps[6], N,
+                                                                      fmax=feats.amax().reshape(1))
+    grads = _lib.critic_wgrad(dp3, dp2, dp1, aux, cos_i, h1_i, h2_i, r3_i, scales, B, N)
+    daenc_t = _lib.critic_backward(dz, r3_i, h2_i, None, feats, aenc, ps[2], ps[4], ps[6], N, full=False)
+    torch.cuda.synchronize()
+    _lib.critic_backward_status()
+    _lib.critic_wgrad_status()
+    M = B * N
+    Ps = _autograd64(tau, feats, aenc, ps, dz)[3]
+    fb = (feats > 0).unsqueeze(1).expand(B, N, 256).reshape(M, 256)
+    ab = (aenc > 0).unsqueeze(1).expand(B, N, 128).reshape(M, 128)
+    gates, flips = [], 0
+    fe = feats.double().unsqueeze(1).expand(B, N, 256).reshape(M, 256)
+    ae = aenc.double().unsqueeze(1).expand(B, N, 128).reshape(M, 128)
+    for img, P, known, fac in ((h1_i, Ps[0].reshape(M, 256), fb, fe), (h2_i, Ps[1].reshape(M, 128), ab, ae),
+                               (r3_i, Ps[2].reshape(M, 128), None, None)):
+        gate = _decode(img)[:M] > 0
+        if known is not None:
+            # the saved product factor * relu(P) says nothing where the factor is zero, or where the product is below the
+            # two-piece fp16 image's resolution (2^-25); there dP = dH . factor . gate is zero / negligible either way
+            # (an image entry > 0 always is the product's open gate; a pre-activation inside the rounding margin whose
+            # product vanished is a closed gate of the product — one of the flips counted below)
+            gate = gate | (~gate & (fac * P.abs() <= 1e-7) & (P > 2e-5 * P.abs().max()))
+        diff = gate != (P > 0)
+        flips += int(diff.sum())
+        assert float((P.abs() * diff).max()) <= 2e-5 * float(P.abs().max()), "a gate differs outside the rounding margin"
+        gates.append(gate.double())
+    assert flips <= 1e-4 * 4 * M * 128 + 8, f"{flips} flipped gates"   # 4 M 128 gates; ~1e-4 of them lie inside the margin
+    wf, wa, wp, _ = _autograd64(tau, feats, aenc, ps, dz, gates)
+    # feats and aenc are ReLU outputs: where they are exactly zero the producing gate is closed and the gradient is
+    # discarded downstream (ACIQN:9-13, 441-451); K11 returns 0 there (it divides the saved product by the factor)
+    wf, wa = wf * (feats > 0), wa * (aenc > 0)
+    # K11 recovers relu(P + b) as H / factor from the two-piece fp16 image of H (absolute resolution 2^-25): entries
+    # whose factor is below ~1e-2 of the tensor's scale lose relative accuracy in proportion; what flows on into the
+    # parameter gradients is factor-weighted, so that is the second yardstick
+    for name, got, want, fac in (("dfeats", dfeats, wf, feats), ("daenc", daenc, wa, aenc), ("daenc (actor pass)", daenc_t, wa, aenc)):
+        big = fac >= 1e-2 * fac.max()
+        _grad_check(name + " where the factor is >= 1e-2 of its scale", got * big, want * big)
+        _grad_check(name + " x factor", got * fac, want * fac)
+        _grad_check(name + " overall", got, want, tol=2e-2)
+    d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo = grads
+    for name, got, want in (("d_wc", d_wc, wp[0]), ("d_bc", d_bc, wp[1]), ("d_wh", d_wh, wp[2]), ("d_bh", d_bh, wp[3]),
+                            ("d_wh2", d_wh2, wp[4]), ("d_bh2", d_bh2, wp[5]), ("d_wo", d_wo, wp[6])):
+        _grad_check(name, got, want)

@@ -81,8 +81,17 @@ def _critic_inputs(B, seed):
     return (own, obj, mask), act
 
 
+@pytest.mark.parametrize("umma", [False, True])
 @pytest.mark.parametrize("B,N", [(64, 8), (1024, 32), (3, 5)])
-def test_fused_critic_matches_module_path(B, N):
+def test_fused_critic_matches_module_path(B, N, umma, monkeypatch):
+    """umma = False: K3 + cuBLAS + K5 (the same sgemm as the module path: agreement to rounding).  umma = True: K10 / K11 /
+    K12 where they apply (>= 4096 quantile rows): an independent evaluation order, so ReLU gates of pre-activations
+    inside the rounding margin differ from the torch float32 path's (as that path's differ from float64), and one such
+    gate moves a weight gradient by ~1 / sqrt(B N) of its scale — the gradient arithmetic itself is pinned to 1e-5 with
+    matched gates in tests/test_gpu_critic.py; here the bar on gradients is 2e-4."""
+    from distributional_rl_decision_and_control_b200.policy import iqn_ops
+    monkeypatch.setattr(iqn_ops, "UMMA_TRUNK", umma)
+    gtol = 2e-4 if umma and B * N >= iqn_ops.UMMA_TRUNK_MIN_ROWS else 2e-5
     crit = Critic(7, 5, 5, 56, 40, 256, 128, 2, device=DEV, seed=101).to(DEV)
     x, act = _critic_inputs(B, 7 + B)
     taus = torch.rand((B, N), device=DEV, generator=torch.Generator(device=DEV).manual_seed(1))
@@ -101,13 +110,13 @@ def test_fused_critic_matches_module_path(B, N):
     crit.fused_tower = True        # K6 tower + K5 trunk
     z1, da1, g1 = run(crit.forward_fused)
     close(z1, z0, "quantiles")
-    close(da1, da0, "d/d actions")
+    close(da1, da0, "d/d actions", rtol=gtol / 2)
     for n in g0:
-        close(g1[n], g0[n], f"grad {n}", rtol=2e-5)
+        close(g1[n], g0[n], f"grad {n}", rtol=gtol)
     # the actor update's variant: the same d/d actions, no parameter gradients at all
     z2, da2, g2 = run(crit.forward_fused, param_grads=False)
     assert torch.equal(z2, z1)
-    close(da2, da0, "d/d actions (actor pass)")
+    close(da2, da0, "d/d actions (actor pass)", rtol=gtol / 2)
     assert all(v is None for v in g2.values())
 
 

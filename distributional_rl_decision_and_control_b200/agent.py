@@ -373,7 +373,11 @@ class Agent():
         self.critic_optimizer.zero_grad(set_to_none=True)
         fused = self.fused_trunk
         with torch.no_grad():
-            next_actions = target.actor(next_states)                     # AGENT:396
+            if fused and target.actor._fused_policy_ok(next_states):
+                # K9 with eps = 0: tower, both dense layers, head and atan of the target actor in one tcgen05 launch
+                next_actions = target.actor.act_eps_greedy(next_states, 0.0, 0, None)   # AGENT:396
+            else:
+                next_actions = target.actor(next_states)                 # AGENT:396
             crit_t = target.critic.forward_fused if fused else target.critic
             z_next, _ = crit_t(next_states, next_actions, N, taus=taus.get("target"))  # AGENT:399
         crit = local.critic.forward_fused if fused else local.critic

@@ -30,6 +30,7 @@ def _unit_scale(B, D, device):
         if len(_UNIT) > 64:
             _UNIT.clear()
         t = _UNIT[key] = torch.ones((B, D), dtype=torch.float32, device=device)
+        t._asvrl_unit = True  # lets K5's backward regroup the rows (iqn_ops._LinearScaleRelu)
     return t
 
 

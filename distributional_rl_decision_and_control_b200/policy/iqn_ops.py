@@ -76,6 +76,8 @@ def _wgrad(d_out, x, splits=64):
     product (K = M, a 128 x 256 output) on a handful of CTAs (~110 us at C3), so the contraction is
     split into `splits` batched GEMMs and the partial products are summed (~35-50 us)."""
     M = d_out.shape[0]
+    if x.shape[1] <= 8:   # a 2-column input (the action encoder): x^T d_out is a thin product cuBLAS runs well
+        return (x.t() @ d_out).t()
     if M >= 4096 and M % splits == 0:
         part = torch.bmm(d_out.view(splits, M // splits, -1).transpose(1, 2), x.view(splits, M // splits, -1))
         return part.sum(0)
@@ -281,7 +283,12 @@ class _LinearScaleRelu(torch.autograd.Function):
         x, W, bias, scale, pre = ctx.saved_tensors
         need = ctx.needs_input_grad
         want_dpre = need[0] or need[1]
-        dpre, dscale, dbias = _lib.iqn_scale_relu_bwd(dout.contiguous(), pre, bias, scale, ctx.n_tau,
+        n_tau, B = ctx.n_tau, scale.shape[0]
+        if n_tau == 1 and not need[3] and getattr(scale, "_asvrl_unit", False) and B % 32 == 0:
+            # a plain Linear + ReLU over B rows (unit scale, no d scale): K5 walks them as B / 32 groups of 32 rows, so the
+            # bias gradient is 16 x fewer per-CTA partials for the last CTA to add
+            scale, n_tau = scale[:B // 32], 32
+        dpre, dscale, dbias = _lib.iqn_scale_relu_bwd(dout.contiguous(), pre, bias, scale, n_tau,
                                                       want_dpre=want_dpre, want_dscale=need[3], want_dbias=need[2])
         dx = dpre @ W if need[0] else None
         dW = _wgrad(dpre, x) if need[1] else None

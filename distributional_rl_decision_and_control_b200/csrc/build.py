@@ -35,7 +35,8 @@ def build(force=False, verbose=False):
     if not (force or stale()):
         return SO
     srcs = [os.path.join(HERE, s) for s in SOURCES if os.path.exists(os.path.join(HERE, s))]
-    cmd = [nvcc()] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + srcs
+    extra = os.environ.get("ASVRL_NVCC_FLAGS", "").split()  # e.g. -DCF_TRACE for profiles/probes/k10_trace.py
+    cmd = [nvcc()] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", SO] + srcs
     r = subprocess.run(cmd, cwd=HERE, capture_output=True, text=True)
     if verbose or r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)

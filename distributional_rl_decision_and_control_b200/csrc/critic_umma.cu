@@ -18,10 +18,12 @@
 // Mapping.  One CTA per SM walks 128-row tiles (tile = blockIdx.x + i * gridDim.x); even and odd tiles of a CTA
 // run in two SLOTS, each with its own 8 epilogue warps, two 32 KB operand buffers and 256 TMEM columns, so one
 // slot's CUDA-core work overlaps the other's tensor work.  20 warps:
-//   warp 0      W producer: one thread streams the packed weight chunks (32 KB = hi | lo tile of 128 out x 64 k)
-//               into a 3-stage ring with cp.async.bulk, in the MMA thread's consumption order
-//   warp 1      MMA issuer: one thread, 12 tcgen05.mma per chunk; static order per tile pair
-//               L1(A) L1(B) L2(A) L2(B) L3(A) L3(B)
+//   warps 0, 3  W producers, one per slot: one thread streams the packed weights as half chunks (16 KB = hi | lo tile
+//               of 64 out x 64 k) into the slot's own 3-stage ring with cp.async.bulk — a slot consumes its weights in
+//               a fixed order, whatever the other slot does
+//   warp 1      MMA issuer: one thread POLLS both slots (mbarrier.test_wait) and issues the next half chunk (12
+//               tcgen05.mma, N = 64) of whichever slot has its operand and its weights ready, so one slot's tensor work
+//               runs under the other's CUDA-core work instead of the two marching in lock step
 //   warp 2      TMEM allocation
 //   warps 4-11  slot 0, warps 12-19 slot 1: warp e of a slot owns TMEM lanes 32 (e % 4) .. and the column half
 //               e / 4.  Per tile: E0 tau -> cos -> A chunk; E1 D1 -> feats * relu(. + bc) -> 4 A chunks of layer 2;
@@ -43,19 +45,36 @@ constexpr int CF_ROWS = 128;                       // rows per tile = UMMA M
 constexpr int CF_NCOS = 64, CF_W = 256, CF_H = 128;
 constexpr int CF_TILE_B = CF_ROWS * 128;           // one fp16 piece of a [128 x 64] chunk: 16 KB
 constexpr int CF_CHUNK_B = 2 * CF_TILE_B;          // hi | lo
-constexpr int CF_WSTAGES = 3;
+constexpr int CF_WSTAGES = 3;                      // per slot, of half chunks
+constexpr int CF_HALF_B = CF_CHUNK_B / 2;          // hi | lo of 64 out x 64 k
+constexpr int CF_PIECE_B = CF_TILE_B / 2;          // 64 rows of one fp16 piece
 constexpr int CF_W_CHUNKS = 8;                     // Wc: 2 (n halves), Wh: 4 (k chunks), Wh2: 2
 constexpr int CF_IMAGE_B = CF_W_CHUNKS * CF_CHUNK_B;   // 256 KB packed weights
 constexpr float CF_WSCALE = 64.0f, CF_WUNSCALE = 1.0f / 64.0f;
 
 constexpr int CF_OFF_X = 0;                                        // [slot][buffer] operand chunks
 constexpr int CF_OFF_WR = 4 * CF_CHUNK_B;                          // weight ring
-constexpr int CF_OFF_BAR = CF_OFF_WR + CF_WSTAGES * CF_CHUNK_B;    // 229376
-constexpr int CF_NBAR = 2 * 8 + 2 * CF_WSTAGES;                    // per slot a_full[2] x_free[2] d_full[4]; w_full, w_empty
+constexpr int CF_OFF_BAR = CF_OFF_WR + 2 * CF_WSTAGES * CF_HALF_B; // 229376
+constexpr int CF_NBAR = 2 * (8 + 2 * CF_WSTAGES);                  // per slot a_full[2] x_free[2] d_full[4] w_full[3] w_empty[3]
 constexpr int CF_OFF_MISC = CF_OFF_BAR + CF_NBAR * 8;              // tmem slot, abort flag
 constexpr int CF_OFF_ZPART = CF_OFF_MISC + 16;                     // [slot][128] floats
 constexpr int CF_SMEM_B = CF_OFF_ZPART + 2 * CF_ROWS * 4 + 1024;   // + alignment slack
 static_assert(CF_SMEM_B <= 232448, "K10 shared memory");
+
+#ifdef CF_TRACE
+// timeline of CTA 0 for profiles/probes/k10_trace.py: [writer][event] = (globaltimer << 8) | tag
+__device__ unsigned long long cf_trace_buf[8][2048];
+__device__ int cf_trace_n[8];
+#define CF_TR(writer, tag)                                                                              \
+  do {                                                                                                   \
+    if (blockIdx.x == 0) {                                                                               \
+      const int n_ = cf_trace_n[writer];                                                                 \
+      if (n_ < 2048) { cf_trace_buf[writer][n_] = (um_globaltimer() << 8) | (unsigned)(tag); cf_trace_n[writer] = n_ + 1; } \
+    }                                                                                                    \
+  } while (0)
+#else
+#define CF_TR(writer, tag) do {} while (0)
+#endif
 
 struct CriticArgs {
   const float* tau_in;                        // [rows] or null (Philox stream 3)
@@ -111,14 +130,15 @@ critic_forward_kernel(const CriticArgs a) {
   extern __shared__ __align__(1024) unsigned char cf_raw[];
   unsigned char* base = cf_raw + ((1024u - (um_smem(cf_raw) & 1023u)) & 1023u);
   const uint32_t sb = um_smem(base);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform: role code stays in the uniform datapath
 
   const uint32_t bar0 = sb + CF_OFF_BAR;
-  auto bar_a_full = [&](int s, int x) { return bar0 + 8u * (8 * s + x); };
-  auto bar_x_free = [&](int s, int x) { return bar0 + 8u * (8 * s + 2 + x); };
-  auto bar_d_full = [&](int s, int d) { return bar0 + 8u * (8 * s + 4 + d); };
-  auto bar_w_full = [&](int st) { return bar0 + 8u * (16 + st); };
-  auto bar_w_empty = [&](int st) { return bar0 + 8u * (16 + CF_WSTAGES + st); };
+  auto bar_a_full = [&](int s, int x) { return bar0 + 8u * (14 * s + x); };
+  auto bar_x_free = [&](int s, int x) { return bar0 + 8u * (14 * s + 2 + x); };
+  auto bar_d_full = [&](int s, int d) { return bar0 + 8u * (14 * s + 4 + d); };
+  auto bar_w_full = [&](int s, int st) { return bar0 + 8u * (14 * s + 8 + st); };
+  auto bar_w_empty = [&](int s, int st) { return bar0 + 8u * (14 * s + 8 + CF_WSTAGES + st); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(base + CF_OFF_MISC);
   volatile uint32_t* abort_flag = reinterpret_cast<volatile uint32_t*>(base + CF_OFF_MISC + 4);
   float* zpart = reinterpret_cast<float*>(base + CF_OFF_ZPART);
@@ -130,10 +150,10 @@ critic_forward_kernel(const CriticArgs a) {
         um_mbar_init(bar_x_free(s, x), 1);
       }
       for (int d = 0; d < 4; ++d) um_mbar_init(bar_d_full(s, d), 1);
-    }
-    for (int st = 0; st < CF_WSTAGES; ++st) {
-      um_mbar_init(bar_w_full(st), 1);
-      um_mbar_init(bar_w_empty(st), 1);
+      for (int st = 0; st < CF_WSTAGES; ++st) {
+        um_mbar_init(bar_w_full(s, st), 1);
+        um_mbar_init(bar_w_empty(s, st), 1);
+      }
     }
     *abort_flag = 0u;
     um_mbar_init_fence();
@@ -142,104 +162,121 @@ critic_forward_kernel(const CriticArgs a) {
   um_tc_before();
   __syncthreads();
   um_tc_after();
-  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   const int n_my = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   // A timed-out wait sets the CTA's abort flag and the status word; every later wait then returns at once and the
   // roles run their loops to the end on garbage, so no named barrier is left short of a participant.
   auto wait = [&](uint32_t bar, uint32_t parity, int code) { (void)um_mbar_wait(bar, parity, abort_flag, a.status, code); };
 
-  if (warp == 0) {
-    // =============== W producer ===============
+  if (warp == 0 || warp == 3) {
+    // =============== W producers: slot 0 (warp 0), slot 1 (warp 3) ===============
     if (lane == 0) {
-      int pos = 0;
-      auto emit = [&](int first, int n) {
-        for (int c = first; c < first + n; ++c, ++pos) {
-          const int st = pos % CF_WSTAGES;
-          if (pos >= CF_WSTAGES) wait(bar_w_empty(st), (uint32_t)((pos / CF_WSTAGES) - 1) & 1u, UM_TIMEOUT_RING);
-          um_mbar_arrive_expect_tx(bar_w_full(st), CF_CHUNK_B);
-          um_bulk_g2s(sb + CF_OFF_WR + st * CF_CHUNK_B, a.image + (size_t)c * CF_CHUNK_B, CF_CHUNK_B, bar_w_full(st));
+      const int s = warp == 0 ? 0 : 1;
+      int wpos = 0;
+      for (int i = s; i < n_my; i += 2)
+        for (int h = 0; h < 2 * CF_W_CHUNKS; ++h, ++wpos) {   // half chunk h: chunk h / 2, output rows [64 (h & 1), +64)
+          const int st = wpos % CF_WSTAGES;
+          if (wpos >= CF_WSTAGES) wait(bar_w_empty(s, st), (uint32_t)((wpos / CF_WSTAGES) - 1) & 1u, UM_TIMEOUT_RING);
+          um_mbar_arrive_expect_tx(bar_w_full(s, st), CF_HALF_B);
+          CF_TR(3 + s, h);
+          const unsigned char* src = a.image + (size_t)(h >> 1) * CF_CHUNK_B + (h & 1) * CF_PIECE_B;
+          const uint32_t dst = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st) * CF_HALF_B;
+          um_bulk_g2s(dst, src, CF_PIECE_B, bar_w_full(s, st));                              // hi
+          um_bulk_g2s(dst + CF_PIECE_B, src + CF_TILE_B, CF_PIECE_B, bar_w_full(s, st));     // lo
         }
-      };
-      for (int i = 0; i < n_my; i += 2) {
-        const bool two = i + 1 < n_my;
-        emit(0, 2); if (two) emit(0, 2);
-        emit(2, 4); if (two) emit(2, 4);
-        emit(6, 2); if (two) emit(6, 2);
-      }
     }
   } else if (warp == 1) {
-    // =============== MMA issuer ===============
-    if (lane == 0) {
-      constexpr uint32_t idesc = um_idesc_f16(CF_ROWS, CF_H);
-      int pos = 0;
-      uint32_t u[2] = {0u, 0u};
-      auto xaddr = [&](int s, uint32_t uu) { return sb + CF_OFF_X + (uint32_t)(2 * s + (int)(uu & 1u)) * CF_CHUNK_B; };
-      auto use_wait = [&](int s, uint32_t uu) {
-        wait(bar_a_full(s, (int)(uu & 1u)), (uu >> 1) & 1u, UM_TIMEOUT_INPUT);
-        um_tc_after();
-      };
-      auto use_done = [&](int s, bool mma) {
-        const uint32_t x = u[s] & 1u;
-        if (mma) um_commit(bar_x_free(s, (int)x)); else um_mbar_arrive(bar_x_free(s, (int)x));
-        ++u[s];
-      };
-      auto chunk = [&](uint32_t ax, uint32_t d_tmem, bool first) {
-        const int st = pos % CF_WSTAGES;
-        wait(bar_w_full(st), (uint32_t)(pos / CF_WSTAGES) & 1u, UM_TIMEOUT_RING);
-        um_tc_after();
-        const uint32_t ah = ax, al = ax + CF_TILE_B;
-        const uint32_t wh = sb + CF_OFF_WR + st * CF_CHUNK_B, wl = wh + CF_TILE_B;
+    // =============== MMA issuer: polls both slots ===============
+    // The whole warp runs the (uniform) scheduling loop; one elected lane issues the tcgen05 instructions.
+    {
+      constexpr uint32_t idesc = um_idesc_f16(CF_ROWS, 64);
+      constexpr int HC = CF_W_CHUNKS + (SAVE ? 2 : 0);       // chunks of a tile (+ SAVE: the two R3 uses, no MMA)
+      constexpr uint32_t USES = SAVE ? 9u : 7u;               // operand-buffer uses of a tile
+      int it0 = 0, it1 = 1, hc0 = 0, hc1 = 0, wp0 = 0, wp1 = 0;
+      uint32_t ub0 = 0u, ub1 = 0u;
+      uint64_t t_last = 0;
+      uint32_t idle = 0;
+      while (it0 < n_my || it1 < n_my) {
+        bool progressed = false;
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {   // 4 x (K = 16 fp16 = 32 B) per 128-byte row
-          const uint32_t o = ks * 32;
-          um_mma_f16(d_tmem, um_desc_sw128(al + o), um_desc_sw128(wh + o), idesc, (first && ks == 0) ? 0u : 1u);  // small terms first
-          um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wl + o), idesc, 1u);
-          um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wh + o), idesc, 1u);
-        }
-        um_commit(bar_w_empty(st));
-        ++pos;
-      };
-      auto S1 = [&](int s) {   // cos x Wc^T, two N = 128 halves
-        const uint32_t d = tmem + (uint32_t)(256 * s);
-        if (SAVE && u[s] > 0u)
-          for (int j = 0; j < 2; ++j) {   // the previous tile's two R3 chunks passed through the buffers without an MMA
-            use_wait(s, u[s]);
-            use_done(s, false);
+        for (int s = 0; s < 2; ++s) {
+          int& it = s ? it1 : it0;
+          int& hc = s ? hc1 : hc0;
+          int& wpos = s ? wp1 : wp0;
+          uint32_t& u0 = s ? ub1 : ub0;
+          if (it >= n_my) continue;
+          const int c = hc;
+          auto ready = [&](uint32_t use) {
+            return __all_sync(0xffffffffu, um_mbar_test(bar_a_full(s, (int)(use & 1u)), (use >> 1) & 1u) != 0u) != 0;
+          };
+          bool go = true;
+          uint32_t use;
+          if (SAVE && c >= CF_W_CHUNKS) {   // an R3 chunk passes through its buffer: free it once it is published
+            use = u0 + 7u + (uint32_t)(c - CF_W_CHUNKS);
+            go = ready(use);
+            if (go && um_elect()) um_mbar_arrive(bar_x_free(s, (int)(use & 1u)));
+          } else {
+            // operand use of chunk c: the cos chunk serves chunks 0 and 1, then one use per chunk
+            use = u0 + (uint32_t)(c < 2 ? 0 : c - 1);
+            if (c != 1) {
+              go = ready(use);
+              // layer 2 accumulates into columns [0,128): both chunks built from them must exist first
+              if (go && c == 2) go = ready(use + 1u);
+            }
+            const int st0 = wpos % CF_WSTAGES, st1 = (wpos + 1) % CF_WSTAGES;
+            if (go) go = __all_sync(0xffffffffu, um_mbar_test(bar_w_full(s, st0), (uint32_t)(wpos / CF_WSTAGES) & 1u) != 0u) != 0;
+            if (go) go = __all_sync(0xffffffffu, um_mbar_test(bar_w_full(s, st1), (uint32_t)((wpos + 1) / CF_WSTAGES) & 1u) != 0u) != 0;
+            if (go) {
+              um_tc_after();
+              if (lane == 0) CF_TR(0, s * 32 + c);
+              const uint32_t d0 = tmem + (uint32_t)(256 * s + ((c == 1 || c >= 6) ? 128 : 0)), d1 = d0 + 64u;
+              const bool first = c < 3 || c == 6;
+              const uint32_t ah = sb + CF_OFF_X + (uint32_t)(2 * s + (int)(use & 1u)) * CF_CHUNK_B, al = ah + CF_TILE_B;
+              const uint32_t wh0 = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st0) * CF_HALF_B, wl0 = wh0 + CF_PIECE_B;
+              const uint32_t wh1 = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st1) * CF_HALF_B, wl1 = wh1 + CF_PIECE_B;
+              if (um_elect()) {
+                // the two 64-column halves are independent accumulation chains: alternate between them
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {   // 4 x (K = 16 fp16 = 32 B) per 128-byte row
+                  const uint32_t o = ks * 32;
+                  const uint32_t acc0 = (first && ks == 0) ? 0u : 1u;
+                  um_mma_f16(d0, um_desc_sw128(al + o), um_desc_sw128(wh0 + o), idesc, acc0);  // small terms first
+                  um_mma_f16(d1, um_desc_sw128(al + o), um_desc_sw128(wh1 + o), idesc, acc0);
+                  um_mma_f16(d0, um_desc_sw128(ah + o), um_desc_sw128(wl0 + o), idesc, 1u);
+                  um_mma_f16(d1, um_desc_sw128(ah + o), um_desc_sw128(wl1 + o), idesc, 1u);
+                  um_mma_f16(d0, um_desc_sw128(ah + o), um_desc_sw128(wh0 + o), idesc, 1u);
+                  um_mma_f16(d1, um_desc_sw128(ah + o), um_desc_sw128(wh1 + o), idesc, 1u);
+                }
+                um_commit(bar_w_empty(s, st0));
+                um_commit(bar_w_empty(s, st1));
+                if (c >= 1) um_commit(bar_x_free(s, (int)(use & 1u)));
+                if (c == 0) um_commit(bar_d_full(s, 0));
+                else if (c == 1) um_commit(bar_d_full(s, 1));
+                else if (c == 5) um_commit(bar_d_full(s, 2));
+                else if (c == 7) um_commit(bar_d_full(s, 3));
+              }
+              __syncwarp();
+              wpos += 2;
+            }
           }
-        use_wait(s, u[s]);
-        const uint32_t ax = xaddr(s, u[s]);
-        chunk(ax, d, true);
-        um_commit(bar_d_full(s, 0));
-        chunk(ax, d + 128u, true);
-        um_commit(bar_d_full(s, 1));
-        use_done(s, true);
-      };
-      auto S2 = [&](int s) {   // H1 x Wh^T into columns [0,128): both chunks built from them must exist first
-        const uint32_t d = tmem + (uint32_t)(256 * s);
-        use_wait(s, u[s]);
-        use_wait(s, u[s] + 1u);
-        for (int j = 0; j < 4; ++j) {
-          if (j >= 2) use_wait(s, u[s]);
-          chunk(xaddr(s, u[s]), d, j == 0);
-          use_done(s, true);
+          if (go) {
+            if (++hc == HC) { hc = 0; u0 += USES; it += 2; }
+            progressed = true;
+          }
         }
-        um_commit(bar_d_full(s, 2));
-      };
-      auto S3 = [&](int s) {   // H2 x Wh2^T into columns [128,256)
-        const uint32_t d = tmem + (uint32_t)(256 * s) + 128u;
-        for (int j = 0; j < 2; ++j) {
-          use_wait(s, u[s]);
-          chunk(xaddr(s, u[s]), d, j == 0);
-          use_done(s, true);
+        if (progressed) {
+          idle = 0;
+        } else if ((++idle & 1023u) == 0u) {
+          if (*abort_flag) break;
+          const uint64_t now = um_globaltimer();
+          if (idle == 1024u) t_last = now;
+          else if (now - t_last > UM_TIMEOUT_NS) {
+            *abort_flag = 1u;
+            if (a.status) atomicCAS(a.status, 0, UM_TIMEOUT_INPUT);
+            break;
+          }
         }
-        um_commit(bar_d_full(s, 3));
-      };
-      for (int i = 0; i < n_my; i += 2) {
-        const bool two = i + 1 < n_my;
-        S1(0); if (two) S1(1);
-        S2(0); if (two) S2(1);
-        S3(0); if (two) S3(1);
       }
     }
   } else if (warp >= 4) {
@@ -312,17 +349,22 @@ critic_forward_kernel(const CriticArgs a) {
         if (hh == 0 && a.tau_out) a.tau_out[m] = tau;
       }
       {
+        if (elected) CF_TR(1 + s, 0);
         const uint32_t xa = acquire();
+        if (elected) CF_TR(1 + s, 1);
         if (hh == 0) cf_cos_octets<0>(tau, xa + row_off, r7); else cf_cos_octets<32>(tau, xa + row_off, r7);
         publish(xa, SAVE ? a.cos_img + (size_t)tile * CF_CHUNK_B : nullptr);
+        if (elected) CF_TR(1 + s, 2);
       }
 
       // ---- E1: D1 -> H1 = feats[b] * relu(D1 / 64 + bc) -> the four A chunks of layer 2 ----
       wait(bar_d_full(s, 0), kpar, UM_TIMEOUT_ACC);
+      if (elected) CF_TR(1 + s, 3);
       for (int j = 0; j < 4; ++j) {
         if (j == 1) wait(bar_d_full(s, 1), kpar, UM_TIMEOUT_ACC);   // also: layer 1 has read the cos chunk's buffer
         um_tc_after();
         const uint32_t xa = acquire();
+        if (elected) CF_TR(1 + s, 4 + 2 * j);
         uint32_t v[32];
         um_tmem_ld32(lane_addr + (uint32_t)(64 * j + 32 * hh), v);
         um_tmem_ld_wait();
@@ -338,10 +380,12 @@ critic_forward_kernel(const CriticArgs a) {
           um_put8(xa + row_off + (uint32_t)(((4 * hh + t) ^ r7) << 4), CF_TILE_B, h);
         }
         publish(xa, SAVE ? a.h1_img + ((size_t)tile * 4 + j) * CF_CHUNK_B : nullptr);
+        if (elected) CF_TR(1 + s, 5 + 2 * j);
       }
 
       // ---- E2: D2 -> H2 = aenc[b] * relu(D2 / 64 + bh) -> the two A chunks of layer 3 ----
       wait(bar_d_full(s, 2), kpar, UM_TIMEOUT_ACC);
+      if (elected) CF_TR(1 + s, 12);
       for (int j = 0; j < 2; ++j) {
         um_tc_after();
         const uint32_t xa = acquire();
@@ -362,10 +406,12 @@ critic_forward_kernel(const CriticArgs a) {
           um_put8(xa + row_off + (uint32_t)(((4 * hh + t) ^ r7) << 4), CF_TILE_B, h);
         }
         publish(xa, SAVE ? a.h2_img + ((size_t)tile * 2 + j) * CF_CHUNK_B : nullptr);
+        if (elected) CF_TR(1 + s, 13 + j);
       }
 
       // ---- E3: D3 -> R3 = relu(D3 / 64 + bh2); z = R3 . wo + bo.  This warp: columns [64 hh, 64 hh + 64) ----
       wait(bar_d_full(s, 3), kpar, UM_TIMEOUT_ACC);
+      if (elected) CF_TR(1 + s, 15);
       um_tc_after();
       float acc = 0.0f;
       uint32_t xr[2] = {0u, 0u};
@@ -403,6 +449,7 @@ critic_forward_kernel(const CriticArgs a) {
       if (hh == 1) zpart[s * CF_ROWS + r] = acc;
       um_bar_sync(pair_bar, 64);
       if (hh == 0 && live) a.z[m] = acc + zpart[s * CF_ROWS + r] + bo;
+      if (elected) CF_TR(1 + s, 16);
     }
     if (SAVE && elected) um_bulk_wait<0>();
   }
@@ -481,6 +528,18 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
   }
   return check_launch("asvrl_critic_forward");
 }
+
+#ifdef CF_TRACE
+// debug build only: copies CTA 0's timeline out ([8][2048] events, [8] counts) and resets it
+extern "C" __attribute__((visibility("default"))) int asvrl_critic_forward_trace(unsigned long long* events, int* counts) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(events, cf_trace_buf, sizeof(unsigned long long) * 8 * 2048);
+  cudaMemcpyFromSymbol(counts, cf_trace_n, sizeof(int) * 8);
+  int zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  cudaMemcpyToSymbol(cf_trace_n, zero, sizeof zero);
+  return 0;
+}
+#endif
 
 // synchronous read of K10's device status word (0 = every bounded wait completed)
 extern "C" int asvrl_critic_forward_status(int* status_out) {

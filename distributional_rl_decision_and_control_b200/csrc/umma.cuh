@@ -19,6 +19,14 @@ __device__ __forceinline__ uint64_t um_globaltimer() {
   return t;
 }
 
+// one lane of the (converged) warp; the others skip.  Keeping the MMA warp converged and electing only around the
+// tcgen05 instructions lets the compiler hold descriptors and addresses in uniform registers (no R2UR per operand).
+__device__ __forceinline__ bool um_elect() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}\n" : "=r"(pred));
+  return pred != 0u;
+}
+
 // ---- mbarrier ----
 __device__ __forceinline__ void um_mbar_init(uint32_t mbar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(mbar), "r"(count) : "memory");
@@ -34,6 +42,14 @@ __device__ __forceinline__ void um_mbar_arrive_expect_tx(uint32_t mbar, uint32_t
 __device__ __forceinline__ uint32_t um_mbar_try(uint32_t mbar, uint32_t parity) {
   uint32_t done;
   asm volatile("{\n\t.reg .pred P;\n\tmbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\tselp.u32 %0, 1, 0, P;\n\t}\n"
+               : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
+  return done;
+}
+
+// non-blocking: has the phase of this parity completed?
+__device__ __forceinline__ uint32_t um_mbar_test(uint32_t mbar, uint32_t parity) {
+  uint32_t done;
+  asm volatile("{\n\t.reg .pred P;\n\tmbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\tselp.u32 %0, 1, 0, P;\n\t}\n"
                : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
   return done;
 }

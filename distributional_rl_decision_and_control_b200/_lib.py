@@ -71,7 +71,7 @@ _SIGNATURES = {
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
     "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
-                             + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p, vp, vp, vp, vp, vp]),
+                             + [C.c_int, C.c_int, C.c_int, C.c_int, vp, f32p, f32p, vp, vp, vp, vp, vp]),
     "asvrl_critic_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_critic_backward_workspace": (C.c_long, []),
     "asvrl_critic_backward": (C.c_int, [f32p, vp, vp, vp] + [f32p] * 6 + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p,
@@ -482,13 +482,14 @@ def critic_workspace(key, device):
 
 
 def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspace, tau_in=None, seed=0, counter=0,
-                   counter_dev=None, cvar=1.0, repack=True, save=False):
+                   counter_dev=None, cvar=1.0, repack=True, save=False, mean_hidden=False):
     """z (B, N), tau (B, N) [, images] of the IQN critic trunk in one persistent tcgen05 launch (K10).
-    ``save``: also return the operand images (cos, h1, h2, r3) the backward kernels read."""
+    ``save``: also return the operand images (cos, h1, h2, r3) the backward kernels read.  ``mean_hidden`` (n_tau = 32,
+    no aenc / wo / bo): z is (B, 128), the mean of the last hidden layer over the quantile rows (IQN's act)."""
     B = feats.shape[0]
     dev = feats.device
     f = torch.float32
-    z = torch.empty((B, n_tau), dtype=f, device=dev)
+    z = torch.empty((B, 128 if mean_hidden else n_tau), dtype=f, device=dev)
     tau = torch.empty((B, n_tau), dtype=f, device=dev) if tau_in is None else tau_in
     imgs = (None, None, None, None)
     if save:
@@ -498,7 +499,7 @@ def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspa
     rc = lib().asvrl_critic_forward(
         ptr(tau_in, f), int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), ptr(counter_dev, torch.int64), float(cvar),
         ptr(feats, f), ptr(aenc, f), ptr(wc, f), ptr(bc, f), ptr(wh, f), ptr(bh, f), ptr(wh2, f), ptr(bh2, f),
-        ptr(wo, f), ptr(bo, f), B, int(n_tau), int(bool(repack)), workspace.data_ptr(),
+        ptr(wo, f), ptr(bo, f), B, int(n_tau), int(bool(mean_hidden)), int(bool(repack)), workspace.data_ptr(),
         None if tau_in is not None else ptr(tau, f), ptr(z, f),
         *[None if t is None else t.data_ptr() for t in imgs], stream_ptr())
     check(rc, "asvrl_critic_forward")

@@ -281,8 +281,11 @@ class Agent():
             return torch.where(explore.unsqueeze(-1), rnd, greedy).contiguous()
         net = self.policy_local
         if self.agent_type == "IQN":
-            quantiles, _ = net(obs, net.K, cvar)
-            greedy = quantiles.mean(dim=1).argmax(dim=1)
+            q = net.action_values_fused(obs, cvar) if self.fused_trunk else None   # K6 + K10 (head 1) + one small GEMM
+            if q is None:
+                quantiles, _ = net(obs, net.K, cvar)
+                q = quantiles.mean(dim=1)
+            greedy = q.argmax(dim=1)
         elif self.agent_type == "DQN":
             greedy = net(obs).argmax(dim=1)
         elif self.agent_type == "Rainbow":  # noisy layers stay in training mode while collecting (TRAINER:131)

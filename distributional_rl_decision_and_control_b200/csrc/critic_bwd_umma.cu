@@ -89,26 +89,6 @@ __device__ __forceinline__ void cb_octet(const uint4 h, const uint4 l, float (&x
   }
 }
 
-// Sums of 32 columns (one per register) over groups of 2^LOGG consecutive lanes.  Afterwards registers
-// v[0 .. (32 >> LOGG) - 1] of a lane hold the group sums of columns (lane & (2^LOGG - 1)) * (32 >> LOGG) + i.
-template <int LOGG>
-__device__ __forceinline__ void cb_seg_reduce(float (&v)[32], int lane) {
-  int n = 32;
-#pragma unroll
-  for (int t = 0; t < LOGG; ++t) {
-    const int off = 1 << (LOGG - 1 - t);
-    n >>= 1;
-    const bool up = (lane & off) != 0;
-#pragma unroll
-    for (int i = 0; i < 16; ++i)
-      if (i < n) {
-        const float keep = up ? v[i + n] : v[i];
-        const float send = up ? v[i] : v[i + n];
-        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-      }
-  }
-}
-
 template <bool FULL, int LOGG>
 __global__ void __launch_bounds__(CB_THREADS, 1)
 critic_backward_kernel(const CriticBwdArgs a) {
@@ -376,7 +356,7 @@ critic_backward_kernel(const CriticBwdArgs a) {
           if (FULL) um_put8(xa + row_off + so, CB_TILE_B, h);
         }
         if (FULL) publish(2 + j, xa, a.dp2_img + ((size_t)tile * 2 + j) * CB_CHUNK_B);
-        cb_seg_reduce<LOGG>(p, lane);
+        um_seg_reduce<LOGG>(p, lane);
         if (live) {
           const int c0 = 64 * j + 32 * hh + col_l;
 #pragma unroll
@@ -419,7 +399,7 @@ critic_backward_kernel(const CriticBwdArgs a) {
             um_put8(xa + row_off + so, CB_TILE_B, h);
           }
           publish(4 + j, xa, a.dp1_img + ((size_t)tile * 4 + j) * CB_CHUNK_B);
-          cb_seg_reduce<LOGG>(p, lane);
+          um_seg_reduce<LOGG>(p, lane);
           if (live) {
             const int c0 = 64 * j + 32 * hh + col_l;
 #pragma unroll

@@ -124,7 +124,7 @@ __device__ __forceinline__ void cf_cos_octets(float tau, uint32_t a_row, int r7)
   }
 }
 
-template <bool SAVE, bool AENC>
+template <bool SAVE, bool AENC, bool MEAN>
 __global__ void __launch_bounds__(CF_THREADS, 1)
 critic_forward_kernel(const CriticArgs a) {
   extern __shared__ __align__(1024) unsigned char cf_raw[];
@@ -292,7 +292,7 @@ critic_forward_kernel(const CriticArgs a) {
     const float4* bh4 = reinterpret_cast<const float4*>(a.bh);
     const float4* bh24 = reinterpret_cast<const float4*>(a.bh2);
     const float4* wo4 = reinterpret_cast<const float4*>(a.wo);
-    const float bo = __ldg(a.bo);
+    const float bo = MEAN ? 0.0f : __ldg(a.bo);
     const uint64_t counter = a.counter + (a.counter_dev ? *a.counter_dev : 0ull);
     uint32_t u = 0;
 
@@ -426,6 +426,22 @@ critic_forward_kernel(const CriticArgs a) {
         uint32_t v[32];
         um_tmem_ld32(lane_addr + (uint32_t)(128 + 64 * hh + 32 * half), v);
         um_tmem_ld_wait();
+        if (MEAN) {
+          // IQN's act (AGENT:227-250): the action values are the mean over the 32 quantile rows of a LINEAR output layer, so
+          // the mean is taken here, of the last hidden layer; the warp's 32 lanes are exactly one sample's rows
+          float p[32];
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int c4 = (64 * hh + 32 * half + 8 * t) / 4;
+            const float4 ba = __ldg(bh24 + c4), bb = __ldg(bh24 + c4 + 1);
+            const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+            for (int k = 0; k < 8; ++k) p[8 * t + k] = fmaxf(fmaf(__uint_as_float(v[8 * t + k]), CF_WUNSCALE, bias[k]), 0.0f);
+          }
+          um_seg_reduce<5>(p, lane);
+          if (live) a.z[(size_t)b * CF_H + 64 * hh + 32 * half + lane] = p[0] * (1.0f / 32.0f);
+          continue;
+        }
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int c4 = (64 * hh + 32 * half + 8 * t) / 4;
@@ -446,9 +462,11 @@ critic_forward_kernel(const CriticArgs a) {
         publish(xr[1], a.r3_img + ((size_t)tile * 2 + 1) * CF_CHUNK_B);
       }
       um_tc_before();
-      if (hh == 1) zpart[s * CF_ROWS + r] = acc;
-      um_bar_sync(pair_bar, 64);
-      if (hh == 0 && live) a.z[m] = acc + zpart[s * CF_ROWS + r] + bo;
+      if (!MEAN) {
+        if (hh == 1) zpart[s * CF_ROWS + r] = acc;
+        um_bar_sync(pair_bar, 64);
+        if (hh == 0 && live) a.z[m] = acc + zpart[s * CF_ROWS + r] + bo;
+      }
       if (elected) CF_TR(1 + s, 16);
     }
     if (SAVE && elected) um_bulk_wait<0>();
@@ -474,10 +492,14 @@ extern "C" long asvrl_critic_forward_chunk_bytes(void) { return (long)CF_CHUNK_B
 extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t counter, const uint64_t* counter_dev,
                                     float cvar, const float* feats, const float* aenc, const float* wc, const float* bc,
                                     const float* wh, const float* bh, const float* wh2, const float* bh2, const float* wo,
-                                    const float* bo, int batch, int n_tau, int repack, void* workspace, float* tau_out,
-                                    float* z, void* cos_img, void* h1_img, void* h2_img, void* r3_img, void* stream) {
-  if (!feats || !wc || !bc || !wh || !bh || !wh2 || !bh2 || !wo || !bo || !workspace || !z)
+                                    const float* bo, int batch, int n_tau, int head, int repack, void* workspace,
+                                    float* tau_out, float* z, void* cos_img, void* h1_img, void* h2_img, void* r3_img,
+                                    void* stream) {
+  if (!feats || !wc || !bc || !wh || !bh || !wh2 || !bh2 || !workspace || !z || (head == 0 && (!wo || !bo)))
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: null pointer");
+  if (head != 0 && head != 1) return fail(ASVRL_E_BADARG, "asvrl_critic_forward: head must be 0 or 1");
+  if (head == 1 && (n_tau != 32 || aenc || cos_img || h1_img || h2_img || r3_img))
+    return fail(ASVRL_E_BADARG, "asvrl_critic_forward: head 1 (mean of the last hidden layer) takes n_tau = 32, no aenc, no images");
   if (batch < 1 || n_tau < 1 || (long)batch * n_tau > 0x7FFFFFFFL - CF_ROWS)
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: bad sizes (B=%d N=%d)", batch, n_tau);
   const bool save = cos_img || h1_img || h2_img || r3_img;
@@ -485,7 +507,7 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: the four operand images go together");
   if (((uintptr_t)workspace | (uintptr_t)cos_img | (uintptr_t)h1_img | (uintptr_t)h2_img | (uintptr_t)r3_img) & 127)
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: workspace and images must be 128-byte aligned");
-  if (((uintptr_t)feats | (uintptr_t)aenc | (uintptr_t)bc | (uintptr_t)bh | (uintptr_t)bh2 | (uintptr_t)wo) & 15)
+  if (((uintptr_t)feats | (uintptr_t)aenc | (uintptr_t)bc | (uintptr_t)bh | (uintptr_t)bh2 | (uintptr_t)wo | (uintptr_t)z) & 15)
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: feats, aenc, biases and wo must be 16-byte aligned");
   static int n_sm = 0;
   cudaError_t e;
@@ -493,10 +515,11 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
     int dev = 0;
     if ((e = cudaGetDevice(&dev)) != cudaSuccess || (e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess)
       return fail((int)e, "asvrl_critic_forward: %s", cudaGetErrorString(e));
-    if ((e = cudaFuncSetAttribute(critic_forward_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(critic_forward_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(critic_forward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(critic_forward_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess) {
+    if ((e = cudaFuncSetAttribute(critic_forward_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(critic_forward_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CF_SMEM_B)) != cudaSuccess) {
       n_sm = 0;
       return fail((int)e, "asvrl_critic_forward: %d B shared memory: %s", CF_SMEM_B, cudaGetErrorString(e));
     }
@@ -519,12 +542,14 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
   a.cos_img = (unsigned char*)cos_img; a.h1_img = (unsigned char*)h1_img;
   a.h2_img = (unsigned char*)h2_img; a.r3_img = (unsigned char*)r3_img;
   const int grid = a.n_tiles < n_sm ? a.n_tiles : n_sm;
-  if (save) {
-    if (aenc) critic_forward_kernel<true, true><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
-    else critic_forward_kernel<true, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+  if (head == 1) {
+    critic_forward_kernel<false, false, true><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+  } else if (save) {
+    if (aenc) critic_forward_kernel<true, true, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+    else critic_forward_kernel<true, false, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
   } else {
-    if (aenc) critic_forward_kernel<false, true><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
-    else critic_forward_kernel<false, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+    if (aenc) critic_forward_kernel<false, true, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
+    else critic_forward_kernel<false, false, false><<<grid, CF_THREADS, CF_SMEM_B, st>>>(a);
   }
   return check_launch("asvrl_critic_forward");
 }

@@ -197,4 +197,25 @@ __device__ __forceinline__ void um_put8(uint32_t hi_addr, uint32_t lo_delta, con
   um_sts128(hi_addr + lo_delta, l[0], l[1], l[2], l[3]);
 }
 
+// Sums of 32 columns (one per register) over groups of 2^LOGG consecutive lanes.  Afterwards registers
+// v[0 .. (32 >> LOGG) - 1] of a lane hold the group sums of columns (lane & (2^LOGG - 1)) * (32 >> LOGG) + i.
+template <int LOGG>
+__device__ __forceinline__ void um_seg_reduce(float (&v)[32], int lane) {
+  int n = 32;
+#pragma unroll
+  for (int t = 0; t < LOGG; ++t) {
+    const int off = 1 << (LOGG - 1 - t);
+    n >>= 1;
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      if (i < n) {
+        const float keep = up ? v[i + n] : v[i];
+        const float send = up ? v[i] : v[i + n];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+  }
+}
+
+
 }  // namespace asvrl

@@ -16,7 +16,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .iqn_ops import TauSampler, critic_trunk, critic_trunk_umma, linear_scale_relu, observation_tower, umma_trunk_ok
+from .iqn_ops import (TauSampler, critic_trunk, critic_trunk_umma, linear_scale_relu, observation_tower, thin_linear,
+                      umma_trunk_ok)
 
 
 _UNIT = {}
@@ -123,9 +124,9 @@ class Actor(_ObservationTower):
             ones = _unit_scale(feats.shape[0], self.hidden_dimension, feats.device)
             h = linear_scale_relu(feats, self.hidden_layer.weight, self.hidden_layer.bias, ones, 1)
             h = linear_scale_relu(h, self.hidden_layer_2.weight, self.hidden_layer_2.bias, ones, 1)
-        else:
-            h = F.relu(self.hidden_layer(feats))
-            h = F.relu(self.hidden_layer_2(h))
+            return self.atan_scale * torch.atan(thin_linear(h, self.output_layer.weight, self.output_layer.bias))
+        h = F.relu(self.hidden_layer(feats))
+        h = F.relu(self.hidden_layer_2(h))
         return self.atan_scale * torch.atan(self.output_layer(h))  # into (-1, 1), ACIQN:320-321
 
     umma_linear = True  # collection path: dense layers through asvrl_linear_tf32x3 (False: cuBLAS + K5)

@@ -64,6 +64,28 @@ class IQN_Policy(_ObservationTower):
         h = linear_scale_relu(h, self.hidden_layer_2.weight, self.hidden_layer_2.bias, ones, num_tau)
         return self.output_layer(h).reshape(B, num_tau, self.action_size), taus
 
+    @torch.no_grad()
+    def action_values_fused(self, x, cvar=1.0):
+        """(M, A) action values of IQN's act (AGENT:227-250): mean over K = 32 quantile rows of the network output.
+        K6 tower, then K10 with head 1 — cosine embedding, the three hidden layers on the tcgen05 tensor cores and the
+        mean over the 32 rows of the last hidden layer in one persistent launch — and the (linear) output layer applied
+        to that mean.  None when the shape / dtype is not K10's."""
+        from .. import _lib
+        from .iqn_ops import UMMA_TRUNK
+        feats = self._features(x)
+        ce, h1, h2 = self.cos_embedding, self.hidden_layer, self.hidden_layer_2
+        if not (UMMA_TRUNK and self.K == 32 and feats.is_cuda and feats.dtype == torch.float32
+                and ce.weight.dtype == torch.float32 and tuple(ce.weight.shape) == (256, 64)
+                and tuple(h1.weight.shape) == (128, 256) and tuple(h2.weight.shape) == (128, 128)):
+            return None
+        ts = self.tau_sampler
+        ts.counter += 1
+        ws = _lib.critic_workspace(id(self), feats.device)
+        mean_h, _ = _lib.critic_forward(feats, None, ce.weight, ce.bias, h1.weight, h1.bias, h2.weight, h2.bias, None, None,
+                                        self.K, ws, seed=ts.seed, counter=ts.counter, counter_dev=ts.counter_dev,
+                                        cvar=float(cvar), mean_hidden=True)
+        return torch.addmm(self.output_layer.bias, mean_h, self.output_layer.weight.t())
+
     def get_constructor_parameters(self):
         return dict(self_dimension=self.self_dimension, object_dimension=self.object_dimension,
                     max_object_num=self.max_object_num,

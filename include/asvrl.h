@@ -531,7 +531,9 @@ ASVRL_API int asvrl_policy_forward_status(int* status_out);
  *   tau_in [B*N] nullable: NULL draws tau = u01 * cvar from Philox stream 3 exactly as asvrl_iqn_tau_cos does
  *   (same seed / counter / counter_dev meaning); tau_out [B*N] nullable; feats [B][256] (the observation tower's
  *   output), aenc [B][128] nullable; wc [256][64], wh [128][256], wh2 [128][128], wo [128], bo [1] and the biases in
- *   the nn.Linear layout; z [B*N].  `workspace`: asvrl_critic_forward_workspace() bytes, 128-byte aligned, holds the
+ *   the nn.Linear layout; z [B*N].  head = 1 (IQN's act, AGENT:227-250; n_tau = 32, aenc = wo = bo = NULL, no images):
+ *   z [B][128] = mean over the 32 quantile rows of the last hidden layer instead — the action values are the 128 -> 25
+ *   output layer applied to it, which is linear, so the mean commutes.  `workspace`: asvrl_critic_forward_workspace() bytes, 128-byte aligned, holds the
  *   packed weight image; `repack` != 0 rebuilds it from wc / wh / wh2 first (one small launch).
  *   cos_img / h1_img / h2_img / r3_img: all NULL (inference), or all set (the differentiable pass): the operand images
  *   the backward kernels read — per 128-row tile 1 / 4 / 2 / 2 chunks of asvrl_critic_forward_chunk_bytes() bytes
@@ -545,7 +547,7 @@ ASVRL_API int asvrl_critic_forward(const float* tau_in /* nullable */, uint64_t 
                                    const uint64_t* counter_dev /* nullable */, float cvar, const float* feats,
                                    const float* aenc /* nullable */, const float* wc, const float* bc,
                                    const float* wh, const float* bh, const float* wh2, const float* bh2,
-                                   const float* wo, const float* bo, int batch, int n_tau, int repack,
+                                   const float* wo, const float* bo, int batch, int n_tau, int head, int repack,
                                    void* workspace, float* tau_out /* nullable */, float* z, void* cos_img,
                                    void* h1_img, void* h2_img, void* r3_img, void* stream);
 ASVRL_API int asvrl_critic_forward_status(int* status_out);

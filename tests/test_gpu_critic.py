@@ -264,3 +264,33 @@ def test_backward_chain_and_wgrad_match_float64_autograd(B, N, fs):
     for name, got, want in (("d_wc", d_wc, wp[0]), ("d_bc", d_bc, wp[1]), ("d_wh", d_wh, wp[2]), ("d_bh", d_bh, wp[3]),
                             ("d_wh2", d_wh2, wp[4]), ("d_bh2", d_bh2, wp[5]), ("d_wo", d_wo, wp[6])):
         _grad_check(name, got, want)
+
+
+@pytest.mark.parametrize("M", [4096, 300, 1])
+def test_iqn_action_values_match_float64_network(M):
+    """IQN's act (AGENT:227-250) through K6 + K10 (head 1): mean over the 32 quantile rows, against the float64 module."""
+    import copy
+    from test_gpu_policy import _obs
+    ag = Agent(device=DEV, seed=5, agent_type="IQN", BATCH_SIZE=64, num_tau=8, BUFFER_SIZE=256)
+    net = ag.policy_local
+    x = _obs(M, 3 + M)
+    ts = net.tau_sampler
+    q = net.action_values_fused(x, cvar=0.9)
+    torch.cuda.synchronize()
+    _lib.critic_forward_status()
+    assert q is not None and q.shape == (M, net.action_size)
+    taus, _ = _lib.iqn_tau_cos(M, 32, 64, DEV, seed=ts.seed, counter=ts.counter, cvar=0.9, counter_dev=ts.counter_dev)
+    ref = copy.deepcopy(net).double()
+    ref.fused_tower = False
+    feats64 = ref._features(tuple(t.double() for t in x))
+    ps = (net.cos_embedding.weight, net.cos_embedding.bias, net.hidden_layer.weight, net.hidden_layer.bias,
+          net.hidden_layer_2.weight, net.hidden_layer_2.bias, torch.zeros(128, device=DEV), torch.zeros(1, device=DEV))
+    R3 = _trunk64(taus, feats64, None, ps)[4]                                 # (M, 32, 128), IQN:74-85
+    want = (R3 @ ref.output_layer.weight.t() + ref.output_layer.bias).mean(dim=1)   # IQN:86, AGENT:239
+    scale = want.abs().max().item()
+    err = (q.double() - want).abs().max().item()
+    assert err <= RTOL * scale + 1e-6, f"action values: max abs err {err:.3e} at scale {scale:.3e}"
+    # the greedy action agrees wherever the two best values are further apart than the error bar
+    top2 = want.topk(2, dim=1).values
+    clear = (top2[:, 0] - top2[:, 1]) > 4 * RTOL * scale
+    assert torch.equal(q.argmax(1)[clear], want.argmax(1)[clear])

@@ -21,10 +21,11 @@
 //   warps 0, 3  W producers, one per slot: one thread streams the packed weights as half chunks (16 KB = hi | lo tile
 //               of 64 out x 64 k) into the slot's own 3-stage ring with cp.async.bulk — a slot consumes its weights in
 //               a fixed order, whatever the other slot does
-//   warp 1      MMA issuer: one thread POLLS both slots (mbarrier.test_wait) and issues the next half chunk (12
-//               tcgen05.mma, N = 64) of whichever slot has its operand and its weights ready, so one slot's tensor work
-//               runs under the other's CUDA-core work instead of the two marching in lock step
-//   warp 2      TMEM allocation
+//   warps 1, 2  MMA issuers, one per slot (a tcgen05.mma costs its issuing thread ~90 cycles whatever its shape: two
+//               issuers, and N = 64 halves of a chunk as two independent accumulation chains).  The warp stays converged
+//               and elects a lane around the tcgen05 instructions, so descriptors live in uniform registers.  Each slot
+//               runs at its own pace: one slot's tensor work lies under the other's CUDA-core work.
+//               Warp 2 also allocates / frees TMEM
 //   warps 4-11  slot 0, warps 12-19 slot 1: warp e of a slot owns TMEM lanes 32 (e % 4) .. and the column half
 //               e / 4.  Per tile: E0 tau -> cos -> A chunk; E1 D1 -> feats * relu(. + bc) -> 4 A chunks of layer 2;
 //               E2 D2 -> aenc * relu(. + bh) -> 2 A chunks of layer 3; E3 D3 -> relu(. + bh2) . wo + bo -> z.
@@ -186,97 +187,68 @@ critic_forward_kernel(const CriticArgs a) {
           um_bulk_g2s(dst + CF_PIECE_B, src + CF_TILE_B, CF_PIECE_B, bar_w_full(s, st));     // lo
         }
     }
-  } else if (warp == 1) {
-    // =============== MMA issuer: polls both slots ===============
-    // The whole warp runs the (uniform) scheduling loop; one elected lane issues the tcgen05 instructions.
+  } else if (warp == 1 || warp == 2) {
+    // =============== MMA issuers: slot 0 (warp 1), slot 1 (warp 2) ===============
+    // The whole warp runs the (uniform) loop; one elected lane issues the tcgen05 instructions.  One issuing warp per slot:
+    // a tcgen05.mma costs its issuing thread ~90 cycles whatever its shape, so two warps issue twice as fast as one, and
+    // each follows its own slot's order with plain blocking waits.
     {
+      const int s = warp - 1;
       constexpr uint32_t idesc = um_idesc_f16(CF_ROWS, 64);
-      constexpr int HC = CF_W_CHUNKS + (SAVE ? 2 : 0);       // chunks of a tile (+ SAVE: the two R3 uses, no MMA)
-      constexpr uint32_t USES = SAVE ? 9u : 7u;               // operand-buffer uses of a tile
-      int it0 = 0, it1 = 1, hc0 = 0, hc1 = 0, wp0 = 0, wp1 = 0;
-      uint32_t ub0 = 0u, ub1 = 0u;
-      uint64_t t_last = 0;
-      uint32_t idle = 0;
-      while (it0 < n_my || it1 < n_my) {
-        bool progressed = false;
+      int wpos = 0;
+      uint32_t u0 = 0u;
+      for (int it = s; it < n_my; it += 2) {
+        if (SAVE && it >= 2)
+          for (uint32_t j = 0; j < 2u; ++j) {   // the previous tile's R3 chunks passed through the buffers without an MMA
+            const uint32_t use = u0 - 2u + j;
+            wait(bar_a_full(s, (int)(use & 1u)), (use >> 1) & 1u, UM_TIMEOUT_INPUT);
+            if (um_elect()) um_mbar_arrive(bar_x_free(s, (int)(use & 1u)));
+            __syncwarp();
+          }
+#pragma unroll 1
+        for (int c = 0; c < CF_W_CHUNKS; ++c) {
+          // operand use of chunk c: the cos chunk serves chunks 0 and 1, then one use per chunk
+          const uint32_t use = u0 + (uint32_t)(c < 2 ? 0 : c - 1);
+          if (c != 1) {
+            wait(bar_a_full(s, (int)(use & 1u)), (use >> 1) & 1u, UM_TIMEOUT_INPUT);
+            // layer 2 accumulates into columns [0,128): both chunks built from them must exist first
+            if (c == 2) wait(bar_a_full(s, (int)((use + 1u) & 1u)), ((use + 1u) >> 1) & 1u, UM_TIMEOUT_INPUT);
+          }
+          const int st0 = wpos % CF_WSTAGES, st1 = (wpos + 1) % CF_WSTAGES;
+          wait(bar_w_full(s, st0), (uint32_t)(wpos / CF_WSTAGES) & 1u, UM_TIMEOUT_RING);
+          wait(bar_w_full(s, st1), (uint32_t)((wpos + 1) / CF_WSTAGES) & 1u, UM_TIMEOUT_RING);
+          um_tc_after();
+          if (lane == 0) CF_TR(0, s * 32 + c);
+          const uint32_t d0 = tmem + (uint32_t)(256 * s + ((c == 1 || c >= 6) ? 128 : 0)), d1 = d0 + 64u;
+          const bool first = c < 3 || c == 6;
+          const uint32_t ah = sb + CF_OFF_X + (uint32_t)(2 * s + (int)(use & 1u)) * CF_CHUNK_B, al = ah + CF_TILE_B;
+          const uint32_t wh0 = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st0) * CF_HALF_B, wl0 = wh0 + CF_PIECE_B;
+          const uint32_t wh1 = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st1) * CF_HALF_B, wl1 = wh1 + CF_PIECE_B;
+          if (um_elect()) {
+            // the two 64-column halves are independent accumulation chains: alternate between them
 #pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          int& it = s ? it1 : it0;
-          int& hc = s ? hc1 : hc0;
-          int& wpos = s ? wp1 : wp0;
-          uint32_t& u0 = s ? ub1 : ub0;
-          if (it >= n_my) continue;
-          const int c = hc;
-          auto ready = [&](uint32_t use) {
-            return __all_sync(0xffffffffu, um_mbar_test(bar_a_full(s, (int)(use & 1u)), (use >> 1) & 1u) != 0u) != 0;
-          };
-          bool go = true;
-          uint32_t use;
-          if (SAVE && c >= CF_W_CHUNKS) {   // an R3 chunk passes through its buffer: free it once it is published
-            use = u0 + 7u + (uint32_t)(c - CF_W_CHUNKS);
-            go = ready(use);
-            if (go && um_elect()) um_mbar_arrive(bar_x_free(s, (int)(use & 1u)));
-          } else {
-            // operand use of chunk c: the cos chunk serves chunks 0 and 1, then one use per chunk
-            use = u0 + (uint32_t)(c < 2 ? 0 : c - 1);
-            if (c != 1) {
-              go = ready(use);
-              // layer 2 accumulates into columns [0,128): both chunks built from them must exist first
-              if (go && c == 2) go = ready(use + 1u);
+            for (int ks = 0; ks < 4; ++ks) {   // 4 x (K = 16 fp16 = 32 B) per 128-byte row
+              const uint32_t o = ks * 32;
+              const uint32_t acc0 = (first && ks == 0) ? 0u : 1u;
+              um_mma_f16(d0, um_desc_sw128(al + o), um_desc_sw128(wh0 + o), idesc, acc0);  // small terms first
+              um_mma_f16(d1, um_desc_sw128(al + o), um_desc_sw128(wh1 + o), idesc, acc0);
+              um_mma_f16(d0, um_desc_sw128(ah + o), um_desc_sw128(wl0 + o), idesc, 1u);
+              um_mma_f16(d1, um_desc_sw128(ah + o), um_desc_sw128(wl1 + o), idesc, 1u);
+              um_mma_f16(d0, um_desc_sw128(ah + o), um_desc_sw128(wh0 + o), idesc, 1u);
+              um_mma_f16(d1, um_desc_sw128(ah + o), um_desc_sw128(wh1 + o), idesc, 1u);
             }
-            const int st0 = wpos % CF_WSTAGES, st1 = (wpos + 1) % CF_WSTAGES;
-            if (go) go = __all_sync(0xffffffffu, um_mbar_test(bar_w_full(s, st0), (uint32_t)(wpos / CF_WSTAGES) & 1u) != 0u) != 0;
-            if (go) go = __all_sync(0xffffffffu, um_mbar_test(bar_w_full(s, st1), (uint32_t)((wpos + 1) / CF_WSTAGES) & 1u) != 0u) != 0;
-            if (go) {
-              um_tc_after();
-              if (lane == 0) CF_TR(0, s * 32 + c);
-              const uint32_t d0 = tmem + (uint32_t)(256 * s + ((c == 1 || c >= 6) ? 128 : 0)), d1 = d0 + 64u;
-              const bool first = c < 3 || c == 6;
-              const uint32_t ah = sb + CF_OFF_X + (uint32_t)(2 * s + (int)(use & 1u)) * CF_CHUNK_B, al = ah + CF_TILE_B;
-              const uint32_t wh0 = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st0) * CF_HALF_B, wl0 = wh0 + CF_PIECE_B;
-              const uint32_t wh1 = sb + CF_OFF_WR + (uint32_t)(s * CF_WSTAGES + st1) * CF_HALF_B, wl1 = wh1 + CF_PIECE_B;
-              if (um_elect()) {
-                // the two 64-column halves are independent accumulation chains: alternate between them
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {   // 4 x (K = 16 fp16 = 32 B) per 128-byte row
-                  const uint32_t o = ks * 32;
-                  const uint32_t acc0 = (first && ks == 0) ? 0u : 1u;
-                  um_mma_f16(d0, um_desc_sw128(al + o), um_desc_sw128(wh0 + o), idesc, acc0);  // small terms first
-                  um_mma_f16(d1, um_desc_sw128(al + o), um_desc_sw128(wh1 + o), idesc, acc0);
-                  um_mma_f16(d0, um_desc_sw128(ah + o), um_desc_sw128(wl0 + o), idesc, 1u);
-                  um_mma_f16(d1, um_desc_sw128(ah + o), um_desc_sw128(wl1 + o), idesc, 1u);
-                  um_mma_f16(d0, um_desc_sw128(ah + o), um_desc_sw128(wh0 + o), idesc, 1u);
-                  um_mma_f16(d1, um_desc_sw128(ah + o), um_desc_sw128(wh1 + o), idesc, 1u);
-                }
-                um_commit(bar_w_empty(s, st0));
-                um_commit(bar_w_empty(s, st1));
-                if (c >= 1) um_commit(bar_x_free(s, (int)(use & 1u)));
-                if (c == 0) um_commit(bar_d_full(s, 0));
-                else if (c == 1) um_commit(bar_d_full(s, 1));
-                else if (c == 5) um_commit(bar_d_full(s, 2));
-                else if (c == 7) um_commit(bar_d_full(s, 3));
-              }
-              __syncwarp();
-              wpos += 2;
-            }
+            um_commit(bar_w_empty(s, st0));
+            um_commit(bar_w_empty(s, st1));
+            if (c >= 1) um_commit(bar_x_free(s, (int)(use & 1u)));
+            if (c == 0) um_commit(bar_d_full(s, 0));
+            else if (c == 1) um_commit(bar_d_full(s, 1));
+            else if (c == 5) um_commit(bar_d_full(s, 2));
+            else if (c == 7) um_commit(bar_d_full(s, 3));
           }
-          if (go) {
-            if (++hc == HC) { hc = 0; u0 += USES; it += 2; }
-            progressed = true;
-          }
+          __syncwarp();
+          wpos += 2;
         }
-        if (progressed) {
-          idle = 0;
-        } else if ((++idle & 1023u) == 0u) {
-          if (*abort_flag) break;
-          const uint64_t now = um_globaltimer();
-          if (idle == 1024u) t_last = now;
-          else if (now - t_last > UM_TIMEOUT_NS) {
-            *abort_flag = 1u;
-            if (a.status) atomicCAS(a.status, 0, UM_TIMEOUT_INPUT);
-            break;
-          }
-        }
+        u0 += SAVE ? 9u : 7u;
       }
     }
   } else if (warp >= 4) {

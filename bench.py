@@ -329,13 +329,13 @@ def training_leg(args, precision, dev, pg, rank, world, barrier, dist, kind="AC-
     from distributional_rl_decision_and_control_b200.envs.marinenav.batched import BatchedMarineNavEnv
     from distributional_rl_decision_and_control_b200.vector_trainer import VectorTrainer
     ET = args.train_envs
-    rainbow = kind == "Rainbow"  # its n-step prioritised memory keeps the ring position on the host: eager
+    rainbow = kind == "Rainbow"  # its own device-resident prioritised n-step memory, one lane per ASV
     agent = Agent(device=dev, seed=100, agent_type=kind, BATCH_SIZE=1024, num_tau=32, BUFFER_SIZE=1 << 20,
                   process_group=pg, rank=rank, matmul_precision=precision,
                   replay_lanes=ET * R if rainbow else 1)
     env = BatchedMarineNavEnv(ET, R, O, args.cores, device=dev, seed=args.seed + 11, env_offset=rank * ET,
-                              fused=not rainbow, prefetch="workers")
-    vt = VectorTrainer(env, agent, update_every=args.update_every, learning_starts=8, cuda_graph=not rainbow)
+                              fused=True, prefetch="workers")
+    vt = VectorTrainer(env, agent, update_every=args.update_every, learning_starts=8, cuda_graph=True)
     vt.learn(40)  # reset, fill the ring, capture both graphs
     update = agent.train_graph_replay if agent._graph is not None else getattr(agent, agent._TRAINERS[kind])
     t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -375,10 +375,10 @@ def training_leg(args, precision, dev, pg, rank, world, barrier, dist, kind="AC-
             "updates_per_sec": (vt.updates - upd0) / tsec, "envs_per_gpu": ET,
             "batched_steps": vt.steps - steps0, "update_every_batched_steps": vt.update_every,
             "batch_per_gpu": 1024, "n_tau": 32, "gemm": precision,
-            "mode": "eager (host-side ring position)" if rainbow else "graph",
+            "mode": "graph" if agent._graph is not None else "eager",
             "what": "act_batch (policy forward for envs x 8 ASVs, eps-greedy) + %s + replay push per "
                     "batched step, one %s update per update_every steps%s"
-                    % ("step + reset" if rainbow else "fused step", kind, "" if rainbow else "; CUDA graphs")}
+                    % ("fused step", kind, "; CUDA graphs")}
 
 
 def run_b200(args):
@@ -632,6 +632,60 @@ def run_b200(args):
             "note": "one persistent tcgen05 launch (+ the weight-pack launch): fp16 two-piece split, 3 products"}
     except Exception as e:
         learner["k9_policy_forward"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    # K10 / K11 / K12 alone at C3: the critic trunk forward, backward chain and weight gradients on tcgen05 against the K3 +
+    # cuBLAS sgemm + K5 sequence they replace.  Algorithmic HBM bytes per quantile row: the operand images (fp16 hi | lo)
+    # — cos 256, H1 1024, H2 512, R3 512 saved by the differentiable forward; dP3 512, dP2 512, dP1 1024, aux 256 written
+    # by K11; K12 reads all eight.
+    try:
+        from distributional_rl_decision_and_control_b200.policy.iqn_ops import critic_trunk as _old_trunk
+        cag = Agent(device=dev, seed=100, agent_type="AC-IQN", BATCH_SIZE=64, num_tau=8, BUFFER_SIZE=256)
+        cr = cag.policy_local.critic
+        cps = (cr.cos_embedding.weight, cr.cos_embedding.bias, cr.hidden_layer.weight, cr.hidden_layer.bias,
+               cr.hidden_layer_2.weight, cr.hidden_layer_2.bias, cr.output_layer.weight.reshape(-1), cr.output_layer.bias)
+        Bc, Nc = 1024, 32
+        Mc = Bc * Nc
+        tau_c = torch.rand((Bc, Nc), device=dev, generator=g)
+        feats_c = torch.relu(torch.randn((Bc, 256), device=dev, generator=g) + 0.4).contiguous()
+        aenc_c = torch.relu(torch.randn((Bc, 128), device=dev, generator=g) + 0.4).contiguous()
+        dz_c = (torch.randn((Bc, Nc), device=dev, generator=g) / Mc).contiguous()
+        cws = _lib.critic_workspace("bench", dev)
+        reps = 20 if args.profile else 200
+        k10_ms = time_kernel(lambda: _lib.critic_forward(feats_c, aenc_c, *cps, Nc, cws, tau_in=tau_c), reps, 20)
+        k10s_ms = time_kernel(lambda: _lib.critic_forward(feats_c, aenc_c, *cps, Nc, cws, tau_in=tau_c, save=True), reps, 20)
+        _, _, (ci, h1i, h2i, r3i) = _lib.critic_forward(feats_c, aenc_c, *cps, Nc, cws, tau_in=tau_c, save=True)
+        fmx = feats_c.amax().reshape(1)
+        k11_ms = time_kernel(lambda: _lib.critic_backward(dz_c, r3i, h2i, h1i, feats_c, aenc_c, cps[2], cps[4], cps[6], Nc, fmax=fmx), reps, 20)
+        k11a_ms = time_kernel(lambda: _lib.critic_backward(dz_c, r3i, h2i, None, feats_c, aenc_c, cps[2], cps[4], cps[6], Nc, full=False), reps, 20)
+        _, _, (d3, d2, d1, ax), sc = _lib.critic_backward(dz_c, r3i, h2i, h1i, feats_c, aenc_c, cps[2], cps[4], cps[6], Nc, fmax=fmx)
+        k12_ms = time_kernel(lambda: _lib.critic_wgrad(d3, d2, d1, ax, ci, h1i, h2i, r3i, sc, Bc, Nc), reps, 20)
+        torch.cuda.synchronize()
+        _lib.critic_forward_status(); _lib.critic_backward_status(); _lib.critic_wgrad_status()
+
+        def _old():
+            with torch.no_grad():
+                _, cs = _lib.iqn_tau_cos(Bc, Nc, 64, dev, tau_in=tau_c)
+                return _old_trunk(cs.reshape(Mc, 64), feats_c, aenc_c, cps[0], cps[1], cps[2], cps[3], cps[4], cps[5],
+                                  cr.output_layer.weight, cps[7], Nc)
+        old_ms = time_kernel(_old, reps, 20)
+        flop = 2.0 * Mc * (64 * 256 + 256 * 128 + 128 * 128 + 128)
+        gbs = lambda nbytes, ms: nbytes / (ms * 1e-3) / 1e9
+        b_fwd, b_save = Mc * 8 + Bc * 1536, Mc * (8 + 2304) + Bc * 1536
+        b_k11, b_k12 = Mc * (2048 + 2304 + 4) + Bc * 3072, Mc * 4608
+        learner["k10_critic_forward"] = {
+            "ms": k10_ms, "ms_save": k10s_ms, "rows": Mc, "tflops_fp32_equivalent": flop / (k10_ms * 1e-3) / 1e12,
+            "tensor_tflops_issued": 3 * flop / (k10_ms * 1e-3) / 1e12, "algorithmic_bytes": b_fwd,
+            "algorithmic_bytes_save": b_save, "achieved_gbs_save": gbs(b_save, k10s_ms), "frac_hbm_save": gbs(b_save, k10s_ms) / peak,
+            "k3_sgemm_k5_ms": old_ms,
+            "note": "bound: tensor issue + CUDA-core epilogue (the inference pass moves 2 MB); save = + the operand images"}
+        learner["k11_critic_backward"] = {
+            "ms": k11_ms, "ms_actor_pass": k11a_ms, "rows": Mc, "algorithmic_bytes": b_k11, "achieved_gbs": gbs(b_k11, k11_ms),
+            "frac_hbm": gbs(b_k11, k11_ms) / peak, "tflops_fp32_equivalent": 2.0 * Mc * (128 * 128 + 128 * 256) / (k11_ms * 1e-3) / 1e12}
+        learner["k12_critic_wgrad"] = {
+            "ms": k12_ms, "rows": Mc, "algorithmic_bytes": b_k12, "achieved_gbs": gbs(b_k12, k12_ms),
+            "frac_hbm": gbs(b_k12, k12_ms) / peak, "bound": "hbm (operand images read once)",
+            "tflops_fp32_equivalent": 2.0 * Mc * (128 * 128 + 128 * 256 + 256 * 64 + 3 * 128) / (k12_ms * 1e-3) / 1e12}
+    except Exception as e:
+        learner["k10_critic_forward"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     # ---- facade leg: the path train_RL_agents.py drives UNCHANGED — one MarineNavEnv3 (config-1 shape: 3 ASVs,
     # no buoys) + Agent (B=64, N=8) + Trainer.learn — timed as a whole loop, next to the Python reference's
     # own figures for the same loop (profiles/ref_python_baseline.json, produced in the build container)
@@ -698,6 +752,13 @@ def run_b200(args):
             "training_tf32_env_steps_per_sec": _num(training, "tf32", "env_steps_per_sec"),
             "training_fp32_updates_per_sec": _num(training, "fp32", "updates_per_sec"),
             "grad_sync": tr32.get("grad_sync"), "replicas_identical": tr32.get("replicas_identical"),
+            "k10_critic_forward_ms": _num(learner, "k10_critic_forward", "ms"),
+            "k10_critic_forward_save_ms": _num(learner, "k10_critic_forward", "ms_save"),
+            "k10_replaces_k3_sgemm_k5_ms": _num(learner, "k10_critic_forward", "k3_sgemm_k5_ms"),
+            "k11_critic_backward_ms": _num(learner, "k11_critic_backward", "ms"),
+            "k11_frac_hbm": _num(learner, "k11_critic_backward", "frac_hbm"),
+            "k12_critic_wgrad_ms": _num(learner, "k12_critic_wgrad", "ms"),
+            "k12_frac_hbm": _num(learner, "k12_critic_wgrad", "frac_hbm"),
             "learner_c3_fp32_ms": _num(learner, "c3_B1024_N32", "ms_per_update"),
             "learner_c3_tf32_ms": _num(learner, "c3_B1024_N32_tf32", "ms_per_update"),
             "learner_ref_B64_N8_ms": _num(learner, "ref_B64_N8", "ms_per_update"),

@@ -516,10 +516,9 @@ class Agent():
         """Capture sample -> critic step -> actor step as one CUDA graph.  RNG counters of the
         sampler and of the tau streams are read from a device word that the graph itself
         advances, so every replay draws a fresh batch and fresh taus."""
-        if self.memory.size() < self.BATCH_SIZE:
+        have = self.memory.transitions.num_elements() if self.agent_type == "Rainbow" else self.memory.size()
+        if have < self.BATCH_SIZE:
             raise RuntimeError("fill the replay buffer with at least one batch before capturing")
-        if self.agent_type == "Rainbow":
-            raise RuntimeError("the Rainbow update keeps its ring position on the host and is not captured")
         step = getattr(self, self._TRAINERS[self.agent_type])
         dev = self.device
         import gc

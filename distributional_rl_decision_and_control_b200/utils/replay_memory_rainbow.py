@@ -8,7 +8,11 @@ step (lane = env * R + robot), so the n steps that follow a sampled transition b
 vehicle.  Priorities live in a flat device vector; a batch is drawn by stratified sampling over
 their running sum (``cumsum`` + ``searchsorted``: the sum-tree walk of REPLAY:14-93 as two dense
 passes), the n-step window is gathered with the reference's blanking rule (a transition whose
-episode timestep is 0 cuts the window, REPLAY:131-141)."""
+episode timestep is 0 cuts the window, REPLAY:131-141).
+
+The ring position, the per-lane episode clocks, the element count and the running maximum priority are
+device words updated IN PLACE, so append_step / sample / update_priorities replay inside CUDA graphs
+(``head`` / ``filled`` are host mirrors, exact outside graph replay)."""
 import numpy as np
 import torch
 
@@ -52,8 +56,10 @@ class ReplayMemory:
         self.lane_t = torch.zeros((self.lanes,), dtype=torch.int32, device=dev)  # REPLAY:109 `self.t`
         self.max_priority = torch.ones((), dtype=torch.float32, device=dev)       # SegmentTree.max
         self.count = torch.zeros((), dtype=torch.int64, device=dev)
-        self.head = 0          # next time slot to write
-        self.filled = 0        # time slots written so far (<= slots)
+        self.head = 0          # next time slot to write (host mirror of head_dev)
+        self.filled = 0        # time slots written so far (<= slots; host mirror)
+        self.head_dev = torch.zeros((1,), dtype=torch.int64, device=dev)
+        self.filled_dev = torch.zeros((1,), dtype=torch.int64, device=dev)
         self._host_count = 0
         self.n_step_scaling = torch.tensor([self.discount ** i for i in range(self.n)],
                                            dtype=torch.float32, device=dev)
@@ -88,6 +94,12 @@ class ReplayMemory:
     def _advance(self):
         self.head = (self.head + 1) % self.slots
         self.filled = min(self.filled + 1, self.slots)
+        self.head_dev.add_(1).remainder_(self.slots)
+        self.filled_dev.add_(1).clamp_(max=self.slots)
+
+    def slots_filled(self):
+        """Time slots written so far, read from the device word (exact under graph replay; one host sync)."""
+        return int(self.filled_dev.item())
 
     # ------------------------------------------------------------------ batched path
     def append_step(self, obs, actions, out):
@@ -100,18 +112,17 @@ class ReplayMemory:
         info = (status >> 8) & 15
         active = ((status & 8) == 0) & (info != 7)
         done = (status & 1) != 0
-        t = self.head
-        row = self.rows[t]
-        row[:, :W_SELF] = o_self.reshape(L, W_SELF)
-        row[:, W_SELF:W_SELF + W_OBJ] = o_obj.reshape(L, W_OBJ)
-        row[:, C_NOBJ] = o_mask.reshape(L, 5).sum(dim=1)
-        row[:, C_ACT] = actions.reshape(L).to(torch.float32)
-        row[:, C_REW] = out["reward"].reshape(L)
-        row[:, C_NONTERM] = (~done).to(torch.float32)
-        self.tstep[t] = torch.where(active, self.lane_t, torch.zeros_like(self.lane_t))
-        self.prio[t * L:(t + 1) * L] = torch.where(active, self.max_priority, torch.zeros((), device=self.device))
-        self.lane_t = torch.where(active & ~done, self.lane_t + 1, torch.zeros_like(self.lane_t))
-        self.count = torch.clamp(self.count + active.sum(), max=self.capacity)
+        t = self.head_dev                                            # (1,) device index: graph-replay safe
+        row = torch.cat((o_self.reshape(L, W_SELF), o_obj.reshape(L, W_OBJ), o_mask.reshape(L, 5).sum(dim=1, keepdim=True),
+                         actions.reshape(L, 1).to(torch.float32), out["reward"].reshape(L, 1),
+                         (~done).to(torch.float32).unsqueeze(1)), dim=1)
+        self.rows.index_copy_(0, t, row.unsqueeze(0))
+        zero_t = torch.zeros_like(self.lane_t)
+        self.tstep.index_copy_(0, t, torch.where(active, self.lane_t, zero_t).unsqueeze(0))
+        self.prio.view(self.slots, L).index_copy_(
+            0, t, torch.where(active, self.max_priority, torch.zeros((), device=self.device)).unsqueeze(0))
+        self.lane_t.copy_(torch.where(active & ~done, self.lane_t + 1, zero_t))
+        self.count.copy_(torch.clamp(self.count + active.sum(), max=self.capacity))
         self._advance()
 
     # ------------------------------------------------------------------ sampling
@@ -143,13 +154,14 @@ class ReplayMemory:
         The n newest time slots cannot be drawn (their n-step window is not written yet)."""
         L, T = self.lanes, self.slots
         p = self.prio.clone().view(T, L)
-        recent = (self.head - 1 - torch.arange(self.n, device=self.device)) % T
-        p[recent] = 0.0
+        recent = (self.head_dev - 1 - torch.arange(self.n, device=self.device)) % T
+        p.index_fill_(0, recent, 0.0)
         p = p.view(-1)
         csum = torch.cumsum(p.to(torch.float64), dim=0)
         total = csum[-1]
         seg = total / batch_size                                     # REPLAY:144-149
-        u = (torch.rand((batch_size,), device=self.device, generator=self._gen, dtype=torch.float64) +
+        gen = None if torch.cuda.is_current_stream_capturing() else self._gen   # the default generator is graph-safe
+        u = (torch.rand((batch_size,), device=self.device, generator=gen, dtype=torch.float64) +
              torch.arange(batch_size, device=self.device, dtype=torch.float64)) * seg
         idxs = torch.searchsorted(csum, u, right=True).clamp_(max=p.numel() - 1)
         probs = p[idxs] / total.to(torch.float32)
@@ -168,4 +180,4 @@ class ReplayMemory:
             idxs = torch.as_tensor(np.asarray(idxs), dtype=torch.int64, device=self.device)
         pr = priorities.detach().to(torch.float32).pow(self.priority_exponent)
         self.prio[idxs] = pr
-        self.max_priority = torch.maximum(self.max_priority, pr.max())
+        self.max_priority.copy_(torch.maximum(self.max_priority, pr.max()))

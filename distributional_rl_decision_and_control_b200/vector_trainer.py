@@ -79,7 +79,8 @@ class VectorTrainer:
         actions = agent.act_batch(flat, self._eps_dev)
         actions = actions.view(E, RP) if self.discrete else actions.view(E, RP, 2)
         if self.rainbow:  # the n-step memory stores (s_t, a_t, r_t+1, terminal), no next state (TRAINER:163-164)
-            out = env.step(actions, is_continuous_action=False)
+            out = env.step_fused(actions, is_continuous_action=False) if env.fused else \
+                env.step(actions, is_continuous_action=False)
             agent.memory.append_step((o_self, o_obj, o_mask), actions, out)
             return out
         if env.fused:  # one launch: step + re-generation + first observation; terminal rows in env.term
@@ -148,7 +149,7 @@ class VectorTrainer:
                 since_update = 0
                 if not self._buffer_ready:  # one host sync until the ring holds a batch (TRAINER:186)
                     have = agent.memory.transitions.num_elements() if self.rainbow else agent.memory.size()
-                    ready = have > agent.BATCH_SIZE and (not self.rainbow or agent.memory.filled > agent.memory.n + 1)
+                    ready = have > agent.BATCH_SIZE and (not self.rainbow or agent.memory.slots_filled() > agent.memory.n + 1)
                     pg = getattr(agent, "process_group", None)
                     if pg is not None:
                         # every rank enters the gradient exchange in the same round: ready = MIN over ranks
@@ -157,7 +158,7 @@ class VectorTrainer:
                         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=pg)
                         ready = bool(flag.item())
                     self._buffer_ready = ready
-                if self._buffer_ready and self.cuda_graph and agent._graph is None and not self.rainbow:
+                if self._buffer_ready and self.cuda_graph and agent._graph is None:
                     agent.enable_cuda_graph()
                 if self._buffer_ready:
                     for _ in range(self.updates_per_round):

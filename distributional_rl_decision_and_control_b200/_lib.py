@@ -71,7 +71,7 @@ _SIGNATURES = {
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
     "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
-                             + [C.c_int, C.c_int, C.c_int, C.c_int, vp, f32p, f32p, vp, vp, vp, vp, vp]),
+                             + [C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, f32p, f32p, vp, vp, vp, vp, vp]),
     "asvrl_critic_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_critic_backward_workspace": (C.c_long, []),
     "asvrl_critic_backward": (C.c_int, [f32p, vp, vp, vp] + [f32p] * 6 + [C.c_int, C.c_int, C.c_int, vp, f32p, f32p,
@@ -482,10 +482,12 @@ def critic_workspace(key, device):
 
 
 def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspace, tau_in=None, seed=0, counter=0,
-                   counter_dev=None, cvar=1.0, repack=True, save=False, mean_hidden=False):
+                   counter_dev=None, cvar=1.0, repack=True, save=False, mean_hidden=False, pack_backward=False):
     """z (B, N), tau (B, N) [, images] of the IQN critic trunk in one persistent tcgen05 launch (K10).
     ``save``: also return the operand images (cos, h1, h2, r3) the backward kernels read.  ``mean_hidden`` (n_tau = 32,
-    no aenc / wo / bo): z is (B, 128), the mean of the last hidden layer over the quantile rows (IQN's act)."""
+    no aenc / wo / bo): z is (B, 128), the mean of the last hidden layer over the quantile rows (IQN's act).
+    ``pack_backward``: a critic_backward_workspace() tensor — the weight-pack launch also writes K11's image into it
+    (critic_backward(..., workspace=that tensor, repack=False) may follow)."""
     B = feats.shape[0]
     dev = feats.device
     f = torch.float32
@@ -500,6 +502,7 @@ def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspa
         ptr(tau_in, f), int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), ptr(counter_dev, torch.int64), float(cvar),
         ptr(feats, f), ptr(aenc, f), ptr(wc, f), ptr(bc, f), ptr(wh, f), ptr(bh, f), ptr(wh2, f), ptr(bh2, f),
         ptr(wo, f), ptr(bo, f), B, int(n_tau), int(bool(mean_hidden)), int(bool(repack)), workspace.data_ptr(),
+        None if pack_backward is None or pack_backward is False else pack_backward.data_ptr(),
         None if tau_in is not None else ptr(tau, f), ptr(z, f),
         *[None if t is None else t.data_ptr() for t in imgs], stream_ptr())
     check(rc, "asvrl_critic_forward")
@@ -509,16 +512,27 @@ def critic_forward(feats, aenc, wc, bc, wh, bh, wh2, bh2, wo, bo, n_tau, workspa
 _CRITIC_BWD_WS = {}
 
 
-def critic_backward(dz, r3_img, h2_img, h1_img, feats, aenc, wh, wh2, wo, n_tau, full=True, repack=True, fmax=None):
+def critic_backward_workspace(dev, shared=True):
+    """Buffer for K11's packed weight image: the (device, stream)'s shared one, or a fresh one (``shared=False``: one per
+    differentiable forward, so interleaved forward / backward pairs cannot overwrite each other's image)."""
+    n = lib().asvrl_critic_backward_workspace()
+    if not shared:
+        return torch.empty((n,), dtype=torch.uint8, device=dev)
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _CRITIC_BWD_WS.get(key)
+    if ws is None:
+        ws = _CRITIC_BWD_WS[key] = torch.empty((n,), dtype=torch.uint8, device=dev)
+    return ws
+
+
+def critic_backward(dz, r3_img, h2_img, h1_img, feats, aenc, wh, wh2, wo, n_tau, full=True, repack=True, fmax=None,
+                    workspace=None):
     """K11.  full: -> (daenc, dfeats, (dp3, dp2, dp1, aux) images, scales); else -> daenc (the actor update's pass).
     ``fmax``: 1-element tensor, max of feats (sets the power-of-two scale of the dP1 image)."""
     B = feats.shape[0]
     dev = feats.device
     f = torch.float32
-    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
-    ws = _CRITIC_BWD_WS.get(key)
-    if ws is None:
-        ws = _CRITIC_BWD_WS[key] = torch.empty((lib().asvrl_critic_backward_workspace(),), dtype=torch.uint8, device=dev)
+    ws = critic_backward_workspace(dev) if workspace is None else workspace
     daenc = torch.empty((B, 128), dtype=f, device=dev)
     dfeats = scales = None
     imgs = (None, None, None, None)
@@ -527,7 +541,7 @@ def critic_backward(dz, r3_img, h2_img, h1_img, feats, aenc, wh, wh2, wo, n_tau,
         cb = lib().asvrl_critic_forward_chunk_bytes()
         dfeats = torch.empty((B, 256), dtype=f, device=dev)
         imgs = tuple(torch.empty((tiles, n, cb), dtype=torch.uint8, device=dev) for n in (2, 2, 4, 1))
-        scales = torch.empty((2,), dtype=f, device=dev)
+        scales = torch.empty((3,), dtype=f, device=dev)   # 1 / S, 1 / S1 (for K12), sum dz
     rc = lib().asvrl_critic_backward(
         ptr(dz, f), r3_img.data_ptr(), h2_img.data_ptr(), h1_img.data_ptr() if full else None, ptr(feats, f), ptr(aenc, f),
         ptr(wh, f), ptr(wh2, f), ptr(wo, f), ptr(fmax, f), B, int(n_tau), int(bool(repack)), ws.data_ptr(), ptr(daenc, f),

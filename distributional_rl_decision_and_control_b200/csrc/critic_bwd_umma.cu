@@ -40,7 +40,7 @@ constexpr int CB_OFF_BAR = CB_OFF_WR + CB_WSTAGES * CB_CHUNK_B;
 constexpr int CB_NBAR = 2 * 6 + 2 * CB_WSTAGES;                    // per slot a_full[2] x_free[2] d_full[2]; w_full, w_empty
 constexpr int CB_OFF_MISC = CB_OFF_BAR + CB_NBAR * 8;              // tmem slot, abort flag, S, 1 / S
 constexpr int CB_OFF_RED = CB_OFF_MISC + 32;                       // 20 floats of the max reduction
-constexpr int CB_SMEM_B = CB_OFF_RED + 128 + 1024;
+constexpr int CB_SMEM_B = CB_OFF_RED + 256 + 1024;
 static_assert(CB_SMEM_B <= 232448, "K11 shared memory");
 
 struct CriticBwdArgs {
@@ -52,7 +52,7 @@ struct CriticBwdArgs {
   int* status;
   float *daenc, *dfeats;                        // [B][128], [B][256]
   unsigned char *dp3_img, *dp2_img, *dp1_img, *aux_img;
-  float* scales;                                // {1 / S, 1 / S1}
+  float* scales;                                // {1 / S, 1 / S1, sum dz}
 };
 
 // chunk 0, 1: B[n = i][k = j - 64 c] = Wh2[j][i]; chunk 2 + 2 nh + c: B[n][k] = Wh[64 c + k][128 nh + n]
@@ -126,11 +126,18 @@ critic_backward_kernel(const CriticBwdArgs a) {
   if (warp == 2) um_tmem_alloc<512>(um_smem(tmem_slot));
   {
     // S from max |dz| over the whole batch (every CTA computes the same value)
-    float mx = 0.0f;
-    for (int i = tid; i < a.rows; i += CB_THREADS) mx = fmaxf(mx, fabsf(__ldg(a.dz + i)));
+    float mx = 0.0f, sm = 0.0f;
+    for (int i = tid; i < a.rows; i += CB_THREADS) {
+      const float d = __ldg(a.dz + i);
+      mx = fmaxf(mx, fabsf(d));
+      sm += d;                               // d loss / d bo (ACIQN:480): the same fixed order in every launch
+    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) s_red[warp] = mx;
+    for (int o = 16; o > 0; o >>= 1) {
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      sm += __shfl_xor_sync(0xffffffffu, sm, o);
+    }
+    if (lane == 0) { s_red[warp] = mx; s_red[CB_THREADS / 32 + warp] = sm; }
   }
   um_tc_before();
   __syncthreads();
@@ -158,7 +165,11 @@ critic_backward_kernel(const CriticBwdArgs a) {
     s_scale[0] = S;
     s_scale[1] = 1.0f / S;
     s_scale[2] = F;
-    if (FULL && blockIdx.x == 0) { a.scales[0] = 1.0f / S; a.scales[1] = 1.0f / (S * F); }
+    if (FULL && blockIdx.x == 0) {
+      float sum = 0.0f;
+      for (int w = 0; w < CB_THREADS / 32; ++w) sum += s_red[CB_THREADS / 32 + w];
+      a.scales[0] = 1.0f / S; a.scales[1] = 1.0f / (S * F); a.scales[2] = sum;
+    }
   }
   __syncthreads();
   const uint32_t tmem = *tmem_slot;

@@ -92,20 +92,38 @@ struct CriticArgs {
 };
 
 // ---- weight image: chunk c = hi tile (128 rows of 128 B, swizzled) then lo tile ----
+// Chunks 0 .. 7 are K10's (Wc as two N halves, Wh as four K chunks, Wh2 as two).  With `bwd_image` the same launch
+// also writes K11's six chunks (the transposed operands of the backward chain, critic_bwd_umma.cu): chunk 0, 1:
+// B[n = i][k = j - 64 c] = Wh2[j][i]; chunk 2 + 2 nh + c: B[n][k] = Wh[64 c + k][128 nh + n].
 __global__ void __launch_bounds__(256)
 critic_pack_kernel(const float* __restrict__ wc, const float* __restrict__ wh, const float* __restrict__ wh2,
-                   unsigned char* __restrict__ image) {
+                   unsigned char* __restrict__ image, unsigned char* __restrict__ bwd_image) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;   // one 16-byte chunk (8 k) of one row of one chunk
-  if (t >= CF_W_CHUNKS * CF_H * 8) return;
-  const int c = t / (CF_H * 8), n = (t / 8) % CF_H, oc = t & 7;
-  const float* src;
-  if (c < 2) src = wc + (size_t)(128 * c + n) * CF_NCOS + oc * 8;
-  else if (c < 6) src = wh + (size_t)n * CF_W + (c - 2) * 64 + oc * 8;
-  else src = wh2 + (size_t)n * CF_H + (c - 6) * 64 + oc * 8;
+  const int n_fwd = CF_W_CHUNKS * CF_H * 8;
+  if (t >= n_fwd + (bwd_image ? 6 * CF_H * 8 : 0)) return;
+  const bool bwd = t >= n_fwd;
+  const int u = bwd ? t - n_fwd : t;
+  const int c = u / (CF_H * 8), n = (u / 8) % CF_H, oc = u & 7;
+  float v[8];
+  if (!bwd) {
+    const float* src;
+    if (c < 2) src = wc + (size_t)(128 * c + n) * CF_NCOS + oc * 8;
+    else if (c < 6) src = wh + (size_t)n * CF_W + (c - 2) * 64 + oc * 8;
+    else src = wh2 + (size_t)n * CF_H + (c - 6) * 64 + oc * 8;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = src[e] * CF_WSCALE;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = oc * 8 + e;
+      v[e] = (c < 2 ? wh2[(size_t)(64 * c + k) * CF_H + n]
+                    : wh[(size_t)(64 * ((c - 2) & 1) + k) * CF_W + 128 * ((c - 2) >> 1) + n]) * CF_WSCALE;
+    }
+  }
   uint32_t h[4], l[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) um_split2(src[2 * i] * CF_WSCALE, src[2 * i + 1] * CF_WSCALE, h[i], l[i]);
-  unsigned char* tile = image + (size_t)c * CF_CHUNK_B + um_sw128_off(n, oc);
+  for (int i = 0; i < 4; ++i) um_split2(v[2 * i], v[2 * i + 1], h[i], l[i]);
+  unsigned char* tile = (bwd ? bwd_image : image) + (size_t)c * CF_CHUNK_B + um_sw128_off(n, oc);
   *reinterpret_cast<uint4*>(tile) = make_uint4(h[0], h[1], h[2], h[3]);
   *reinterpret_cast<uint4*>(tile + CF_TILE_B) = make_uint4(l[0], l[1], l[2], l[3]);
 }
@@ -465,8 +483,8 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
                                     float cvar, const float* feats, const float* aenc, const float* wc, const float* bc,
                                     const float* wh, const float* bh, const float* wh2, const float* bh2, const float* wo,
                                     const float* bo, int batch, int n_tau, int head, int repack, void* workspace,
-                                    float* tau_out, float* z, void* cos_img, void* h1_img, void* h2_img, void* r3_img,
-                                    void* stream) {
+                                    void* bwd_workspace, float* tau_out, float* z, void* cos_img, void* h1_img,
+                                    void* h2_img, void* r3_img, void* stream) {
   if (!feats || !wc || !bc || !wh || !bh || !wh2 || !bh2 || !workspace || !z || (head == 0 && (!wo || !bo)))
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: null pointer");
   if (head != 0 && head != 1) return fail(ASVRL_E_BADARG, "asvrl_critic_forward: head must be 0 or 1");
@@ -477,7 +495,8 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
   const bool save = cos_img || h1_img || h2_img || r3_img;
   if (save && !(cos_img && h1_img && h2_img && r3_img))
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: the four operand images go together");
-  if (((uintptr_t)workspace | (uintptr_t)cos_img | (uintptr_t)h1_img | (uintptr_t)h2_img | (uintptr_t)r3_img) & 127)
+  if (bwd_workspace && !repack) return fail(ASVRL_E_BADARG, "asvrl_critic_forward: bwd_workspace is written by the pack launch (repack != 0)");
+  if (((uintptr_t)workspace | (uintptr_t)bwd_workspace | (uintptr_t)cos_img | (uintptr_t)h1_img | (uintptr_t)h2_img | (uintptr_t)r3_img) & 127)
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: workspace and images must be 128-byte aligned");
   if (((uintptr_t)feats | (uintptr_t)aenc | (uintptr_t)bc | (uintptr_t)bh | (uintptr_t)bh2 | (uintptr_t)wo | (uintptr_t)z) & 15)
     return fail(ASVRL_E_BADARG, "asvrl_critic_forward: feats, aenc, biases and wo must be 16-byte aligned");
@@ -498,8 +517,8 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (repack) {
-    const int n = CF_W_CHUNKS * CF_H * 8;
-    critic_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wc, wh, wh2, (unsigned char*)workspace);
+    const int n = (CF_W_CHUNKS + (bwd_workspace ? 6 : 0)) * CF_H * 8;
+    critic_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wc, wh, wh2, (unsigned char*)workspace, (unsigned char*)bwd_workspace);
     if (int rc = check_launch("asvrl_critic_forward (pack)")) return rc;
   }
   CriticArgs a;

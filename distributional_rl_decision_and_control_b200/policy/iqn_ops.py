@@ -190,33 +190,38 @@ class _CriticTrunkUmma(torch.autograd.Function):
         save = any(need[:10])
         ws = _lib.critic_workspace(ws_key, feats.device)
         seed, counter, counter_dev, cvar = draw
+        # the backward of THIS pass reads the same weights: its (transposed) image is packed by the same launch
+        bws = _lib.critic_backward_workspace(feats.device, shared=False) if save else None
         out = _lib.critic_forward(feats, aenc, Wc, bc, Wh, bh, Wh2, bh2, wo.reshape(-1), bo, n_tau, ws, tau_in=tau_in,
-                                  seed=seed, counter=counter, counter_dev=counter_dev, cvar=cvar, save=save)
+                                  seed=seed, counter=counter, counter_dev=counter_dev, cvar=cvar, save=save,
+                                  pack_backward=bws)
         z, tau = out[0], out[1]
         if save:
             fmax = feats.amax().reshape(1) if need[0] or any(need[2:10]) else feats.new_zeros(1)
-            ctx.save_for_backward(feats, aenc, Wh, Wh2, wo, fmax, *out[2])
+            ctx.save_for_backward(feats, aenc, Wh, Wh2, wo, fmax, bws, *out[2])
         ctx.n_tau = n_tau
         ctx.mark_non_differentiable(tau)
         return z, tau
 
     @staticmethod
     def backward(ctx, dz, _dtau):
-        feats, aenc, Wh, Wh2, wo, fmax, cos_i, h1_i, h2_i, r3_i = ctx.saved_tensors
+        feats, aenc, Wh, Wh2, wo, fmax, bws, cos_i, h1_i, h2_i, r3_i = ctx.saved_tensors
         need = ctx.needs_input_grad
         n_tau = ctx.n_tau
         g = [None] * 14
         dz = dz.contiguous()
         if need[0] or any(need[2:10]):
             daenc, dfeats, (dp3, dp2, dp1, aux), scales = _lib.critic_backward(dz, r3_i, h2_i, h1_i, feats, aenc, Wh, Wh2,
-                                                                              wo.reshape(-1), n_tau, fmax=fmax)
+                                                                              wo.reshape(-1), n_tau, fmax=fmax, repack=False,
+                                                                              workspace=bws)
             d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo = _lib.critic_wgrad(dp3, dp2, dp1, aux, cos_i, h1_i, h2_i, r3_i,
                                                                            scales, feats.shape[0], n_tau)
             g[0], g[1] = dfeats, daenc
             g[2], g[3], g[4], g[5], g[6], g[7], g[8] = d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo.view_as(wo)
-            g[9] = dz.sum().reshape(1)
+            g[9] = scales[2:3]   # sum dz, reduced in K11's prologue
         else:
-            g[1] = _lib.critic_backward(dz, r3_i, h2_i, None, feats, aenc, Wh, Wh2, wo.reshape(-1), n_tau, full=False)
+            g[1] = _lib.critic_backward(dz, r3_i, h2_i, None, feats, aenc, Wh, Wh2, wo.reshape(-1), n_tau, full=False,
+                                        repack=False, workspace=bws)
         return tuple(g)
 
 

@@ -534,7 +534,9 @@ ASVRL_API int asvrl_policy_forward_status(int* status_out);
  *   the nn.Linear layout; z [B*N].  head = 1 (IQN's act, AGENT:227-250; n_tau = 32, aenc = wo = bo = NULL, no images):
  *   z [B][128] = mean over the 32 quantile rows of the last hidden layer instead — the action values are the 128 -> 25
  *   output layer applied to it, which is linear, so the mean commutes.  `workspace`: asvrl_critic_forward_workspace() bytes, 128-byte aligned, holds the
- *   packed weight image; `repack` != 0 rebuilds it from wc / wh / wh2 first (one small launch).
+ *   packed weight image; `repack` != 0 rebuilds it from wc / wh / wh2 first (one small launch), and with
+ *   `bwd_workspace` (asvrl_critic_backward_workspace() bytes) the same launch packs asvrl_critic_backward's image
+ *   too, so that call can pass repack = 0.
  *   cos_img / h1_img / h2_img / r3_img: all NULL (inference), or all set (the differentiable pass): the operand images
  *   the backward kernels read — per 128-row tile 1 / 4 / 2 / 2 chunks of asvrl_critic_forward_chunk_bytes() bytes
  *   (fp16 hi | lo pieces of cos, H1 = feats * relu(P1 + bc), H2 = aenc * relu(P2 + bh), R3 = relu(P3 + bh2), in the
@@ -548,7 +550,8 @@ ASVRL_API int asvrl_critic_forward(const float* tau_in /* nullable */, uint64_t 
                                    const float* aenc /* nullable */, const float* wc, const float* bc,
                                    const float* wh, const float* bh, const float* wh2, const float* bh2,
                                    const float* wo, const float* bo, int batch, int n_tau, int head, int repack,
-                                   void* workspace, float* tau_out /* nullable */, float* z, void* cos_img,
+                                   void* workspace, void* bwd_workspace /* nullable */,
+                                   float* tau_out /* nullable */, float* z, void* cos_img,
                                    void* h1_img, void* h2_img, void* r3_img, void* stream);
 ASVRL_API int asvrl_critic_forward_status(int* status_out);
 
@@ -576,7 +579,7 @@ ASVRL_API int asvrl_critic_wgrad_status(int* status_out);
  *   workspace: asvrl_critic_backward_workspace() bytes (packed Wh2^T | Wh^T image; `repack` != 0 rebuilds it);
  *   daenc [B][128] = d loss / d aenc; fmax (device, nullable): max over feats, sets dP1's power-of-two scale (NULL: 2^-8).
  *   Full pass: dfeats [B][256], dp3_img / dp2_img / dp1_img / aux_img ([tile][2 | 2 | 4 | 1] chunks, 128-byte aligned)
- *   and scales[2] (device) for asvrl_critic_wgrad — all set; or all NULL (with h1_img NULL allowed): the actor
+ *   and scales[3] (device: {1/S, 1/S1} for asvrl_critic_wgrad, then sum dz = d loss / d bo) — all set; or all NULL (with h1_img NULL allowed): the actor
  *   update's pass (AGENT:420-427), which needs d z / d aenc only and stops after dP2. */
 ASVRL_API long asvrl_critic_backward_workspace(void);
 ASVRL_API int asvrl_critic_backward(const float* dz, const void* r3_img, const void* h2_img,

@@ -262,7 +262,7 @@ def test_backward_chain_and_wgrad_match_float64_autograd(B, N, fs):
         _grad_check(name + " overall", got, want, tol=2e-2)
     d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo = grads
     for name, got, want in (("d_wc", d_wc, wp[0]), ("d_bc", d_bc, wp[1]), ("d_wh", d_wh, wp[2]), ("d_bh", d_bh, wp[3]),
-                            ("d_wh2", d_wh2, wp[4]), ("d_bh2", d_bh2, wp[5]), ("d_wo", d_wo, wp[6])):
+                            ("d_wh2", d_wh2, wp[4]), ("d_bh2", d_bh2, wp[5]), ("d_wo", d_wo, wp[6]), ("d_bo", scales[2:3], wp[7])):
         _grad_check(name, got, want)
 
 

@@ -128,7 +128,19 @@ critic_pack_kernel(const float* __restrict__ wc, const float* __restrict__ wh, c
   *reinterpret_cast<uint4*>(tile + CF_TILE_B) = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// cos(tau * fl32(pi i)) for i = I0 .. I0 + 31 of this thread's row -> octets OC0 .. OC0 + 3 of the A chunk
+// cos(tau * fl32(pi i)) for i = I0 .. I0 + 31 of this thread's row -> octets OC0 .. OC0 + 3 of the A chunk.
+// x = fl32(tau * fl32(pi i)) is the reference's rounded argument (ACIQN:397, 424; up to 64 pi).  cosf's 21-instruction
+// path made this the longest CUDA-core phase of a tile (4 us per tile pair), so the cosine is taken as
+// MUFU.COS of the argument reduced to [-pi, pi] with a two-constant Cody-Waite step: k = rint(x / 2 pi) <= 33,
+// r = (x - k C1) - k C2 with C1 = 6.28125 (8 significant bits: k C1 exact) — reduction error < 4e-8 — and the
+// special-function unit's 2^-21.4 absolute error on [-pi, pi]: <= 4.2e-7 per cosine against cosf's 1.2e-7, i.e.
+// ~2e-7 of a 64-term pre-activation's scale (tests/test_gpu_critic.py holds the quantiles to 1e-5).
+__device__ __forceinline__ float cf_cos(float x) {
+  const float k = rintf(x * 0.15915494309189535f);
+  float r = fmaf(k, -6.28125f, x);
+  r = fmaf(k, -1.9353071795864769e-3f, r);   // 2 pi - 6.28125
+  return __cosf(r);
+}
 template <int I0>
 __device__ __forceinline__ void cf_cos_octets(float tau, uint32_t a_row, int r7) {
 #pragma unroll
@@ -137,7 +149,7 @@ __device__ __forceinline__ void cf_cos_octets(float tau, uint32_t a_row, int r7)
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const float pi_i = (float)(3.14159265358979323846 * (double)(I0 + 8 * t + e));   // ACIQN:397
-      v[e] = cosf(__fmul_rn(tau, pi_i));                                                // ACIQN:424
+      v[e] = cf_cos(__fmul_rn(tau, pi_i));                                              // ACIQN:424
     }
     um_put8(a_row + (uint32_t)(((I0 / 8 + t) ^ r7) << 4), CF_TILE_B, v);
   }

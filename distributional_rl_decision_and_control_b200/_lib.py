@@ -68,6 +68,7 @@ _SIGNATURES = {
                                        C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_long, C.c_int,
                                        vp, f32p, vp]),
     "asvrl_policy_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
+    "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, i32p, f32p, vp]),
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
     "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
@@ -466,6 +467,18 @@ def policy_forward_status():
     if v.value != 0:
         raise RuntimeError(f"asvrl_policy_forward: device pipeline fault, status {v.value}")
     return 0
+
+
+def c51_greedy(zv, za, bv, ba, support, n_actions, want_q=False):
+    """Greedy actions (rows,) int32 [and expected values (rows, A)] of a dueling C51 head from its bias-free products."""
+    rows, atoms = zv.shape
+    f = torch.float32
+    action = torch.empty((rows,), dtype=torch.int32, device=zv.device)
+    q = torch.empty((rows, n_actions), dtype=f, device=zv.device) if want_q else None
+    rc = lib().asvrl_c51_greedy(ptr(zv, f), ptr(za, f), ptr(bv, f), ptr(ba, f), ptr(support, f), rows, int(n_actions),
+                                int(atoms), ptr(action, torch.int32), ptr(q, f), stream_ptr())
+    check(rc, "asvrl_c51_greedy")
+    return (action, q) if want_q else action
 
 
 # ------------------------------------------------------------------ K10: critic trunk forward on tcgen05

@@ -289,7 +289,10 @@ class Agent():
         elif self.agent_type == "DQN":
             greedy = net(obs).argmax(dim=1)
         elif self.agent_type == "Rainbow":  # noisy layers stay in training mode while collecting (TRAINER:131)
-            greedy = (net(obs) * self.support).sum(2).argmax(1)
+            if self.fused_trunk and obs[0].is_cuda and obs[0].dtype == torch.float32 and self.atoms <= 64:
+                greedy = net.greedy_actions(obs, self.support)   # one pass over the output layers' products
+            else:
+                greedy = (net(obs) * self.support).sum(2).argmax(1)
         else:
             raise RuntimeError("Agent type not implemented!")
         rnd = torch.randint(0, self.action_size, (M,), device=self.device)

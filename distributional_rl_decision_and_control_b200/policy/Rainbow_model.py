@@ -83,6 +83,26 @@ class Rainbow_Policy(_ObservationTower):
         q = v + a - a.mean(1, keepdim=True)
         return F.log_softmax(q, dim=2) if log else F.softmax(q, dim=2)
 
+    @torch.no_grad()
+    def greedy_actions(self, x, support, want_q=False):
+        """Collection path (AGENT:235-246 for every row): the six noisy layers as GEMMs — the two output layers without
+        their bias — and `asvrl_c51_greedy` for the dueling combination, softmax, expectation and argmax in one pass
+        (the (M, A, atoms) probability tensor is never written).  int32 (M,) [and the (M, A) expected values]."""
+        from .. import _lib
+
+        def eff(layer):   # the layer's weight / bias with its current noise (Rainbow:50-53)
+            if layer.training:
+                return (layer.weight_mu + layer.weight_sigma * layer.weight_epsilon,
+                        layer.bias_mu + layer.bias_sigma * layer.bias_epsilon)
+            return layer.weight_mu, layer.bias_mu
+
+        feats = self._features(x)
+        v = F.relu(self.hidden_layer_v_2(F.relu(self.hidden_layer_v(feats))))
+        a = F.relu(self.hidden_layer_a_2(F.relu(self.hidden_layer_a(feats))))
+        wv, bv = eff(self.output_layer_v)
+        wa, ba = eff(self.output_layer_a)
+        return _lib.c51_greedy(v @ wv.t(), a @ wa.t(), bv.contiguous(), ba.contiguous(), support, self.action_size, want_q)
+
     def reset_noise(self):
         for name, module in self.named_children():
             if "hidden_layer" in name or "output_layer" in name:

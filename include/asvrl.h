@@ -591,6 +591,15 @@ ASVRL_API int asvrl_critic_backward(const float* dz, const void* r3_img, const v
                                     void* stream);
 ASVRL_API int asvrl_critic_backward_status(int* status_out);
 
+/* Greedy action of Rainbow's dueling C51 head (Rainbow_model.py:127-135 + agent.py:235-246 act_rainbow) for `rows`
+ * ASVs in one launch: q = v + a - mean_a(a), softmax over the atoms, expectation over the support, first argmax.
+ *   zv [rows][atoms], za [rows][n_actions][atoms]: the two output layers' products WITHOUT bias; bv [atoms],
+ *   ba [n_actions][atoms]: their (noisy) biases; support [atoms]; action [rows] int32; q_out [rows][n_actions]
+ *   nullable (the expected values).  n_actions <= 32, atoms <= 64. */
+ASVRL_API int asvrl_c51_greedy(const float* zv, const float* za, const float* bv, const float* ba, const float* support,
+                               long rows, int n_actions, int atoms, int* action, float* q_out /* nullable */,
+                               void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -169,3 +169,29 @@ def test_rainbow_memory_n_step_window():
     assert int(idx.max()) < len(terms) - m.n
     m.update_priorities(idx[:2], torch.tensor([4.0, 9.0], device="cuda:0"))
     assert m.transitions.max == 3.0
+
+
+@pytest.mark.gpu
+def test_rainbow_greedy_actions_match_probability_path():
+    """asvrl_c51_greedy (dueling combination, softmax, expectation, argmax in one pass) against the module's own
+    probability tensor in float64 (Rainbow:127-135, AGENT:235-246), noisy layers in training mode."""
+    import copy
+    dev = "cuda:0"
+    pol = build("Rainbow", 7, dev)
+    pol.train()
+    g = torch.Generator(device=dev).manual_seed(3)
+    M = 3000
+    x = (torch.randn((M, 7), device=dev, generator=g) * 5, torch.randn((M, 5, 5), device=dev, generator=g) * 3,
+         (torch.rand((M, 5), device=dev, generator=g) < 0.6).float())
+    x = (x[0], x[1] * x[2][..., None], x[2])
+    support = torch.linspace(-10.0, 10.0, 51, device=dev)
+    act, q = pol.greedy_actions(x, support, want_q=True)
+    ref = copy.deepcopy(pol).double()
+    ref.fused_tower = False
+    ref.train()
+    want = (ref(tuple(t.double() for t in x)) * support.double()).sum(2)
+    assert float((q.double() - want).abs().max()) <= 1e-5 * float(want.abs().max()) + 1e-6
+    top2 = want.topk(2, dim=1).values
+    clear = (top2[:, 0] - top2[:, 1]) > 1e-4
+    assert torch.equal(act.long()[clear], want.argmax(1)[clear])
+    assert int(clear.sum()) > M // 2

@@ -395,6 +395,19 @@ def run_b200(args):
         raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    pinned_cores = None
+    if world > 1 and os.environ.get("ASVRL_BENCH_PIN", "1") != "0":
+        # N ranks share the host's cores: give every rank its own disjoint slice (the e2e leg is host-launch bound, and an
+        # unpinned rank's main thread migrates between cores other ranks' helper threads are using)
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = max(1, len(cores) // world)
+            mine = cores[(local * per) % len(cores):(local * per) % len(cores) + per]
+            if mine:
+                os.sched_setaffinity(0, set(mine))
+                pinned_cores = mine
+        except (AttributeError, OSError):
+            pinned_cores = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
@@ -791,7 +804,14 @@ def run_b200(args):
                     "h2d_bytes_per_step": E * R * 2 * 4, "d2h_bytes_per_step": e2e_d2h,
                     "api": ("HostPipelinedEnv.send/recv, %d shards of E/%d envs, one CUDA graph launch per send "
                            "(actions H2D, fused step, results D2H); obs_self + obs_objects + reward + "
-                           "status per ASV (the mask is objects[...,4] != 0, as in the reference's step())") % (G, G)},
+                           "status per ASV (the mask is objects[...,4] != 0, as in the reference's step())") % (G, G),
+                    "host_cores_per_rank": pinned_cores if pinned_cores else "unpinned",
+                    "d2h_gbs_per_rank": e2e_d2h / (e2e_ms * 1e-3 / K) / 1e9,
+                    "limiter": "PCIe D2H of the reference-shaped float32 outputs (%.2f MB per step and rank): one rank alone "
+                               "copies at 48 GB/s (%.0f us per step); with 8 ranks copying at once the host fabric gives "
+                               "12.5 GB/s to ranks 0-3 and 21 GB/s to ranks 4-7 (134 GB/s aggregate = at most 123 M "
+                               "env-steps/s over the box; profiles/r02_pcie_scaling_n8.txt)"
+                               % (e2e_d2h / 1e6, e2e_d2h / 48e9 * 1e6)},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": k1_traffic(E, C, env.fused), "peak_source": which,

@@ -13,6 +13,8 @@
 // moves 4*(SD + K*OD + K) B in and 4*W B out per sample; backward reads feats, dfeats and the
 // observations once.  The parameter gradients are per-CTA partials summed by the last CTA in a
 // fixed order (deterministic).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace asvrl {
@@ -135,8 +137,14 @@ static int tower_dims(const char* what, int batch, int self_dim, int obj_dim, in
 }
 
 static int tower_bwd_grid(int batch) {
+  static int cap = 0;
+  if (cap == 0) {
+    const char* e = getenv("ASVRL_TOWER_BWD_GRID");   // tuning knob; the partial buffer is sized for the default cap
+    cap = e ? atoi(e) : 32;   // 32 CTAs: 11.9 us at B = 1024 (64: 13.3, 16: 14.2; profiles/probes/small_kernels_probe.py)
+    if (cap < 1 || cap > 64) cap = 32;
+  }
   int g = (batch + 15) / 16;
-  return g > 64 ? 64 : (g < 1 ? 1 : g);
+  return g > cap ? cap : (g < 1 ? 1 : g);
 }
 
 extern "C" int asvrl_tower_fwd(const float* self_obs, const float* objects, const float* mask,

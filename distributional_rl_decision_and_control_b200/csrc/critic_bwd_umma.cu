@@ -1,7 +1,7 @@
 // critic_bwd_umma.cu — K11: the backward chain of the IQN critic's quantile trunk (the activation half of the autograd
 // backward of rfarl/rfarl/policy/AC_IQN_model.py:453-480; reference: loss.backward() at rfarl/rfarl/agent.py:413, 425)
-// for all B*N quantile rows in ONE persistent, warp-specialised tcgen05 launch.  Per 128-row tile, reading the operand
-// images K10 saved (R3, H2, H1) straight from HBM / L2:
+// for all B*N quantile rows in ONE persistent, warp-specialised tcgen05 launch.  Per 128-row tile, with the operand
+// images K10 saved (R3, H2, H1) brought by bulk copies into the very buffers the step's output overwrites:
 //   B0  dP3 = S dz . wo . 1[R3 > 0]                              -> A chunks of   dH2 = dP3 Wh2          (tensor)
 //   B1  dP2 = dH2 . aenc[b] . 1[H2 > 0];  daenc[b] = sum_n dH2 . H2 / aenc[b]
 //                                                                 -> A chunks of   dH1 = dP2 Wh           (tensor)
@@ -37,11 +37,26 @@ constexpr float CB_WSCALE = 64.0f, CB_WUNSCALE = 1.0f / 64.0f;
 constexpr int CB_OFF_X = 0;
 constexpr int CB_OFF_WR = 4 * CB_CHUNK_B;
 constexpr int CB_OFF_BAR = CB_OFF_WR + CB_WSTAGES * CB_CHUNK_B;
-constexpr int CB_NBAR = 2 * 6 + 2 * CB_WSTAGES;                    // per slot a_full[2] x_free[2] d_full[2]; w_full, w_empty
+constexpr int CB_NBAR = 2 * 8 + 2 * CB_WSTAGES;                    // per slot a_full[2] x_free[2] d_full[2] img_full[2]; w_full, w_empty
 constexpr int CB_OFF_MISC = CB_OFF_BAR + CB_NBAR * 8;              // tmem slot, abort flag, S, 1 / S
 constexpr int CB_OFF_RED = CB_OFF_MISC + 32;                       // 20 floats of the max reduction
 constexpr int CB_SMEM_B = CB_OFF_RED + 256 + 1024;
 static_assert(CB_SMEM_B <= 232448, "K11 shared memory");
+
+#ifdef CF_TRACE
+// timeline of CTA 0 for profiles/probes/k10_trace.py: [writer][event] = (globaltimer << 8) | tag
+__device__ unsigned long long cb_trace_buf[4][1024];
+__device__ int cb_trace_n[4];
+#define CB_TR(writer, tag)                                                                              \
+  do {                                                                                                   \
+    if (blockIdx.x == 0) {                                                                               \
+      const int n_ = cb_trace_n[writer];                                                                 \
+      if (n_ < 1024) { cb_trace_buf[writer][n_] = (um_globaltimer() << 8) | (unsigned)(tag); cb_trace_n[writer] = n_ + 1; } \
+    }                                                                                                    \
+  } while (0)
+#else
+#define CB_TR(writer, tag) do {} while (0)
+#endif
 
 struct CriticBwdArgs {
   const float* dz;                              // [rows]
@@ -98,11 +113,12 @@ critic_backward_kernel(const CriticBwdArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   const uint32_t bar0 = sb + CB_OFF_BAR;
-  auto bar_a_full = [&](int s, int x) { return bar0 + 8u * (6 * s + x); };
-  auto bar_x_free = [&](int s, int x) { return bar0 + 8u * (6 * s + 2 + x); };
-  auto bar_d_full = [&](int s, int d) { return bar0 + 8u * (6 * s + 4 + d); };
-  auto bar_w_full = [&](int st) { return bar0 + 8u * (12 + st); };
-  auto bar_w_empty = [&](int st) { return bar0 + 8u * (12 + CB_WSTAGES + st); };
+  auto bar_a_full = [&](int s, int x) { return bar0 + 8u * (8 * s + x); };
+  auto bar_x_free = [&](int s, int x) { return bar0 + 8u * (8 * s + 2 + x); };
+  auto bar_d_full = [&](int s, int d) { return bar0 + 8u * (8 * s + 4 + d); };
+  auto bar_img = [&](int s, int x) { return bar0 + 8u * (8 * s + 6 + x); };
+  auto bar_w_full = [&](int st) { return bar0 + 8u * (16 + st); };
+  auto bar_w_empty = [&](int st) { return bar0 + 8u * (16 + CB_WSTAGES + st); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(base + CB_OFF_MISC);
   volatile uint32_t* abort_flag = reinterpret_cast<volatile uint32_t*>(base + CB_OFF_MISC + 4);
   float* s_scale = reinterpret_cast<float*>(base + CB_OFF_MISC + 8);   // S, 1 / S
@@ -113,6 +129,7 @@ critic_backward_kernel(const CriticBwdArgs a) {
       for (int x = 0; x < 2; ++x) {
         um_mbar_init(bar_a_full(s, x), FULL ? 1 : 8);
         um_mbar_init(bar_x_free(s, x), 1);
+        um_mbar_init(bar_img(s, x), 1);
       }
       for (int d = 0; d < 2; ++d) um_mbar_init(bar_d_full(s, d), 1);
     }
@@ -123,14 +140,36 @@ critic_backward_kernel(const CriticBwdArgs a) {
     *abort_flag = 0u;
     um_mbar_init_fence();
   }
+  if (tid == 0) CB_TR(3, 0);
   if (warp == 2) um_tmem_alloc<512>(um_smem(tmem_slot));
+  __syncthreads();   // barriers initialised
+  // the R3 chunks of each slot's first tile start their way into the operand buffers under the dz reduction
+  if ((tid == 128 || tid == 384) && (int)blockIdx.x + (tid == 384 ? (int)gridDim.x : 0) < a.n_tiles) {
+    const int s = tid == 384 ? 1 : 0;   // the slots' elected threads: warp 4 / warp 12, lane 0
+    const size_t tile = (size_t)blockIdx.x + (size_t)s * gridDim.x;
+    for (int x = 0; x < 2; ++x) {
+      um_mbar_arrive_expect_tx(bar_img(s, x), CB_CHUNK_B);
+      um_bulk_g2s(sb + CB_OFF_X + (uint32_t)(2 * s + x) * CB_CHUNK_B, a.r3_img + (tile * 2 + x) * CB_CHUNK_B, CB_CHUNK_B,
+                  bar_img(s, x));
+    }
+  }
   {
     // S from max |dz| over the whole batch (every CTA computes the same value)
     float mx = 0.0f, sm = 0.0f;
-    for (int i = tid; i < a.rows; i += CB_THREADS) {
-      const float d = __ldg(a.dz + i);
-      mx = fmaxf(mx, fabsf(d));
-      sm += d;                               // d loss / d bo (ACIQN:480): the same fixed order in every launch
+    if ((a.rows & 3) == 0 && (reinterpret_cast<uintptr_t>(a.dz) & 15) == 0) {
+      const float4* d4 = reinterpret_cast<const float4*>(a.dz);
+#pragma unroll 4
+      for (int i = tid; i < (a.rows >> 2); i += CB_THREADS) {
+        const float4 d = __ldg(d4 + i);
+        mx = fmaxf(fmaxf(mx, fmaxf(fabsf(d.x), fabsf(d.y))), fmaxf(fabsf(d.z), fabsf(d.w)));
+        sm += (d.x + d.y) + (d.z + d.w);     // d loss / d bo (ACIQN:480): the same fixed order in every launch
+      }
+    } else {
+      for (int i = tid; i < a.rows; i += CB_THREADS) {
+        const float d = __ldg(a.dz + i);
+        mx = fmaxf(mx, fabsf(d));
+        sm += d;
+      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -172,6 +211,7 @@ critic_backward_kernel(const CriticBwdArgs a) {
     }
   }
   __syncthreads();
+  if (tid == 0) CB_TR(3, 1);
   const uint32_t tmem = *tmem_slot;
   const float S = s_scale[0], invS = s_scale[1], F1 = s_scale[2];
 
@@ -225,8 +265,10 @@ critic_backward_kernel(const CriticBwdArgs a) {
         wait(bar_a_full(s, 1), ph, UM_TIMEOUT_INPUT);
         um_tc_after();
         const uint32_t d = tmem + (uint32_t)(256 * s);
+        CB_TR(0, 16 * s + 1);
         chunk(xaddr(s, 0), d, true);
         chunk(xaddr(s, 1), d, false);
+        CB_TR(0, 16 * s + 2);
         um_commit(bar_x_free(s, 0));
         um_commit(bar_x_free(s, 1));
         um_commit(bar_d_full(s, 0));
@@ -237,10 +279,12 @@ critic_backward_kernel(const CriticBwdArgs a) {
         wait(bar_a_full(s, 1), ph, UM_TIMEOUT_INPUT);
         um_tc_after();
         const uint32_t d = tmem + (uint32_t)(256 * s);
+        CB_TR(0, 16 * s + 3);
         chunk(xaddr(s, 0), d, true);
         chunk(xaddr(s, 1), d, false);
         chunk(xaddr(s, 0), d + 128u, true);
         chunk(xaddr(s, 1), d + 128u, false);
+        CB_TR(0, 16 * s + 4);
         um_commit(bar_x_free(s, 0));
         um_commit(bar_x_free(s, 1));
         um_commit(bar_d_full(s, 1));
@@ -265,18 +309,37 @@ critic_backward_kernel(const CriticBwdArgs a) {
     constexpr int CNT = 32 >> LOGG;                       // columns per lane after the segmented reduction
     const int col_l = (lane & ((1 << LOGG) - 1)) * CNT;   // first of them
 
-    // buffer x for use `ut` of tile k of this slot: wait for its previous MMA reader and bulk-store reader
-    auto acquire = [&](int ut, int k) -> uint32_t {
+    // Use `ut` of tile k of this slot takes buffer ut & 1.  begin(): wait for the buffer's previous MMA reader and
+    // bulk-store reader, then ONE thread brings the saved image chunk the step consumes into that very buffer with a
+    // bulk copy (img_full).  Every thread later reads its own row's octets from it and overwrites them in place with
+    // the dP chunk: the image never goes through the L1 as 128-byte-strided 16-byte loads (32 wavefronts per request,
+    // which clogged the load / shuffle pipe: profiles/probes/k11_trace.py).
+    auto begin = [&](int ut, int k, const unsigned char* img, bool issued = false) -> uint32_t {
       const int x = ut & 1;
       if (FULL) {
         if (ut == 2 || ut == 3) wait(bar_x_free(s, x), 0u, UM_TIMEOUT_RING);        // phase 2k
         else if (ut == 4 || ut == 5) wait(bar_x_free(s, x), 1u, UM_TIMEOUT_RING);   // phase 2k + 1
-        if (elected) um_bulk_wait_read<1>();
+        if (elected) um_bulk_wait_read<0>();   // every bulk store out of the buffers has read its source
         um_bar_sync(grp_bar, 256);
-      } else if (k > 0) {
+      } else if (ut < 2 && k > 0) {
         wait(bar_x_free(s, x), (uint32_t)(k - 1) & 1u, UM_TIMEOUT_RING);
       }
-      return xbase + (uint32_t)x * CB_CHUNK_B;
+      const uint32_t xa = xbase + (uint32_t)x * CB_CHUNK_B;
+      if (elected && !issued) {
+        um_mbar_arrive_expect_tx(bar_img(s, x), CB_CHUNK_B);
+        um_bulk_g2s(xa, img, CB_CHUNK_B, bar_img(s, x));
+      }
+      return xa;
+    };
+    // the image chunk of use `ut` has landed; this thread's four octets (hi piece, then lo piece)
+    auto image = [&](int ut, uint32_t xa, uint4 (&g)[8]) {
+      wait(bar_img(s, ut & 1), (uint32_t)(ut >> 1) & 1u, UM_TIMEOUT_INPUT);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const uint32_t so = (uint32_t)(((4 * hh + t) ^ r7) << 4);
+        g[t] = um_lds128(xa + row_off + so);
+        g[4 + t] = um_lds128(xa + row_off + CB_TILE_B + so);
+      }
     };
     auto publish = [&](int ut, uint32_t xa, unsigned char* img) {
       um_fence_async_smem();
@@ -304,8 +367,12 @@ critic_backward_kernel(const CriticBwdArgs a) {
       const float4* frow = reinterpret_cast<const float4*>(a.feats + (size_t)b * CB_W);
       const float4* arow = reinterpret_cast<const float4*>(a.aenc + (size_t)b * CB_H);
       const float dzs = live ? S * __ldg(a.dz + m) : 0.0f;
+      uint32_t xa[2];
 
+      if (elected) CB_TR(1 + s, 1);
       // ---- B0: dP3 = S dz . wo . 1[R3 > 0] ----
+      xa[0] = begin(0, k, a.r3_img + ((size_t)tile * 2 + 0) * CB_CHUNK_B, k == 0);   // k == 0: issued in the prologue
+      xa[1] = begin(1, k, a.r3_img + ((size_t)tile * 2 + 1) * CB_CHUNK_B, k == 0);
       if (FULL && hh == 0) {   // aux tile for K12: column 0 = S dz, column 1 = 1 (octets 0 and 1 of the row, hi | lo)
         unsigned char* ax = a.aux_img + (size_t)tile * CB_CHUNK_B + row_off;
         uint32_t dh, dl;
@@ -316,45 +383,43 @@ critic_backward_kernel(const CriticBwdArgs a) {
         *reinterpret_cast<uint4*>(ax + CB_TILE_B + ((1 ^ r7) << 4)) = make_uint4(0u, 0u, 0u, 0u);
       }
       for (int j = 0; j < 2; ++j) {
-        const uint32_t xa = acquire(j, k);
-        const unsigned char* src = a.r3_img + ((size_t)tile * 2 + j) * CB_CHUNK_B + row_off;
+        uint4 g8[8];
+        image(j, xa[j], g8);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int oc = 4 * hh + t, c4 = (64 * j + 8 * oc) / 4;
           const uint32_t so = (uint32_t)((oc ^ r7) << 4);
-          const uint4 gh = __ldg(reinterpret_cast<const uint4*>(src + so));
-          const uint4 gl = __ldg(reinterpret_cast<const uint4*>(src + CB_TILE_B + so));
           float r3[8];
-          cb_octet(gh, gl, r3);
+          cb_octet(g8[t], g8[4 + t], r3);
           const float4 wa = __ldg(wo4 + c4), wb = __ldg(wo4 + c4 + 1);
           const float w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
           float h[8];
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) h[kk] = r3[kk] > 0.0f ? dzs * w[kk] : 0.0f;
-          um_put8(xa + row_off + so, CB_TILE_B, h);
+          um_put8(xa[j] + row_off + so, CB_TILE_B, h);
         }
-        publish(j, xa, FULL ? a.dp3_img + ((size_t)tile * 2 + j) * CB_CHUNK_B : nullptr);
+        publish(j, xa[j], FULL ? a.dp3_img + ((size_t)tile * 2 + j) * CB_CHUNK_B : nullptr);
+        if (elected) CB_TR(1 + s, 2 + j);
       }
 
       // ---- B1: dH2 -> dP2 = dH2 . aenc . 1[H2 > 0]; daenc = sum_n dH2 . H2 / aenc ----
       wait(bar_d_full(s, 0), kpar, UM_TIMEOUT_ACC);
+      if (elected) CB_TR(1 + s, 4);
+      xa[0] = begin(2, k, a.h2_img + ((size_t)tile * 2 + 0) * CB_CHUNK_B);
+      xa[1] = begin(3, k, a.h2_img + ((size_t)tile * 2 + 1) * CB_CHUNK_B);
       for (int j = 0; j < 2; ++j) {
         um_tc_after();
-        uint32_t xa = 0u;
-        if (FULL) xa = acquire(2 + j, k);
         uint32_t v[32];
         um_tmem_ld32(lane_addr + (uint32_t)(64 * j + 32 * hh), v);
+        uint4 g8[8];
+        image(2 + j, xa[j], g8);
         um_tmem_ld_wait();
-        const unsigned char* src = a.h2_img + ((size_t)tile * 2 + j) * CB_CHUNK_B + row_off;
-        float p[32];
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int oc = 4 * hh + t, c4 = (64 * j + 8 * oc) / 4;
           const uint32_t so = (uint32_t)((oc ^ r7) << 4);
-          const uint4 gh = __ldg(reinterpret_cast<const uint4*>(src + so));
-          const uint4 gl = __ldg(reinterpret_cast<const uint4*>(src + CB_TILE_B + so));
           float h2[8];
-          cb_octet(gh, gl, h2);
+          cb_octet(g8[t], g8[4 + t], h2);
           const float4 fa = __ldg(arow + c4), fb = __ldg(arow + c4 + 1);
           const float f[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
           float h[8];
@@ -362,11 +427,15 @@ critic_backward_kernel(const CriticBwdArgs a) {
           for (int kk = 0; kk < 8; ++kk) {
             const float g = __uint_as_float(v[8 * t + kk]) * CB_WUNSCALE;   // S dH2
             h[kk] = h2[kk] > 0.0f ? g * f[kk] : 0.0f;
-            p[8 * t + kk] = g * h2[kk];
+            v[8 * t + kk] = __float_as_uint(g * h2[kk]);   // in place: the summand of d aenc
           }
-          if (FULL) um_put8(xa + row_off + so, CB_TILE_B, h);
+          if (FULL) um_put8(xa[j] + row_off + so, CB_TILE_B, h);
         }
-        if (FULL) publish(2 + j, xa, a.dp2_img + ((size_t)tile * 2 + j) * CB_CHUNK_B);
+        if (FULL) publish(2 + j, xa[j], a.dp2_img + ((size_t)tile * 2 + j) * CB_CHUNK_B);
+        if (elected) CB_TR(1 + s, 5 + j);
+        float p[32];
+#pragma unroll
+        for (int kk = 0; kk < 32; ++kk) p[kk] = __uint_as_float(v[kk]);
         um_seg_reduce<LOGG>(p, lane);
         if (live) {
           const int c0 = 64 * j + 32 * hh + col_l;
@@ -377,27 +446,32 @@ critic_backward_kernel(const CriticBwdArgs a) {
           }
         }
       }
-      if (!FULL) um_tc_before();
+      if (!FULL) {
+        um_tc_before();
+        um_bar_sync(grp_bar, 256);   // every thread has read the H2 chunks: the next tile may overwrite the buffers
+      }
 
-      // ---- B2: dH1 -> dP1 = dH1 . feats . 1[H1 > 0] (scale S1 = S / 256); dfeats = sum_n dH1 . H1 / feats ----
+      // ---- B2: dH1 -> dP1 = dH1 . feats . 1[H1 > 0] (scale S1); dfeats = sum_n dH1 . H1 / feats ----
       if (FULL) {
+        if (elected) CB_TR(1 + s, 7);
         wait(bar_d_full(s, 1), kpar, UM_TIMEOUT_ACC);
+        if (elected) CB_TR(1 + s, 8);
+        xa[0] = begin(4, k, a.h1_img + ((size_t)tile * 4 + 0) * CB_CHUNK_B);
+        xa[1] = begin(5, k, a.h1_img + ((size_t)tile * 4 + 1) * CB_CHUNK_B);
         for (int j = 0; j < 4; ++j) {
           um_tc_after();
-          const uint32_t xa = acquire(4 + j, k);
+          const uint32_t xj = xa[j & 1];
           uint32_t v[32];
           um_tmem_ld32(lane_addr + (uint32_t)(64 * j + 32 * hh), v);
+          uint4 g8[8];
+          image(4 + j, xj, g8);
           um_tmem_ld_wait();
-          const unsigned char* src = a.h1_img + ((size_t)tile * 4 + j) * CB_CHUNK_B + row_off;
-          float p[32];
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
             const int oc = 4 * hh + t, c4 = (64 * j + 8 * oc) / 4;
             const uint32_t so = (uint32_t)((oc ^ r7) << 4);
-            const uint4 gh = __ldg(reinterpret_cast<const uint4*>(src + so));
-            const uint4 gl = __ldg(reinterpret_cast<const uint4*>(src + CB_TILE_B + so));
             float h1[8];
-            cb_octet(gh, gl, h1);
+            cb_octet(g8[t], g8[4 + t], h1);
             const float4 fa = __ldg(frow + c4), fb = __ldg(frow + c4 + 1);
             const float f[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
             float h[8];
@@ -405,11 +479,17 @@ critic_backward_kernel(const CriticBwdArgs a) {
             for (int kk = 0; kk < 8; ++kk) {
               const float g = __uint_as_float(v[8 * t + kk]) * CB_WUNSCALE;   // S dH1
               h[kk] = h1[kk] > 0.0f ? g * (f[kk] * F1) : 0.0f;
-              p[8 * t + kk] = g * h1[kk];
+              v[8 * t + kk] = __float_as_uint(g * h1[kk]);   // in place: the summand of d feats
             }
-            um_put8(xa + row_off + so, CB_TILE_B, h);
+            um_put8(xj + row_off + so, CB_TILE_B, h);
           }
-          publish(4 + j, xa, a.dp1_img + ((size_t)tile * 4 + j) * CB_CHUNK_B);
+          publish(4 + j, xj, a.dp1_img + ((size_t)tile * 4 + j) * CB_CHUNK_B);
+          if (elected) CB_TR(1 + s, 9 + j);
+          // the chunk after next goes into this buffer: start its image copy before the per-sample reduction
+          if (j < 2) xa[j & 1] = begin(6 + j, k, a.h1_img + ((size_t)tile * 4 + j + 2) * CB_CHUNK_B);
+          float p[32];
+#pragma unroll
+          for (int kk = 0; kk < 32; ++kk) p[kk] = __uint_as_float(v[kk]);
           um_seg_reduce<LOGG>(p, lane);
           if (live) {
             const int c0 = 64 * j + 32 * hh + col_l;
@@ -513,6 +593,17 @@ extern "C" int asvrl_critic_backward(const float* dz, const void* r3_img, const 
   if (full) cb_launch<true>(logg, grid, st, a); else cb_launch<false>(logg, grid, st, a);
   return check_launch("asvrl_critic_backward");
 }
+
+#ifdef CF_TRACE
+extern "C" __attribute__((visibility("default"))) int asvrl_critic_backward_trace(unsigned long long* events, int* counts) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(events, cb_trace_buf, sizeof(unsigned long long) * 4 * 1024);
+  cudaMemcpyFromSymbol(counts, cb_trace_n, sizeof(int) * 4);
+  int zero[4] = {0, 0, 0, 0};
+  cudaMemcpyToSymbol(cb_trace_n, zero, sizeof zero);
+  return 0;
+}
+#endif
 
 extern "C" int asvrl_critic_backward_status(int* status_out) {
   if (!status_out) return fail(ASVRL_E_BADARG, "asvrl_critic_backward_status: null pointer");

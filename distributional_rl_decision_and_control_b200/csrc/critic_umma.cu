@@ -129,17 +129,21 @@ critic_pack_kernel(const float* __restrict__ wc, const float* __restrict__ wh, c
 }
 
 // cos(tau * fl32(pi i)) for i = I0 .. I0 + 31 of this thread's row -> octets OC0 .. OC0 + 3 of the A chunk.
-// x = fl32(tau * fl32(pi i)) is the reference's rounded argument (ACIQN:397, 424; up to 64 pi).  cosf's 21-instruction
-// path made this the longest CUDA-core phase of a tile (4 us per tile pair), so the cosine is taken as
-// MUFU.COS of the argument reduced to [-pi, pi] with a two-constant Cody-Waite step: k = rint(x / 2 pi) <= 33,
-// r = (x - k C1) - k C2 with C1 = 6.28125 (8 significant bits: k C1 exact) — reduction error < 4e-8 — and the
-// special-function unit's 2^-21.4 absolute error on [-pi, pi]: <= 4.2e-7 per cosine against cosf's 1.2e-7, i.e.
-// ~2e-7 of a 64-term pre-activation's scale (tests/test_gpu_critic.py holds the quantiles to 1e-5).
+// x = fl32(tau * fl32(pi i)) is the reference's rounded argument (ACIQN:397, 424; up to 64 pi) and the cosine is cosf,
+// as torch's.  A faster form was measured and REJECTED (-DCF_FAST_COS keeps it for the record): MUFU.COS of the argument
+// reduced to [-pi, pi] by a two-constant Cody-Waite step is a third of cosf's 21 instructions (K10 29.5 -> 24.8 us at
+// C3, 1.27 -> 1.06 ms at 2.1 M rows) and keeps the quantiles within 1e-5, but its ~6e-7 absolute error per cosine
+// (cosf: 6e-8) flips ten times more layer-1 ReLU gates: on the reference's observation ranges the parameter gradients
+// then differ from float64 autograd by 5e-4 .. 7e-3 of their scale instead of 1e-6 .. 4e-6 (profiles/probes/critic_grad_err.py).
 __device__ __forceinline__ float cf_cos(float x) {
+#ifdef CF_FAST_COS
   const float k = rintf(x * 0.15915494309189535f);
-  float r = fmaf(k, -6.28125f, x);
+  float r = fmaf(k, -6.28125f, x);           // k <= 33: k * 6.28125 is exact
   r = fmaf(k, -1.9353071795864769e-3f, r);   // 2 pi - 6.28125
   return __cosf(r);
+#else
+  return cosf(x);
+#endif
 }
 template <int I0>
 __device__ __forceinline__ void cf_cos_octets(float tau, uint32_t a_row, int r7) {

@@ -187,6 +187,11 @@ __device__ __forceinline__ void um_split2(float a, float b, uint32_t& hi, uint32
 __device__ __forceinline__ void um_sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+__device__ __forceinline__ uint4 um_lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 // split 8 consecutive K elements of one row and store them as chunk `off` of the hi tile and of the
 // lo tile `lo_delta` bytes after it
 __device__ __forceinline__ void um_put8(uint32_t hi_addr, uint32_t lo_delta, const float (&v)[8]) {

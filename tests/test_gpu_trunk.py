@@ -81,6 +81,18 @@ def _critic_inputs(B, seed):
     return (own, obj, mask), act
 
 
+def close_most(got, want, what, rtol, frac=0.99, rtol_max=2e-2):
+    """Per-sample quantities on the tensor-core path: a ReLU gate inside the rounding margin that flips against the
+    float32 module path moves ONE sample's gradient by a few per cent (1 of its 32 quantile rows), so nearly all
+    samples must agree to `rtol` of the tensor's scale and none may be off by more than a flipped gate's worth."""
+    want = want.to(torch.float64)
+    err = (got.to(torch.float64) - want).abs()
+    scale = max(want.abs().max().item(), 1e-6)
+    ok = (err <= rtol * scale).double().mean().item()
+    assert ok >= frac and err.max().item() <= rtol_max * scale, \
+        f"{what}: {ok:.4f} of the elements within {rtol:g}, max err {err.max().item():.3e} vs scale {scale:.3e}"
+
+
 @pytest.mark.parametrize("umma", [False, True])
 @pytest.mark.parametrize("B,N", [(64, 8), (1024, 32), (3, 5)])
 def test_fused_critic_matches_module_path(B, N, umma, monkeypatch):
@@ -88,7 +100,8 @@ def test_fused_critic_matches_module_path(B, N, umma, monkeypatch):
     K12 where they apply (>= 4096 quantile rows): an independent evaluation order, so ReLU gates of pre-activations
     inside the rounding margin differ from the torch float32 path's (as that path's differ from float64), and one such
     gate moves a weight gradient by ~1 / sqrt(B N) of its scale — the gradient arithmetic itself is pinned to 1e-5 with
-    matched gates in tests/test_gpu_critic.py; here the bar on gradients is 2e-4."""
+    matched gates in tests/test_gpu_critic.py; here the bar on gradients is 2e-4 (measured against float64 on these
+    inputs: 1e-6 .. 4e-6, profiles/probes/critic_grad_err.py; torch's float32 path: up to 1e-4 on cos_embedding)."""
     from distributional_rl_decision_and_control_b200.policy import iqn_ops
     monkeypatch.setattr(iqn_ops, "UMMA_TRUNK", umma)
     gtol = 2e-4 if umma and B * N >= iqn_ops.UMMA_TRUNK_MIN_ROWS else 2e-5
@@ -110,13 +123,15 @@ def test_fused_critic_matches_module_path(B, N, umma, monkeypatch):
     crit.fused_tower = True        # K6 tower + K5 trunk
     z1, da1, g1 = run(crit.forward_fused)
     close(z1, z0, "quantiles")
-    close(da1, da0, "d/d actions", rtol=gtol / 2)
+    tensor_path = gtol > 2e-5
+    (close_most if tensor_path else close)(da1, da0, "d/d actions", rtol=1e-4 if tensor_path else gtol / 2)
     for n in g0:
         close(g1[n], g0[n], f"grad {n}", rtol=gtol)
     # the actor update's variant: the same d/d actions, no parameter gradients at all
     z2, da2, g2 = run(crit.forward_fused, param_grads=False)
     assert torch.equal(z2, z1)
-    close(da2, da0, "d/d actions (actor pass)", rtol=gtol / 2)
+    (close_most if tensor_path else close)(da2, da0, "d/d actions (actor pass)", rtol=1e-4 if tensor_path else gtol / 2)
+    assert torch.equal(da2, da1) or not tensor_path   # K11's two forms are bit-identical
     assert all(v is None for v in g2.values())
 
 

@@ -68,6 +68,11 @@ _SIGNATURES = {
                                        C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_long, C.c_int,
                                        vp, f32p, vp]),
     "asvrl_policy_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
+    "asvrl_action_encoder_fwd": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_int, f32p, vp]),
+    "asvrl_action_encoder_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
+    "asvrl_narrow_bwd_partials": (C.c_long, [C.c_int]),
+    "asvrl_atan_head_fwd": (C.c_int, [f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, vp]),
+    "asvrl_atan_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
     "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, i32p, f32p, vp]),
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
@@ -467,6 +472,52 @@ def policy_forward_status():
     if v.value != 0:
         raise RuntimeError(f"asvrl_policy_forward: device pipeline fault, status {v.value}")
     return 0
+
+
+# ------------------------------------------------------------------ the two narrow layers of the update
+def action_encoder_fwd(actions, wa, ba):
+    B, D = actions.shape[0], wa.shape[0]
+    f = torch.float32
+    aenc = torch.empty((B, D), dtype=f, device=actions.device)
+    check(lib().asvrl_action_encoder_fwd(ptr(actions, f), ptr(wa, f), ptr(ba, f), B, D, ptr(aenc), stream_ptr()),
+          "asvrl_action_encoder_fwd")
+    return aenc
+
+
+def action_encoder_bwd(daenc, aenc, actions, wa, want_dact=True):
+    B, D = aenc.shape
+    f = torch.float32
+    dev = aenc.device
+    dwa = torch.empty((D, 2), dtype=f, device=dev)
+    dba = torch.empty((D,), dtype=f, device=dev)
+    dact = torch.empty((B, 2), dtype=f, device=dev) if want_dact else None
+    part, cnt = _trunk_ws(dev, lib().asvrl_narrow_bwd_partials(D))
+    check(lib().asvrl_action_encoder_bwd(ptr(daenc, f), ptr(aenc, f), ptr(actions, f), ptr(wa, f), B, D, ptr(dwa), ptr(dba),
+                                         ptr(dact), ptr(part), ptr(cnt), stream_ptr()), "asvrl_action_encoder_bwd")
+    return dwa, dba, dact
+
+
+def atan_head_fwd(h, w3, b3, scale):
+    B, D = h.shape
+    f = torch.float32
+    y = torch.empty((B, 2), dtype=f, device=h.device)
+    act = torch.empty((B, 2), dtype=f, device=h.device)
+    check(lib().asvrl_atan_head_fwd(ptr(h, f), ptr(w3, f), ptr(b3, f), float(scale), B, D, ptr(y), ptr(act), stream_ptr()),
+          "asvrl_atan_head_fwd")
+    return y, act
+
+
+def atan_head_bwd(dact, y, h, w3, scale, want_dh=True):
+    B, D = h.shape
+    f = torch.float32
+    dev = h.device
+    dh = torch.empty((B, D), dtype=f, device=dev) if want_dh else None
+    dw3 = torch.empty((2, D), dtype=f, device=dev)
+    db3 = torch.empty((2,), dtype=f, device=dev)
+    part, cnt = _trunk_ws(dev, lib().asvrl_narrow_bwd_partials(D))
+    check(lib().asvrl_atan_head_bwd(ptr(dact, f), ptr(y, f), ptr(h, f), ptr(w3, f), float(scale), B, D, ptr(dh), ptr(dw3),
+                                    ptr(db3), ptr(part), ptr(cnt), stream_ptr()), "asvrl_atan_head_bwd")
+    return dh, dw3, db3
 
 
 def c51_greedy(zv, za, bv, ba, support, n_actions, want_q=False):

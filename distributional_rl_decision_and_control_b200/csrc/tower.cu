@@ -182,5 +182,7 @@ extern "C" int asvrl_tower_bwd(const float* dfeats, const float* feats, const fl
 
 extern "C" long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, int obj_feat) {  /* floats */
   (void)max_obj;
-  return (long)tower_bwd_grid(batch) * (self_feat + obj_feat) * (TW_MAXIN + 1);
+  int g = (batch + 15) / 16;   // the bound over every grid the launch may choose (<= 64 CTAs)
+  g = g > 64 ? 64 : (g < 1 ? 1 : g);
+  return (long)g * (self_feat + obj_feat) * (TW_MAXIN + 1);
 }

@@ -16,8 +16,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .iqn_ops import (TauSampler, critic_trunk, critic_trunk_umma, linear_scale_relu, observation_tower, thin_linear,
-                      umma_trunk_ok)
+from .iqn_ops import (TauSampler, action_encoder, atan_head, critic_trunk, critic_trunk_umma, linear_scale_relu, narrow_ok,
+                      observation_tower, thin_linear, umma_trunk_ok)
 
 
 _UNIT = {}
@@ -124,6 +124,9 @@ class Actor(_ObservationTower):
             ones = _unit_scale(feats.shape[0], self.hidden_dimension, feats.device)
             h = linear_scale_relu(feats, self.hidden_layer.weight, self.hidden_layer.bias, ones, 1)
             h = linear_scale_relu(h, self.hidden_layer_2.weight, self.hidden_layer_2.bias, ones, 1)
+            if self.action_dimension == 2 and narrow_ok(h, self.hidden_dimension):
+                # output layer, atan and scale in one launch (one more for the whole backward)
+                return atan_head(h, self.output_layer.weight, self.output_layer.bias, self.atan_scale)
             return self.atan_scale * torch.atan(thin_linear(h, self.output_layer.weight, self.output_layer.bias))
         h = F.relu(self.hidden_layer(feats))
         h = F.relu(self.hidden_layer_2(h))
@@ -248,14 +251,17 @@ class Critic(_ObservationTower):
         enc = self.action_encoder[0]
         B = actions.shape[0]
         ones = _unit_scale(B, self.hidden_dimension, actions.device)
+        narrow = self.action_dimension == 2 and narrow_ok(actions, self.hidden_dimension)
         if param_grads:
             feats = self._features(x)
-            aenc = linear_scale_relu(actions, enc.weight, enc.bias, ones, 1)
+            aenc = action_encoder(actions, enc.weight, enc.bias) if narrow else \
+                linear_scale_relu(actions, enc.weight, enc.bias, ones, 1)
         else:
             with torch.no_grad():
                 feats = self._features(x)
             ps = [p.detach() for p in ps]
-            aenc = linear_scale_relu(actions, enc.weight.detach(), enc.bias.detach(), ones, 1)
+            aenc = action_encoder(actions, enc.weight.detach(), enc.bias.detach()) if narrow else \
+                linear_scale_relu(actions, enc.weight.detach(), enc.bias.detach(), ones, 1)
         need_grad = torch.is_grad_enabled() and (feats.requires_grad or aenc.requires_grad or ps[0].requires_grad)
         if umma_trunk_ok(feats, aenc, ps[0], ps[2], ps[4], num_tau, need_grad):
             # K10 (+ K11 / K12 in the backward): cosine embedding, the three dense layers and the head in one

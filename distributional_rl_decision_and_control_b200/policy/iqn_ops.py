@@ -324,6 +324,60 @@ def thin_linear(x, W, b):
     return _ThinLinear.apply(x, W, b)
 
 
+NARROW_MAX_ROWS = 8192   # the backward kernels of the two narrow layers use at most 64 CTAs
+
+
+def narrow_ok(x, D):
+    return (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.shape[0] <= NARROW_MAX_ROWS
+            and 32 <= D <= 256 and 1024 % D == 0)
+
+
+class _ActionEncoder(torch.autograd.Function):
+    """aenc = relu(Wa a + ba) (ACIQN:399, 472) for the B sampled states: one launch forward, one backward (d Wa, d ba and,
+    for the actor update, d a) instead of sgemm + K5 and K5 backward + two thin products."""
+
+    @staticmethod
+    def forward(ctx, actions, wa, ba):
+        actions = actions.contiguous()
+        aenc = _lib.action_encoder_fwd(actions, wa, ba)
+        ctx.save_for_backward(actions, wa, aenc)
+        return aenc
+
+    @staticmethod
+    def backward(ctx, daenc):
+        actions, wa, aenc = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        dwa, dba, dact = _lib.action_encoder_bwd(daenc.contiguous(), aenc, actions, wa, want_dact=need[0])
+        return dact, dwa if need[1] else None, dba if need[2] else None
+
+
+def action_encoder(actions, wa, ba):
+    return _ActionEncoder.apply(actions, wa, ba)
+
+
+class _AtanHead(torch.autograd.Function):
+    """act = s atan(W3 h + b3) (ACIQN:318-321): one launch forward, one backward."""
+
+    @staticmethod
+    def forward(ctx, h, w3, b3, scale):
+        h = h.contiguous()
+        y, act = _lib.atan_head_fwd(h, w3, b3, scale)
+        ctx.save_for_backward(h, w3, y)
+        ctx.scale = float(scale)
+        return act
+
+    @staticmethod
+    def backward(ctx, dact):
+        h, w3, y = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        dh, dw3, db3 = _lib.atan_head_bwd(dact.contiguous(), y, h, w3, ctx.scale, want_dh=need[0])
+        return dh, dw3 if need[1] else None, db3 if need[2] else None, None
+
+
+def atan_head(h, w3, b3, scale):
+    return _AtanHead.apply(h, w3, b3, scale)
+
+
 def linear_scale_relu(x, W, bias, scale, n_tau):
     if not x.is_cuda:
         raise RuntimeError("linear_scale_relu runs on CUDA only (no CPU fallback)")

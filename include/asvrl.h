@@ -600,6 +600,26 @@ ASVRL_API int asvrl_c51_greedy(const float* zv, const float* za, const float* bv
                                long rows, int n_actions, int atoms, int* action, float* q_out /* nullable */,
                                void* stream);
 
+/* The two narrow layers of the AC-IQN update, each direction in one launch (batch = the learner's sampled states; the
+ * backward kernels keep per-CTA partial column sums in `partials` — asvrl_narrow_bwd_partials(dim) floats — and the last
+ * CTA, by the zero-initialised ticket `counter` which it leaves at zero, adds them in a fixed order: deterministic).
+ * 32 <= dim <= 256, a divisor of 1024.
+ *   action encoder (ACIQN:399, 472): aenc [B][dim] = relu(wa a + ba), actions [B][2], wa [dim][2], ba [dim];
+ *     backward: dwa [dim][2], dba [dim], dact [B][2] (nullable) from daenc [B][dim] and the saved aenc.
+ *   actor head (ACIQN:318-321): y [B][2] = w3 h + b3, actions = atan_scale * atan(y); h [B][dim], w3 [2][dim], b3 [2];
+ *     backward: dh [B][dim] (nullable), dw3 [2][dim], db3 [2] from dact [B][2] and the saved y, h. */
+ASVRL_API int asvrl_action_encoder_fwd(const float* actions, const float* wa, const float* ba, int batch, int dim,
+                                       float* aenc, void* stream);
+ASVRL_API int asvrl_action_encoder_bwd(const float* daenc, const float* aenc, const float* actions, const float* wa,
+                                       int batch, int dim, float* dwa, float* dba, float* dact /* nullable */,
+                                       float* partials, uint32_t* counter, void* stream);
+ASVRL_API long asvrl_narrow_bwd_partials(int dim);
+ASVRL_API int asvrl_atan_head_fwd(const float* h, const float* w3, const float* b3, float atan_scale, int batch, int dim,
+                                  float* y, float* actions, void* stream);
+ASVRL_API int asvrl_atan_head_bwd(const float* dact, const float* y, const float* h, const float* w3, float atan_scale,
+                                  int batch, int dim, float* dh /* nullable */, float* dw3, float* db3, float* partials,
+                                  uint32_t* counter, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -330,3 +330,34 @@ def test_linear_tf32x3_in_a_cuda_graph_and_rejects_bad_shapes():
             _lib.linear_tf32x3(torch.zeros(bad, device=DEV), torch.zeros((128, bad[1]), device=DEV))
     with pytest.raises(RuntimeError):
         _lib.linear_tf32x3(torch.zeros((64, 64), device=DEV), torch.zeros((100, 64), device=DEV))
+
+
+@pytest.mark.parametrize("B", [1024, 64, 1, 77, 4096])
+def test_narrow_layers_match_torch(B):
+    """The action encoder and the actor's atan head (one launch each way) against the same layers in float64 autograd."""
+    from distributional_rl_decision_and_control_b200.policy.iqn_ops import action_encoder, atan_head
+    g = torch.Generator(device=DEV).manual_seed(B)
+    r = lambda *s: torch.randn(s, device=DEV, generator=g)
+    D = 128
+    a, wa, ba, up = (r(B, 2).clamp(-1, 1).requires_grad_(True), (r(D, 2) * 0.7).requires_grad_(True),
+                     (r(D) * 0.7).requires_grad_(True), r(B, D))
+    out = action_encoder(a, wa, ba)
+    out.backward(up)
+    a64, wa64, ba64 = (t.detach().double().requires_grad_(True) for t in (a, wa, ba))
+    ref = torch.relu(a64 @ wa64.t() + ba64)
+    ref.backward(up.double())
+    close(out.detach(), ref.detach(), "aenc")
+    for name, got, want in (("d actions", a.grad, a64.grad), ("d wa", wa.grad, wa64.grad), ("d ba", ba.grad, ba64.grad)):
+        close(got, want, name)
+    h, w3, b3, upa = r(B, D).relu().requires_grad_(True), (r(2, D) * 0.1).requires_grad_(True), r(2).requires_grad_(True), r(B, 2)
+    s = 2.0 / 3.141592653589793
+    act = atan_head(h, w3, b3, s)
+    act.backward(upa)
+    h64, w64, b64 = (t.detach().double().requires_grad_(True) for t in (h, w3, b3))
+    ref = s * torch.atan(h64 @ w64.t() + b64)
+    ref.backward(upa.double())
+    close(act.detach(), ref.detach(), "actions")
+    for name, got, want in (("d h", h.grad, h64.grad), ("d w3", w3.grad, w64.grad), ("d b3", b3.grad, b64.grad)):
+        close(got, want, name)
+    act2 = atan_head(h.detach().requires_grad_(True), w3, b3, s)
+    assert torch.equal(act2.detach(), act.detach())   # deterministic

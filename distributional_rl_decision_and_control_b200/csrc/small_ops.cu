@@ -89,6 +89,7 @@ action_encoder_bwd_kernel(const float* __restrict__ daenc, const float* __restri
   if (!so_last_cta(counter)) return;
   if (tid < D) {
     float t0 = 0.0f, t1 = 0.0f, tb = 0.0f;
+#pragma unroll 8
     for (int g = 0; g < (int)gridDim.x; ++g) {
       const float* pr = part + (size_t)g * 3 * D;
       t0 += __ldcg(pr + tid); t1 += __ldcg(pr + D + tid); tb += __ldcg(pr + 2 * D + tid);
@@ -125,7 +126,7 @@ atan_head_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w3, 
 }
 
 // dy = dact . s / (1 + y^2);  dh[b] = dy[b][0] w3[0] + dy[b][1] w3[1];  dw3[q][c] = sum_b dy[b][q] h[b][c];
-// db3[q] = sum_b dy[b][q].  CTAs of `rpc` rows, partials part[cta][2 D + 2], last CTA sums in CTA order.
+// db3[q] = sum_b dy[b][q].  CTAs of `rpc` rows, partials part[cta][2 D + 2], last CTA sums in a fixed order.
 __global__ void __launch_bounds__(SO_T)
 atan_head_bwd_kernel(const float2* __restrict__ dact, const float2* __restrict__ y, const float* __restrict__ h,
                      const float* __restrict__ w3, float s, int B, int D, int rpc, float* __restrict__ dh,
@@ -147,30 +148,38 @@ atan_head_bwd_kernel(const float2* __restrict__ dact, const float2* __restrict__
     t0 += d0;   // the same in every column thread; column 0's copy is the one kept
     t1 += d1;
   }
+  __shared__ float st[2 * 32];   // parts <= 32
   sm[tid] = s0; sm[SO_T + tid] = s1;
+  if (c == 0) { st[p0] = t0; st[32 + p0] = t1; }
   __syncthreads();
-  float* pr = part + (size_t)blockIdx.x * (2 * D + 2 * parts);
+  float* pr = part + (size_t)blockIdx.x * (2 * D + 2);
   if (p0 == 0) {
     for (int p = 1; p < parts; ++p) { s0 += sm[p * D + c]; s1 += sm[SO_T + p * D + c]; }
     pr[c] = s0; pr[D + c] = s1;
   }
-  if (c == 0) { pr[2 * D + 2 * p0] = t0; pr[2 * D + 2 * p0 + 1] = t1; }
+  if (tid < 2) {
+    float t = 0.0f;
+    for (int p = 0; p < parts; ++p) t += st[32 * tid + p];
+    pr[2 * D + tid] = t;
+  }
   if (!so_last_cta(counter)) return;
   if (tid < D) {
     float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll 8
     for (int g = 0; g < (int)gridDim.x; ++g) {
-      const float* q = part + (size_t)g * (2 * D + 2 * parts);
+      const float* q = part + (size_t)g * (2 * D + 2);
       a0 += __ldcg(q + tid); a1 += __ldcg(q + D + tid);
     }
     dw3[tid] = a0;
     dw3[D + tid] = a1;
   }
-  if (tid == SO_T - 2 || tid == SO_T - 1) {
-    const int q2 = tid - (SO_T - 2);
+  if (tid >= SO_T - 64) {   // the last two warps: db3[0], db3[1] over the <= 64 CTAs, fixed shuffle tree
+    const int q2 = (tid - (SO_T - 64)) >> 5, lane = tid & 31;
     float t = 0.0f;
-    for (int g = 0; g < (int)gridDim.x; ++g)
-      for (int p = 0; p < parts; ++p) t += __ldcg(part + (size_t)g * (2 * D + 2 * parts) + 2 * D + 2 * p + q2);
-    db3[q2] = t;
+    for (int g = lane; g < (int)gridDim.x; g += 32) t += __ldcg(part + (size_t)g * (2 * D + 2) + 2 * D + q2);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) db3[q2] = t;
   }
   if (tid == 0) *counter = 0u;
 }

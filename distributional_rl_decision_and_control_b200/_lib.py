@@ -73,6 +73,7 @@ _SIGNATURES = {
     "asvrl_narrow_bwd_partials": (C.c_long, [C.c_int]),
     "asvrl_atan_head_fwd": (C.c_int, [f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, vp]),
     "asvrl_atan_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
+    "asvrl_neg_mean": (C.c_int, [f32p, C.c_long, f32p, vp]),
     "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, i32p, f32p, vp]),
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
@@ -518,6 +519,14 @@ def atan_head_bwd(dact, y, h, w3, scale, want_dh=True):
     check(lib().asvrl_atan_head_bwd(ptr(dact, f), ptr(y, f), ptr(h, f), ptr(w3, f), float(scale), B, D, ptr(dh), ptr(dw3),
                                     ptr(db3), ptr(part), ptr(cnt), stream_ptr()), "asvrl_atan_head_bwd")
     return dh, dw3, db3
+
+
+def neg_mean(x):
+    """-mean(x) as a 0-d tensor: one launch, fixed summation order."""
+    x = x.contiguous()
+    out = torch.empty((), dtype=torch.float32, device=x.device)
+    check(lib().asvrl_neg_mean(ptr(x, torch.float32), x.numel(), ptr(out), stream_ptr()), "asvrl_neg_mean")
+    return out
 
 
 def c51_greedy(zv, za, bv, ba, support, n_actions, want_q=False):

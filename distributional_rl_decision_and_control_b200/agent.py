@@ -31,7 +31,8 @@ from .policy.DQN_model import DQN_Policy
 from .policy.IQN_model import IQN_Policy
 from .policy.Rainbow_model import Rainbow_Policy
 from .policy.SAC_model import SAC_Policy
-from .policy.iqn_ops import quantile_huber_loss
+from . import _lib
+from .policy.iqn_ops import quantile_huber_loss, quantile_huber_loss_grad
 from .utils.replay_buffer import ReplayBuffer, state_batch
 
 _TARGET_SALT = 0x9E3779B97F4A7C15
@@ -86,6 +87,7 @@ class Agent():
         # AC-IQN: the critic's quantile trunk runs through K5 (policy/iqn_ops.critic_trunk); False
         # keeps the module-by-module autograd path (the torch fp32 reference of the parity tests)
         self.fused_trunk = bool(fused_trunk)
+        self._actor_dz = None   # the constant gradient of the actor loss, (B, N) of -1 / (B N)
         self._graph = None
         self._dims = (self_dimension, object_dimension, max_object_num, self_feature_dimension,
                       object_feature_dimension, concat_feature_dimension, hidden_dimension)
@@ -388,9 +390,14 @@ class Agent():
             z_next, _ = crit_t(next_states, next_actions, N, taus=taus.get("target"))  # AGENT:399
         crit = local.critic.forward_fused if fused else local.critic
         z, tau = crit(states, actions, N, taus=taus.get("local"))        # AGENT:403
-        critic_loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones,
-                                             self.GAMMA, 1.0)            # K4 = AGENT:401-412
-        critic_loss.backward()
+        if fused:
+            # K4 = AGENT:401-412; its launch already holds d loss / d z, so the backward starts at z
+            critic_loss, _, dz = quantile_huber_loss_grad(z, tau.squeeze(-1), z_next, rewards, dones, self.GAMMA, 1.0)
+            z.backward(dz)
+        else:
+            critic_loss, _ = quantile_huber_loss(z, tau.squeeze(-1), z_next, rewards, dones,
+                                                 self.GAMMA, 1.0)        # K4 = AGENT:401-412
+            critic_loss.backward()
         self._clip_and_step(self.critic_optimizer, list(local.critic.parameters()))  # AGENT:414-416
 
         # actor step -------------------------------------------------------------------
@@ -400,8 +407,15 @@ class Agent():
                                               param_grads=False)         # AGENT:420-422
         else:
             q, _ = local.critic(states, local.actor(states), N, taus=taus.get("actor"))
-        actor_loss = -q.mean()
-        actor_loss.backward()
+        if fused:
+            # AGENT:423-425: the loss in one launch; its gradient is the constant -1 / (B N), kept between updates
+            actor_loss = _lib.neg_mean(q.detach())
+            if self._actor_dz is None or self._actor_dz.shape != q.shape:
+                self._actor_dz = torch.full_like(q, -1.0 / q.numel(), requires_grad=False)
+            q.backward(self._actor_dz)
+        else:
+            actor_loss = -q.mean()
+            actor_loss.backward()
         self._clip_and_step(self.actor_optimizer, list(local.actor.parameters()))  # AGENT:424-427
         return critic_loss.detach(), actor_loss.detach()
 

@@ -14,8 +14,9 @@
 // Scaling.  Gradients are small numbers and the operands are two fp16 pieces, so dz is multiplied by a power of two S
 // chosen in the prologue from max |dz| (S max|dz| in [256, 512)); dP1 = dH1 . feats also carries the observation
 // features' range (thrust up to 1000 N gives features in the hundreds) and uses S1 = S 2^-k with 2^-k max feats in
-// (1, 2] (`fmax`, a device word the caller reduces from feats).  Both are exact and are removed again here (daenc,
-// dfeats) and in K12's finalize pass.
+// (1, 2] (max feats: `fmax`, a device word of the caller, or — `fmax` NULL and `repack` 0 — the 64 partial maxima that
+// K10's weight-pack launch leaves behind the image when it prepares this workspace).  Both are exact and are removed
+// again here (daenc, dfeats) and in K12's finalize pass.
 //
 // The per-sample sums over the N quantile rows are warp transposes (lane = row): N must be a power of two <= 32.
 // Structure, operand buffers, barriers and the two tile slots are K10's (critic_umma.cu); the weight ring streams
@@ -32,6 +33,7 @@ constexpr int CB_CHUNK_B = 2 * CB_TILE_B;
 constexpr int CB_WSTAGES = 3;
 constexpr int CB_W_CHUNKS = 6;
 constexpr int CB_IMAGE_B = CB_W_CHUNKS * CB_CHUNK_B;   // 192 KB
+constexpr int CB_FPART = 64;                           // partial maxima of feats kept behind the image (float each)
 constexpr float CB_WSCALE = 64.0f, CB_WUNSCALE = 1.0f / 64.0f;
 
 constexpr int CB_OFF_X = 0;
@@ -72,8 +74,12 @@ struct CriticBwdArgs {
 
 // chunk 0, 1: B[n = i][k = j - 64 c] = Wh2[j][i]; chunk 2 + 2 nh + c: B[n][k] = Wh[64 c + k][128 nh + n]
 __global__ void __launch_bounds__(256)
-critic_bwd_pack_kernel(const float* __restrict__ wh, const float* __restrict__ wh2, unsigned char* __restrict__ image) {
+critic_bwd_pack_kernel(const float* __restrict__ wh, const float* __restrict__ wh2, unsigned char* __restrict__ image,
+                       const float* __restrict__ fmax) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  // the 64 partial maxima of feats behind the image (written by K10's pack launch when it prepares this workspace):
+  // a stand-alone pack leaves the caller's value, or the documented default (2^8, i.e. S1 = S 2^-8)
+  if (t < CB_FPART) reinterpret_cast<float*>(image + CB_IMAGE_B)[t] = t ? 0.0f : (fmax ? __ldg(fmax) : 256.0f);
   if (t >= CB_W_CHUNKS * CB_H * 8) return;
   const int c = t / (CB_H * 8), n = (t / 8) % CB_H, oc = t & 7;
   float v[8];
@@ -177,6 +183,14 @@ critic_backward_kernel(const CriticBwdArgs a) {
       sm += __shfl_xor_sync(0xffffffffu, sm, o);
     }
     if (lane == 0) { s_red[warp] = mx; s_red[CB_THREADS / 32 + warp] = sm; }
+    if (FULL && warp == 0) {
+      // max feats: the caller's word, else the partial maxima the forward's pack launch left behind the weight image
+      const float* fp = reinterpret_cast<const float*>(a.image + CB_IMAGE_B);
+      float fm = a.fmax ? __ldg(a.fmax) : fmaxf(__ldg(fp + lane), __ldg(fp + 32 + lane));
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) fm = fmaxf(fm, __shfl_xor_sync(0xffffffffu, fm, o));
+      if (lane == 0) s_red[2 * (CB_THREADS / 32)] = fm;
+    }
   }
   um_tc_before();
   __syncthreads();
@@ -192,8 +206,8 @@ critic_backward_kernel(const CriticBwdArgs a) {
       S = ldexpf(1.0f, p);                  // S mx in [256, 512)
     }
     float F = 1.0f / 256.0f;   // S1 / S
-    if (FULL && a.fmax) {
-      const float fm = __ldg(a.fmax);
+    if (FULL) {
+      const float fm = s_red[2 * (CB_THREADS / 32)];
       F = 1.0f;
       if (fm > 2.0f && fm < 3.0e38f) {
         int e;
@@ -535,7 +549,7 @@ static cudaError_t cb_attr() {
 
 using namespace asvrl;
 
-extern "C" long asvrl_critic_backward_workspace(void) { return (long)CB_IMAGE_B; }
+extern "C" long asvrl_critic_backward_workspace(void) { return (long)CB_IMAGE_B + CB_FPART * (long)sizeof(float); }
 
 extern "C" int asvrl_critic_backward(const float* dz, const void* r3_img, const void* h2_img, const void* h1_img,
                                      const float* feats, const float* aenc, const float* wh, const float* wh2,
@@ -573,7 +587,7 @@ extern "C" int asvrl_critic_backward(const float* dz, const void* r3_img, const 
   cudaStream_t st = (cudaStream_t)stream;
   if (repack) {
     const int n = CB_W_CHUNKS * CB_H * 8;
-    critic_bwd_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wh, wh2, (unsigned char*)workspace);
+    critic_bwd_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wh, wh2, (unsigned char*)workspace, fmax);
     if (int rc = check_launch("asvrl_critic_backward (pack)")) return rc;
   }
   CriticBwdArgs a;

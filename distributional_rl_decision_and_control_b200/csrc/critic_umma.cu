@@ -97,9 +97,31 @@ struct CriticArgs {
 // B[n = i][k = j - 64 c] = Wh2[j][i]; chunk 2 + 2 nh + c: B[n][k] = Wh[64 c + k][128 nh + n].
 __global__ void __launch_bounds__(256)
 critic_pack_kernel(const float* __restrict__ wc, const float* __restrict__ wh, const float* __restrict__ wh2,
-                   unsigned char* __restrict__ image, unsigned char* __restrict__ bwd_image) {
+                   unsigned char* __restrict__ image, unsigned char* __restrict__ bwd_image,
+                   const float4* __restrict__ feats4, int n_feats4, float* __restrict__ fpart) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;   // one 16-byte chunk (8 k) of one row of one chunk
   const int n_fwd = CF_W_CHUNKS * CF_H * 8;
+  if (fpart) {
+    // K11 scales its dP1 image by a power of two chosen from max feats (critic_bwd_umma.cu): every CTA of this launch
+    // leaves the maximum of its grid-stride share in fpart[blockIdx.x] (64 slots; the unused ones are zeroed), K11's
+    // prologue takes the maximum of the 64.  No extra launch, no atomics, order independent.
+    __shared__ float wmax[8];
+    float m = 0.0f;
+#pragma unroll 4
+    for (int i = t; i < n_feats4; i += (int)(gridDim.x * blockDim.x)) {
+      const float4 f = __ldg(feats4 + i);
+      m = fmaxf(fmaxf(m, fmaxf(f.x, f.y)), fmaxf(f.z, f.w));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int w = 1; w < 8; ++w) m = fmaxf(m, wmax[w]);
+      if (blockIdx.x < 64) fpart[blockIdx.x] = m;
+    }
+    if (blockIdx.x == 0 && threadIdx.x >= gridDim.x && threadIdx.x < 64) fpart[threadIdx.x] = 0.0f;
+  }
   if (t >= n_fwd + (bwd_image ? 6 * CF_H * 8 : 0)) return;
   const bool bwd = t >= n_fwd;
   const int u = bwd ? t - n_fwd : t;
@@ -534,7 +556,10 @@ extern "C" int asvrl_critic_forward(const float* tau_in, uint64_t seed, uint64_t
   cudaStream_t st = (cudaStream_t)stream;
   if (repack) {
     const int n = (CF_W_CHUNKS + (bwd_workspace ? 6 : 0)) * CF_H * 8;
-    critic_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wc, wh, wh2, (unsigned char*)workspace, (unsigned char*)bwd_workspace);
+    // with a backward workspace the launch also leaves max feats for K11 behind the packed image (64 partial maxima)
+    float* fpart = bwd_workspace ? reinterpret_cast<float*>((unsigned char*)bwd_workspace + 6 * CF_CHUNK_B) : nullptr;
+    critic_pack_kernel<<<(n + 255) / 256, 256, 0, st>>>(wc, wh, wh2, (unsigned char*)workspace, (unsigned char*)bwd_workspace,
+                                                        reinterpret_cast<const float4*>(feats), batch * (CF_W / 4), fpart);
     if (int rc = check_launch("asvrl_critic_forward (pack)")) return rc;
   }
   CriticArgs a;

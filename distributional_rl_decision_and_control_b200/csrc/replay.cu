@@ -49,52 +49,39 @@ replay_count_kernel(const uint32_t* __restrict__ status, int n_asv, int n_groups
   if (!is_last) return;
   __threadfence();
   // exclusive scan of n_groups counts by one CTA: chunked serial + shared scan
-  __shared__ uint32_t chunk_sum[SCAN_T];
+  __shared__ uint32_t warp_tot[SCAN_T / 32];
   const int per = (n_groups + SCAN_T - 1) / SCAN_T;
   const int b0 = min(threadIdx.x * per, n_groups), b1 = min(b0 + per, n_groups);
   uint32_t s = 0;
+#pragma unroll 4
   for (int b = b0; b < b1; ++b) s += __ldcg(&ws[4 + b]);
-  chunk_sum[threadIdx.x] = s;
+  // block-wide exclusive scan of the per-thread sums: shuffles inside a warp, then over the 8 warp totals
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t inc = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_tot[w] = inc;
   __syncthreads();
+  uint32_t run = inc - s, total_new = 0;
+#pragma unroll
+  for (int t = 0; t < SCAN_T / 32; ++t) {
+    const uint32_t c = warp_tot[t];
+    if (t < w) run += c;
+    total_new += c;
+  }
   if (threadIdx.x == 0) {
-    uint32_t run = 0;
-    for (int t = 0; t < SCAN_T; ++t) { uint32_t c = chunk_sum[t]; chunk_sum[t] = run; run += c; }
     const unsigned long long base = head_size[0];
-    ws[1] = run;
+    ws[1] = total_new;
     ws[2] = (uint32_t)base; ws[3] = (uint32_t)(base >> 32);
-    const unsigned long long total = base + run;
+    const unsigned long long total = base + total_new;
     head_size[0] = total;
     head_size[1] = total < (unsigned long long)capacity ? total : (unsigned long long)capacity;
     ws[0] = 0u;  // ticket left clean for the next call
   }
-  __syncthreads();
-  uint32_t run = chunk_sum[threadIdx.x];
   for (int b = b0; b < b1; ++b) { uint32_t c = __ldcg(&ws[4 + b]); ws[4 + b] = run; run += c; }
-}
-
-// source of element q of a row (RB:60-67 padding is already in the obs tensors: zero rows)
-__device__ __forceinline__ float row_elem(int q, size_t i, const float* obs_self, const float* obs_obj,
-                                          const float* obs_mask, const void* actions, int discrete,
-                                          const float* reward, const float* nself, const float* nobj,
-                                          const float* nmask, const uint32_t* status) {
-  if (q < ASVRL_ROW_OBJ) return obs_self[i * 7 + q];
-  if (q < ASVRL_ROW_NOBJ) return obs_obj[i * 25 + (q - ASVRL_ROW_OBJ)];
-  if (q == ASVRL_ROW_NOBJ) {
-    const float* mk = obs_mask + i * 5;
-    return mk[0] + mk[1] + mk[2] + mk[3] + mk[4];
-  }
-  if (q < ASVRL_ROW_REW) {
-    if (discrete) return q == ASVRL_ROW_ACT ? (float)((const int32_t*)actions)[i] : 0.0f;
-    return ((const float*)actions)[i * 2 + (q - ASVRL_ROW_ACT)];
-  }
-  if (q == ASVRL_ROW_REW) return reward[i];
-  if (q < ASVRL_ROW_NOBJ_F) return nself[i * 7 + (q - ASVRL_ROW_NSELF)];
-  if (q < ASVRL_ROW_NNOBJ) return nobj[i * 25 + (q - ASVRL_ROW_NOBJ_F)];
-  if (q == ASVRL_ROW_NNOBJ) {
-    const float* mk = nmask + i * 5;
-    return mk[0] + mk[1] + mk[2] + mk[3] + mk[4];
-  }
-  return (status[i] & ASVRL_S_DONE) ? 1.0f : 0.0f;
 }
 
 // pass 2: a CTA owns one 64-ASV group; the (row, element) items are flattened over its threads, so
@@ -128,15 +115,59 @@ replay_scatter_kernel(float* __restrict__ rows, int64_t capacity, const float* _
     use_term[tid] = (ended && i < n_asv) ? ended[i / rpe] : 0;
   }
   __syncthreads();
-#pragma unroll 2
-  for (int e = tid; e < PUSH_G * ASVRL_ROW; e += SCAT_T) {
-    const int r = e / ASVRL_ROW, q = e - r * ASVRL_ROW;
+  // 18 items per thread in batches of 6.  The source of an item is chosen by selects (no branch around a load) and
+  // every item is ONE 4-byte load, so a thread has its 6 requests in flight before the first store; the two object
+  // counts of a row (5 mask loads and a sum each) are left to a second, equally flat pass.  With a branch chain
+  // around the loads the divergent paths of a warp serialised: 18 dependent round trips per thread.
+  constexpr int ITEMS = PUSH_G * ASVRL_ROW, PER_T = (ITEMS + SCAT_T - 1) / SCAT_T, BATCH = 6;
+  static_assert(PER_T % BATCH == 0, "batching of the scatter loop");
+  for (int k0 = 0; k0 < PER_T; k0 += BATCH) {
+    uint32_t v[BATCH];
+    int kind[BATCH];      // 0 float, 1 int32 action id, 2 status word -> done, 3 constant zero
+    long long dst[BATCH];
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      const int e = tid + (k0 + k) * SCAT_T;
+      const int r = min(e / ASVRL_ROW, PUSH_G - 1), q = e - (e / ASVRL_ROW) * ASVRL_ROW;
+      const long long d = e < ITEMS ? dst_row[r] : -1;
+      const bool skip = q == ASVRL_ROW_NOBJ || q == ASVRL_ROW_NNOBJ;
+      dst[k] = (d >= 0 && !skip) ? d * ASVRL_ROW + q : -1;
+      const size_t i = (size_t)(i0 + r);
+      const bool t = use_term[r];  // the env ended: its next state is the kept terminal observation
+      const float* src = obs_self + i * 7 + q;
+      int kd = 0;
+      if (q >= ASVRL_ROW_OBJ) src = obs_obj + i * 25 + (q - ASVRL_ROW_OBJ);
+      if (q >= ASVRL_ROW_ACT) {
+        src = discrete ? (const float*)actions + i : (const float*)actions + i * 2 + (q - ASVRL_ROW_ACT);
+        kd = discrete ? (q == ASVRL_ROW_ACT ? 1 : 3) : 0;
+      }
+      if (q >= ASVRL_ROW_REW) { src = reward + i; kd = 0; }
+      if (q >= ASVRL_ROW_NSELF) src = (t ? tself : nself) + i * 7 + (q - ASVRL_ROW_NSELF);
+      if (q >= ASVRL_ROW_NOBJ_F) src = (t ? tobj : nobj) + i * 25 + (q - ASVRL_ROW_NOBJ_F);
+      if (q >= ASVRL_ROW_DONE) { src = (const float*)status + i; kd = 2; }
+      kind[k] = kd;
+      v[k] = 0u;
+      if (dst[k] >= 0) v[k] = __ldg(reinterpret_cast<const uint32_t*>(src));
+    }
+#pragma unroll
+    for (int k = 0; k < BATCH; ++k) {
+      if (dst[k] < 0) continue;
+      float f = __uint_as_float(v[k]);
+      if (kind[k] == 1) f = (float)(int32_t)v[k];
+      else if (kind[k] == 2) f = (v[k] & ASVRL_S_DONE) ? 1.0f : 0.0f;
+      else if (kind[k] == 3) f = 0.0f;
+      rows[dst[k]] = f;
+    }
+  }
+  // the object counts (RB:60-67: the mask is "first n ones"): one thread per (row, state / next state)
+  if (tid < 2 * PUSH_G) {
+    const int r = tid >> 1, nx = tid & 1;
     const long long d = dst_row[r];
     if (d >= 0) {
-      const bool t = use_term[r];  // the env ended: its next state is the kept terminal observation
-      rows[(size_t)d * ASVRL_ROW + q] = row_elem(q, (size_t)(i0 + r), obs_self, obs_obj, obs_mask, actions,
-                                                 discrete, reward, t ? tself : nself, t ? tobj : nobj,
-                                                 t ? tmask : nmask, status);
+      const size_t i = (size_t)(i0 + r);
+      const float* mk = (nx ? (use_term[r] ? tmask : nmask) : obs_mask) + i * 5;
+      const float m0 = __ldg(mk), m1 = __ldg(mk + 1), m2 = __ldg(mk + 2), m3 = __ldg(mk + 3), m4 = __ldg(mk + 4);
+      rows[d * ASVRL_ROW + (nx ? ASVRL_ROW_NNOBJ : ASVRL_ROW_NOBJ)] = m0 + m1 + m2 + m3 + m4;
     }
   }
 }

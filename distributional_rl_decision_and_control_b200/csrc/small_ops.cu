@@ -184,6 +184,42 @@ atan_head_bwd_kernel(const float2* __restrict__ dact, const float2* __restrict__
   if (tid == 0) *counter = 0u;
 }
 
+// out[0] = -mean(x): the actor loss (AGENT:423, "-Q.mean()") by ONE CTA in a fixed order (torch: mean + neg = two
+// launches, and their autograd nodes cost four more; the loss' gradient is the constant -1 / n, which the caller keeps).
+__global__ void __launch_bounds__(SO_T)
+neg_mean_kernel(const float* __restrict__ x, long n, float* __restrict__ out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float acc = 0.0f;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    const long n4 = n >> 2;
+    for (long i0 = 0; i0 < n4; i0 += 8L * SO_T) {
+      float4 v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const long i = i0 + (long)k * SO_T + tid;
+        v[k] = i < n4 ? __ldg(x4 + i) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+    }
+    for (long i = (n4 << 2) + tid; i < n; i += SO_T) acc += __ldg(x + i);
+  } else {
+    for (long i = tid; i < n; i += SO_T) acc += __ldg(x + i);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float wsum[SO_T / 32];
+  if (lane == 0) wsum[warp] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    float t = lane < SO_T / 32 ? wsum[lane] : 0.0f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) out[0] = -t / (float)n;
+  }
+}
+
 }  // namespace asvrl
 
 using namespace asvrl;
@@ -247,4 +283,11 @@ extern "C" int asvrl_atan_head_bwd(const float* dact, const float* y, const floa
   atan_head_bwd_kernel<<<grid, SO_T, 0, (cudaStream_t)stream>>>((const float2*)dact, (const float2*)y, h, w3, atan_scale,
                                                                batch, dim, rpc, dh, dw3, db3, partials, counter);
   return check_launch("asvrl_atan_head_bwd");
+}
+
+extern "C" int asvrl_neg_mean(const float* x, long n, float* out, void* stream) {
+  if (!x || !out) return fail(ASVRL_E_BADARG, "asvrl_neg_mean: null pointer");
+  if (n < 1 || n > (1L << 24)) return fail(ASVRL_E_BADARG, "asvrl_neg_mean: n = %ld outside [1, 2^24]", n);
+  neg_mean_kernel<<<1, SO_T, 0, (cudaStream_t)stream>>>(x, n, out);
+  return check_launch("asvrl_neg_mean");
 }

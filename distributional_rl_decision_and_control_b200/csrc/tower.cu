@@ -75,6 +75,7 @@ tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ fea
     const bool own = j < d.SF;
     const int k = own ? 0 : (j - d.SF) / d.OF;
     const int nin = own ? d.SD : d.OD;
+#pragma unroll 4   // four rows' loads in flight per thread
     for (int b = blockIdx.x * RL + rl; b < d.B; b += gridDim.x * RL) {
       const size_t i = (size_t)b * d.W + j;
       const float g = feats[i] > 0.0f ? dfeats[i] : 0.0f;  // ReLU' and the mask: a masked row is 0
@@ -112,7 +113,7 @@ tower_bwd_kernel(const float* __restrict__ dfeats, const float* __restrict__ fea
     const int nin = c < d.SF ? d.SD : d.OD;
     if (q < TW_MAXIN && q >= nin) continue;
     float s = 0.0f;
-#pragma unroll 8
+#pragma unroll 16
     for (int g = 0; g < (int)gridDim.x; ++g) s += __ldcg(part + (size_t)g * n_val + o);
     if (c < d.SF) { if (q == TW_MAXIN) dbs[c] = s; else dWs[c * d.SD + q] = s; }
     else { const int f = c - d.SF; if (q == TW_MAXIN) dbo[f] = s; else dWo[f * d.OD + q] = s; }
@@ -140,8 +141,8 @@ static int tower_bwd_grid(int batch) {
   static int cap = 0;
   if (cap == 0) {
     const char* e = getenv("ASVRL_TOWER_BWD_GRID");   // tuning knob; the partial buffer is sized for the default cap
-    cap = e ? atoi(e) : 32;   // 32 CTAs: 11.9 us at B = 1024 (64: 13.3, 16: 14.2; profiles/probes/small_kernels_probe.py)
-    if (cap < 1 || cap > 64) cap = 32;
+    cap = e ? atoi(e) : 64;   // 64 CTAs: 8.7 us at B = 1024 (32: 9.4; profiles/probes/small_kernels_probe.py)
+    if (cap < 1 || cap > 64) cap = 64;
   }
   int g = (batch + 15) / 16;
   return g > cap ? cap : (g < 1 ? 1 : g);

@@ -71,6 +71,23 @@ def quantile_huber_loss(z, tau, z_next, r, done, gamma=0.99, kappa=1.0):
                                 gamma, kappa, ws)
 
 
+def quantile_huber_loss_grad(z, tau, z_next, r, done, gamma=0.99, kappa=1.0):
+    """The same launch without an autograd node: -> (scalar loss, per-sample loss, d loss / d z).  For a caller that
+    continues with ``z.backward(grad)`` itself — ``loss.backward()`` would only multiply ``grad`` by a freshly filled
+    one and zero-fill a gradient for the per-sample output (three small launches per update)."""
+    if not z.is_cuda:
+        raise RuntimeError("quantile_huber_loss_grad runs on CUDA only (no CPU fallback)")
+    key = (z.device.index, torch.cuda.current_stream(z.device).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None:
+        ws = _WS[key] = torch.zeros(1, dtype=torch.int32, device=z.device)
+    with torch.no_grad():
+        loss, lps, grad = _lib.qhuber_fwd_bwd(z.detach().contiguous(), tau.reshape(z.shape).contiguous(),
+                                              z_next.contiguous(), r.reshape(-1).contiguous(),
+                                              done.reshape(-1).contiguous(), float(gamma), float(kappa), ws)
+    return loss.reshape(()), lps, grad
+
+
 def _wgrad(d_out, x, splits=64):
     """d_out^T x for (M, a) and (M, b) with M = B*N in the tens of thousands: cuBLAS runs the plain
     product (K = M, a 128 x 256 output) on a handful of CTAs (~110 us at C3), so the contraction is
@@ -197,22 +214,25 @@ class _CriticTrunkUmma(torch.autograd.Function):
                                   pack_backward=bws)
         z, tau = out[0], out[1]
         if save:
-            fmax = feats.amax().reshape(1) if need[0] or any(need[2:10]) else feats.new_zeros(1)
-            ctx.save_for_backward(feats, aenc, Wh, Wh2, wo, fmax, bws, *out[2])
+            # max feats (the scale of K11's dP1 image) is left behind the backward image by the same pack launch
+            ctx.save_for_backward(feats, aenc, Wh, Wh2, wo, bws, *out[2])
         ctx.n_tau = n_tau
         ctx.mark_non_differentiable(tau)
+        ctx.set_materialize_grads(False)   # no (B, N) zero fill for d tau
         return z, tau
 
     @staticmethod
     def backward(ctx, dz, _dtau):
-        feats, aenc, Wh, Wh2, wo, fmax, bws, cos_i, h1_i, h2_i, r3_i = ctx.saved_tensors
+        g = [None] * 14
+        if dz is None:
+            return tuple(g)
+        feats, aenc, Wh, Wh2, wo, bws, cos_i, h1_i, h2_i, r3_i = ctx.saved_tensors
         need = ctx.needs_input_grad
         n_tau = ctx.n_tau
-        g = [None] * 14
         dz = dz.contiguous()
         if need[0] or any(need[2:10]):
             daenc, dfeats, (dp3, dp2, dp1, aux), scales = _lib.critic_backward(dz, r3_i, h2_i, h1_i, feats, aenc, Wh, Wh2,
-                                                                              wo.reshape(-1), n_tau, fmax=fmax, repack=False,
+                                                                              wo.reshape(-1), n_tau, fmax=None, repack=False,
                                                                               workspace=bws)
             d_wc, d_bc, d_wh, d_bh, d_wh2, d_bh2, d_wo = _lib.critic_wgrad(dp3, dp2, dp1, aux, cos_i, h1_i, h2_i, r3_i,
                                                                            scales, feats.shape[0], n_tau)

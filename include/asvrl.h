@@ -536,7 +536,7 @@ ASVRL_API int asvrl_policy_forward_status(int* status_out);
  *   output layer applied to it, which is linear, so the mean commutes.  `workspace`: asvrl_critic_forward_workspace() bytes, 128-byte aligned, holds the
  *   packed weight image; `repack` != 0 rebuilds it from wc / wh / wh2 first (one small launch), and with
  *   `bwd_workspace` (asvrl_critic_backward_workspace() bytes) the same launch packs asvrl_critic_backward's image
- *   too, so that call can pass repack = 0.
+ *   and the partial maxima of feats behind it, so that call can pass repack = 0 and fmax = NULL.
  *   cos_img / h1_img / h2_img / r3_img: all NULL (inference), or all set (the differentiable pass): the operand images
  *   the backward kernels read — per 128-row tile 1 / 4 / 2 / 2 chunks of asvrl_critic_forward_chunk_bytes() bytes
  *   (fp16 hi | lo pieces of cos, H1 = feats * relu(P1 + bc), H2 = aenc * relu(P2 + bh), R3 = relu(P3 + bh2), in the
@@ -577,7 +577,9 @@ ASVRL_API int asvrl_critic_wgrad_status(int* status_out);
  * -> dP1, dfeats, reading the operand images asvrl_critic_forward saved.  n_tau: a power of two <= 32.
  *   dz [B*N]; feats [B][256], aenc [B][128], wo [128], wh [128][256], wh2 [128][128] as in asvrl_critic_forward;
  *   workspace: asvrl_critic_backward_workspace() bytes (packed Wh2^T | Wh^T image; `repack` != 0 rebuilds it);
- *   daenc [B][128] = d loss / d aenc; fmax (device, nullable): max over feats, sets dP1's power-of-two scale (NULL: 2^-8).
+ *   daenc [B][128] = d loss / d aenc; fmax (device, nullable): max over feats, sets dP1's power-of-two scale.  NULL:
+ *   with `repack` != 0 the scale is 2^-8; with `repack` == 0 it comes from the 64 partial maxima of feats that
+ *   asvrl_critic_forward's weight-pack launch wrote behind the image when it was given this buffer as `bwd_workspace`.
  *   Full pass: dfeats [B][256], dp3_img / dp2_img / dp1_img / aux_img ([tile][2 | 2 | 4 | 1] chunks, 128-byte aligned)
  *   and scales[3] (device: {1/S, 1/S1} for asvrl_critic_wgrad, then sum dz = d loss / d bo) — all set; or all NULL (with h1_img NULL allowed): the actor
  *   update's pass (AGENT:420-427), which needs d z / d aenc only and stops after dP2. */
@@ -619,6 +621,10 @@ ASVRL_API int asvrl_atan_head_fwd(const float* h, const float* w3, const float* 
 ASVRL_API int asvrl_atan_head_bwd(const float* dact, const float* y, const float* h, const float* w3, float atan_scale,
                                   int batch, int dim, float* dh /* nullable */, float* dw3, float* db3, float* partials,
                                   uint32_t* counter, void* stream);
+
+/* out[0] = -mean(x[0 .. n)) in one launch and a fixed order: the actor loss "-Q.mean()" of AGENT:423 (its gradient is
+ * the constant -1 / n, so the learner needs no autograd node for it).  n <= 2^24. */
+ASVRL_API int asvrl_neg_mean(const float* x, long n, float* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -294,3 +294,39 @@ def test_iqn_action_values_match_float64_network(M):
     top2 = want.topk(2, dim=1).values
     clear = (top2[:, 0] - top2[:, 1]) > 4 * RTOL * scale
     assert torch.equal(q.argmax(1)[clear], want.argmax(1)[clear])
+
+
+@pytest.mark.parametrize("B,N,fs", [(1024, 32, 150.0), (64, 8, 1.0), (37, 8, 9.0)])
+def test_feats_maximum_left_by_the_pack_launch(B, N, fs):
+    """K10's weight-pack launch leaves max feats behind K11's image: K11 with fmax = NULL / repack = 0 on that workspace is
+    bit-identical to K11 with the caller's feats.amax() (the scale S1 is a power of two chosen from the same maximum)."""
+    c = _critic()
+    tau, feats, aenc = _inputs(B, N, 7 * B + N, feat_scale=fs)
+    ps = _params(c)
+    g = torch.Generator(device=DEV).manual_seed(B + 1)
+    dz = (torch.randn((B, N), device=DEV, generator=g) * (1.0 / (B * N))).contiguous()
+    bws = _lib.critic_backward_workspace(DEV, shared=False)
+    bws.fill_(0xFF)   # NaN words where nothing is written
+    _, _, (cos_i, h1_i, h2_i, r3_i) = _run(c, tau, feats, aenc, save=True, pack_backward=bws)
+    tail = bws[-256:].view(torch.float32)
+    assert float(tail.max()) == float(feats.amax()) and not bool(torch.isnan(tail).any())
+    a = _lib.critic_backward(dz, r3_i, h2_i, h1_i, feats, aenc, ps[2], ps[4], ps[6], N, fmax=None, repack=False, workspace=bws)
+    b = _lib.critic_backward(dz, r3_i, h2_i, h1_i, feats, aenc, ps[2], ps[4], ps[6], N, fmax=feats.amax().reshape(1))
+    torch.cuda.synchronize()
+    _lib.critic_backward_status()
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[3], b[3])
+    # the dP images (their padding is never written, so compare what K12 makes of them)
+    ga = _lib.critic_wgrad(*a[2], cos_i, h1_i, h2_i, r3_i, a[3], B, N)
+    gb = _lib.critic_wgrad(*b[2], cos_i, h1_i, h2_i, r3_i, b[3], B, N)
+    for x, y in zip(ga, gb):
+        assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("n", [1, 37, 512, 32768, 32768 + 5, 300000])
+def test_neg_mean(n):
+    g = torch.Generator(device=DEV).manual_seed(n)
+    x = torch.randn((n + 1,), device=DEV, generator=g) * 3 + 0.5
+    for v in (x[:n], x[1:]):   # 16-byte aligned and not
+        got = _lib.neg_mean(v)
+        want = -v.double().mean()
+        assert got.shape == () and abs(float(got) - float(want)) <= 1e-6 * max(1.0, float(v.abs().mean()))

@@ -59,6 +59,7 @@ _SIGNATURES = {
     "asvrl_tower_fwd": (C.c_int, [f32p] * 7 + [C.c_int] * 6 + [f32p, vp]),
     "asvrl_tower_bwd": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 5 + [u32p, vp]),
     "asvrl_tower_bwd_partials": (C.c_long, [C.c_int] * 4),
+    "asvrl_tower_bwd_static": (C.c_int, [f32p] * 4 + [C.c_int] * 6 + [f32p] * 4 + [vp]),
     "asvrl_linear_tf32x3": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_long, C.c_int, C.c_int, f32p, C.c_void_p]),
     "asvrl_linear_tf32x3_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_actor_head": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, f32p, C.c_float, C.POINTER(C.c_float * 2),

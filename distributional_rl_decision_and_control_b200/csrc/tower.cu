@@ -187,3 +187,70 @@ extern "C" long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, 
   g = g > 64 ? 64 : (g < 1 ? 1 : g);
   return (long)g * (self_feat + obj_feat) * (TW_MAXIN + 1);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// asvrl_tower_bwd_static: asvrl_tower_bwd for callers that can neither allocate nor bring scratch memory (CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  The per-CTA partial sums and the arrival ticket of
+// tower_bwd_kernel live in a file-scope device array instead of the caller's `partials` / `counter`:
+//   tw_static_scratch = [0] the ticket (a 256-byte header), then 64 CTAs x TW_STATIC_MAXC columns x 9 floats
+// = 295 168 bytes, held by every GPU that loads the library until the process exits.  Host code must not pass the
+// array's NAME to a kernel (on the host it is a stand-in symbol, not a device address): the device address is asked for
+// once per device with cudaGetSymbolAddress, with that device current, and cached.  No cudaMalloc / cudaFree / library
+// allocation on this path.  Every call shares the array: calls that overlap on the GPU (two streams, two threads) race.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace asvrl {
+constexpr int TW_STATIC_MAXC = ASVRL_TOWER_BWD_STATIC_MAX_FEATURES;   // self_feat + obj_feat <= 128 (the reference's tower: 56 + 40)
+constexpr int TW_STATIC_HDR = 64;     // floats in front of the partials (the ticket word, 256-byte aligned rest)
+constexpr long TW_STATIC_FLOATS = TW_STATIC_HDR + 64L * TW_STATIC_MAXC * (TW_MAXIN + 1);
+static __device__ __align__(256) float tw_static_scratch[TW_STATIC_FLOATS];
+}  // namespace asvrl
+
+static float* tw_static_address(const char* what, int* rc_out) {
+  constexpr int MAX_DEV = 64;
+  static float* ptrs[MAX_DEV] = {nullptr};   // per device ordinal; a racing first call resolves to the same address
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+    *rc_out = fail(e != cudaSuccess ? (int)e : ASVRL_E_LIMIT, "%s: cudaGetDevice: %s (device %d)", what,
+                   cudaGetErrorString(e), dev);
+    return nullptr;
+  }
+  float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    e = cudaGetSymbolAddress((void**)&p, tw_static_scratch);   // the current device's copy of the array
+    if (e != cudaSuccess || !p) {
+      *rc_out = fail(e != cudaSuccess ? (int)e : ASVRL_E_NODEV, "%s: cudaGetSymbolAddress: %s", what, cudaGetErrorString(e));
+      return nullptr;
+    }
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+  }
+  *rc_out = 0;
+  return p;
+}
+
+extern "C" int asvrl_tower_bwd_static(const float* dfeats, const float* feats, const float* self_obs,
+                                      const float* objects, int batch, int self_dim, int obj_dim, int max_obj,
+                                      int self_feat, int obj_feat, float* dw_self, float* db_self, float* dw_obj,
+                                      float* db_obj, void* stream) {
+  const char* what = "asvrl_tower_bwd_static";
+  if (!dfeats || !feats || !self_obs || !objects || !dw_self || !db_self || !dw_obj || !db_obj)
+    return fail(ASVRL_E_BADARG, "%s: null pointer", what);
+  TowerDims d;
+  if (int rc = tower_dims(what, batch, self_dim, obj_dim, max_obj, self_feat, obj_feat, &d)) return rc;
+  if (self_feat + obj_feat > TW_STATIC_MAXC)
+    return fail(ASVRL_E_LIMIT, "%s: self_feat + obj_feat = %d exceeds the static scratch (%d columns); use asvrl_tower_bwd "
+                "with caller scratch", what, self_feat + obj_feat, TW_STATIC_MAXC);
+  int rc = 0;
+  float* scratch = tw_static_address(what, &rc);
+  if (!scratch) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the ticket must start at zero; a finished launch leaves it so, an aborted one may not: clear it in stream order
+  cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(uint32_t), st);
+  if (e != cudaSuccess) return fail((int)e, "%s: cudaMemsetAsync: %s", what, cudaGetErrorString(e));
+  const int W32 = (d.W + 31) / 32 * 32, RL = 1024 / W32;
+  const size_t smem = (size_t)RL * d.W * (TW_MAXIN + 1) * sizeof(float);
+  tower_bwd_kernel<<<tower_bwd_grid(batch), RL * W32, smem, st>>>(
+      dfeats, feats, self_obs, objects, d, W32, dw_self, db_self, dw_obj, db_obj, scratch + TW_STATIC_HDR,
+      reinterpret_cast<uint32_t*>(scratch));
+  return check_launch(what);
+}

@@ -429,6 +429,19 @@ ASVRL_API int asvrl_tower_bwd(const float* dfeats, const float* feats, const flo
                               int self_feat, int obj_feat, float* dw_self, float* db_self, float* dw_obj,
                               float* db_obj, float* partials, uint32_t* counter, void* stream);
 ASVRL_API long asvrl_tower_bwd_partials(int batch, int max_obj, int self_feat, int obj_feat);
+/* asvrl_tower_bwd without caller scratch and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and results as asvrl_tower_bwd minus `partials` / `counter`: the
+ * per-CTA partial sums and the arrival ticket live in a file-scope device array of the library (295 168 bytes per GPU
+ * that loads it, held until exit; its device address is resolved once per device with cudaGetSymbolAddress).
+ * Limit: self_feat + obj_feat <= ASVRL_TOWER_BWD_STATIC_MAX_FEATURES, beyond it ASVRL_E_LIMIT.  The call performs no
+ * cudaMalloc / cudaFree / library allocation.  Every call shares the one array, and the ticket is cleared in stream
+ * order before each launch: calls that overlap on the GPU (different streams or threads) RACE — serialise them. */
+#define ASVRL_TOWER_BWD_STATIC_MAX_FEATURES 128
+ASVRL_API int asvrl_tower_bwd_static(const float* dfeats, const float* feats, const float* self_obs,
+                                     const float* objects, int batch, int self_dim, int obj_dim, int max_obj,
+                                     int self_feat, int obj_feat, float* dw_self, float* db_self, float* dw_obj,
+                                     float* db_obj, void* stream);
 
 /* K7 — replaces torch.nn.utils.clip_grad_norm_(params, max_norm) followed by Adam.step()
  * (AGENT:414-416, 424-427 and the other agents' twins) with two launches over a list of tensors:

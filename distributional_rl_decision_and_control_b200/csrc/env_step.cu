@@ -231,7 +231,11 @@ __device__ __forceinline__ void current_at(const EnvConsts& k, const float4* cor
     const float rx = rx0[i * A] - dx, ry = ry0[i * A] - dy;
     const float d2 = rx * rx + ry * ry;
     const float g = co.w * co.z;  // signed circulation: +clockwise, -counter-clockwise (ENV:483-487)
-    const float f = d2 <= r2 ? g * k.solid_k : __fdividef(g * k.inv_2pi, d2);  // ENV:497-501
+    // ENV:497-501.  d2 > core_r^2 on this branch, so the reciprocal needs none of __fdividef's range guards
+    // (six predicated instructions per core on the integration's serial chain); same bits for normal operands
+    float rcp;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(d2));
+    const float f = d2 <= r2 ? g * k.solid_k : (g * k.inv_2pi) * rcp;
     ax -= ry * f;
     ay += rx * f;
   }
@@ -385,6 +389,15 @@ static int pick_shape(int max_robots, int max_obs, int max_cores, int EPB) {
   return max_cores == shape_cores(1) ? 1 : (max_cores == shape_cores(2) ? 2 : 0);
 }
 
+// -DK1_TRACE (debug builds, profiles/probes/k1_trace.py): SM clock of the first step CTA at the phase boundaries
+#ifdef K1_TRACE
+__device__ unsigned long long k1_trace_buf[32];
+#define K1_TR(slot, thread) do { if ((int)blockIdx.x == (FUSED ? fa.n_workers : 0) && threadIdx.x == (thread) && !second) \
+    k1_trace_buf[slot] = clock64(); } while (0)
+#else
+#define K1_TR(slot, thread) do { } while (0)
+#endif
+
 template <bool INJECT, bool FUSED, int SHAPE = 0>
 __global__ void __launch_bounds__(TPB, 7)
 env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ SmemLayout L_,
@@ -419,6 +432,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
   // global load of the prologue — counts, buoy / vortex tables, the state row, the fused tail's
   // episode number and stage tag — is issued before the first dependent use, so a CTA pays ONE
   // DRAM round trip with cold data instead of one per dependent stage. ----
+  K1_TR(0, 0);
   int c_nr = 0, c_no = 0, c_nc = 0, c_ep = 0, c_epn = 0, c_epi = 0, c_tag = -1;
   bool c_v = false;
   if (tid < EPB) {
@@ -499,6 +513,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     m.r_of[tid] = (uint8_t)r;
     m.det_lo[tid] = 0; m.det_hi[tid] = 0;
   }
+  K1_TR(1, 0);
   if (tid < 4) m.cnt[tid] = 0;
   if (!second) {  // CTAs whose envs are all masked out leave at once (the masked re-observation after resets)
     if (!__syncthreads_or(tid < EPB && c_v)) return;
@@ -506,6 +521,8 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     __syncthreads();
   }
 
+  K1_TR(2, 0);
+  K1_TR(3, 32);
   // ---- phase P: compact the (ego, slot) pairs that can possibly end up detected into plist, so
   // the expensive per-pair work below (Philox, Box-Muller, von Mises, fp64 geometry) runs with
   // full warps instead of the ~20 % of lanes a flat pair loop keeps busy.  The filter uses the
@@ -545,6 +562,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       if (keep) m.plist[base + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)((a << 6) | sl);
     }
   }
+  K1_TR(4, 32);
   asm volatile("bar.sync 2, 96;" ::: "memory");
   asm volatile("bar.arrive 1, 128;" ::: "memory");
   }
@@ -579,6 +597,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
           rx0[i * A] = (float)((double)co.x - x);
           ry0[i * A] = (float)((double)co.y - y);
         }
+        K1_TR(5, 0);
         const double x_start = x, y_start = y;
         double dxg = (double)gx - x, dyg = (double)gy - y;
         const double dis_before = sqrt(dxg * dxg + dyg * dyg);  // ENV:254
@@ -620,6 +639,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
           vr1 = s * u_r + c * v_r;
           vr2 = rr;
         }
+        K1_TR(6, 0);
         dxg = (double)gx - x; dyg = (double)gy - y;
         const double dis_after = sqrt(dxg * dxg + dyg * dyg);
         rew = k.timestep_penalty + (float)(dis_before - dis_after);  // ENV:271-277
@@ -645,6 +665,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       }
       m.fl[tid] = fnew;
     }
+    K1_TR(7, 0);
     asm volatile("bar.sync 1, 128;" ::: "memory");  // plist / cnt[0] of warps 1..3 are complete
   }
   if (!INJECT) {
@@ -670,8 +691,11 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       }
     }
   }
+  K1_TR(8, 0);
+  K1_TR(9, 32);
   __syncthreads();
   const int n_pairs = m.cnt[0];
+  K1_TR(10, 0);
 
   // ---- phase B: the compacted pairs, one per thread, with the post-step poses: detection and
   // collision predicates in fp64, body-frame observation and sort key into shared memory;
@@ -738,6 +762,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
   for (int i = tid; i < A * 5; i += TPB) { m.st_mask[i] = 0.0f; m.chit[i] = 0; }
   __syncthreads();
 
+  K1_TR(11, 0);
   // ---- phase B2: rank of every detected candidate among its ego's keys (stable: ties keep slot
   // order, like heapq.nsmallest, WAMV:513-515); the 5 smallest go to the staged observation.
   // Only detected slots have keys, and only their bits are walked. ----
@@ -753,132 +778,151 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
     if (rank < ASVRL_MAX_OBJ) {
       const float* cd = m.cand + (a * S + sl) * 5;
       float* so = m.st_obj + a * 25 + rank * 5;
+      float o5[5];
 #pragma unroll
-      for (int q = 0; q < 5; ++q) so[q] = cd[q];
+      for (int q = 0; q < 5; ++q) { o5[q] = cd[q]; so[q] = o5[q]; }
       m.st_mask[a * 5 + rank] = 1.0f;
       if (out.top_ids && !second) out.top_ids[((size_t)e0 * RP + a) * 5 + rank] = sl;
-    }
-  }
-  __syncthreads();
-
-  // ---- phase C1: COLREGs test of every kept object, one thread per (ego, rank) ----
-  for (int i = tid; i < A * 5; i += TPB) {
-    const int a = i / 5;
-    if (m.st_mask[i] != 0.0f) {
+      // COLREGs test of the kept object (WAMV:398-423) by the thread that placed it: no (ego, rank) pass of its own
+      // (160 items on 128 threads were two rounds) and one CTA barrier fewer on the CTA's serial chain
       const float c = m.c[a], s = m.s[a];
       const float w0 = c * m.vx[a] + s * m.vy[a], w1 = -s * m.vx[a] + c * m.vy[a];
       float phi = 0.0f;
-      const bool hit = colregs_one(k, m.st_obj + i * 5, w0, w1, phi);
-      m.chit[i] = hit ? 1 : 0;
-      m.cphi[i] = phi;
+      const bool hit = colregs_one(k, o5, w0, w1, phi);
+      m.chit[a * 5 + rank] = hit ? 1 : 0;
+      m.cphi[a * 5 + rank] = phi;
     }
   }
   __syncthreads();
 
-  // ---- phase C2: one thread per ego: self observation, reward / done / info ----
-  if (tid < A) {
-    const int a = tid, el = a / RP, r = a - el * RP;
-    const int e = e0 + el;
-    const size_t g = (size_t)e * RP + r;
-    float* ss = m.st_self + a * 7;
-#pragma unroll
-    for (int q = 0; q < 7; ++q) ss[q] = 0.0f;
-    if (m.ok[el]) {
-      const bool present = r < m.nr[el];
-      const uint32_t f0 = m.fl0[a];
-      uint32_t f = m.fl[a], status = 0;
-      float reward = 0.0f, phi = 0.0f;
-      if (!present) {
-        status = (uint32_t)ASVRL_INFO_ABSENT << ASVRL_S_INFO_SHIFT;
-        f = 0;
-      } else if (f0 & ASVRL_F_DEACTIVATED) {  // WAMV:437-438, ENV:295-304
-        const int info = (f0 & ASVRL_F_COLLISION) ? ASVRL_INFO_DEACT_COLLISION
-                         : (f0 & ASVRL_F_REACH_GOAL) ? ASVRL_INFO_DEACT_GOAL : ASVRL_INFO_DEACT_INVALID;
-        status = ASVRL_S_DONE | ASVRL_S_WAS_DEACTIVATED | ((uint32_t)info << ASVRL_S_INFO_SHIFT);
-      } else {
-        const float c = m.c[a], s = m.s[a];
-        const float dgx = (float)((double)m.gx[a] - m.px[a]), dgy = (float)((double)m.gy[a] - m.py[a]);
-        ss[0] = c * dgx + s * dgy; ss[1] = -s * dgx + c * dgy;  // WAMV:443-453
-        ss[2] = c * m.vx[a] + s * m.vy[a]; ss[3] = -s * m.vx[a] + c * m.vy[a];
-        ss[4] = m.vz[a]; ss[5] = m.Tl[a]; ss[6] = m.Tr[a];
-        bool apply = false;  // first hit in sorted order wins, WAMV:517-521
-#pragma unroll
-        for (int t = 0; t < ASVRL_MAX_OBJ; ++t)
-          if (!apply && m.chit[a * 5 + t]) { apply = true; phi = m.cphi[a * 5 + t]; }
-        if (apply) status |= ASVRL_S_COLREGS;
-        int info = ASVRL_INFO_NORMAL;
-        if (dyn) {  // ENV:306-328
-          reward = m.rew[a];
-          if (apply) reward += k.colregs_penalty * phi;
-          if (m.ep[el] >= k.max_ep) { status |= ASVRL_S_DONE; info = ASVRL_INFO_TOO_LONG; }
-          else if (f & ASVRL_F_COLLISION) { reward += k.collision_penalty; status |= ASVRL_S_DONE; info = ASVRL_INFO_COLLISION; }
-          else if (f & ASVRL_F_REACH_GOAL) { reward += k.goal_reward; status |= ASVRL_S_DONE; info = ASVRL_INFO_REACH_GOAL; }
-        }
-        status |= (uint32_t)info << ASVRL_S_INFO_SHIFT;
-        if ((mode & ASVRL_M_AUTO_DEACTIVATE) && (f & (ASVRL_F_COLLISION | ASVRL_F_REACH_GOAL)))
-          f |= ASVRL_F_DEACTIVATED;  // TRAINER:168-170
-        if (f != f0) st.flags[g] = f;
-        m.fl[a] = f;
-      }
-      if (present) {
-        if (f & ASVRL_F_COLLISION) status |= ASVRL_S_COLLISION;
-        if (f & ASVRL_F_REACH_GOAL) status |= ASVRL_S_REACH_GOAL;
-      }
-      if (!second) {  // reward / status describe the transition, not the fresh episode
-      out.reward[g] = reward;
-      out.status[g] = status;
-      out.phi[g] = phi;
-      if (out.top_ids) {
-        const int kept = (int)(m.st_mask[a * 5] + m.st_mask[a * 5 + 1] + m.st_mask[a * 5 + 2] +
-                               m.st_mask[a * 5 + 3] + m.st_mask[a * 5 + 4]);
-        for (int t = kept; t < 5; ++t) out.top_ids[g * 5 + t] = -1;
-      }
-      if (out.detected)
-        out.detected[g] = (unsigned long long)m.det_lo[a] | ((unsigned long long)m.det_hi[a] << 32);
-      }
-    }
-  }
-  __syncthreads();
-
-  // ---- phase D: coalesced observation rows + env-level reductions ----
-  {
-    const int n_env = min(EPB, E - e0);
-    const size_t a0 = (size_t)e0 * RP;
-    const int n_asv = n_env * RP;
+  K1_TR(13, 0);
+  // ---- phases C2 and D side by side.  Warp 0, one lane per ego: self observation, reward / done / info, then its
+  // own rows and the env-level reductions (ballots over the env's lanes); warps 1..3 meanwhile store the object rows
+  // and masks, complete since the barrier above.  No CTA barrier between the two any more. ----
+  const int n_env = min(EPB, E - e0);
+  const size_t a0 = (size_t)e0 * RP;
+  const int n_asv = n_env * RP;
+  int my_end = 0;
+  if (tid >= 32) {
+    const int t = tid - 32;
+    constexpr int T3 = TPB - 32;
     if (!env_mask && !second) {
-      for (int i = tid; i < n_asv * 25; i += TPB) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
-      for (int i = tid; i < n_asv * 7; i += TPB) out.obs_self[a0 * 7 + i] = m.st_self[i];
-      for (int i = tid; i < n_asv * 5; i += TPB) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
+      for (int i = t; i < n_asv * 25; i += T3) out.obs_objects[a0 * 25 + i] = m.st_obj[i];
+      for (int i = t; i < n_asv * 5; i += T3) out.obs_mask[a0 * 5 + i] = m.st_mask[i];
     } else {
       for (int el = 0; el < n_env; ++el) {
         if (!m.ok[el]) continue;
         const size_t b0 = a0 + (size_t)el * RP;
         const int l0 = el * RP;
-        for (int i = tid; i < RP * 25; i += TPB) out.obs_objects[b0 * 25 + i] = m.st_obj[l0 * 25 + i];
-        for (int i = tid; i < RP * 7; i += TPB) out.obs_self[b0 * 7 + i] = m.st_self[l0 * 7 + i];
-        for (int i = tid; i < RP * 5; i += TPB) out.obs_mask[b0 * 5 + i] = m.st_mask[l0 * 5 + i];
+        for (int i = t; i < RP * 25; i += T3) out.obs_objects[b0 * 25 + i] = m.st_obj[l0 * 25 + i];
+        for (int i = t; i < RP * 5; i += T3) out.obs_mask[b0 * 5 + i] = m.st_mask[l0 * 5 + i];
       }
     }
-    int my_end = 0;
-    if (tid < n_env && m.ok[tid] && !second) {
-      const int el = tid, e = e0 + el, nr = m.nr[el];
-      bool all_deact = true, any_coll = false, all_goal = true;
-      for (int r = 0; r < nr; ++r) {
-        const uint32_t f = m.fl[el * RP + r];
-        all_deact &= (f & ASVRL_F_DEACTIVATED) != 0;   // ENV:178-184
-        any_coll |= (f & ASVRL_F_COLLISION) != 0;      // ENV:194-200
-        all_goal &= (f & ASVRL_F_REACH_GOAL) != 0;     // ENV:186-192
+  } else {
+    uint32_t f_fin = 0;
+    bool pres = false;
+    if (tid < A) {
+      const int a = tid, el = a / RP, r = a - el * RP;
+      const int e = e0 + el;
+      const size_t g = (size_t)e * RP + r;
+      float* ss = m.st_self + a * 7;
+#pragma unroll
+      for (int q = 0; q < 7; ++q) ss[q] = 0.0f;
+      if (m.ok[el]) {
+        const bool present = r < m.nr[el];
+        const uint32_t f0 = m.fl0[a];
+        uint32_t f = m.fl[a], status = 0;
+        float reward = 0.0f, phi = 0.0f;
+        if (!present) {
+          status = (uint32_t)ASVRL_INFO_ABSENT << ASVRL_S_INFO_SHIFT;
+          f = 0;
+        } else if (f0 & ASVRL_F_DEACTIVATED) {  // WAMV:437-438, ENV:295-304
+          const int info = (f0 & ASVRL_F_COLLISION) ? ASVRL_INFO_DEACT_COLLISION
+                           : (f0 & ASVRL_F_REACH_GOAL) ? ASVRL_INFO_DEACT_GOAL : ASVRL_INFO_DEACT_INVALID;
+          status = ASVRL_S_DONE | ASVRL_S_WAS_DEACTIVATED | ((uint32_t)info << ASVRL_S_INFO_SHIFT);
+        } else {
+          const float c = m.c[a], s = m.s[a];
+          const float dgx = (float)((double)m.gx[a] - m.px[a]), dgy = (float)((double)m.gy[a] - m.py[a]);
+          ss[0] = c * dgx + s * dgy; ss[1] = -s * dgx + c * dgy;  // WAMV:443-453
+          ss[2] = c * m.vx[a] + s * m.vy[a]; ss[3] = -s * m.vx[a] + c * m.vy[a];
+          ss[4] = m.vz[a]; ss[5] = m.Tl[a]; ss[6] = m.Tr[a];
+          bool apply = false;  // first hit in sorted order wins, WAMV:517-521
+#pragma unroll
+          for (int t = 0; t < ASVRL_MAX_OBJ; ++t)
+            if (!apply && m.chit[a * 5 + t]) { apply = true; phi = m.cphi[a * 5 + t]; }
+          if (apply) status |= ASVRL_S_COLREGS;
+          int info = ASVRL_INFO_NORMAL;
+          if (dyn) {  // ENV:306-328
+            reward = m.rew[a];
+            if (apply) reward += k.colregs_penalty * phi;
+            if (m.ep[el] >= k.max_ep) { status |= ASVRL_S_DONE; info = ASVRL_INFO_TOO_LONG; }
+            else if (f & ASVRL_F_COLLISION) { reward += k.collision_penalty; status |= ASVRL_S_DONE; info = ASVRL_INFO_COLLISION; }
+            else if (f & ASVRL_F_REACH_GOAL) { reward += k.goal_reward; status |= ASVRL_S_DONE; info = ASVRL_INFO_REACH_GOAL; }
+          }
+          status |= (uint32_t)info << ASVRL_S_INFO_SHIFT;
+          if ((mode & ASVRL_M_AUTO_DEACTIVATE) && (f & (ASVRL_F_COLLISION | ASVRL_F_REACH_GOAL)))
+            f |= ASVRL_F_DEACTIVATED;  // TRAINER:168-170
+          if (f != f0) st.flags[g] = f;
+          m.fl[a] = f;
+        }
+        f_fin = f; pres = present;
+        if (present) {
+          if (f & ASVRL_F_COLLISION) status |= ASVRL_S_COLLISION;
+          if (f & ASVRL_F_REACH_GOAL) status |= ASVRL_S_REACH_GOAL;
+        }
+        if (!second) {  // reward / status describe the transition, not the fresh episode
+        out.reward[g] = reward;
+        out.status[g] = status;
+        out.phi[g] = phi;
+        if (out.top_ids) {
+          const int kept = (int)(m.st_mask[a * 5] + m.st_mask[a * 5 + 1] + m.st_mask[a * 5 + 2] +
+                                 m.st_mask[a * 5 + 3] + m.st_mask[a * 5 + 4]);
+          for (int t = kept; t < 5; ++t) out.top_ids[g * 5 + t] = -1;
+        }
+        if (out.detected)
+          out.detected[g] = (unsigned long long)m.det_lo[a] | ((unsigned long long)m.det_hi[a] << 32);
+        }
       }
-      const uint32_t es = (all_deact ? 1u : 0u) | (m.ep[el] >= k.max_ep ? 2u : 0u) |
-                          (any_coll ? 4u : 0u) | (all_goal ? 8u : 0u);
-      out.env_status[e] = es;
-      if (out.ended) out.ended[e] = (es & 3u) ? 1 : 0;
-      if (dyn) st.ep_steps[e] = m.ep[el] + 1;  // ENV:330
-      my_end = (es & 3u) ? 1 : 0;
     }
+    __syncwarp();
+    K1_TR(14, 0);
+    if (!env_mask && !second) {
+      for (int i = tid; i < n_asv * 7; i += 32) out.obs_self[a0 * 7 + i] = m.st_self[i];
+    } else {
+      for (int el = 0; el < n_env; ++el) {
+        if (!m.ok[el]) continue;
+        const size_t b0 = a0 + (size_t)el * RP;
+        for (int i = tid; i < RP * 7; i += 32) out.obs_self[b0 * 7 + i] = m.st_self[el * RP * 7 + i];
+      }
+    }
+    // env-level reductions over the env's present robots (ENV:178-200)
+    const unsigned b_pr = __ballot_sync(0xffffffffu, pres);
+    const unsigned b_de = __ballot_sync(0xffffffffu, pres && (f_fin & ASVRL_F_DEACTIVATED));
+    const unsigned b_co = __ballot_sync(0xffffffffu, pres && (f_fin & ASVRL_F_COLLISION));
+    const unsigned b_go = __ballot_sync(0xffffffffu, pres && (f_fin & ASVRL_F_REACH_GOAL));
+    if (tid < A) {
+      const int el = tid / RP, r = tid - el * RP;
+      if (r == 0) {
+        if (el < n_env && m.ok[el] && !second) {
+          const int e = e0 + el;
+          const unsigned msk = (RP >= 32 ? 0xffffffffu : ((1u << RP) - 1u)) << (el * RP);
+          const unsigned P = b_pr & msk;
+          const bool all_deact = (b_de & msk) == P, any_coll = (b_co & msk) != 0u, all_goal = (b_go & msk) == P;
+          const uint32_t es = (all_deact ? 1u : 0u) | (m.ep[el] >= k.max_ep ? 2u : 0u) |
+                              (any_coll ? 4u : 0u) | (all_goal ? 8u : 0u);
+          out.env_status[e] = es;
+          if (out.ended) out.ended[e] = (es & 3u) ? 1 : 0;
+          if (dyn) st.ep_steps[e] = m.ep[el] + 1;  // ENV:330
+          my_end = (es & 3u) ? 1 : 0;
+        }
+        if (FUSED && !second) m.ended[el] = my_end;
+      }
+    }
+  }
+  {
+    K1_TR(15, 0);
     if (!FUSED || second) return;
     // ---- fused tail: episodes that just ended (TRAINER:172, 240-245) ----
-    if (tid < EPB) m.ended[tid] = my_end;
     if (!__syncthreads_or(my_end)) return;
     if (fa.term_self) {  // the terminal observation rows stay available to the replay push
       for (int el = 0; el < n_env; ++el) {
@@ -898,7 +942,7 @@ env_step_kernel(const __grid_constant__ EnvConsts k, const __grid_constant__ Sme
       // thread el decides for its env: 2 = the stage holds its next episode, 1 = generate it here.
       // Episode number and tag were read in phase 0; only a stage that was not ready then is
       // looked at again (the side stream may have published it meanwhile).
-      if (tid < EPB && my_end) {
+      if (tid < EPB && m.ended[tid]) {
         const int e = e0 + tid;
         const int ep = m.pre_ep[tid];
         m.epn[tid] = ep;
@@ -1189,3 +1233,10 @@ extern "C" int asvrl_env_noise(const asvrl_env_params* params, uint64_t seed, ui
                                                            env_offset, noise_out);
   return check_launch("asvrl_env_noise");
 }
+
+#ifdef K1_TRACE
+extern "C" __attribute__((visibility("default"))) int asvrl_env_step_trace(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  return (int)cudaMemcpyFromSymbol(out, asvrl::k1_trace_buf, sizeof(unsigned long long) * 32);
+}
+#endif

@@ -115,59 +115,80 @@ replay_scatter_kernel(float* __restrict__ rows, int64_t capacity, const float* _
     use_term[tid] = (ended && i < n_asv) ? ended[i / rpe] : 0;
   }
   __syncthreads();
-  // 18 items per thread in batches of 6.  The source of an item is chosen by selects (no branch around a load) and
-  // every item is ONE 4-byte load, so a thread has its 6 requests in flight before the first store; the two object
-  // counts of a row (5 mask loads and a sum each) are left to a second, equally flat pass.  With a branch chain
-  // around the loads the divergent paths of a warp serialised: 18 dependent round trips per thread.
-  constexpr int ITEMS = PUSH_G * ASVRL_ROW, PER_T = (ITEMS + SCAT_T - 1) / SCAT_T, BATCH = 6;
-  static_assert(PER_T % BATCH == 0, "batching of the scatter loop");
-  for (int k0 = 0; k0 < PER_T; k0 += BATCH) {
-    uint32_t v[BATCH];
-    int kind[BATCH];      // 0 float, 1 int32 action id, 2 status word -> done, 3 constant zero
-    long long dst[BATCH];
+  // One warp per row, eight rows per warp.  A row is 70 floats = three passes of a warp (q = lane, lane + 32,
+  // lane + 64), so what a lane copies is fixed for the whole launch: its three source arrays, offsets and per-ASV
+  // strides are computed ONCE, and a row costs each lane three loads and three stores at `base + i * stride`.  (A flat
+  // (row, element) loop spent ~150 instructions per element on index arithmetic and source selection: 21.5 M warp
+  // instructions for 4.6 M elements, issue bound at 35 us; profiles/r02_scatter_*.)  The two object counts of a row
+  // (RB:60-67: the mask is "first n ones") are summed from five lanes' mask loads of the third pass by shuffles.
+  static_assert(ASVRL_ROW_OBJ == 7 && ASVRL_ROW_NOBJ == 32 && ASVRL_ROW_ACT == 33 && ASVRL_ROW_REW == 35 &&
+                ASVRL_ROW_NSELF == 36 && ASVRL_ROW_NOBJ_F == 43 && ASVRL_ROW_NNOBJ == 68 && ASVRL_ROW_DONE == 69 &&
+                ASVRL_ROW == 70 && PUSH_G == 64 && SCAT_T == 256, "lane roles of the scatter kernel");
+  const int lane = tid & 31, w = tid >> 5;
+  const bool have_term = ended != nullptr;
+  // pass 0, q = lane: own state (7) | objects 0 .. 24
+  const float* s0 = lane < 7 ? obs_self + lane : obs_obj + (lane - 7);
+  const int st0 = lane < 7 ? 7 : 25;
+  // pass 1, q = 32 + lane: [count] | action (2) | reward | next own state (7) | next objects 0 .. 20
+  const float *s1a, *s1b;
+  int st1, kind1 = 0;   // 0 float, 1 int32 action id, 3 constant zero, 4 the object count
+  if (lane == 0) { s1a = s1b = reward; st1 = 1; kind1 = 4; }
+  else if (lane < 3) {
+    s1a = s1b = discrete ? (const float*)actions : (const float*)actions + (lane - 1);
+    st1 = discrete ? 1 : 2;
+    kind1 = discrete ? (lane == 1 ? 1 : 3) : 0;
+  } else if (lane == 3) { s1a = s1b = reward; st1 = 1; }
+  else if (lane < 11) { s1a = nself + (lane - 4); s1b = have_term ? tself + (lane - 4) : s1a; st1 = 7; }
+  else { s1a = nobj + (lane - 11); s1b = have_term ? tobj + (lane - 11) : s1a; st1 = 25; }
+  // pass 2, q = 64 + lane: next objects 21 .. 24 | [next count] | done; lanes 8 .. 12 / 16 .. 20 fetch the two masks
+  const float *s2a = reward, *s2b = reward;
+  int st2 = 1, kind2 = 5;   // 0 float, 2 status word -> done, 4 next object count, 5 nothing to store
+  if (lane < 4) { s2a = nobj + (21 + lane); s2b = have_term ? tobj + (21 + lane) : s2a; st2 = 25; kind2 = 0; }
+  else if (lane == 4) { kind2 = 4; }
+  else if (lane == 5) { s2a = s2b = (const float*)status; kind2 = 2; }
+  else if (lane >= 8 && lane < 13) { s2a = s2b = obs_mask + (lane - 8); st2 = 5; }
+  else if (lane >= 16 && lane < 21) { s2a = nmask + (lane - 16); s2b = have_term ? tmask + (lane - 16) : s2a; st2 = 5; }
+  constexpr int RPW = PUSH_G / (SCAT_T / 32), RB = 4;   // rows per warp, rows whose loads are in flight together
 #pragma unroll
-    for (int k = 0; k < BATCH; ++k) {
-      const int e = tid + (k0 + k) * SCAT_T;
-      const int r = min(e / ASVRL_ROW, PUSH_G - 1), q = e - (e / ASVRL_ROW) * ASVRL_ROW;
-      const long long d = e < ITEMS ? dst_row[r] : -1;
-      const bool skip = q == ASVRL_ROW_NOBJ || q == ASVRL_ROW_NNOBJ;
-      dst[k] = (d >= 0 && !skip) ? d * ASVRL_ROW + q : -1;
-      const size_t i = (size_t)(i0 + r);
-      const bool t = use_term[r];  // the env ended: its next state is the kept terminal observation
-      const float* src = obs_self + i * 7 + q;
-      int kd = 0;
-      if (q >= ASVRL_ROW_OBJ) src = obs_obj + i * 25 + (q - ASVRL_ROW_OBJ);
-      if (q >= ASVRL_ROW_ACT) {
-        src = discrete ? (const float*)actions + i : (const float*)actions + i * 2 + (q - ASVRL_ROW_ACT);
-        kd = discrete ? (q == ASVRL_ROW_ACT ? 1 : 3) : 0;
+  for (int r0 = 0; r0 < RPW; r0 += RB) {
+    uint32_t v0[RB], v1[RB], v2[RB];
+    long long d[RB];
+#pragma unroll
+    for (int j = 0; j < RB; ++j) {
+      const int r = w * RPW + r0 + j;
+      d[j] = dst_row[r];
+      v0[j] = v1[j] = v2[j] = 0u;
+      if (d[j] >= 0) {   // warp-uniform
+        const size_t i = (size_t)(i0 + r);
+        const bool t = use_term[r];  // the env ended: its next state is the kept terminal observation
+        v0[j] = __ldg(reinterpret_cast<const uint32_t*>(s0 + i * st0));
+        v1[j] = __ldg(reinterpret_cast<const uint32_t*>((t ? s1b : s1a) + i * st1));
+        v2[j] = __ldg(reinterpret_cast<const uint32_t*>((t ? s2b : s2a) + i * st2));
       }
-      if (q >= ASVRL_ROW_REW) { src = reward + i; kd = 0; }
-      if (q >= ASVRL_ROW_NSELF) src = (t ? tself : nself) + i * 7 + (q - ASVRL_ROW_NSELF);
-      if (q >= ASVRL_ROW_NOBJ_F) src = (t ? tobj : nobj) + i * 25 + (q - ASVRL_ROW_NOBJ_F);
-      if (q >= ASVRL_ROW_DONE) { src = (const float*)status + i; kd = 2; }
-      kind[k] = kd;
-      v[k] = 0u;
-      if (dst[k] >= 0) v[k] = __ldg(reinterpret_cast<const uint32_t*>(src));
     }
 #pragma unroll
-    for (int k = 0; k < BATCH; ++k) {
-      if (dst[k] < 0) continue;
-      float f = __uint_as_float(v[k]);
-      if (kind[k] == 1) f = (float)(int32_t)v[k];
-      else if (kind[k] == 2) f = (v[k] & ASVRL_S_DONE) ? 1.0f : 0.0f;
-      else if (kind[k] == 3) f = 0.0f;
-      rows[dst[k]] = f;
-    }
-  }
-  // the object counts (RB:60-67: the mask is "first n ones"): one thread per (row, state / next state)
-  if (tid < 2 * PUSH_G) {
-    const int r = tid >> 1, nx = tid & 1;
-    const long long d = dst_row[r];
-    if (d >= 0) {
-      const size_t i = (size_t)(i0 + r);
-      const float* mk = (nx ? (use_term[r] ? tmask : nmask) : obs_mask) + i * 5;
-      const float m0 = __ldg(mk), m1 = __ldg(mk + 1), m2 = __ldg(mk + 2), m3 = __ldg(mk + 3), m4 = __ldg(mk + 4);
-      rows[d * ASVRL_ROW + (nx ? ASVRL_ROW_NNOBJ : ASVRL_ROW_NOBJ)] = m0 + m1 + m2 + m3 + m4;
+    for (int j = 0; j < RB; ++j) {
+      if (d[j] < 0) continue;
+      float* row = rows + d[j] * ASVRL_ROW;
+      const float mk = __uint_as_float(v2[j]);
+      float n_obj = __shfl_sync(0xffffffffu, mk, 8), n_nobj = __shfl_sync(0xffffffffu, mk, 16);
+#pragma unroll
+      for (int q = 1; q < 5; ++q) {
+        n_obj += __shfl_sync(0xffffffffu, mk, 8 + q);
+        n_nobj += __shfl_sync(0xffffffffu, mk, 16 + q);
+      }
+      row[lane] = __uint_as_float(v0[j]);
+      float f1 = __uint_as_float(v1[j]);
+      if (kind1 == 1) f1 = (float)(int32_t)v1[j];
+      else if (kind1 == 3) f1 = 0.0f;
+      else if (kind1 == 4) f1 = n_obj;
+      row[32 + lane] = f1;
+      if (kind2 != 5) {
+        float f2 = mk;
+        if (kind2 == 2) f2 = (v2[j] & ASVRL_S_DONE) ? 1.0f : 0.0f;
+        else if (kind2 == 4) f2 = n_nobj;
+        row[64 + lane] = f2;
+      }
     }
   }
 }

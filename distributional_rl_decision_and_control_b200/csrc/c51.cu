@@ -16,54 +16,95 @@ namespace asvrl {
 constexpr int C51_MAX_A = 32;
 constexpr int C51_WARPS = 8;
 
-// One warp per row.  The row's A x atoms advantages (+ bias) are staged in shared memory with coalesced loads (the
-// atom count is not a multiple of 32), then lanes run over the atoms: conflict-free column sums for the mean over
-// the actions, and per action a softmax expectation = three interleaved warp reductions.
+// One warp per row, rows double-buffered in shared memory.  The row's A x atoms advantages (5.1 KB at 25 x 51, not a
+// multiple of 16 bytes, so 4-byte cp.async) are fetched for the NEXT row while the current one is reduced: with
+// register-staged loads a warp had 8 requests in flight and then waited (ncu: 84 % of the stall samples on the staging
+// loop, 13 % of the DRAM rate, 320 us for 65 536 rows); now every warp keeps a whole row in flight.
+// Per row: lanes first run over the ATOMS (conflict-free column sums: v - mean_a(a) per atom, left in shared memory),
+// then over the ACTIONS: lane a walks its own action's atoms sequentially (bank (a * atoms + j) mod 32 is conflict-free
+// for odd atom counts) — a softmax expectation without cross-lane reductions; the argmax is the only warp reduction.
+__device__ __forceinline__ void c51_cp4(float* dst_smem, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src));
+}
+
 __global__ void __launch_bounds__(C51_WARPS * 32)
 c51_greedy_kernel(const float* __restrict__ zv, const float* __restrict__ za, const float* __restrict__ bv,
                   const float* __restrict__ ba, const float* __restrict__ support, int rows, int A, int atoms,
                   int* __restrict__ action, float* __restrict__ q_out) {
-  extern __shared__ float c51_sm[];   // [warp][A * atoms]
+  extern __shared__ float c51_sm[];   // [warp][2][A * atoms] rows | [warp][64] v - mean | [A * atoms] ba | [64] support
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warps = gridDim.x * C51_WARPS;
   const int n = A * atoms;
-  float* sm = c51_sm + (size_t)w * n;
+  float* buf = c51_sm + (size_t)w * 2 * n;
+  float* vm = c51_sm + (size_t)C51_WARPS * 2 * n + w * 64;
+  float* bas = c51_sm + (size_t)C51_WARPS * (2 * n + 64);
+  float* sup = bas + n;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) bas[e] = ba[e];
+  if (threadIdx.x < 64) sup[threadIdx.x] = threadIdx.x < atoms ? support[threadIdx.x] : 0.0f;
+  __syncthreads();
   const int j0 = lane, j1 = lane + 32;
   const bool h0 = j0 < atoms, h1 = j1 < atoms;
-  const float s0 = h0 ? support[j0] : 0.0f, s1 = h1 ? support[j1] : 0.0f;
   const float bv0 = h0 ? bv[j0] : 0.0f, bv1 = h1 ? bv[j1] : 0.0f;
+  float bs0 = 0.0f, bs1 = 0.0f;   // column sums of the advantage bias
+  for (int a = 0; a < A; ++a) {
+    if (h0) bs0 += bas[a * atoms + j0];
+    if (h1) bs1 += bas[a * atoms + j1];
+  }
   const float inv = 1.0f / (float)A;
-  for (int m = blockIdx.x * C51_WARPS + w; m < rows; m += warps) {
+  auto fetch = [&](int m, float* dst) {
     const float* ar = za + (size_t)m * n;
-    for (int e = lane; e < n; e += 32) sm[e] = ar[e] + __ldg(ba + e);
+    for (int e = lane; e < n; e += 32) c51_cp4(dst + e, ar + e);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int m = blockIdx.x * C51_WARPS + w, x = 0;
+  if (m < rows) fetch(m, buf);
+  for (; m < rows; m += warps, x ^= 1) {
+    float* sm = buf + (size_t)x * n;
+    const float z0 = h0 ? __ldg(zv + (size_t)m * atoms + j0) : 0.0f, z1 = h1 ? __ldg(zv + (size_t)m * atoms + j1) : 0.0f;
+    if (m + warps < rows) {
+      fetch(m + warps, buf + (size_t)(x ^ 1) * n);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
     __syncwarp();
     float m0 = 0.0f, m1 = 0.0f;
+#pragma unroll 5
     for (int a = 0; a < A; ++a) {
       if (h0) m0 += sm[a * atoms + j0];
       if (h1) m1 += sm[a * atoms + j1];
     }
-    const float v0 = (h0 ? zv[(size_t)m * atoms + j0] + bv0 : 0.0f) - m0 * inv;   // v - mean_a(a), per atom
-    const float v1 = (h1 ? zv[(size_t)m * atoms + j1] + bv1 : 0.0f) - m1 * inv;
-    float best = -INFINITY;
-    int best_a = 0;
-    for (int a = 0; a < A; ++a) {
-      const float q0 = h0 ? v0 + sm[a * atoms + j0] : -INFINITY, q1 = h1 ? v1 + sm[a * atoms + j1] : -INFINITY;
-      float mx = fmaxf(q0, q1);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      const float e0 = h0 ? __expf(q0 - mx) : 0.0f, e1 = h1 ? __expf(q1 - mx) : 0.0f;
-      float den = e0 + e1, num = e0 * s0 + e1 * s1;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        den += __shfl_xor_sync(0xffffffffu, den, o);
-        num += __shfl_xor_sync(0xffffffffu, num, o);
+    if (h0) vm[j0] = (z0 + bv0) - (m0 + bs0) * inv;   // v - mean_a(a + ba), per atom
+    if (h1) vm[j1] = (z1 + bv1) - (m1 + bs1) * inv;
+    __syncwarp();
+    float ev = -INFINITY;
+    if (lane < A) {
+      const float* mine = sm + lane * atoms;
+      const float* mb = bas + lane * atoms;
+      float mx = -INFINITY;
+#pragma unroll 4
+      for (int j = 0; j < atoms; ++j) mx = fmaxf(mx, vm[j] + (mine[j] + mb[j]));
+      float den = 0.0f, num = 0.0f;
+#pragma unroll 4
+      for (int j = 0; j < atoms; ++j) {
+        const float e = __expf(vm[j] + (mine[j] + mb[j]) - mx);
+        den += e;
+        num = fmaf(e, sup[j], num);
       }
-      const float ev = num / den;   // sum_j softmax(q)_j support_j
-      if (q_out && lane == 0) q_out[(size_t)m * A + a] = ev;
-      if (ev > best) { best = ev; best_a = a; }   // first maximum, as torch.argmax
+      ev = num / den;   // sum_j softmax(q)_j support_j
+      if (q_out) q_out[(size_t)m * A + lane] = ev;
+    }
+    // first maximum over the actions, as torch.argmax
+    float best = ev;
+    int best_a = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, best_a, o);
+      if (ob > best || (ob == best && oa < best_a)) { best = ob; best_a = oa; }
     }
     if (lane == 0) action[m] = best_a;
-    __syncwarp();
+    __syncwarp();   // every lane is done with this buffer before the next iteration's fetch overwrites it
   }
 }
 
@@ -78,11 +119,13 @@ extern "C" int asvrl_c51_greedy(const float* zv, const float* za, const float* b
     return fail(ASVRL_E_BADARG, "asvrl_c51_greedy: rows >= 1, 1 <= actions <= %d, 1 <= atoms <= 64 (rows=%ld A=%d atoms=%d)",
                 C51_MAX_A, rows, n_actions, atoms);
   long grid = (rows + C51_WARPS - 1) / C51_WARPS;
-  if (grid > 148 * 4) grid = 148 * 4;
-  const size_t smem = (size_t)C51_WARPS * n_actions * atoms * sizeof(float);   // <= 64 KB
+  if (grid > 148 * 2) grid = 148 * 2;   // two 88 KB CTAs per SM
+  const size_t n = (size_t)n_actions * atoms;
+  const size_t smem = ((size_t)C51_WARPS * (2 * n + 64) + n + 64) * sizeof(float);   // 88 KB at 25 x 51
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(c51_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 32 * 64 * 4);
+    cudaError_t e = cudaFuncSetAttribute(c51_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (C51_WARPS * (2 * C51_MAX_A * 64 + 64) + C51_MAX_A * 64 + 64) * 4);
     if (e != cudaSuccess) return fail((int)e, "asvrl_c51_greedy: %s", cudaGetErrorString(e));
     attr = true;
   }

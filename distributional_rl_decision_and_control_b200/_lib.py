@@ -75,7 +75,7 @@ _SIGNATURES = {
     "asvrl_atan_head_fwd": (C.c_int, [f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, vp]),
     "asvrl_atan_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
     "asvrl_neg_mean": (C.c_int, [f32p, C.c_long, f32p, vp]),
-    "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, i32p, f32p, vp]),
+    "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_long, i32p, f32p, vp]),
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),
     "asvrl_critic_forward": (C.c_int, [f32p, C.c_uint64, C.c_uint64, u64p, C.c_float] + [f32p] * 10
@@ -530,14 +530,18 @@ def neg_mean(x):
     return out
 
 
-def c51_greedy(zv, za, bv, ba, support, n_actions, want_q=False):
-    """Greedy actions (rows,) int32 [and expected values (rows, A)] of a dueling C51 head from its bias-free products."""
-    rows, atoms = zv.shape
+def c51_greedy(zv, za, bv, ba, support, n_actions, want_q=False, actions_per_block=0):
+    """Greedy actions (rows,) int32 [and expected values (rows, A)] of a dueling C51 head from its bias-free products.
+    zv (rows, >= atoms); za (rows, A * atoms), or with ``actions_per_block`` (n_blocks, rows, ld) blocks."""
+    rows = zv.shape[0]
+    atoms = support.numel()
     f = torch.float32
     action = torch.empty((rows,), dtype=torch.int32, device=zv.device)
     q = torch.empty((rows, n_actions), dtype=f, device=zv.device) if want_q else None
+    za_ld, za_bs = (za.shape[2], za.stride(0)) if actions_per_block else (0, 0)
     rc = lib().asvrl_c51_greedy(ptr(zv, f), ptr(za, f), ptr(bv, f), ptr(ba, f), ptr(support, f), rows, int(n_actions),
-                                int(atoms), ptr(action, torch.int32), ptr(q, f), stream_ptr())
+                                int(atoms), int(zv.shape[1]), int(actions_per_block), int(za_ld), int(za_bs),
+                                ptr(action, torch.int32), ptr(q, f), stream_ptr())
     check(rc, "asvrl_c51_greedy")
     return (action, q) if want_q else action
 

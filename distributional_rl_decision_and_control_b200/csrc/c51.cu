@@ -30,7 +30,7 @@ __device__ __forceinline__ void c51_cp4(float* dst_smem, const float* src) {
 __global__ void __launch_bounds__(C51_WARPS * 32)
 c51_greedy_kernel(const float* __restrict__ zv, const float* __restrict__ za, const float* __restrict__ bv,
                   const float* __restrict__ ba, const float* __restrict__ support, int rows, int A, int atoms,
-                  int* __restrict__ action, float* __restrict__ q_out) {
+                  int zv_ld, int apb, int za_ld, long za_bs, int* __restrict__ action, float* __restrict__ q_out) {
   extern __shared__ float c51_sm[];   // [warp][2][A * atoms] rows | [warp][64] v - mean | [A * atoms] ba | [64] support
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int warps = gridDim.x * C51_WARPS;
@@ -51,16 +51,22 @@ c51_greedy_kernel(const float* __restrict__ zv, const float* __restrict__ za, co
     if (h1) bs1 += bas[a * atoms + j1];
   }
   const float inv = 1.0f / (float)A;
+  // za is stored in blocks of `apb` actions: block k holds [rows][za_ld] with the actions' atoms packed at the front
+  // (one block of all A actions with za_ld = A * atoms is the dense layout)
   auto fetch = [&](int m, float* dst) {
-    const float* ar = za + (size_t)m * n;
-    for (int e = lane; e < n; e += 32) c51_cp4(dst + e, ar + e);
+    for (int a0 = 0, k = 0; a0 < A; a0 += apb, ++k) {
+      const int cnt = min(apb, A - a0) * atoms;
+      const float* ar = za + (size_t)k * za_bs + (size_t)m * za_ld;
+      float* d = dst + a0 * atoms;
+      for (int e = lane; e < cnt; e += 32) c51_cp4(d + e, ar + e);
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   int m = blockIdx.x * C51_WARPS + w, x = 0;
   if (m < rows) fetch(m, buf);
   for (; m < rows; m += warps, x ^= 1) {
     float* sm = buf + (size_t)x * n;
-    const float z0 = h0 ? __ldg(zv + (size_t)m * atoms + j0) : 0.0f, z1 = h1 ? __ldg(zv + (size_t)m * atoms + j1) : 0.0f;
+    const float z0 = h0 ? __ldg(zv + (size_t)m * zv_ld + j0) : 0.0f, z1 = h1 ? __ldg(zv + (size_t)m * zv_ld + j1) : 0.0f;
     if (m + warps < rows) {
       fetch(m + warps, buf + (size_t)(x ^ 1) * n);
       asm volatile("cp.async.wait_group 1;" ::: "memory");
@@ -113,11 +119,18 @@ c51_greedy_kernel(const float* __restrict__ zv, const float* __restrict__ za, co
 using namespace asvrl;
 
 extern "C" int asvrl_c51_greedy(const float* zv, const float* za, const float* bv, const float* ba, const float* support,
-                                long rows, int n_actions, int atoms, int* action, float* q_out, void* stream) {
+                                long rows, int n_actions, int atoms, int zv_ld, int za_actions_per_block, int za_ld,
+                                long za_block_stride, int* action, float* q_out, void* stream) {
   if (!zv || !za || !bv || !ba || !support || !action) return fail(ASVRL_E_BADARG, "asvrl_c51_greedy: null pointer");
   if (rows < 1 || rows > 0x7FFFFFFFL || n_actions < 1 || n_actions > C51_MAX_A || atoms < 1 || atoms > 64)
     return fail(ASVRL_E_BADARG, "asvrl_c51_greedy: rows >= 1, 1 <= actions <= %d, 1 <= atoms <= 64 (rows=%ld A=%d atoms=%d)",
                 C51_MAX_A, rows, n_actions, atoms);
+  if (zv_ld == 0) zv_ld = atoms;
+  if (za_actions_per_block == 0) { za_actions_per_block = n_actions; za_ld = n_actions * atoms; za_block_stride = 0; }
+  if (zv_ld < atoms || za_actions_per_block < 1 || za_actions_per_block > n_actions ||
+      za_ld < za_actions_per_block * atoms || za_block_stride < 0)
+    return fail(ASVRL_E_BADARG, "asvrl_c51_greedy: zv_ld %d, %d actions per block, za_ld %d, block stride %ld", zv_ld,
+                za_actions_per_block, za_ld, za_block_stride);
   long grid = (rows + C51_WARPS - 1) / C51_WARPS;
   if (grid > 148 * 2) grid = 148 * 2;   // two 88 KB CTAs per SM
   const size_t n = (size_t)n_actions * atoms;
@@ -130,6 +143,7 @@ extern "C" int asvrl_c51_greedy(const float* zv, const float* za, const float* b
     attr = true;
   }
   c51_greedy_kernel<<<(int)grid, C51_WARPS * 32, smem, (cudaStream_t)stream>>>(zv, za, bv, ba, support, (int)rows,
-                                                                               n_actions, atoms, action, q_out);
+                                                                               n_actions, atoms, zv_ld, za_actions_per_block,
+                                                                               za_ld, za_block_stride, action, q_out);
   return check_launch("asvrl_c51_greedy");
 }

@@ -97,8 +97,9 @@ class Rainbow_Policy(_ObservationTower):
             return layer.weight_mu, layer.bias_mu
 
         feats = self._features(x)
-        if feats.is_cuda and feats.shape[0] >= 4096 and feats.shape[1] % 32 == 0 and self.hidden_dimension % 32 == 0 \
-                and self.hidden_dimension <= 256:
+        umma = feats.is_cuda and feats.shape[0] >= 4096 and feats.shape[1] % 32 == 0 and self.hidden_dimension % 32 == 0 \
+            and self.hidden_dimension <= 256
+        if umma:
             # the four hidden noisy layers on the tensor cores at fp32 accuracy (K8: three TF32 products, bias and ReLU
             # in the epilogue): 55 / 35 us per layer at 65 536 rows against ~145 / ~105 us for cuBLAS SIMT sgemm + its
             # separate bias epilogue + ReLU
@@ -112,7 +113,27 @@ class Rainbow_Policy(_ObservationTower):
             a = F.relu(self.hidden_layer_a_2(F.relu(self.hidden_layer_a(feats))))
         wv, bv = eff(self.output_layer_v)
         wa, ba = eff(self.output_layer_a)
-        return _lib.c51_greedy(v @ wv.t(), a @ wa.t(), bv.contiguous(), ba.contiguous(), support, self.action_size, want_q)
+        atoms, A, H = self.atoms, self.action_size, self.hidden_dimension
+        if umma and atoms <= 256:
+            # the two output layers on the tensor cores too (K8 takes <= 256 outputs, a multiple of 16, per call): the
+            # value layer padded to 64 outputs, the advantage layer `apb` actions at a time (5 x 51 = 255 -> 256) into
+            # blocks that asvrl_c51_greedy reads in place; zero weight rows fill the padding
+            vp = -(-atoms // 16) * 16
+            wvp = torch.zeros((vp, H), dtype=wv.dtype, device=wv.device)
+            wvp[:atoms] = wv
+            zv = _lib.linear_tf32x3(v, wvp)
+            apb = min(A, 256 // atoms)
+            nb = -(-A // apb)
+            ld = -(-(apb * atoms) // 16) * 16
+            wap = torch.zeros((nb, ld, H), dtype=wa.dtype, device=wa.device)
+            for k in range(nb):
+                rows_k = min(apb, A - k * apb) * atoms
+                wap[k, :rows_k] = wa[k * apb * atoms:k * apb * atoms + rows_k]
+            za = torch.empty((nb, v.shape[0], ld), dtype=torch.float32, device=v.device)
+            for k in range(nb):
+                _lib.linear_tf32x3(a, wap[k], out=za[k])
+            return _lib.c51_greedy(zv, za, bv.contiguous(), ba.contiguous(), support, A, want_q, actions_per_block=apb)
+        return _lib.c51_greedy(v @ wv.t(), a @ wa.t(), bv.contiguous(), ba.contiguous(), support, A, want_q)
 
     def reset_noise(self):
         for name, module in self.named_children():

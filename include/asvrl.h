@@ -610,10 +610,13 @@ ASVRL_API int asvrl_critic_backward_status(int* status_out);
  * ASVs in one launch: q = v + a - mean_a(a), softmax over the atoms, expectation over the support, first argmax.
  *   zv [rows][atoms], za [rows][n_actions][atoms]: the two output layers' products WITHOUT bias; bv [atoms],
  *   ba [n_actions][atoms]: their (noisy) biases; support [atoms]; action [rows] int32; q_out [rows][n_actions]
- *   nullable (the expected values).  n_actions <= 32, atoms <= 64. */
+ *   nullable (the expected values).  n_actions <= 32, atoms <= 64.  Layout of the products (0 = dense): zv_ld = row
+ *   stride of zv in floats (>= atoms); za may be stored in blocks of `za_actions_per_block` actions — block k is
+ *   [rows][za_ld] with its actions' atoms packed at the front, blocks `za_block_stride` floats apart — which is what
+ *   asvrl_linear_tf32x3 produces when the advantage layer is evaluated 5 actions (255 -> 256 outputs) at a time. */
 ASVRL_API int asvrl_c51_greedy(const float* zv, const float* za, const float* bv, const float* ba, const float* support,
-                               long rows, int n_actions, int atoms, int* action, float* q_out /* nullable */,
-                               void* stream);
+                               long rows, int n_actions, int atoms, int zv_ld, int za_actions_per_block, int za_ld,
+                               long za_block_stride, int* action, float* q_out /* nullable */, void* stream);
 
 /* The two narrow layers of the AC-IQN update, each direction in one launch (batch = the learner's sampled states; the
  * backward kernels keep per-CTA partial column sums in `partials` — asvrl_narrow_bwd_partials(dim) floats — and the last

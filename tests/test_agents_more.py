@@ -172,15 +172,16 @@ def test_rainbow_memory_n_step_window():
 
 
 @pytest.mark.gpu
-def test_rainbow_greedy_actions_match_probability_path():
+@pytest.mark.parametrize("M", [3000, 5000])
+def test_rainbow_greedy_actions_match_probability_path(M):
     """asvrl_c51_greedy (dueling combination, softmax, expectation, argmax in one pass) against the module's own
-    probability tensor in float64 (Rainbow:127-135, AGENT:235-246), noisy layers in training mode."""
+    probability tensor in float64 (Rainbow:127-135, AGENT:235-246), noisy layers in training mode.  M = 5000 takes the
+    tensor-core path (the six noisy layers through K8, the advantage products in 5-action blocks)."""
     import copy
     dev = "cuda:0"
     pol = build("Rainbow", 7, dev)
     pol.train()
     g = torch.Generator(device=dev).manual_seed(3)
-    M = 3000
     x = (torch.randn((M, 7), device=dev, generator=g) * 5, torch.randn((M, 5, 5), device=dev, generator=g) * 3,
          (torch.rand((M, 5), device=dev, generator=g) < 0.6).float())
     x = (x[0], x[1] * x[2][..., None], x[2])

@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 import torch
 
+from distributional_rl_decision_and_control_b200 import _lib
 from distributional_rl_decision_and_control_b200.policy.DDPG_model import DDPG_Policy
 from distributional_rl_decision_and_control_b200.policy.DQN_model import DQN_Policy
 from distributional_rl_decision_and_control_b200.policy.Rainbow_model import Rainbow_Policy
@@ -196,3 +197,31 @@ def test_rainbow_greedy_actions_match_probability_path(M):
     clear = (top2[:, 0] - top2[:, 1]) > 1e-4
     assert torch.equal(act.long()[clear], want.argmax(1)[clear])
     assert int(clear.sum()) > M // 2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["DQN", "SAC"])
+def test_collection_hidden_layers_on_tensor_cores_match_float64(kind):
+    """A no-grad forward over >= 4 096 rows takes K8 for the two hidden layers (`_ObservationTower._hidden`); the
+    action values / the actor's mean stay within 1e-5 of the float64 module."""
+    import copy
+    dev = "cuda:0"
+    pol = build(kind, 11, dev)
+    net = pol if kind == "DQN" else pol.actor
+    g = torch.Generator(device=dev).manual_seed(5)
+    M = 5000
+    x = (torch.randn((M, 7), device=dev, generator=g) * 5, torch.randn((M, 5, 5), device=dev, generator=g) * 3,
+         (torch.rand((M, 5), device=dev, generator=g) < 0.6).float())
+    x = (x[0], x[1] * x[2][..., None], x[2])
+    ref = copy.deepcopy(net).double()
+    ref.fused_tower = False
+    x64 = tuple(t.double() for t in x)
+    with torch.no_grad():
+        if kind == "DQN":
+            got, want = net(x), ref(x64)
+        else:
+            z = torch.zeros((M, 2), device=dev)
+            got, want = net(x, noise=z)[0], ref(x64, noise=z.double())[0]
+    torch.cuda.synchronize()
+    _lib.linear_tf32x3_status()
+    assert float((got.double() - want).abs().max()) <= 1e-5 * float(want.abs().max()) + 1e-6

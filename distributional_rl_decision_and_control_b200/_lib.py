@@ -69,6 +69,7 @@ _SIGNATURES = {
                                        C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_long, C.c_int,
                                        vp, f32p, vp]),
     "asvrl_policy_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
+    "asvrl_policy_hidden": (C.c_int, [f32p] * 11 + [C.c_long, C.c_int, vp, f32p, vp]),
     "asvrl_action_encoder_fwd": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_int, f32p, vp]),
     "asvrl_action_encoder_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
     "asvrl_narrow_bwd_partials": (C.c_long, [C.c_int]),
@@ -464,6 +465,22 @@ def policy_forward(self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1
         int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), ptr(counter_dev, torch.int64), M, int(bool(repack)),
         ws.data_ptr(), ptr(out, f), stream_ptr())
     check(rc, "asvrl_policy_forward")
+    return out
+
+
+def policy_hidden(self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2):
+    """(rows, 128): tower -> 256 -> 128 -> 128 (ReLU) of the policy family in K9's persistent tcgen05 launch."""
+    M = self_obs.shape[0]
+    dev = self_obs.device
+    ws = _POLICY_WS.get(dev)
+    if ws is None:
+        ws = _POLICY_WS[dev] = torch.empty((lib().asvrl_policy_forward_workspace(),), dtype=torch.uint8, device=dev)
+    out = torch.empty((M, 128), dtype=torch.float32, device=dev)
+    f = torch.float32
+    rc = lib().asvrl_policy_hidden(
+        ptr(self_obs, f), ptr(objects, f), ptr(mask, f), ptr(w_self, f), ptr(b_self, f), ptr(w_obj, f), ptr(b_obj, f),
+        ptr(w1, f), ptr(b1, f), ptr(w2, f), ptr(b2, f), M, 1, ws.data_ptr(), ptr(out, f), stream_ptr())
+    check(rc, "asvrl_policy_hidden")
     return out
 
 

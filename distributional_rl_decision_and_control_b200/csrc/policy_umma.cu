@@ -88,6 +88,7 @@ struct PolicyArgs {
   const float *w_self, *b_self, *w_obj, *b_obj;                 // encoders (nn.Linear layout)
   const float *b1, *b2, *w_out, *b_out;                         // hidden biases, head [2][128], [2]
   const unsigned char* image;                                   // packed W1 | W2 chunks (policy_pack_kernel)
+  float* hidden;                                                  // non-null: store the second hidden layer [rows][128], no head
   float atan_scale, eps;
   const float* eps_dev;
   float lo0, hi0, lo1, hi1;
@@ -203,7 +204,7 @@ policy_forward_kernel(const PolicyArgs a) {
     float* b2 = reinterpret_cast<float*>(base + PF_OFF_B2);
     float* wo = reinterpret_cast<float*>(base + PF_OFF_WOUT);
     for (int i = tid; i < PF_H; i += PF_THREADS) { b1[i] = a.b1[i]; b2[i] = a.b2[i]; }
-    for (int i = tid; i < 2 * PF_H; i += PF_THREADS) wo[i] = a.w_out[i];
+    for (int i = tid; i < 2 * PF_H; i += PF_THREADS) wo[i] = a.w_out ? a.w_out[i] : 0.0f;
   }
   um_tc_before();
   __syncthreads();
@@ -373,6 +374,8 @@ policy_forward_kernel(const PolicyArgs a) {
       if (!ok) break;
       um_tc_after();
       float a0 = 0.0f, a1 = 0.0f;
+      const long m = (long)tile * PF_ROWS + r;
+      float4* hrow = (a.hidden && m < a.rows) ? reinterpret_cast<float4*>(a.hidden + (size_t)m * PF_H) : nullptr;
 #pragma unroll
       for (int c0 = 0; c0 < PF_H; c0 += 32) {
         uint32_t v[32];
@@ -385,6 +388,7 @@ policy_forward_kernel(const PolicyArgs a) {
           const float h1 = fmaxf(fmaf(__uint_as_float(v[4 * g + 1]), PF_WUNSCALE, bb.y), 0.0f);
           const float h2 = fmaxf(fmaf(__uint_as_float(v[4 * g + 2]), PF_WUNSCALE, bb.z), 0.0f);
           const float h3 = fmaxf(fmaf(__uint_as_float(v[4 * g + 3]), PF_WUNSCALE, bb.w), 0.0f);
+          if (hrow) hrow[c0 / 4 + g] = make_float4(h0, h1, h2, h3);   // the policy family's shared trunk output
           a0 = fmaf(h0, u0.x, a0); a0 = fmaf(h1, u0.y, a0); a0 = fmaf(h2, u0.z, a0); a0 = fmaf(h3, u0.w, a0);
           a1 = fmaf(h0, u1.x, a1); a1 = fmaf(h1, u1.y, a1); a1 = fmaf(h2, u1.z, a1); a1 = fmaf(h3, u1.w, a1);
         }
@@ -392,8 +396,7 @@ policy_forward_kernel(const PolicyArgs a) {
       um_tc_before();
       __syncwarp();
       if (lane == 0) um_mbar_arrive(bar_d2_empty(b));
-      const long m = (long)tile * PF_ROWS + r;
-      if (m < a.rows) {
+      if (m < a.rows && !a.hidden) {
         float2 act = make_float2(a.atan_scale * atanf(a0 + bo0), a.atan_scale * atanf(a1 + bo1));
         if (eps > 0.0f) {
           const uint4 u = philox_at(a.seed, STREAM_EXPLORE, counter, (int64_t)m, 0u, 0u, 0u);
@@ -480,16 +483,15 @@ using namespace asvrl;
 
 extern "C" long asvrl_policy_forward_workspace(void) { return (long)PF_IMAGE_B; }
 
-extern "C" int asvrl_policy_forward(const float* self_obs, const float* objects, const float* mask,
-                                    const float* w_self, const float* b_self, const float* w_obj, const float* b_obj,
-                                    const float* w1, const float* b1, const float* w2, const float* b2,
-                                    const float* w_out, const float* b_out, float atan_scale, const float* eps_dev,
-                                    float eps, const float* action_lo, const float* action_hi, uint64_t seed,
-                                    uint64_t counter, const uint64_t* counter_dev, long rows, int repack,
-                                    void* workspace, float* actions, void* stream) {
-  if (!self_obs || !objects || !mask || !w_self || !b_self || !w_obj || !b_obj || !w1 || !b1 || !w2 || !b2 || !w_out ||
-      !b_out || !action_lo || !action_hi || !workspace || !actions)
-    return fail(ASVRL_E_BADARG, "asvrl_policy_forward: null pointer");
+static int pf_run(const char* what, const float* self_obs, const float* objects, const float* mask,
+                  const float* w_self, const float* b_self, const float* w_obj, const float* b_obj,
+                  const float* w1, const float* b1, const float* w2, const float* b2,
+                  const float* w_out, const float* b_out, float atan_scale, const float* eps_dev,
+                  float eps, const float* action_lo, const float* action_hi, uint64_t seed,
+                  uint64_t counter, const uint64_t* counter_dev, long rows, int repack,
+                  void* workspace, float* actions, float* hidden, void* stream) {
+  if (!self_obs || !objects || !mask || !w_self || !b_self || !w_obj || !b_obj || !w1 || !b1 || !w2 || !b2 || !workspace)
+    return fail(ASVRL_E_BADARG, "%s: null pointer", what);
   if (rows < 1 || rows > 0x7FFFFFFFL - PF_ROWS) return fail(ASVRL_E_BADARG, "asvrl_policy_forward: rows %ld", rows);
   if ((uintptr_t)workspace & 127) return fail(ASVRL_E_BADARG, "asvrl_policy_forward: workspace must be 128-byte aligned");
   static int n_sm = 0;
@@ -521,9 +523,38 @@ extern "C" int asvrl_policy_forward(const float* self_obs, const float* objects,
   if (cudaGetSymbolAddress((void**)&status, pf_status_word) != cudaSuccess) status = nullptr;
   a.status = status;
   a.actions = actions;
+  a.hidden = hidden;
   const int grid = a.n_tiles < n_sm ? a.n_tiles : n_sm;
   policy_forward_kernel<<<grid, PF_THREADS, PF_SMEM_B, st>>>(a);
-  return check_launch("asvrl_policy_forward");
+  return check_launch(what);
+}
+
+extern "C" int asvrl_policy_forward(const float* self_obs, const float* objects, const float* mask,
+                                    const float* w_self, const float* b_self, const float* w_obj, const float* b_obj,
+                                    const float* w1, const float* b1, const float* w2, const float* b2,
+                                    const float* w_out, const float* b_out, float atan_scale, const float* eps_dev,
+                                    float eps, const float* action_lo, const float* action_hi, uint64_t seed,
+                                    uint64_t counter, const uint64_t* counter_dev, long rows, int repack,
+                                    void* workspace, float* actions, void* stream) {
+  if (!w_out || !b_out || !action_lo || !action_hi || !actions)
+    return fail(ASVRL_E_BADARG, "asvrl_policy_forward: null pointer");
+  return pf_run("asvrl_policy_forward", self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2, w_out, b_out,
+                atan_scale, eps_dev, eps, action_lo, action_hi, seed, counter, counter_dev, rows, repack, workspace, actions,
+                nullptr, stream);
+}
+
+// The trunk alone: tower -> 256 -> 128 -> 128 (ReLU) of the same launch, the second hidden layer written out.  Every
+// policy of the family (DQN:50-77, SAC's actor, Rainbow's two noisy streams) shares this front end and differs in the
+// layers after it.
+extern "C" int asvrl_policy_hidden(const float* self_obs, const float* objects, const float* mask, const float* w_self,
+                                   const float* b_self, const float* w_obj, const float* b_obj, const float* w1,
+                                   const float* b1, const float* w2, const float* b2, long rows, int repack,
+                                   void* workspace, float* hidden, void* stream) {
+  if (!hidden || ((uintptr_t)hidden & 15)) return fail(ASVRL_E_BADARG, "asvrl_policy_hidden: hidden must be non-null, 16-byte aligned");
+  static const float zero2[2] = {0.0f, 0.0f};
+  // the head's operands are read into shared memory by every CTA: point them at the (valid) second-layer bias
+  return pf_run("asvrl_policy_hidden", self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2, nullptr, b2,
+                1.0f, nullptr, 0.0f, zero2, zero2, 0, 0, nullptr, rows, repack, workspace, nullptr, hidden, stream);
 }
 
 // synchronous read of K9's device status word (0 = every bounded wait completed)

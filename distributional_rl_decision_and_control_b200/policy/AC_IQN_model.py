@@ -79,20 +79,42 @@ class _ObservationTower(nn.Module):
             others = (enc * (mask >= 0.5).unsqueeze(-1).to(enc.dtype)).reshape(B, width)
         return torch.cat((own, others), dim=1)
 
-    def _hidden(self, feats, l1, l2):
-        """relu(l2(relu(l1(feats)))) — the two hidden layers every policy of the family has.  A no-grad pass over
-        >= 4 096 rows in fp32 mode (collection for the whole env batch) runs them on the tensor cores at fp32 accuracy
-        (K8: three TF32 products per step, bias + ReLU in the epilogue; 55 + 40 us at 65 536 rows against ~250 us for
-        two cuBLAS SIMT sgemm + bias + ReLU); everything else takes the module path."""
-        if (not torch.is_grad_enabled() and feats.is_cuda and feats.dtype == torch.float32 and feats.shape[0] >= 4096
-                and l1.weight.dtype == torch.float32 and not torch.backends.cuda.matmul.allow_tf32
-                and l1.in_features % 32 == 0 and l2.in_features % 32 == 0
-                and l1.out_features % 16 == 0 and l1.out_features <= 256
-                and l2.out_features % 16 == 0 and l2.out_features <= 256 and self.fused_tower):
+    def _trunk(self, x, l1, l2, eff=None):
+        """relu(l2(relu(l1(features(x))))).  A no-grad pass over >= 4 096 rows of the reference's fixed shape
+        (7 / 5 x 5 observations, 56 + 5 x 40 features, 256 -> 128 -> 128) in fp32 mode runs tower and both layers in ONE
+        persistent tcgen05 launch (K9's trunk, asvrl_policy_hidden: 42 us at 65 536 rows; K6 + 2 x K8 took 145 us).
+        ``eff(layer)`` -> (weight, bias) overrides the parameters (Rainbow's noisy layers)."""
+        w1, b1 = eff(l1) if eff else (l1.weight, l1.bias)
+        w2, b2 = eff(l2) if eff else (l2.weight, l2.bias)
+        so, ob, mk = x
+        if (not torch.is_grad_enabled() and self.fused_tower and ob is not None and so.is_cuda and so.dtype == torch.float32
+                and so.shape[0] >= 4096 and w1.dtype == torch.float32 and not torch.backends.cuda.matmul.allow_tf32
+                and (self.self_dimension, self.object_dimension, self.max_object_num) == (7, 5, 5)
+                and (self.self_feature_dimension, self.object_feature_dimension) == (56, 40)
+                and tuple(w1.shape) == (128, 256) and tuple(w2.shape) == (128, 128)):
             from .. import _lib
-            h = _lib.linear_tf32x3(feats.contiguous(), l1.weight, l1.bias, relu=True)
-            return _lib.linear_tf32x3(h, l2.weight, l2.bias, relu=True)
-        return F.relu(l2(F.relu(l1(feats))))
+            se, oe = self.self_encoder[0], self.object_encoder[0]
+            M = so.shape[0]
+            return _lib.policy_hidden(so.contiguous(), ob.reshape(M, 5, 5).contiguous(), mk.to(torch.float32).contiguous(),
+                                      se.weight, se.bias, oe.weight, oe.bias, w1.contiguous(), b1.contiguous(),
+                                      w2.contiguous(), b2.contiguous())
+        return self._hidden_w(self._features(x), w1, b1, w2, b2)
+
+    def _hidden(self, feats, l1, l2):
+        return self._hidden_w(feats, l1.weight, l1.bias, l2.weight, l2.bias)
+
+    def _hidden_w(self, feats, w1, b1, w2, b2):
+        """relu(relu(feats w1^T + b1) w2^T + b2).  A no-grad pass over >= 4 096 rows in fp32 mode whose shape K9's trunk
+        does not cover runs the two layers through K8 (three TF32 products per step, bias + ReLU in the epilogue; 55 +
+        40 us at 65 536 rows against ~250 us for two cuBLAS SIMT sgemm + bias + ReLU); everything else is F.linear."""
+        if (not torch.is_grad_enabled() and feats.is_cuda and feats.dtype == torch.float32 and feats.shape[0] >= 4096
+                and w1.dtype == torch.float32 and not torch.backends.cuda.matmul.allow_tf32 and self.fused_tower
+                and w1.shape[1] % 32 == 0 and w2.shape[1] % 32 == 0
+                and w1.shape[0] % 16 == 0 and w1.shape[0] <= 256 and w2.shape[0] % 16 == 0 and w2.shape[0] <= 256):
+            from .. import _lib
+            h = _lib.linear_tf32x3(feats.contiguous(), w1.contiguous(), b1.contiguous(), relu=True)
+            return _lib.linear_tf32x3(h, w2.contiguous(), b2.contiguous(), relu=True)
+        return F.relu(F.linear(F.relu(F.linear(feats, w1, b1)), w2, b2))
 
     def _dump(self, directory, stem):
         torch.save(self.state_dict(), os.path.join(directory, f"{stem}_network_params.pth"))

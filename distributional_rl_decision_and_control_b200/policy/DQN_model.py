@@ -26,7 +26,7 @@ class DQN_Policy(_ObservationTower):
         self.output_layer = nn.Linear(hidden_dimension, action_size)
 
     def forward(self, x):
-        h = self._hidden(self._features(x), self.hidden_layer, self.hidden_layer_2)  # DQN:50-77
+        h = self._trunk(x, self.hidden_layer, self.hidden_layer_2)  # DQN:50-77
         return self.output_layer(h)
 
     def get_constructor_parameters(self):

@@ -96,21 +96,12 @@ class Rainbow_Policy(_ObservationTower):
                         layer.bias_mu + layer.bias_sigma * layer.bias_epsilon)
             return layer.weight_mu, layer.bias_mu
 
-        feats = self._features(x)
-        umma = feats.is_cuda and feats.shape[0] >= 4096 and feats.shape[1] % 32 == 0 and self.hidden_dimension % 32 == 0 \
-            and self.hidden_dimension <= 256
-        if umma:
-            # the four hidden noisy layers on the tensor cores at fp32 accuracy (K8: three TF32 products, bias and ReLU
-            # in the epilogue): 55 / 35 us per layer at 65 536 rows against ~145 / ~105 us for cuBLAS SIMT sgemm + its
-            # separate bias epilogue + ReLU
-            def lin(h, layer):
-                w, b = eff(layer)
-                return _lib.linear_tf32x3(h.contiguous(), w.contiguous(), b.contiguous(), relu=True)
-            v = lin(lin(feats, self.hidden_layer_v), self.hidden_layer_v_2)
-            a = lin(lin(feats, self.hidden_layer_a), self.hidden_layer_a_2)
-        else:
-            v = F.relu(self.hidden_layer_v_2(F.relu(self.hidden_layer_v(feats))))
-            a = F.relu(self.hidden_layer_a_2(F.relu(self.hidden_layer_a(feats))))
+        # the two noisy streams' hidden layers: K9's trunk (tower + both layers in one launch) per stream on the
+        # reference's shape, K8 or F.linear otherwise (_ObservationTower._trunk)
+        v = self._trunk(x, self.hidden_layer_v, self.hidden_layer_v_2, eff)
+        a = self._trunk(x, self.hidden_layer_a, self.hidden_layer_a_2, eff)
+        umma = v.is_cuda and v.shape[0] >= 4096 and self.hidden_dimension % 32 == 0 and self.hidden_dimension <= 256 \
+            and v.dtype == torch.float32
         wv, bv = eff(self.output_layer_v)
         wa, ba = eff(self.output_layer_a)
         atoms, A, H = self.atoms, self.action_size, self.hidden_dimension

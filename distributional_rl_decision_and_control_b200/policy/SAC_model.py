@@ -44,7 +44,7 @@ class Actor(_ObservationTower):
     def forward(self, x, noise=None):
         """-> (actions (B, 2) in (-1, 1), log_prob (B, 1)).  ``noise`` injects the standard-normal
         draw of the reparameterisation (parity tests); default torch.randn_like."""
-        h = self._hidden(self._features(x), self.hidden_layer, self.hidden_layer_2)
+        h = self._trunk(x, self.hidden_layer, self.hidden_layer_2)
         mu = self.output_layer_mu(h)
         log_std = torch.clamp(self.output_layer_log_std(h), self.min_log_std, self.max_log_std)
         return self.compute_action(mu, log_std, noise)

@@ -534,6 +534,14 @@ ASVRL_API int asvrl_policy_forward(const float* self_obs, const float* objects, 
                                    const float* action_hi, uint64_t seed, uint64_t counter,
                                    const uint64_t* counter_dev /* nullable */, long rows, int repack,
                                    void* workspace, float* actions, void* stream);
+/* The trunk of asvrl_policy_forward alone — tower -> 256 -> 128 -> 128 (ReLU) — with the second hidden layer written to
+ * hidden [rows][128] (16-byte aligned) instead of the actor's head: the front end that DQN_model.py:50-77, SAC's actor
+ * (SAC_model.py Actor.forward) and Rainbow's two noisy streams (Rainbow_model.py:100-135) share; their own output
+ * layers follow.  Same kernel, workspace and status word as asvrl_policy_forward. */
+ASVRL_API int asvrl_policy_hidden(const float* self_obs, const float* objects, const float* mask, const float* w_self,
+                                  const float* b_self, const float* w_obj, const float* b_obj, const float* w1,
+                                  const float* b1, const float* w2, const float* b2, long rows, int repack,
+                                  void* workspace, float* hidden, void* stream);
 ASVRL_API int asvrl_policy_forward_status(int* status_out);
 
 /* K10 — the IQN critic's quantile trunk forward (ACIQN:410-426 calc_cos, ACIQN:453-480 the three dense layers with the

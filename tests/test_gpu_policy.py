@@ -145,3 +145,23 @@ def test_policy_forward_ddpg_actor():
     want = _actor64(ag.policy_local.actor)(tuple(t.double() for t in x))
     got = ag.act_batch(x, eps=0.0)
     assert (got.double() - want).abs().max().item() <= ATOL
+
+
+@pytest.mark.parametrize("M", [65536, 5000, 129, 1])
+def test_policy_hidden_matches_float64_trunk(M):
+    """asvrl_policy_hidden (K9's trunk with the second hidden layer written out: the front end DQN, SAC's actor and
+    Rainbow's streams share) against the float64 modules, on the reference's observation ranges."""
+    actor = _agent().policy_local.actor
+    x = _obs(M, 2000 + M)
+    se, oe = actor.self_encoder[0], actor.object_encoder[0]
+    l1, l2 = actor.hidden_layer, actor.hidden_layer_2
+    got = _lib.policy_hidden(x[0], x[1], x[2], se.weight, se.bias, oe.weight, oe.bias, l1.weight, l1.bias, l2.weight, l2.bias)
+    torch.cuda.synchronize()
+    _lib.policy_forward_status()
+    a64 = _actor64(actor)
+    f64 = a64._features(tuple(t.double() for t in x))
+    want = torch.relu(a64.hidden_layer_2(torch.relu(a64.hidden_layer(f64))))
+    assert got.shape == (M, 128)
+    scale = float(want.abs().max())
+    err = float((got.double() - want).abs().max())
+    assert err <= 1e-5 * scale + 1e-6, f"hidden layer: max abs err {err:.3e} at scale {scale:.3e}"

@@ -76,6 +76,8 @@ _SIGNATURES = {
     "asvrl_atan_head_fwd": (C.c_int, [f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, vp]),
     "asvrl_atan_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
     "asvrl_neg_mean": (C.c_int, [f32p, C.c_long, f32p, vp]),
+    "asvrl_rainbow_append": (C.c_int, [f32p, f32p, f32p, i32p, f32p, u32p, C.c_int, C.c_long, C.c_long, f32p, i32p, f32p, i32p,
+                                      f32p, i64p, i64p, i64p, u32p, vp]),
     "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_long, i32p, f32p, vp]),
     "asvrl_critic_forward_workspace": (C.c_long, []),
     "asvrl_critic_forward_chunk_bytes": (C.c_long, []),

@@ -64,6 +64,8 @@ class ReplayMemory:
         self.n_step_scaling = torch.tensor([self.discount ** i for i in range(self.n)],
                                            dtype=torch.float32, device=dev)
         self.transitions = _Transitions(self)
+        self.fused_append = True   # append_step through asvrl_rainbow_append (False: the torch statements, its reference)
+        self._append_scratch = torch.zeros((2,), dtype=torch.int32, device=dev)
         self._gen = torch.Generator(device=dev)
         self._gen.manual_seed(0x5EED)
 
@@ -108,6 +110,23 @@ class ReplayMemory:
         deactivated (or is padding) get priority 0 and cut every window that reaches them."""
         L = self.lanes
         o_self, o_obj, o_mask = obs
+        if self.fused_append and o_self.dtype == torch.float32 and out["status"].dtype in (torch.int32, torch.uint32):
+            # the whole append in one launch (asvrl_rainbow_append); the torch statements below are its specification
+            from .. import _lib
+            f, i32 = torch.float32, torch.int32
+            acts = actions.reshape(L)
+            acts = acts if acts.dtype == i32 else acts.to(i32)
+            _lib.check(_lib.lib().asvrl_rainbow_append(
+                _lib.ptr(o_self.reshape(L, W_SELF).contiguous(), f), _lib.ptr(o_obj.reshape(L, W_OBJ).contiguous(), f),
+                _lib.ptr(o_mask.reshape(L, 5).to(f).contiguous(), f), _lib.ptr(acts.contiguous(), i32),
+                _lib.ptr(out["reward"].reshape(L).contiguous(), f), out["status"].reshape(L).contiguous().data_ptr(),
+                L, self.slots, self.capacity, _lib.ptr(self.rows, f), _lib.ptr(self.tstep, i32), _lib.ptr(self.prio, f),
+                _lib.ptr(self.lane_t, i32), _lib.ptr(self.max_priority, f), _lib.ptr(self.head_dev, torch.int64),
+                _lib.ptr(self.filled_dev, torch.int64), _lib.ptr(self.count, torch.int64),
+                self._append_scratch.data_ptr(), _lib.stream_ptr()), "asvrl_rainbow_append")
+            self.head = (self.head + 1) % self.slots
+            self.filled = min(self.filled + 1, self.slots)
+            return
         status = out["status"].reshape(L)
         info = (status >> 8) & 15
         active = ((status & 8) == 0) & (info != 7)

@@ -626,6 +626,18 @@ ASVRL_API int asvrl_c51_greedy(const float* zv, const float* za, const float* bv
                                long rows, int n_actions, int atoms, int zv_ld, int za_actions_per_block, int za_ld,
                                long za_block_stride, int* action, float* q_out /* nullable */, void* stream);
 
+/* Rainbow's prioritised n-step memory: the batched append of one env step (the reference appends one transition per
+ * call, rfarl/rfarl/policy/replay_memory_rainbow.py:125-131; here one row per ASV, lane = env * R + robot) in ONE
+ * launch, graph-replay safe.  rows [slots][lanes][36] = [self 7 | objects 25 | n_obj | action | reward | nonterminal],
+ * tstep [slots][lanes] (the lane's episode clock, 0 cuts an n-step window), prio [slots * lanes] (max_priority for an
+ * active ASV, 0 otherwise), lane_t [lanes]; head / filled / count: the ring's device words (int64[1] each), advanced by
+ * the last CTA; scratch: two zero-initialised uint32 (left zero).  status: the env step's status words. */
+ASVRL_API int asvrl_rainbow_append(const float* obs_self, const float* obs_objects, const float* obs_mask,
+                                   const int* actions, const float* reward, const uint32_t* status, int lanes, long slots,
+                                   long capacity, float* rows, int* tstep, float* prio, int* lane_t,
+                                   const float* max_priority, long long* head, long long* filled, long long* count,
+                                   uint32_t* scratch, void* stream);
+
 /* The two narrow layers of the AC-IQN update, each direction in one launch (batch = the learner's sampled states; the
  * backward kernels keep per-CTA partial column sums in `partials` — asvrl_narrow_bwd_partials(dim) floats — and the last
  * CTA, by the zero-initialised ticket `counter` which it leaves at zero, adds them in a fixed order: deterministic).

@@ -225,3 +225,35 @@ def test_collection_hidden_layers_on_tensor_cores_match_float64(kind):
     torch.cuda.synchronize()
     _lib.linear_tf32x3_status()
     assert float((got.double() - want).abs().max()) <= 1e-5 * float(want.abs().max()) + 1e-6
+
+
+@pytest.mark.gpu
+def test_rainbow_batched_append_kernel_matches_torch_statements():
+    """asvrl_rainbow_append (one launch per batched step) against the torch statements it replaces, over a ring that
+    wraps, with deactivated / absent / finishing ASVs."""
+    from distributional_rl_decision_and_control_b200.utils.replay_memory_rainbow import ReplayMemory
+    dev = "cuda:0"
+    E, R = 37, 8
+    L = E * R
+    mems = [ReplayMemory(dev, 8 * L, lanes=L), ReplayMemory(dev, 8 * L, lanes=L)]
+    mems[1].fused_append = False
+    g = torch.Generator(device=dev).manual_seed(9)
+    for step in range(13):
+        obs = (torch.randn((E, R, 7), device=dev, generator=g), torch.randn((E, R, 5, 5), device=dev, generator=g),
+               (torch.rand((E, R, 5), device=dev, generator=g) < 0.5).float())
+        actions = torch.randint(0, 25, (E, R), device=dev, generator=g, dtype=torch.int32)
+        u = torch.rand((E, R), device=dev, generator=g)
+        status = torch.zeros((E, R), dtype=torch.int32, device=dev)
+        status |= (u < 0.15).int() * 1                    # done
+        status |= ((u > 0.8) & (u < 0.9)).int() * 8       # was deactivated
+        status |= (u >= 0.9).int() * (7 << 8)             # absent
+        status |= ((u >= 0.3) & (u < 0.8)).int() * (1 << 8)
+        out = {"status": status, "reward": torch.randn((E, R), device=dev, generator=g)}
+        for m in mems:
+            m.max_priority.fill_(1.0 + 0.25 * step)
+            m.append_step(obs, actions, out)
+    torch.cuda.synchronize()
+    a, b = mems
+    for name in ("rows", "tstep", "prio", "lane_t", "count", "head_dev", "filled_dev"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    assert a.head == b.head and a.filled == b.filled and int(a._append_scratch.abs().sum()) == 0

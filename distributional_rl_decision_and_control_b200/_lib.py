@@ -69,13 +69,16 @@ _SIGNATURES = {
                                        C.POINTER(C.c_float * 2), C.c_uint64, C.c_uint64, u64p, C.c_long, C.c_int,
                                        vp, f32p, vp]),
     "asvrl_policy_forward_status": (C.c_int, [C.POINTER(C.c_int)]),
-    "asvrl_policy_hidden": (C.c_int, [f32p] * 11 + [C.c_long, C.c_int, vp, f32p, vp]),
+    "asvrl_policy_hidden": (C.c_int, [f32p] * 11 + [C.c_long, C.c_int, vp, f32p, vp, vp]),
     "asvrl_action_encoder_fwd": (C.c_int, [f32p, f32p, f32p, C.c_int, C.c_int, f32p, vp]),
     "asvrl_action_encoder_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
     "asvrl_narrow_bwd_partials": (C.c_long, [C.c_int]),
     "asvrl_atan_head_fwd": (C.c_int, [f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, vp]),
     "asvrl_atan_head_bwd": (C.c_int, [f32p, f32p, f32p, f32p, C.c_float, C.c_int, C.c_int, f32p, f32p, f32p, f32p, u32p, vp]),
     "asvrl_neg_mean": (C.c_int, [f32p, C.c_long, f32p, vp]),
+    "asvrl_c51_head_workspace": (C.c_long, []),
+    "asvrl_c51_head": (C.c_int, [vp, f32p, C.c_int, f32p, f32p, f32p, f32p, C.c_long, C.c_int, C.c_int, vp, i32p, f32p, vp]),
+    "asvrl_c51_head_status": (C.c_int, [C.POINTER(C.c_int)]),
     "asvrl_rainbow_append": (C.c_int, [f32p, f32p, f32p, i32p, f32p, u32p, C.c_int, C.c_long, C.c_long, f32p, i32p, f32p, i32p,
                                       f32p, i64p, i64p, i64p, u32p, vp]),
     "asvrl_c51_greedy": (C.c_int, [f32p] * 5 + [C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_long, i32p, f32p, vp]),
@@ -470,18 +473,23 @@ def policy_forward(self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1
     return out
 
 
-def policy_hidden(self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2):
-    """(rows, 128): tower -> 256 -> 128 -> 128 (ReLU) of the policy family in K9's persistent tcgen05 launch."""
+def policy_hidden(self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2, image=False):
+    """(rows, 128): tower -> 256 -> 128 -> 128 (ReLU) of the policy family in K9's persistent tcgen05 launch.
+    ``image``: return the operand image (tiles, 2, 32768) uint8 instead (what c51_head reads)."""
     M = self_obs.shape[0]
     dev = self_obs.device
     ws = _POLICY_WS.get(dev)
     if ws is None:
         ws = _POLICY_WS[dev] = torch.empty((lib().asvrl_policy_forward_workspace(),), dtype=torch.uint8, device=dev)
-    out = torch.empty((M, 128), dtype=torch.float32, device=dev)
     f = torch.float32
+    if image:
+        out = torch.empty(((M + 127) // 128, 2, 32768), dtype=torch.uint8, device=dev)
+    else:
+        out = torch.empty((M, 128), dtype=f, device=dev)
     rc = lib().asvrl_policy_hidden(
         ptr(self_obs, f), ptr(objects, f), ptr(mask, f), ptr(w_self, f), ptr(b_self, f), ptr(w_obj, f), ptr(b_obj, f),
-        ptr(w1, f), ptr(b1, f), ptr(w2, f), ptr(b2, f), M, 1, ws.data_ptr(), ptr(out, f), stream_ptr())
+        ptr(w1, f), ptr(b1, f), ptr(w2, f), ptr(b2, f), M, 1, ws.data_ptr(), None if image else ptr(out, f),
+        out.data_ptr() if image else None, stream_ptr())
     check(rc, "asvrl_policy_hidden")
     return out
 
@@ -539,6 +547,36 @@ def atan_head_bwd(dact, y, h, w3, scale, want_dh=True):
     check(lib().asvrl_atan_head_bwd(ptr(dact, f), ptr(y, f), ptr(h, f), ptr(w3, f), float(scale), B, D, ptr(dh), ptr(dw3),
                                     ptr(db3), ptr(part), ptr(cnt), stream_ptr()), "asvrl_atan_head_bwd")
     return dh, dw3, db3
+
+
+_C51_HEAD_WS = {}
+
+
+def c51_head(h_img, zv, wa, ba, bv, support, rows, n_actions, want_q=False):
+    """K13: greedy actions (rows,) int32 [and expected values (rows, A)] of Rainbow's dueling C51 head from the advantage
+    stream's hidden-layer image (policy_hidden(..., image=True)) and the value stream's bias-free product zv (rows, >= 64)."""
+    dev = zv.device
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _C51_HEAD_WS.get(key)
+    if ws is None:
+        ws = _C51_HEAD_WS[key] = torch.empty((lib().asvrl_c51_head_workspace(),), dtype=torch.uint8, device=dev)
+    f = torch.float32
+    atoms = support.numel()
+    action = torch.empty((rows,), dtype=torch.int32, device=dev)
+    q = torch.empty((rows, n_actions), dtype=f, device=dev) if want_q else None
+    rc = lib().asvrl_c51_head(h_img.data_ptr(), ptr(zv, f), int(zv.shape[1]), ptr(wa, f), ptr(ba, f), ptr(bv, f),
+                              ptr(support, f), int(rows), int(n_actions), int(atoms), ws.data_ptr(),
+                              ptr(action, torch.int32), ptr(q, f), stream_ptr())
+    check(rc, "asvrl_c51_head")
+    return (action, q) if want_q else action
+
+
+def c51_head_status():
+    v = C.c_int(0)
+    check(lib().asvrl_c51_head_status(C.byref(v)), "asvrl_c51_head_status")
+    if v.value != 0:
+        raise RuntimeError(f"asvrl_c51_head: device pipeline fault, status {v.value}")
+    return 0
 
 
 def neg_mean(x):

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 SO = os.path.join(PKG, "libasvrl.so")
-SOURCES = ["api.cu", "env_step.cu", "env_reset.cu", "replay.cu", "iqn.cu", "trunk.cu", "tower.cu", "optim.cu", "linear_umma.cu", "policy_umma.cu", "critic_umma.cu", "wgrad_umma.cu", "critic_bwd_umma.cu", "c51.cu", "small_ops.cu"]
+SOURCES = ["api.cu", "env_step.cu", "env_reset.cu", "replay.cu", "iqn.cu", "trunk.cu", "tower.cu", "optim.cu", "linear_umma.cu", "policy_umma.cu", "critic_umma.cu", "wgrad_umma.cu", "critic_bwd_umma.cu", "c51.cu", "small_ops.cu", "c51_head_umma.cu"]
 HEADERS = ["common.cuh", "umma.cuh", "env_consts.cuh", "env_reset.cuh", os.path.join("..", "..", "include", "asvrl.h")]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "--shared", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",

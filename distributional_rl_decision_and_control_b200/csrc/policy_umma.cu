@@ -42,6 +42,7 @@ constexpr int PF_THREADS = 512;
 constexpr int PF_ROWS = 128;                       // rows per tile = UMMA M
 constexpr int PF_SD = 7, PF_OD = 5, PF_NOBJ = 5, PF_SF = 56, PF_OF = 40, PF_W = 256, PF_H = 128;
 constexpr int PF_TILE_B = PF_ROWS * 128;           // one operand tile: 128 rows x 128 B = 16 KB
+constexpr int PF_CHUNK_B = 2 * PF_TILE_B;          // hi | lo pieces of a 128 x 64 operand chunk
 constexpr int PF_STAGE_B = 4 * PF_TILE_B;          // A_hi | A_lo | W_hi | W_lo
 constexpr int PF_STAGES = 3;
 constexpr int PF_L1_CHUNKS = PF_W / 64, PF_L2_CHUNKS = PF_H / 64;
@@ -89,6 +90,7 @@ struct PolicyArgs {
   const float *b1, *b2, *w_out, *b_out;                         // hidden biases, head [2][128], [2]
   const unsigned char* image;                                   // packed W1 | W2 chunks (policy_pack_kernel)
   float* hidden;                                                  // non-null: store the second hidden layer [rows][128], no head
+  unsigned char* hidden_img;                                      // non-null: ... as a tcgen05 operand image [tile][2][32 KB] (hi | lo fp16, swizzled)
   float atan_scale, eps;
   const float* eps_dev;
   float lo0, hi0, lo1, hi1;
@@ -376,27 +378,44 @@ policy_forward_kernel(const PolicyArgs a) {
       float a0 = 0.0f, a1 = 0.0f;
       const long m = (long)tile * PF_ROWS + r;
       float4* hrow = (a.hidden && m < a.rows) ? reinterpret_cast<float4*>(a.hidden + (size_t)m * PF_H) : nullptr;
+      unsigned char* irow = a.hidden_img ? a.hidden_img + (size_t)tile * 2 * PF_CHUNK_B : nullptr;
+      const bool live_row = m < a.rows;
 #pragma unroll
       for (int c0 = 0; c0 < PF_H; c0 += 32) {
         uint32_t v[32];
         um_tmem_ld32(lane_addr + (uint32_t)(2 * PF_H + b * PF_H + c0), v);
         um_tmem_ld_wait();
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          const float4 bb = b2[c0 / 4 + g], u0 = w0[c0 / 4 + g], u1 = w1[c0 / 4 + g];
-          const float h0 = fmaxf(fmaf(__uint_as_float(v[4 * g + 0]), PF_WUNSCALE, bb.x), 0.0f);
-          const float h1 = fmaxf(fmaf(__uint_as_float(v[4 * g + 1]), PF_WUNSCALE, bb.y), 0.0f);
-          const float h2 = fmaxf(fmaf(__uint_as_float(v[4 * g + 2]), PF_WUNSCALE, bb.z), 0.0f);
-          const float h3 = fmaxf(fmaf(__uint_as_float(v[4 * g + 3]), PF_WUNSCALE, bb.w), 0.0f);
-          if (hrow) hrow[c0 / 4 + g] = make_float4(h0, h1, h2, h3);   // the policy family's shared trunk output
-          a0 = fmaf(h0, u0.x, a0); a0 = fmaf(h1, u0.y, a0); a0 = fmaf(h2, u0.z, a0); a0 = fmaf(h3, u0.w, a0);
-          a1 = fmaf(h0, u1.x, a1); a1 = fmaf(h1, u1.y, a1); a1 = fmaf(h2, u1.z, a1); a1 = fmaf(h3, u1.w, a1);
+        for (int gp = 0; gp < 4; ++gp) {
+          float h[8];
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            const int g = 2 * gp + half;
+            const float4 bb = b2[c0 / 4 + g], u0 = w0[c0 / 4 + g], u1 = w1[c0 / 4 + g];
+            const float h0 = fmaxf(fmaf(__uint_as_float(v[4 * g + 0]), PF_WUNSCALE, bb.x), 0.0f);
+            const float h1 = fmaxf(fmaf(__uint_as_float(v[4 * g + 1]), PF_WUNSCALE, bb.y), 0.0f);
+            const float h2 = fmaxf(fmaf(__uint_as_float(v[4 * g + 2]), PF_WUNSCALE, bb.z), 0.0f);
+            const float h3 = fmaxf(fmaf(__uint_as_float(v[4 * g + 3]), PF_WUNSCALE, bb.w), 0.0f);
+            if (hrow) hrow[c0 / 4 + g] = make_float4(h0, h1, h2, h3);   // the policy family's shared trunk output
+            h[4 * half + 0] = h0; h[4 * half + 1] = h1; h[4 * half + 2] = h2; h[4 * half + 3] = h3;
+            a0 = fmaf(h0, u0.x, a0); a0 = fmaf(h1, u0.y, a0); a0 = fmaf(h2, u0.z, a0); a0 = fmaf(h3, u0.w, a0);
+            a1 = fmaf(h0, u1.x, a1); a1 = fmaf(h1, u1.y, a1); a1 = fmaf(h2, u1.z, a1); a1 = fmaf(h3, u1.w, a1);
+          }
+          if (irow) {   // octet (c0 + 8 gp) / 8 of the row, two fp16 pieces, in the K-major 128-byte-swizzled tile layout
+            const int k0 = c0 + 8 * gp;
+            unsigned char* dst = irow + (size_t)(k0 >> 6) * PF_CHUNK_B + um_sw128_off(r, (k0 & 63) >> 3);
+            uint32_t hh[4], ll[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) um_split2(live_row ? h[2 * i] : 0.0f, live_row ? h[2 * i + 1] : 0.0f, hh[i], ll[i]);
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+            *reinterpret_cast<uint4*>(dst + PF_TILE_B) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+          }
         }
       }
       um_tc_before();
       __syncwarp();
       if (lane == 0) um_mbar_arrive(bar_d2_empty(b));
-      if (m < a.rows && !a.hidden) {
+      if (m < a.rows && !a.hidden && !a.hidden_img) {
         float2 act = make_float2(a.atan_scale * atanf(a0 + bo0), a.atan_scale * atanf(a1 + bo1));
         if (eps > 0.0f) {
           const uint4 u = philox_at(a.seed, STREAM_EXPLORE, counter, (int64_t)m, 0u, 0u, 0u);
@@ -489,7 +508,7 @@ static int pf_run(const char* what, const float* self_obs, const float* objects,
                   const float* w_out, const float* b_out, float atan_scale, const float* eps_dev,
                   float eps, const float* action_lo, const float* action_hi, uint64_t seed,
                   uint64_t counter, const uint64_t* counter_dev, long rows, int repack,
-                  void* workspace, float* actions, float* hidden, void* stream) {
+                  void* workspace, float* actions, float* hidden, void* hidden_img, void* stream) {
   if (!self_obs || !objects || !mask || !w_self || !b_self || !w_obj || !b_obj || !w1 || !b1 || !w2 || !b2 || !workspace)
     return fail(ASVRL_E_BADARG, "%s: null pointer", what);
   if (rows < 1 || rows > 0x7FFFFFFFL - PF_ROWS) return fail(ASVRL_E_BADARG, "asvrl_policy_forward: rows %ld", rows);
@@ -524,6 +543,7 @@ static int pf_run(const char* what, const float* self_obs, const float* objects,
   a.status = status;
   a.actions = actions;
   a.hidden = hidden;
+  a.hidden_img = (unsigned char*)hidden_img;
   const int grid = a.n_tiles < n_sm ? a.n_tiles : n_sm;
   policy_forward_kernel<<<grid, PF_THREADS, PF_SMEM_B, st>>>(a);
   return check_launch(what);
@@ -540,7 +560,7 @@ extern "C" int asvrl_policy_forward(const float* self_obs, const float* objects,
     return fail(ASVRL_E_BADARG, "asvrl_policy_forward: null pointer");
   return pf_run("asvrl_policy_forward", self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2, w_out, b_out,
                 atan_scale, eps_dev, eps, action_lo, action_hi, seed, counter, counter_dev, rows, repack, workspace, actions,
-                nullptr, stream);
+                nullptr, nullptr, stream);
 }
 
 // The trunk alone: tower -> 256 -> 128 -> 128 (ReLU) of the same launch, the second hidden layer written out.  Every
@@ -549,12 +569,13 @@ extern "C" int asvrl_policy_forward(const float* self_obs, const float* objects,
 extern "C" int asvrl_policy_hidden(const float* self_obs, const float* objects, const float* mask, const float* w_self,
                                    const float* b_self, const float* w_obj, const float* b_obj, const float* w1,
                                    const float* b1, const float* w2, const float* b2, long rows, int repack,
-                                   void* workspace, float* hidden, void* stream) {
-  if (!hidden || ((uintptr_t)hidden & 15)) return fail(ASVRL_E_BADARG, "asvrl_policy_hidden: hidden must be non-null, 16-byte aligned");
+                                   void* workspace, float* hidden, void* hidden_img, void* stream) {
+  if ((!hidden && !hidden_img) || ((uintptr_t)hidden & 15) || ((uintptr_t)hidden_img & 127))
+    return fail(ASVRL_E_BADARG, "asvrl_policy_hidden: hidden (16-byte aligned) and / or hidden_img (128-byte aligned)");
   static const float zero2[2] = {0.0f, 0.0f};
   // the head's operands are read into shared memory by every CTA: point them at the (valid) second-layer bias
   return pf_run("asvrl_policy_hidden", self_obs, objects, mask, w_self, b_self, w_obj, b_obj, w1, b1, w2, b2, nullptr, b2,
-                1.0f, nullptr, 0.0f, zero2, zero2, 0, 0, nullptr, rows, repack, workspace, nullptr, hidden, stream);
+                1.0f, nullptr, 0.0f, zero2, zero2, 0, 0, nullptr, rows, repack, workspace, nullptr, hidden, hidden_img, stream);
 }
 
 // synchronous read of K9's device status word (0 = every bounded wait completed)

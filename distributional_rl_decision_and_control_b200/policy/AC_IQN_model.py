@@ -79,11 +79,12 @@ class _ObservationTower(nn.Module):
             others = (enc * (mask >= 0.5).unsqueeze(-1).to(enc.dtype)).reshape(B, width)
         return torch.cat((own, others), dim=1)
 
-    def _trunk(self, x, l1, l2, eff=None):
+    def _trunk(self, x, l1, l2, eff=None, image=False):
         """relu(l2(relu(l1(features(x))))).  A no-grad pass over >= 4 096 rows of the reference's fixed shape
         (7 / 5 x 5 observations, 56 + 5 x 40 features, 256 -> 128 -> 128) in fp32 mode runs tower and both layers in ONE
         persistent tcgen05 launch (K9's trunk, asvrl_policy_hidden: 42 us at 65 536 rows; K6 + 2 x K8 took 145 us).
-        ``eff(layer)`` -> (weight, bias) overrides the parameters (Rainbow's noisy layers)."""
+        ``eff(layer)`` -> (weight, bias) overrides the parameters (Rainbow's noisy layers).  ``image``: return the
+        tcgen05 operand image of the result (for asvrl_c51_head), or None when the one-launch path does not apply."""
         w1, b1 = eff(l1) if eff else (l1.weight, l1.bias)
         w2, b2 = eff(l2) if eff else (l2.weight, l2.bias)
         so, ob, mk = x
@@ -97,7 +98,9 @@ class _ObservationTower(nn.Module):
             M = so.shape[0]
             return _lib.policy_hidden(so.contiguous(), ob.reshape(M, 5, 5).contiguous(), mk.to(torch.float32).contiguous(),
                                       se.weight, se.bias, oe.weight, oe.bias, w1.contiguous(), b1.contiguous(),
-                                      w2.contiguous(), b2.contiguous())
+                                      w2.contiguous(), b2.contiguous(), image=image)
+        if image:
+            return None
         return self._hidden_w(self._features(x), w1, b1, w2, b2)
 
     def _hidden(self, feats, l1, l2):

@@ -11,6 +11,9 @@ import torch.nn.functional as F
 
 from .AC_IQN_model import _ObservationTower, encoder
 
+# collection: the dueling C51 head through K13 (asvrl_c51_head); ASVRL_C51_HEAD=0 keeps K8 blocks + asvrl_c51_greedy
+C51_HEAD = os.environ.get("ASVRL_C51_HEAD", "1") != "0"
+
 
 class NoisyLinear(nn.Module):
     """y = (W_mu + W_sigma * eps_out eps_in^T) x + (b_mu + b_sigma * eps_out) while training,
@@ -98,13 +101,25 @@ class Rainbow_Policy(_ObservationTower):
 
         # the two noisy streams' hidden layers: K9's trunk (tower + both layers in one launch) per stream on the
         # reference's shape, K8 or F.linear otherwise (_ObservationTower._trunk)
+        atoms, A, H = self.atoms, self.action_size, self.hidden_dimension
         v = self._trunk(x, self.hidden_layer_v, self.hidden_layer_v_2, eff)
+        a_img = None
+        if C51_HEAD and atoms <= 64 and A <= 32 and H == 128:
+            # K13: the advantage layer, the dueling combination, softmax, expectation and argmax in one tcgen05 launch
+            # from the advantage stream's hidden layer as an operand image (None: K9's trunk does not cover this shape)
+            a_img = self._trunk(x, self.hidden_layer_a, self.hidden_layer_a_2, eff, image=True)
+        if a_img is not None:
+            wv, bv = eff(self.output_layer_v)
+            wa, ba = eff(self.output_layer_a)
+            wvp = torch.zeros((64, H), dtype=wv.dtype, device=wv.device)
+            wvp[:atoms] = wv
+            zv = _lib.linear_tf32x3(v.contiguous(), wvp)   # the value stream's product, 64-padded (K8)
+            return _lib.c51_head(a_img, zv, wa.contiguous(), ba.contiguous(), bv.contiguous(), support, v.shape[0], A, want_q)
         a = self._trunk(x, self.hidden_layer_a, self.hidden_layer_a_2, eff)
         umma = v.is_cuda and v.shape[0] >= 4096 and self.hidden_dimension % 32 == 0 and self.hidden_dimension <= 256 \
             and v.dtype == torch.float32
         wv, bv = eff(self.output_layer_v)
         wa, ba = eff(self.output_layer_a)
-        atoms, A, H = self.atoms, self.action_size, self.hidden_dimension
         if umma and atoms <= 256:
             # the two output layers on the tensor cores too (K8 takes <= 256 outputs, a multiple of 16, per call): the
             # value layer padded to 64 outputs, the advantage layer `apb` actions at a time (5 x 51 = 255 -> 256) into

@@ -537,11 +537,15 @@ ASVRL_API int asvrl_policy_forward(const float* self_obs, const float* objects, 
 /* The trunk of asvrl_policy_forward alone — tower -> 256 -> 128 -> 128 (ReLU) — with the second hidden layer written to
  * hidden [rows][128] (16-byte aligned) instead of the actor's head: the front end that DQN_model.py:50-77, SAC's actor
  * (SAC_model.py Actor.forward) and Rainbow's two noisy streams (Rainbow_model.py:100-135) share; their own output
- * layers follow.  Same kernel, workspace and status word as asvrl_policy_forward. */
+ * layers follow.  hidden_img (128-byte aligned, ceil(rows / 128) * 65536 bytes): the same values as a tcgen05 operand
+ * image — per 128-row tile two chunks (columns 0-63, 64-127) of fp16 hi | lo pieces in the 128-byte-swizzled K-major
+ * layout, rows beyond `rows` zero — which asvrl_c51_head consumes by bulk copy.  At least one of the two outputs.
+ * Same kernel, workspace and status word as asvrl_policy_forward. */
 ASVRL_API int asvrl_policy_hidden(const float* self_obs, const float* objects, const float* mask, const float* w_self,
                                   const float* b_self, const float* w_obj, const float* b_obj, const float* w1,
                                   const float* b1, const float* w2, const float* b2, long rows, int repack,
-                                  void* workspace, float* hidden, void* stream);
+                                  void* workspace, float* hidden /* nullable */, void* hidden_img /* nullable */,
+                                  void* stream);
 ASVRL_API int asvrl_policy_forward_status(int* status_out);
 
 /* K10 — the IQN critic's quantile trunk forward (ACIQN:410-426 calc_cos, ACIQN:453-480 the three dense layers with the
@@ -625,6 +629,21 @@ ASVRL_API int asvrl_critic_backward_status(int* status_out);
 ASVRL_API int asvrl_c51_greedy(const float* zv, const float* za, const float* bv, const float* ba, const float* support,
                                long rows, int n_actions, int atoms, int zv_ld, int za_actions_per_block, int za_ld,
                                long za_block_stride, int* action, float* q_out /* nullable */, void* stream);
+
+/* K13 — Rainbow's dueling C51 head for `rows` ASVs in ONE persistent tcgen05 launch (+ a weight-pack launch): the
+ * 128 -> n_actions * atoms advantage layer, the dueling combination q = v + a - mean_a(a) (Rainbow_model.py:127-135),
+ * softmax over the atoms, expectation over the support and the greedy action (agent.py:235-246), without the
+ * (rows, n_actions, atoms) product ever reaching HBM (accumulated in TMEM two actions at a time).
+ *   h_img: the advantage stream's second hidden layer as the operand image asvrl_policy_hidden writes (128-byte aligned);
+ *   zv [rows][zv_ld]: the value stream's output product WITHOUT bias (zv_ld >= 64, a multiple of 4; rows 16-byte aligned);
+ *   wa [n_actions * atoms][128], ba [n_actions * atoms], bv [atoms]: the (noisy) output layers' parameters; support [atoms];
+ *   workspace: asvrl_c51_head_workspace() bytes, 128-byte aligned; action [rows] int32; q_out [rows][n_actions] nullable.
+ *   n_actions <= 32, atoms <= 64, hidden width 128.  Bounded waits report through asvrl_c51_head_status. */
+ASVRL_API long asvrl_c51_head_workspace(void);
+ASVRL_API int asvrl_c51_head(const void* h_img, const float* zv, int zv_ld, const float* wa, const float* ba,
+                             const float* bv, const float* support, long rows, int n_actions, int atoms, void* workspace,
+                             int* action, float* q_out /* nullable */, void* stream);
+ASVRL_API int asvrl_c51_head_status(int* status_out);
 
 /* Rainbow's prioritised n-step memory: the batched append of one env step (the reference appends one transition per
  * call, rfarl/rfarl/policy/replay_memory_rainbow.py:125-131; here one row per ASV, lane = env * R + robot) in ONE

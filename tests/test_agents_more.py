@@ -173,11 +173,14 @@ def test_rainbow_memory_n_step_window():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("M", [3000, 5000])
-def test_rainbow_greedy_actions_match_probability_path(M):
+@pytest.mark.parametrize("M,head", [(3000, True), (5000, True), (5000, False), (65536 + 77, True)])
+def test_rainbow_greedy_actions_match_probability_path(M, head, monkeypatch):
     """asvrl_c51_greedy (dueling combination, softmax, expectation, argmax in one pass) against the module's own
     probability tensor in float64 (Rainbow:127-135, AGENT:235-246), noisy layers in training mode.  M = 5000 takes the
-    tensor-core path (the six noisy layers through K8, the advantage products in 5-action blocks)."""
+    tensor-core paths: K9's trunk per stream, then K13 (asvrl_c51_head: advantage layer + dueling C51 in one tcgen05
+    launch) or, with head = False, K8 blocks + asvrl_c51_greedy."""
+    from distributional_rl_decision_and_control_b200.policy import Rainbow_model
+    monkeypatch.setattr(Rainbow_model, "C51_HEAD", head)
     import copy
     dev = "cuda:0"
     pol = build("Rainbow", 7, dev)
@@ -188,6 +191,9 @@ def test_rainbow_greedy_actions_match_probability_path(M):
     x = (x[0], x[1] * x[2][..., None], x[2])
     support = torch.linspace(-10.0, 10.0, 51, device=dev)
     act, q = pol.greedy_actions(x, support, want_q=True)
+    torch.cuda.synchronize()
+    _lib.c51_head_status()
+    _lib.policy_forward_status()
     ref = copy.deepcopy(pol).double()
     ref.fused_tower = False
     ref.train()

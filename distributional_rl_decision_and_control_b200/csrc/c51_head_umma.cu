@@ -39,7 +39,9 @@ constexpr int CH_OFF_BAR = CH_OFF_WR + CH_WSTAGES * CH_CHUNK_B;
 constexpr int CH_NBAR = 2 + 2 * CH_WSTAGES + 2 * CH_DBUF;
 constexpr int CH_OFF_MISC = CH_OFF_BAR + CH_NBAR * 8;         // tmem slot, abort flag
 constexpr int CH_OFF_BEST = CH_OFF_MISC + 16;                 // [2][128] (value, index) of the odd warps
-constexpr int CH_SMEM_B = CH_OFF_BEST + 2 * CH_ROWS * 4 + 1024;
+constexpr int CH_OFF_TAB = CH_OFF_BEST + 2 * CH_ROWS * 4;     // tb | ba | support (CH_TAB_FLOATS floats, 16-byte aligned)
+constexpr int CH_SMEM_B = CH_OFF_TAB + CH_TAB_FLOATS * 4 + 1024;
+static_assert(CH_OFF_TAB % 16 == 0, "table alignment");
 static_assert(CH_SMEM_B <= 232448, "K13 shared memory");
 
 struct C51HeadArgs {
@@ -71,6 +73,7 @@ c51_head_pack_kernel(const float* __restrict__ wa, const float* __restrict__ ba,
     } else if (t < 64 + CH_MAX_A * 64) {            // ba padded to 64 columns per action
       const int a = (t - 64) >> 6, j = (t - 64) & 63;
       if (a < A && j < atoms) v = ba[a * atoms + j];
+      else if (j >= atoms) v = -INFINITY;   // padded atoms: logit -inf, weight exp(-inf) = 0 without a predicate
     } else {
       const int j = t - 64 - CH_MAX_A * 64;
       if (j < atoms) v = support[j];
@@ -107,44 +110,63 @@ c51_head_pack_kernel(const float* __restrict__ wa, const float* __restrict__ ba,
 
 static __device__ int ch_status_word = 0;
 
-// expected value of one action for the thread's row: logits x[j] = acc[j] / 64 + ba[j] + T[j], softmax over the atoms,
-// expectation over the support.  acc: the action's 64 TMEM columns.
-__device__ __forceinline__ float ch_action_value(uint32_t taddr, const float (&T)[64], const float4* __restrict__ ba4,
-                                                 const float4* __restrict__ sup4, int atoms) {
-  uint32_t v0[32], v1[32];
-  um_tmem_ld32(taddr, v0);
-  um_tmem_ld32(taddr + 32u, v1);
+// step -> unit of the image: 0 first, then 1 .. units - 1 rotated by `rot`
+__device__ __forceinline__ int ch_unit(int step, int units, int rot) {
+  if (step == 0) return 0;
+  int u = step + rot;
+  if (u >= units) u -= units - 1;
+  return u;
+}
+
+// One half (32 atoms) of an action for the thread's row: logits x[j] = acc[j] / 64 + ba[j] + T[j] (padded atoms carry
+// ba = -inf), their maximum, and sum exp(x - max), sum exp(x - max) support[j] with four independent accumulators.
+// The bias and support reads (shared memory, broadcast) are issued before the TMEM load is waited for.
+__device__ __forceinline__ void ch_half(uint32_t taddr, const float* T32, uint32_t ba_s, uint32_t sup_s, float& mx,
+                                        float& den, float& num) {
+  uint32_t v[32];
+  um_tmem_ld32(taddr, v);
+  uint4 b[8];
+#pragma unroll
+  for (int g = 0; g < 8; ++g) b[g] = um_lds128(ba_s + 16u * g);
   um_tmem_ld_wait();
-  float x[64];
-  float mx = -INFINITY;
+  float x[32];
 #pragma unroll
-  for (int g = 0; g < 16; ++g) {
-    const float4 b = __ldg(ba4 + g);
-    const float bb[4] = {b.x, b.y, b.z, b.w};
+  for (int g = 0; g < 8; ++g) {
+    const uint32_t bw[4] = {b[g].x, b[g].y, b[g].z, b[g].w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[4 * g + i] = fmaf(__uint_as_float(v[4 * g + i]), CH_WUNSCALE, __uint_as_float(bw[i])) + T32[4 * g + i];
+  }
+  float m4[4] = {x[0], x[1], x[2], x[3]};
+#pragma unroll
+  for (int j = 4; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], x[j]);
+  mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+  float d4[4] = {0.0f, 0.0f, 0.0f, 0.0f}, n4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  const float sh = -mx * 1.4426950408889634f;
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    const uint4 sv = um_lds128(sup_s + 16u * g);
+    const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const int j = 4 * g + i;
-      const float acc = __uint_as_float(j < 32 ? v0[j & 31] : v1[j & 31]);
-      x[j] = fmaf(acc, CH_WUNSCALE, bb[i]) + T[j];
-      if (j < atoms) mx = fmaxf(mx, x[j]);
+      const float e = exp2f(fmaf(x[4 * g + i], 1.4426950408889634f, sh));   // exp(x - mx)
+      d4[i] += e;
+      n4[i] = fmaf(e, __uint_as_float(sw[i]), n4[i]);
     }
   }
-  float den = 0.0f, num = 0.0f;
-#pragma unroll
-  for (int g = 0; g < 16; ++g) {
-    const float4 s = __ldg(sup4 + g);
-    const float ss[4] = {s.x, s.y, s.z, s.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int j = 4 * g + i;
-      if (j < atoms) {
-        const float e = __expf(x[j] - mx);
-        den += e;
-        num = fmaf(e, ss[i], num);
-      }
-    }
-  }
-  return num / den;
+  den = (d4[0] + d4[1]) + (d4[2] + d4[3]);
+  num = (n4[0] + n4[1]) + (n4[2] + n4[3]);
+}
+
+// expected value of one action: softmax over the atoms, expectation over the support (two halves, merged)
+__device__ __forceinline__ float ch_action_value(uint32_t taddr, const float (&T)[64], uint32_t ba_s, uint32_t sup_s, int atoms) {
+  float m0, d0, n0;
+  ch_half(taddr, T, ba_s, sup_s, m0, d0, n0);
+  if (atoms <= 32) return n0 / d0;
+  float m1, d1, n1;
+  ch_half(taddr + 32u, T + 32, ba_s + 128u, sup_s + 128u, m1, d1, n1);
+  const float mx = fmaxf(m0, m1);
+  const float f0 = __expf(m0 - mx), f1 = __expf(m1 - mx);
+  return fmaf(n0, f0, n1 * f1) / fmaf(d0, f0, d1 * f1);
 }
 
 __global__ void __launch_bounds__(CH_THREADS, 1)
@@ -173,10 +195,19 @@ c51_head_kernel(const C51HeadArgs a) {
     um_mbar_init_fence();
   }
   if (warp == 1) um_tmem_alloc<512>(um_smem(tmem_slot));
+  {
+    const float* tab = reinterpret_cast<const float*>(a.image + (size_t)a.units * 2 * CH_CHUNK_B);
+    float* tab_s = reinterpret_cast<float*>(base + CH_OFF_TAB);
+    for (int i2 = tid; i2 < CH_TAB_FLOATS; i2 += CH_THREADS) tab_s[i2] = __ldg(tab + i2);
+  }
   um_tc_before();
   __syncthreads();
   um_tc_after();
   const uint32_t tmem = *tmem_slot;
+  // Every CTA streams the whole weight image per tile.  After unit 0 (the mean, needed first) CTA b walks the other
+  // units from a different start, so that at any instant the 148 SMs read different lines of the image instead of
+  // all hammering the same L2 slices.
+  const int rot = a.units > 1 ? (int)(blockIdx.x % (unsigned)(a.units - 1)) : 0;
   const int n_my = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   auto wait = [&](uint32_t bar, uint32_t parity, int code) { (void)um_mbar_wait(bar, parity, abort_flag, a.status, code); };
 
@@ -194,7 +225,9 @@ c51_head_kernel(const C51HeadArgs a) {
           const int st = pos % CH_WSTAGES;
           if (pos >= CH_WSTAGES) wait(bar_w_empty(st), (uint32_t)((pos / CH_WSTAGES) - 1) & 1u, UM_TIMEOUT_RING);
           um_mbar_arrive_expect_tx(bar_w_full(st), CH_CHUNK_B);
-          um_bulk_g2s(sb + CH_OFF_WR + st * CH_CHUNK_B, a.image + (size_t)c * CH_CHUNK_B, CH_CHUNK_B, bar_w_full(st));
+          const int uu = ch_unit(c >> 1, a.units, rot);
+          um_bulk_g2s(sb + CH_OFF_WR + st * CH_CHUNK_B, a.image + (size_t)(2 * uu + (c & 1)) * CH_CHUNK_B, CH_CHUNK_B,
+                      bar_w_full(st));
         }
       }
     }
@@ -233,10 +266,8 @@ c51_head_kernel(const C51HeadArgs a) {
     // =============== epilogue: lane = row of TMEM quadrant q; the quadrant's two warps alternate units ===============
     const int q = warp & 3, e = (warp - 2) >> 2, r = 32 * q + lane;
     const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
-    const float* tab = reinterpret_cast<const float*>(a.image + (size_t)a.units * 2 * CH_CHUNK_B);
-    const float4* tb4 = reinterpret_cast<const float4*>(tab);
-    const float4* ba4 = reinterpret_cast<const float4*>(tab + 64);
-    const float4* sup4 = reinterpret_cast<const float4*>(tab + 64 + CH_MAX_A * 64);
+    const float4* tb4 = reinterpret_cast<const float4*>(base + CH_OFF_TAB);
+    const uint32_t ba_s = sb + CH_OFF_TAB + 64u * 4u, sup_s = ba_s + (uint32_t)(CH_MAX_A * 64 * 4);
     int gu = 0;
     for (int i = 0; i < n_my; ++i) {
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
@@ -251,6 +282,7 @@ c51_head_kernel(const C51HeadArgs a) {
         wait(bar_d_full(buf), (uint32_t)(gu / CH_DBUF) & 1u, UM_TIMEOUT_ACC);
         um_tc_after();
         const uint32_t t0 = lane_addr + (uint32_t)(buf * CH_UNIT_N);
+        const int uu = ch_unit(u, a.units, rot);
         if (u == 0) {
           // T[j] = z_v[j] + (b_v[j] - bbar[j]) - h_a . Wbar[j]
           uint32_t v0[32], v1[32];
@@ -260,7 +292,7 @@ c51_head_kernel(const C51HeadArgs a) {
 #pragma unroll
           for (int g = 0; g < 16; ++g) {
             const float4 z = 4 * g < a.atoms ? __ldg(z4 + g) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            const float4 b = __ldg(tb4 + g);
+            const float4 b = tb4[g];
             const float zz[4] = {z.x, z.y, z.z, z.w}, bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -270,18 +302,18 @@ c51_head_kernel(const C51HeadArgs a) {
             }
           }
           if (e == 0) {
-            const float ev = ch_action_value(t0 + 64u, T, ba4, sup4, a.atoms);
+            const float ev = ch_action_value(t0 + 64u, T, ba_s, sup_s, a.atoms);
             if (a.q_out && live) a.q_out[(size_t)m * a.A] = ev;
             best = ev; best_a = 0;
           }
         } else if ((u & 1) == e) {
 #pragma unroll 1
           for (int half = 0; half < 2; ++half) {
-            const int act = 2 * u - 1 + half;
+            const int act = 2 * uu - 1 + half;
             if (act < a.A) {
-              const float ev = ch_action_value(t0 + (uint32_t)(64 * half), T, ba4 + 16 * act, sup4, a.atoms);
+              const float ev = ch_action_value(t0 + (uint32_t)(64 * half), T, ba_s + (uint32_t)(256 * act), sup_s, a.atoms);
               if (a.q_out && live) a.q_out[(size_t)m * a.A + act] = ev;
-              if (ev > best) { best = ev; best_a = act; }   // ascending actions: the first maximum stays
+              if (ev > best || (ev == best && act < best_a)) { best = ev; best_a = act; }   // the first maximum
             }
           }
         }

@@ -9,7 +9,7 @@ rfarl/rfarl/envs/marinenav/env.py:33-54.
 import ctypes as C
 import math
 
-VERSION = 100
+VERSION = 200
 MAX_OBJ = 5
 SELF_DIM = 7
 OBJ_DIM = 5

@@ -38,7 +38,7 @@ extern "C" {
 #define ASVRL_API
 #endif
 
-#define ASVRL_VERSION 100 /* 0.1.0 */
+#define ASVRL_VERSION 200 /* 0.2.0: round 2 (K9 - K13, asvrl_c51_greedy layout arguments, static-scratch tower backward) */
 
 /* fixed by the network input shape ((1,7),(1,5,5),(1,5)): WAMV:14, AGENT:20-22 */
 #define ASVRL_MAX_OBJ 5

@@ -110,6 +110,16 @@ c51_head_pack_kernel(const float* __restrict__ wa, const float* __restrict__ ba,
 
 static __device__ int ch_status_word = 0;
 
+// -DCH_TRACE (debug builds, profiles/probes/k13_trace.py): CTA 0's timeline, [writer][event] = (clock << 8) | tag
+#ifdef CH_TRACE
+__device__ unsigned long long ch_trace_buf[4][512];
+__device__ int ch_trace_n[4];
+#define CH_TR(writer, tag) do { if (blockIdx.x == 0) { const int i_ = ch_trace_n[writer]; if (i_ < 512) { \
+    ch_trace_buf[writer][i_] = ((unsigned long long)clock64() << 8) | (unsigned)(tag); ch_trace_n[writer] = i_ + 1; } } } while (0)
+#else
+#define CH_TR(writer, tag) do { } while (0)
+#endif
+
 // step -> unit of the image: 0 first, then 1 .. units - 1 rotated by `rot`
 __device__ __forceinline__ int ch_unit(int step, int units, int rot) {
   if (step == 0) return 0;
@@ -229,12 +239,15 @@ c51_head_kernel(const C51HeadArgs a) {
           const int uu = ch_unit(c >> 1, a.units, rot);
           um_bulk_g2s(sb + CH_OFF_WR + st * CH_CHUNK_B, a.image + (size_t)(2 * uu + (c & 1)) * CH_CHUNK_B, CH_CHUNK_B,
                       bar_w_full(st));
+          CH_TR(0, c);
         }
       }
     }
   } else if (warp == 1) {
     // =============== MMA issuer ===============
-    if (lane == 0) {
+    // The warp stays converged and one elected lane issues: descriptors and addresses then live in uniform registers
+    // (with `if (lane == 0)` every operand of every tcgen05.mma costs an R2UR: 107 cycles per MMA against 68 of tensor work).
+    {
       constexpr uint32_t idesc = um_idesc_f16(CH_ROWS, CH_UNIT_N);
       int pos = 0, gu = 0;
       for (int i = 0; i < n_my; ++i) {
@@ -243,24 +256,31 @@ c51_head_kernel(const C51HeadArgs a) {
           const int buf = gu % CH_DBUF;
           if (gu >= CH_DBUF) wait(bar_d_empty(buf), (uint32_t)((gu / CH_DBUF) - 1) & 1u, UM_TIMEOUT_ACC);
           const uint32_t d_tmem = tmem + (uint32_t)(buf * CH_UNIT_N);
+          if (lane == 0) CH_TR(1, 2 * u);
+#pragma unroll 1
           for (int c = 0; c < 2; ++c, ++pos) {
             const int st = pos % CH_WSTAGES;
             wait(bar_w_full(st), (uint32_t)(pos / CH_WSTAGES) & 1u, UM_TIMEOUT_RING);
             um_tc_after();
             const uint32_t ah = sb + CH_OFF_A + (uint32_t)c * CH_CHUNK_B, al = ah + CH_TILE_B;
             const uint32_t wh = sb + CH_OFF_WR + (uint32_t)st * CH_CHUNK_B, wl = wh + CH_TILE_B;
+            if (um_elect()) {
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) {
-              const uint32_t o = ks * 32;
-              um_mma_f16(d_tmem, um_desc_sw128(al + o), um_desc_sw128(wh + o), idesc, (c == 0 && ks == 0) ? 0u : 1u);
-              um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wl + o), idesc, 1u);
-              um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wh + o), idesc, 1u);
+              for (int ks = 0; ks < 4; ++ks) {
+                const uint32_t o = ks * 32;
+                um_mma_f16(d_tmem, um_desc_sw128(al + o), um_desc_sw128(wh + o), idesc, (c == 0 && ks == 0) ? 0u : 1u);
+                um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wl + o), idesc, 1u);
+                um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wh + o), idesc, 1u);
+              }
+              um_commit(bar_w_empty(st));
+              if (c == 1) um_commit(bar_d_full(buf));
             }
-            um_commit(bar_w_empty(st));
+            __syncwarp();
           }
-          um_commit(bar_d_full(buf));
+          if (lane == 0) CH_TR(1, 2 * u + 1);
         }
-        um_commit(bar_a_free);
+        if (um_elect()) um_commit(bar_a_free);
+        __syncwarp();
       }
     }
   } else {
@@ -282,6 +302,7 @@ c51_head_kernel(const C51HeadArgs a) {
         const int buf = gu % CH_DBUF;
         wait(bar_d_full(buf), (uint32_t)(gu / CH_DBUF) & 1u, UM_TIMEOUT_ACC);
         um_tc_after();
+        if (lane == 0 && q == 2) CH_TR(2 + e, 2 * u);
         const uint32_t t0 = lane_addr + (uint32_t)(buf * CH_UNIT_N);
         const int uu = ch_unit(u, a.units, rot);
         if (u == 0) {
@@ -318,6 +339,7 @@ c51_head_kernel(const C51HeadArgs a) {
             }
           }
         }
+        if (lane == 0 && q == 2) CH_TR(2 + e, 2 * u + 1);
         um_tc_before();
         __syncwarp();
         if (lane == 0) um_mbar_arrive(bar_d_empty(buf));
@@ -398,3 +420,14 @@ extern "C" int asvrl_c51_head_status(int* status_out) {
   if (e != cudaSuccess) return fail((int)e, "asvrl_c51_head_status: %s", cudaGetErrorString(e));
   return 0;
 }
+
+#ifdef CH_TRACE
+extern "C" __attribute__((visibility("default"))) int asvrl_c51_head_trace(unsigned long long* events, int* counts) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(events, ch_trace_buf, sizeof(unsigned long long) * 4 * 512);
+  cudaMemcpyFromSymbol(counts, ch_trace_n, sizeof(int) * 4);
+  int zero[4] = {0, 0, 0, 0};
+  cudaMemcpyToSymbol(ch_trace_n, zero, sizeof zero);
+  return 0;
+}
+#endif

@@ -16,8 +16,9 @@
 //
 // Arithmetic: the fp16 two-piece split of K9 - K12 (x = hi + lo, three products, fp32 accumulation), weights pre-scaled
 // by 2^6.  The A operand (h_a) arrives as the operand image asvrl_policy_hidden writes: two 32 KB chunks per 128-row
-// tile, moved by bulk copy.  Structure: warp 0 = weight producer (4 x 32 KB ring, every tile streams the whole image
-// from L2), warp 1 = MMA issuer, warps 2 - 9 = epilogue (two per TMEM lane quadrant, alternating units).
+// tile, moved by bulk copy.  Structure: tiles are taken two at a time (slots) so that one pass over the weight image
+// (2 x 32 KB ring; the stream out of L2 is what bounds the kernel) serves both; warp 0 = producer, warps 1 and 10 = the
+// slots' MMA issuers, warps 2 - 5 / 6 - 9 = the slots' epilogue warps (one per TMEM lane quadrant, lane = row).
 #include "umma.cuh"
 
 namespace asvrl {
@@ -26,20 +27,20 @@ constexpr int CH_ROWS = 128, CH_K = 128, CH_UNIT_N = 128, CH_COLS = 64;   // row
 constexpr int CH_TILE_B = CH_ROWS * 128;          // 16 KB: 128 rows x 64 fp16
 constexpr int CH_CHUNK_B = 2 * CH_TILE_B;         // hi | lo
 constexpr int CH_MAX_A = 32, CH_MAX_UNITS = (CH_MAX_A + 2) / 2;
-constexpr int CH_WSTAGES = 4, CH_DBUF = 4;
-constexpr int CH_THREADS = 320;
+constexpr int CH_SLOTS = 2;                       // tiles that share one pass over the weight image
+constexpr int CH_WSTAGES = 2, CH_DBUF = 2;        // weight ring stages; TMEM buffers of CH_SLOTS x 128 columns
+constexpr int CH_THREADS = 352;   // producer, MMA issuer of slot 0, 8 epilogue warps, MMA issuer of slot 1
 constexpr float CH_WSCALE = 64.0f, CH_WUNSCALE = 1.0f / 64.0f;
 // workspace: weight image [units][2 k-chunks][32 KB] | tb [64] (b_v - bbar) | ba [A][64] | support [64]
 constexpr int CH_TAB_FLOATS = 64 + CH_MAX_A * 64 + 64;
 constexpr long CH_WS_B = (long)CH_MAX_UNITS * 2 * CH_CHUNK_B + CH_TAB_FLOATS * 4;
 // shared memory
-constexpr int CH_OFF_A = 0;                                   // 2 chunks
-constexpr int CH_OFF_WR = 2 * CH_CHUNK_B;                     // weight ring
+constexpr int CH_OFF_A = 0;                                   // per slot: 2 chunks
+constexpr int CH_OFF_WR = CH_SLOTS * 2 * CH_CHUNK_B;          // weight ring
 constexpr int CH_OFF_BAR = CH_OFF_WR + CH_WSTAGES * CH_CHUNK_B;
-constexpr int CH_NBAR = 2 + 2 * CH_WSTAGES + 2 * CH_DBUF;
+constexpr int CH_NBAR = 2 * CH_SLOTS + 2 * CH_WSTAGES + 2 * CH_DBUF * CH_SLOTS;
 constexpr int CH_OFF_MISC = CH_OFF_BAR + CH_NBAR * 8;         // tmem slot, abort flag
-constexpr int CH_OFF_BEST = CH_OFF_MISC + 16;                 // [2][128] (value, index) of the odd warps
-constexpr int CH_OFF_TAB = CH_OFF_BEST + 2 * CH_ROWS * 4;     // tb | ba | support (CH_TAB_FLOATS floats, 16-byte aligned)
+constexpr int CH_OFF_TAB = CH_OFF_MISC + 16;                  // tb | ba | support (CH_TAB_FLOATS floats, 16-byte aligned)
 constexpr int CH_SMEM_B = CH_OFF_TAB + CH_TAB_FLOATS * 4 + 1024;
 static_assert(CH_OFF_TAB % 16 == 0, "table alignment");
 static_assert(CH_SMEM_B <= 232448, "K13 shared memory");
@@ -114,6 +115,7 @@ static __device__ int ch_status_word = 0;
 #ifdef CH_TRACE
 __device__ unsigned long long ch_trace_buf[4][512];
 __device__ int ch_trace_n[4];
+__device__ unsigned long long ch_cta_ns[256][2];   // globaltimer at the start / end of every CTA
 #define CH_TR(writer, tag) do { if (blockIdx.x == 0) { const int i_ = ch_trace_n[writer]; if (i_ < 512) { \
     ch_trace_buf[writer][i_] = ((unsigned long long)clock64() << 8) | (unsigned)(tag); ch_trace_n[writer] = i_ + 1; } } } while (0)
 #else
@@ -187,21 +189,23 @@ c51_head_kernel(const C51HeadArgs a) {
   const uint32_t sb = um_smem(base);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t bar0 = sb + CH_OFF_BAR;
-  const uint32_t bar_a_full = bar0, bar_a_free = bar0 + 8u;
-  auto bar_w_full = [&](int st) { return bar0 + 8u * (2 + st); };
-  auto bar_w_empty = [&](int st) { return bar0 + 8u * (2 + CH_WSTAGES + st); };
-  auto bar_d_full = [&](int b) { return bar0 + 8u * (2 + 2 * CH_WSTAGES + b); };
-  auto bar_d_empty = [&](int b) { return bar0 + 8u * (2 + 2 * CH_WSTAGES + CH_DBUF + b); };
+  auto bar_a_full = [&](int sl) { return bar0 + 8u * sl; };
+  auto bar_a_free = [&](int sl) { return bar0 + 8u * (CH_SLOTS + sl); };
+  auto bar_w_full = [&](int st) { return bar0 + 8u * (2 * CH_SLOTS + st); };
+  auto bar_w_empty = [&](int st) { return bar0 + 8u * (2 * CH_SLOTS + CH_WSTAGES + st); };
+  auto bar_d_full = [&](int b, int sl) { return bar0 + 8u * (2 * CH_SLOTS + 2 * CH_WSTAGES + CH_SLOTS * b + sl); };
+  auto bar_d_empty = [&](int b, int sl) { return bar0 + 8u * (2 * CH_SLOTS + 2 * CH_WSTAGES + CH_SLOTS * (CH_DBUF + b) + sl); };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(base + CH_OFF_MISC);
   volatile uint32_t* abort_flag = reinterpret_cast<volatile uint32_t*>(base + CH_OFF_MISC + 4);
-  float* s_best = reinterpret_cast<float*>(base + CH_OFF_BEST);
-  int* s_idx = reinterpret_cast<int*>(base + CH_OFF_BEST + CH_ROWS * 4);
 
+#ifdef CH_TRACE
+  if (tid == 0 && blockIdx.x < 256) ch_cta_ns[blockIdx.x][0] = um_globaltimer();
+#endif
   if (tid == 0) {
-    um_mbar_init(bar_a_full, 1);
-    um_mbar_init(bar_a_free, 1);
-    for (int st = 0; st < CH_WSTAGES; ++st) { um_mbar_init(bar_w_full(st), 1); um_mbar_init(bar_w_empty(st), 1); }
-    for (int b = 0; b < CH_DBUF; ++b) { um_mbar_init(bar_d_full(b), 1); um_mbar_init(bar_d_empty(b), 8); }
+    for (int sl = 0; sl < CH_SLOTS; ++sl) { um_mbar_init(bar_a_full(sl), 1); um_mbar_init(bar_a_free(sl), 1); }
+    for (int st = 0; st < CH_WSTAGES; ++st) { um_mbar_init(bar_w_full(st), 1); um_mbar_init(bar_w_empty(st), CH_SLOTS); }
+    for (int b = 0; b < CH_DBUF; ++b)
+      for (int sl = 0; sl < CH_SLOTS; ++sl) { um_mbar_init(bar_d_full(b, sl), 1); um_mbar_init(bar_d_empty(b, sl), 4); }
     *abort_flag = 0u;
     um_mbar_init_fence();
   }
@@ -222,16 +226,25 @@ c51_head_kernel(const C51HeadArgs a) {
   const int n_my = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   auto wait = [&](uint32_t bar, uint32_t parity, int code) { (void)um_mbar_wait(bar, parity, abort_flag, a.status, code); };
 
+  // Tiles are taken two at a time ("slots"): every weight stage serves both tiles' MMAs, which halves the weight stream
+  // out of L2 — the stream, at ~41 GB/s per SM with all SMs pulling the same image, is what bounds this kernel
+  // (profiles/probes/k13_trace.py), not the tensor pipe and not the epilogue.
+  const int n_pairs = (n_my + CH_SLOTS - 1) / CH_SLOTS;
   if (warp == 0) {
-    // =============== producer: the tile's A image, then every weight chunk through the ring ===============
+    // =============== producer: the pair's A images, then every weight chunk through the ring ===============
     if (lane == 0) {
       int pos = 0;
-      for (int i = 0; i < n_my; ++i) {
-        const int tile = (int)blockIdx.x + i * (int)gridDim.x;
-        if (i > 0) wait(bar_a_free, (uint32_t)(i - 1) & 1u, UM_TIMEOUT_INPUT);
-        um_mbar_arrive_expect_tx(bar_a_full, 2 * CH_CHUNK_B);
-        um_bulk_g2s(sb + CH_OFF_A, a.h_img + (size_t)tile * 2 * CH_CHUNK_B, CH_CHUNK_B, bar_a_full);
-        um_bulk_g2s(sb + CH_OFF_A + CH_CHUNK_B, a.h_img + ((size_t)tile * 2 + 1) * CH_CHUNK_B, CH_CHUNK_B, bar_a_full);
+      for (int p = 0; p < n_pairs; ++p) {
+        for (int sl = 0; sl < CH_SLOTS; ++sl) {
+          const int i = CH_SLOTS * p + sl;
+          if (i >= n_my) break;
+          const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+          if (p > 0) wait(bar_a_free(sl), (uint32_t)(p - 1) & 1u, UM_TIMEOUT_INPUT);
+          const uint32_t dst = sb + CH_OFF_A + (uint32_t)sl * 2 * CH_CHUNK_B;
+          um_mbar_arrive_expect_tx(bar_a_full(sl), 2 * CH_CHUNK_B);
+          um_bulk_g2s(dst, a.h_img + (size_t)tile * 2 * CH_CHUNK_B, CH_CHUNK_B, bar_a_full(sl));
+          um_bulk_g2s(dst + CH_CHUNK_B, a.h_img + ((size_t)tile * 2 + 1) * CH_CHUNK_B, CH_CHUNK_B, bar_a_full(sl));
+        }
         for (int c = 0; c < 2 * a.units; ++c, ++pos) {
           const int st = pos % CH_WSTAGES;
           if (pos >= CH_WSTAGES) wait(bar_w_empty(st), (uint32_t)((pos / CH_WSTAGES) - 1) & 1u, UM_TIMEOUT_RING);
@@ -243,123 +256,122 @@ c51_head_kernel(const C51HeadArgs a) {
         }
       }
     }
-  } else if (warp == 1) {
-    // =============== MMA issuer ===============
-    // The warp stays converged and one elected lane issues: descriptors and addresses then live in uniform registers
-    // (with `if (lane == 0)` every operand of every tcgen05.mma costs an R2UR: 107 cycles per MMA against 68 of tensor work).
+  } else if (warp == 1 || warp == 10) {
+    // =============== MMA issuers, one per tile slot ===============
+    // A tcgen05.mma costs its issuing thread ~100 cycles whatever its shape (68 cycles of tensor work at N = 128), so
+    // each slot has its own issuer; the warp stays converged and one elected lane issues (uniform registers).  Both
+    // issuers walk every weight stage; the stage is free when both have committed (or, for an idle slot, arrived).
     {
+      const int sl = warp == 1 ? 0 : 1;
       constexpr uint32_t idesc = um_idesc_f16(CH_ROWS, CH_UNIT_N);
       int pos = 0, gu = 0;
-      for (int i = 0; i < n_my; ++i) {
-        wait(bar_a_full, (uint32_t)i & 1u, UM_TIMEOUT_INPUT);
-        for (int u = 0; u < a.units; ++u, ++gu) {
+      for (int p = 0; p < n_pairs; ++p) {
+        const bool active = CH_SLOTS * p + sl < n_my;
+        if (active) wait(bar_a_full(sl), (uint32_t)p & 1u, UM_TIMEOUT_INPUT);
+        for (int u = 0; u < a.units; ++u) {
           const int buf = gu % CH_DBUF;
-          if (gu >= CH_DBUF) wait(bar_d_empty(buf), (uint32_t)((gu / CH_DBUF) - 1) & 1u, UM_TIMEOUT_ACC);
-          const uint32_t d_tmem = tmem + (uint32_t)(buf * CH_UNIT_N);
-          if (lane == 0) CH_TR(1, 2 * u);
+          if (active && gu >= CH_DBUF) wait(bar_d_empty(buf, sl), (uint32_t)((gu / CH_DBUF) - 1) & 1u, UM_TIMEOUT_ACC);
+          if (lane == 0 && sl == 0) CH_TR(1, 2 * u);
+          const uint32_t d_tmem = tmem + (uint32_t)(buf * CH_SLOTS * CH_UNIT_N + sl * CH_UNIT_N);
 #pragma unroll 1
           for (int c = 0; c < 2; ++c, ++pos) {
             const int st = pos % CH_WSTAGES;
             wait(bar_w_full(st), (uint32_t)(pos / CH_WSTAGES) & 1u, UM_TIMEOUT_RING);
             um_tc_after();
-            const uint32_t ah = sb + CH_OFF_A + (uint32_t)c * CH_CHUNK_B, al = ah + CH_TILE_B;
             const uint32_t wh = sb + CH_OFF_WR + (uint32_t)st * CH_CHUNK_B, wl = wh + CH_TILE_B;
+            const uint32_t ah = sb + CH_OFF_A + (uint32_t)(sl * 2 + c) * CH_CHUNK_B, al = ah + CH_TILE_B;
             if (um_elect()) {
+              if (active) {
 #pragma unroll
-              for (int ks = 0; ks < 4; ++ks) {
-                const uint32_t o = ks * 32;
-                um_mma_f16(d_tmem, um_desc_sw128(al + o), um_desc_sw128(wh + o), idesc, (c == 0 && ks == 0) ? 0u : 1u);
-                um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wl + o), idesc, 1u);
-                um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wh + o), idesc, 1u);
+                for (int ks = 0; ks < 4; ++ks) {
+                  const uint32_t o = ks * 32;
+                  um_mma_f16(d_tmem, um_desc_sw128(al + o), um_desc_sw128(wh + o), idesc, (c == 0 && ks == 0) ? 0u : 1u);
+                  um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wl + o), idesc, 1u);
+                  um_mma_f16(d_tmem, um_desc_sw128(ah + o), um_desc_sw128(wh + o), idesc, 1u);
+                }
+                um_commit(bar_w_empty(st));
+                if (c == 1) um_commit(bar_d_full(buf, sl));
+              } else {
+                um_mbar_arrive(bar_w_empty(st));
               }
-              um_commit(bar_w_empty(st));
-              if (c == 1) um_commit(bar_d_full(buf));
             }
             __syncwarp();
           }
-          if (lane == 0) CH_TR(1, 2 * u + 1);
+          if (lane == 0 && sl == 0) CH_TR(1, 2 * u + 1);
+          if (active) ++gu;
         }
-        if (um_elect()) um_commit(bar_a_free);
+        if (active && um_elect()) um_commit(bar_a_free(sl));
         __syncwarp();
       }
     }
   } else {
-    // =============== epilogue: lane = row of TMEM quadrant q; the quadrant's two warps alternate units ===============
-    const int q = warp & 3, e = (warp - 2) >> 2, r = 32 * q + lane;
-    const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16);
+    // =============== epilogue: lane = row of TMEM quadrant q of tile slot sl; every unit of its tile ===============
+    const int q = warp & 3, sl = (warp - 2) >> 2, r = 32 * q + lane;
+    const uint32_t lane_addr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(sl * CH_UNIT_N);
     const float4* tb4 = reinterpret_cast<const float4*>(base + CH_OFF_TAB);
     const uint32_t ba_s = sb + CH_OFF_TAB + 64u * 4u, sup_s = ba_s + (uint32_t)(CH_MAX_A * 64 * 4);
     int gu = 0;
-    for (int i = 0; i < n_my; ++i) {
+    for (int p = 0; p < n_pairs; ++p) {
+      const int i = CH_SLOTS * p + sl;
+      const bool have = i < n_my;   // the last pair may hold one tile only
+      if (!have) break;
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
       const long m = (long)tile * CH_ROWS + r;
-      const bool live = m < (long)a.rows;
+      const bool live = have && m < (long)a.rows;
       const float4* z4 = reinterpret_cast<const float4*>(a.zv + (size_t)(live ? m : 0) * a.zv_ld);
       float T[64];
       float best = -INFINITY;
-      int best_a = 0;
+      int best_a = 0x7fffffff;
       for (int u = 0; u < a.units; ++u, ++gu) {
         const int buf = gu % CH_DBUF;
-        wait(bar_d_full(buf), (uint32_t)(gu / CH_DBUF) & 1u, UM_TIMEOUT_ACC);
+        wait(bar_d_full(buf, sl), (uint32_t)(gu / CH_DBUF) & 1u, UM_TIMEOUT_ACC);
         um_tc_after();
-        if (lane == 0 && q == 2) CH_TR(2 + e, 2 * u);
-        const uint32_t t0 = lane_addr + (uint32_t)(buf * CH_UNIT_N);
+        if (lane == 0 && q == 2) CH_TR(2 + sl, 2 * u);
+        const uint32_t t0 = lane_addr + (uint32_t)(buf * CH_SLOTS * CH_UNIT_N);
         const int uu = ch_unit(u, a.units, rot);
-        if (u == 0) {
-          // T[j] = z_v[j] + (b_v[j] - bbar[j]) - h_a . Wbar[j]
-          uint32_t v0[32], v1[32];
-          um_tmem_ld32(t0, v0);
-          um_tmem_ld32(t0 + 32u, v1);
-          um_tmem_ld_wait();
+        if (have) {
+          if (u == 0) {
+            // T[j] = z_v[j] + (b_v[j] - bbar[j]) - h_a . Wbar[j]
+            uint32_t v0[32], v1[32];
+            um_tmem_ld32(t0, v0);
+            um_tmem_ld32(t0 + 32u, v1);
+            um_tmem_ld_wait();
 #pragma unroll
-          for (int g = 0; g < 16; ++g) {
-            const float4 z = 4 * g < a.atoms ? __ldg(z4 + g) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            const float4 b = tb4[g];
-            const float zz[4] = {z.x, z.y, z.z, z.w}, bb[4] = {b.x, b.y, b.z, b.w};
+            for (int g = 0; g < 16; ++g) {
+              const float4 z = 4 * g < a.atoms ? __ldg(z4 + g) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+              const float4 b = tb4[g];
+              const float zz[4] = {z.x, z.y, z.z, z.w}, bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const int j = 4 * g + k;
-              const float acc = __uint_as_float(j < 32 ? v0[j & 31] : v1[j & 31]);
-              T[j] = (zz[k] + bb[k]) - acc * CH_WUNSCALE;
+              for (int k = 0; k < 4; ++k) {
+                const int j = 4 * g + k;
+                const float acc = __uint_as_float(j < 32 ? v0[j & 31] : v1[j & 31]);
+                T[j] = (zz[k] + bb[k]) - acc * CH_WUNSCALE;
+              }
             }
           }
-          if (e == 0) {
-            const float ev = ch_action_value(t0 + 64u, T, ba_s, sup_s, a.atoms);
-            if (a.q_out && live) a.q_out[(size_t)m * a.A] = ev;
-            best = ev; best_a = 0;
-          }
-        } else if ((u & 1) == e) {
 #pragma unroll 1
           for (int half = 0; half < 2; ++half) {
-            const int act = 2 * uu - 1 + half;
-            if (act < a.A) {
+            const int act = 2 * uu - 1 + half;   // unit 0: [mean | action 0]
+            if (act >= 0 && act < a.A) {
               const float ev = ch_action_value(t0 + (uint32_t)(64 * half), T, ba_s + (uint32_t)(256 * act), sup_s, a.atoms);
               if (a.q_out && live) a.q_out[(size_t)m * a.A + act] = ev;
-              if (ev > best || (ev == best && act < best_a)) { best = ev; best_a = act; }   // the first maximum
+              if (ev > best || (ev == best && act < best_a)) { best = ev; best_a = act; }   // the first maximum, as torch.argmax
             }
           }
         }
-        if (lane == 0 && q == 2) CH_TR(2 + e, 2 * u + 1);
+        if (lane == 0 && q == 2) CH_TR(2 + sl, 2 * u + 1);
         um_tc_before();
         __syncwarp();
-        if (lane == 0) um_mbar_arrive(bar_d_empty(buf));
+        if (lane == 0) um_mbar_arrive(bar_d_empty(buf, sl));
       }
-      // the quadrant's two warps: first maximum over all actions, as torch.argmax
-      if (e == 1) { s_best[r] = best; s_idx[r] = best_a; }
-      um_bar_sync(1 + q, 64);
-      if (e == 0) {
-        const float ob = s_best[r];
-        const int oa = s_idx[r];
-        // warp e = 1 never sees action 0; an action it holds wins only with a strictly larger value or an equal value
-        // and a smaller index
-        if (ob > best || (ob == best && oa < best_a)) best_a = oa;
-        if (live) a.action[m] = best_a;
-      }
-      um_bar_sync(1 + q, 64);
+      if (live) a.action[m] = best_a == 0x7fffffff ? 0 : best_a;
     }
   }
   um_tc_before();
   __syncthreads();
+#ifdef CH_TRACE
+  if (tid == 0 && blockIdx.x < 256) ch_cta_ns[blockIdx.x][1] = um_globaltimer();
+#endif
   if (warp == 1) {
     um_tc_after();
     um_tmem_free<512>(tmem);
@@ -422,6 +434,10 @@ extern "C" int asvrl_c51_head_status(int* status_out) {
 }
 
 #ifdef CH_TRACE
+extern "C" __attribute__((visibility("default"))) int asvrl_c51_head_cta_times(unsigned long long* ns) {
+  cudaDeviceSynchronize();
+  return (int)cudaMemcpyFromSymbol(ns, ch_cta_ns, sizeof(unsigned long long) * 256 * 2);
+}
 extern "C" __attribute__((visibility("default"))) int asvrl_c51_head_trace(unsigned long long* events, int* counts) {
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(events, ch_trace_buf, sizeof(unsigned long long) * 4 * 512);

@@ -38,3 +38,14 @@ for w in range(4):
     print("  " + "  ".join(f"{t}:{tag}" for t, tag in seq[:60 if w else 28]))
     if n:
         print(f"  last event at {seq[-1][0]} cycles = {seq[-1][0] / 1965:.1f} us")
+
+ns = np.zeros((256, 2), dtype=np.uint64)
+so.asvrl_c51_head_cta_times(ns.ctypes.data_as(C.c_void_p))
+ns = ns[:148].astype(np.int64)
+k0 = ns[:, 0].min()
+start, end = (ns[:, 0] - k0) / 1e3, (ns[:, 1] - k0) / 1e3
+print(f"--- per CTA (us from the first CTA's start): start min {start.min():.1f} max {start.max():.1f}; end min {end.min():.1f} "
+      f"median {np.median(end):.1f} max {end.max():.1f}; duration min {(end - start).min():.1f} max {(end - start).max():.1f}")
+order = np.argsort(end)
+print("  slowest CTAs:", [(int(i), round(float(start[i]), 1), round(float(end[i]), 1)) for i in order[-6:]])
+print("  fastest CTAs:", [(int(i), round(float(start[i]), 1), round(float(end[i]), 1)) for i in order[:6]])

@@ -272,9 +272,10 @@ class Agent():
             return actions
         explore = torch.rand((M,), device=self.device) < eps
         if self.agent_type in ("AC-IQN", "DDPG", "SAC"):
-            greedy = self.policy_local.actor(obs)
             if self.agent_type == "SAC":
-                greedy = greedy[0]
+                greedy = self.policy_local.actor.act(obs)   # the sampled action without the log-probability terms
+            else:
+                greedy = self.policy_local.actor(obs)
             if not hasattr(self, "_act_lo"):
                 self._act_lo = torch.tensor([r[0] for r in self.value_ranges_of_action], device=self.device)
                 self._act_hi = torch.tensor([r[1] for r in self.value_ranges_of_action], device=self.device)

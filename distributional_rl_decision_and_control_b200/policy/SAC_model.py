@@ -49,6 +49,20 @@ class Actor(_ObservationTower):
         log_std = torch.clamp(self.output_layer_log_std(h), self.min_log_std, self.max_log_std)
         return self.compute_action(mu, log_std, noise)
 
+    @torch.no_grad()
+    def act(self, x, noise=None):
+        """Collection: the sampled, squashed action of ``forward`` only (same draw, same arithmetic) — both heads as ONE
+        128 -> 4 product and none of the log-probability terms, which acting never reads (AGENT: act of the SAC agent
+        uses actions only)."""
+        h = self._trunk(x, self.hidden_layer, self.hidden_layer_2)
+        w = torch.cat((self.output_layer_mu.weight, self.output_layer_log_std.weight), dim=0)
+        b = torch.cat((self.output_layer_mu.bias, self.output_layer_log_std.bias), dim=0)
+        y = F.linear(h, w, b)
+        d = self.action_dimension
+        mu, log_std = y[:, :d], torch.clamp(y[:, d:], self.min_log_std, self.max_log_std)
+        eps = torch.randn_like(mu) if noise is None else noise
+        return self.atan_scale * torch.atan(mu + torch.exp(log_std) * eps)
+
     def compute_action(self, mu, log_std, noise=None):
         sigma = torch.exp(log_std)
         eps = torch.randn_like(mu) if noise is None else noise

@@ -263,3 +263,20 @@ def test_rainbow_batched_append_kernel_matches_torch_statements():
     for name in ("rows", "tstep", "prio", "lane_t", "count", "head_dev", "filled_dev"):
         assert torch.equal(getattr(a, name), getattr(b, name)), name
     assert a.head == b.head and a.filled == b.filled and int(a._append_scratch.abs().sum()) == 0
+
+
+@pytest.mark.gpu
+def test_sac_act_equals_forward_actions():
+    """Actor.act (one 128 -> 4 product, no log-probability terms) returns the actions of Actor.forward for the same draw."""
+    dev = "cuda:0"
+    actor = build("SAC", 13, dev).actor
+    g = torch.Generator(device=dev).manual_seed(8)
+    for M in (300, 5000):
+        x = (torch.randn((M, 7), device=dev, generator=g) * 5, torch.randn((M, 5, 5), device=dev, generator=g) * 3,
+             (torch.rand((M, 5), device=dev, generator=g) < 0.6).float())
+        x = (x[0], x[1] * x[2][..., None], x[2])
+        z = torch.randn((M, 2), device=dev, generator=g)
+        with torch.no_grad():
+            want = actor(x, noise=z)[0]
+        got = actor.act(x, noise=z)
+        assert float((got - want).abs().max()) <= 2e-6

@@ -279,4 +279,4 @@ def test_sac_act_equals_forward_actions():
         with torch.no_grad():
             want = actor(x, noise=z)[0]
         got = actor.act(x, noise=z)
-        assert float((got - want).abs().max()) <= 2e-6
+        assert float((got - want).abs().max()) <= 1e-5   # two cuBLAS products of different shapes: summation order only
